@@ -1,0 +1,157 @@
+/*
+ * sphb.h — C ABI of the B200-native back-end for the SPH hot path.
+ *
+ * The reference (alxvth/SPH @ 8d54e737) has no FFI: its hot path is a set of
+ * C++ free functions in namespace sph::utils that call faiss / HDILib / Eigen
+ * on host containers.  This header is the seam a maintainer binds instead
+ * (INTEGRATION.md shows the shim for every entry point).  Every function cites
+ * the reference interface it replaces.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; the caller owns every buffer;
+ *   - entry points without a suffix take HOST pointers (pageable or pinned) and
+ *     do their own H2D / D2H copies; `_dev` variants take DEVICE pointers and a
+ *     cudaStream_t (passed as void*) and never touch the host — they are what a
+ *     pipeline that keeps data resident in HBM calls;
+ *   - return 0 on success, non-zero on error; sphb_last_error() gives the text.
+ *     The reference's convention is "log + early return, outputs untouched"
+ *     (sph/LevelSimilarities.cpp:123-142); the shim maps non-zero to that;
+ *   - there is NO CPU fallback: without a CUDA device every call fails with
+ *     SPHB_ERR_NO_DEVICE;
+ *   - single caller at a time per process (the reference facade is sequential,
+ *     sph/ComputeHierarchy.cpp:262-276).
+ *   - sparse matrices cross the boundary as CSR: int64 rowptr[n+1],
+ *     uint32 col[nnz] (column-sorted within a row), float val[nnz] — the flat
+ *     form of SparseMatSPH / SparseMatHDI (sph/utils/CommonDefinitions.hpp:87-93).
+ */
+#ifndef SPHB_H
+#define SPHB_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SPHB_API __attribute__((visibility("default")))
+#else
+#define SPHB_API
+#endif
+
+enum {
+    SPHB_OK = 0,
+    SPHB_ERR_NO_DEVICE = 1,
+    SPHB_ERR_INVALID = 2,
+    SPHB_ERR_CUDA = 3,
+    SPHB_ERR_CAPACITY = 4,
+    SPHB_ERR_UNSUPPORTED = 5
+};
+
+/* faiss::MetricType values used at the reference call sites
+ * (sph/NearestNeighbors.cpp:81-96): METRIC_INNER_PRODUCT = 0, METRIC_L2 = 1. */
+enum { SPHB_METRIC_INNER_PRODUCT = 0, SPHB_METRIC_L2 = 1 };
+
+/* sph::utils::ImportanceWeighting (sph/utils/Settings.hpp, used at
+ * sph/utils/SparseMatrixAlgorithms.cpp:137-161). */
+enum { SPHB_W_CONSTANT = 0, SPHB_W_LINEAR = 1, SPHB_W_NORMAL = 2, SPHB_W_ONLYLAST = 3, SPHB_W_FIRST_VISIT = 4 };
+
+/* ---- lifetime ---------------------------------------------------------- */
+SPHB_API int sphb_init(int device);          /* selects the device, creates the stream; idempotent */
+SPHB_API void sphb_shutdown(void);           /* releases device scratch */
+SPHB_API const char* sphb_last_error(void);
+SPHB_API int sphb_version(void);
+/* number of kernels this library has launched since sphb_init / the last reset */
+SPHB_API int64_t sphb_launch_count(void);
+SPHB_API void sphb_reset_launch_count(void);
+/* the stream all host-pointer entry points run on (cudaStream_t) */
+SPHB_API void* sphb_stream(void);
+
+/* ---- Stage A: exact kNN graph ------------------------------------------ */
+/*
+ * Replaces utils::computeButeForce / utils::computeIndexFlat
+ *   (sph/utils/Knn.hpp:10-11, sph/utils/Knn.cpp:56-136)
+ * fused with the post-passes NearestNeighbors::compute applies right after
+ *   (sph/NearestNeighbors.cpp:152-167: ensureFloatingPointIntegrity :233-242,
+ *    squareRootOfAllDistances :224-231, ensureClosestPointIsSelf
+ *    sph/utils/GraphUtils.cpp:23-95).
+ * x: n*d float32 point-major.  ids/dist: n*k, caller-owned (the reference
+ * pre-fills -1 / -1.0f, sph/NearestNeighbors.cpp:113-118; slots that cannot be
+ * filled because n < k keep that value).  Row p is ordered by (distance, index),
+ * distances are the fp64-accumulated squared L2 rounded once to fp32, then
+ * `<= FLT_EPSILON -> 0`, then sqrt unless l2_squared, then self moved first.
+ */
+SPHB_API int sphb_knn_exact(const float* x, int64_t n, int d, int k, int metric, int l2_squared,
+                            int64_t* ids, float* dist);
+/* Same for query rows [q0, q1) against the full database (multi-GPU shard):
+ * ids/dist are (q1-q0)*k. */
+SPHB_API int sphb_knn_exact_slab(const float* x, int64_t n, int d, int k, int metric, int l2_squared,
+                                 int64_t q0, int64_t q1, int64_t* ids, float* dist);
+SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared,
+                                int64_t q0, int64_t q1, int64_t* d_ids, float* d_dist, void* stream);
+/* kNN statistics of the last call: [0] tensor-core path used (0/1), [1] candidate
+ * compactions, [2] candidates accepted by the filter, [3] Kp (GEMM K extent),
+ * [4] database tiles per query tile, [5] query tiles. */
+SPHB_API int sphb_knn_last_stats(int64_t* out6);
+
+/* ---- Stage B: perplexity-calibrated probability rows -------------------- */
+/*
+ * Replaces utils::computeGaussianDistributions(const GraphBaseInterface&, vector<T>&, float)
+ *   (sph/utils/GraphNormalization.hpp:16-21, .cpp:191-338) on a fixed-k graph whose
+ * first neighbour is the point itself.  perplexity <= 0 means (k-1)/3.
+ * cols/vals: n*(k-1), each row column-sorted (MapMemEff / SparseVector order).
+ * sigma (optional, may be NULL): n doubles.
+ */
+SPHB_API int sphb_prow_gaussian_graph(const int64_t* ids, const float* dist, int64_t n, int k, float perplexity,
+                                      uint32_t* cols, float* vals, double* sigma);
+SPHB_API int sphb_prow_gaussian_graph_dev(const int64_t* d_ids, const float* d_dist, int64_t n, int k, float perplexity,
+                                          uint32_t* d_cols, float* d_vals, double* d_sigma, void* stream);
+/* utils::computeLinearDistributions (sph/utils/GraphNormalization.cpp:340-411). */
+SPHB_API int sphb_prow_linear_graph(const int64_t* ids, const float* dist, int64_t n, int k,
+                                    uint32_t* cols, float* vals);
+/* utils::computeGaussianDistributions(vector<T>&, float, int) in place on sparse rows
+ *   (sph/utils/GraphNormalization.cpp:38-189); ignore = -1 on level >= 1. */
+SPHB_API int sphb_prow_gaussian_inplace(int64_t n, const int64_t* rowptr, float* val, float perplexity, int ignore);
+/* utils::computeGaussianDistributions(dist², idx, nn, rows, params) flat variant
+ *   (sph/utils/HDILibHelper.hpp:112-140; tol 1e-5): fills temp[n*k]; the caller scatters. */
+SPHB_API int sphb_prow_gaussian_flat(const float* dist, int64_t n, int k, double perplexity, float* temp);
+/* utils::symmetrizeTSNE / symmetrizeUMAP (sph/utils/HDILibHelper.hpp:260-302).
+ * out_* capacity `cap` entries (2*nnz always suffices); *out_nnz receives the size. */
+SPHB_API int sphb_symmetrize(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int umap,
+                             int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t cap, int64_t* out_nnz);
+
+/* ---- Stage C: random walks --------------------------------------------- */
+/*
+ * Replaces utils::doRandomWalks (sph/utils/SparseMatrixAlgorithms.hpp:73, .cpp:34-290).
+ * Counter-based RNG (Philox4x32-10 keyed by seed, start point, walk, step): the
+ * result is independent of thread layout; parity with the reference's
+ * mt19937_64 streams is statistical.
+ */
+SPHB_API int sphb_random_walks(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                               uint64_t num_walks, uint64_t walk_len, int weighting, float prune_value, uint64_t prune_steps,
+                               uint64_t seed, int remove_diagonal, int normalize,
+                               int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t cap, int64_t* out_nnz);
+/* utils::mergeNodesRandomWalks (sph/utils/SparseMatrixAlgorithms.hpp:82, .cpp:292-352). */
+SPHB_API int sphb_rw_merge(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                           const uint64_t* parents, int64_t n_merged, int norm, int weight_by_size,
+                           int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t cap, int64_t* out_nnz);
+
+/* ---- Stage D: level similarities ---------------------------------------- */
+/*
+ * Replaces utils::createSimilarities (sph/utils/SparseMatrixAlgorithms.hpp:121, .cpp:963-1378):
+ * -log(sqrt(A)·sqrt(A)ᵀ), pruned, per-row bottom-k by (value, column), column-sorted,
+ * L1-normalised.  variant: 0 auto (n > 5000 -> HDI path), 1 HDI, 2 Eigen.
+ * comp_sizes may be NULL.  out: fixed stride k, cols padded 0xFFFFFFFF, row_nnz[n].
+ */
+SPHB_API int sphb_create_similarities(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                                      int64_t k, float prune_val, int variant, const int64_t* comp_sizes,
+                                      uint32_t* out_cols, float* out_vals, int32_t* row_nnz);
+/* Batched utils::randomWalksBhattacharyya (mode 0) / single overlap (mode 1)
+ *   (sph/utils/Similarities.cpp:374-396) over an edge list. */
+SPHB_API int sphb_pair_sims(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                            const int64_t* pa, const int64_t* pb, int64_t npairs, int mode, float* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPHB_H */

@@ -23,7 +23,7 @@
 
 namespace {
 
-enum Metric { METRIC_L2 = 0, METRIC_IP = 1 };
+enum Metric { METRIC_IP = 0, METRIC_L2 = 1 };  // faiss::MetricType values, as at the reference call sites
 
 inline float pair_key(const float* xi, const float* xj, int d, int metric) {
     double acc = 0.0;

@@ -1,0 +1,251 @@
+"""ctypes binding of the C ABI (include/sphb.h) — numpy in, numpy out.
+
+This is the thin Python view of the library used by the tests and bench.py; a
+C++ caller binds the same symbols through include/sph_b200/*.hpp.  There is no
+CPU fallback: if the shared library is missing or no B200 is visible the calls
+raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libsphb200.so"
+_lib = None
+
+METRIC_INNER_PRODUCT = 0
+METRIC_L2 = 1
+W_CONSTANT, W_LINEAR, W_NORMAL, W_ONLYLAST, W_FIRST_VISIT = range(5)
+
+i64p = C.POINTER(C.c_int64)
+u64p = C.POINTER(C.c_uint64)
+u32p = C.POINTER(C.c_uint32)
+i32p = C.POINTER(C.c_int32)
+f32p = C.POINTER(C.c_float)
+f64p = C.POINTER(C.c_double)
+
+# name -> (restype, argtypes); must list every symbol include/sphb.h declares
+SIGNATURES = {
+    "sphb_init": (C.c_int, [C.c_int]),
+    "sphb_shutdown": (None, []),
+    "sphb_last_error": (C.c_char_p, []),
+    "sphb_version": (C.c_int, []),
+    "sphb_launch_count": (C.c_int64, []),
+    "sphb_reset_launch_count": (None, []),
+    "sphb_stream": (C.c_void_p, []),
+    "sphb_knn_exact": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, i64p, f32p]),
+    "sphb_knn_exact_slab": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, i64p, f32p]),
+    "sphb_knn_exact_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sphb_knn_last_stats": (C.c_int, [i64p]),
+    "sphb_prow_gaussian_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, C.c_float, u32p, f32p, f64p]),
+    "sphb_prow_gaussian_graph_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sphb_prow_linear_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, u32p, f32p]),
+    "sphb_prow_gaussian_inplace": (C.c_int, [C.c_int64, i64p, f32p, C.c_float, C.c_int]),
+    "sphb_prow_gaussian_flat": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_double, f32p]),
+    "sphb_symmetrize": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
+    "sphb_random_walks": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_uint64, C.c_uint64, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
+                                    C.c_int, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
+    "sphb_rw_merge": (C.c_int, [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, C.c_int, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
+    "sphb_create_similarities": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, u32p, f32p, i32p]),
+    "sphb_pair_sims": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, i64p, C.c_int64, C.c_int, f32p]),
+}
+
+
+class SphbError(RuntimeError):
+    pass
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def load():
+    """Loads the C-ABI library (no compute, no GPU needed)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise SphbError(f"{_LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (there is no CPU fallback)")
+    lib = C.CDLL(str(_LIB_PATH))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    # testing hook, not part of the public header
+    lib.sphb_debug_force_knn_path.restype = None
+    lib.sphb_debug_force_knn_path.argtypes = [C.c_int]
+    _lib = lib
+    return lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise SphbError(f"sphb error {rc}: {load().sphb_last_error().decode()}")
+
+
+def _p(a: np.ndarray, t):
+    return a.ctypes.data_as(t)
+
+
+def init(device: int = -1):
+    _check(load().sphb_init(device))
+
+
+def launch_count() -> int:
+    return int(load().sphb_launch_count())
+
+
+def reset_launch_count():
+    load().sphb_reset_launch_count()
+
+
+def stream_ptr() -> int:
+    return int(load().sphb_stream() or 0)
+
+
+def force_knn_path(path: int):
+    """0 auto, 1 SIMT exact kernel, 2 tcgen05 sweep (tests only)."""
+    load().sphb_debug_force_knn_path(path)
+
+
+def knn_last_stats() -> dict:
+    out = np.zeros(6, np.int64)
+    _check(load().sphb_knn_last_stats(_p(out, i64p)))
+    return dict(tensor_core=int(out[0]), compactions=int(out[1]), accepted=int(out[2]), kp=int(out[3]), db_tiles=int(out[4]), q_tiles=int(out[5]))
+
+
+# ------------------------------------------------------------------ Stage A
+def knn_exact(x: np.ndarray, k: int, metric: int = METRIC_L2, l2_squared: bool = False, q0: int = 0, q1: int | None = None):
+    """Exact kNN of rows [q0,q1) of x against all rows; returns (ids int64 [nq,k], dist float32 [nq,k])."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, d = x.shape
+    q1 = n if q1 is None else q1
+    nq = q1 - q0
+    ids = np.full((nq, k), -1, np.int64)
+    dist = np.full((nq, k), -1.0, np.float32)
+    _check(load().sphb_knn_exact_slab(_p(x, f32p), n, d, k, metric, int(l2_squared), q0, q1, _p(ids, i64p), _p(dist, f32p)))
+    return ids, dist
+
+
+def knn_exact_dev(x_ptr: int, n: int, d: int, k: int, metric: int, l2_squared: bool, q0: int, q1: int, ids_ptr: int, dist_ptr: int, stream: int):
+    _check(load().sphb_knn_exact_dev(x_ptr, n, d, k, metric, int(l2_squared), q0, q1, ids_ptr, dist_ptr, stream))
+
+
+# ------------------------------------------------------------------ Stage B
+def prow_gaussian_graph(ids: np.ndarray, dist: np.ndarray, perplexity: float = 0.0, want_sigma: bool = False):
+    ids = np.ascontiguousarray(ids, np.int64)
+    dist = np.ascontiguousarray(dist, np.float32)
+    n, k = ids.shape
+    cols = np.zeros((n, k - 1), np.uint32)
+    vals = np.zeros((n, k - 1), np.float32)
+    sigma = np.zeros(n, np.float64) if want_sigma else None
+    _check(load().sphb_prow_gaussian_graph(_p(ids, i64p), _p(dist, f32p), n, k, perplexity, _p(cols, u32p), _p(vals, f32p),
+                                           _p(sigma, f64p) if want_sigma else None))
+    return (cols, vals, sigma) if want_sigma else (cols, vals)
+
+
+def prow_gaussian_graph_dev(ids_ptr: int, dist_ptr: int, n: int, k: int, perplexity: float, cols_ptr: int, vals_ptr: int, stream: int):
+    _check(load().sphb_prow_gaussian_graph_dev(ids_ptr, dist_ptr, n, k, perplexity, cols_ptr, vals_ptr, None, stream))
+
+
+def prow_linear_graph(ids: np.ndarray, dist: np.ndarray):
+    ids = np.ascontiguousarray(ids, np.int64)
+    dist = np.ascontiguousarray(dist, np.float32)
+    n, k = ids.shape
+    cols = np.zeros((n, k - 1), np.uint32)
+    vals = np.zeros((n, k - 1), np.float32)
+    _check(load().sphb_prow_linear_graph(_p(ids, i64p), _p(dist, f32p), n, k, _p(cols, u32p), _p(vals, f32p)))
+    return cols, vals
+
+
+def prow_gaussian_inplace(rowptr: np.ndarray, val: np.ndarray, perplexity: float = 0.0, ignore: int = -1) -> np.ndarray:
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    out = np.array(val, dtype=np.float32, copy=True)
+    _check(load().sphb_prow_gaussian_inplace(len(rowptr) - 1, _p(rowptr, i64p), _p(out, f32p), perplexity, ignore))
+    return out
+
+
+def prow_gaussian_flat(dist: np.ndarray, perplexity: float) -> np.ndarray:
+    dist = np.ascontiguousarray(dist, np.float32)
+    n, k = dist.shape
+    temp = np.zeros((n, k), np.float32)
+    _check(load().sphb_prow_gaussian_flat(_p(dist, f32p), n, k, float(perplexity), _p(temp, f32p)))
+    return temp
+
+
+def symmetrize(rowptr, col, val, umap: bool = False):
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    cap = max(1, 2 * len(col))
+    orp = np.zeros(n + 1, np.int64)
+    oc = np.zeros(cap, np.uint32)
+    ov = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_symmetrize(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), int(umap), _p(orp, i64p), _p(oc, u32p), _p(ov, f32p), cap, _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oc[:m].copy(), ov[:m].copy()
+
+
+# ------------------------------------------------------------------ Stage C
+def random_walks(rowptr, col, val, num_walks: int, walk_len: int, weighting: int = W_CONSTANT, prune_value: float = 0.0, prune_steps: int = 0,
+                 seed: int = 0, remove_diagonal: bool = True, normalize: bool = True):
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    cap = max(1, n * min(n, num_walks * walk_len))
+    orp = np.zeros(n + 1, np.int64)
+    oc = np.zeros(cap, np.uint32)
+    ov = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_random_walks(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), num_walks, walk_len, weighting, prune_value, prune_steps,
+                                    seed, int(remove_diagonal), int(normalize), _p(orp, i64p), _p(oc, u32p), _p(ov, f32p), cap, _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oc[:m].copy(), ov[:m].copy()
+
+
+def rw_merge(rowptr, col, val, parents, n_merged: int, norm: bool = True, weight_by_size: bool = True):
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    parents = np.ascontiguousarray(parents, np.uint64)
+    n = len(rowptr) - 1
+    cap = max(1, len(col))
+    orp = np.zeros(n_merged + 1, np.int64)
+    oc = np.zeros(cap, np.uint32)
+    ov = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_rw_merge(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(parents, u64p), n_merged, int(norm), int(weight_by_size),
+                                _p(orp, i64p), _p(oc, u32p), _p(ov, f32p), cap, _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oc[:m].copy(), ov[:m].copy()
+
+
+# ------------------------------------------------------------------ Stage D
+def create_similarities(rowptr, col, val, k: int, prune_val: float = 1e-4, variant: int = 0, comp_sizes=None):
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    oc = np.zeros((n, k), np.uint32)
+    ov = np.zeros((n, k), np.float32)
+    nnz = np.zeros(n, np.int32)
+    cs = None if comp_sizes is None else np.ascontiguousarray(comp_sizes, np.int64)
+    _check(load().sphb_create_similarities(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), k, prune_val, variant,
+                                           _p(cs, i64p) if cs is not None else None, _p(oc, u32p), _p(ov, f32p), _p(nnz, i32p)))
+    return oc, ov, nnz
+
+
+def pair_sims(rowptr, col, val, pa, pb, mode: int = 0) -> np.ndarray:
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    pa = np.ascontiguousarray(pa, np.int64)
+    pb = np.ascontiguousarray(pb, np.int64)
+    out = np.zeros(len(pa), np.float32)
+    _check(load().sphb_pair_sims(len(rowptr) - 1, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(pa, i64p), _p(pb, i64p), len(pa), mode, _p(out, f32p)))
+    return out

@@ -1,0 +1,224 @@
+// C-ABI entry points (include/sphb.h): context, Stage A and Stage B wrappers.
+#include "../../include/sphb.h"
+#include "common.cuh"
+
+#include <atomic>
+#include <mutex>
+#include <algorithm>
+
+namespace sphb {
+
+static Context g_ctx;
+static std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+
+Context& ctx() { return g_ctx; }
+void set_error(const std::string& msg) { g_err = msg; }
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+void count_launch(int64_t n) { g_launches += n; }
+
+int ensure_init() {
+    if (g_ctx.ready) return 0;
+    return sphb_init(-1);
+}
+
+// kernels / launchers implemented in the other translation units
+int knn_simt_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, int64_t*, float*, cudaStream_t);
+int knn_tc_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, int64_t*, float*, cudaStream_t);
+bool knn_tc_supported(int64_t n, int d, int k);
+void knn_set_stats(const int64_t* s);
+void knn_get_stats(int64_t* s);
+int prow_graph_launch(const int64_t*, const float*, int64_t, int, float, int, uint32_t*, float*, double*, cudaStream_t);
+int prow_inplace_launch(int64_t, const int64_t*, float*, int, float, int, cudaStream_t);
+int prow_flat_launch(const float*, int64_t, int, double, float*, cudaStream_t);
+
+static int g_force_path = 0;  // 0 auto, 1 SIMT, 2 tensor core (testing hook)
+
+}  // namespace sphb
+
+using namespace sphb;
+
+extern "C" {
+
+SPHB_API int sphb_init(int device) {
+    if (g_ctx.ready && (device < 0 || device == g_ctx.device)) return SPHB_OK;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return fail(SPHB_ERR_NO_DEVICE, "no CUDA device available (this back-end has no CPU fallback)");
+    }
+    if (device < 0) {
+        if (cudaGetDevice(&device) != cudaSuccess) device = 0;
+    }
+    if (device >= count) return fail(SPHB_ERR_INVALID, "device index out of range");
+    SPHB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    SPHB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(SPHB_ERR_UNSUPPORTED, std::string("sm_100a build, found ") + prop.name);
+    if (g_ctx.stream) cudaStreamDestroy(g_ctx.stream);
+    SPHB_CUDA(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+    // keep freed stream-ordered allocations cached in the pool between calls
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        uint64_t thresh = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh);
+    }
+    g_ctx.device = device;
+    g_ctx.num_sms = prop.multiProcessorCount;
+    g_ctx.ready = true;
+    return SPHB_OK;
+}
+
+SPHB_API void sphb_shutdown(void) {
+    if (!g_ctx.ready) return;
+    cudaStreamSynchronize(g_ctx.stream);
+    cudaStreamDestroy(g_ctx.stream);
+    g_ctx.stream = nullptr;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, g_ctx.device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+    g_ctx.ready = false;
+}
+
+SPHB_API const char* sphb_last_error(void) { return g_err.c_str(); }
+SPHB_API int sphb_version(void) { return 100; }
+SPHB_API int64_t sphb_launch_count(void) { return g_launches.load(); }
+SPHB_API void sphb_reset_launch_count(void) { g_launches = 0; }
+SPHB_API void* sphb_stream(void) { return g_ctx.ready ? static_cast<void*>(g_ctx.stream) : nullptr; }
+
+// testing hook (not in the public header): 0 auto, 1 force SIMT, 2 force tensor-core path
+SPHB_API void sphb_debug_force_knn_path(int path) { g_force_path = path; }
+
+// ---------------------------------------------------------------- Stage A
+SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1,
+                                int64_t* d_ids, float* d_dist, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (n <= 0 || d <= 0 || k <= 0 || q0 < 0 || q1 > n || q0 > q1) return fail(SPHB_ERR_INVALID, "knn: bad sizes");
+    if (metric != SPHB_METRIC_L2 && metric != SPHB_METRIC_INNER_PRODUCT) return fail(SPHB_ERR_INVALID, "knn: unknown metric");
+    if (n >= (1ll << 32) - 1) return fail(SPHB_ERR_UNSUPPORTED, "knn: n must fit in uint32");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    bool use_tc = knn_tc_supported(n, d, k);
+    if (g_force_path == 1) use_tc = false;
+    if (g_force_path == 2) {
+        if (!use_tc) return fail(SPHB_ERR_UNSUPPORTED, "knn: tensor-core path unsupported for this shape");
+    }
+    if (use_tc) return knn_tc_launch(d_x, n, d, k, metric, l2_squared, q0, q1, d_ids, d_dist, s);
+    const int64_t st[6] = {0, 0, 0, 0, 0, 0};
+    knn_set_stats(st);
+    return knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, d_ids, d_dist, s);
+}
+
+SPHB_API int sphb_knn_exact_slab(const float* x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1,
+                                 int64_t* ids, float* dist) {
+    if (int rc = ensure_init()) return rc;
+    if (!x || !ids || !dist) return fail(SPHB_ERR_INVALID, "knn: null pointer");
+    if (n <= 0 || d <= 0 || k <= 0 || q0 < 0 || q1 > n || q0 > q1) return fail(SPHB_ERR_INVALID, "knn: bad sizes");
+    cudaStream_t s = g_ctx.stream;
+    const int64_t nq = q1 - q0;
+    DevBuf<float> dx, ddist;
+    DevBuf<int64_t> dids;
+    SPHB_CUDA(dx.alloc(static_cast<size_t>(n) * d, s));
+    SPHB_CUDA(dids.alloc(static_cast<size_t>(nq) * k, s));
+    SPHB_CUDA(ddist.alloc(static_cast<size_t>(nq) * k, s));
+    SPHB_CUDA(cudaMemcpyAsync(dx.p, x, static_cast<size_t>(n) * d * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (int rc = sphb_knn_exact_dev(dx.p, n, d, k, metric, l2_squared, q0, q1, dids.p, ddist.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(ids, dids.p, static_cast<size_t>(nq) * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(dist, ddist.p, static_cast<size_t>(nq) * k * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_knn_exact(const float* x, int64_t n, int d, int k, int metric, int l2_squared, int64_t* ids, float* dist) {
+    return sphb_knn_exact_slab(x, n, d, k, metric, l2_squared, 0, n, ids, dist);
+}
+
+SPHB_API int sphb_knn_last_stats(int64_t* out6) {
+    if (!out6) return fail(SPHB_ERR_INVALID, "null pointer");
+    knn_get_stats(out6);
+    return SPHB_OK;
+}
+
+// ---------------------------------------------------------------- Stage B
+SPHB_API int sphb_prow_gaussian_graph_dev(const int64_t* d_ids, const float* d_dist, int64_t n, int k, float perplexity, uint32_t* d_cols,
+                                          float* d_vals, double* d_sigma, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    return prow_graph_launch(d_ids, d_dist, n, k, perplexity, 0, d_cols, d_vals, d_sigma, static_cast<cudaStream_t>(stream));
+}
+
+static int prow_graph_host(const int64_t* ids, const float* dist, int64_t n, int k, float perplexity, int mode, uint32_t* cols, float* vals,
+                           double* sigma) {
+    if (int rc = ensure_init()) return rc;
+    if (!ids || !dist || !cols || !vals) return fail(SPHB_ERR_INVALID, "prow: null pointer");
+    if (n < 0 || k < 2) return fail(SPHB_ERR_INVALID, "prow: bad sizes");
+    if (n == 0) return SPHB_OK;
+    cudaStream_t s = g_ctx.stream;
+    const size_t nk = static_cast<size_t>(n) * k, ne = static_cast<size_t>(n) * (k - 1);
+    DevBuf<int64_t> dids;
+    DevBuf<float> ddist, dvals;
+    DevBuf<uint32_t> dcols;
+    DevBuf<double> dsig;
+    SPHB_CUDA(dids.alloc(nk, s));
+    SPHB_CUDA(ddist.alloc(nk, s));
+    SPHB_CUDA(dcols.alloc(ne, s));
+    SPHB_CUDA(dvals.alloc(ne, s));
+    if (sigma) SPHB_CUDA(dsig.alloc(n, s));
+    SPHB_CUDA(cudaMemcpyAsync(dids.p, ids, nk * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    SPHB_CUDA(cudaMemcpyAsync(ddist.p, dist, nk * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (int rc = prow_graph_launch(dids.p, ddist.p, n, k, perplexity, mode, dcols.p, dvals.p, sigma ? dsig.p : nullptr, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(cols, dcols.p, ne * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(vals, dvals.p, ne * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (sigma) SPHB_CUDA(cudaMemcpyAsync(sigma, dsig.p, n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_prow_gaussian_graph(const int64_t* ids, const float* dist, int64_t n, int k, float perplexity, uint32_t* cols, float* vals,
+                                      double* sigma) {
+    return prow_graph_host(ids, dist, n, k, perplexity, 0, cols, vals, sigma);
+}
+
+SPHB_API int sphb_prow_linear_graph(const int64_t* ids, const float* dist, int64_t n, int k, uint32_t* cols, float* vals) {
+    return prow_graph_host(ids, dist, n, k, 0.f, 1, cols, vals, nullptr);
+}
+
+SPHB_API int sphb_prow_gaussian_inplace(int64_t n, const int64_t* rowptr, float* val, float perplexity, int ignore) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || !rowptr || (!val && n > 0 && rowptr[n] > 0)) return fail(SPHB_ERR_INVALID, "prow_inplace: bad arguments");
+    if (n == 0 || rowptr[n] == 0) return SPHB_OK;
+    cudaStream_t s = g_ctx.stream;
+    const int64_t nnz = rowptr[n];
+    int64_t max_nnz = 0;
+    for (int64_t i = 0; i < n; ++i) max_nnz = std::max(max_nnz, rowptr[i + 1] - rowptr[i]);
+    if (max_nnz > 1024) return fail(SPHB_ERR_UNSUPPORTED, "prow_inplace: rows with more than 1024 entries unsupported");
+    DevBuf<int64_t> drp;
+    DevBuf<float> dval;
+    SPHB_CUDA(drp.alloc(n + 1, s));
+    SPHB_CUDA(dval.alloc(nnz, s));
+    SPHB_CUDA(cudaMemcpyAsync(drp.p, rowptr, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    SPHB_CUDA(cudaMemcpyAsync(dval.p, val, nnz * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (int rc = prow_inplace_launch(n, drp.p, dval.p, static_cast<int>(max_nnz), perplexity, ignore, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(val, dval.p, nnz * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_prow_gaussian_flat(const float* dist, int64_t n, int k, double perplexity, float* temp) {
+    if (int rc = ensure_init()) return rc;
+    if (!dist || !temp || n < 0 || k < 1) return fail(SPHB_ERR_INVALID, "prow_flat: bad arguments");
+    if (n == 0) return SPHB_OK;
+    cudaStream_t s = g_ctx.stream;
+    const size_t nk = static_cast<size_t>(n) * k;
+    DevBuf<float> dd, dt;
+    SPHB_CUDA(dd.alloc(nk, s));
+    SPHB_CUDA(dt.alloc(nk, s));
+    SPHB_CUDA(cudaMemcpyAsync(dd.p, dist, nk * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (int rc = prow_flat_launch(dd.p, n, k, perplexity, dt.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(temp, dt.p, nk * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+}  // extern "C"

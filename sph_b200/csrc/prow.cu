@@ -1,0 +1,306 @@
+// Stage B: perplexity-calibrated probability rows (t-SNE P matrix), one warp per row.
+//   B1 sph/utils/HDILibHelper.hpp:23-109   binary search on beta (fp64, fp32 round trip of p)
+//   B2 sph/utils/GraphNormalization.cpp:191-338  graph -> column-sorted rows (+ min-sigma fallback)
+//   B3 sph/utils/GraphNormalization.cpp:38-189   in place on sparse rows (+ the 1e-10 cursor quirk)
+//   B4 sph/utils/HDILibHelper.hpp:112-140        flat variant, tol 1e-5
+//   B5 sph/utils/GraphNormalization.cpp:340-411  linear rows
+// Distances live in registers (R values per lane), all reductions are warp shuffles,
+// the beta loop never touches memory.  HBM traffic is the one read of (ids, dist)
+// and the one write of (cols, vals).
+#include "common.cuh"
+#include <cfloat>
+
+namespace sphb {
+
+// Returns sigma (0 when not found).  On return p[] holds the fp32 probabilities
+// exactly as the reference leaves them (normalised if found, uniform if not).
+template <int R>
+__device__ __forceinline__ double perplexity_search(const float (&dist)[R], float (&p)[R], int nn, int lane, double perplexity, double tol,
+                                                    int ignore) {
+    bool found = false;
+    double beta = 1.0;
+    double min_beta = -DBL_MAX, max_beta = DBL_MAX;
+    double sum = DBL_MIN;
+    const double logp = log(perplexity);
+    int iter = 0;
+    while (!found && iter < 200) {
+        double s = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            if (idx < nn) {
+                if (idx == ignore) {
+                    p[r] = 0.f;
+                } else {
+                    const double v = exp(-beta * static_cast<double>(dist[r]));
+                    p[r] = static_cast<float>(v);
+                    s += v;
+                }
+            }
+        }
+        s = warp_sum(s);
+        sum = DBL_MIN + s;
+        double h = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            if (idx < nn && idx != ignore) h += beta * static_cast<double>(dist[r] * p[r]);
+        }
+        h = warp_sum(h);
+        const double H = (h / sum) + log(sum);
+        const double Hdiff = H - logp;
+        if (Hdiff < tol && -Hdiff < tol) {
+            found = true;
+        } else if (Hdiff > 0) {
+            min_beta = beta;
+            if (max_beta == DBL_MAX || max_beta == -DBL_MAX) beta *= 2.0;
+            else beta = (beta + max_beta) / 2.0;
+        } else {
+            max_beta = beta;
+            if (min_beta == -DBL_MAX || min_beta == DBL_MAX) beta /= 2.0;
+            else beta = (beta + min_beta) / 2.0;
+        }
+        ++iter;
+    }
+    if (!found) {
+        const float v = static_cast<float>(1. / (nn + ((ignore < 0 || ignore >= nn) ? 0 : -1)));
+#pragma unroll
+        for (int r = 0; r < R; ++r) p[r] = v;
+        return 0.0;
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) p[r] = static_cast<float>(static_cast<double>(p[r]) / sum);
+    return sqrt(1.0 / (2.0 * beta));
+}
+
+template <int R>
+__device__ __forceinline__ bool all_zero(const float (&p)[R], int nn, int lane) {
+    bool z = true;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (lane + 32 * r < nn && p[r] != 0.f) z = false;
+    return __all_sync(0xffffffffu, z);
+}
+template <int R>
+__device__ __forceinline__ void normalize_unit(float (&p)[R], int nn, int lane) {
+    double s = 0.0;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (lane + 32 * r < nn) s += static_cast<double>(p[r]);
+    s = warp_sum(s);
+#pragma unroll
+    for (int r = 0; r < R; ++r) p[r] = static_cast<float>(static_cast<double>(p[r]) / s);
+}
+// min-sigma fallback (GraphNormalization.cpp:96-130 / :249-282)
+template <int R>
+__device__ __forceinline__ void min_sigma_fallback(const float (&dist)[R], float (&p)[R], int nn, int lane, bool zero_first) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) p[r] = dist[r];
+    const float same = 1.f / (nn - 1);
+    if (all_zero<R>(p, nn, lane)) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) p[r] = same;
+        return;
+    }
+    normalize_unit<R>(p, nn, lane);
+#pragma unroll
+    for (int r = 0; r < R; ++r) p[r] = 1.0f - p[r];
+    if (all_zero<R>(p, nn, lane)) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) p[r] = same;
+        return;
+    }
+    if (zero_first && lane == 0) p[0] = 0.f;
+    normalize_unit<R>(p, nn, lane);
+}
+
+// mode 0: Gaussian (B2), mode 1: linear (B5)
+template <int R>
+__global__ void __launch_bounds__(128) prow_graph_kernel(const int64_t* __restrict__ ids, const float* __restrict__ dist, int64_t n, int k,
+                                                         float fixed_perplexity, int mode, int cap, uint32_t* __restrict__ cols,
+                                                         float* __restrict__ vals, double* __restrict__ sigma_out) {
+    extern __shared__ uint64_t smem_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+    const int ne = k - 1;
+    for (int64_t p = gw; p < n; p += nw) {
+        float dv[R], pv[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            dv[r] = idx < k ? dist[p * k + idx] : 0.f;
+            pv[r] = 0.f;
+        }
+        if (mode == 0) {
+            const float perplexity = fixed_perplexity > 0 ? fixed_perplexity : ne / 3.f;
+            const double sigma = perplexity_search<R>(dv, pv, k, lane, static_cast<double>(perplexity), 1e-6, 0);
+            if (sigma < 0.001) min_sigma_fallback<R>(dv, pv, k, lane, true);
+            if (sigma_out && lane == 0) sigma_out[p] = sigma;
+        } else {
+            // invlin over neighbours 1..k-1, normalise (double sum)
+            double s = 0.0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int idx = lane + 32 * r;
+                pv[r] = (idx >= 1 && idx < k) ? 1.0f / (1.0f + dv[r]) : 0.f;
+                s += static_cast<double>(pv[r]);
+            }
+            s = warp_sum(s);
+#pragma unroll
+            for (int r = 0; r < R; ++r) pv[r] = static_cast<float>(static_cast<double>(pv[r]) / s);
+        }
+        // column sort of entries 1..k-1
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            if (idx < cap) {
+                uint64_t key = ~0ull;
+                if (idx >= 1 && idx < k) key = (static_cast<uint64_t>(static_cast<uint32_t>(ids[p * k + idx])) << 32) | __float_as_uint(pv[r]);
+                sm[idx] = key;
+            }
+        }
+        for (int t = 32 * R + lane; t < cap; t += 32) sm[t] = ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        for (int e = lane; e < ne; e += 32) {
+            const uint64_t key = sm[e];
+            cols[p * ne + e] = static_cast<uint32_t>(key >> 32);
+            vals[p * ne + e] = __uint_as_float(static_cast<uint32_t>(key));
+        }
+        __syncwarp();
+    }
+}
+
+// B3: in place on CSR rows.
+template <int R>
+__global__ void __launch_bounds__(128) prow_inplace_kernel(int64_t n, const int64_t* __restrict__ rowptr, float* __restrict__ val,
+                                                           float fixed_perplexity, int ignore, int* __restrict__ err) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+    for (int64_t p = gw; p < n; p += nw) {
+        const int64_t b = rowptr[p];
+        const int64_t nn64 = rowptr[p + 1] - b;
+        if (nn64 <= 1) continue;
+        if (nn64 > 32 * R) {
+            if (lane == 0) atomicExch(err, 1);
+            continue;
+        }
+        const int nn = static_cast<int>(nn64);
+        float dv[R], pv[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            dv[r] = idx < nn ? val[b + idx] : 0.f;
+            pv[r] = 0.f;
+        }
+        const float perplexity = fixed_perplexity > 0 ? fixed_perplexity : nn / 3.f;
+        const double sigma = perplexity_search<R>(dv, pv, nn, lane, static_cast<double>(perplexity), 1e-6, ignore);
+        if (sigma < 0.001) min_sigma_fallback<R>(dv, pv, nn, lane, ignore >= 0);
+        // write-back cursor stops at the first p < 1e-10 (GraphNormalization.cpp:132-153)
+        int z = 0x7fffffff;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            if (idx < nn && pv[r] < 1.0e-10f) z = min(z, idx);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) z = min(z, __shfl_xor_sync(0xffffffffu, z, o));
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            if (idx < nn && idx < z) val[b + idx] = pv[r];
+        }
+    }
+}
+
+// B4: flat variant -> temp[n*k]
+template <int R>
+__global__ void __launch_bounds__(128) prow_flat_kernel(const float* __restrict__ dist, int64_t n, int k, double perplexity,
+                                                        float* __restrict__ temp) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+    for (int64_t p = gw; p < n; p += nw) {
+        float dv[R], pv[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            dv[r] = idx < k ? dist[p * k + idx] : 0.f;
+            pv[r] = 0.f;
+        }
+        perplexity_search<R>(dv, pv, k, lane, perplexity, 1e-5, 0);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            if (idx < k) temp[p * k + idx] = pv[r];
+        }
+    }
+}
+
+static int pow2_at_least(int v) {
+    int p = 32;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+template <int R>
+static int launch_graph(const int64_t* ids, const float* dist, int64_t n, int k, float perplexity, int mode, uint32_t* cols, float* vals,
+                        double* sigma, cudaStream_t stream) {
+    const int cap = pow2_at_least(32 * R);
+    const size_t smem = 4 * static_cast<size_t>(cap) * sizeof(uint64_t);
+    SPHB_CUDA(cudaFuncSetAttribute(prow_graph_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    const int64_t blocks = std::min<int64_t>((n + 3) / 4, static_cast<int64_t>(ctx().num_sms) * 16);
+    prow_graph_kernel<R><<<static_cast<unsigned>(blocks), 128, smem, stream>>>(ids, dist, n, k, perplexity, mode, cap, cols, vals, sigma);
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int prow_graph_launch(const int64_t* d_ids, const float* d_dist, int64_t n, int k, float perplexity, int mode, uint32_t* d_cols,
+                      float* d_vals, double* d_sigma, cudaStream_t stream) {
+    if (n <= 0) return 0;
+    if (k < 2) return fail(2, "prow: k must be >= 2");
+    if (k <= 32) return launch_graph<1>(d_ids, d_dist, n, k, perplexity, mode, d_cols, d_vals, d_sigma, stream);
+    if (k <= 64) return launch_graph<2>(d_ids, d_dist, n, k, perplexity, mode, d_cols, d_vals, d_sigma, stream);
+    if (k <= 96) return launch_graph<3>(d_ids, d_dist, n, k, perplexity, mode, d_cols, d_vals, d_sigma, stream);
+    if (k <= 128) return launch_graph<4>(d_ids, d_dist, n, k, perplexity, mode, d_cols, d_vals, d_sigma, stream);
+    if (k <= 320) return launch_graph<10>(d_ids, d_dist, n, k, perplexity, mode, d_cols, d_vals, d_sigma, stream);
+    if (k <= 1024) return launch_graph<32>(d_ids, d_dist, n, k, perplexity, mode, d_cols, d_vals, d_sigma, stream);
+    return fail(5, "prow: k > 1024 unsupported");
+}
+
+int prow_inplace_launch(int64_t n, const int64_t* d_rowptr, float* d_val, int max_nnz, float perplexity, int ignore, cudaStream_t stream) {
+    if (n <= 0) return 0;
+    DevBuf<int> err;
+    SPHB_CUDA(err.alloc(1, stream));
+    SPHB_CUDA(cudaMemsetAsync(err.p, 0, sizeof(int), stream));
+    const int64_t blocks = std::min<int64_t>((n + 3) / 4, static_cast<int64_t>(ctx().num_sms) * 16);
+    if (max_nnz <= 128) prow_inplace_kernel<4><<<static_cast<unsigned>(blocks), 128, 0, stream>>>(n, d_rowptr, d_val, perplexity, ignore, err.p);
+    else if (max_nnz <= 320) prow_inplace_kernel<10><<<static_cast<unsigned>(blocks), 128, 0, stream>>>(n, d_rowptr, d_val, perplexity, ignore, err.p);
+    else if (max_nnz <= 1024) prow_inplace_kernel<32><<<static_cast<unsigned>(blocks), 128, 0, stream>>>(n, d_rowptr, d_val, perplexity, ignore, err.p);
+    else return fail(5, "prow_inplace: rows with more than 1024 entries unsupported");
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    int herr = 0;
+    SPHB_CUDA(cudaMemcpyAsync(&herr, err.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    SPHB_CUDA(cudaStreamSynchronize(stream));
+    if (herr) return fail(5, "prow_inplace: row longer than the dispatched register tile");
+    return 0;
+}
+
+int prow_flat_launch(const float* d_dist, int64_t n, int k, double perplexity, float* d_temp, cudaStream_t stream) {
+    if (n <= 0) return 0;
+    const int64_t blocks = std::min<int64_t>((n + 3) / 4, static_cast<int64_t>(ctx().num_sms) * 16);
+    if (k <= 128) prow_flat_kernel<4><<<static_cast<unsigned>(blocks), 128, 0, stream>>>(d_dist, n, k, perplexity, d_temp);
+    else if (k <= 320) prow_flat_kernel<10><<<static_cast<unsigned>(blocks), 128, 0, stream>>>(d_dist, n, k, perplexity, d_temp);
+    else if (k <= 1024) prow_flat_kernel<32><<<static_cast<unsigned>(blocks), 128, 0, stream>>>(d_dist, n, k, perplexity, d_temp);
+    else return fail(5, "prow_flat: k > 1024 unsupported");
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace sphb
