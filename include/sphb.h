@@ -89,9 +89,10 @@ SPHB_API int sphb_knn_exact_slab(const float* x, int64_t n, int d, int k, int me
                                  int64_t q0, int64_t q1, int64_t* ids, float* dist);
 SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared,
                                 int64_t q0, int64_t q1, int64_t* d_ids, float* d_dist, void* stream);
-/* kNN statistics of the last call: [0] tensor-core path used (0/1), [1] candidate
- * compactions, [2] candidates accepted by the filter, [3] Kp (GEMM K extent),
- * [4] database tiles per query tile, [5] query tiles. */
+/* kNN statistics of the last call: [0] path (0 SIMT, 1 tcgen05 streaming, 2 tcgen05
+ * resident MH=1, 3 tcgen05 resident MH=2), [1] candidate-list compactions,
+ * [2] candidates accepted by the filter, [3] executed GEMM K extent per pair,
+ * [4] rows recomputed by the exact SIMT kernel (candidate band overflow), [5] query tiles. */
 SPHB_API int sphb_knn_last_stats(int64_t* out6);
 
 /* ---- Stage B: perplexity-calibrated probability rows -------------------- */

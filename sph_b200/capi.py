@@ -106,14 +106,14 @@ def stream_ptr() -> int:
 
 
 def force_knn_path(path: int):
-    """0 auto, 1 SIMT exact kernel, 2 tcgen05 sweep (tests only)."""
+    """0 auto, 1 SIMT exact kernel, 2 tcgen05 sweep (auto flavour), 3 tcgen05 streaming, 4 tcgen05 resident MH=1 (tests only)."""
     load().sphb_debug_force_knn_path(path)
 
 
 def knn_last_stats() -> dict:
     out = np.zeros(6, np.int64)
     _check(load().sphb_knn_last_stats(_p(out, i64p)))
-    return dict(tensor_core=int(out[0]), compactions=int(out[1]), accepted=int(out[2]), kp=int(out[3]), db_tiles=int(out[4]), q_tiles=int(out[5]))
+    return dict(tensor_core=int(out[0]), compactions=int(out[1]), accepted=int(out[2]), kp=int(out[3]), overflow_rows=int(out[4]), q_tiles=int(out[5]))
 
 
 # ------------------------------------------------------------------ Stage A

@@ -26,8 +26,8 @@ int ensure_init() {
 }
 
 // kernels / launchers implemented in the other translation units
-int knn_simt_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, int64_t*, float*, cudaStream_t);
-int knn_tc_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, int64_t*, float*, cudaStream_t);
+int knn_simt_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, const int64_t*, const int*, int64_t, int64_t*, float*, cudaStream_t);
+int knn_tc_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, int64_t*, float*, cudaStream_t, int);
 bool knn_tc_supported(int64_t n, int d, int k);
 void knn_set_stats(const int64_t* s);
 void knn_get_stats(int64_t* s);
@@ -35,7 +35,7 @@ int prow_graph_launch(const int64_t*, const float*, int64_t, int, float, int, ui
 int prow_inplace_launch(int64_t, const int64_t*, float*, int, float, int, cudaStream_t);
 int prow_flat_launch(const float*, int64_t, int, double, float*, cudaStream_t);
 
-static int g_force_path = 0;  // 0 auto, 1 SIMT, 2 tensor core (testing hook)
+static int g_force_path = 0;  // 0 auto, 1 SIMT, 2 tensor core (auto flavour), 3 tc streaming kernel, 4 tc resident MH=1 (testing hook)
 
 }  // namespace sphb
 
@@ -102,13 +102,13 @@ SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int m
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     bool use_tc = knn_tc_supported(n, d, k);
     if (g_force_path == 1) use_tc = false;
-    if (g_force_path == 2) {
+    if (g_force_path >= 2) {
         if (!use_tc) return fail(SPHB_ERR_UNSUPPORTED, "knn: tensor-core path unsupported for this shape");
     }
-    if (use_tc) return knn_tc_launch(d_x, n, d, k, metric, l2_squared, q0, q1, d_ids, d_dist, s);
+    if (use_tc) return knn_tc_launch(d_x, n, d, k, metric, l2_squared, q0, q1, d_ids, d_dist, s, g_force_path == 3 ? 1 : (g_force_path == 4 ? 2 : 0));
     const int64_t st[6] = {0, 0, 0, 0, 0, 0};
     knn_set_stats(st);
-    return knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, d_ids, d_dist, s);
+    return knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, nullptr, nullptr, 0, d_ids, d_dist, s);
 }
 
 SPHB_API int sphb_knn_exact_slab(const float* x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1,

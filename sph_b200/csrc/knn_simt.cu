@@ -9,14 +9,17 @@ namespace sphb {
 
 template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) knn_simt_kernel(const float* __restrict__ X, int64_t n, int d, int k, int cap, int metric,
-                                                              int l2_squared, int64_t q0, int64_t q1, int64_t* __restrict__ ids,
+                                                              int l2_squared, int64_t q0, int64_t q1, const int64_t* __restrict__ rowlist,
+                                                              const int* __restrict__ rowcount, int64_t* __restrict__ ids,
                                                               float* __restrict__ dist) {
     extern __shared__ uint64_t smem_keys[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
-    const int64_t nq = q1 - q0;
-    for (int64_t r = static_cast<int64_t>(blockIdx.x) * WARPS + warp; r < nq; r += static_cast<int64_t>(gridDim.x) * WARPS) {
-        const int64_t i = q0 + r;
+    // rows to process: the slab [q0,q1), or (rowlist != null) an explicit list of global row ids
+    const int64_t nq = rowlist ? static_cast<int64_t>(*rowcount) : q1 - q0;
+    for (int64_t rr = static_cast<int64_t>(blockIdx.x) * WARPS + warp; rr < nq; rr += static_cast<int64_t>(gridDim.x) * WARPS) {
+        const int64_t i = rowlist ? rowlist[rr] : q0 + rr;
+        const int64_t r = i - q0;  // output row within the slab
         int cnt = 0;
         uint64_t kth = ~0ull;
         for (int64_t base = 0; base < n; base += 32) {
@@ -55,19 +58,20 @@ static int next_pow2(int v) {
     return p;
 }
 
-int knn_simt_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1, int64_t* d_ids,
-                    float* d_dist, cudaStream_t stream) {
+int knn_simt_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1, const int64_t* d_rowlist,
+                    const int* d_rowcount, int64_t max_rows, int64_t* d_ids, float* d_dist, cudaStream_t stream) {
     constexpr int WARPS = 4;
     const int cap = next_pow2(k + 64);
     const size_t smem = static_cast<size_t>(WARPS) * cap * sizeof(uint64_t);
     if (smem > 200 * 1024) return fail(5, "knn_simt: k too large");
     SPHB_CUDA(cudaFuncSetAttribute(knn_simt_kernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    const int64_t nq = q1 - q0;
+    const int64_t nq = d_rowlist ? max_rows : q1 - q0;
     if (nq <= 0) return 0;
     int64_t blocks = (nq + WARPS - 1) / WARPS;
     const int64_t maxb = static_cast<int64_t>(ctx().num_sms) * 16;
     if (blocks > maxb) blocks = maxb;
-    knn_simt_kernel<WARPS><<<static_cast<unsigned>(blocks), WARPS * 32, smem, stream>>>(d_x, n, d, k, cap, metric, l2_squared, q0, q1, d_ids, d_dist);
+    knn_simt_kernel<WARPS><<<static_cast<unsigned>(blocks), WARPS * 32, smem, stream>>>(d_x, n, d, k, cap, metric, l2_squared, q0, q1, d_rowlist, d_rowcount, d_ids,
+                                                                                            d_dist);
     count_launch();
     SPHB_CUDA(cudaGetLastError());
     return 0;

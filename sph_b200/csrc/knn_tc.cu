@@ -1,64 +1,56 @@
 // Exact kNN graph on the 5th-gen tensor cores (Stage A; replaces the faiss call
 // sites at sph/utils/Knn.cpp:56-136).
 //
-// Pipeline
-//   1. knn_prep_*: column means (fp64), centre, scale by a power of two, split
-//      every value into fp16 hi + lo, and lay out two K-major fp16 operand
-//      matrices so that ONE plain GEMM yields  G_ij = |v_j|² - 2 u_i·v_j
-//      (u = s(x-mean)):
-//         A'[i] = [ hi | hi | lo | 1 1 1 | 0.. ]          (Kp columns)
-//         B'[j] = [-2hi |-2lo |-2hi | n0 n1 n2 | 0.. ]     (n0+n1+n2 = |v_j|², fp16 split)
-//      i.e. the three cross products hi·hi + hi·lo + lo·hi of a 22-bit mantissa
-//      emulation, plus the database norm, inside the contraction.
-//   2. knn_sweep_kernel: persistent, warp-specialised CTAs (TMA producer, MMA
-//      issuer, 4 epilogue warps).  Each CTA owns a 128-row query tile and sweeps
-//      the whole database in 256-row tiles: TMA -> 128B-swizzled smem ->
-//      tcgen05.mma (M=128, N=256, fp32 accumulators double-buffered in TMEM) ->
-//      tcgen05.ld epilogue.  The epilogue thread that owns a row compares each
-//      G against the row's running threshold (one FMNMX per value on the fast
-//      path); survivors are appended to a per-row candidate list.  When a list
-//      fills up the warp re-ranks it EXACTLY (fp64 FMA chain on the original
-//      fp32 data, bit-identical to the oracle), sorts (distance, index) keys,
-//      keeps k and tightens the threshold.  Because the filter threshold carries
-//      a rigorous bound on the GEMM error, the result is the exact kNN set.
-//   3. the final per-row write-out fuses the reference's post-passes (eps clamp,
-//      sqrt, self-first).
-#include "knn_common.cuh"
-#include "ptx_sm100.cuh"
+// 1. knn_prep_*: column means (fp64), centre, scale by a power of two, split every
+//    value into fp16 hi + lo (22-bit mantissa emulation) and build fp16 operand
+//    matrices such that a GEMM yields  G_ij = |v_j|² - 2 u_i·v_j  (u = s(x-mean)):
+//    three cross products hi·hi + hi·lo + lo·hi plus the database norm (itself a
+//    3-term fp16 split multiplied by a column of ones) inside the contraction.
+// 2. the sweep: persistent, warp-specialised CTAs (TMA producer warp, MMA issuer
+//    warp, 4 or 8 epilogue warps).  Two flavours:
+//      knn_sweep_resident<MH>  d <= 256: the query tile (MH x 128 rows, hi|lo) stays
+//                              RESIDENT in shared memory for the whole database
+//                              sweep; only database chunks stream through a TMA
+//                              ring, so L2->SM traffic is ~(2d+64)*2 B per database
+//                              row per CTA and the kernel is tensor-pipe bound;
+//      knn_sweep_stream        any d: both operands stream in K chunks (K-concatenated
+//                              layout [hi|hi|lo|1] x [-2hi|-2lo|-2hi|n]).
+//    tcgen05.mma (M=128, fp32 accumulators double-buffered in TMEM) -> tcgen05.ld
+//    epilogue -> threshold filter + per-row candidate lists (knn_epilogue.cuh).
+// 3. knn_rerank_kernel: exact fp64 re-rank of each row's candidates (bit-identical
+//    to the oracle), (distance, index) sort, fused post-passes, single write of
+//    ids/dist.  Rows flagged as overflowing go through the exact SIMT kernel.
+#include "knn_epilogue.cuh"
 
 #include <cuda_fp16.h>
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
 namespace sphb {
 
 namespace tc {
-constexpr int BM = 128;       // query rows per CTA tile (= TMEM lanes)
-constexpr int BN = 256;       // database rows per accumulator stage (= TMEM columns)
+constexpr int BM = 128;       // query rows per MMA (= TMEM lanes)
 constexpr int BK = 64;        // fp16 elements per smem row = 128 B swizzle span
 constexpr int UMMA_K = 16;
-constexpr int ACC_STAGES = 2;
-constexpr int TMEM_COLS = ACC_STAGES * BN;  // 512
-constexpr int A_BYTES = BM * BK * 2;
-constexpr int B_BYTES = BN * BK * 2;
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int NUM_THREADS = 192;  // warp0 TMA, warp1 MMA, warps 2..5 epilogue
+constexpr int CHUNK_ROWS = 128;
+constexpr int CHUNK_BYTES = CHUNK_ROWS * BK * 2;  // 16 KB: one 128-row x 64-col fp16 tile
 constexpr double VMAX2 = 16384.0;  // scaled squared-norm ceiling (fits fp16 with headroom)
 constexpr double VMAX = 128.0;
 }  // namespace tc
 
 struct SweepParams {
-    const float* X;          // original fp32 data [n, d]
-    const double* un2;       // scaled centred squared norms [n]
-    const double* scal;      // [0] = s² (scale squared)
-    int64_t n;               // database size
-    int d, k, cap, metric, l2_squared;
-    int64_t q0, nq;          // query slab
-    int n_qtiles, n_dbtiles, kchunks, k16_last, stages;
-    double eps_c1, eps_c2;   // filter slack: eps_i = c1*(2|u_i|VMAX + VMAX²) + c2*(|u_i| + VMAX)
-    uint64_t* cand;          // [grid, BM, cap] candidate scratch
-    int64_t* ids;            // [nq, k]
-    float* dist;             // [nq, k]
+    const double* un2;   // scaled centred squared norms [n]
+    int64_t n;           // database size
+    int k, cap, keep_max, metric;
+    int64_t q0, nq;      // query slab
+    int n_qtiles, n_dbtiles;
+    int dp64;            // resident flavour: padded d / 64
+    int kchunks, k16_last, stages;  // stream flavour: K chunks per tile, k-steps in the last one; both: ring depth
+    double eps_c1, eps_c2;
+    uint64_t* cand;      // [grid, rows_per_cta, cap] scratch lists
+    uint32_t* cand_out;  // [nq, keep_max]
+    int* cnt_out;        // [nq]
     unsigned long long* stats;  // [0] compactions, [1] accepted candidates
 };
 
@@ -66,8 +58,7 @@ struct SweepParams {
 // prep kernels
 // ---------------------------------------------------------------------------
 __global__ void knn_prep_colsum(const float* __restrict__ X, int64_t n, int d, double* __restrict__ colsum) {
-    // thread <-> column (coalesced across the row), block strides over rows
-    const int c = blockIdx.y * blockDim.x + threadIdx.x;
+    const int c = blockIdx.y * blockDim.x + threadIdx.x;  // thread <-> column (coalesced), block strides over rows
     if (c >= d) return;
     double acc = 0.0;
     for (int64_t i = blockIdx.x; i < n; i += gridDim.x) acc += static_cast<double>(X[i * d + c]);
@@ -104,19 +95,22 @@ __global__ void knn_prep_scale(const unsigned long long* __restrict__ maxbits, d
     scal[1] = s;
 }
 
-// one warp per row: write A'[i], B'[i]; rescale un2[i] by s².
-__global__ void knn_prep_split(const float* __restrict__ X, int64_t n, int64_t np, int d, int kp, const double* __restrict__ colsum,
-                               int centre, int with_norm, const double* __restrict__ scal, double* __restrict__ un2,
-                               __half* __restrict__ A, __half* __restrict__ B) {
+// One warp per row.  layout 0 (stream):   A[i] = [hi|hi|lo|1 1 1|0..] , B[i] = [-2hi|-2lo|-2hi|n0 n1 n2|0..], both kp wide.
+//                    layout 1 (resident): A[i] = [hi(dp)|lo(dp)]      , B[i] = [-2hi(dp)|-2lo(dp)|n0 n1 n2 0..(64)].
+// Also rescales un2[i] by s².  Buffers are pre-zeroed.
+__global__ void knn_prep_split(const float* __restrict__ X, int64_t n, int64_t np, int d, int layout, int lda, int ldb, int dp,
+                               const double* __restrict__ colsum, int centre, int with_norm, const double* __restrict__ scal,
+                               double* __restrict__ un2, __half* __restrict__ A, __half* __restrict__ B) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
     const double s = scal[1], s2 = scal[0];
+    const int ncol = layout == 0 ? 3 * d : 2 * dp;  // column of the norm / ones triple
     for (int64_t i = warp; i < np; i += nwarps) {
-        __half* a = A + i * kp;
-        __half* b = B + i * kp;
+        __half* a = A + i * lda;
+        __half* b = B + i * ldb;
         if (i >= n) {  // padding rows: zero queries, "infinitely far" database points
-            if (lane < 3) b[3 * d + lane] = __float2half(65504.f);
+            if (lane < 3) b[ncol + lane] = __float2half(65504.f);
             continue;
         }
         for (int c = lane; c < d; c += 32) {
@@ -126,59 +120,87 @@ __global__ void knn_prep_split(const float* __restrict__ X, int64_t n, int64_t n
             const __half lo = __double2half(u - static_cast<double>(__half2float(hi)));
             const __half mhi = __float2half(-2.f * __half2float(hi));
             const __half mlo = __float2half(-2.f * __half2float(lo));
-            a[c] = hi;         a[d + c] = hi;      a[2 * d + c] = lo;
-            b[c] = mhi;        b[d + c] = mlo;     b[2 * d + c] = mhi;
+            if (layout == 0) {
+                a[c] = hi;  a[d + c] = hi;  a[2 * d + c] = lo;
+                b[c] = mhi; b[d + c] = mlo; b[2 * d + c] = mhi;
+            } else {
+                a[c] = hi;  a[dp + c] = lo;
+                b[c] = mhi; b[dp + c] = mlo;
+            }
         }
         if (lane == 0) {
             const double nn = un2[i] * s2;
             un2[i] = nn;
-            const __half one = __float2half(1.f);
-            a[3 * d] = one; a[3 * d + 1] = one; a[3 * d + 2] = one;
+            if (layout == 0) {
+                const __half one = __float2half(1.f);
+                a[ncol] = one; a[ncol + 1] = one; a[ncol + 2] = one;
+            }
             if (with_norm) {
                 const __half n0 = __double2half(nn);
                 const double r1 = nn - static_cast<double>(__half2float(n0));
                 const __half n1 = __double2half(r1);
                 const double r2 = r1 - static_cast<double>(__half2float(n1));
                 const __half n2 = __double2half(r2);
-                b[3 * d] = n0; b[3 * d + 1] = n1; b[3 * d + 2] = n2;
+                b[ncol] = n0; b[ncol + 1] = n1; b[ncol + 2] = n2;
             }
         }
     }
 }
 
+__global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [1 1 1 0 ...]
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 128 * 64) ones[i] = __float2half((i & 63) < 3 ? 1.f : 0.f);
+}
+
 // ---------------------------------------------------------------------------
-// the sweep
+// sweep, resident-query flavour (d <= 256)
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(tc::NUM_THREADS, 1)
-knn_sweep_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, const SweepParams P) {
+// smem: [A: MH x (2*dp64) chunks | ONES chunk | B ring: stages chunks | sort buffers | barriers | tmem slot]
+// B chunk sequence per 128-row database tile: dp64 hi chunks, dp64 lo chunks, 1 norm chunk.
+template <int MH>
+__global__ void __launch_bounds__(64 + 128 * MH, 1)
+knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
+                   const __grid_constant__ CUtensorMap tmapO, const SweepParams P, const int k16_tail) {
     using namespace tc;
+    constexpr int BN = 128;
+    constexpr int ACC_COLS = MH * BN;          // columns per accumulator stage
+    constexpr int TMEM_COLS = 2 * ACC_COLS;    // double buffered
+    constexpr int EPI_WARPS = 4 * MH;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    // carve: [stages * STAGE_BYTES | sort buffers 4*cap*8 | barriers | tmem slot]
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int stages = P.stages;
-    uint64_t* sortbuf = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(stages) * STAGE_BYTES);
-    uint64_t* bars = sortbuf + 4 * static_cast<size_t>(P.cap);
-    // bars: full[stages], empty[stages], tmem_full[2], tmem_empty[2]
+    const int stages = P.stages, dp64 = P.dp64;
+    const int nA = 2 * dp64;          // A chunks per M half
+    const int nB = 2 * dp64 + 1;      // B chunks per database tile
+    const uint32_t smem_base = ptx::smem_u32(smem);
+    const uint32_t sA = smem_base;                                   // [m][c] -> sA + (m*nA + c)*CHUNK_BYTES
+    const uint32_t sO = sA + MH * nA * CHUNK_BYTES;
+    const uint32_t sB = sO + CHUNK_BYTES;
+    uint64_t* sortbuf = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(MH * nA + 1 + stages) * CHUNK_BYTES);
+    uint64_t* bars = sortbuf + static_cast<size_t>(EPI_WARPS) * P.cap;
     const uint32_t bar_full = ptx::smem_u32(bars);
     const uint32_t bar_empty = ptx::smem_u32(bars + stages);
     const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * stages);
-    const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * stages + ACC_STAGES);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 2 * ACC_STAGES);
+    const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * stages + 2);
+    const uint32_t bar_afull = ptx::smem_u32(bars + 2 * stages + 4);
+    const uint32_t bar_aempty = ptx::smem_u32(bars + 2 * stages + 5);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 6);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t smem_base = ptx::smem_u32(smem);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmapA);
         ptx::prefetch_tmap(&tmapB);
+        ptx::prefetch_tmap(&tmapO);
         for (int s = 0; s < stages; ++s) {
             ptx::mbar_init(bar_full + 8 * s, 1);
             ptx::mbar_init(bar_empty + 8 * s, 1);
         }
-        for (int s = 0; s < ACC_STAGES; ++s) {
+        for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(bar_tfull + 8 * s, 1);
-            ptx::mbar_init(bar_tempty + 8 * s, 4);  // one arrive per epilogue warp
+            ptx::mbar_init(bar_tempty + 8 * s, EPI_WARPS);
         }
+        ptx::mbar_init(bar_afull, 1);
+        ptx::mbar_init(bar_aempty, 1);
         ptx::fence_barrier_init();
     }
     if (warp == 1) {
@@ -192,6 +214,186 @@ knn_sweep_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
 
     if (warp == 0) {
         // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0, aphase = 0;
+            bool first = true;
+            for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+                ptx::mbar_wait(bar_aempty, aphase ^ 1);  // previous query tile fully consumed
+                ptx::mbar_expect_tx(bar_afull, (MH * nA + (first ? 1 : 0)) * CHUNK_BYTES);
+                for (int m = 0; m < MH; ++m) {
+                    const int32_t qrow = static_cast<int32_t>(P.q0 + (static_cast<int64_t>(qt) * MH + m) * BM);
+                    for (int c = 0; c < nA; ++c) ptx::tma_load_2d(sA + (m * nA + c) * CHUNK_BYTES, &tmapA, bar_afull, c * BK, qrow);
+                }
+                if (first) ptx::tma_load_2d(sO, &tmapO, bar_afull, 0, 0);
+                first = false;
+                aphase ^= 1;
+                for (int dt = 0; dt < P.n_dbtiles; ++dt) {
+                    for (int c = 0; c < nB; ++c) {
+                        ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                        ptx::mbar_expect_tx(bar_full + 8 * stage, CHUNK_BYTES);
+                        ptx::tma_load_2d(sB + stage * CHUNK_BYTES, &tmapB, bar_full + 8 * stage, c * BK, dt * BN);
+                        if (++stage == stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_f16(BM, BN);
+            int stage = 0;
+            uint32_t phase = 0, aphase = 0;
+            int as = 0;
+            uint32_t accphase = 0;
+            const uint64_t odesc = ptx::make_smem_desc_sw128(sO);
+            for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+                ptx::mbar_wait(bar_afull, aphase);
+                aphase ^= 1;
+                ptx::tc_fence_after();
+                for (int dt = 0; dt < P.n_dbtiles; ++dt) {
+                    ptx::mbar_wait(bar_tempty + 8 * as, accphase ^ 1);
+                    ptx::tc_fence_after();
+                    for (int c = 0; c < nB; ++c) {
+                        ptx::mbar_wait(bar_full + 8 * stage, phase);
+                        ptx::tc_fence_after();
+                        const uint64_t bdesc = ptx::make_smem_desc_sw128(sB + stage * CHUNK_BYTES);
+#pragma unroll
+                        for (int m = 0; m < MH; ++m) {
+                            const uint32_t tmem_d = tmem_base + as * ACC_COLS + m * BN;
+                            if (c < dp64) {
+                                // database hi chunk c: x query hi chunk c and x query lo chunk c
+                                const int nk = (c == dp64 - 1) ? k16_tail : 4;
+                                const uint64_t ah = ptx::make_smem_desc_sw128(sA + (m * nA + c) * CHUNK_BYTES);
+                                const uint64_t al = ptx::make_smem_desc_sw128(sA + (m * nA + dp64 + c) * CHUNK_BYTES);
+                                for (int kk = 0; kk < nk; ++kk) ptx::umma_f16(tmem_d, ah + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0);
+                                for (int kk = 0; kk < nk; ++kk) ptx::umma_f16(tmem_d, al + 2 * kk, bdesc + 2 * kk, idesc, 1);
+                            } else if (c < 2 * dp64) {
+                                // database lo chunk: x query hi chunk
+                                const int cc = c - dp64;
+                                const int nk = (cc == dp64 - 1) ? k16_tail : 4;
+                                const uint64_t ah = ptx::make_smem_desc_sw128(sA + (m * nA + cc) * CHUNK_BYTES);
+                                for (int kk = 0; kk < nk; ++kk) ptx::umma_f16(tmem_d, ah + 2 * kk, bdesc + 2 * kk, idesc, 1);
+                            } else {
+                                // norm chunk: ones x (n0 n1 n2), one k-step
+                                ptx::umma_f16(tmem_d, odesc, bdesc, idesc, 1);
+                            }
+                        }
+                        ptx::umma_commit(bar_empty + 8 * stage);
+                        if (++stage == stages) { stage = 0; phase ^= 1; }
+                    }
+                    ptx::umma_commit(bar_tfull + 8 * as);
+                    if (++as == 2) { as = 0; accphase ^= 1; }
+                }
+                ptx::umma_commit(bar_aempty);  // query tile consumed: A region may be overwritten
+            }
+        }
+    } else {
+        // ===================== epilogue =====================
+        const int ew = warp - 2;       // 0 .. EPI_WARPS-1
+        const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+        const int mhalf = ew >> 2;
+        uint64_t* sm = sortbuf + static_cast<size_t>(ew) * P.cap;
+        const int cap = P.cap, k = P.k, keep_max = P.keep_max;
+        int as = 0;
+        uint32_t accphase = 0;
+        unsigned long long n_compact = 0, n_accept = 0;
+        for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+            const int row_in_tile = mhalf * BM + quarter * 32 + lane;
+            const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
+            const bool valid = r < P.nq;
+            uint64_t* warp_buf = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + (row_in_tile - lane)) * cap;
+            uint64_t* mybuf = warp_buf + static_cast<size_t>(lane) * cap;
+            RowList me;
+            me.thr = valid ? INFINITY : -INFINITY;
+            me.eps2 = row_eps2(valid ? P.un2[P.q0 + r] : 0.0, P.eps_c1, P.eps_c2, VMAX, VMAX2);
+            me.cnt = 0;
+            me.ovf = 0;
+            for (int dt = 0; dt < P.n_dbtiles; ++dt) {
+                ptx::mbar_wait(bar_tfull + 8 * as, accphase);
+                ptx::tc_fence_after();
+                const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
+#pragma unroll 1
+                for (int c = 0; c < BN / 32; ++c) {
+                    float v[32];
+                    ptx::tmem_ld_32x32(taddr + c * 32, v);
+                    filter_chunk(v, jbase + c * 32, P.n, me, mybuf, n_accept);
+                    compact_full_rows(me, warp_buf, sm, cap, k, keep_max, lane, n_compact);
+                }
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
+                if (++as == 2) { as = 0; accphase ^= 1; }
+            }
+            export_rows(me, r - lane, P.nq, warp_buf, sm, cap, k, keep_max, P.cand_out, P.cnt_out, lane);
+        }
+        if (P.stats) {
+            n_accept = warp_sum(static_cast<double>(n_accept));
+            if (lane == 0) {
+                atomicAdd(P.stats + 0, n_compact);
+                atomicAdd(P.stats + 1, static_cast<unsigned long long>(n_accept));
+            }
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------
+// sweep, streaming flavour (any d; used for d > 256)
+// ---------------------------------------------------------------------------
+namespace tcs {
+constexpr int BN = 256;
+constexpr int A_BYTES = tc::BM * tc::BK * 2;
+constexpr int B_BYTES = BN * tc::BK * 2;
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int TMEM_COLS = 2 * BN;
+constexpr int NUM_THREADS = 192;
+}  // namespace tcs
+
+__global__ void __launch_bounds__(tcs::NUM_THREADS, 1)
+knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, const SweepParams P) {
+    using namespace tc;
+    using namespace tcs;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    const int stages = P.stages;
+    uint64_t* sortbuf = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(stages) * STAGE_BYTES);
+    uint64_t* bars = sortbuf + 4 * static_cast<size_t>(P.cap);
+    const uint32_t bar_full = ptx::smem_u32(bars);
+    const uint32_t bar_empty = ptx::smem_u32(bars + stages);
+    const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * stages);
+    const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * stages + 2);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 4);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t smem_base = ptx::smem_u32(smem);
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmapA);
+        ptx::prefetch_tmap(&tmapB);
+        for (int s = 0; s < stages; ++s) {
+            ptx::mbar_init(bar_full + 8 * s, 1);
+            ptx::mbar_init(bar_empty + 8 * s, 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(bar_tfull + 8 * s, 1);
+            ptx::mbar_init(bar_tempty + 8 * s, 4);
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) {
+        ptx::tmem_alloc(ptx::smem_u32(tmem_slot), TMEM_COLS);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
@@ -210,16 +412,15 @@ knn_sweep_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
         if (lane == 0) {
             constexpr uint32_t idesc = ptx::make_idesc_f16(BM, BN);
             int stage = 0;
             uint32_t phase = 0;
             int as = 0;
-            uint32_t aphase = 0;
+            uint32_t accphase = 0;
             for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
                 for (int dt = 0; dt < P.n_dbtiles; ++dt) {
-                    ptx::mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+                    ptx::mbar_wait(bar_tempty + 8 * as, accphase ^ 1);
                     ptx::tc_fence_after();
                     const uint32_t tmem_d = tmem_base + as * BN;
                     for (int kc = 0; kc < P.kchunks; ++kc) {
@@ -229,136 +430,106 @@ knn_sweep_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                         const uint64_t adesc = ptx::make_smem_desc_sw128(sa);
                         const uint64_t bdesc = ptx::make_smem_desc_sw128(sa + A_BYTES);
                         const int nk = (kc == P.kchunks - 1) ? P.k16_last : (BK / UMMA_K);
-                        for (int kk = 0; kk < nk; ++kk) {
-                            // advance 16 fp16 = 32 B inside the 128 B swizzle span: +2 in the (addr >> 4) field
-                            ptx::umma_f16(tmem_d, adesc + 2 * kk, bdesc + 2 * kk, idesc, (kc | kk) != 0);
-                        }
-                        ptx::umma_commit(bar_empty + 8 * stage);  // frees the smem slot when these MMAs retire
+                        for (int kk = 0; kk < nk; ++kk) ptx::umma_f16(tmem_d, adesc + 2 * kk, bdesc + 2 * kk, idesc, (kc | kk) != 0);
+                        ptx::umma_commit(bar_empty + 8 * stage);
                         if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
-                    ptx::umma_commit(bar_tfull + 8 * as);  // accumulator ready for the epilogue
-                    if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+                    ptx::umma_commit(bar_tfull + 8 * as);
+                    if (++as == 2) { as = 0; accphase ^= 1; }
                 }
             }
         }
     } else {
-        // ===================== epilogue: filter + exact top-k =====================
-        const int quarter = warp & 3;  // TMEM lane quarter this warp may access
-        uint64_t* sm = sortbuf + static_cast<size_t>(warp - 2) * P.cap;
-        const int cap = P.cap, k = P.k;
-        const double s2 = P.scal[0];
-        const double scaleG = (P.metric == METRIC_L2) ? s2 : 2.0 * s2;
+        const int ew = warp - 2;
+        const int quarter = warp & 3;
+        uint64_t* sm = sortbuf + static_cast<size_t>(ew) * P.cap;
+        const int cap = P.cap, k = P.k, keep_max = P.keep_max;
         int as = 0;
-        uint32_t aphase = 0;
+        uint32_t accphase = 0;
         unsigned long long n_compact = 0, n_accept = 0;
-
         for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
             const int row_in_tile = quarter * 32 + lane;
-            const int64_t r = static_cast<int64_t>(qt) * BM + row_in_tile;  // row within the slab
+            const int64_t r = static_cast<int64_t>(qt) * BM + row_in_tile;
             const bool valid = r < P.nq;
-            const int64_t gi = P.q0 + r;  // global point id of my row
-            uint64_t* mybuf = P.cand + (static_cast<size_t>(blockIdx.x) * BM + row_in_tile) * cap;
-            const double my_un2 = valid ? P.un2[gi] : 0.0;
-            const double my_off = (P.metric == METRIC_L2) ? my_un2 : 0.0;
-            const double my_eps = P.eps_c1 * (2.0 * sqrt(my_un2) * VMAX + VMAX2) + P.eps_c2 * (sqrt(my_un2) + VMAX);
-            float thr = valid ? INFINITY : -INFINITY;
-            int cnt = 0;  // entries in mybuf: [0,nk) exact sorted keys, [nk,cnt) new candidate indices
-            int nk = 0;
-
-            // warp-cooperative exact re-rank + sort + truncate of lane L's row
-            auto compact_row = [&](int L) {
-                const int cntL = __shfl_sync(0xffffffffu, cnt, L);
-                const int nkL = __shfl_sync(0xffffffffu, nk, L);
-                const int64_t giL = P.q0 + static_cast<int64_t>(qt) * BM + quarter * 32 + L;
-                uint64_t* buf = P.cand + (static_cast<size_t>(blockIdx.x) * BM + quarter * 32 + L) * cap;
-                for (int t = lane; t < cap; t += 32) {
-                    uint64_t key = ~0ull;
-                    if (t < nkL) key = buf[t];
-                    else if (t < cntL) {
-                        const uint32_t j = static_cast<uint32_t>(buf[t]);
-                        key = make_key(exact_key(P.X, giL, static_cast<int64_t>(j), P.d, P.metric), j);
-                    }
-                    sm[t] = key;
-                }
-                __syncwarp();
-                warp_bitonic_sort(sm, cap, lane);
-                const int newnk = min(k, cntL);
-                for (int t = lane; t < newnk; t += 32) buf[t] = sm[t];
-                if (lane == L) {
-                    cnt = newnk;
-                    nk = newnk;
-                    if (newnk == k) {
-                        const double kv = static_cast<double>(key_val(sm[k - 1]));
-                        const double g = scaleG * kv;
-                        const double t = g + fabs(g) * 2.4e-7 - my_off + my_eps + (fabs(g) + my_off) * 2.4e-7;
-                        thr = __double2float_ru(t);
-                    }
-                }
-                __syncwarp();
-            };
-
+            uint64_t* warp_buf = P.cand + (static_cast<size_t>(blockIdx.x) * BM + quarter * 32) * cap;
+            uint64_t* mybuf = warp_buf + static_cast<size_t>(lane) * cap;
+            RowList me;
+            me.thr = valid ? INFINITY : -INFINITY;
+            me.eps2 = row_eps2(valid ? P.un2[P.q0 + r] : 0.0, P.eps_c1, P.eps_c2, VMAX, VMAX2);
+            me.cnt = 0;
+            me.ovf = 0;
             for (int dt = 0; dt < P.n_dbtiles; ++dt) {
-                ptx::mbar_wait(bar_tfull + 8 * as, aphase);
+                ptx::mbar_wait(bar_tfull + 8 * as, accphase);
                 ptx::tc_fence_after();
                 const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN;
 #pragma unroll 1
                 for (int c = 0; c < BN / 32; ++c) {
                     float v[32];
-                    ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN + c * 32, v);
-                    float m = v[0];
-#pragma unroll
-                    for (int t = 1; t < 32; ++t) m = fminf(m, v[t]);
-                    if (m <= thr) {
-#pragma unroll
-                        for (int t = 0; t < 32; ++t) {
-                            if (v[t] <= thr) {
-                                const uint32_t j = jbase + c * 32 + t;
-                                if (j < P.n) {
-                                    mybuf[cnt++] = j;
-                                    ++n_accept;
-                                }
-                            }
-                        }
-                    }
-                    unsigned full = __ballot_sync(0xffffffffu, cnt > cap - 32);
-                    while (full) {
-                        const int L = __ffs(full) - 1;
-                        full &= full - 1;
-                        compact_row(L);
-                        ++n_compact;
-                    }
+                    ptx::tmem_ld_32x32(taddr + c * 32, v);
+                    filter_chunk(v, jbase + c * 32, P.n, me, mybuf, n_accept);
+                    compact_full_rows(me, warp_buf, sm, cap, k, keep_max, lane, n_compact);
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
-                if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+                if (++as == 2) { as = 0; accphase ^= 1; }
             }
-
-            // finalise the 32 rows of this warp
-            for (int L = 0; L < 32; ++L) {
-                const int64_t rL = static_cast<int64_t>(qt) * BM + quarter * 32 + L;
-                if (rL >= P.nq) break;
-                compact_row(L);
-                const int nkL = __shfl_sync(0xffffffffu, nk, L);
-                write_row(sm, nkL, k, P.q0 + rL, P.metric, P.l2_squared, P.ids + rL * k, P.dist + rL * k, lane);
-                __syncwarp();
+            export_rows(me, r - lane, P.nq, warp_buf, sm, cap, k, keep_max, P.cand_out, P.cnt_out, lane);
+        }
+        if (P.stats) {
+            n_accept = warp_sum(static_cast<double>(n_accept));
+            if (lane == 0) {
+                atomicAdd(P.stats + 0, n_compact);
+                atomicAdd(P.stats + 1, static_cast<unsigned long long>(n_accept));
             }
         }
-        if (lane == 0 && P.stats) {
-            atomicAdd(P.stats + 0, n_compact);
-        }
-        n_accept = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(n_accept & 0xffffffffu));
-        if (lane == 0 && P.stats) atomicAdd(P.stats + 1, n_accept);
     }
-
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 // ---------------------------------------------------------------------------
+// exact re-rank of the surviving candidates (one warp per query row)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) knn_rerank_kernel(const float* __restrict__ X, int d, int k, int cap, int keep_max, int metric,
+                                                         int l2_squared, int64_t q0, int64_t nq, const uint32_t* __restrict__ cand,
+                                                         const int* __restrict__ cnt, int64_t* __restrict__ ids, float* __restrict__ dist,
+                                                         int64_t* __restrict__ ovf_rows, int* __restrict__ ovf_count) {
+    extern __shared__ uint64_t smem_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+    for (int64_t r = gw; r < nq; r += nw) {
+        const int c = cnt[r];
+        if (c & OVERFLOW_FLAG) {
+            if (lane == 0) ovf_rows[atomicAdd(ovf_count, 1)] = q0 + r;
+            continue;
+        }
+        const int m = c;
+        const int64_t gi = q0 + r;
+        for (int t = lane; t < cap; t += 32) {
+            uint64_t key = ~0ull;
+            if (t < m) {
+                const uint32_t j = cand[r * keep_max + t];
+                key = make_key(exact_key(X, gi, static_cast<int64_t>(j), d, metric), j);
+            }
+            sm[t] = key;
+        }
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        write_row(sm, min(m, k), k, gi, metric, l2_squared, ids + r * k, dist + r * k, lane);
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
+int knn_simt_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, const int64_t*, const int*, int64_t, int64_t*, float*, cudaStream_t);
+
 using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
@@ -373,11 +544,12 @@ static EncodeFn get_encode_fn() {
     return fn;
 }
 
-static int make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int kp, int box_rows) {
+// 2-D fp16 row-major [rows, cols] tensor, box = 64 columns x box_rows rows, 128B swizzle, zero OOB fill.
+static int make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t cols, int box_rows) {
     EncodeFn enc = get_encode_fn();
     if (!enc) return fail(3, "cuTensorMapEncodeTiled entry point not found");
-    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(kp), static_cast<cuuint64_t>(rows)};
-    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(kp) * 2};
+    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 2};
     const cuuint32_t box[2] = {static_cast<cuuint32_t>(tc::BK), static_cast<cuuint32_t>(box_rows)};
     const cuuint32_t estr[2] = {1, 1};
     const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -404,40 +576,59 @@ bool knn_tc_supported(int64_t n, int d, int k) {
     return true;
 }
 
+// flavour: 0 auto, 1 force streaming kernel, 2 force resident MH=1 (d <= 256)
 int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1, int64_t* d_ids,
-                  float* d_dist, cudaStream_t stream) {
+                  float* d_dist, cudaStream_t stream, int flavour) {
     using namespace tc;
     const int64_t nq = q1 - q0;
     if (nq <= 0) return 0;
     const int centre = metric == METRIC_L2 ? 1 : 0;
-    const int kp = ((3 * d + 3) + 15) / 16 * 16;
-    const int64_t np = (n + BN - 1) / BN * BN;
+    const int sms = ctx().num_sms;
     const int cap = next_pow2_i(k + 96);
-    const int kchunks = (kp + BK - 1) / BK;
-    const int k16_last = (kp - (kchunks - 1) * BK) / UMMA_K;
-    const int n_qtiles = static_cast<int>((nq + BM - 1) / BM);
-    const int n_dbtiles = static_cast<int>(np / BN);
-    const int grid = std::min(ctx().num_sms, n_qtiles);
+    const int keep_max = cap - 64;
+
+    // ---- choose the kernel flavour and the operand layout
+    const int dp = (d + 63) / 64 * 64;
+    int MH = 0;  // 0 = streaming
+    if (flavour != 1 && dp <= 256) MH = (dp <= 128 && flavour != 2) ? 2 : 1;
+    const int layout = MH ? 1 : 0;
+    const int kp = ((3 * d + 3) + 15) / 16 * 16;  // streaming K extent
+    const int lda = MH ? 2 * dp : kp;
+    const int ldb = MH ? 2 * dp + 64 : kp;
+    const int bn = MH ? 128 : tcs::BN;
+    const int64_t np = (n + 255) / 256 * 256;
+    const int rows_per_cta = MH ? MH * BM : BM;
+    const int n_qtiles = static_cast<int>((nq + rows_per_cta - 1) / rows_per_cta);
+    const int n_dbtiles = static_cast<int>(np / bn);
+    const int grid = std::min(sms, n_qtiles);
 
     DevBuf<double> colsum, un2, scal;
     DevBuf<unsigned long long> maxbits, stats;
-    DevBuf<__half> A, B;
+    DevBuf<__half> A, B, ones;
     DevBuf<uint64_t> cand;
+    DevBuf<uint32_t> cand_out;
+    DevBuf<int> cnt_out, ovf_count;
+    DevBuf<int64_t> ovf_rows;
     SPHB_CUDA(colsum.alloc(d, stream));
     SPHB_CUDA(un2.alloc(n, stream));
     SPHB_CUDA(scal.alloc(2, stream));
     SPHB_CUDA(maxbits.alloc(1, stream));
     SPHB_CUDA(stats.alloc(2, stream));
-    SPHB_CUDA(A.alloc(static_cast<size_t>(np) * kp, stream));
-    SPHB_CUDA(B.alloc(static_cast<size_t>(np) * kp, stream));
-    SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * BM * cap, stream));
+    SPHB_CUDA(A.alloc(static_cast<size_t>(np) * lda, stream));
+    SPHB_CUDA(B.alloc(static_cast<size_t>(np) * ldb, stream));
+    SPHB_CUDA(ones.alloc(128 * 64, stream));
+    SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * rows_per_cta * cap, stream));
+    SPHB_CUDA(cand_out.alloc(static_cast<size_t>(nq) * keep_max, stream));
+    SPHB_CUDA(cnt_out.alloc(nq, stream));
+    SPHB_CUDA(ovf_count.alloc(1, stream));
+    SPHB_CUDA(ovf_rows.alloc(nq, stream));
     SPHB_CUDA(cudaMemsetAsync(colsum.p, 0, d * sizeof(double), stream));
     SPHB_CUDA(cudaMemsetAsync(maxbits.p, 0, sizeof(unsigned long long), stream));
     SPHB_CUDA(cudaMemsetAsync(stats.p, 0, 2 * sizeof(unsigned long long), stream));
-    SPHB_CUDA(cudaMemsetAsync(A.p, 0, static_cast<size_t>(np) * kp * sizeof(__half), stream));
-    SPHB_CUDA(cudaMemsetAsync(B.p, 0, static_cast<size_t>(np) * kp * sizeof(__half), stream));
+    SPHB_CUDA(cudaMemsetAsync(ovf_count.p, 0, sizeof(int), stream));
+    SPHB_CUDA(cudaMemsetAsync(A.p, 0, static_cast<size_t>(np) * lda * sizeof(__half), stream));
+    SPHB_CUDA(cudaMemsetAsync(B.p, 0, static_cast<size_t>(np) * ldb * sizeof(__half), stream));
 
-    const int sms = ctx().num_sms;
     if (centre) {
         dim3 g(static_cast<unsigned>(std::min<int64_t>(n, sms * 8)), static_cast<unsigned>((d + 127) / 128));
         knn_prep_colsum<<<g, 128, 0, stream>>>(d_x, n, d, colsum.p);
@@ -445,39 +636,82 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     }
     knn_prep_norms<<<sms * 8, 256, 0, stream>>>(d_x, n, d, colsum.p, centre, un2.p, maxbits.p);
     knn_prep_scale<<<1, 1, 0, stream>>>(maxbits.p, scal.p);
-    knn_prep_split<<<sms * 8, 256, 0, stream>>>(d_x, n, np, d, kp, colsum.p, centre, metric == METRIC_L2 ? 1 : 0, scal.p, un2.p, A.p, B.p);
-    count_launch(3);
+    knn_prep_split<<<sms * 8, 256, 0, stream>>>(d_x, n, np, d, layout, lda, ldb, dp, colsum.p, centre, metric == METRIC_L2 ? 1 : 0, scal.p,
+                                                un2.p, A.p, B.p);
+    knn_prep_ones<<<32, 256, 0, stream>>>(ones.p);
+    count_launch(4);
     SPHB_CUDA(cudaGetLastError());
 
-    CUtensorMap tmA, tmB;
-    if (int rc = make_tmap(&tmA, A.p, np, kp, BM)) return rc;
-    if (int rc = make_tmap(&tmB, B.p, np, kp, BN)) return rc;
-
-    // shared memory budget: pipeline stages + sort buffers + barriers
-    const size_t fixed = 4 * static_cast<size_t>(cap) * 8 + 256 + 1024;
-    int stages = 4;
-    while (stages > 2 && static_cast<size_t>(stages) * STAGE_BYTES + fixed > 227 * 1024) --stages;
-    const size_t smem = static_cast<size_t>(stages) * STAGE_BYTES + fixed;
-    SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-
     SweepParams P{};
-    P.X = d_x; P.un2 = un2.p; P.scal = scal.p; P.n = n; P.d = d; P.k = k; P.cap = cap; P.metric = metric; P.l2_squared = l2_squared;
-    P.q0 = q0; P.nq = nq; P.n_qtiles = n_qtiles; P.n_dbtiles = n_dbtiles; P.kchunks = kchunks; P.k16_last = k16_last; P.stages = stages;
-    // GEMM error bound: split truncation 6·2^-22 + accumulation (kp/16 steps)·2^-22,
+    P.un2 = un2.p; P.n = n; P.k = k; P.cap = cap; P.keep_max = keep_max; P.metric = metric;
+    P.q0 = q0; P.nq = nq; P.n_qtiles = n_qtiles; P.n_dbtiles = n_dbtiles;
+    P.cand = cand.p; P.cand_out = cand_out.p; P.cnt_out = cnt_out.p; P.stats = stats.p;
+    // GEMM error bound: split truncation 6·2^-22 + accumulation (one 2^-22 per k-step),
     // times the magnitude (2|u||v| + |v|²); plus the fp16 subnormal floor; safety factor 2.
-    const double nsteps = static_cast<double>(kp / UMMA_K);
-    P.eps_c1 = 2.0 * (6.0 + nsteps) * std::ldexp(1.0, -22);
+    const int ksteps = MH ? (3 * dp / UMMA_K + 1) : kp / UMMA_K;
+    P.eps_c1 = 2.0 * (6.0 + ksteps) * std::ldexp(1.0, -22);
     P.eps_c2 = 2.0 * std::ldexp(1.0, -23) * std::sqrt(static_cast<double>(d));
-    P.cand = cand.p; P.ids = d_ids; P.dist = d_dist; P.stats = stats.p;
 
-    knn_sweep_kernel<<<grid, NUM_THREADS, smem, stream>>>(tmA, tmB, P);
+    CUtensorMap tmA, tmB, tmO;
+    if (int rc = make_tmap(&tmA, A.p, np, lda, BM)) return rc;
+    if (int rc = make_tmap(&tmB, B.p, np, ldb, bn)) return rc;
+    if (int rc = make_tmap(&tmO, ones.p, 128, 64, 128)) return rc;
+
+    const size_t smem_limit = 227 * 1024;
+    if (MH) {
+        const int dp64 = dp / 64;
+        const int epi_warps = 4 * MH;
+        const size_t fixed = static_cast<size_t>(MH * 2 * dp64 + 1) * CHUNK_BYTES + static_cast<size_t>(epi_warps) * cap * 8 + 256 + 1024;
+        int stages = 8;
+        while (stages > 2 && fixed + static_cast<size_t>(stages) * CHUNK_BYTES > smem_limit) --stages;
+        const size_t smem = fixed + static_cast<size_t>(stages) * CHUNK_BYTES;
+        if (smem > smem_limit) return fail(5, "knn: shared memory budget exceeded (k too large for the resident kernel)");
+        P.dp64 = dp64; P.stages = stages;
+        const int tail = d - 64 * (dp64 - 1);
+        const int k16_tail = (tail + 15) / 16;
+        if (MH == 2) {
+            SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+            knn_sweep_resident<2><<<grid, 64 + 128 * 2, smem, stream>>>(tmA, tmB, tmO, P, k16_tail);
+        } else {
+            SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+            knn_sweep_resident<1><<<grid, 64 + 128, smem, stream>>>(tmA, tmB, tmO, P, k16_tail);
+        }
+    } else {
+        const int kchunks = (kp + BK - 1) / BK;
+        P.kchunks = kchunks;
+        P.k16_last = (kp - (kchunks - 1) * BK) / UMMA_K;
+        const size_t fixed = 4 * static_cast<size_t>(cap) * 8 + 256 + 1024;
+        int stages = 4;
+        while (stages > 2 && static_cast<size_t>(stages) * tcs::STAGE_BYTES + fixed > smem_limit) --stages;
+        P.stages = stages;
+        const size_t smem = static_cast<size_t>(stages) * tcs::STAGE_BYTES + fixed;
+        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        knn_sweep_stream<<<grid, tcs::NUM_THREADS, smem, stream>>>(tmA, tmB, P);
+    }
     count_launch();
     SPHB_CUDA(cudaGetLastError());
 
+    {
+        const size_t smem = 8 * static_cast<size_t>(cap) * sizeof(uint64_t);
+        SPHB_CUDA(cudaFuncSetAttribute(knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        const int64_t blocks = std::min<int64_t>((nq + 7) / 8, static_cast<int64_t>(sms) * 8);
+        knn_rerank_kernel<<<static_cast<unsigned>(blocks), 256, smem, stream>>>(d_x, d, k, cap, keep_max, metric, l2_squared, q0, nq, cand_out.p,
+                                                                                 cnt_out.p, d_ids, d_dist, ovf_rows.p, ovf_count.p);
+        count_launch();
+        SPHB_CUDA(cudaGetLastError());
+    }
+
     unsigned long long hstats[2] = {0, 0};
+    int hovf = 0;
     SPHB_CUDA(cudaMemcpyAsync(hstats, stats.p, sizeof(hstats), cudaMemcpyDeviceToHost, stream));
+    SPHB_CUDA(cudaMemcpyAsync(&hovf, ovf_count.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
     SPHB_CUDA(cudaStreamSynchronize(stream));
-    const int64_t st[6] = {1, static_cast<int64_t>(hstats[0]), static_cast<int64_t>(hstats[1]), kp, n_dbtiles, n_qtiles};
+    if (hovf > 0) {
+        // rows whose candidate band overflowed (massive ties): exact SIMT recompute, never a truncated answer
+        if (int rc = knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, ovf_rows.p, ovf_count.p, hovf, d_ids, d_dist, stream)) return rc;
+        SPHB_CUDA(cudaStreamSynchronize(stream));
+    }
+    const int64_t st[6] = {1 + MH, static_cast<int64_t>(hstats[0]), static_cast<int64_t>(hstats[1]), MH ? 3 * dp + 16 : kp, hovf, n_qtiles};
     knn_set_stats(st);
     return 0;
 }

@@ -52,13 +52,17 @@ def test_simt_duplicates_and_ties(capi, oracle):
     _check(capi, oracle, x, 16, path=1, l2_squared=True)
 
 
-@pytest.mark.parametrize("n,d,k", [(2048, 32, 16), (4100, 128, 91), (3000, 200, 91), (2500, 21, 5)])
-def test_tc_matches_oracle(capi, oracle, n, d, k):
+# path 2: auto flavour (resident MH=2 for d<=128, MH=1 for d<=256, streaming above), 3: streaming, 4: resident MH=1
+@pytest.mark.parametrize("n,d,k,path,flavour", [
+    (2048, 32, 16, 2, 3), (4100, 128, 91, 2, 3), (3000, 200, 91, 2, 2), (2500, 21, 5, 2, 3), (2300, 300, 40, 2, 1),
+    (4100, 128, 91, 3, 1), (2500, 21, 5, 3, 1), (3000, 100, 30, 4, 2), (2048, 64, 301, 2, 3),
+])
+def test_tc_matches_oracle(capi, oracle, n, d, k, path, flavour):
     rng = np.random.default_rng(n * 7 + d)
     x = (rng.standard_normal((n, d)) * 0.3 + rng.uniform(0, 1, (1, d))).astype(np.float32)
-    _check(capi, oracle, x, k, path=2)
+    _check(capi, oracle, x, k, path=path)
     st = capi.knn_last_stats()
-    assert st["tensor_core"] == 1
+    assert st["tensor_core"] == flavour
 
 
 def test_tc_hyperspectral_c1_shape(capi, oracle):
@@ -75,6 +79,11 @@ def test_tc_duplicates(capi, oracle):
     x = np.concatenate([base, base, base[:300], np.round(base * 4) / 4])  # exact duplicates + a coarse lattice
     _check(capi, oracle, x, 8, path=2)
     _check(capi, oracle, x, 130, path=2)
+    _check(capi, oracle, x, 8, path=3)
+    # heavy ties: 64 copies of each of 40 points -> the candidate band overflows and rows fall back to the exact kernel
+    y = np.repeat(rng.standard_normal((40, 16)).astype(np.float32), 64, axis=0)
+    _check(capi, oracle, y, 100, path=2)
+    assert capi.knn_last_stats()["overflow_rows"] >= 0
 
 
 def test_tc_equals_simt_on_device(capi):
