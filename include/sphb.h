@@ -94,6 +94,18 @@ SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int m
  * [2] candidates accepted by the filter, [3] executed GEMM K extent per pair,
  * [4] rows recomputed by the exact SIMT kernel (candidate band overflow), [5] query tiles. */
 SPHB_API int sphb_knn_last_stats(int64_t* out6);
+/* device time of the last tensor-core kNN call in ms (CUDA events on its stream): [0] operand
+ * preparation, [1] the tcgen05 sweep kernel, [2] the exact re-rank kernel. */
+SPHB_API int sphb_knn_last_timing(float* ms3);
+/*
+ * Stage A followed by the level-0 P rows of Stage B in one call — the pair
+ * ComputeHierarchy::compute() runs back to back (computeKnnGraph, sph/ComputeHierarchy.cpp:97-159,
+ * then ImageHierarchy::computePreparations -> normalizeKnnDistances, sph/ImageHierarchy.cpp:153).
+ * x goes up once, the graph stays in HBM between the stages, the four outputs come back once.
+ * Query rows [q0,q1): ids/dist (q1-q0)*k, cols/vals (q1-q0)*(k-1).
+ */
+SPHB_API int sphb_knn_graph_prow(const float* x, int64_t n, int d, int k, int metric, int l2_squared, float perplexity,
+                                 int64_t q0, int64_t q1, int64_t* ids, float* dist, uint32_t* cols, float* vals);
 
 /* ---- Stage B: perplexity-calibrated probability rows -------------------- */
 /*

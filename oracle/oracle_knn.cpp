@@ -101,7 +101,12 @@ ORC_API void orc_renorm_l2(const float* x, int64_t n, int d, float* out) {
 // Post-passes in the order NearestNeighbors::compute applies them
 // (sph/NearestNeighbors.cpp:152-167): A6 eps clamp, A7 sqrt, A8 monotone
 // re-sort (stable by distance), A9 self first.  Returns the number of rows A9 adjusted.
+// row_ids (optional): the point id of each row (a slab of query rows); default row r <-> point r.
+ORC_API int64_t orc_knn_postprocess_rows(int64_t* ids, float* dist, int64_t n, int k, int l2squared, const int64_t* row_ids);
 ORC_API int64_t orc_knn_postprocess(int64_t* ids, float* dist, int64_t n, int k, int l2squared) {
+    return orc_knn_postprocess_rows(ids, dist, n, k, l2squared, nullptr);
+}
+ORC_API int64_t orc_knn_postprocess_rows(int64_t* ids, float* dist, int64_t n, int k, int l2squared, const int64_t* row_ids) {
     const int64_t total = n * static_cast<int64_t>(k);
     // A6: ensureFloatingPointIntegrity (NearestNeighbors.cpp:233-242)
     for (int64_t e = 0; e < total; ++e)
@@ -129,9 +134,10 @@ ORC_API int64_t orc_knn_postprocess(int64_t* ids, float* dist, int64_t n, int k,
     }
     // A9: ensureClosestPointIsSelf (GraphUtils.cpp:23-95)
     int64_t adjusted = 0;
-    for (int64_t p = 0; p < n; ++p) {
-        float* dp = dist + p * k;
-        int64_t* ip = ids + p * k;
+    for (int64_t row = 0; row < n; ++row) {
+        const int64_t p = row_ids ? row_ids[row] : row;
+        float* dp = dist + row * k;
+        int64_t* ip = ids + row * k;
         if (ip[0] == p) continue;
         int swap_pos = k - 1;
         int found = -1;

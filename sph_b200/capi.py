@@ -39,6 +39,8 @@ SIGNATURES = {
     "sphb_knn_exact_slab": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, i64p, f32p]),
     "sphb_knn_exact_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sphb_knn_last_stats": (C.c_int, [i64p]),
+    "sphb_knn_last_timing": (C.c_int, [f32p]),
+    "sphb_knn_graph_prow": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int64, i64p, f32p, u32p, f32p]),
     "sphb_prow_gaussian_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, C.c_float, u32p, f32p, f64p]),
     "sphb_prow_gaussian_graph_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sphb_prow_linear_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, u32p, f32p]),
@@ -114,6 +116,26 @@ def knn_last_stats() -> dict:
     out = np.zeros(6, np.int64)
     _check(load().sphb_knn_last_stats(_p(out, i64p)))
     return dict(tensor_core=int(out[0]), compactions=int(out[1]), accepted=int(out[2]), kp=int(out[3]), overflow_rows=int(out[4]), q_tiles=int(out[5]))
+
+
+def knn_last_timing() -> dict:
+    out = np.zeros(3, np.float32)
+    _check(load().sphb_knn_last_timing(_p(out, f32p)))
+    return dict(prep_ms=float(out[0]), sweep_ms=float(out[1]), rerank_ms=float(out[2]))
+
+
+def knn_graph_prow(x: np.ndarray, k: int, perplexity: float = 0.0, metric: int = METRIC_L2, l2_squared: bool = False, q0: int = 0,
+                   q1: int | None = None, out=None):
+    """Stage A + level-0 P rows through the host-buffer entry point; `out` = (ids, dist, cols, vals) to reuse (e.g. pinned) buffers."""
+    n, d = x.shape
+    q1 = n if q1 is None else q1
+    nq = q1 - q0
+    if out is None:
+        out = (np.empty((nq, k), np.int64), np.empty((nq, k), np.float32), np.empty((nq, k - 1), np.uint32), np.empty((nq, k - 1), np.float32))
+    ids, dist, cols, vals = out
+    _check(load().sphb_knn_graph_prow(_p(x, f32p), n, d, k, metric, int(l2_squared), perplexity, q0, q1, _p(ids, i64p), _p(dist, f32p),
+                                      _p(cols, u32p), _p(vals, f32p)))
+    return out
 
 
 # ------------------------------------------------------------------ Stage A

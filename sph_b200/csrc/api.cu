@@ -31,6 +31,7 @@ int knn_tc_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, i
 bool knn_tc_supported(int64_t n, int d, int k);
 void knn_set_stats(const int64_t* s);
 void knn_get_stats(int64_t* s);
+void knn_get_timing(float* ms3);
 int prow_graph_launch(const int64_t*, const float*, int64_t, int, float, int, uint32_t*, float*, double*, cudaStream_t);
 int prow_inplace_launch(int64_t, const int64_t*, float*, int, float, int, cudaStream_t);
 int prow_flat_launch(const float*, int64_t, int, double, float*, cudaStream_t);
@@ -138,6 +139,41 @@ SPHB_API int sphb_knn_exact(const float* x, int64_t n, int d, int k, int metric,
 SPHB_API int sphb_knn_last_stats(int64_t* out6) {
     if (!out6) return fail(SPHB_ERR_INVALID, "null pointer");
     knn_get_stats(out6);
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_knn_last_timing(float* ms3) {
+    if (!ms3) return fail(SPHB_ERR_INVALID, "null pointer");
+    knn_get_timing(ms3);
+    return SPHB_OK;
+}
+
+// Stage A + level-0 P rows in one call: x goes up once, the graph stays in HBM between the two
+// stages, (ids, dist, cols, vals) come back once.
+SPHB_API int sphb_knn_graph_prow(const float* x, int64_t n, int d, int k, int metric, int l2_squared, float perplexity, int64_t q0, int64_t q1,
+                                 int64_t* ids, float* dist, uint32_t* cols, float* vals) {
+    if (int rc = ensure_init()) return rc;
+    if (!x || !ids || !dist || !cols || !vals) return fail(SPHB_ERR_INVALID, "knn_graph_prow: null pointer");
+    if (n <= 0 || d <= 0 || k < 2 || q0 < 0 || q1 > n || q0 > q1) return fail(SPHB_ERR_INVALID, "knn_graph_prow: bad sizes");
+    cudaStream_t s = g_ctx.stream;
+    const size_t nq = static_cast<size_t>(q1 - q0);
+    DevBuf<float> dx, ddist, dvals;
+    DevBuf<int64_t> dids;
+    DevBuf<uint32_t> dcols;
+    SPHB_CUDA(dx.alloc(static_cast<size_t>(n) * d, s));
+    SPHB_CUDA(dids.alloc(nq * k, s));
+    SPHB_CUDA(ddist.alloc(nq * k, s));
+    SPHB_CUDA(dcols.alloc(nq * (k - 1), s));
+    SPHB_CUDA(dvals.alloc(nq * (k - 1), s));
+    SPHB_CUDA(cudaMemcpyAsync(dx.p, x, static_cast<size_t>(n) * d * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (int rc = sphb_knn_exact_dev(dx.p, n, d, k, metric, l2_squared, q0, q1, dids.p, ddist.p, s)) return rc;
+    // the rows of a slab are points q0.., but prow only uses ids for the column labels, so the slab graph can be fed as is
+    if (int rc = prow_graph_launch(dids.p, ddist.p, static_cast<int64_t>(nq), k, perplexity, 0, dcols.p, dvals.p, nullptr, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(ids, dids.p, nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(dist, ddist.p, nq * k * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(cols, dcols.p, nq * (k - 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(vals, dvals.p, nq * (k - 1) * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
     return SPHB_OK;
 }
 

@@ -565,6 +565,13 @@ static int next_pow2_i(int v) {
 }
 
 static int64_t g_knn_stats[6] = {0, 0, 0, 0, 0, 0};
+static float g_knn_ms[3] = {0.f, 0.f, 0.f};  // prep, sweep, rerank (CUDA events on the launching stream)
+void knn_get_timing(float* ms3) { for (int i = 0; i < 3; ++i) ms3[i] = g_knn_ms[i]; }
+struct EventQuad {
+    cudaEvent_t e[4] = {nullptr, nullptr, nullptr, nullptr};
+    EventQuad() { for (auto& x : e) cudaEventCreate(&x); }
+    ~EventQuad() { for (auto& x : e) if (x) cudaEventDestroy(x); }
+};
 void knn_set_stats(const int64_t* s) { for (int i = 0; i < 6; ++i) g_knn_stats[i] = s[i]; }
 void knn_get_stats(int64_t* s) { for (int i = 0; i < 6; ++i) s[i] = g_knn_stats[i]; }
 
@@ -629,6 +636,8 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     SPHB_CUDA(cudaMemsetAsync(A.p, 0, static_cast<size_t>(np) * lda * sizeof(__half), stream));
     SPHB_CUDA(cudaMemsetAsync(B.p, 0, static_cast<size_t>(np) * ldb * sizeof(__half), stream));
 
+    EventQuad ev;
+    cudaEventRecord(ev.e[0], stream);
     if (centre) {
         dim3 g(static_cast<unsigned>(std::min<int64_t>(n, sms * 8)), static_cast<unsigned>((d + 127) / 128));
         knn_prep_colsum<<<g, 128, 0, stream>>>(d_x, n, d, colsum.p);
@@ -658,6 +667,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     if (int rc = make_tmap(&tmO, ones.p, 128, 64, 128)) return rc;
 
     const size_t smem_limit = 227 * 1024;
+    cudaEventRecord(ev.e[1], stream);
     if (MH) {
         const int dp64 = dp / 64;
         const int epi_warps = 4 * MH;
@@ -690,6 +700,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     }
     count_launch();
     SPHB_CUDA(cudaGetLastError());
+    cudaEventRecord(ev.e[2], stream);
 
     {
         const size_t smem = 8 * static_cast<size_t>(cap) * sizeof(uint64_t);
@@ -701,11 +712,13 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         SPHB_CUDA(cudaGetLastError());
     }
 
+    cudaEventRecord(ev.e[3], stream);
     unsigned long long hstats[2] = {0, 0};
     int hovf = 0;
     SPHB_CUDA(cudaMemcpyAsync(hstats, stats.p, sizeof(hstats), cudaMemcpyDeviceToHost, stream));
     SPHB_CUDA(cudaMemcpyAsync(&hovf, ovf_count.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
     SPHB_CUDA(cudaStreamSynchronize(stream));
+    for (int i = 0; i < 3; ++i) cudaEventElapsedTime(&g_knn_ms[i], ev.e[i], ev.e[i + 1]);
     if (hovf > 0) {
         // rows whose candidate band overflowed (massive ties): exact SIMT recompute, never a truncated answer
         if (int rc = knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, ovf_rows.p, ovf_count.p, hovf, d_ids, d_dist, stream)) return rc;

@@ -42,6 +42,8 @@ class Oracle:
         L.orc_renorm_l2.argtypes = [f32p, C.c_int64, C.c_int, f32p]
         L.orc_knn_postprocess.argtypes = [i64p, f32p, C.c_int64, C.c_int, C.c_int]
         L.orc_knn_postprocess.restype = C.c_int64
+        L.orc_knn_postprocess_rows.argtypes = [i64p, f32p, C.c_int64, C.c_int, C.c_int, i64p]
+        L.orc_knn_postprocess_rows.restype = C.c_int64
         L.orc_check_all_neighbors_exist.argtypes = [i64p, C.c_int64]
         L.orc_blas_init.argtypes = [C.c_char_p]
         L.orc_knn_blas_l2.argtypes = [f32p, C.c_int64, C.c_int, C.c_int, C.c_int64, C.c_int64, i64p, f32p]
@@ -87,15 +89,8 @@ class Oracle:
         n, k = ids.shape
         if row_ids is None:
             return int(self.lib.orc_knn_postprocess(_p(ids, i64p), _p(dist, f32p), n, k, int(l2_squared)))
-        adj = 0
-        for r, p in enumerate(row_ids):
-            # run the pass on a one-row view whose "point id" is p: shift ids so that p maps to row 0
-            i1 = (ids[r:r + 1] - p).copy()
-            d1 = dist[r:r + 1].copy()
-            adj += int(self.lib.orc_knn_postprocess(_p(i1, i64p), _p(d1, f32p), 1, k, int(l2_squared)))
-            ids[r] = i1[0] + p
-            dist[r] = d1[0]
-        return adj
+        row_ids = np.ascontiguousarray(row_ids, np.int64)
+        return int(self.lib.orc_knn_postprocess_rows(_p(ids, i64p), _p(dist, f32p), n, k, int(l2_squared), _p(row_ids, i64p)))
 
     def knn_reference_graph(self, x, k, l2_squared=False, rows=None, metric=1):
         ids, dist = self.knn_exact(x, k, metric, rows)

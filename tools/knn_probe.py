@@ -15,7 +15,8 @@ dx = torch.from_numpy(x).cuda()
 ids = torch.empty((nq, k), dtype=torch.int64, device="cuda")
 dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
 s = torch.cuda.current_stream().cuda_stream
-for it in range(3):
+import os
+for it in range(int(os.environ.get("PROBE_ITERS", "3"))):
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
     e0.record()
