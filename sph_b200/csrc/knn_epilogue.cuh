@@ -26,21 +26,79 @@ struct RowList {
     int ovf;     // overflow flag
 };
 
-// Sort + band-truncate the list of lane L's row (whole warp participates).
-__device__ __forceinline__ void compact_row_approx(RowList& me, int L, uint64_t* __restrict__ buf_L, uint64_t* sm, int cap, int k, int keep_max,
+// Ascending bitonic sort of 32*R u64 keys held in registers, element e = lane*R + r.
+// Partner distances below R are register swaps, the others one 64-bit shuffle per key.
+// The stage loops are real loops (only the per-register work is unrolled): a fully unrolled
+// network is ~3000 instructions per call site and thrashes the instruction cache.
+template <int R, int J2>
+__device__ __forceinline__ void bitonic_inlane_stage(uint64_t (&x)[R], int lane, int k2) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        if ((r & J2) == 0) {
+            const bool up = (((lane * R + r) & k2) == 0);
+            const uint64_t a = x[r], b = x[r | J2];
+            const bool sw = (a > b) == up;
+            x[r] = sw ? b : a;
+            x[r | J2] = sw ? a : b;
+        }
+    }
+}
+template <int R, int J2>
+__device__ __forceinline__ void bitonic_inlane_from(uint64_t (&x)[R], int lane, int k2) {
+    // stages j2 = J2, J2/2, ..., 1, skipping those with j2 >= k2
+    if constexpr (J2 >= 1) {
+        if (J2 < k2) bitonic_inlane_stage<R, J2>(x, lane, k2);
+        bitonic_inlane_from<R, J2 / 2>(x, lane, k2);
+    }
+}
+template <int R>
+__device__ __forceinline__ void warp_bitonic_sort_regs(uint64_t (&x)[R], int lane) {
+#pragma unroll 1
+    for (int k2 = 2; k2 <= 32 * R; k2 <<= 1) {
+#pragma unroll 1
+        for (int lj = (k2 >> 1) / R; lj > 0; lj >>= 1) {  // cross-lane stages, partner lane = lane ^ lj
+            const bool lower = (lane & lj) == 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const uint64_t other = __shfl_xor_sync(0xffffffffu, x[r], lj);
+                const bool up = (((lane * R + r) & k2) == 0);
+                const bool keep_min = (lower == up);
+                const uint64_t mn = x[r] < other ? x[r] : other;
+                const uint64_t mx = x[r] < other ? other : x[r];
+                x[r] = keep_min ? mn : mx;
+            }
+        }
+        bitonic_inlane_from<R, R / 2>(x, lane, k2);
+    }
+}
+
+// Sort + band-truncate the list of lane L's row (whole warp participates); the sorted keys stay in
+// x[] (element e = lane*R + r) for the caller.  cap = 32*R.
+template <int R>
+__device__ __forceinline__ void compact_row_approx(RowList& me, int L, uint64_t* __restrict__ buf_L, uint64_t (&x)[R], int k, int keep_max,
                                                    int lane) {
     const int cntL = __shfl_sync(0xffffffffu, me.cnt, L);
     const float eps2L = __shfl_sync(0xffffffffu, me.eps2, L);
-    for (int t = lane; t < cap; t += 32) sm[t] = (t < cntL) ? buf_L[t] : ~0ull;
-    __syncwarp();
-    warp_bitonic_sort(sm, cap, lane);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int e = lane * R + r;
+        x[r] = (e < cntL) ? buf_L[e] : ~0ull;
+    }
+    warp_bitonic_sort_regs<R>(x, lane);
     int m = cntL;
     float limit = INFINITY;
     int ovf = 0;
     if (cntL >= k) {
-        limit = __fadd_ru(key_val(sm[k - 1]), eps2L);
+        // k-th smallest key lives in lane (k-1)/R, register (k-1)%R
+        uint64_t kth = 0;
+        const int kr = (k - 1) % R;
+#pragma unroll
+        for (int r = 0; r < R; ++r) kth = (r == kr) ? x[r] : kth;
+        kth = __shfl_sync(0xffffffffu, kth, (k - 1) / R);
+        limit = __fadd_ru(key_val(kth), eps2L);
         int c = 0;
-        for (int t = lane; t < cap; t += 32) c += (t < cntL && key_val(sm[t]) <= limit) ? 1 : 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) c += (lane * R + r < cntL && key_val(x[r]) <= limit) ? 1 : 0;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
         m = c;
@@ -49,7 +107,11 @@ __device__ __forceinline__ void compact_row_approx(RowList& me, int L, uint64_t*
             ovf = 1;
         }
     }
-    for (int t = lane; t < m; t += 32) buf_L[t] = sm[t];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int e = lane * R + r;
+        if (e < m) buf_L[e] = x[r];
+    }
     if (lane == L) {
         me.cnt = m;
         me.thr = limit;
@@ -59,48 +121,70 @@ __device__ __forceinline__ void compact_row_approx(RowList& me, int L, uint64_t*
 }
 
 // Filter one 32-column chunk of the accumulator tile held in v[] (columns jbase..jbase+31).
-__device__ __forceinline__ void filter_chunk(const float (&v)[32], uint32_t jbase, int64_t n, RowList& me, uint64_t* __restrict__ mybuf,
+// Fast path: 8 group minima (4 columns each) + their minimum, one compare.  Slow path (some
+// column passes): only the groups whose minimum passes are scanned.
+__device__ __forceinline__ void filter_chunk(const float (&v)[32], uint32_t jbase, uint32_t n, RowList& me, uint64_t* __restrict__ mybuf,
                                              unsigned long long& n_accept) {
-    float m = v[0];
+    float g[8];
 #pragma unroll
-    for (int t = 1; t < 32; ++t) m = fminf(m, v[t]);
+    for (int q = 0; q < 8; ++q) g[q] = fminf(fminf(v[4 * q], v[4 * q + 1]), fminf(v[4 * q + 2], v[4 * q + 3]));
+    const float m = fminf(fminf(fminf(g[0], g[1]), fminf(g[2], g[3])), fminf(fminf(g[4], g[5]), fminf(g[6], g[7])));
     if (m <= me.thr) {
+        const float thr = me.thr;
+        int cnt = me.cnt;
 #pragma unroll
-        for (int t = 0; t < 32; ++t) {
-            if (v[t] <= me.thr) {
-                const uint32_t j = jbase + t;
-                if (j < n) {
-                    mybuf[me.cnt++] = make_key(v[t], j);
-                    ++n_accept;
+        for (int q = 0; q < 8; ++q) {
+            if (g[q] <= thr) {
+#pragma unroll
+                for (int t = 4 * q; t < 4 * q + 4; ++t) {
+                    const uint32_t j = jbase + t;
+                    if (v[t] <= thr && j < n) mybuf[cnt++] = make_key(v[t], j);
                 }
             }
         }
+        n_accept += static_cast<unsigned long long>(cnt - me.cnt);
+        me.cnt = cnt;
     }
 }
 
 // After filter_chunk: compact every row of this warp whose list is close to full.
-__device__ __forceinline__ void compact_full_rows(RowList& me, uint64_t* __restrict__ warp_buf, uint64_t* sm, int cap, int k, int keep_max,
-                                                  int lane, unsigned long long& n_compact) {
+template <int R>
+__device__ __forceinline__ void compact_full_rows(RowList& me, uint64_t* __restrict__ warp_buf, int k, int keep_max, int lane,
+                                                  unsigned long long& n_compact, long long& t_compact) {
+    constexpr int cap = 32 * R;
     unsigned full = __ballot_sync(0xffffffffu, me.cnt > cap - 32);
+    if (full == 0) return;
+    const long long c0 = clock64();
+    __syncwarp();  // the owner lanes' list appends must be visible to the whole warp
     while (full) {
         const int L = __ffs(full) - 1;
         full &= full - 1;
-        compact_row_approx(me, L, warp_buf + static_cast<size_t>(L) * cap, sm, cap, k, keep_max, lane);
+        uint64_t x[R];
+        compact_row_approx<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, x, k, keep_max, lane);
         ++n_compact;
     }
+    t_compact += clock64() - c0;
 }
 
 // End of sweep: final compaction of the warp's 32 rows and export of the candidate ids.
 //   r0: slab-row of lane 0; cand_out [nq, keep_max] uint32, cnt_out [nq] (bit 30 = overflow).
-__device__ __forceinline__ void export_rows(RowList& me, int64_t r0, int64_t nq, uint64_t* __restrict__ warp_buf, uint64_t* sm, int cap, int k,
-                                            int keep_max, uint32_t* __restrict__ cand_out, int* __restrict__ cnt_out, int lane) {
+template <int R>
+__device__ __forceinline__ void export_rows(RowList& me, int64_t r0, int64_t nq, uint64_t* __restrict__ warp_buf, int k, int keep_max,
+                                            uint32_t* __restrict__ cand_out, int* __restrict__ cnt_out, int lane) {
+    constexpr int cap = 32 * R;
+    __syncwarp();
     for (int L = 0; L < 32; ++L) {
         const int64_t rL = r0 + L;
         if (rL >= nq) break;
-        compact_row_approx(me, L, warp_buf + static_cast<size_t>(L) * cap, sm, cap, k, keep_max, lane);
+        uint64_t x[R];
+        compact_row_approx<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, x, k, keep_max, lane);
         const int m = __shfl_sync(0xffffffffu, me.cnt, L);
         const int ovf = __shfl_sync(0xffffffffu, me.ovf, L);
-        for (int t = lane; t < m; t += 32) cand_out[rL * keep_max + t] = key_idx(sm[t]);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int e = lane * R + r;
+            if (e < m) cand_out[rL * keep_max + e] = key_idx(x[r]);
+        }
         if (lane == 0) cnt_out[rL] = m | (ovf ? OVERFLOW_FLAG : 0);
         __syncwarp();
     }

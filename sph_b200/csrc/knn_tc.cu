@@ -25,6 +25,7 @@
 #include <cuda_fp16.h>
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 namespace sphb {
@@ -46,12 +47,15 @@ struct SweepParams {
     int64_t q0, nq;      // query slab
     int n_qtiles, n_dbtiles;
     int dp64;            // resident flavour: padded d / 64
+    int stagger;         // database-tile start offset per CTA (desynchronises the CTAs' L2 reads)
     int kchunks, k16_last, stages;  // stream flavour: K chunks per tile, k-steps in the last one; both: ring depth
     double eps_c1, eps_c2;
     uint64_t* cand;      // [grid, rows_per_cta, cap] scratch lists
     uint32_t* cand_out;  // [nq, keep_max]
     int* cnt_out;        // [nq]
     unsigned long long* stats;  // [0] compactions, [1] accepted candidates
+    int debug_skip_epilogue;    // debug: epilogue releases the accumulator without reading it (pure MMA rate)
+    unsigned long long* prof;   // optional [grid][16] cycle counters (debug: SPHB_KNN_PROF=1)
 };
 
 // ---------------------------------------------------------------------------
@@ -157,7 +161,7 @@ __global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [
 // ---------------------------------------------------------------------------
 // smem: [A: MH x (2*dp64) chunks | ONES chunk | B ring: stages chunks | sort buffers | barriers | tmem slot]
 // B chunk sequence per 128-row database tile: dp64 hi chunks, dp64 lo chunks, 1 norm chunk.
-template <int MH>
+template <int MH, int R>
 __global__ void __launch_bounds__(64 + 128 * MH, 1)
 knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                    const __grid_constant__ CUtensorMap tmapO, const SweepParams P, const int k16_tail) {
@@ -175,8 +179,7 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     const uint32_t sA = smem_base;                                   // [m][c] -> sA + (m*nA + c)*CHUNK_BYTES
     const uint32_t sO = sA + MH * nA * CHUNK_BYTES;
     const uint32_t sB = sO + CHUNK_BYTES;
-    uint64_t* sortbuf = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(MH * nA + 1 + stages) * CHUNK_BYTES);
-    uint64_t* bars = sortbuf + static_cast<size_t>(EPI_WARPS) * P.cap;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(MH * nA + 1 + stages) * CHUNK_BYTES);
     const uint32_t bar_full = ptx::smem_u32(bars);
     const uint32_t bar_empty = ptx::smem_u32(bars + stages);
     const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * stages);
@@ -186,6 +189,7 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 6);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int dt0 = static_cast<int>((static_cast<int64_t>(blockIdx.x) * P.stagger) % P.n_dbtiles);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmapA);
@@ -213,51 +217,71 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (warp-uniform control flow, one elected lane issues) =====================
+        {
             int stage = 0;
             uint32_t phase = 0, aphase = 0;
             bool first = true;
+            long long pw = 0, pt0 = clock64();
             for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
                 ptx::mbar_wait(bar_aempty, aphase ^ 1);  // previous query tile fully consumed
-                ptx::mbar_expect_tx(bar_afull, (MH * nA + (first ? 1 : 0)) * CHUNK_BYTES);
-                for (int m = 0; m < MH; ++m) {
-                    const int32_t qrow = static_cast<int32_t>(P.q0 + (static_cast<int64_t>(qt) * MH + m) * BM);
-                    for (int c = 0; c < nA; ++c) ptx::tma_load_2d(sA + (m * nA + c) * CHUNK_BYTES, &tmapA, bar_afull, c * BK, qrow);
+                if (ptx::elect_one_sync()) {
+                    ptx::mbar_expect_tx(bar_afull, (MH * nA + (first ? 1 : 0)) * CHUNK_BYTES);
+                    for (int m = 0; m < MH; ++m) {
+                        const int32_t qrow = static_cast<int32_t>(P.q0 + (static_cast<int64_t>(qt) * MH + m) * BM);
+                        for (int c = 0; c < nA; ++c) ptx::tma_load_2d(sA + (m * nA + c) * CHUNK_BYTES, &tmapA, bar_afull, c * BK, qrow);
+                    }
+                    if (first) ptx::tma_load_2d(sO, &tmapO, bar_afull, 0, 0);
                 }
-                if (first) ptx::tma_load_2d(sO, &tmapO, bar_afull, 0, 0);
+                __syncwarp();
                 first = false;
                 aphase ^= 1;
-                for (int dt = 0; dt < P.n_dbtiles; ++dt) {
+                for (int t = 0; t < P.n_dbtiles; ++t) {
+                    const int dt = (dt0 + t) % P.n_dbtiles;
                     for (int c = 0; c < nB; ++c) {
+                        const long long w0 = clock64();
                         ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                        ptx::mbar_expect_tx(bar_full + 8 * stage, CHUNK_BYTES);
-                        ptx::tma_load_2d(sB + stage * CHUNK_BYTES, &tmapB, bar_full + 8 * stage, c * BK, dt * BN);
+                        pw += clock64() - w0;
+                        if (ptx::elect_one_sync()) {
+                            ptx::mbar_expect_tx(bar_full + 8 * stage, CHUNK_BYTES);
+                            ptx::tma_load_2d(sB + stage * CHUNK_BYTES, &tmapB, bar_full + 8 * stage, c * BK, dt * BN);
+                        }
+                        __syncwarp();
                         if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
                 }
             }
+            if (P.prof && lane == 0) {
+                P.prof[blockIdx.x * 16 + 0] = pw;
+                P.prof[blockIdx.x * 16 + 1] = clock64() - pt0;
+            }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // ===================== MMA issuer (warp-uniform control flow, one elected lane issues) =====================
+        {
             constexpr uint32_t idesc = ptx::make_idesc_f16(BM, BN);
             int stage = 0;
             uint32_t phase = 0, aphase = 0;
             int as = 0;
             uint32_t accphase = 0;
             const uint64_t odesc = ptx::make_smem_desc_sw128(sO);
+            long long mw_te = 0, mw_f = 0, mt0 = clock64();
             for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
                 ptx::mbar_wait(bar_afull, aphase);
                 aphase ^= 1;
                 ptx::tc_fence_after();
-                for (int dt = 0; dt < P.n_dbtiles; ++dt) {
+                for (int t = 0; t < P.n_dbtiles; ++t) {
+                    long long w0 = clock64();
                     ptx::mbar_wait(bar_tempty + 8 * as, accphase ^ 1);
+                    mw_te += clock64() - w0;
                     ptx::tc_fence_after();
                     for (int c = 0; c < nB; ++c) {
+                        w0 = clock64();
                         ptx::mbar_wait(bar_full + 8 * stage, phase);
+                        mw_f += clock64() - w0;
                         ptx::tc_fence_after();
                         const uint64_t bdesc = ptx::make_smem_desc_sw128(sB + stage * CHUNK_BYTES);
+                        if (ptx::elect_one_sync()) {
 #pragma unroll
                         for (int m = 0; m < MH; ++m) {
                             const uint32_t tmem_d = tmem_base + as * ACC_COLS + m * BN;
@@ -280,12 +304,19 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
                             }
                         }
                         ptx::umma_commit(bar_empty + 8 * stage);
+                        if (c == nB - 1) ptx::umma_commit(bar_tfull + 8 * as);
+                        if (c == nB - 1 && t == P.n_dbtiles - 1) ptx::umma_commit(bar_aempty);  // query tile consumed
+                        }
+                        __syncwarp();
                         if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
-                    ptx::umma_commit(bar_tfull + 8 * as);
                     if (++as == 2) { as = 0; accphase ^= 1; }
                 }
-                ptx::umma_commit(bar_aempty);  // query tile consumed: A region may be overwritten
+            }
+            if (P.prof && lane == 0) {
+                P.prof[blockIdx.x * 16 + 2] = mw_te;
+                P.prof[blockIdx.x * 16 + 3] = mw_f;
+                P.prof[blockIdx.x * 16 + 4] = clock64() - mt0;
             }
         }
     } else {
@@ -293,11 +324,13 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         const int ew = warp - 2;       // 0 .. EPI_WARPS-1
         const int quarter = warp & 3;  // TMEM lane quarter this warp may access
         const int mhalf = ew >> 2;
-        uint64_t* sm = sortbuf + static_cast<size_t>(ew) * P.cap;
-        const int cap = P.cap, k = P.k, keep_max = P.keep_max;
+        constexpr int cap = 32 * R;
+        const int k = P.k, keep_max = P.keep_max;
         int as = 0;
         uint32_t accphase = 0;
         unsigned long long n_compact = 0, n_accept = 0;
+        const uint32_t n32 = static_cast<uint32_t>(P.n);
+        long long ew_tf = 0, e_ld = 0, e_filt = 0, e_exp = 0, e_cmp = 0, et0 = clock64();
         for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
             const int row_in_tile = mhalf * BM + quarter * 32 + lane;
             const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
@@ -309,24 +342,46 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             me.eps2 = row_eps2(valid ? P.un2[P.q0 + r] : 0.0, P.eps_c1, P.eps_c2, VMAX, VMAX2);
             me.cnt = 0;
             me.ovf = 0;
-            for (int dt = 0; dt < P.n_dbtiles; ++dt) {
+            for (int t = 0; t < P.n_dbtiles; ++t) {
+                const int dt = (dt0 + t) % P.n_dbtiles;
+                long long w0 = clock64();
                 ptx::mbar_wait(bar_tfull + 8 * as, accphase);
+                ew_tf += clock64() - w0;
                 ptx::tc_fence_after();
                 const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
 #pragma unroll 1
-                for (int c = 0; c < BN / 32; ++c) {
-                    float v[32];
-                    ptx::tmem_ld_32x32(taddr + c * 32, v);
-                    filter_chunk(v, jbase + c * 32, P.n, me, mybuf, n_accept);
-                    compact_full_rows(me, warp_buf, sm, cap, k, keep_max, lane, n_compact);
+                for (int c = 0; c < (P.debug_skip_epilogue ? 0 : BN / 32); c += 2) {
+                    float v0[32], v1[32];
+                    w0 = clock64();
+                    ptx::tmem_ld_32x32(taddr + c * 32, v0);       // two loads in flight before the wait
+                    ptx::tmem_ld_32x32(taddr + c * 32 + 32, v1);
+                    ptx::tmem_ld_wait(v0);
+                    ptx::tmem_ld_wait(v1);
+                    const long long w1 = clock64();
+                    e_ld += w1 - w0;
+                    filter_chunk(v0, jbase + c * 32, n32, me, mybuf, n_accept);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, n_compact, e_cmp);
+                    filter_chunk(v1, jbase + c * 32 + 32, n32, me, mybuf, n_accept);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, n_compact, e_cmp);
+                    e_filt += clock64() - w1;
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
                 if (++as == 2) { as = 0; accphase ^= 1; }
             }
-            export_rows(me, r - lane, P.nq, warp_buf, sm, cap, k, keep_max, P.cand_out, P.cnt_out, lane);
+            const long long x0 = clock64();
+            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane);
+            e_exp += clock64() - x0;
+        }
+        if (P.prof && lane == 0) {
+            atomicAdd(P.prof + blockIdx.x * 16 + 5, static_cast<unsigned long long>(ew_tf));
+            atomicAdd(P.prof + blockIdx.x * 16 + 6, static_cast<unsigned long long>(e_ld));
+            atomicAdd(P.prof + blockIdx.x * 16 + 7, static_cast<unsigned long long>(e_filt));
+            atomicAdd(P.prof + blockIdx.x * 16 + 8, static_cast<unsigned long long>(e_exp));
+            atomicAdd(P.prof + blockIdx.x * 16 + 9, static_cast<unsigned long long>(clock64() - et0));
+            atomicAdd(P.prof + blockIdx.x * 16 + 10, static_cast<unsigned long long>(e_cmp));
         }
         if (P.stats) {
             n_accept = warp_sum(static_cast<double>(n_accept));
@@ -354,6 +409,7 @@ constexpr int TMEM_COLS = 2 * BN;
 constexpr int NUM_THREADS = 192;
 }  // namespace tcs
 
+template <int R>
 __global__ void __launch_bounds__(tcs::NUM_THREADS, 1)
 knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, const SweepParams P) {
     using namespace tc;
@@ -361,8 +417,7 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int stages = P.stages;
-    uint64_t* sortbuf = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(stages) * STAGE_BYTES);
-    uint64_t* bars = sortbuf + 4 * static_cast<size_t>(P.cap);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(stages) * STAGE_BYTES);
     const uint32_t bar_full = ptx::smem_u32(bars);
     const uint32_t bar_empty = ptx::smem_u32(bars + stages);
     const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * stages);
@@ -370,6 +425,7 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t smem_base = ptx::smem_u32(smem);
+    const int dt0 = static_cast<int>((static_cast<int64_t>(blockIdx.x) * P.stagger) % P.n_dbtiles);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmapA);
@@ -399,7 +455,8 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             uint32_t phase = 0;
             for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
                 const int32_t qrow = static_cast<int32_t>(P.q0 + static_cast<int64_t>(qt) * BM);
-                for (int dt = 0; dt < P.n_dbtiles; ++dt) {
+                for (int t = 0; t < P.n_dbtiles; ++t) {
+                    const int dt = (dt0 + t) % P.n_dbtiles;
                     for (int kc = 0; kc < P.kchunks; ++kc) {
                         ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                         const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -440,13 +497,14 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             }
         }
     } else {
-        const int ew = warp - 2;
         const int quarter = warp & 3;
-        uint64_t* sm = sortbuf + static_cast<size_t>(ew) * P.cap;
-        const int cap = P.cap, k = P.k, keep_max = P.keep_max;
+        constexpr int cap = 32 * R;
+        const int k = P.k, keep_max = P.keep_max;
         int as = 0;
         uint32_t accphase = 0;
         unsigned long long n_compact = 0, n_accept = 0;
+        long long e_cmp = 0;
+        const uint32_t n32 = static_cast<uint32_t>(P.n);
         for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
             const int row_in_tile = quarter * 32 + lane;
             const int64_t r = static_cast<int64_t>(qt) * BM + row_in_tile;
@@ -458,24 +516,30 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             me.eps2 = row_eps2(valid ? P.un2[P.q0 + r] : 0.0, P.eps_c1, P.eps_c2, VMAX, VMAX2);
             me.cnt = 0;
             me.ovf = 0;
-            for (int dt = 0; dt < P.n_dbtiles; ++dt) {
+            for (int t = 0; t < P.n_dbtiles; ++t) {
+                const int dt = (dt0 + t) % P.n_dbtiles;
                 ptx::mbar_wait(bar_tfull + 8 * as, accphase);
                 ptx::tc_fence_after();
                 const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN;
 #pragma unroll 1
-                for (int c = 0; c < BN / 32; ++c) {
-                    float v[32];
-                    ptx::tmem_ld_32x32(taddr + c * 32, v);
-                    filter_chunk(v, jbase + c * 32, P.n, me, mybuf, n_accept);
-                    compact_full_rows(me, warp_buf, sm, cap, k, keep_max, lane, n_compact);
+                for (int c = 0; c < BN / 32; c += 2) {
+                    float v0[32], v1[32];
+                    ptx::tmem_ld_32x32(taddr + c * 32, v0);       // two loads in flight before the wait
+                    ptx::tmem_ld_32x32(taddr + c * 32 + 32, v1);
+                    ptx::tmem_ld_wait(v0);
+                    ptx::tmem_ld_wait(v1);
+                    filter_chunk(v0, jbase + c * 32, n32, me, mybuf, n_accept);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, n_compact, e_cmp);
+                    filter_chunk(v1, jbase + c * 32 + 32, n32, me, mybuf, n_accept);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, n_compact, e_cmp);
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
                 if (++as == 2) { as = 0; accphase ^= 1; }
             }
-            export_rows(me, r - lane, P.nq, warp_buf, sm, cap, k, keep_max, P.cand_out, P.cnt_out, lane);
+            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane);
         }
         if (P.stats) {
             n_accept = warp_sum(static_cast<double>(n_accept));
@@ -591,7 +655,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     if (nq <= 0) return 0;
     const int centre = metric == METRIC_L2 ? 1 : 0;
     const int sms = ctx().num_sms;
-    const int cap = next_pow2_i(k + 96);
+    const int cap = std::max(256, next_pow2_i(k + 96));
     const int keep_max = cap - 64;
 
     // ---- choose the kernel flavour and the operand layout
@@ -655,6 +719,20 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     P.un2 = un2.p; P.n = n; P.k = k; P.cap = cap; P.keep_max = keep_max; P.metric = metric;
     P.q0 = q0; P.nq = nq; P.n_qtiles = n_qtiles; P.n_dbtiles = n_dbtiles;
     P.cand = cand.p; P.cand_out = cand_out.p; P.cnt_out = cnt_out.p; P.stats = stats.p;
+    P.debug_skip_epilogue = getenv("SPHB_KNN_DEBUG_SKIP_EPI") ? 1 : 0;
+    DevBuf<unsigned long long> prof;
+    const bool want_prof = getenv("SPHB_KNN_PROF") != nullptr;
+    if (want_prof) {
+        SPHB_CUDA(prof.alloc(static_cast<size_t>(grid) * 16, stream));
+        SPHB_CUDA(cudaMemsetAsync(prof.p, 0, static_cast<size_t>(grid) * 16 * sizeof(unsigned long long), stream));
+        P.prof = prof.p;
+    }
+    {
+        // CTA b starts its database sweep b*stagger tiles in: the CTAs then read different lines at any
+        // moment (no L2 hot lines) while the union of their positions stays inside an L2-sized window.
+        const char* e = getenv("SPHB_KNN_STAGGER");
+        P.stagger = e ? atoi(e) : 4;
+    }
     // GEMM error bound: split truncation 6·2^-22 + accumulation (one 2^-22 per k-step),
     // times the magnitude (2|u||v| + |v|²); plus the fp16 subnormal floor; safety factor 2.
     const int ksteps = MH ? (3 * dp / UMMA_K + 1) : kp / UMMA_K;
@@ -670,8 +748,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     cudaEventRecord(ev.e[1], stream);
     if (MH) {
         const int dp64 = dp / 64;
-        const int epi_warps = 4 * MH;
-        const size_t fixed = static_cast<size_t>(MH * 2 * dp64 + 1) * CHUNK_BYTES + static_cast<size_t>(epi_warps) * cap * 8 + 256 + 1024;
+        const size_t fixed = static_cast<size_t>(MH * 2 * dp64 + 1) * CHUNK_BYTES + 256 + 1024;
         int stages = 8;
         while (stages > 2 && fixed + static_cast<size_t>(stages) * CHUNK_BYTES > smem_limit) --stages;
         const size_t smem = fixed + static_cast<size_t>(stages) * CHUNK_BYTES;
@@ -679,24 +756,36 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         P.dp64 = dp64; P.stages = stages;
         const int tail = d - 64 * (dp64 - 1);
         const int k16_tail = (tail + 15) / 16;
-        if (MH == 2) {
-            SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-            knn_sweep_resident<2><<<grid, 64 + 128 * 2, smem, stream>>>(tmA, tmB, tmO, P, k16_tail);
-        } else {
-            SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-            knn_sweep_resident<1><<<grid, 64 + 128, smem, stream>>>(tmA, tmB, tmO, P, k16_tail);
-        }
+#define SPHB_LAUNCH_RESIDENT(MH_, R_)                                                                                                      \
+    do {                                                                                                                                   \
+        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<MH_, R_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
+        knn_sweep_resident<MH_, R_><<<grid, 64 + 128 * MH_, smem, stream>>>(tmA, tmB, tmO, P, k16_tail);                                   \
+    } while (0)
+        if (MH == 2 && cap == 256) SPHB_LAUNCH_RESIDENT(2, 8);
+        else if (MH == 2 && cap == 512) SPHB_LAUNCH_RESIDENT(2, 16);
+        else if (MH == 2) SPHB_LAUNCH_RESIDENT(2, 32);
+        else if (cap == 256) SPHB_LAUNCH_RESIDENT(1, 8);
+        else if (cap == 512) SPHB_LAUNCH_RESIDENT(1, 16);
+        else SPHB_LAUNCH_RESIDENT(1, 32);
+#undef SPHB_LAUNCH_RESIDENT
     } else {
         const int kchunks = (kp + BK - 1) / BK;
         P.kchunks = kchunks;
         P.k16_last = (kp - (kchunks - 1) * BK) / UMMA_K;
-        const size_t fixed = 4 * static_cast<size_t>(cap) * 8 + 256 + 1024;
+        const size_t fixed = 256 + 1024;
         int stages = 4;
         while (stages > 2 && static_cast<size_t>(stages) * tcs::STAGE_BYTES + fixed > smem_limit) --stages;
         P.stages = stages;
         const size_t smem = static_cast<size_t>(stages) * tcs::STAGE_BYTES + fixed;
-        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        knn_sweep_stream<<<grid, tcs::NUM_THREADS, smem, stream>>>(tmA, tmB, P);
+#define SPHB_LAUNCH_STREAM(R_)                                                                                                         \
+    do {                                                                                                                               \
+        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_stream<R_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));     \
+        knn_sweep_stream<R_><<<grid, tcs::NUM_THREADS, smem, stream>>>(tmA, tmB, P);                                                   \
+    } while (0)
+        if (cap == 256) SPHB_LAUNCH_STREAM(8);
+        else if (cap == 512) SPHB_LAUNCH_STREAM(16);
+        else SPHB_LAUNCH_STREAM(32);
+#undef SPHB_LAUNCH_STREAM
     }
     count_launch();
     SPHB_CUDA(cudaGetLastError());
@@ -719,6 +808,18 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     SPHB_CUDA(cudaMemcpyAsync(&hovf, ovf_count.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
     SPHB_CUDA(cudaStreamSynchronize(stream));
     for (int i = 0; i < 3; ++i) cudaEventElapsedTime(&g_knn_ms[i], ev.e[i], ev.e[i + 1]);
+    if (want_prof) {
+        std::vector<unsigned long long> hp(static_cast<size_t>(grid) * 16);
+        cudaMemcpy(hp.data(), prof.p, hp.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+        double acc[16] = {0};
+        for (int b = 0; b < grid; ++b)
+            for (int i = 0; i < 16; ++i) acc[i] += static_cast<double>(hp[b * 16 + i]) / grid;
+        const int ew = MH ? 4 * MH : 4;
+        fprintf(stderr,
+                "[knn prof] mean cycles per CTA: producer wait_empty %.3g of %.3g | mma wait_tempty %.3g wait_full %.3g of %.3g | "
+                "epilogue(per warp) wait_tfull %.3g ld %.3g filter+compact %.3g (compact %.3g) export %.3g of %.3g | sweep %.2f ms\n",
+                acc[0], acc[1], acc[2], acc[3], acc[4], acc[5] / ew, acc[6] / ew, acc[7] / ew, acc[10] / ew, acc[8] / ew, acc[9] / ew, g_knn_ms[1]);
+    }
     if (hovf > 0) {
         // rows whose candidate band overflowed (massive ties): exact SIMT recompute, never a truncated answer
         if (int rc = knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, ovf_rows.p, ovf_count.p, hovf, d_ids, d_dist, stream)) return rc;
