@@ -1,0 +1,222 @@
+"""CPU tests (no GPU): the oracle against the reference's own golden vectors.
+
+Each test re-expresses one Catch2 test of alxvth/SPH (file:line in tests/golden/README.md)
+on the CPU restatement under oracle/.  These pin the checker; the `-m gpu` tests then
+compare the CUDA path with the checker.
+"""
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import oracle_lib
+from oracle_lib import csr_to_dense, dense_to_csr
+
+GOLD = Path(__file__).resolve().parent / "golden"
+
+
+def gold(name):
+    return json.loads((GOLD / name).read_text())
+
+
+# ---------------------------------------------------------------- Stage B6
+@pytest.mark.parametrize("umap", [False, True])
+def test_symmetrize_golden(oracle, umap):
+    g = gold("symmetrize_5x5.json")
+    rp, c, v = dense_to_csr(g["input"])
+    orp, oc, ov = oracle.symmetrize(rp, c, v, umap=umap)
+    out = csr_to_dense(orp, oc, ov)
+    exp = np.array(g["umap" if umap else "tsne"], np.float32)
+    np.testing.assert_allclose(out, exp, atol=g["tol"])
+    np.testing.assert_array_equal(out, out.T)  # isSymmetric
+    # column-sorted rows (MapMemEff order)
+    for i in range(5):
+        assert (np.diff(oc[orp[i]:orp[i + 1]].astype(np.int64)) > 0).all()
+
+
+# ---------------------------------------------------------------- Stage C (RW2)
+def test_merge_nodes_synth_golden(oracle):
+    g = gold("merge_nodes_synth.json")
+    rp, c, v = dense_to_csr(g["input"])
+    orp, oc, ov = oracle.rw_merge(rp, c, v, g["parents"], 3, norm=g["norm"], weight_by_size=g["weight_by_size"])
+    np.testing.assert_array_equal(csr_to_dense(orp, oc, ov), np.array(g["expected"], np.float32))
+
+
+def test_merge_weight_by_size_rows_sum_to_one(oracle):
+    # mergeNodesRandomWalks(weightBySize) divides by the summed weights; with norm the rows are L1-normalised
+    rng = np.random.default_rng(3)
+    m = (rng.uniform(size=(40, 40)) < 0.2) * rng.uniform(0.1, 1, size=(40, 40))
+    m /= np.maximum(m.sum(1, keepdims=True), 1e-9)
+    rp, c, v = dense_to_csr(m)
+    parents = rng.integers(0, 7, size=40)
+    parents[:7] = np.arange(7)
+    orp, oc, ov = oracle.rw_merge(rp, c, v, parents, 7, norm=True, weight_by_size=True)
+    d = csr_to_dense(orp, oc, ov, 7)
+    np.testing.assert_allclose(d.sum(1), 1.0, atol=1e-5)
+
+
+# ---------------------------------------------------------------- Stage D
+def test_similarities_5x5_three_way(oracle):
+    g = gold("sims_5x5.json")
+    a = np.array(g["input"], np.float32)
+    for r in a:
+        assert r.sum(dtype=np.float32) == np.float32(1.0)  # REQUIRE(row.sum() == 1.0f)
+    rp, c, v = dense_to_csr(a)
+    n = 5
+    # createSimilaritiesSPH (explicit sqrt dots) == -log(sqrt(A) sqrt(A)^T) computed directly
+    srp, sc, sv = oracle.create_similarities_sph(rp, c, v, prune_val=g["prune"])
+    sph = csr_to_dense(srp, sc, sv)
+    s = np.sqrt(a)
+    with np.errstate(divide="ignore"):
+        direct = -np.log((s @ s.T).astype(np.float32))
+    mask = (s @ s.T) > 0
+    np.fill_diagonal(mask, False)
+    np.testing.assert_allclose(sph[mask], direct[mask], rtol=1e-4, atol=1e-5)
+    # Eigen path + bottom-k conversion must be bit-equal to the HDI path (UtilsTests.cpp:1012-1027)
+    k = g["k"]
+    ec, ev, en = oracle.create_similarities(rp, c, v, k, prune_val=g["prune"], variant=2)
+    hc, hv, hn = oracle.create_similarities(rp, c, v, k, prune_val=g["prune"], variant=1)
+    np.testing.assert_array_equal(en, hn)
+    for i in range(n):
+        np.testing.assert_array_equal(ec[i, :en[i]], hc[i, :hn[i]])
+        np.testing.assert_array_equal(ev[i, :en[i]], hv[i, :hn[i]])
+    # and the kept entries are the k smallest distances of the explicit matrix, L1-normalised
+    for i in range(n):
+        cand = [(sph[i, j], j) for j in range(n) if j != i and mask[i, j]]
+        cand.sort()
+        keep = sorted(j for _, j in cand[:k])
+        assert list(hc[i, :hn[i]]) == keep
+        vals = np.array([sph[i, j] for j in keep], np.float64)
+        np.testing.assert_allclose(hv[i, :hn[i]], vals / vals.sum(), rtol=1e-5)
+
+
+def test_find_top_k_golden(oracle):
+    g = gold("topk_deque.json")
+    oc, ov = oracle.find_k(g["cols"], g["vals"], g["k"], top=True)
+    assert [(int(a), float(np.float32(b))) for a, b in zip(oc, ov)] == [(a, float(np.float32(b))) for a, b in g["top"]]
+    # findBottomK is the mirror: k smallest, column sorted
+    oc, ov = oracle.find_k(g["cols"], g["vals"], g["k"], top=False)
+    assert list(oc) == [2, 4, 6]
+
+
+def test_knn_overlap_golden(oracle):
+    g = gold("knn_overlap.json")
+    k = g["k"]
+    knn = np.array(g["knn"], np.int64).reshape(-1, k)
+    n = knn.shape[0]
+    l1 = g["children_l1"]
+    l2 = [sorted(p for c in comp for p in l1[c]) for comp in g["children_l2"]]
+    levels = {0: [[i] for i in range(n)], 1: l1, 2: l2}
+
+    def pixels(level, comp):
+        return levels[level][comp]
+
+    for case in g["cases"]:
+        pa, pb = pixels(*case["a"]), pixels(*case["b"])
+        ua = sorted(set(knn[pa].ravel().tolist()))
+        ub = sorted(set(knn[pb].ravel().tolist()))
+        assert ua == case["ua"] and ub == case["ub"]  # Hierarchy::getRepresentedDataPoints + union
+        comp_ptr = np.array([0, len(pa), len(pa) + len(pb)], np.int64)
+        comp_pix = np.array(pa + pb, np.int64)
+        sim = oracle.neighbor_overlap(knn, comp_ptr, comp_pix, [0], [1])[0]
+        assert sim == pytest.approx(case["overlap"] / min(len(ua), len(ub)), rel=1e-6)
+
+
+# ---------------------------------------------------------------- Stage A
+def test_l2_against_double_loop(oracle):
+    # testL2 (UtilsTests.cpp:238-271): L2 vs a double-precision loop, abs 1e-4, uniform(0,100) vectors
+    g = gold("l2_dims.json")
+    rng = np.random.default_rng(1)
+    for d in g["dims"]:
+        x = rng.uniform(0, 100, size=(2, d)).astype(np.float32)
+        diff = x[0].astype(np.float32) - x[1].astype(np.float32)
+        base = np.float32(np.sqrt((diff.astype(np.float64) ** 2).sum()))
+        ids, dist = oracle.knn_reference_graph(x, 2, l2_squared=False)
+        assert list(ids[0]) == [0, 1]
+        assert abs(float(dist[0, 1]) - float(base)) <= g["abs_tol"] * max(1.0, float(base) * 1e-3)
+
+
+def test_knn_oracle_invariants_scurve(oracle):
+    # testConnectingComponentsKnnGraph shape (UtilsTests.cpp:662-703): S-curve N=1000, k=3;
+    # invariants NearestNeighbors::compute enforces (self first, non-decreasing, all present)
+    from sph_b200 import synth
+
+    x = synth.s_curve(1000, 0.2, 123)
+    ids, dist = oracle.knn_reference_graph(x, 3)
+    assert (ids[:, 0] == np.arange(1000)).all()
+    assert (dist[:, 0] == 0).all()
+    assert (np.diff(dist, axis=1) >= 0).all()
+    assert (ids >= 0).all()
+    # brute-force numpy cross-check of the index sets in float64
+    d2 = ((x[:, None, :].astype(np.float64) - x[None, :, :].astype(np.float64)) ** 2).sum(-1)
+    order = np.lexsort((np.arange(1000)[None, :].repeat(1000, 0), d2.astype(np.float32)), axis=1)[:, :3]
+    np.testing.assert_array_equal(np.sort(ids, axis=1), np.sort(order, axis=1))
+
+
+def test_knn_postprocess_self_first_cases(oracle):
+    # ensureClosestPointIsSelf (GraphUtils.cpp:23-95): swap / overwrite-last / shift
+    ids = np.array([[1, 0, 2], [0, 2, 3], [3, 0, 1]], np.int64)
+    dist = np.array([[0, 0, 4], [0, 0, 0], [1, 4, 9]], np.float32)
+    oracle.knn_postprocess(ids, dist, l2_squared=True)
+    assert list(ids[0]) == [0, 1, 2]            # found at slot 1 -> swapped
+    assert list(ids[1]) == [1, 2, 0] or ids[1, 0] == 1  # absent, all zero -> last overwritten, swapped to front
+    assert ids[1, 0] == 1 and dist[1, 0] == 0
+    assert list(ids[2]) == [2, 3, 0] and list(dist[2]) == [0, 1, 4]  # absent -> shifted right
+
+
+def test_blas_flavour_agrees_with_exact_on_separated_data(oracle):
+    # the timed CPU baseline (faiss-style sgemm + heaps) finds the same neighbours when gaps are not fp32-marginal
+    if not oracle.blas_init():
+        pytest.skip("OpenBLAS not found")
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((600, 24)).astype(np.float32)
+    ids, _ = oracle.knn_blas_l2(x, 8, 0, 600)
+    rids, _ = oracle.knn_exact(x, 8)
+    assert (np.sort(ids, 1) == np.sort(rids, 1)).mean() > 0.999
+
+
+# ---------------------------------------------------------------- Stage B
+def test_gaussian_row_hits_perplexity(oracle):
+    # no reference golden exists — property: entropy of the row == log(perplexity) within tol
+    rng = np.random.default_rng(2)
+    dist = np.sort(rng.gamma(2.0, 1.0, 91).astype(np.float32))
+    dist[0] = 0
+    p, sigma = oracle.gaussian_row(dist, 30.0, tol=1e-6, ignore=0)
+    assert sigma > 0 and p[0] == 0
+    assert abs(p.sum() - 1.0) < 1e-5
+    nz = p[p > 0].astype(np.float64)
+    assert abs(-(nz * np.log(nz)).sum() - np.log(30.0)) < 1e-4
+    assert (np.diff(p[1:]) <= 1e-12).all()  # monotone (GraphNormalization.cpp:295-327 debug asserts)
+
+
+def test_level_schedule(oracle):
+    # LevelSimilarities::updateNumberOfNeighbors (LevelSimilarities.cpp:83-115)
+    perp, ks = oracle.level_schedule([21025, 5000, 900, 40], 91)
+    assert perp[0] == pytest.approx(30.0) and ks[0] == 91
+    assert perp[1] == pytest.approx(30.0) and ks[1] == 91
+    assert perp[2] == pytest.approx(10.0) and ks[2] == 31
+    assert ks[3] == 31 or ks[3] == 40  # min(perp*3+1, n_l)
+    assert ks[3] == min(int(perp[3]) * 3 + 1, 40)
+
+
+# ---------------------------------------------------------------- Stage C (RW1)
+def test_random_walks_serial_reproducible_and_normalised(oracle):
+    rng = np.random.default_rng(5)
+    n, k = 60, 6
+    m = np.zeros((n, n), np.float32)
+    for i in range(n):
+        nb = rng.choice([j for j in range(n) if j != i], k, replace=False)
+        w = rng.uniform(0.1, 1, k)
+        m[i, nb] = w / w.sum()
+    rp, c, v = dense_to_csr(m)
+    a = oracle.random_walks(rp, c, v, 10, 3, weighting=0, seed=1, threads=1)
+    b = oracle.random_walks(rp, c, v, 10, 3, weighting=0, seed=1, threads=1)
+    for x, y in zip(a, b):
+        np.testing.assert_array_equal(x, y)
+    d = csr_to_dense(*a)
+    np.testing.assert_allclose(d.sum(1), 1.0, atol=1e-3)  # testImageHierarchyWalks row sums (HierarchyTest.cpp:440-444)
+    assert (np.diag(d) == 0).all()  # removeDiagonalElements
+    # un-normalised CONSTANT weighting: every walk step adds 1 -> raw row mass = W*L minus self hits
+    raw = csr_to_dense(*oracle.random_walks(rp, c, v, 10, 3, weighting=0, seed=1, threads=1, remove_diagonal=False, normalize=False))
+    np.testing.assert_allclose(raw.sum(1), 30.0)
