@@ -89,14 +89,15 @@ SPHB_API int sphb_knn_exact_slab(const float* x, int64_t n, int d, int k, int me
                                  int64_t q0, int64_t q1, int64_t* ids, float* dist);
 SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared,
                                 int64_t q0, int64_t q1, int64_t* d_ids, float* d_dist, void* stream);
-/* kNN statistics of the last call: [0] path (0 SIMT, 1 tcgen05 streaming, 2 tcgen05
- * resident MH=1, 3 tcgen05 resident MH=2), [1] candidate-list compactions,
- * [2] candidates accepted by the filter, [3] executed GEMM K extent per pair,
- * [4] rows recomputed by the exact SIMT kernel (candidate band overflow), [5] query tiles. */
-SPHB_API int sphb_knn_last_stats(int64_t* out6);
+/* kNN statistics of the last call: [0] path (0 SIMT, 1 tcgen05 streaming, 2 tcgen05 resident MH=1,
+ * 3 tcgen05 resident MH=2), [1] candidate-list compactions, [2] candidates accepted by the filter,
+ * [3] executed GEMM K extent per pair of the main sweep, [4] rows recomputed by the exact SIMT kernel
+ * (candidate band overflow), [5] query tiles, [6] fp16 products per pair of the main sweep (1 or 3),
+ * [7] rows re-swept with the 3-product filter after overflowing the 1-product band. */
+SPHB_API int sphb_knn_last_stats(int64_t* out8);
 /* device time of the last tensor-core kNN call in ms (CUDA events on its stream): [0] operand
- * preparation, [1] the tcgen05 sweep kernel, [2] the exact re-rank kernel. */
-SPHB_API int sphb_knn_last_timing(float* ms3);
+ * preparation, [1] the tcgen05 sweep kernel(s), [2] the exact re-rank kernel(s), [3] overflow fallbacks. */
+SPHB_API int sphb_knn_last_timing(float* ms4);
 /*
  * Stage A followed by the level-0 P rows of Stage B in one call — the pair
  * ComputeHierarchy::compute() runs back to back (computeKnnGraph, sph/ComputeHierarchy.cpp:97-159,

@@ -40,17 +40,21 @@ def _digest() -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
+def build(force: bool = False, verbose: bool = False, profile: bool = False) -> Path:
+    """profile=True builds lib/libsphb200_prof.so with the sweep's cycle counters compiled in
+    (-DSPHB_KNN_PROFILE; select it with SPHB_LIB=<path>, enable with SPHB_KNN_PROF=1)."""
     LIBDIR.mkdir(exist_ok=True)
-    stamp = LIBDIR / "build.stamp"
+    tag = "_prof" if profile else ""
+    lib = LIBDIR / f"libsphb200{tag}.so"
+    stamp = LIBDIR / f"build{tag}.stamp"
     dig = _digest()
-    if not force and LIB.exists() and stamp.exists() and stamp.read_text() == dig:
-        return LIB
+    if not force and lib.exists() and stamp.exists() and stamp.read_text() == dig:
+        return lib
     objs = []
     procs = []
     for src in sources():
-        obj = LIBDIR / (src.stem + ".o")
-        cmd = [NVCC, *FLAGS, "-c", str(src), "-o", str(obj)]
+        obj = LIBDIR / (src.stem + tag + ".o")
+        cmd = [NVCC, *FLAGS, *(["-DSPHB_KNN_PROFILE"] if profile else []), "-c", str(src), "-o", str(obj)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
@@ -63,11 +67,11 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         failed |= p.returncode != 0
     if failed:
         raise RuntimeError("nvcc failed")
-    cmd = [NVCC, *FLAGS, "-shared", "-o", str(LIB), *map(str, objs), "-ldl"]
+    cmd = [NVCC, *FLAGS, "-shared", "-o", str(lib), *map(str, objs), "-ldl"]
     subprocess.run(cmd, check=True)
     stamp.write_text(dig)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, profile="--profile" in sys.argv))

@@ -8,11 +8,13 @@ raise.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
 
-_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libsphb200.so"
+# SPHB_LIB selects another build of the same library (e.g. the -DSPHB_KNN_PROFILE one)
+_LIB_PATH = Path(os.environ.get("SPHB_LIB") or (Path(__file__).resolve().parent / "lib" / "libsphb200.so")).resolve()
 _lib = None
 
 METRIC_INNER_PRODUCT = 0
@@ -108,20 +110,21 @@ def stream_ptr() -> int:
 
 
 def force_knn_path(path: int):
-    """0 auto, 1 SIMT exact kernel, 2 tcgen05 sweep (auto flavour), 3 tcgen05 streaming, 4 tcgen05 resident MH=1 (tests only)."""
+    """0 auto, 1 SIMT exact kernel, 2 tcgen05 (auto), 3 streaming 3-pass, 4 resident MH=1 3-pass, 5 3-pass (auto flavour), 6 1-pass, 7 1-pass streaming (tests only)."""
     load().sphb_debug_force_knn_path(path)
 
 
 def knn_last_stats() -> dict:
-    out = np.zeros(6, np.int64)
+    out = np.zeros(8, np.int64)
     _check(load().sphb_knn_last_stats(_p(out, i64p)))
-    return dict(tensor_core=int(out[0]), compactions=int(out[1]), accepted=int(out[2]), kp=int(out[3]), overflow_rows=int(out[4]), q_tiles=int(out[5]))
+    return dict(tensor_core=int(out[0]), compactions=int(out[1]), accepted=int(out[2]), kp=int(out[3]), overflow_rows=int(out[4]), q_tiles=int(out[5]),
+                passes=int(out[6]), resweep_rows=int(out[7]))
 
 
 def knn_last_timing() -> dict:
-    out = np.zeros(3, np.float32)
+    out = np.zeros(4, np.float32)
     _check(load().sphb_knn_last_timing(_p(out, f32p)))
-    return dict(prep_ms=float(out[0]), sweep_ms=float(out[1]), rerank_ms=float(out[2]))
+    return dict(prep_ms=float(out[0]), sweep_ms=float(out[1]), rerank_ms=float(out[2]), fallback_ms=float(out[3]))
 
 
 def knn_graph_prow(x: np.ndarray, k: int, perplexity: float = 0.0, metric: int = METRIC_L2, l2_squared: bool = False, q0: int = 0,

@@ -31,12 +31,14 @@ int knn_tc_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, i
 bool knn_tc_supported(int64_t n, int d, int k);
 void knn_set_stats(const int64_t* s);
 void knn_get_stats(int64_t* s);
-void knn_get_timing(float* ms3);
+void knn_get_timing(float* ms4);
 int prow_graph_launch(const int64_t*, const float*, int64_t, int, float, int, uint32_t*, float*, double*, cudaStream_t);
 int prow_inplace_launch(int64_t, const int64_t*, float*, int, float, int, cudaStream_t);
 int prow_flat_launch(const float*, int64_t, int, double, float*, cudaStream_t);
 
-static int g_force_path = 0;  // 0 auto, 1 SIMT, 2 tensor core (auto flavour), 3 tc streaming kernel, 4 tc resident MH=1 (testing hook)
+// testing hook: 0 auto, 1 SIMT, 2 tensor core (auto), 3 tc streaming 3-pass, 4 tc resident MH=1 3-pass, 5 tc 3-pass (auto flavour),
+// 6 tc 1-pass (resident when d allows), 7 tc 1-pass streaming
+static int g_force_path = 0;
 
 }  // namespace sphb
 
@@ -106,8 +108,8 @@ SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int m
     if (g_force_path >= 2) {
         if (!use_tc) return fail(SPHB_ERR_UNSUPPORTED, "knn: tensor-core path unsupported for this shape");
     }
-    if (use_tc) return knn_tc_launch(d_x, n, d, k, metric, l2_squared, q0, q1, d_ids, d_dist, s, g_force_path == 3 ? 1 : (g_force_path == 4 ? 2 : 0));
-    const int64_t st[6] = {0, 0, 0, 0, 0, 0};
+    if (use_tc) return knn_tc_launch(d_x, n, d, k, metric, l2_squared, q0, q1, d_ids, d_dist, s, g_force_path >= 3 ? g_force_path - 2 : 0);
+    const int64_t st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     knn_set_stats(st);
     return knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, nullptr, nullptr, 0, d_ids, d_dist, s);
 }
@@ -136,15 +138,15 @@ SPHB_API int sphb_knn_exact(const float* x, int64_t n, int d, int k, int metric,
     return sphb_knn_exact_slab(x, n, d, k, metric, l2_squared, 0, n, ids, dist);
 }
 
-SPHB_API int sphb_knn_last_stats(int64_t* out6) {
-    if (!out6) return fail(SPHB_ERR_INVALID, "null pointer");
-    knn_get_stats(out6);
+SPHB_API int sphb_knn_last_stats(int64_t* out8) {
+    if (!out8) return fail(SPHB_ERR_INVALID, "null pointer");
+    knn_get_stats(out8);
     return SPHB_OK;
 }
 
-SPHB_API int sphb_knn_last_timing(float* ms3) {
-    if (!ms3) return fail(SPHB_ERR_INVALID, "null pointer");
-    knn_get_timing(ms3);
+SPHB_API int sphb_knn_last_timing(float* ms4) {
+    if (!ms4) return fail(SPHB_ERR_INVALID, "null pointer");
+    knn_get_timing(ms4);
     return SPHB_OK;
 }
 

@@ -55,8 +55,13 @@ __device__ __forceinline__ float exact_key(const float* __restrict__ X, int64_t 
 // Fused write-out of one row (executed by one warp).
 //   sm[0..nvalid): keys sorted ascending by (value, index); p = global row id.
 //   Applies, in the reference's order (sph/NearestNeighbors.cpp:152-167):
-//   A6 `d <= FLT_EPSILON -> 0`, A7 sqrt unless l2_squared, A9 self first
+//   A6 `d <= FLT_EPSILON -> 0`, A7 sqrt unless l2_squared, A8 monotone re-sort, A9 self first
 //   (sph/utils/GraphUtils.cpp:23-95: swap / overwrite-last-then-swap / shift).
+//   A8 (checkDistancesAreNonDecreasing + stable synchronizedSort, NearestNeighbors.cpp:244-269) never
+//   fires for L2.  For the inner product faiss returns DESCENDING similarities, so the reference re-sorts
+//   every row that is not constant: a stable ascending sort of a non-increasing sequence reverses the
+//   order of the runs of equal values and keeps the order inside each run — output slot s takes the
+//   element gs + ge - m, m = nvalid-1-s, [gs, ge] = the run of equal values around m.
 //   Slots t >= nvalid keep the caller's -1 / -1.0f convention.
 __device__ __forceinline__ void write_row(const uint64_t* sm, int nvalid, int k, int64_t p, int metric, int l2_squared,
                                           int64_t* __restrict__ ids_out, float* __restrict__ dist_out, int lane) {
@@ -67,11 +72,27 @@ __device__ __forceinline__ void write_row(const uint64_t* sm, int nvalid, int k,
         if (!l2_squared) v = sqrtf(v);
         return v;
     };
+    // A8 for the inner product: does the row need the re-sort (any strict decrease)?
+    bool resort = false;
+    if (metric != METRIC_L2 && nvalid > 1) {
+        bool dec = false;
+        for (int t = lane + 1; t < nvalid; t += 32) dec |= dist_of(sm[t]) < dist_of(sm[t - 1]);
+        resort = __any_sync(0xffffffffu, dec);
+    }
+    auto at = [&](int s) -> uint64_t {  // key at position s of the A8-ordered row
+        if (!resort) return sm[s];
+        const int m = nvalid - 1 - s;
+        const float v = dist_of(sm[m]);
+        int gs = m, ge = m;
+        while (gs > 0 && dist_of(sm[gs - 1]) == v) --gs;
+        while (ge + 1 < nvalid && dist_of(sm[ge + 1]) == v) ++ge;
+        return sm[gs + ge - m];
+    };
     // locate self and test "all distances zero"
     int self_pos = 0x7fffffff;
     bool all_zero = true;
     for (int t = lane; t < nvalid; t += 32) {
-        const uint64_t key = sm[t];
+        const uint64_t key = at(t);
         if (static_cast<int64_t>(key_idx(key)) == p) self_pos = min(self_pos, t);
         if (dist_of(key) != 0.f) all_zero = false;
     }
@@ -98,7 +119,7 @@ __device__ __forceinline__ void write_row(const uint64_t* sm, int nvalid, int k,
                 if (t == 0) is_self = true;
                 else src = t - 1;
             }
-            const uint64_t key = sm[src];
+            const uint64_t key = at(src);
             id = is_self ? p : static_cast<int64_t>(key_idx(key));
             dv = (mode == 3 && t == 0) ? 0.f : dist_of(key);
         }

@@ -11,9 +11,23 @@
 // the exact fp64 re-rank (knn_rerank_kernel) then picks the final k.  If more than
 // keep_max entries fall inside the band (massive ties) the row is flagged and is
 // recomputed by the exact SIMT kernel instead — never silently truncated.
+//
+// Two error models:
+//   passes = 3  split-fp16 operands (hi·hi + hi·lo + lo·hi): eps_i is a per-row constant.
+//   passes = 1  single fp16 product: the operand rounding error is bounded with the ACTUAL
+//               rounding-error norms |u_i - fp16(u_i)| computed by the prep kernel, and with an
+//               adaptive radius R_i >= |v_j| for every database point that can matter, derived from
+//               the row's current k-th value (band_1pass below).
 #pragma once
 #include "knn_common.cuh"
 #include "ptx_sm100.cuh"
+
+// Cycle-counter instrumentation of the sweep (build with -DSPHB_KNN_PROFILE, run with SPHB_KNN_PROF=1).
+#ifdef SPHB_KNN_PROFILE
+#define SPHB_CLOCK() clock64()
+#else
+#define SPHB_CLOCK() 0ll
+#endif
 
 namespace sphb {
 
@@ -21,10 +35,42 @@ constexpr int OVERFLOW_FLAG = 1 << 30;
 
 struct RowList {
     float thr;   // accept iff G <= thr
-    float eps2;  // 2 * eps_i, rounded up
+    float eps2;  // passes = 3: 2 * eps_i, rounded up
+    float un;    // passes = 1: |u_i| (scaled, centred), rounded up
+    float dun;   // passes = 1: |u_i - fp16(u_i)|, rounded up
     int cnt;     // entries currently in the row's scratch list
     int ovf;     // overflow flag
 };
+
+// Constants of the band computation, identical for every row of a launch.
+struct BandConsts {
+    int passes;    // 1 or 3
+    int l2;        // 1: L2 metric (the adaptive radius applies), 0: inner product
+    float vmax;    // upper bound on every |v_j| (scaled)
+    float dvmax;   // max_j |v_j - fp16(v_j)|, rounded up
+    float acc_c;   // accumulation-error coefficient (relative to 2|u||v| + |v|²)
+    float sub_c;   // fp16 subnormal floor of a row's rounding-error norm: sqrt(d) * 2^-25
+};
+
+// passes = 1.  Error of one computed G_ij against the true value, for |v_j| <= R:
+//   2 (|du_i| |fp16(v_j)| + |u_i| |dv_j|) + accumulation, with |dv_j| <= min(dvmax, 2^-11 R + sub_c).
+__device__ __forceinline__ float pair_err_1pass(float R, float un, float dun, const BandConsts& bc) {
+    const float Rh = R * 1.0005f;  // |fp16(v)| <= |v| (1 + 2^-11)
+    const float dv = fminf(bc.dvmax, 0.00048877f * R + bc.sub_c);
+    return 2.f * (dun * Rh + un * dv) + bc.acc_c * (2.f * un * Rh + Rh * Rh);
+}
+// Width of the band above the current k-th value Gk that must be kept so that no true neighbour is
+// lost: E(j') + E(j*) for the two database points of the proof in DESIGN.md, both of which have
+// |v| <= |u_i| + sqrt(Gk + Emax + |u_i|²) (L2 only; for the inner product R = vmax).
+__device__ __forceinline__ float band_1pass(float Gk, float un, float dun, const BandConsts& bc) {
+    float R = bc.vmax;
+    if (bc.l2) {
+        const float emax = pair_err_1pass(R, un, dun, bc);
+        const float D = fmaxf(Gk + emax + un * un * 1.0001f, 0.f) * 1.0001f;
+        R = fminf(R, (un + sqrtf(D)) * 1.0005f);
+    }
+    return 2.f * pair_err_1pass(R, un, dun, bc) * 1.001f;
+}
 
 // Ascending bitonic sort of 32*R u64 keys held in registers, element e = lane*R + r.
 // Partner distances below R are register swaps, the others one 64-bit shuffle per key.
@@ -76,9 +122,8 @@ __device__ __forceinline__ void warp_bitonic_sort_regs(uint64_t (&x)[R], int lan
 // x[] (element e = lane*R + r) for the caller.  cap = 32*R.
 template <int R>
 __device__ __forceinline__ void compact_row_approx(RowList& me, int L, uint64_t* __restrict__ buf_L, uint64_t (&x)[R], int k, int keep_max,
-                                                   int lane) {
+                                                   int lane, const BandConsts& bc) {
     const int cntL = __shfl_sync(0xffffffffu, me.cnt, L);
-    const float eps2L = __shfl_sync(0xffffffffu, me.eps2, L);
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const int e = lane * R + r;
@@ -95,7 +140,9 @@ __device__ __forceinline__ void compact_row_approx(RowList& me, int L, uint64_t*
 #pragma unroll
         for (int r = 0; r < R; ++r) kth = (r == kr) ? x[r] : kth;
         kth = __shfl_sync(0xffffffffu, kth, (k - 1) / R);
-        limit = __fadd_ru(key_val(kth), eps2L);
+        // every lane evaluates the band with its own row constants; lane L's result is the one used
+        const float band = bc.passes == 3 ? me.eps2 : band_1pass(key_val(kth), me.un, me.dun, bc);
+        limit = __fadd_ru(key_val(kth), __shfl_sync(0xffffffffu, band, L));
         int c = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r) c += (lane * R + r < cntL && key_val(x[r]) <= limit) ? 1 : 0;
@@ -150,34 +197,34 @@ __device__ __forceinline__ void filter_chunk(const float (&v)[32], uint32_t jbas
 // After filter_chunk: compact every row of this warp whose list is close to full.
 template <int R>
 __device__ __forceinline__ void compact_full_rows(RowList& me, uint64_t* __restrict__ warp_buf, int k, int keep_max, int lane,
-                                                  unsigned long long& n_compact, long long& t_compact) {
+                                                  const BandConsts& bc, unsigned long long& n_compact, long long& t_compact) {
     constexpr int cap = 32 * R;
     unsigned full = __ballot_sync(0xffffffffu, me.cnt > cap - 32);
     if (full == 0) return;
-    const long long c0 = clock64();
+    const long long c0 = SPHB_CLOCK();
     __syncwarp();  // the owner lanes' list appends must be visible to the whole warp
     while (full) {
         const int L = __ffs(full) - 1;
         full &= full - 1;
         uint64_t x[R];
-        compact_row_approx<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, x, k, keep_max, lane);
+        compact_row_approx<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, x, k, keep_max, lane, bc);
         ++n_compact;
     }
-    t_compact += clock64() - c0;
+    t_compact += SPHB_CLOCK() - c0;
 }
 
 // End of sweep: final compaction of the warp's 32 rows and export of the candidate ids.
 //   r0: slab-row of lane 0; cand_out [nq, keep_max] uint32, cnt_out [nq] (bit 30 = overflow).
 template <int R>
 __device__ __forceinline__ void export_rows(RowList& me, int64_t r0, int64_t nq, uint64_t* __restrict__ warp_buf, int k, int keep_max,
-                                            uint32_t* __restrict__ cand_out, int* __restrict__ cnt_out, int lane) {
+                                            uint32_t* __restrict__ cand_out, int* __restrict__ cnt_out, int lane, const BandConsts& bc) {
     constexpr int cap = 32 * R;
     __syncwarp();
     for (int L = 0; L < 32; ++L) {
         const int64_t rL = r0 + L;
         if (rL >= nq) break;
         uint64_t x[R];
-        compact_row_approx<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, x, k, keep_max, lane);
+        compact_row_approx<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, x, k, keep_max, lane, bc);
         const int m = __shfl_sync(0xffffffffu, me.cnt, L);
         const int ovf = __shfl_sync(0xffffffffu, me.ovf, L);
 #pragma unroll

@@ -41,22 +41,66 @@ constexpr double VMAX = 128.0;
 }  // namespace tc
 
 struct SweepParams {
-    const double* un2;   // scaled centred squared norms [n]
-    int64_t n;           // database size
+    const double* un2;     // scaled centred squared norms, indexed by GLOBAL row id [n]
+    const float* dun;      // |u_i - fp16(u_i)| (scaled), by global row id [n]
+    const float* dvmax;    // device scalar: max_i dun[i]
+    const int64_t* qrows;  // optional explicit list of query rows [nq] (re-sweep of a subset); null: row r <-> q0 + r
+    int64_t n;             // database size
     int k, cap, keep_max, metric;
-    int64_t q0, nq;      // query slab
+    int64_t q0, nq;        // query slab (q0 = first global row when qrows is null)
+    int64_t a_row0;        // row of the A operand matrix that holds query 0 of this launch
     int n_qtiles, n_dbtiles;
-    int dp64;            // resident flavour: padded d / 64
-    int stagger;         // database-tile start offset per CTA (desynchronises the CTAs' L2 reads)
+    int dp64;              // resident flavour: padded d / 64
+    int passes;            // 1: single fp16 product, 3: split fp16 (hi·hi + lo·hi + hi·lo)
+    int norm_bytes;        // resident flavour: bytes of the norm chunk of one database tile (16 KB wide / 4 KB narrow)
+    int stagger;           // database-tile start offset per CTA (desynchronises the CTAs' L2 reads)
+    int lead;              // the sweep of a wave of query tiles starts `lead` database tiles before the wave's own rows
     int kchunks, k16_last, stages;  // stream flavour: K chunks per tile, k-steps in the last one; both: ring depth
-    double eps_c1, eps_c2;
-    uint64_t* cand;      // [grid, rows_per_cta, cap] scratch lists
-    uint32_t* cand_out;  // [nq, keep_max]
-    int* cnt_out;        // [nq]
+    double eps_c1, eps_c2; // passes = 3 error model
+    float acc_c, sub_c;    // passes = 1 error model (knn_epilogue.cuh BandConsts)
+    uint64_t* cand;        // [grid, rows_per_cta, cap] scratch lists
+    uint32_t* cand_out;    // [nq, keep_max]
+    int* cnt_out;          // [nq]
     unsigned long long* stats;  // [0] compactions, [1] accepted candidates
     int debug_skip_epilogue;    // debug: epilogue releases the accumulator without reading it (pure MMA rate)
-    unsigned long long* prof;   // optional [grid][16] cycle counters (debug: SPHB_KNN_PROF=1)
+    unsigned long long* prof;   // optional [grid][16] cycle counters (build -DSPHB_KNN_PROFILE, run SPHB_KNN_PROF=1)
 };
+
+__device__ __forceinline__ BandConsts make_band_consts(const SweepParams& P) {
+    BandConsts bc;
+    bc.passes = P.passes;
+    bc.l2 = P.metric == METRIC_L2 ? 1 : 0;
+    bc.vmax = static_cast<float>(tc::VMAX) * 1.001f;
+    bc.dvmax = P.passes == 1 ? __ldg(P.dvmax) : 0.f;
+    bc.acc_c = P.acc_c;
+    bc.sub_c = P.sub_c;
+    return bc;
+}
+
+// Per-row state at the start of a query tile.
+__device__ __forceinline__ void init_row(RowList& me, const SweepParams& P, int64_t r, bool valid) {
+    const int64_t gi = valid ? (P.qrows ? P.qrows[r] : P.q0 + r) : 0;
+    const double un2 = valid ? P.un2[gi] : 0.0;
+    me.thr = valid ? INFINITY : -INFINITY;
+    me.eps2 = row_eps2(un2, P.eps_c1, P.eps_c2, tc::VMAX, tc::VMAX2);
+    me.un = __double2float_ru(sqrt(un2)) * 1.0001f;
+    me.dun = (valid && P.passes == 1) ? P.dun[gi] : 0.f;
+    me.cnt = 0;
+    me.ovf = 0;
+}
+
+// First database tile of the sweep of query tile qt.  All CTAs of a wave (query tiles qt - blockIdx.x ...)
+// start just before the wave's own rows — pixels with nearby indices are the likeliest neighbours, so the
+// rows' thresholds tighten within the first few percent of the sweep and the filter's slow path becomes
+// rare — each shifted by blockIdx.x * stagger tiles so that the CTAs read different L2 lines at any moment
+// while the union of their positions stays inside an L2-sized window.
+__device__ __forceinline__ int sweep_start(const SweepParams& P, int qt, int rows_per_cta, int bn) {
+    const int64_t r0 = static_cast<int64_t>(qt - static_cast<int>(blockIdx.x)) * rows_per_cta;
+    const int64_t anchor = P.qrows ? P.qrows[r0 < P.nq ? r0 : P.nq - 1] : P.q0 + r0;
+    int64_t t = (anchor / bn - P.lead + static_cast<int64_t>(blockIdx.x) * P.stagger) % P.n_dbtiles;
+    if (t < 0) t += P.n_dbtiles;
+    return static_cast<int>(t);
+}
 
 // ---------------------------------------------------------------------------
 // prep kernels
@@ -99,56 +143,85 @@ __global__ void knn_prep_scale(const unsigned long long* __restrict__ maxbits, d
     scal[1] = s;
 }
 
-// One warp per row.  layout 0 (stream):   A[i] = [hi|hi|lo|1 1 1|0..] , B[i] = [-2hi|-2lo|-2hi|n0 n1 n2|0..], both kp wide.
-//                    layout 1 (resident): A[i] = [hi(dp)|lo(dp)]      , B[i] = [-2hi(dp)|-2lo(dp)|n0 n1 n2 0..(64)].
-// Also rescales un2[i] by s².  Buffers are pre-zeroed.
-__global__ void knn_prep_split(const float* __restrict__ X, int64_t n, int64_t np, int d, int layout, int lda, int ldb, int dp,
-                               const double* __restrict__ colsum, int centre, int with_norm, const double* __restrict__ scal,
-                               double* __restrict__ un2, __half* __restrict__ A, __half* __restrict__ B) {
+__global__ void knn_prep_rescale(double* __restrict__ un2, int64_t n, const double* __restrict__ scal) {
+    const double s2 = scal[0];
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        un2[i] *= s2;
+}
+
+// Builds the fp16 operand rows, one warp per output row.  Output row r holds point i = rowlist ? rowlist[r] : r.
+//   layout 0 (stream, K-concatenated), passes 3:  A = [hi|hi|lo|1 1 1|0..]   B = [-2hi|-2lo|-2hi|n0 n1 n2|0..]
+//                                      passes 1:  A = [hi|1 1 1|0..]         B = [-2hi|n0 n1 n2|0..]
+//   layout 1 (resident),               passes 3:  A = [hi(dp)|lo(dp)]        B = [-2hi(dp)|-2lo(dp)]    Nrm = [n0 n1 n2 0..]
+//                                      passes 1:  A = [hi(dp)]               B = [-2hi(dp)]             Nrm = [n0 n1 n2 0..]
+// (n0 n1 n2) = 3-term fp16 split of the scaled squared norm un2[i] (already rescaled).  A, B, Nrm may each be null.
+// Rows r >= nvalid are padding: zero queries, "infinitely far" database points.  dun (optional) receives
+// |u_i - hi_i| rounded up and dvmax its maximum (float bits, non-negative -> unsigned atomicMax).
+__global__ void knn_prep_split(const float* __restrict__ X, int64_t n, int64_t nvalid, int64_t nrows, const int64_t* __restrict__ rowlist, int d,
+                               int layout, int passes, int lda, int ldb, int ldn, int dp, const double* __restrict__ colsum, int centre,
+                               int with_norm, const double* __restrict__ scal, const double* __restrict__ un2, __half* __restrict__ A,
+                               __half* __restrict__ B, __half* __restrict__ Nrm, float* __restrict__ dun, unsigned int* __restrict__ dvmax) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
-    const double s = scal[1], s2 = scal[0];
-    const int ncol = layout == 0 ? 3 * d : 2 * dp;  // column of the norm / ones triple
-    for (int64_t i = warp; i < np; i += nwarps) {
-        __half* a = A + i * lda;
-        __half* b = B + i * ldb;
-        if (i >= n) {  // padding rows: zero queries, "infinitely far" database points
-            if (lane < 3) b[ncol + lane] = __float2half(65504.f);
+    const double s = scal[1];
+    const int ncol = layout == 0 ? (passes == 3 ? 3 * d : d) : 0;  // column of the norm / ones triple (layout 0)
+    float wmax = 0.f;
+    for (int64_t r = warp; r < nrows; r += nwarps) {
+        __half* a = A ? A + r * lda : nullptr;
+        __half* b = B ? B + r * ldb : nullptr;
+        __half* nr = Nrm ? Nrm + r * ldn : (b && layout == 0 ? b + ncol : nullptr);
+        if (r >= nvalid) {
+            if (nr && lane < 3) nr[lane] = __float2half(65504.f);
             continue;
         }
+        const int64_t i = rowlist ? rowlist[r] : r;
+        double err2 = 0.0;
         for (int c = lane; c < d; c += 32) {
             const double mu = centre ? colsum[c] / static_cast<double>(n) : 0.0;
             const double u = s * (static_cast<double>(X[i * d + c]) - mu);
             const __half hi = __double2half(u);
-            const __half lo = __double2half(u - static_cast<double>(__half2float(hi)));
+            const double rem = u - static_cast<double>(__half2float(hi));
+            const __half lo = __double2half(rem);
+            err2 = fma(rem, rem, err2);
             const __half mhi = __float2half(-2.f * __half2float(hi));
             const __half mlo = __float2half(-2.f * __half2float(lo));
             if (layout == 0) {
-                a[c] = hi;  a[d + c] = hi;  a[2 * d + c] = lo;
-                b[c] = mhi; b[d + c] = mlo; b[2 * d + c] = mhi;
+                if (passes == 3) {
+                    if (a) { a[c] = hi;  a[d + c] = hi;  a[2 * d + c] = lo; }
+                    if (b) { b[c] = mhi; b[d + c] = mlo; b[2 * d + c] = mhi; }
+                } else {
+                    if (a) a[c] = hi;
+                    if (b) b[c] = mhi;
+                }
             } else {
-                a[c] = hi;  a[dp + c] = lo;
-                b[c] = mhi; b[dp + c] = mlo;
+                if (a) { a[c] = hi; if (passes == 3) a[dp + c] = lo; }
+                if (b) { b[c] = mhi; if (passes == 3) b[dp + c] = mlo; }
             }
         }
+        err2 = warp_sum(err2);
         if (lane == 0) {
-            const double nn = un2[i] * s2;
-            un2[i] = nn;
-            if (layout == 0) {
+            if (dun) {
+                const float e = __double2float_ru(sqrt(err2)) * 1.0001f;
+                dun[i] = e;
+                wmax = fmaxf(wmax, e);
+            }
+            if (layout == 0 && a) {
                 const __half one = __float2half(1.f);
                 a[ncol] = one; a[ncol + 1] = one; a[ncol + 2] = one;
             }
-            if (with_norm) {
+            if (with_norm && nr) {
+                const double nn = un2[i];
                 const __half n0 = __double2half(nn);
                 const double r1 = nn - static_cast<double>(__half2float(n0));
                 const __half n1 = __double2half(r1);
                 const double r2 = r1 - static_cast<double>(__half2float(n1));
                 const __half n2 = __double2half(r2);
-                b[ncol] = n0; b[ncol + 1] = n1; b[ncol + 2] = n2;
+                nr[0] = n0; nr[1] = n1; nr[2] = n2;
             }
         }
     }
+    if (dvmax && lane == 0 && wmax > 0.f) atomicMax(dvmax, __float_as_uint(wmax));
 }
 
 __global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [1 1 1 0 ...]
@@ -157,14 +230,17 @@ __global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [
 }
 
 // ---------------------------------------------------------------------------
-// sweep, resident-query flavour (d <= 256)
+// sweep, resident-query flavour (1 pass: d <= 512, 3 passes: d <= 256)
 // ---------------------------------------------------------------------------
-// smem: [A: MH x (2*dp64) chunks | ONES chunk | B ring: stages chunks | sort buffers | barriers | tmem slot]
-// B chunk sequence per 128-row database tile: dp64 hi chunks, dp64 lo chunks, 1 norm chunk.
+// smem: [A: MH x nA chunks | ONES chunk | B ring: stages chunks | barriers | tmem slot]
+// B chunk sequence per 128-row database tile: dp64 hi chunks, (3 passes: dp64 lo chunks,) 1 norm chunk.
+// The norm chunk is a separate [np, 64] (wide, SWIZZLE_128B) or [np, 16] (narrow, SWIZZLE_32B) matrix;
+// only its first 16 columns (one k-step against the ONES tile) are used.
 template <int MH, int R>
 __global__ void __launch_bounds__(64 + 128 * MH, 1)
 knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
-                   const __grid_constant__ CUtensorMap tmapO, const SweepParams P, const int k16_tail) {
+                   const __grid_constant__ CUtensorMap tmapN, const __grid_constant__ CUtensorMap tmapO, const SweepParams P,
+                   const int k16_tail) {
     using namespace tc;
     constexpr int BN = 128;
     constexpr int ACC_COLS = MH * BN;          // columns per accumulator stage
@@ -173,8 +249,9 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int stages = P.stages, dp64 = P.dp64;
-    const int nA = 2 * dp64;          // A chunks per M half
-    const int nB = 2 * dp64 + 1;      // B chunks per database tile
+    const bool three = P.passes == 3;
+    const int nA = three ? 2 * dp64 : dp64;  // A chunks per M half
+    const int nB = nA + 1;                   // B chunks per database tile (the last one is the norm chunk)
     const uint32_t smem_base = ptx::smem_u32(smem);
     const uint32_t sA = smem_base;                                   // [m][c] -> sA + (m*nA + c)*CHUNK_BYTES
     const uint32_t sO = sA + MH * nA * CHUNK_BYTES;
@@ -189,11 +266,11 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 6);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int dt0 = static_cast<int>((static_cast<int64_t>(blockIdx.x) * P.stagger) % P.n_dbtiles);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmapA);
         ptx::prefetch_tmap(&tmapB);
+        ptx::prefetch_tmap(&tmapN);
         ptx::prefetch_tmap(&tmapO);
         for (int s = 0; s < stages; ++s) {
             ptx::mbar_init(bar_full + 8 * s, 1);
@@ -218,106 +295,112 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
 
     if (warp == 0) {
         // ===================== TMA producer (warp-uniform control flow, one elected lane issues) =====================
-        {
-            int stage = 0;
-            uint32_t phase = 0, aphase = 0;
-            bool first = true;
-            long long pw = 0, pt0 = clock64();
-            for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
-                ptx::mbar_wait(bar_aempty, aphase ^ 1);  // previous query tile fully consumed
-                if (ptx::elect_one_sync()) {
-                    ptx::mbar_expect_tx(bar_afull, (MH * nA + (first ? 1 : 0)) * CHUNK_BYTES);
-                    for (int m = 0; m < MH; ++m) {
-                        const int32_t qrow = static_cast<int32_t>(P.q0 + (static_cast<int64_t>(qt) * MH + m) * BM);
-                        for (int c = 0; c < nA; ++c) ptx::tma_load_2d(sA + (m * nA + c) * CHUNK_BYTES, &tmapA, bar_afull, c * BK, qrow);
-                    }
-                    if (first) ptx::tma_load_2d(sO, &tmapO, bar_afull, 0, 0);
+        int stage = 0;
+        uint32_t phase = 0, aphase = 0;
+        bool first = true;
+        long long pw = 0, pt0 = SPHB_CLOCK();
+        for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+            ptx::mbar_wait(bar_aempty, aphase ^ 1);  // previous query tile fully consumed
+            if (ptx::elect_one_sync()) {
+                ptx::mbar_expect_tx(bar_afull, (MH * nA + (first ? 1 : 0)) * CHUNK_BYTES);
+                for (int m = 0; m < MH; ++m) {
+                    const int32_t qrow = static_cast<int32_t>(P.a_row0 + (static_cast<int64_t>(qt) * MH + m) * BM);
+                    for (int c = 0; c < nA; ++c) ptx::tma_load_2d(sA + (m * nA + c) * CHUNK_BYTES, &tmapA, bar_afull, c * BK, qrow);
                 }
-                __syncwarp();
-                first = false;
-                aphase ^= 1;
-                for (int t = 0; t < P.n_dbtiles; ++t) {
-                    const int dt = (dt0 + t) % P.n_dbtiles;
-                    for (int c = 0; c < nB; ++c) {
-                        const long long w0 = clock64();
-                        ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                        pw += clock64() - w0;
-                        if (ptx::elect_one_sync()) {
+                if (first) ptx::tma_load_2d(sO, &tmapO, bar_afull, 0, 0);
+            }
+            __syncwarp();
+            first = false;
+            aphase ^= 1;
+            const int dt0 = sweep_start(P, qt, MH * BM, BN);
+            for (int t = 0; t < P.n_dbtiles; ++t) {
+                const int dt = (dt0 + t) % P.n_dbtiles;
+                for (int c = 0; c < nB; ++c) {
+                    const long long w0 = SPHB_CLOCK();
+                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    pw += SPHB_CLOCK() - w0;
+                    if (ptx::elect_one_sync()) {
+                        if (c < nB - 1) {
                             ptx::mbar_expect_tx(bar_full + 8 * stage, CHUNK_BYTES);
                             ptx::tma_load_2d(sB + stage * CHUNK_BYTES, &tmapB, bar_full + 8 * stage, c * BK, dt * BN);
+                        } else {
+                            ptx::mbar_expect_tx(bar_full + 8 * stage, P.norm_bytes);
+                            ptx::tma_load_2d(sB + stage * CHUNK_BYTES, &tmapN, bar_full + 8 * stage, 0, dt * BN);
                         }
-                        __syncwarp();
-                        if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
+                    __syncwarp();
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
             }
-            if (P.prof && lane == 0) {
-                P.prof[blockIdx.x * 16 + 0] = pw;
-                P.prof[blockIdx.x * 16 + 1] = clock64() - pt0;
-            }
+        }
+        if (P.prof && lane == 0) {
+            P.prof[blockIdx.x * 16 + 0] = pw;
+            P.prof[blockIdx.x * 16 + 1] = SPHB_CLOCK() - pt0;
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (warp-uniform control flow, one elected lane issues) =====================
-        {
-            constexpr uint32_t idesc = ptx::make_idesc_f16(BM, BN);
-            int stage = 0;
-            uint32_t phase = 0, aphase = 0;
-            int as = 0;
-            uint32_t accphase = 0;
-            const uint64_t odesc = ptx::make_smem_desc_sw128(sO);
-            long long mw_te = 0, mw_f = 0, mt0 = clock64();
-            for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
-                ptx::mbar_wait(bar_afull, aphase);
-                aphase ^= 1;
+        constexpr uint32_t idesc = ptx::make_idesc_f16(BM, BN);
+        int stage = 0;
+        uint32_t phase = 0, aphase = 0;
+        int as = 0;
+        uint32_t accphase = 0;
+        const uint64_t odesc = ptx::make_smem_desc_sw128(sO);
+        const bool narrow = P.norm_bytes != CHUNK_BYTES;
+        long long mw_te = 0, mw_f = 0, mt0 = SPHB_CLOCK();
+        for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+            ptx::mbar_wait(bar_afull, aphase);
+            aphase ^= 1;
+            ptx::tc_fence_after();
+            for (int t = 0; t < P.n_dbtiles; ++t) {
+                long long w0 = SPHB_CLOCK();
+                ptx::mbar_wait(bar_tempty + 8 * as, accphase ^ 1);
+                mw_te += SPHB_CLOCK() - w0;
                 ptx::tc_fence_after();
-                for (int t = 0; t < P.n_dbtiles; ++t) {
-                    long long w0 = clock64();
-                    ptx::mbar_wait(bar_tempty + 8 * as, accphase ^ 1);
-                    mw_te += clock64() - w0;
+                for (int c = 0; c < nB; ++c) {
+                    w0 = SPHB_CLOCK();
+                    ptx::mbar_wait(bar_full + 8 * stage, phase);
+                    mw_f += SPHB_CLOCK() - w0;
                     ptx::tc_fence_after();
-                    for (int c = 0; c < nB; ++c) {
-                        w0 = clock64();
-                        ptx::mbar_wait(bar_full + 8 * stage, phase);
-                        mw_f += clock64() - w0;
-                        ptx::tc_fence_after();
-                        const uint64_t bdesc = ptx::make_smem_desc_sw128(sB + stage * CHUNK_BYTES);
-                        if (ptx::elect_one_sync()) {
+                    const uint32_t sb = sB + stage * CHUNK_BYTES;
+                    const uint64_t bdesc = ptx::make_smem_desc_sw128(sb);
+                    if (ptx::elect_one_sync()) {
 #pragma unroll
                         for (int m = 0; m < MH; ++m) {
                             const uint32_t tmem_d = tmem_base + as * ACC_COLS + m * BN;
                             if (c < dp64) {
-                                // database hi chunk c: x query hi chunk c and x query lo chunk c
+                                // database hi chunk c  x  query hi chunk c (and, 3 passes, query lo chunk c)
                                 const int nk = (c == dp64 - 1) ? k16_tail : 4;
                                 const uint64_t ah = ptx::make_smem_desc_sw128(sA + (m * nA + c) * CHUNK_BYTES);
-                                const uint64_t al = ptx::make_smem_desc_sw128(sA + (m * nA + dp64 + c) * CHUNK_BYTES);
                                 for (int kk = 0; kk < nk; ++kk) ptx::umma_f16(tmem_d, ah + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0);
-                                for (int kk = 0; kk < nk; ++kk) ptx::umma_f16(tmem_d, al + 2 * kk, bdesc + 2 * kk, idesc, 1);
-                            } else if (c < 2 * dp64) {
-                                // database lo chunk: x query hi chunk
+                                if (three) {
+                                    const uint64_t al = ptx::make_smem_desc_sw128(sA + (m * nA + dp64 + c) * CHUNK_BYTES);
+                                    for (int kk = 0; kk < nk; ++kk) ptx::umma_f16(tmem_d, al + 2 * kk, bdesc + 2 * kk, idesc, 1);
+                                }
+                            } else if (c < nB - 1) {
+                                // (3 passes) database lo chunk  x  query hi chunk
                                 const int cc = c - dp64;
                                 const int nk = (cc == dp64 - 1) ? k16_tail : 4;
                                 const uint64_t ah = ptx::make_smem_desc_sw128(sA + (m * nA + cc) * CHUNK_BYTES);
                                 for (int kk = 0; kk < nk; ++kk) ptx::umma_f16(tmem_d, ah + 2 * kk, bdesc + 2 * kk, idesc, 1);
                             } else {
                                 // norm chunk: ones x (n0 n1 n2), one k-step
-                                ptx::umma_f16(tmem_d, odesc, bdesc, idesc, 1);
+                                ptx::umma_f16(tmem_d, odesc, narrow ? ptx::make_smem_desc_sw32(sb) : bdesc, idesc, 1);
                             }
                         }
                         ptx::umma_commit(bar_empty + 8 * stage);
                         if (c == nB - 1) ptx::umma_commit(bar_tfull + 8 * as);
                         if (c == nB - 1 && t == P.n_dbtiles - 1) ptx::umma_commit(bar_aempty);  // query tile consumed
-                        }
-                        __syncwarp();
-                        if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
-                    if (++as == 2) { as = 0; accphase ^= 1; }
+                    __syncwarp();
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
+                if (++as == 2) { as = 0; accphase ^= 1; }
             }
-            if (P.prof && lane == 0) {
-                P.prof[blockIdx.x * 16 + 2] = mw_te;
-                P.prof[blockIdx.x * 16 + 3] = mw_f;
-                P.prof[blockIdx.x * 16 + 4] = clock64() - mt0;
-            }
+        }
+        if (P.prof && lane == 0) {
+            P.prof[blockIdx.x * 16 + 2] = mw_te;
+            P.prof[blockIdx.x * 16 + 3] = mw_f;
+            P.prof[blockIdx.x * 16 + 4] = SPHB_CLOCK() - mt0;
         }
     } else {
         // ===================== epilogue =====================
@@ -326,11 +409,12 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         const int mhalf = ew >> 2;
         constexpr int cap = 32 * R;
         const int k = P.k, keep_max = P.keep_max;
+        const BandConsts bc = make_band_consts(P);
         int as = 0;
         uint32_t accphase = 0;
         unsigned long long n_compact = 0, n_accept = 0;
         const uint32_t n32 = static_cast<uint32_t>(P.n);
-        long long ew_tf = 0, e_ld = 0, e_filt = 0, e_exp = 0, e_cmp = 0, et0 = clock64();
+        long long ew_tf = 0, e_ld = 0, e_filt = 0, e_exp = 0, e_cmp = 0, et0 = SPHB_CLOCK();
         for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
             const int row_in_tile = mhalf * BM + quarter * 32 + lane;
             const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
@@ -338,49 +422,47 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             uint64_t* warp_buf = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + (row_in_tile - lane)) * cap;
             uint64_t* mybuf = warp_buf + static_cast<size_t>(lane) * cap;
             RowList me;
-            me.thr = valid ? INFINITY : -INFINITY;
-            me.eps2 = row_eps2(valid ? P.un2[P.q0 + r] : 0.0, P.eps_c1, P.eps_c2, VMAX, VMAX2);
-            me.cnt = 0;
-            me.ovf = 0;
+            init_row(me, P, r, valid);
+            const int dt0 = sweep_start(P, qt, MH * BM, BN);
             for (int t = 0; t < P.n_dbtiles; ++t) {
                 const int dt = (dt0 + t) % P.n_dbtiles;
-                long long w0 = clock64();
+                long long w0 = SPHB_CLOCK();
                 ptx::mbar_wait(bar_tfull + 8 * as, accphase);
-                ew_tf += clock64() - w0;
+                ew_tf += SPHB_CLOCK() - w0;
                 ptx::tc_fence_after();
                 const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
 #pragma unroll 1
                 for (int c = 0; c < (P.debug_skip_epilogue ? 0 : BN / 32); c += 2) {
                     float v0[32], v1[32];
-                    w0 = clock64();
+                    w0 = SPHB_CLOCK();
                     ptx::tmem_ld_32x32(taddr + c * 32, v0);       // two loads in flight before the wait
                     ptx::tmem_ld_32x32(taddr + c * 32 + 32, v1);
                     ptx::tmem_ld_wait(v0);
                     ptx::tmem_ld_wait(v1);
-                    const long long w1 = clock64();
+                    const long long w1 = SPHB_CLOCK();
                     e_ld += w1 - w0;
                     filter_chunk(v0, jbase + c * 32, n32, me, mybuf, n_accept);
-                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, n_compact, e_cmp);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
                     filter_chunk(v1, jbase + c * 32 + 32, n32, me, mybuf, n_accept);
-                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, n_compact, e_cmp);
-                    e_filt += clock64() - w1;
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
+                    e_filt += SPHB_CLOCK() - w1;
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
                 if (++as == 2) { as = 0; accphase ^= 1; }
             }
-            const long long x0 = clock64();
-            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane);
-            e_exp += clock64() - x0;
+            const long long x0 = SPHB_CLOCK();
+            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
+            e_exp += SPHB_CLOCK() - x0;
         }
         if (P.prof && lane == 0) {
             atomicAdd(P.prof + blockIdx.x * 16 + 5, static_cast<unsigned long long>(ew_tf));
             atomicAdd(P.prof + blockIdx.x * 16 + 6, static_cast<unsigned long long>(e_ld));
             atomicAdd(P.prof + blockIdx.x * 16 + 7, static_cast<unsigned long long>(e_filt));
             atomicAdd(P.prof + blockIdx.x * 16 + 8, static_cast<unsigned long long>(e_exp));
-            atomicAdd(P.prof + blockIdx.x * 16 + 9, static_cast<unsigned long long>(clock64() - et0));
+            atomicAdd(P.prof + blockIdx.x * 16 + 9, static_cast<unsigned long long>(SPHB_CLOCK() - et0));
             atomicAdd(P.prof + blockIdx.x * 16 + 10, static_cast<unsigned long long>(e_cmp));
         }
         if (P.stats) {
@@ -425,7 +507,6 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t smem_base = ptx::smem_u32(smem);
-    const int dt0 = static_cast<int>((static_cast<int64_t>(blockIdx.x) * P.stagger) % P.n_dbtiles);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmapA);
@@ -454,7 +535,8 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             int stage = 0;
             uint32_t phase = 0;
             for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
-                const int32_t qrow = static_cast<int32_t>(P.q0 + static_cast<int64_t>(qt) * BM);
+                const int32_t qrow = static_cast<int32_t>(P.a_row0 + static_cast<int64_t>(qt) * BM);
+                const int dt0 = sweep_start(P, qt, BM, BN);
                 for (int t = 0; t < P.n_dbtiles; ++t) {
                     const int dt = (dt0 + t) % P.n_dbtiles;
                     for (int kc = 0; kc < P.kchunks; ++kc) {
@@ -500,6 +582,7 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
         const int quarter = warp & 3;
         constexpr int cap = 32 * R;
         const int k = P.k, keep_max = P.keep_max;
+        const BandConsts bc = make_band_consts(P);
         int as = 0;
         uint32_t accphase = 0;
         unsigned long long n_compact = 0, n_accept = 0;
@@ -512,10 +595,8 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             uint64_t* warp_buf = P.cand + (static_cast<size_t>(blockIdx.x) * BM + quarter * 32) * cap;
             uint64_t* mybuf = warp_buf + static_cast<size_t>(lane) * cap;
             RowList me;
-            me.thr = valid ? INFINITY : -INFINITY;
-            me.eps2 = row_eps2(valid ? P.un2[P.q0 + r] : 0.0, P.eps_c1, P.eps_c2, VMAX, VMAX2);
-            me.cnt = 0;
-            me.ovf = 0;
+            init_row(me, P, r, valid);
+            const int dt0 = sweep_start(P, qt, BM, BN);
             for (int t = 0; t < P.n_dbtiles; ++t) {
                 const int dt = (dt0 + t) % P.n_dbtiles;
                 ptx::mbar_wait(bar_tfull + 8 * as, accphase);
@@ -530,16 +611,16 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                     ptx::tmem_ld_wait(v0);
                     ptx::tmem_ld_wait(v1);
                     filter_chunk(v0, jbase + c * 32, n32, me, mybuf, n_accept);
-                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, n_compact, e_cmp);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
                     filter_chunk(v1, jbase + c * 32 + 32, n32, me, mybuf, n_accept);
-                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, n_compact, e_cmp);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
                 if (++as == 2) { as = 0; accphase ^= 1; }
             }
-            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane);
+            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
         }
         if (P.stats) {
             n_accept = warp_sum(static_cast<double>(n_accept));
@@ -557,9 +638,11 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
 // ---------------------------------------------------------------------------
 // exact re-rank of the surviving candidates (one warp per query row)
 // ---------------------------------------------------------------------------
+// Row r of this launch is point gi = qrows ? qrows[r] : q0 + r; it is written to output row gi - out_q0.
 __global__ void __launch_bounds__(256) knn_rerank_kernel(const float* __restrict__ X, int d, int k, int cap, int keep_max, int metric,
-                                                         int l2_squared, int64_t q0, int64_t nq, const uint32_t* __restrict__ cand,
-                                                         const int* __restrict__ cnt, int64_t* __restrict__ ids, float* __restrict__ dist,
+                                                         int l2_squared, int64_t q0, int64_t nq, const int64_t* __restrict__ qrows,
+                                                         int64_t out_q0, const uint32_t* __restrict__ cand, const int* __restrict__ cnt,
+                                                         int64_t* __restrict__ ids, float* __restrict__ dist,
                                                          int64_t* __restrict__ ovf_rows, int* __restrict__ ovf_count) {
     extern __shared__ uint64_t smem_keys[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -568,12 +651,12 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(const float* __restrict
     const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
     for (int64_t r = gw; r < nq; r += nw) {
         const int c = cnt[r];
+        const int64_t gi = qrows ? qrows[r] : q0 + r;
         if (c & OVERFLOW_FLAG) {
-            if (lane == 0) ovf_rows[atomicAdd(ovf_count, 1)] = q0 + r;
+            if (lane == 0) ovf_rows[atomicAdd(ovf_count, 1)] = gi;
             continue;
         }
         const int m = c;
-        const int64_t gi = q0 + r;
         for (int t = lane; t < cap; t += 32) {
             uint64_t key = ~0ull;
             if (t < m) {
@@ -584,7 +667,8 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(const float* __restrict
         }
         __syncwarp();
         warp_bitonic_sort(sm, cap, lane);
-        write_row(sm, min(m, k), k, gi, metric, l2_squared, ids + r * k, dist + r * k, lane);
+        const int64_t orow = gi - out_q0;
+        write_row(sm, min(m, k), k, gi, metric, l2_squared, ids + orow * k, dist + orow * k, lane);
         __syncwarp();
     }
 }
@@ -608,16 +692,18 @@ static EncodeFn get_encode_fn() {
     return fn;
 }
 
-// 2-D fp16 row-major [rows, cols] tensor, box = 64 columns x box_rows rows, 128B swizzle, zero OOB fill.
-static int make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t cols, int box_rows) {
+// 2-D fp16 row-major [rows, cols] tensor, box = box_cols columns x box_rows rows, zero OOB fill.
+// box_cols = 64 -> SWIZZLE_128B (one 128 B swizzle span per row), box_cols = 16 -> SWIZZLE_32B.
+static int make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t cols, int box_rows, int box_cols = tc::BK) {
     EncodeFn enc = get_encode_fn();
     if (!enc) return fail(3, "cuTensorMapEncodeTiled entry point not found");
     const cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
     const cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 2};
-    const cuuint32_t box[2] = {static_cast<cuuint32_t>(tc::BK), static_cast<cuuint32_t>(box_rows)};
+    const cuuint32_t box[2] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows)};
     const cuuint32_t estr[2] = {1, 1};
+    const CUtensorMapSwizzle sw = box_cols == 16 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B;
     const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                           sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(3, "cuTensorMapEncodeTiled failed: " + std::to_string(static_cast<int>(r)));
     return 0;
 }
@@ -628,100 +714,132 @@ static int next_pow2_i(int v) {
     return p;
 }
 
-static int64_t g_knn_stats[6] = {0, 0, 0, 0, 0, 0};
-static float g_knn_ms[3] = {0.f, 0.f, 0.f};  // prep, sweep, rerank (CUDA events on the launching stream)
-void knn_get_timing(float* ms3) { for (int i = 0; i < 3; ++i) ms3[i] = g_knn_ms[i]; }
-struct EventQuad {
-    cudaEvent_t e[4] = {nullptr, nullptr, nullptr, nullptr};
-    EventQuad() { for (auto& x : e) cudaEventCreate(&x); }
-    ~EventQuad() { for (auto& x : e) if (x) cudaEventDestroy(x); }
-};
-void knn_set_stats(const int64_t* s) { for (int i = 0; i < 6; ++i) g_knn_stats[i] = s[i]; }
-void knn_get_stats(int64_t* s) { for (int i = 0; i < 6; ++i) s[i] = g_knn_stats[i]; }
+static int64_t g_knn_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+static float g_knn_ms[4] = {0.f, 0.f, 0.f, 0.f};  // prep, main sweep(s), re-rank(s), fallback (CUDA events on the launching stream)
+void knn_get_timing(float* ms4) { for (int i = 0; i < 4; ++i) ms4[i] = g_knn_ms[i]; }
+void knn_set_stats(const int64_t* s) { for (int i = 0; i < 8; ++i) g_knn_stats[i] = s[i]; }
+void knn_get_stats(int64_t* s) { for (int i = 0; i < 8; ++i) s[i] = g_knn_stats[i]; }
 
 bool knn_tc_supported(int64_t n, int d, int k) {
     if (d < 8 || n < 1024) return false;
     if (n >= (1ll << 31)) return false;
     if (3 * d + 3 > 65536) return false;
-    if (next_pow2_i(k + 96) > 1024) return false;
+    if (next_pow2_i(k + 160) > 1024) return false;
     return true;
 }
 
-// flavour: 0 auto, 1 force streaming kernel, 2 force resident MH=1 (d <= 256)
-int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1, int64_t* d_ids,
-                  float* d_dist, cudaStream_t stream, int flavour) {
-    using namespace tc;
-    const int64_t nq = q1 - q0;
-    if (nq <= 0) return 0;
-    const int centre = metric == METRIC_L2 ? 1 : 0;
-    const int sms = ctx().num_sms;
-    const int cap = std::max(256, next_pow2_i(k + 96));
-    const int keep_max = cap - 64;
+namespace {
 
-    // ---- choose the kernel flavour and the operand layout
-    const int dp = (d + 63) / 64 * 64;
-    int MH = 0;  // 0 = streaming
-    if (flavour != 1 && dp <= 256) MH = (dp <= 128 && flavour != 2) ? 2 : 1;
-    const int layout = MH ? 1 : 0;
-    const int kp = ((3 * d + 3) + 15) / 16 * 16;  // streaming K extent
-    const int lda = MH ? 2 * dp : kp;
-    const int ldb = MH ? 2 * dp + 64 : kp;
-    const int bn = MH ? 128 : tcs::BN;
-    const int64_t np = (n + 255) / 256 * 256;
-    const int rows_per_cta = MH ? MH * BM : BM;
-    const int n_qtiles = static_cast<int>((nq + rows_per_cta - 1) / rows_per_cta);
-    const int n_dbtiles = static_cast<int>(np / bn);
-    const int grid = std::min(sms, n_qtiles);
+struct EventTimer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    EventTimer() { cudaEventCreate(&a); cudaEventCreate(&b); }
+    ~EventTimer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+    void start(cudaStream_t s) { cudaEventRecord(a, s); }
+    void stop(cudaStream_t s) { cudaEventRecord(b, s); }
+    float ms() { float v = 0.f; cudaEventSynchronize(b); cudaEventElapsedTime(&v, a, b); return v; }
+};
 
+// fp16 operand matrices of one (passes, flavour) combination
+struct Operands {
+    int passes = 0, MH = 0;       // MH = 0: streaming flavour
+    int lda = 0, ldb = 0, ldn = 0;
+    int64_t a_rows = 0;           // rows of A (np for the full matrix, padded list length for a gathered one)
+    DevBuf<__half> A, B, N;
+    bool built_b = false;
+};
+
+// Everything one kNN call shares between its sweeps.
+struct KnnJob {
+    const float* x; int64_t n; int d, k, metric, l2_squared;
+    int64_t np; int dp; int centre, sms;
+    cudaStream_t stream;
     DevBuf<double> colsum, un2, scal;
     DevBuf<unsigned long long> maxbits, stats;
-    DevBuf<__half> A, B, ones;
+    DevBuf<float> dun;
+    DevBuf<unsigned int> dvmax;
+    DevBuf<__half> ones;
+    bool narrow_norm;
+    int64_t sum_compactions = 0, sum_accepted = 0;
+};
+
+int build_operands(KnnJob& J, Operands& op, int passes, int MH, const int64_t* d_rowlist, int64_t nlist, bool want_a, bool want_b) {
+    const int d = J.d, dp = J.dp;
+    const int layout = MH ? 1 : 0;
+    op.passes = passes; op.MH = MH;
+    const int kp = ((passes == 3 ? 3 * d + 3 : d + 3) + 15) / 16 * 16;
+    op.lda = MH ? (passes == 3 ? 2 * dp : dp) : kp;
+    op.ldb = op.lda;
+    op.ldn = MH ? (J.narrow_norm ? 16 : 64) : 0;
+    const int64_t rows_a = d_rowlist ? (nlist + 255) / 256 * 256 : J.np;
+    cudaStream_t s = J.stream;
+    if (want_a) {
+        op.a_rows = rows_a;
+        SPHB_CUDA(op.A.alloc(static_cast<size_t>(rows_a) * op.lda, s));
+        SPHB_CUDA(cudaMemsetAsync(op.A.p, 0, static_cast<size_t>(rows_a) * op.lda * sizeof(__half), s));
+    }
+    if (want_b) {
+        SPHB_CUDA(op.B.alloc(static_cast<size_t>(J.np) * op.ldb, s));
+        SPHB_CUDA(cudaMemsetAsync(op.B.p, 0, static_cast<size_t>(J.np) * op.ldb * sizeof(__half), s));
+        if (MH) {
+            SPHB_CUDA(op.N.alloc(static_cast<size_t>(J.np) * op.ldn, s));
+            SPHB_CUDA(cudaMemsetAsync(op.N.p, 0, static_cast<size_t>(J.np) * op.ldn * sizeof(__half), s));
+        }
+        op.built_b = true;
+    }
+    const int with_norm = J.metric == METRIC_L2 ? 1 : 0;
+    if (d_rowlist) {
+        // gathered A rows only (the database side is always the full matrix)
+        knn_prep_split<<<J.sms * 8, 256, 0, s>>>(J.x, J.n, nlist, rows_a, d_rowlist, d, layout, passes, op.lda, op.ldb, op.ldn, dp, J.colsum.p,
+                                                 J.centre, with_norm, J.scal.p, J.un2.p, op.A.p, nullptr, nullptr, nullptr, nullptr);
+    } else {
+        knn_prep_split<<<J.sms * 8, 256, 0, s>>>(J.x, J.n, J.n, J.np, nullptr, d, layout, passes, op.lda, op.ldb, op.ldn, dp, J.colsum.p, J.centre,
+                                                 with_norm, J.scal.p, J.un2.p, want_a ? op.A.p : nullptr, want_b ? op.B.p : nullptr,
+                                                 want_b && MH ? op.N.p : nullptr, J.dun.p, J.dvmax.p);
+    }
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// One sweep + exact re-rank of query rows: either the slab [qa, qb) (A rows taken from the full operand
+// matrix) or the explicit list d_qrows[0..nq) (A rows from the gathered matrix opA).  Rows whose band
+// overflowed are appended to ovf_rows / ovf_count (device) and their number is returned in *n_ovf.
+int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_t qa, int64_t qb, const int64_t* d_qrows, int64_t out_q0,
+                     int64_t* d_ids, float* d_dist, int64_t* d_ovf_rows, int* d_ovf_count, int* n_ovf, float* sweep_ms, float* rerank_ms) {
+    using namespace tc;
+    cudaStream_t stream = J.stream;
+    const int passes = opB.passes, MH = opB.MH, d = J.d, k = J.k, dp = J.dp;
+    const int64_t nq = qb - qa;
+    if (nq <= 0) { *n_ovf = 0; return 0; }
+    const int cap = passes == 1 ? std::max(512, next_pow2_i(k + 160)) : std::max(256, next_pow2_i(k + 96));
+    const int keep_max = cap - 64;
+    const int bn = MH ? 128 : tcs::BN;
+    const int rows_per_cta = MH ? MH * BM : BM;
+    const int n_qtiles = static_cast<int>((nq + rows_per_cta - 1) / rows_per_cta);
+    const int n_dbtiles = static_cast<int>(J.np / bn);
+    const int grid = std::min(J.sms, n_qtiles);
+
     DevBuf<uint64_t> cand;
     DevBuf<uint32_t> cand_out;
-    DevBuf<int> cnt_out, ovf_count;
-    DevBuf<int64_t> ovf_rows;
-    SPHB_CUDA(colsum.alloc(d, stream));
-    SPHB_CUDA(un2.alloc(n, stream));
-    SPHB_CUDA(scal.alloc(2, stream));
-    SPHB_CUDA(maxbits.alloc(1, stream));
-    SPHB_CUDA(stats.alloc(2, stream));
-    SPHB_CUDA(A.alloc(static_cast<size_t>(np) * lda, stream));
-    SPHB_CUDA(B.alloc(static_cast<size_t>(np) * ldb, stream));
-    SPHB_CUDA(ones.alloc(128 * 64, stream));
+    DevBuf<int> cnt_out;
     SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * rows_per_cta * cap, stream));
     SPHB_CUDA(cand_out.alloc(static_cast<size_t>(nq) * keep_max, stream));
     SPHB_CUDA(cnt_out.alloc(nq, stream));
-    SPHB_CUDA(ovf_count.alloc(1, stream));
-    SPHB_CUDA(ovf_rows.alloc(nq, stream));
-    SPHB_CUDA(cudaMemsetAsync(colsum.p, 0, d * sizeof(double), stream));
-    SPHB_CUDA(cudaMemsetAsync(maxbits.p, 0, sizeof(unsigned long long), stream));
-    SPHB_CUDA(cudaMemsetAsync(stats.p, 0, 2 * sizeof(unsigned long long), stream));
-    SPHB_CUDA(cudaMemsetAsync(ovf_count.p, 0, sizeof(int), stream));
-    SPHB_CUDA(cudaMemsetAsync(A.p, 0, static_cast<size_t>(np) * lda * sizeof(__half), stream));
-    SPHB_CUDA(cudaMemsetAsync(B.p, 0, static_cast<size_t>(np) * ldb * sizeof(__half), stream));
-
-    EventQuad ev;
-    cudaEventRecord(ev.e[0], stream);
-    if (centre) {
-        dim3 g(static_cast<unsigned>(std::min<int64_t>(n, sms * 8)), static_cast<unsigned>((d + 127) / 128));
-        knn_prep_colsum<<<g, 128, 0, stream>>>(d_x, n, d, colsum.p);
-        count_launch();
-    }
-    knn_prep_norms<<<sms * 8, 256, 0, stream>>>(d_x, n, d, colsum.p, centre, un2.p, maxbits.p);
-    knn_prep_scale<<<1, 1, 0, stream>>>(maxbits.p, scal.p);
-    knn_prep_split<<<sms * 8, 256, 0, stream>>>(d_x, n, np, d, layout, lda, ldb, dp, colsum.p, centre, metric == METRIC_L2 ? 1 : 0, scal.p,
-                                                un2.p, A.p, B.p);
-    knn_prep_ones<<<32, 256, 0, stream>>>(ones.p);
-    count_launch(4);
-    SPHB_CUDA(cudaGetLastError());
+    SPHB_CUDA(cudaMemsetAsync(J.stats.p, 0, 2 * sizeof(unsigned long long), stream));
 
     SweepParams P{};
-    P.un2 = un2.p; P.n = n; P.k = k; P.cap = cap; P.keep_max = keep_max; P.metric = metric;
-    P.q0 = q0; P.nq = nq; P.n_qtiles = n_qtiles; P.n_dbtiles = n_dbtiles;
-    P.cand = cand.p; P.cand_out = cand_out.p; P.cnt_out = cnt_out.p; P.stats = stats.p;
+    P.un2 = J.un2.p; P.dun = J.dun.p; P.dvmax = reinterpret_cast<const float*>(J.dvmax.p); P.qrows = d_qrows;
+    P.n = J.n; P.k = k; P.cap = cap; P.keep_max = keep_max; P.metric = J.metric;
+    P.q0 = qa; P.nq = nq; P.a_row0 = d_qrows ? 0 : qa; P.n_qtiles = n_qtiles; P.n_dbtiles = n_dbtiles;
+    P.passes = passes;
+    P.cand = cand.p; P.cand_out = cand_out.p; P.cnt_out = cnt_out.p; P.stats = J.stats.p;
     P.debug_skip_epilogue = getenv("SPHB_KNN_DEBUG_SKIP_EPI") ? 1 : 0;
     DevBuf<unsigned long long> prof;
+#ifdef SPHB_KNN_PROFILE
     const bool want_prof = getenv("SPHB_KNN_PROF") != nullptr;
+#else
+    const bool want_prof = false;
+#endif
     if (want_prof) {
         SPHB_CUDA(prof.alloc(static_cast<size_t>(grid) * 16, stream));
         SPHB_CUDA(cudaMemsetAsync(prof.p, 0, static_cast<size_t>(grid) * 16 * sizeof(unsigned long long), stream));
@@ -732,34 +850,45 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         // moment (no L2 hot lines) while the union of their positions stays inside an L2-sized window.
         const char* e = getenv("SPHB_KNN_STAGGER");
         P.stagger = e ? atoi(e) : 4;
+        const char* l = getenv("SPHB_KNN_LEAD_ROWS");
+        P.lead = (l ? atoi(l) : 16384) / bn;
     }
-    // GEMM error bound: split truncation 6·2^-22 + accumulation (one 2^-22 per k-step),
-    // times the magnitude (2|u||v| + |v|²); plus the fp16 subnormal floor; safety factor 2.
-    const int ksteps = MH ? (3 * dp / UMMA_K + 1) : kp / UMMA_K;
+    // Error models.  3 passes: split truncation 6·2^-22 + accumulation (one 2^-22 per
+    // k-step), times the magnitude (2|u||v| + |v|²), plus the fp16 subnormal floor; safety factor 2.
+    // 1 pass: operand rounding is bounded from the measured |u - fp16(u)| norms (knn_epilogue.cuh); the
+    // accumulation coefficient is 8·2^-22 per k-step.
+    const int kp = opB.lda;
+    const int ksteps = MH ? ((passes == 3 ? 3 : 1) * dp / UMMA_K + 1) : kp / UMMA_K;
     P.eps_c1 = 2.0 * (6.0 + ksteps) * std::ldexp(1.0, -22);
     P.eps_c2 = 2.0 * std::ldexp(1.0, -23) * std::sqrt(static_cast<double>(d));
+    P.acc_c = static_cast<float>(8.0 * (ksteps + 1) * std::ldexp(1.0, -22));
+    P.sub_c = static_cast<float>(std::sqrt(static_cast<double>(d)) * std::ldexp(1.0, -25) * 1.01);
 
-    CUtensorMap tmA, tmB, tmO;
-    if (int rc = make_tmap(&tmA, A.p, np, lda, BM)) return rc;
-    if (int rc = make_tmap(&tmB, B.p, np, ldb, bn)) return rc;
-    if (int rc = make_tmap(&tmO, ones.p, 128, 64, 128)) return rc;
+    CUtensorMap tmA, tmB, tmN, tmO;
+    if (int rc = make_tmap(&tmA, opA.A.p, opA.a_rows, opA.lda, BM)) return rc;
+    if (int rc = make_tmap(&tmB, opB.B.p, J.np, opB.ldb, bn)) return rc;
+    if (int rc = make_tmap(&tmO, J.ones.p, 128, 64, 128)) return rc;
 
     const size_t smem_limit = 227 * 1024;
-    cudaEventRecord(ev.e[1], stream);
+    EventTimer tsweep, trerank;
+    tsweep.start(stream);
     if (MH) {
+        if (int rc = make_tmap(&tmN, opB.N.p, J.np, opB.ldn, bn, opB.ldn == 16 ? 16 : 64)) return rc;
         const int dp64 = dp / 64;
-        const size_t fixed = static_cast<size_t>(MH * 2 * dp64 + 1) * CHUNK_BYTES + 256 + 1024;
+        const int nA = (passes == 3 ? 2 : 1) * dp64;
+        const size_t fixed = static_cast<size_t>(MH * nA + 1) * CHUNK_BYTES + 256 + 1024;
         int stages = 8;
         while (stages > 2 && fixed + static_cast<size_t>(stages) * CHUNK_BYTES > smem_limit) --stages;
         const size_t smem = fixed + static_cast<size_t>(stages) * CHUNK_BYTES;
-        if (smem > smem_limit) return fail(5, "knn: shared memory budget exceeded (k too large for the resident kernel)");
+        if (smem > smem_limit) return fail(5, "knn: shared memory budget exceeded for the resident kernel");
         P.dp64 = dp64; P.stages = stages;
+        P.norm_bytes = opB.ldn == 16 ? 128 * 32 : CHUNK_BYTES;
         const int tail = d - 64 * (dp64 - 1);
         const int k16_tail = (tail + 15) / 16;
 #define SPHB_LAUNCH_RESIDENT(MH_, R_)                                                                                                      \
     do {                                                                                                                                   \
         SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<MH_, R_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
-        knn_sweep_resident<MH_, R_><<<grid, 64 + 128 * MH_, smem, stream>>>(tmA, tmB, tmO, P, k16_tail);                                   \
+        knn_sweep_resident<MH_, R_><<<grid, 64 + 128 * MH_, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                              \
     } while (0)
         if (MH == 2 && cap == 256) SPHB_LAUNCH_RESIDENT(2, 8);
         else if (MH == 2 && cap == 512) SPHB_LAUNCH_RESIDENT(2, 16);
@@ -789,25 +918,29 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     }
     count_launch();
     SPHB_CUDA(cudaGetLastError());
-    cudaEventRecord(ev.e[2], stream);
+    tsweep.stop(stream);
 
+    trerank.start(stream);
     {
         const size_t smem = 8 * static_cast<size_t>(cap) * sizeof(uint64_t);
         SPHB_CUDA(cudaFuncSetAttribute(knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        const int64_t blocks = std::min<int64_t>((nq + 7) / 8, static_cast<int64_t>(sms) * 8);
-        knn_rerank_kernel<<<static_cast<unsigned>(blocks), 256, smem, stream>>>(d_x, d, k, cap, keep_max, metric, l2_squared, q0, nq, cand_out.p,
-                                                                                 cnt_out.p, d_ids, d_dist, ovf_rows.p, ovf_count.p);
+        const int64_t blocks = std::min<int64_t>((nq + 7) / 8, static_cast<int64_t>(J.sms) * 8);
+        knn_rerank_kernel<<<static_cast<unsigned>(blocks), 256, smem, stream>>>(J.x, d, k, cap, keep_max, J.metric, J.l2_squared, qa, nq, d_qrows,
+                                                                                 out_q0, cand_out.p, cnt_out.p, d_ids, d_dist, d_ovf_rows,
+                                                                                 d_ovf_count);
         count_launch();
         SPHB_CUDA(cudaGetLastError());
     }
+    trerank.stop(stream);
 
-    cudaEventRecord(ev.e[3], stream);
     unsigned long long hstats[2] = {0, 0};
-    int hovf = 0;
-    SPHB_CUDA(cudaMemcpyAsync(hstats, stats.p, sizeof(hstats), cudaMemcpyDeviceToHost, stream));
-    SPHB_CUDA(cudaMemcpyAsync(&hovf, ovf_count.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    SPHB_CUDA(cudaMemcpyAsync(hstats, J.stats.p, sizeof(hstats), cudaMemcpyDeviceToHost, stream));
+    SPHB_CUDA(cudaMemcpyAsync(n_ovf, d_ovf_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
     SPHB_CUDA(cudaStreamSynchronize(stream));
-    for (int i = 0; i < 3; ++i) cudaEventElapsedTime(&g_knn_ms[i], ev.e[i], ev.e[i + 1]);
+    J.sum_compactions += static_cast<int64_t>(hstats[0]);
+    J.sum_accepted += static_cast<int64_t>(hstats[1]);
+    *sweep_ms += tsweep.ms();
+    *rerank_ms += trerank.ms();
     if (want_prof) {
         std::vector<unsigned long long> hp(static_cast<size_t>(grid) * 16);
         cudaMemcpy(hp.data(), prof.p, hp.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
@@ -816,16 +949,152 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
             for (int i = 0; i < 16; ++i) acc[i] += static_cast<double>(hp[b * 16 + i]) / grid;
         const int ew = MH ? 4 * MH : 4;
         fprintf(stderr,
-                "[knn prof] mean cycles per CTA: producer wait_empty %.3g of %.3g | mma wait_tempty %.3g wait_full %.3g of %.3g | "
+                "[knn prof] passes %d mean cycles per CTA: producer wait_empty %.3g of %.3g | mma wait_tempty %.3g wait_full %.3g of %.3g | "
                 "epilogue(per warp) wait_tfull %.3g ld %.3g filter+compact %.3g (compact %.3g) export %.3g of %.3g | sweep %.2f ms\n",
-                acc[0], acc[1], acc[2], acc[3], acc[4], acc[5] / ew, acc[6] / ew, acc[7] / ew, acc[10] / ew, acc[8] / ew, acc[9] / ew, g_knn_ms[1]);
+                passes, acc[0], acc[1], acc[2], acc[3], acc[4], acc[5] / ew, acc[6] / ew, acc[7] / ew, acc[10] / ew, acc[8] / ew, acc[9] / ew,
+                tsweep.ms());
     }
-    if (hovf > 0) {
-        // rows whose candidate band overflowed (massive ties): exact SIMT recompute, never a truncated answer
-        if (int rc = knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, ovf_rows.p, ovf_count.p, hovf, d_ids, d_dist, stream)) return rc;
-        SPHB_CUDA(cudaStreamSynchronize(stream));
+    return 0;
+}
+
+}  // namespace
+
+// flavour: 0 auto, 1 streaming kernel 3 passes, 2 resident MH=1 3 passes, 3 resident 3 passes (MH auto),
+//          4 one pass (resident when d allows, else streaming), 5 one pass streaming
+int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1, int64_t* d_ids,
+                  float* d_dist, cudaStream_t stream, int flavour) {
+    using namespace tc;
+    const int64_t nq = q1 - q0;
+    if (nq <= 0) return 0;
+    KnnJob J{};
+    J.x = d_x; J.n = n; J.d = d; J.k = k; J.metric = metric; J.l2_squared = l2_squared; J.stream = stream;
+    J.centre = metric == METRIC_L2 ? 1 : 0;
+    J.sms = ctx().num_sms;
+    J.dp = (d + 63) / 64 * 64;
+    J.np = (n + 255) / 256 * 256;
+    {
+        const char* e = getenv("SPHB_KNN_NORM_WIDE");
+        J.narrow_norm = !(e && atoi(e) != 0);
     }
-    const int64_t st[6] = {1 + MH, static_cast<int64_t>(hstats[0]), static_cast<int64_t>(hstats[1]), MH ? 3 * dp + 16 : kp, hovf, n_qtiles};
+    const int dp = J.dp, sms = J.sms;
+
+    // ---- which kernel: passes and flavour
+    int passes_first = (flavour >= 1 && flavour <= 3) ? 3 : 1;
+    if (const char* e = getenv("SPHB_KNN_PASSES")) { if (flavour == 0) passes_first = atoi(e) == 3 ? 3 : 1; }
+    auto pick_mh = [&](int passes) {
+        if (flavour == 1 || flavour == 5) return 0;
+        if (passes == 3) return dp <= 128 ? (flavour == 2 ? 1 : 2) : (dp <= 256 ? 1 : 0);
+        return dp <= 256 ? 2 : (dp <= 512 ? 1 : 0);
+    };
+
+    EventTimer tprep;
+    tprep.start(stream);
+    SPHB_CUDA(J.colsum.alloc(d, stream));
+    SPHB_CUDA(J.un2.alloc(n, stream));
+    SPHB_CUDA(J.scal.alloc(2, stream));
+    SPHB_CUDA(J.maxbits.alloc(1, stream));
+    SPHB_CUDA(J.stats.alloc(2, stream));
+    SPHB_CUDA(J.dun.alloc(n, stream));
+    SPHB_CUDA(J.dvmax.alloc(1, stream));
+    SPHB_CUDA(J.ones.alloc(128 * 64, stream));
+    SPHB_CUDA(cudaMemsetAsync(J.colsum.p, 0, d * sizeof(double), stream));
+    SPHB_CUDA(cudaMemsetAsync(J.maxbits.p, 0, sizeof(unsigned long long), stream));
+    SPHB_CUDA(cudaMemsetAsync(J.dvmax.p, 0, sizeof(unsigned int), stream));
+    if (J.centre) {
+        dim3 g(static_cast<unsigned>(std::min<int64_t>(n, sms * 8)), static_cast<unsigned>((d + 127) / 128));
+        knn_prep_colsum<<<g, 128, 0, stream>>>(d_x, n, d, J.colsum.p);
+        count_launch();
+    }
+    knn_prep_norms<<<sms * 8, 256, 0, stream>>>(d_x, n, d, J.colsum.p, J.centre, J.un2.p, J.maxbits.p);
+    knn_prep_scale<<<1, 1, 0, stream>>>(J.maxbits.p, J.scal.p);
+    knn_prep_rescale<<<sms * 4, 256, 0, stream>>>(J.un2.p, n, J.scal.p);
+    knn_prep_ones<<<32, 256, 0, stream>>>(J.ones.p);
+    count_launch(4);
+    SPHB_CUDA(cudaGetLastError());
+
+    Operands op1, op3;  // full operand sets (A and B) for 1 pass / 3 passes, built on demand
+    auto ensure_full = [&](Operands& op, int passes) -> int {
+        if (op.built_b) return 0;
+        return build_operands(J, op, passes, pick_mh(passes), nullptr, 0, true, true);
+    };
+    if (int rc = ensure_full(passes_first == 1 ? op1 : op3, passes_first)) return rc;
+    tprep.stop(stream);
+
+    DevBuf<int> ovf_count;
+    DevBuf<int64_t> ovf_rows;
+    SPHB_CUDA(ovf_count.alloc(1, stream));
+    SPHB_CUDA(ovf_rows.alloc(nq, stream));
+
+    float sweep_ms = 0.f, rerank_ms = 0.f, fallback_ms = 0.f;
+    int64_t resweep_rows = 0, simt_rows = 0, rows_1pass = 0;
+    int n_qtiles_total = 0;
+
+    // Sweeps [qa, qb) with `passes`; overflow rows of a 1-pass sweep are re-swept with 3 passes, what still
+    // overflows (massive ties) goes to the exact SIMT kernel — never a truncated answer.
+    auto process = [&](int64_t qa, int64_t qb, int passes, double* ovf_frac) -> int {
+        Operands& op = passes == 1 ? op1 : op3;
+        if (int rc = ensure_full(op, passes)) return rc;
+        SPHB_CUDA(cudaMemsetAsync(ovf_count.p, 0, sizeof(int), stream));
+        int hovf = 0;
+        if (int rc = sweep_and_rerank(J, op, op, qa, qb, nullptr, q0, d_ids, d_dist, ovf_rows.p, ovf_count.p, &hovf, &sweep_ms, &rerank_ms)) return rc;
+        const int rpc = op.MH ? op.MH * BM : BM;
+        n_qtiles_total += static_cast<int>((qb - qa + rpc - 1) / rpc);
+        if (passes == 1) rows_1pass += qb - qa;
+        if (ovf_frac) *ovf_frac = static_cast<double>(hovf) / static_cast<double>(qb - qa);
+        if (hovf == 0) return 0;
+        EventTimer tf;
+        tf.start(stream);
+        int hovf2 = hovf;
+        DevBuf<int> ovf2_count;
+        DevBuf<int64_t> ovf2_rows;
+        const int64_t* simt_rows_p = ovf_rows.p;
+        const int* simt_count_p = ovf_count.p;
+        if (passes == 1) {
+            if (int rc = ensure_full(op3, 3)) return rc;
+            Operands sub;
+            if (int rc = build_operands(J, sub, 3, op3.MH, ovf_rows.p, hovf, true, false)) return rc;
+            SPHB_CUDA(ovf2_count.alloc(1, stream));
+            SPHB_CUDA(ovf2_rows.alloc(hovf, stream));
+            SPHB_CUDA(cudaMemsetAsync(ovf2_count.p, 0, sizeof(int), stream));
+            float sm = 0.f, rm = 0.f;
+            if (int rc = sweep_and_rerank(J, sub, op3, 0, hovf, ovf_rows.p, q0, d_ids, d_dist, ovf2_rows.p, ovf2_count.p, &hovf2, &sm, &rm)) return rc;
+            resweep_rows += hovf;
+            simt_rows_p = ovf2_rows.p;
+            simt_count_p = ovf2_count.p;
+        }
+        if (hovf2 > 0) {
+            if (int rc = knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, simt_rows_p, simt_count_p, hovf2, d_ids, d_dist, stream)) return rc;
+            SPHB_CUDA(cudaStreamSynchronize(stream));
+            simt_rows += hovf2;
+        }
+        tf.stop(stream);
+        fallback_ms += tf.ms();
+        return 0;
+    };
+
+    if (passes_first == 1 && flavour == 0) {
+        // pilot: one wave of query tiles with the 1-pass filter; if its band overflows for too many rows
+        // (distance-concentrated data) the rest of the slab uses the split-precision filter directly.
+        const int rpc = (pick_mh(1) ? pick_mh(1) * BM : BM);
+        const int64_t pilot = static_cast<int64_t>(sms) * rpc;
+        if (nq > 3 * pilot) {
+            double frac = 0.0;
+            if (int rc = process(q0, q0 + pilot, 1, &frac)) return rc;
+            if (int rc = process(q0 + pilot, q1, frac > 0.25 ? 3 : 1, nullptr)) return rc;
+        } else {
+            if (int rc = process(q0, q1, 1, nullptr)) return rc;
+        }
+    } else {
+        if (int rc = process(q0, q1, passes_first, nullptr)) return rc;
+    }
+
+    g_knn_ms[0] = tprep.ms();
+    g_knn_ms[1] = sweep_ms;
+    g_knn_ms[2] = rerank_ms;
+    g_knn_ms[3] = fallback_ms;
+    const Operands& opm = rows_1pass > 0 ? op1 : op3;
+    const int kexec = opm.MH ? ((opm.passes == 3 ? 3 : 1) * dp + 16) : opm.lda;
+    const int64_t st[8] = {1 + opm.MH, J.sum_compactions, J.sum_accepted, kexec, simt_rows, n_qtiles_total, rows_1pass > 0 ? 1 : 3, resweep_rows};
     knn_set_stats(st);
     return 0;
 }

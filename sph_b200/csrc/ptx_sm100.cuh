@@ -127,6 +127,17 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr) {
     return desc;
 }
 
+// Same for a narrow K-major tile: rows of 16 fp16 (32 B), SWIZZLE_32B, 8-row groups 256 B apart.
+__device__ __forceinline__ uint64_t make_smem_desc_sw32(uint32_t smem_addr) {
+    uint64_t desc = 0;
+    desc |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+    desc |= static_cast<uint64_t>(1) << 16;
+    desc |= static_cast<uint64_t>(256 >> 4) << 32;               // SBO
+    desc |= static_cast<uint64_t>(1) << 46;                      // version
+    desc |= static_cast<uint64_t>(6) << 61;                      // SWIZZLE_32B
+    return desc;
+}
+
 // Instruction descriptor, kind::f16: fp16 A/B (K-major), fp32 accumulate, MxN tile.
 __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {
     return (1u << 4)                                  // c_format = F32

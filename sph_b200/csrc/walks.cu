@@ -1,0 +1,267 @@
+// Stage C, RW1: Monte-Carlo random-walk transition sums (replaces utils::doRandomWalks,
+// sph/utils/SparseMatrixAlgorithms.cpp:34-290).
+//
+// One warp per start point.  Lane l runs walks l, l+32, ...; every step draws a counter-based
+// uniform (Philox4x32-10 keyed by the seed, counter = (start, walk, step)), scans the current row in
+// ascending column order accumulating fp64 probability until u < cum (stays put otherwise, :129-135)
+// and records the event (column, walk*L + step) in the warp's shared-memory event list.  The list is
+// then sorted by (column, event order) and reduced run by run IN EVENT ORDER with the step weights
+// recomputed from the step index — the same fp32 addition order as the reference's
+// `hits[next] += stepWeight` for the same paths, so sums are deterministic and layout independent.
+// Row post-processing follows the reference: FIRST_VISIT transform (:176-218), prune (:221-233),
+// removeDiagonalElements(keepSingleEntry) (:704-718), L1 normalisation (:253-267).
+// The HBM traffic is the random row gathers (8 B x half a row per step); rows are written once.
+#include "../../include/sphb.h"
+#include "graph_common.cuh"
+
+namespace sphb {
+
+struct WalkParams {
+    int64_t n;
+    const int64_t* rowptr;
+    const uint32_t* col;
+    const float* val;
+    uint32_t W, L;
+    int weighting;
+    float prune_value;
+    uint64_t seed;
+    int remove_diagonal, normalize;
+    int cap_ev;         // events per start, power of two >= W*L
+    int64_t start0, nstarts;
+    int tmp_stride;     // entries per start in the temp buffers
+    uint32_t* tmp_col;
+    float* tmp_val;
+    int* row_nnz;       // [nstarts]
+};
+
+__device__ __forceinline__ float step_weight(int weighting, uint32_t step, uint32_t L) {
+    switch (weighting) {
+        case SPHB_W_LINEAR: return static_cast<float>(1.0 - (static_cast<double>(step) / L));
+        case SPHB_W_NORMAL: {
+            const float index = step * 3.f / L;
+            return expf(-0.5f * (index * index));
+        }
+        case SPHB_W_ONLYLAST: return (step < L - 1) ? 0.f : 1.f;
+        case SPHB_W_FIRST_VISIT: return static_cast<float>(step + 1);
+        default: return 1.f;
+    }
+}
+
+constexpr int FV_MAX_LEN = 64;  // FIRST_VISIT keeps the visited set of a walk in registers/local memory
+
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) random_walk_kernel(const WalkParams P) {
+    extern __shared__ uint64_t smem_ev[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* ev = smem_ev + static_cast<size_t>(warp) * P.cap_ev;
+    const uint32_t W = P.W, L = P.L;
+    const uint32_t total = W * L;
+    const uint2 key = make_uint2(static_cast<uint32_t>(P.seed), static_cast<uint32_t>(P.seed >> 32));
+    for (int64_t s = static_cast<int64_t>(blockIdx.x) * WARPS + warp; s < P.nstarts; s += static_cast<int64_t>(gridDim.x) * WARPS) {
+        const int64_t start = P.start0 + s;
+        // ---- 1. the walks
+        for (uint32_t w = lane; w < W; w += 32) {
+            int64_t cur = start;
+            uint32_t visited[FV_MAX_LEN + 1];
+            int nvis = 0;
+            if (P.weighting == SPHB_W_FIRST_VISIT) visited[nvis++] = static_cast<uint32_t>(cur);
+            for (uint32_t step = 0; step < L; ++step) {
+                const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(start), static_cast<uint32_t>(start >> 32), w, step), key);
+                const double u = u01_from_bits(r.x, r.y);
+                int64_t next = cur;
+                double inc = 0.0;
+                const int64_t e1 = P.rowptr[cur + 1];
+                for (int64_t e = P.rowptr[cur]; e < e1; ++e) {
+                    inc += static_cast<double>(__ldg(P.val + e));
+                    if (u < inc) {
+                        next = __ldg(P.col + e);
+                        break;
+                    }
+                }
+                bool record = true;
+                if (P.weighting == SPHB_W_ONLYLAST) record = step == L - 1;
+                if (P.weighting == SPHB_W_FIRST_VISIT) {
+                    bool seen = false;
+                    for (int t = 0; t < nvis; ++t) seen |= visited[t] == static_cast<uint32_t>(next);
+                    record = !seen;
+                    if (!seen && nvis <= FV_MAX_LEN) visited[nvis++] = static_cast<uint32_t>(next);
+                }
+                const uint32_t order = w * L + step;
+                ev[order] = record ? ((static_cast<uint64_t>(next) << 32) | order) : ~0ull;
+                cur = next;
+            }
+        }
+        for (int t = total + lane; t < P.cap_ev; t += 32) ev[t] = ~0ull;
+        __syncwarp();
+        // ---- 2. sort by (column, event order)
+        warp_bitonic_sort(ev, P.cap_ev, lane);
+        // ---- 3. reduce every run of equal columns in event order; compact (col, value) in place
+        int m = 0;  // entries written so far
+        uint32_t prev_col = 0xffffffffu;
+        bool have_prev = false;
+        for (int base = 0; base < static_cast<int>(total); base += 32) {
+            const int t = base + lane;
+            uint64_t k = t < static_cast<int>(total) ? ev[t] : ~0ull;
+            const bool valid = k != ~0ull;
+            const uint32_t c = static_cast<uint32_t>(k >> 32);
+            uint32_t pc = __shfl_up_sync(0xffffffffu, c, 1);
+            bool pv = __shfl_up_sync(0xffffffffu, valid ? 1 : 0, 1) != 0;
+            if (lane == 0) { pc = prev_col; pv = have_prev; }
+            const bool head = valid && !(pv && pc == c);
+            float sum = 0.f;
+            int cnt = 0;
+            if (head) {
+                for (int u = t; u < static_cast<int>(total); ++u) {
+                    const uint64_t ku = ev[u];
+                    if (ku == ~0ull || static_cast<uint32_t>(ku >> 32) != c) break;
+                    sum += step_weight(P.weighting, static_cast<uint32_t>(ku) % L, L);
+                    ++cnt;
+                }
+                if (P.weighting == SPHB_W_FIRST_VISIT) {
+                    // hits /= hitCount, then the linear map onto [0, 1] (SparseMatrixAlgorithms.cpp:176-218)
+                    sum /= static_cast<float>(cnt);
+                    const float mm = -1.f / (L - 1.f), cc = L / (L - 1.f);
+                    sum = fmaxf(0.f, mm * sum + cc);
+                }
+            }
+            bool keep = head;
+            if (keep && P.prune_value > 0.f && (sum <= P.prune_value || sum == 0.f)) keep = false;
+            prev_col = __shfl_sync(0xffffffffu, c, 31);
+            have_prev = __shfl_sync(0xffffffffu, valid ? 1 : 0, 31) != 0;
+            const unsigned mask = __ballot_sync(0xffffffffu, keep);
+            __syncwarp();  // all reads of this chunk (and the forward run scans) are done before the in-place writes
+            if (keep) ev[m + __popc(mask & ((1u << lane) - 1u))] = (static_cast<uint64_t>(c) << 32) | __float_as_uint(sum);
+            m += __popc(mask);
+            __syncwarp();
+            if (!__any_sync(0xffffffffu, valid)) break;  // sorted: only sentinels follow
+        }
+        // ---- 4. removeDiagonalElements(keepSingleEntry = true): with more than one entry, drop the diagonal and every exact zero
+        if (P.remove_diagonal && m > 1) {
+            int m2 = 0;
+            for (int base = 0; base < m; base += 32) {
+                const int t = base + lane;
+                const uint64_t k = t < m ? ev[t] : 0ull;
+                const bool keep = t < m && static_cast<int64_t>(k >> 32) != start && __uint_as_float(static_cast<uint32_t>(k)) != 0.f;
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                __syncwarp();
+                if (keep) ev[m2 + __popc(mask & ((1u << lane) - 1u))] = k;
+                m2 += __popc(mask);
+                __syncwarp();
+            }
+            m = m2;
+        }
+        // ---- 5. L1 normalisation: fp32 sum in column order (Eigen sum()), then the single write of the row
+        float nv = 1.f;
+        if (P.normalize) {
+            float acc = 0.f;
+            if (lane == 0)
+                for (int t = 0; t < m; ++t) acc += __uint_as_float(static_cast<uint32_t>(ev[t]));
+            nv = __shfl_sync(0xffffffffu, acc, 0);
+        }
+        uint32_t* oc = P.tmp_col + s * P.tmp_stride;
+        float* ov = P.tmp_val + s * P.tmp_stride;
+        for (int t = lane; t < m; t += 32) {
+            const uint64_t k = ev[t];
+            oc[t] = static_cast<uint32_t>(k >> 32);
+            const float v = __uint_as_float(static_cast<uint32_t>(k));
+            ov[t] = P.normalize ? v / nv : v;
+        }
+        if (lane == 0) P.row_nnz[s] = m;
+        __syncwarp();
+    }
+}
+
+// fixed-stride temp rows -> CSR at the scanned offsets
+__global__ void walks_compact(int64_t nstarts, int tmp_stride, const uint32_t* __restrict__ tmp_col, const float* __restrict__ tmp_val,
+                              const int64_t* __restrict__ offs, int64_t base, int64_t cap, int64_t* __restrict__ rowptr_out,
+                              uint32_t* __restrict__ out_col, float* __restrict__ out_val) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t s = warp; s < nstarts; s += nwarps) {
+        const int64_t b = base + offs[s], e = base + offs[s + 1];
+        if (lane == 0) rowptr_out[s + 1] = e;
+        if (e > cap) continue;
+        for (int64_t t = lane; t < e - b; t += 32) {
+            out_col[b + t] = tmp_col[s * tmp_stride + t];
+            out_val[b + t] = tmp_val[s * tmp_stride + t];
+        }
+    }
+}
+__global__ void widen_counts(const int* __restrict__ in, int64_t num, int64_t* __restrict__ out) {
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t <= num; t += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        out[t] = t < num ? in[t] : 0;
+}
+
+int random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, uint64_t num_walks, uint64_t walk_len,
+                     int weighting, float prune_value, uint64_t prune_steps, uint64_t seed, int remove_diagonal, int normalize,
+                     int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s) {
+    *out_nnz = 0;
+    SPHB_CUDA(cudaMemsetAsync(d_out_rowptr, 0, (n + 1) * sizeof(int64_t), s));
+    if (n == 0 || num_walks == 0) return 0;
+    const uint64_t total = num_walks * walk_len;
+    if (total > 8192) return fail(SPHB_ERR_UNSUPPORTED, "random_walks: numRandomWalks * singleWalkLength > 8192 unsupported");
+    if (weighting == SPHB_W_FIRST_VISIT && walk_len > FV_MAX_LEN) return fail(SPHB_ERR_UNSUPPORTED, "random_walks: FIRST_VISIT with walk length > 64 unsupported");
+    // pruneValue from pruneSteps (SparseMatrixAlgorithms.cpp:48-66)
+    float pv = prune_value;
+    if (prune_steps > 0) {
+        const uint64_t ps = std::min<uint64_t>(walk_len - 1, prune_steps);
+        const uint64_t inv = walk_len - ps;
+        if (weighting == SPHB_W_LINEAR) pv = static_cast<float>(1.0 - (static_cast<double>(inv) / walk_len));
+        else if (weighting == SPHB_W_NORMAL) { const float idx = inv * 3.f / walk_len; pv = std::exp(-0.5f * std::pow(idx, 2.f)); }
+        else if (weighting == SPHB_W_CONSTANT) pv = static_cast<float>(inv);
+        else if (weighting == SPHB_W_FIRST_VISIT) pv = static_cast<float>(ps) / walk_len;
+        if (pv > 0.5f) pv = 0.5f;
+    }
+    int cap_ev = 32;
+    while (cap_ev < static_cast<int>(total)) cap_ev <<= 1;
+    const int sms = ctx().num_sms;
+    constexpr int WARPS = 4;
+    int warps = WARPS;
+    size_t smem = static_cast<size_t>(WARPS) * cap_ev * sizeof(uint64_t);
+    if (smem > 200 * 1024) { warps = 1; smem = static_cast<size_t>(cap_ev) * sizeof(uint64_t); }
+    const int tmp_stride = static_cast<int>(std::min<uint64_t>(total, static_cast<uint64_t>(n)));
+    // chunk of start points per launch: bounded temp storage (<= 4 GiB), rows compacted chunk by chunk
+    int64_t chunk = std::max<int64_t>(1024, (4ll << 30) / (static_cast<int64_t>(tmp_stride) * 8));
+    chunk = std::min<int64_t>(chunk, n);
+    DevBuf<uint32_t> tcol;
+    DevBuf<float> tval;
+    DevBuf<int> cnt;
+    DevBuf<int64_t> cnt64, offs;
+    SPHB_CUDA(tcol.alloc(static_cast<size_t>(chunk) * tmp_stride, s));
+    SPHB_CUDA(tval.alloc(static_cast<size_t>(chunk) * tmp_stride, s));
+    SPHB_CUDA(cnt.alloc(chunk, s));
+    SPHB_CUDA(cnt64.alloc(chunk + 1, s));
+    SPHB_CUDA(offs.alloc(chunk + 1, s));
+    if (warps == WARPS) SPHB_CUDA(cudaFuncSetAttribute(random_walk_kernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    else SPHB_CUDA(cudaFuncSetAttribute(random_walk_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int64_t base = 0;
+    for (int64_t s0 = 0; s0 < n; s0 += chunk) {
+        const int64_t ns = std::min(chunk, n - s0);
+        WalkParams P{};
+        P.n = n; P.rowptr = d_rowptr; P.col = d_col; P.val = d_val;
+        P.W = static_cast<uint32_t>(num_walks); P.L = static_cast<uint32_t>(walk_len);
+        P.weighting = weighting; P.prune_value = pv; P.seed = seed; P.remove_diagonal = remove_diagonal; P.normalize = normalize;
+        P.cap_ev = cap_ev; P.start0 = s0; P.nstarts = ns; P.tmp_stride = tmp_stride;
+        P.tmp_col = tcol.p; P.tmp_val = tval.p; P.row_nnz = cnt.p;
+        const int64_t blocks = std::min<int64_t>((ns + warps - 1) / warps, static_cast<int64_t>(sms) * 16);
+        if (warps == WARPS) random_walk_kernel<WARPS><<<static_cast<unsigned>(blocks), WARPS * 32, smem, s>>>(P);
+        else random_walk_kernel<1><<<static_cast<unsigned>(blocks), 32, smem, s>>>(P);
+        widen_counts<<<static_cast<unsigned>(std::min<int64_t>((ns + 256) / 256, sms * 8)), 256, 0, s>>>(cnt.p, ns, cnt64.p);
+        count_launch(2);
+        if (int rc = exclusive_sum<int64_t>(cnt64.p, offs.p, ns + 1, s)) return rc;
+        int64_t chunk_nnz = 0;
+        SPHB_CUDA(cudaMemcpyAsync(&chunk_nnz, offs.p + ns, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+        walks_compact<<<static_cast<unsigned>(std::min<int64_t>((ns * 32 + 255) / 256, sms * 8)), 256, 0, s>>>(ns, tmp_stride, tcol.p, tval.p, offs.p, base, cap,
+                                                                                                              d_out_rowptr + s0, d_out_col, d_out_val);
+        count_launch();
+        SPHB_CUDA(cudaGetLastError());
+        SPHB_CUDA(cudaStreamSynchronize(s));
+        base += chunk_nnz;
+        if (base > cap) return fail(SPHB_ERR_CAPACITY, "random_walks: output capacity too small");
+    }
+    *out_nnz = base;
+    return 0;
+}
+
+}  // namespace sphb

@@ -52,17 +52,62 @@ def test_simt_duplicates_and_ties(capi, oracle):
     _check(capi, oracle, x, 16, path=1, l2_squared=True)
 
 
-# path 2: auto flavour (resident MH=2 for d<=128, MH=1 for d<=256, streaming above), 3: streaming, 4: resident MH=1
-@pytest.mark.parametrize("n,d,k,path,flavour", [
-    (2048, 32, 16, 2, 3), (4100, 128, 91, 2, 3), (3000, 200, 91, 2, 2), (2500, 21, 5, 2, 3), (2300, 300, 40, 2, 1),
-    (4100, 128, 91, 3, 1), (2500, 21, 5, 3, 1), (3000, 100, 30, 4, 2), (2048, 64, 301, 2, 3),
+# paths (capi.force_knn_path): 2 auto (1-pass fp16 filter, 3-pass re-sweep of overflow rows), 3 streaming 3-pass,
+# 4 resident MH=1 3-pass, 5 3-pass auto flavour, 6 1-pass, 7 1-pass streaming.
+# flavour (stats["tensor_core"]): 1 streaming, 2 resident MH=1, 3 resident MH=2.
+@pytest.mark.parametrize("n,d,k,path,flavour,passes", [
+    (2048, 32, 16, 2, 3, 1), (4100, 128, 91, 2, 3, 1), (3000, 200, 91, 2, 3, 1), (2500, 21, 5, 2, 3, 1), (2300, 300, 40, 2, 2, 1),
+    (2100, 600, 20, 2, 1, 1), (4100, 128, 91, 6, 3, 1), (2500, 21, 5, 7, 1, 1), (2048, 64, 301, 6, 3, 1),
+    (4100, 128, 91, 5, 3, 3), (3000, 200, 91, 5, 2, 3), (2300, 300, 40, 5, 1, 3),
+    (4100, 128, 91, 3, 1, 3), (2500, 21, 5, 3, 1, 3), (3000, 100, 30, 4, 2, 3), (2048, 64, 301, 5, 3, 3),
 ])
-def test_tc_matches_oracle(capi, oracle, n, d, k, path, flavour):
+def test_tc_matches_oracle(capi, oracle, n, d, k, path, flavour, passes):
     rng = np.random.default_rng(n * 7 + d)
     x = (rng.standard_normal((n, d)) * 0.3 + rng.uniform(0, 1, (1, d))).astype(np.float32)
     _check(capi, oracle, x, k, path=path)
     st = capi.knn_last_stats()
     assert st["tensor_core"] == flavour
+    assert st["passes"] == passes
+
+
+@pytest.mark.parametrize("wide", ["0", "1"])
+def test_tc_norm_chunk_layouts(capi, oracle, wide, monkeypatch):
+    # the |v|² chunk is a narrow (16-column, SWIZZLE_32B) or wide (64-column, SWIZZLE_128B) tile
+    monkeypatch.setenv("SPHB_KNN_NORM_WIDE", wide)
+    x = synth.hyperspectral(64, 64, 96, endmembers=8, seed=21)
+    _check(capi, oracle, x, 31, path=6)
+    _check(capi, oracle, x, 31, path=5)
+
+
+def test_tc_one_pass_overflow_resweep(capi, oracle):
+    # a tight cluster far from the data mean: |u| is large against the intra-cluster distances, the 1-pass
+    # band holds the whole cluster -> those rows are re-swept with the 3-pass filter (and what still overflows
+    # goes to the exact SIMT kernel); results stay exact
+    rng = np.random.default_rng(17)
+    a = (10.0 + 0.01 * rng.standard_normal((5000, 32))).astype(np.float32)
+    b = (-50.0 + rng.standard_normal((1000, 32))).astype(np.float32)
+    x = np.concatenate([a, b])
+    rows = np.arange(0, 6000, 47)
+    _check(capi, oracle, x, 91, path=6, rows=rows)
+    st = capi.knn_last_stats()
+    assert st["passes"] == 1 and st["resweep_rows"] > 0
+    _check(capi, oracle, x, 91, path=2, rows=rows)
+
+
+def test_tc_inner_product(capi, oracle):
+    rng = np.random.default_rng(23)
+    x = rng.standard_normal((3000, 48)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)  # COSINE = renormalise + inner product (NearestNeighbors.cpp:208-222)
+    for path in (1, 6, 5):
+        _check(capi, oracle, x, 20, path=path, metric=0)
+
+
+def test_tc_auto_pilot_large(capi, oracle):
+    # more than three waves of query tiles: the auto path runs a one-wave 1-pass pilot first
+    x = synth.hyperspectral(360, 360, 16, endmembers=6, seed=31)
+    rows = np.random.default_rng(1).choice(x.shape[0], 96, replace=False)
+    rows.sort()
+    _check(capi, oracle, x, 12, path=0, rows=rows)
 
 
 def test_tc_hyperspectral_c1_shape(capi, oracle):
@@ -80,10 +125,15 @@ def test_tc_duplicates(capi, oracle):
     _check(capi, oracle, x, 8, path=2)
     _check(capi, oracle, x, 130, path=2)
     _check(capi, oracle, x, 8, path=3)
-    # heavy ties: 64 copies of each of 40 points -> the candidate band overflows and rows fall back to the exact kernel
-    y = np.repeat(rng.standard_normal((40, 16)).astype(np.float32), 64, axis=0)
+    _check(capi, oracle, x, 130, path=5)
+    # heavy ties: 600 copies of each of 10 points -> the candidate band overflows in both filters and the rows
+    # fall back to the exact SIMT kernel
+    y = np.repeat(rng.standard_normal((10, 16)).astype(np.float32), 600, axis=0)
     _check(capi, oracle, y, 100, path=2)
-    assert capi.knn_last_stats()["overflow_rows"] >= 0
+    st = capi.knn_last_stats()
+    assert st["resweep_rows"] > 0 and st["overflow_rows"] > 0
+    _check(capi, oracle, y, 100, path=5)
+    assert capi.knn_last_stats()["overflow_rows"] > 0
 
 
 def test_tc_equals_simt_on_device(capi):

@@ -25,4 +25,4 @@ for it in range(int(os.environ.get("PROBE_ITERS", "3"))):
     ms = e0.elapsed_time(e1)
     st = capi.knn_last_stats()
     fl = 2.0 * nq * n * d
-    print(f"iter {it}: {ms:.1f} ms  alg {fl/ms/1e9:.1f} TF/s  exec {2.0*nq*n*st['kp']/ms/1e9:.1f} TF/s  stats {st}  accepted/row {st['accepted']/nq:.0f} compactions/row {st['compactions']/nq:.2f}", flush=True)
+    print(f"iter {it}: {ms:.1f} ms  alg {fl/ms/1e9:.1f} TF/s  exec {2.0*nq*n*st['kp']/ms/1e9:.1f} TF/s  stats {st}  accepted/row {st['accepted']/nq:.0f} compactions/row {st['compactions']/nq:.2f} timing {capi.knn_last_timing()}", flush=True)
