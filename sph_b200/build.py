@@ -40,11 +40,12 @@ def _digest() -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False, profile: bool = False) -> Path:
+def build(force: bool = False, verbose: bool = False, profile: bool = False, tag: str = "", defines: tuple = ()) -> Path:
     """profile=True builds lib/libsphb200_prof.so with the sweep's cycle counters compiled in
     (-DSPHB_KNN_PROFILE; select it with SPHB_LIB=<path>, enable with SPHB_KNN_PROF=1)."""
     LIBDIR.mkdir(exist_ok=True)
-    tag = "_prof" if profile else ""
+    tag = tag or ("_prof" if profile else "")
+    defines = list(defines) + (["-DSPHB_KNN_PROFILE"] if profile else [])
     lib = LIBDIR / f"libsphb200{tag}.so"
     stamp = LIBDIR / f"build{tag}.stamp"
     dig = _digest()
@@ -54,7 +55,7 @@ def build(force: bool = False, verbose: bool = False, profile: bool = False) -> 
     procs = []
     for src in sources():
         obj = LIBDIR / (src.stem + tag + ".o")
-        cmd = [NVCC, *FLAGS, *(["-DSPHB_KNN_PROFILE"] if profile else []), "-c", str(src), "-o", str(obj)]
+        cmd = [NVCC, *FLAGS, *defines, "-c", str(src), "-o", str(obj)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

@@ -194,12 +194,52 @@ __device__ __forceinline__ void filter_chunk(const float (&v)[32], uint32_t jbas
     }
 }
 
+// Two 32-column chunks at once: the two min trees are independent (twice the ILP of two filter_chunk
+// calls) and there is one branch per 64 columns.  Appends at most 64 keys.
+__device__ __forceinline__ void filter_pair(const float (&v0)[32], const float (&v1)[32], uint32_t jbase, uint32_t n, RowList& me,
+                                            uint64_t* __restrict__ mybuf, unsigned long long& n_accept) {
+    float g0[8], g1[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        g0[q] = fminf(fminf(v0[4 * q], v0[4 * q + 1]), fminf(v0[4 * q + 2], v0[4 * q + 3]));
+        g1[q] = fminf(fminf(v1[4 * q], v1[4 * q + 1]), fminf(v1[4 * q + 2], v1[4 * q + 3]));
+    }
+    const float m0 = fminf(fminf(fminf(g0[0], g0[1]), fminf(g0[2], g0[3])), fminf(fminf(g0[4], g0[5]), fminf(g0[6], g0[7])));
+    const float m1 = fminf(fminf(fminf(g1[0], g1[1]), fminf(g1[2], g1[3])), fminf(fminf(g1[4], g1[5]), fminf(g1[6], g1[7])));
+    if (fminf(m0, m1) <= me.thr) {
+        const float thr = me.thr;
+        int cnt = me.cnt;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            if (g0[q] <= thr) {
+#pragma unroll
+                for (int t = 4 * q; t < 4 * q + 4; ++t) {
+                    const uint32_t j = jbase + t;
+                    if (v0[t] <= thr && j < n) mybuf[cnt++] = make_key(v0[t], j);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            if (g1[q] <= thr) {
+#pragma unroll
+                for (int t = 4 * q; t < 4 * q + 4; ++t) {
+                    const uint32_t j = jbase + 32 + t;
+                    if (v1[t] <= thr && j < n) mybuf[cnt++] = make_key(v1[t], j);
+                }
+            }
+        }
+        n_accept += static_cast<unsigned long long>(cnt - me.cnt);
+        me.cnt = cnt;
+    }
+}
+
 // After filter_chunk: compact every row of this warp whose list is close to full.
 template <int R>
 __device__ __forceinline__ void compact_full_rows(RowList& me, uint64_t* __restrict__ warp_buf, int k, int keep_max, int lane,
                                                   const BandConsts& bc, unsigned long long& n_compact, long long& t_compact) {
     constexpr int cap = 32 * R;
-    unsigned full = __ballot_sync(0xffffffffu, me.cnt > cap - 32);
+    unsigned full = __ballot_sync(0xffffffffu, me.cnt > cap - 64);  // room for one more filter_pair (<= 64 appends)
     if (full == 0) return;
     const long long c0 = SPHB_CLOCK();
     __syncwarp();  // the owner lanes' list appends must be visible to the whole warp

@@ -52,6 +52,7 @@ struct SweepParams {
     int n_qtiles, n_dbtiles;
     int dp64;              // resident flavour: padded d / 64
     int passes;            // 1: single fp16 product, 3: split fp16 (hi·hi + lo·hi + hi·lo)
+    int half_major;        // resident lean issue loop: all chunks for M half 0, then for half 1 (needs stages >= 2 chunks-per-tile)
     int norm_bytes;        // resident flavour: bytes of the norm chunk of one database tile (16 KB wide / 4 KB narrow)
     int stagger;           // database-tile start offset per CTA (desynchronises the CTAs' L2 reads)
     int lead;              // the sweep of a wave of query tiles starts `lead` database tiles before the wave's own rows
@@ -63,8 +64,20 @@ struct SweepParams {
     int* cnt_out;          // [nq]
     unsigned long long* stats;  // [0] compactions, [1] accepted candidates
     int debug_skip_epilogue;    // debug: epilogue releases the accumulator without reading it (pure MMA rate)
+    unsigned long long* trace;  // optional (profile build): CTA 0, first query tile, database tiles [trace_t0, trace_t0+64): 32 clock stamps per tile
+    int trace_t0;
     unsigned long long* prof;   // optional [grid][16] cycle counters (build -DSPHB_KNN_PROFILE, run SPHB_KNN_PROF=1)
 };
+
+#ifdef SPHB_KNN_PROFILE
+#define SPHB_TRACE(P, qt, t, slot)                                                                                   \
+    do {                                                                                                             \
+        if ((P).trace && blockIdx.x == 0 && (qt) == 0 && (t) >= (P).trace_t0 && (t) < (P).trace_t0 + 64 && (threadIdx.x & 31) == 0) \
+            (P).trace[((t) - (P).trace_t0) * 32 + (slot)] = clock64();                                                   \
+    } while (0)
+#else
+#define SPHB_TRACE(P, qt, t, slot) do { } while (0)
+#endif
 
 __device__ __forceinline__ BandConsts make_band_consts(const SweepParams& P) {
     BandConsts bc;
@@ -236,7 +249,10 @@ __global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [
 // B chunk sequence per 128-row database tile: dp64 hi chunks, (3 passes: dp64 lo chunks,) 1 norm chunk.
 // The norm chunk is a separate [np, 64] (wide, SWIZZLE_128B) or [np, 16] (narrow, SWIZZLE_32B) matrix;
 // only its first 16 columns (one k-step against the ONES tile) are used.
-template <int MH, int R>
+// DP64T > 0: 1-pass specialisation with the chunk count known at compile time (the MMA issue loop is
+// straight-line code with pre-built descriptors; every hi chunk runs all 4 k-steps, the zero padding of
+// the operands makes that exact); DP64T = 0: generic (runtime chunk count, 1 or 3 passes, partial last chunk).
+template <int MH, int R, int DP64T>
 __global__ void __launch_bounds__(64 + 128 * MH, 1)
 knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                    const __grid_constant__ CUtensorMap tmapN, const __grid_constant__ CUtensorMap tmapO, const SweepParams P,
@@ -245,7 +261,6 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     constexpr int BN = 128;
     constexpr int ACC_COLS = MH * BN;          // columns per accumulator stage
     constexpr int TMEM_COLS = 2 * ACC_COLS;    // double buffered
-    constexpr int EPI_WARPS = 4 * MH;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int stages = P.stages, dp64 = P.dp64;
@@ -259,13 +274,16 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(MH * nA + 1 + stages) * CHUNK_BYTES);
     const uint32_t bar_full = ptx::smem_u32(bars);
     const uint32_t bar_empty = ptx::smem_u32(bars + stages);
+    // accumulator barriers are per (stage, M half): index as * MH + m; the 4 epilogue warps of a half release it
     const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * stages);
-    const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * stages + 2);
-    const uint32_t bar_afull = ptx::smem_u32(bars + 2 * stages + 4);
-    const uint32_t bar_aempty = ptx::smem_u32(bars + 2 * stages + 5);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 6);
+    const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * stages + 4);
+    const uint32_t bar_afull = ptx::smem_u32(bars + 2 * stages + 8);
+    const uint32_t bar_aempty = ptx::smem_u32(bars + 2 * stages + 9);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 10);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // warps: 0 TMA producer, 1 MMA issuer, 2.. epilogue.  (A second issuer warp, one per M half, was measured: no gain —
+    // the MMA side is bound by the shared-memory operand bandwidth of M=128 x N=128 tiles, not by issue.)
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmapA);
@@ -276,9 +294,9 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             ptx::mbar_init(bar_full + 8 * s, 1);
             ptx::mbar_init(bar_empty + 8 * s, 1);
         }
-        for (int s = 0; s < 2; ++s) {
+        for (int s = 0; s < 2 * MH; ++s) {
             ptx::mbar_init(bar_tfull + 8 * s, 1);
-            ptx::mbar_init(bar_tempty + 8 * s, EPI_WARPS);
+            ptx::mbar_init(bar_tempty + 8 * s, 4);
         }
         ptx::mbar_init(bar_afull, 1);
         ptx::mbar_init(bar_aempty, 1);
@@ -339,6 +357,112 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (warp-uniform control flow, one elected lane issues) =====================
+        if constexpr (DP64T > 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_f16(BM, BN);
+            constexpr uint32_t STAGE_DESC = CHUNK_BYTES >> 4;  // descriptor address units (16 B) per ring slot
+            uint64_t adesc[MH][DP64T];
+#pragma unroll
+            for (int m = 0; m < MH; ++m)
+#pragma unroll
+                for (int c = 0; c < DP64T; ++c) adesc[m][c] = ptx::make_smem_desc_sw128(sA + (m * DP64T + c) * CHUNK_BYTES);
+            const uint64_t odesc = ptx::make_smem_desc_sw128(sO);
+            const uint64_t bdesc0 = ptx::make_smem_desc_sw128(sB);
+            const uint64_t ndesc0 = P.norm_bytes != CHUNK_BYTES ? ptx::make_smem_desc_sw32(sB) : bdesc0;
+            int stage = 0, as = 0;
+            uint32_t phase = 0, aphase = 0, accphase = 0;
+            long long mw_te = 0, mw_f = 0, mt0 = SPHB_CLOCK();
+            for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+                ptx::mbar_wait(bar_afull, aphase);
+                aphase ^= 1;
+                ptx::tc_fence_after();
+                for (int t = 0; t < P.n_dbtiles; ++t) {
+                    const uint32_t tmem_d = tmem_base + as * ACC_COLS;
+                    const bool last_tile = t == P.n_dbtiles - 1;
+                    if (P.half_major) {
+                        // all chunks for M half 0, then for half 1: the epilogue warps of half 0 start while half 1 is
+                        // still being multiplied, and a slow warp of one half only delays that half's next tile
+#pragma unroll
+                        for (int m = 0; m < MH; ++m) {
+                            long long w0 = SPHB_CLOCK();
+                            ptx::mbar_wait(bar_tempty + 8 * (as * MH + m), accphase ^ 1);
+                            mw_te += SPHB_CLOCK() - w0;
+                            SPHB_TRACE(P, qt, t, m * 2);
+                            ptx::tc_fence_after();
+#pragma unroll
+                            for (int c = 0; c <= DP64T; ++c) {
+                                int st = stage + c;
+                                uint32_t ph = phase;
+                                if (st >= stages) { st -= stages; ph ^= 1; }
+                                if (m == 0) {
+                                    w0 = SPHB_CLOCK();
+                                    ptx::mbar_wait(bar_full + 8 * st, ph);
+                                    mw_f += SPHB_CLOCK() - w0;
+                                    ptx::tc_fence_after();
+                                }
+                                if (ptx::elect_one_sync()) {
+                                    if (c < DP64T) {
+                                        const uint64_t bdesc = bdesc0 + static_cast<uint64_t>(st * STAGE_DESC);
+#pragma unroll
+                                        for (int kk = 0; kk < 4; ++kk)
+                                            ptx::umma_f16(tmem_d + m * BN, adesc[m][c < DP64T ? c : 0] + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0 ? 1u : 0u);
+                                    } else {
+                                        ptx::umma_f16(tmem_d + m * BN, odesc, ndesc0 + static_cast<uint64_t>(st * STAGE_DESC), idesc, 1u);
+                                    }
+                                    if (m == MH - 1) ptx::umma_commit(bar_empty + 8 * st);
+                                    if (c == DP64T) {
+                                        ptx::umma_commit(bar_tfull + 8 * (as * MH + m));
+                                        if (m == MH - 1 && last_tile) ptx::umma_commit(bar_aempty);  // query tile consumed
+                                    }
+                                }
+                                __syncwarp();
+                            }
+                            SPHB_TRACE(P, qt, t, m * 2 + 1);
+                        }
+                        stage += DP64T + 1;
+                        if (stage >= stages) { stage -= stages; phase ^= 1; }
+                    } else {
+#pragma unroll
+                        for (int m = 0; m < MH; ++m) ptx::mbar_wait(bar_tempty + 8 * (as * MH + m), accphase ^ 1);
+                        ptx::tc_fence_after();
+#pragma unroll
+                        for (int c = 0; c < DP64T; ++c) {
+                            ptx::mbar_wait(bar_full + 8 * stage, phase);
+                            ptx::tc_fence_after();
+                            if (ptx::elect_one_sync()) {
+                                const uint64_t bdesc = bdesc0 + static_cast<uint64_t>(stage * STAGE_DESC);
+#pragma unroll
+                                for (int m = 0; m < MH; ++m)
+#pragma unroll
+                                    for (int kk = 0; kk < 4; ++kk)
+                                        ptx::umma_f16(tmem_d + m * BN, adesc[m][c] + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0 ? 1u : 0u);
+                                ptx::umma_commit(bar_empty + 8 * stage);
+                            }
+                            __syncwarp();
+                            if (++stage == stages) { stage = 0; phase ^= 1; }
+                        }
+                        ptx::mbar_wait(bar_full + 8 * stage, phase);
+                        ptx::tc_fence_after();
+                        if (ptx::elect_one_sync()) {
+                            const uint64_t ndesc = ndesc0 + static_cast<uint64_t>(stage * STAGE_DESC);
+#pragma unroll
+                            for (int m = 0; m < MH; ++m) ptx::umma_f16(tmem_d + m * BN, odesc, ndesc, idesc, 1u);  // ones x (n0 n1 n2)
+                            ptx::umma_commit(bar_empty + 8 * stage);
+#pragma unroll
+                            for (int m = 0; m < MH; ++m) ptx::umma_commit(bar_tfull + 8 * (as * MH + m));
+                            if (last_tile) ptx::umma_commit(bar_aempty);  // query tile consumed
+                        }
+                        __syncwarp();
+                        if (++stage == stages) { stage = 0; phase ^= 1; }
+                    }
+                    if (++as == 2) { as = 0; accphase ^= 1; }
+                }
+            }
+            if (P.prof && lane == 0) {
+                P.prof[blockIdx.x * 16 + 2] = mw_te;
+                P.prof[blockIdx.x * 16 + 3] = mw_f;
+                P.prof[blockIdx.x * 16 + 4] = SPHB_CLOCK() - mt0;
+            }
+        } else {
         constexpr uint32_t idesc = ptx::make_idesc_f16(BM, BN);
         int stage = 0;
         uint32_t phase = 0, aphase = 0;
@@ -353,7 +477,8 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             ptx::tc_fence_after();
             for (int t = 0; t < P.n_dbtiles; ++t) {
                 long long w0 = SPHB_CLOCK();
-                ptx::mbar_wait(bar_tempty + 8 * as, accphase ^ 1);
+#pragma unroll
+                for (int m = 0; m < MH; ++m) ptx::mbar_wait(bar_tempty + 8 * (as * MH + m), accphase ^ 1);
                 mw_te += SPHB_CLOCK() - w0;
                 ptx::tc_fence_after();
                 for (int c = 0; c < nB; ++c) {
@@ -388,7 +513,10 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
                             }
                         }
                         ptx::umma_commit(bar_empty + 8 * stage);
-                        if (c == nB - 1) ptx::umma_commit(bar_tfull + 8 * as);
+                        if (c == nB - 1) {
+#pragma unroll
+                            for (int m = 0; m < MH; ++m) ptx::umma_commit(bar_tfull + 8 * (as * MH + m));
+                        }
                         if (c == nB - 1 && t == P.n_dbtiles - 1) ptx::umma_commit(bar_aempty);  // query tile consumed
                     }
                     __syncwarp();
@@ -402,9 +530,10 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             P.prof[blockIdx.x * 16 + 3] = mw_f;
             P.prof[blockIdx.x * 16 + 4] = SPHB_CLOCK() - mt0;
         }
+        }
     } else {
         // ===================== epilogue =====================
-        const int ew = warp - 2;       // 0 .. EPI_WARPS-1
+        const int ew = warp - 2;       // 0 .. 4*MH-1
         const int quarter = warp & 3;  // TMEM lane quarter this warp may access
         const int mhalf = ew >> 2;
         constexpr int cap = 32 * R;
@@ -427,8 +556,9 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             for (int t = 0; t < P.n_dbtiles; ++t) {
                 const int dt = (dt0 + t) % P.n_dbtiles;
                 long long w0 = SPHB_CLOCK();
-                ptx::mbar_wait(bar_tfull + 8 * as, accphase);
+                ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
                 ew_tf += SPHB_CLOCK() - w0;
+                SPHB_TRACE(P, qt, t, 8 + ew * 2);
                 ptx::tc_fence_after();
                 const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
@@ -442,15 +572,21 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
                     ptx::tmem_ld_wait(v1);
                     const long long w1 = SPHB_CLOCK();
                     e_ld += w1 - w0;
+#ifdef SPHB_FILTER_SINGLE
                     filter_chunk(v0, jbase + c * 32, n32, me, mybuf, n_accept);
                     compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
                     filter_chunk(v1, jbase + c * 32 + 32, n32, me, mybuf, n_accept);
                     compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
+#else
+                    filter_pair(v0, v1, jbase + c * 32, n32, me, mybuf, n_accept);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
+#endif
                     e_filt += SPHB_CLOCK() - w1;
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
+                SPHB_TRACE(P, qt, t, 9 + ew * 2);
+                if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * (as * MH + mhalf));
                 if (++as == 2) { as = 0; accphase ^= 1; }
             }
             const long long x0 = SPHB_CLOCK();
@@ -610,10 +746,15 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                     ptx::tmem_ld_32x32(taddr + c * 32 + 32, v1);
                     ptx::tmem_ld_wait(v0);
                     ptx::tmem_ld_wait(v1);
+#ifdef SPHB_FILTER_SINGLE
                     filter_chunk(v0, jbase + c * 32, n32, me, mybuf, n_accept);
                     compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
                     filter_chunk(v1, jbase + c * 32 + 32, n32, me, mybuf, n_accept);
                     compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
+#else
+                    filter_pair(v0, v1, jbase + c * 32, n32, me, mybuf, n_accept);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
+#endif
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
@@ -840,7 +981,12 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
 #else
     const bool want_prof = false;
 #endif
+    DevBuf<unsigned long long> trace;
     if (want_prof) {
+        SPHB_CUDA(trace.alloc(64 * 32, stream));
+        SPHB_CUDA(cudaMemsetAsync(trace.p, 0, 64 * 32 * sizeof(unsigned long long), stream));
+        P.trace = trace.p;
+        P.trace_t0 = getenv("SPHB_KNN_TRACE_T0") ? atoi(getenv("SPHB_KNN_TRACE_T0")) : 2000;
         SPHB_CUDA(prof.alloc(static_cast<size_t>(grid) * 16, stream));
         SPHB_CUDA(cudaMemsetAsync(prof.p, 0, static_cast<size_t>(grid) * 16 * sizeof(unsigned long long), stream));
         P.prof = prof.p;
@@ -882,20 +1028,26 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
         const size_t smem = fixed + static_cast<size_t>(stages) * CHUNK_BYTES;
         if (smem > smem_limit) return fail(5, "knn: shared memory budget exceeded for the resident kernel");
         P.dp64 = dp64; P.stages = stages;
+        P.half_major = (stages >= 2 * (nA + 1) && !getenv("SPHB_KNN_CHUNK_MAJOR")) ? 1 : 0;
         P.norm_bytes = opB.ldn == 16 ? 128 * 32 : CHUNK_BYTES;
         const int tail = d - 64 * (dp64 - 1);
         const int k16_tail = (tail + 15) / 16;
-#define SPHB_LAUNCH_RESIDENT(MH_, R_)                                                                                                      \
-    do {                                                                                                                                   \
-        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<MH_, R_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
-        knn_sweep_resident<MH_, R_><<<grid, 64 + 128 * MH_, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                              \
+#define SPHB_LAUNCH_RESIDENT(MH_, R_, DP_)                                                                                                      \
+    do {                                                                                                                                        \
+        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<MH_, R_, DP_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
+        knn_sweep_resident<MH_, R_, DP_><<<grid, 64 + 128 * MH_, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                              \
     } while (0)
-        if (MH == 2 && cap == 256) SPHB_LAUNCH_RESIDENT(2, 8);
-        else if (MH == 2 && cap == 512) SPHB_LAUNCH_RESIDENT(2, 16);
-        else if (MH == 2) SPHB_LAUNCH_RESIDENT(2, 32);
-        else if (cap == 256) SPHB_LAUNCH_RESIDENT(1, 8);
-        else if (cap == 512) SPHB_LAUNCH_RESIDENT(1, 16);
-        else SPHB_LAUNCH_RESIDENT(1, 32);
+        const bool lean = passes == 1 && MH == 2 && cap == 512 && !getenv("SPHB_KNN_GENERIC_ISSUE");
+        if (lean && dp64 == 1) SPHB_LAUNCH_RESIDENT(2, 16, 1);
+        else if (lean && dp64 == 2) SPHB_LAUNCH_RESIDENT(2, 16, 2);
+        else if (lean && dp64 == 3) SPHB_LAUNCH_RESIDENT(2, 16, 3);
+        else if (lean && dp64 == 4) SPHB_LAUNCH_RESIDENT(2, 16, 4);
+        else if (MH == 2 && cap == 256) SPHB_LAUNCH_RESIDENT(2, 8, 0);
+        else if (MH == 2 && cap == 512) SPHB_LAUNCH_RESIDENT(2, 16, 0);
+        else if (MH == 2) SPHB_LAUNCH_RESIDENT(2, 32, 0);
+        else if (cap == 256) SPHB_LAUNCH_RESIDENT(1, 8, 0);
+        else if (cap == 512) SPHB_LAUNCH_RESIDENT(1, 16, 0);
+        else SPHB_LAUNCH_RESIDENT(1, 32, 0);
 #undef SPHB_LAUNCH_RESIDENT
     } else {
         const int kchunks = (kp + BK - 1) / BK;
@@ -947,6 +1099,16 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
         double acc[16] = {0};
         for (int b = 0; b < grid; ++b)
             for (int i = 0; i < 16; ++i) acc[i] += static_cast<double>(hp[b * 16 + i]) / grid;
+        if (const char* tf = passes == 1 && !d_qrows ? getenv("SPHB_KNN_TRACE_FILE") : nullptr) {
+            std::vector<unsigned long long> ht(64 * 32);
+            cudaMemcpy(ht.data(), trace.p, ht.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+            if (FILE* f = fopen(tf, "w")) {
+                for (int t = 0; t < 64; ++t) {
+                    for (int sl = 0; sl < 32; ++sl) fprintf(f, "%llu%c", ht[t * 32 + sl], sl == 31 ? '\n' : ' ');
+                }
+                fclose(f);
+            }
+        }
         const int ew = MH ? 4 * MH : 4;
         fprintf(stderr,
                 "[knn prof] passes %d mean cycles per CTA: producer wait_empty %.3g of %.3g | mma wait_tempty %.3g wait_full %.3g of %.3g | "

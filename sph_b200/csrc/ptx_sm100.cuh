@@ -39,7 +39,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
+#ifdef SPHB_MBAR_SPIN
+            "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+#else
             "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+#endif
             "selp.u32 %0, 1, 0, p;\n"
             "}\n"
             : "=r"(done)
