@@ -114,6 +114,44 @@ def run_cpu_sample(x, k, budget_s, slab):
     return done, el
 
 
+def level1_p_wall_time(capi, synth):
+    """Second half of BASELINE.json's metric: wall time of the level-1 P matrix on a FIXED hierarchy.
+    Salinas-shaped stack (C2): level-0 kNN + P rows and W=90 x L=15 random walks are inputs (not timed); level 1 = 2x2 pixel
+    blocks (the ImageHierarchy merge loop is host code and out of scope).  Timed, through the host-buffer C ABI:
+    mergeNodesRandomWalks -> createSimilarities(k_1, 1e-4) -> in-place Gaussian rows (ignore = -1) -> symmetrizeTSNE
+    (sph/LevelSimilarities.cpp:460-508, 589-623)."""
+    from sph_b200 import host
+
+    h, w, d, k = 512, 217, 204, 91
+    x = synth.hyperspectral(h, w, d, endmembers=16, seed=1002)
+    n = h * w
+    ids, dist, cols, vals = capi.knn_graph_prow(x, k, 0.0)
+    rp0 = np.arange(n + 1, dtype=np.int64) * (k - 1)
+    t0 = time.perf_counter()
+    wrp, wc, wv = capi.random_walks(rp0, cols.reshape(-1), vals.reshape(-1), 90, 15, capi.W_NORMAL, seed=1, cap=n * 90 * 15 // 2)
+    t_walks = time.perf_counter() - t0
+    rows, colsi = np.divmod(np.arange(n), w)
+    hb, wb = (h + 1) // 2, (w + 1) // 2
+    parents = ((rows // 2) * wb + colsi // 2).astype(np.uint64)
+    n1 = hb * wb
+    _, ks = host.level_schedule([n, n1], k)
+    k1 = ks[1]
+    times = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        mrp, mc, mv = capi.rw_merge(wrp, wc, wv, parents, n1, norm=True, weight_by_size=True)
+        sc, sv, snz = capi.create_similarities(mrp, mc, mv, k1, 1e-4)
+        prp = np.concatenate([[0], np.cumsum(snz, dtype=np.int64)])
+        keep = np.arange(sc.shape[1])[None, :] < snz[:, None]
+        pc, pv = sc[keep], sv[keep]
+        pv = capi.prow_gaussian_inplace(prp, pv, 0.0, -1)
+        orp, oc, ov = capi.symmetrize(prp, pc, pv)
+        times.append(time.perf_counter() - t0)
+    return {"workload": f"C2-shaped {h}x{w}x{d}: level 1 = 2x2 pixel blocks ({n1} components), k_1 = {k1}, walks W=90 L=15 NORMAL",
+            "wall_ms": 1e3 * min(times), "wall_ms_all": [1e3 * t for t in times], "random_walks_level0_wall_ms": 1e3 * t_walks,
+            "walk_nnz": int(wrp[-1]), "merged_nnz": int(mrp[-1]), "p_nnz": int(orp[-1])}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -123,6 +161,7 @@ def main():
     ap.add_argument("--workload", default="C4", choices=["C1", "C2", "C4", "C5", "tiny"])
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-level1", action="store_true", help="skip the level-1 P-matrix wall-time measurement")
     ap.add_argument("--e2e-steps", type=int, default=1)
     args = ap.parse_args()
 
@@ -254,6 +293,20 @@ def main():
                 "kernel_ms": sweep, "prep_ms": float(np.mean(prep_ms)), "rerank_ms": float(np.mean(rerank_ms)),
                 "fallback_ms": float(np.mean(fallback_ms)), "kernel_share_of_step": sweep / ms_per_step}
 
+    # graph pass (Stage B2, level-0 P rows): HBM-bound, algorithmic bytes per row = k*4 + k*8 read + (k-1)*8 written
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    p0.record()
+    for _ in range(5):
+        capi.prow_gaussian_graph_dev(ids.data_ptr(), dst.data_ptr(), nq, k, 0.0, cols.data_ptr(), vals.data_ptr(), stream)
+    p1.record()
+    torch.cuda.synchronize()
+    prow_ms = p0.elapsed_time(p1) / 5
+    prow_bytes = nq * (k * 12 + (k - 1) * 8)
+    graph_pass = {"kernel": "prow_graph_kernel (perplexity rows, warp per row)", "bound": "hbm", "achieved": prow_bytes / (prow_ms * 1e-3) / 1e9,
+                  "peak": peaks["hbm"], "unit": "GB/s", "frac": prow_bytes / (prow_ms * 1e-3) / 1e9 / peaks["hbm"], "kernel_ms": prow_ms,
+                  "algorithmic_bytes_per_launch": prow_bytes}
+
     # end to end through the host-buffer C ABI (pinned host memory; H2D + D2H inside the timed region)
     xh = torch.from_numpy(x).pin_memory()
     out_h = (torch.empty((nq, k), dtype=torch.int64).pin_memory(), torch.empty((nq, k), dtype=torch.float32).pin_memory(),
@@ -271,13 +324,18 @@ def main():
     f1.record(es)
     barrier()
     e2e_ms = max_over_ranks(f0.elapsed_time(f1))
-    e2e_value = n * args.e2e_steps / (e2e_ms * 1e-3)
+    e2e_steps = max(1, args.e2e_steps)
+    e2e_value = n * args.e2e_steps / (e2e_ms * 1e-3) if args.e2e_steps else None
     h2d = world * n * d * 4
     d2h = n * (k * 12 + (k - 1) * 8)
     checksum = int(out_np[0][:, 1].sum() % (1 << 31))
 
     if rank != 0:
         return
+
+    level1 = None
+    if world == 1 and not args.no_level1:
+        level1 = level1_p_wall_time(capi, synth)
 
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
@@ -289,9 +347,9 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f16 tensor-core filter (fp32 accumulate) + f64 exact re-rank",
             "data": "synthetic", "config": config, "clocks": clocks.summary(),
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.e2e_steps,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / e2e_steps,
                     "result_checksum": checksum},
-            "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "gpu_launches": launches, "roofline": roofline, "graph_pass_roofline": graph_pass, "level1_p_matrix": level1, "cpu_baseline": cpu_baseline,
             "knn_stats": stats}
     print(json.dumps(line))
 

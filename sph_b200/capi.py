@@ -217,12 +217,12 @@ def symmetrize(rowptr, col, val, umap: bool = False):
 
 # ------------------------------------------------------------------ Stage C
 def random_walks(rowptr, col, val, num_walks: int, walk_len: int, weighting: int = W_CONSTANT, prune_value: float = 0.0, prune_steps: int = 0,
-                 seed: int = 0, remove_diagonal: bool = True, normalize: bool = True):
+                 seed: int = 0, remove_diagonal: bool = True, normalize: bool = True, cap: int | None = None):
     rowptr = np.ascontiguousarray(rowptr, np.int64)
     col = np.ascontiguousarray(col, np.uint32)
     val = np.ascontiguousarray(val, np.float32)
     n = len(rowptr) - 1
-    cap = max(1, n * min(n, num_walks * walk_len))
+    cap = max(1, n * min(n, num_walks * walk_len)) if cap is None else int(cap)
     orp = np.zeros(n + 1, np.int64)
     oc = np.zeros(cap, np.uint32)
     ov = np.zeros(cap, np.float32)
