@@ -165,6 +165,19 @@ SPHB_API int sphb_create_similarities(int64_t n, const int64_t* rowptr, const ui
 SPHB_API int sphb_pair_sims(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
                             const int64_t* pa, const int64_t* pb, int64_t npairs, int mode, float* out);
 
+/* Batched utils::findTopK (top = 1) / findBottomK (top = 0) (sph/utils/SparseMatrixAlgorithms.cpp:720-776, deque
+ * admission rules of sph/utils/MaxSizeDeque.hpp:97-200) over the rows of a CSR matrix — the per-row conversion
+ * convertEigenSparseVecToHDILibSparseVec does when randomWalkPairSims = false (sph/LevelSimilarities.cpp:481-486).
+ * out: fixed stride k, column-sorted, cols padded 0xFFFFFFFF, row_nnz[n]. */
+SPHB_API int sphb_find_k(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int64_t k, int top,
+                         uint32_t* out_cols, float* out_vals, int32_t* row_nnz);
+/* Batched utils::simNeighborOverlap (sph/utils/Similarities.cpp:174-228): for each pair of components (pa, pb)
+ * card(U_a ∩ U_b) / min(card U_a, card U_b), U_c = sorted-unique union of the data-level kNN lists (knn_ids [n*k]) of
+ * the pixels comp_pix[comp_ptr[c] .. comp_ptr[c+1]) of component c (Hierarchy::getRepresentedDataPoints).
+ * componentDistance = 1 - sim (sph/utils/Similarities.cpp:123-156). */
+SPHB_API int sphb_neighbor_overlap(const int64_t* knn_ids, int64_t n, int k, int64_t ncomp, const int64_t* comp_ptr,
+                                   const int64_t* comp_pix, const int64_t* pa, const int64_t* pb, int64_t npairs, float* out);
+
 #ifdef __cplusplus
 }
 #endif

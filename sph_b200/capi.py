@@ -54,6 +54,8 @@ SIGNATURES = {
     "sphb_rw_merge": (C.c_int, [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, C.c_int, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
     "sphb_create_similarities": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, u32p, f32p, i32p]),
     "sphb_pair_sims": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, i64p, C.c_int64, C.c_int, f32p]),
+    "sphb_find_k": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_int, u32p, f32p, i32p]),
+    "sphb_neighbor_overlap": (C.c_int, [i64p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
 }
 
 
@@ -273,4 +275,30 @@ def pair_sims(rowptr, col, val, pa, pb, mode: int = 0) -> np.ndarray:
     pb = np.ascontiguousarray(pb, np.int64)
     out = np.zeros(len(pa), np.float32)
     _check(load().sphb_pair_sims(len(rowptr) - 1, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(pa, i64p), _p(pb, i64p), len(pa), mode, _p(out, f32p)))
+    return out
+
+
+def find_k(rowptr, col, val, k: int, top: bool):
+    """Batched findTopK / findBottomK: (cols [n,k] padded 0xFFFFFFFF, vals [n,k], nnz [n])."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    oc = np.zeros((n, k), np.uint32)
+    ov = np.zeros((n, k), np.float32)
+    nnz = np.zeros(n, np.int32)
+    _check(load().sphb_find_k(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), k, int(top), _p(oc, u32p), _p(ov, f32p), _p(nnz, i32p)))
+    return oc, ov, nnz
+
+
+def neighbor_overlap(knn_ids, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
+    knn_ids = np.ascontiguousarray(knn_ids, np.int64)
+    comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+    comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+    pa = np.ascontiguousarray(pa, np.int64)
+    pb = np.ascontiguousarray(pb, np.int64)
+    out = np.zeros(len(pa), np.float32)
+    n, k = knn_ids.shape
+    _check(load().sphb_neighbor_overlap(_p(knn_ids, i64p), n, k, len(comp_ptr) - 1, _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p),
+                                        _p(pb, i64p), len(pa), _p(out, f32p)))
     return out

@@ -231,3 +231,57 @@ def test_random_walks_statistical_parity(capi, oracle, weighting):
     assert np.all(np.abs(gpu - expect) <= 6 * sigma + 1e-9), np.abs(gpu - expect) / sigma
     assert np.all(np.abs(ref - expect) <= 6 * sigma + 1e-9)
     assert abs(gpu.sum() - expect.sum()) < 1e-6 * expect.sum()
+
+
+# ---------------------------------------------------------------- D3
+def test_find_k_golden_and_oracle(capi, oracle):
+    g = gold("topk_deque.json")
+    rp = np.array([0, len(g["cols"])], np.int64)
+    oc, ov, nnz = capi.find_k(rp, g["cols"], g["vals"], g["k"], top=True)
+    assert [(int(a), float(b)) for a, b in zip(oc[0, :nnz[0]], ov[0, :nnz[0]])] == [(a, float(np.float32(b))) for a, b in g["top"]]
+    # ragged random rows incl. ties, zeros and an empty row, both directions
+    rng = np.random.default_rng(3)
+    lens = rng.integers(0, 200, size=400)
+    lens[0] = 0
+    rowptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    col = np.concatenate([np.sort(rng.choice(5000, size=m, replace=False)) for m in lens]).astype(np.uint32)
+    val = (rng.integers(0, 12, size=int(rowptr[-1])) / 11.0).astype(np.float32)  # heavy ties, exact zeros
+    for top in (True, False):
+        for k in (5, 31):
+            oc, ov, nnz = capi.find_k(rowptr, col, val, k, top)
+            for i in range(len(lens)):
+                rc, rv = oracle.find_k(col[rowptr[i]:rowptr[i + 1]], val[rowptr[i]:rowptr[i + 1]], k, top)
+                assert nnz[i] == len(rc)
+                np.testing.assert_array_equal(oc[i, :nnz[i]], rc)
+                np.testing.assert_array_equal(ov[i, :nnz[i]], rv)
+
+
+# ---------------------------------------------------------------- D5
+def test_neighbor_overlap_golden(capi):
+    g = gold("knn_overlap.json")
+    k = g["k"]
+    knn = np.array(g["knn"], np.int64).reshape(-1, k)
+    n = knn.shape[0]
+    l1 = g["children_l1"]
+    l2 = [sorted(p for c in comp for p in l1[c]) for comp in g["children_l2"]]
+    levels = {0: [[i] for i in range(n)], 1: l1, 2: l2}
+    for case in g["cases"]:
+        pa, pb = levels[case["a"][0]][case["a"][1]], levels[case["b"][0]][case["b"][1]]
+        comp_ptr = np.array([0, len(pa), len(pa) + len(pb)], np.int64)
+        sim = capi.neighbor_overlap(knn, comp_ptr, np.array(pa + pb, np.int64), [0], [1])[0]
+        assert sim == np.float32(np.float32(case["overlap"]) / np.float32(min(len(case["ua"]), len(case["ub"]))))
+
+
+def test_neighbor_overlap_matches_oracle(capi, oracle):
+    rng = np.random.default_rng(6)
+    n, k, ncomp = 6000, 31, 500
+    knn = np.stack([np.concatenate([[i], np.clip(i + rng.integers(-400, 400, size=k - 1), 0, n - 1)]) for i in range(n)]).astype(np.int64)
+    label = np.sort(rng.integers(0, ncomp, size=n))
+    label[:ncomp] = np.arange(ncomp)
+    order = np.argsort(label, kind="stable")
+    comp_ptr = np.concatenate([[0], np.cumsum(np.bincount(label, minlength=ncomp))]).astype(np.int64)
+    pa = rng.integers(0, ncomp, size=3000)
+    pb = np.clip(pa + rng.integers(-3, 4, size=3000), 0, ncomp - 1)
+    a = capi.neighbor_overlap(knn, comp_ptr, order, pa, pb)
+    b = oracle.neighbor_overlap(knn, comp_ptr, order, pa, pb)
+    np.testing.assert_array_equal(a, b)
