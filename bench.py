@@ -284,7 +284,7 @@ def main():
             traffic = json.loads(tp.read_text()).get(args.workload)
         except Exception:
             traffic = None
-    flavour = {3: "knn_sweep_resident<MH=2>", 2: "knn_sweep_resident<MH=1>", 1: "knn_sweep_stream"}.get(stats["tensor_core"], "knn_simt")
+    flavour = {4: "knn_sweep_pair (cta_group::2, 2 x 256 resident query rows)", 3: "knn_sweep_resident<MH=2>", 2: "knn_sweep_resident<MH=1>", 1: "knn_sweep_stream"}.get(stats["tensor_core"], "knn_simt")
     roofline = {"bound": "tensor", "kernel": f"{flavour}, {stats['passes']} fp16 product(s) per pair",
                 "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": traffic,
                 "peak_source": f"{peaks['src']} bf16 sustained (fp16 runs at the same tensor rate)",

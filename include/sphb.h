@@ -90,7 +90,7 @@ SPHB_API int sphb_knn_exact_slab(const float* x, int64_t n, int d, int k, int me
 SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared,
                                 int64_t q0, int64_t q1, int64_t* d_ids, float* d_dist, void* stream);
 /* kNN statistics of the last call: [0] path (0 SIMT, 1 tcgen05 streaming, 2 tcgen05 resident MH=1,
- * 3 tcgen05 resident MH=2), [1] candidate-list compactions, [2] candidates accepted by the filter,
+ * 3 tcgen05 resident MH=2, 4 tcgen05 CTA pair (cta_group::2)), [1] candidate-list compactions, [2] candidates accepted by the filter,
  * [3] executed GEMM K extent per pair of the main sweep, [4] rows recomputed by the exact SIMT kernel
  * (candidate band overflow), [5] query tiles, [6] fp16 products per pair of the main sweep (1 or 3),
  * [7] rows re-swept with the 3-product filter after overflowing the 1-product band. */

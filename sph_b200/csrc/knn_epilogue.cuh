@@ -167,6 +167,98 @@ __device__ __forceinline__ void compact_row_approx(RowList& me, int L, uint64_t*
     __syncwarp();
 }
 
+// ---- in-sweep compaction: selection on the 32-bit values only --------------------------------------------
+// What a compaction during the sweep has to deliver is the row's new threshold (k-th smallest value + band) and the
+// list without the entries above it; the order of the survivors is irrelevant (export_rows sorts once at the end).
+// So only the ordered 32-bit value halves are sorted — one shuffle and a min/max per element and stage instead of
+// a 64-bit compare-exchange — and the u64 entries, kept in registers, are stream-compacted in place.
+template <int R, int J2>
+__device__ __forceinline__ void bitonic32_inlane_stage(uint32_t (&x)[R], int lane, int k2) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        if ((r & J2) == 0) {
+            const bool up = (((lane * R + r) & k2) == 0);
+            const uint32_t mn = min(x[r], x[r | J2]), mx = max(x[r], x[r | J2]);
+            x[r] = up ? mn : mx;
+            x[r | J2] = up ? mx : mn;
+        }
+    }
+}
+template <int R, int J2>
+__device__ __forceinline__ void bitonic32_inlane_from(uint32_t (&x)[R], int lane, int k2) {
+    if constexpr (J2 >= 1) {
+        if (J2 < k2) bitonic32_inlane_stage<R, J2>(x, lane, k2);
+        bitonic32_inlane_from<R, J2 / 2>(x, lane, k2);
+    }
+}
+template <int R>
+__device__ __forceinline__ void warp_bitonic_sort_regs32(uint32_t (&x)[R], int lane) {
+#pragma unroll 1
+    for (int k2 = 2; k2 <= 32 * R; k2 <<= 1) {
+#pragma unroll 1
+        for (int lj = (k2 >> 1) / R; lj > 0; lj >>= 1) {
+            const bool lower = (lane & lj) == 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const uint32_t other = __shfl_xor_sync(0xffffffffu, x[r], lj);
+                const bool up = (((lane * R + r) & k2) == 0);
+                x[r] = (lower == up) ? min(x[r], other) : max(x[r], other);
+            }
+        }
+        bitonic32_inlane_from<R, R / 2>(x, lane, k2);
+    }
+}
+
+template <int R>
+__device__ __forceinline__ void compact_row_select(RowList& me, int L, uint64_t* __restrict__ buf_L, int k, int keep_max, int lane,
+                                                   const BandConsts& bc) {
+    const int cntL = __shfl_sync(0xffffffffu, me.cnt, L);
+    uint64_t x[R];
+    uint32_t v[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int e = r * 32 + lane;  // coalesced
+        x[r] = (e < cntL) ? buf_L[e] : ~0ull;
+        v[r] = static_cast<uint32_t>(x[r] >> 32);
+    }
+    int m = cntL;
+    float limit = INFINITY;
+    int ovf = 0;
+    if (cntL >= k) {
+        warp_bitonic_sort_regs32<R>(v, lane);  // as a multiset; sorted position p = lane*R + r
+        uint32_t kth = 0;
+        const int kr = (k - 1) % R;
+#pragma unroll
+        for (int r = 0; r < R; ++r) kth = (r == kr) ? v[r] : kth;
+        kth = __shfl_sync(0xffffffffu, kth, (k - 1) / R);
+        const float gk = ord2f(kth);
+        const float band = bc.passes == 3 ? me.eps2 : band_1pass(gk, me.un, me.dun, bc);
+        limit = __fadd_ru(gk, __shfl_sync(0xffffffffu, band, L));
+        const uint32_t lim = f2ord(limit);
+        const unsigned lt = (1u << lane) - 1u;
+        int base = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool keep = (r * 32 + lane < cntL) && static_cast<uint32_t>(x[r] >> 32) <= lim;
+            const unsigned mk = __ballot_sync(0xffffffffu, keep);
+            const int pos = base + __popc(mk & lt);
+            if (keep && pos < keep_max) buf_L[pos] = x[r];  // pos <= r*32 + lane: never ahead of an unread slot (all reads are done)
+            base += __popc(mk);
+        }
+        m = base;
+        if (m > keep_max) {
+            m = keep_max;
+            ovf = 1;
+        }
+    }
+    if (lane == L) {
+        me.cnt = m;
+        me.thr = limit;
+        me.ovf |= ovf;
+    }
+    __syncwarp();
+}
+
 // Filter one 32-column chunk of the accumulator tile held in v[] (columns jbase..jbase+31).
 // Fast path: 8 group minima (4 columns each) + their minimum, one compare.  Slow path (some
 // column passes): only the groups whose minimum passes are scanned.
@@ -209,23 +301,28 @@ __device__ __forceinline__ void filter_pair(const float (&v0)[32], const float (
     if (fminf(m0, m1) <= me.thr) {
         const float thr = me.thr;
         int cnt = me.cnt;
+        // usually one lane passes with one value: only the 32-column half (and 4-column group) that holds it is scanned
+        if (m0 <= thr) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            if (g0[q] <= thr) {
+            for (int q = 0; q < 8; ++q) {
+                if (g0[q] <= thr) {
 #pragma unroll
-                for (int t = 4 * q; t < 4 * q + 4; ++t) {
-                    const uint32_t j = jbase + t;
-                    if (v0[t] <= thr && j < n) mybuf[cnt++] = make_key(v0[t], j);
+                    for (int t = 4 * q; t < 4 * q + 4; ++t) {
+                        const uint32_t j = jbase + t;
+                        if (v0[t] <= thr && j < n) mybuf[cnt++] = make_key(v0[t], j);
+                    }
                 }
             }
         }
+        if (m1 <= thr) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            if (g1[q] <= thr) {
+            for (int q = 0; q < 8; ++q) {
+                if (g1[q] <= thr) {
 #pragma unroll
-                for (int t = 4 * q; t < 4 * q + 4; ++t) {
-                    const uint32_t j = jbase + 32 + t;
-                    if (v1[t] <= thr && j < n) mybuf[cnt++] = make_key(v1[t], j);
+                    for (int t = 4 * q; t < 4 * q + 4; ++t) {
+                        const uint32_t j = jbase + 32 + t;
+                        if (v1[t] <= thr && j < n) mybuf[cnt++] = make_key(v1[t], j);
+                    }
                 }
             }
         }
@@ -246,8 +343,12 @@ __device__ __forceinline__ void compact_full_rows(RowList& me, uint64_t* __restr
     while (full) {
         const int L = __ffs(full) - 1;
         full &= full - 1;
+#ifdef SPHB_COMPACT_FULL_SORT
         uint64_t x[R];
         compact_row_approx<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, x, k, keep_max, lane, bc);
+#else
+        compact_row_select<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, k, keep_max, lane, bc);
+#endif
         ++n_compact;
     }
     t_compact += SPHB_CLOCK() - c0;
@@ -267,6 +368,62 @@ __device__ __forceinline__ void export_rows(RowList& me, int64_t r0, int64_t nq,
         compact_row_approx<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, x, k, keep_max, lane, bc);
         const int m = __shfl_sync(0xffffffffu, me.cnt, L);
         const int ovf = __shfl_sync(0xffffffffu, me.ovf, L);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int e = lane * R + r;
+            if (e < m) cand_out[rL * keep_max + e] = key_idx(x[r]);
+        }
+        if (lane == 0) cnt_out[rL] = m | (ovf ? OVERFLOW_FLAG : 0);
+        __syncwarp();
+    }
+}
+
+// Export for the two-group epilogue: lane L's row has mA = me.cnt survivors in bufA_L and mB (other & ~flag)
+// survivors in bufB_L (both unsorted, each pruned against its own list's k-th value + band, mA, mB <= cap/2).  A true
+// neighbour is among the k smallest of the half of the database its list saw, so it survived there; the union is
+// sorted, pruned against the k-th value of the union + band, and exported like export_rows does.
+template <int R>
+__device__ __forceinline__ void export_rows_merged(RowList& me, int other, int64_t r0, int64_t nq, uint64_t* __restrict__ warp_bufA,
+                                                   uint64_t* __restrict__ warp_bufB, int k, int keep_max, uint32_t* __restrict__ cand_out,
+                                                   int* __restrict__ cnt_out, int lane, const BandConsts& bc) {
+    constexpr int cap = 32 * R;
+    __syncwarp();
+    for (int L = 0; L < 32; ++L) {
+        const int64_t rL = r0 + L;
+        if (rL >= nq) break;
+        const int mA = __shfl_sync(0xffffffffu, me.cnt, L);
+        const int oB = __shfl_sync(0xffffffffu, other, L);
+        const int mB = oB & ~OVERFLOW_FLAG;
+        int ovf = __shfl_sync(0xffffffffu, me.ovf, L) | ((oB & OVERFLOW_FLAG) ? 1 : 0);
+        const uint64_t* bufA = warp_bufA + static_cast<size_t>(L) * cap;
+        const uint64_t* bufB = warp_bufB + static_cast<size_t>(L) * cap;
+        uint64_t x[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int e = lane * R + r;
+            x[r] = e < mA ? bufA[e] : (e < mA + mB ? bufB[e - mA] : ~0ull);
+        }
+        warp_bitonic_sort_regs<R>(x, lane);
+        int m = mA + mB;
+        if (m >= k) {
+            uint64_t kth = 0;
+            const int kr = (k - 1) % R;
+#pragma unroll
+            for (int r = 0; r < R; ++r) kth = (r == kr) ? x[r] : kth;
+            kth = __shfl_sync(0xffffffffu, kth, (k - 1) / R);
+            const float band = bc.passes == 3 ? me.eps2 : band_1pass(key_val(kth), me.un, me.dun, bc);
+            const float limit = __fadd_ru(key_val(kth), __shfl_sync(0xffffffffu, band, L));
+            int c = 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) c += (lane * R + r < m && key_val(x[r]) <= limit) ? 1 : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+            m = c;
+            if (m > keep_max) {
+                m = keep_max;
+                ovf = 1;
+            }
+        }
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int e = lane * R + r;

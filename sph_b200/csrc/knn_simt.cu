@@ -52,6 +52,91 @@ __global__ void __launch_bounds__(WARPS * 32) knn_simt_kernel(const float* __res
     }
 }
 
+// Few rows (the overflow fallback of the tensor-core path): one warp per (row, database segment) keeps the best k of
+// its segment, a second kernel merges the S sorted segment lists of a row.  Same keys, same (value, index) order.
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) knn_simt_seg_kernel(const float* __restrict__ X, int64_t n, int d, int k, int cap, int metric,
+                                                                  const int64_t* __restrict__ rowlist, const int* __restrict__ rowcount, int S,
+                                                                  int64_t seglen, uint64_t* __restrict__ tmp) {
+    extern __shared__ uint64_t smem_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
+    const int64_t nwork = static_cast<int64_t>(*rowcount) * S;
+    for (int64_t w = static_cast<int64_t>(blockIdx.x) * WARPS + warp; w < nwork; w += static_cast<int64_t>(gridDim.x) * WARPS) {
+        const int64_t i = rowlist[w / S];
+        const int64_t j0 = (w % S) * seglen, j1 = min(n, j0 + seglen);
+        int cnt = 0;
+        uint64_t kth = ~0ull;
+        for (int64_t base = j0; base < j1; base += 32) {
+            const int64_t j = base + lane;
+            bool pass = false;
+            uint64_t key = ~0ull;
+            if (j < j1) {
+                key = make_key(exact_key(X, i, j, d, metric), static_cast<uint32_t>(j));
+                pass = key <= kth;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (m) {
+                if (pass) sm[cnt + __popc(m & ((1u << lane) - 1u))] = key;
+                cnt += __popc(m);
+                if (cnt + 32 > cap) {
+                    for (int t = cnt + lane; t < cap; t += 32) sm[t] = ~0ull;
+                    __syncwarp();
+                    warp_bitonic_sort(sm, cap, lane);
+                    cnt = min(cnt, k);
+                    kth = (cnt == k) ? sm[k - 1] : ~0ull;
+                }
+            }
+        }
+        for (int t = cnt + lane; t < cap; t += 32) sm[t] = ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        for (int t = lane; t < k; t += 32) tmp[w * k + t] = sm[t];  // padded with ~0
+        __syncwarp();
+    }
+}
+
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) knn_simt_merge_kernel(const uint64_t* __restrict__ tmp, int S, int k, int cap, int metric, int l2_squared,
+                                                                    int64_t q0, const int64_t* __restrict__ rowlist, const int* __restrict__ rowcount,
+                                                                    int64_t* __restrict__ ids, float* __restrict__ dist) {
+    extern __shared__ uint64_t smem_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
+    const int64_t nq = *rowcount;
+    for (int64_t rr = static_cast<int64_t>(blockIdx.x) * WARPS + warp; rr < nq; rr += static_cast<int64_t>(gridDim.x) * WARPS) {
+        const int64_t i = rowlist[rr];
+        const uint64_t* src = tmp + rr * S * k;
+        const int total = S * k;
+        int cnt = 0;
+        uint64_t kth = ~0ull;
+        for (int base = 0; base < total; base += 32) {
+            const int t = base + lane;
+            const uint64_t key = t < total ? src[t] : ~0ull;
+            const bool pass = key != ~0ull && key <= kth;
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (m) {
+                if (pass) sm[cnt + __popc(m & ((1u << lane) - 1u))] = key;
+                cnt += __popc(m);
+                if (cnt + 32 > cap) {
+                    for (int u = cnt + lane; u < cap; u += 32) sm[u] = ~0ull;
+                    __syncwarp();
+                    warp_bitonic_sort(sm, cap, lane);
+                    cnt = min(cnt, k);
+                    kth = (cnt == k) ? sm[k - 1] : ~0ull;
+                }
+            }
+        }
+        for (int t = cnt + lane; t < cap; t += 32) sm[t] = ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        cnt = min(cnt, k);
+        const int64_t r = i - q0;
+        write_row(sm, cnt, k, i, metric, l2_squared, ids + r * k, dist + r * k, lane);
+        __syncwarp();
+    }
+}
+
 static int next_pow2(int v) {
     int p = 1;
     while (p < v) p <<= 1;
@@ -67,6 +152,26 @@ int knn_simt_launch(const float* d_x, int64_t n, int d, int k, int metric, int l
     SPHB_CUDA(cudaFuncSetAttribute(knn_simt_kernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     const int64_t nq = d_rowlist ? max_rows : q1 - q0;
     if (nq <= 0) return 0;
+    const int64_t target_warps = static_cast<int64_t>(ctx().num_sms) * 32;
+    if (d_rowlist && nq * 2 <= target_warps && n >= 4096) {
+        int S = static_cast<int>(std::min<int64_t>((target_warps + nq - 1) / nq, std::min<int64_t>(256, n / 1024)));
+        if (S < 2) S = 2;
+        const int64_t seglen = ((n + S - 1) / S + 31) / 32 * 32;
+        DevBuf<uint64_t> tmp;
+        SPHB_CUDA(tmp.alloc(static_cast<size_t>(nq) * S * k, stream));
+        SPHB_CUDA(cudaFuncSetAttribute(knn_simt_seg_kernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        SPHB_CUDA(cudaFuncSetAttribute(knn_simt_merge_kernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        const int64_t b1 = std::min<int64_t>((nq * S + WARPS - 1) / WARPS, static_cast<int64_t>(ctx().num_sms) * 16);
+        knn_simt_seg_kernel<WARPS><<<static_cast<unsigned>(b1), WARPS * 32, smem, stream>>>(d_x, n, d, k, cap, metric, d_rowlist, d_rowcount, S, seglen, tmp.p);
+        count_launch();
+        SPHB_CUDA(cudaGetLastError());
+        const int64_t b2 = (nq + WARPS - 1) / WARPS;
+        knn_simt_merge_kernel<WARPS><<<static_cast<unsigned>(b2), WARPS * 32, smem, stream>>>(tmp.p, S, k, cap, metric, l2_squared, q0, d_rowlist, d_rowcount,
+                                                                                              d_ids, d_dist);
+        count_launch();
+        SPHB_CUDA(cudaGetLastError());
+        return 0;
+    }
     int64_t blocks = (nq + WARPS - 1) / WARPS;
     const int64_t maxb = static_cast<int64_t>(ctx().num_sms) * 16;
     if (blocks > maxb) blocks = maxb;

@@ -63,6 +63,7 @@ struct SweepParams {
     uint32_t* cand_out;    // [nq, keep_max]
     int* cnt_out;          // [nq]
     unsigned long long* stats;  // [0] compactions, [1] accepted candidates
+    int pair_debug;             // debug knobs of the CTA-pair kernel (SPHB_KNN_PAIR_DEBUG bit mask; timing experiments only)
     int debug_skip_epilogue;    // debug: epilogue releases the accumulator without reading it (pure MMA rate)
     unsigned long long* trace;  // optional (profile build): CTA 0, first query tile, database tiles [trace_t0, trace_t0+64): 32 clock stamps per tile
     int trace_t0;
@@ -107,12 +108,15 @@ __device__ __forceinline__ void init_row(RowList& me, const SweepParams& P, int6
 // rows' thresholds tighten within the first few percent of the sweep and the filter's slow path becomes
 // rare — each shifted by blockIdx.x * stagger tiles so that the CTAs read different L2 lines at any moment
 // while the union of their positions stays inside an L2-sized window.
-__device__ __forceinline__ int sweep_start(const SweepParams& P, int qt, int rows_per_cta, int bn) {
-    const int64_t r0 = static_cast<int64_t>(qt - static_cast<int>(blockIdx.x)) * rows_per_cta;
+// r0: first query row of the wave, slot: position of the CTA (or CTA pair) inside the wave
+__device__ __forceinline__ int sweep_start_at(const SweepParams& P, int64_t r0, int slot, int bn) {
     const int64_t anchor = P.qrows ? P.qrows[r0 < P.nq ? r0 : P.nq - 1] : P.q0 + r0;
-    int64_t t = (anchor / bn - P.lead + static_cast<int64_t>(blockIdx.x) * P.stagger) % P.n_dbtiles;
+    int64_t t = (anchor / bn - P.lead + static_cast<int64_t>(slot) * P.stagger) % P.n_dbtiles;
     if (t < 0) t += P.n_dbtiles;
     return static_cast<int>(t);
+}
+__device__ __forceinline__ int sweep_start(const SweepParams& P, int qt, int rows_per_cta, int bn) {
+    return sweep_start_at(P, static_cast<int64_t>(qt - static_cast<int>(blockIdx.x)) * rows_per_cta, static_cast<int>(blockIdx.x), bn);
 }
 
 // ---------------------------------------------------------------------------
@@ -252,8 +256,8 @@ __global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [
 // DP64T > 0: 1-pass specialisation with the chunk count known at compile time (the MMA issue loop is
 // straight-line code with pre-built descriptors; every hi chunk runs all 4 k-steps, the zero padding of
 // the operands makes that exact); DP64T = 0: generic (runtime chunk count, 1 or 3 passes, partial last chunk).
-template <int MH, int R, int DP64T>
-__global__ void __launch_bounds__(64 + 128 * MH, 1)
+template <int MH, int R, int DP64T, int G = 1>
+__global__ void __launch_bounds__(64 + 128 * MH * G) __maxnreg__(G == 2 ? 96 : (MH == 2 ? 168 : 255))
 knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                    const __grid_constant__ CUtensorMap tmapN, const __grid_constant__ CUtensorMap tmapO, const SweepParams P,
                    const int k16_tail) {
@@ -280,6 +284,7 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     const uint32_t bar_afull = ptx::smem_u32(bars + 2 * stages + 8);
     const uint32_t bar_aempty = ptx::smem_u32(bars + 2 * stages + 9);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 10);
+    int* xch = reinterpret_cast<int*>(bars + 2 * stages + 11);  // G = 2: [MH * BM] list lengths handed from group 1 to group 0 at export
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // warps: 0 TMA producer, 1 MMA issuer, 2.. epilogue.  (A second issuer warp, one per M half, was measured: no gain —
@@ -533,13 +538,18 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         }
     } else {
         // ===================== epilogue =====================
-        const int ew = warp - 2;       // 0 .. 4*MH-1
-        const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+        // G = 2: two groups of 4*MH epilogue warps; group g owns accumulator stage g, i.e. the database tiles t with
+        // t % 2 == g (n_dbtiles is even), and keeps its own candidate list and threshold per row.  A warp alone is
+        // latency bound (dependent min trees, TMEM loads, list appends); twice the warps hide twice the latency, and a
+        // group has two MMA tile times per tile.  The two lists of a row are merged at export.
+        const int grp = (warp - 2) / (4 * MH);
+        const int ew = (warp - 2) % (4 * MH);  // 0 .. 4*MH-1
+        const int quarter = warp & 3;          // TMEM lane quarter this warp may access
         const int mhalf = ew >> 2;
         constexpr int cap = 32 * R;
         const int k = P.k, keep_max = P.keep_max;
         const BandConsts bc = make_band_consts(P);
-        int as = 0;
+        int as = G == 2 ? grp : 0;
         uint32_t accphase = 0;
         unsigned long long n_compact = 0, n_accept = 0;
         const uint32_t n32 = static_cast<uint32_t>(P.n);
@@ -548,12 +558,12 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             const int row_in_tile = mhalf * BM + quarter * 32 + lane;
             const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
             const bool valid = r < P.nq;
-            uint64_t* warp_buf = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + (row_in_tile - lane)) * cap;
+            uint64_t* warp_buf = P.cand + ((static_cast<size_t>(blockIdx.x) * G + grp) * (MH * BM) + (row_in_tile - lane)) * cap;
             uint64_t* mybuf = warp_buf + static_cast<size_t>(lane) * cap;
             RowList me;
             init_row(me, P, r, valid);
             const int dt0 = sweep_start(P, qt, MH * BM, BN);
-            for (int t = 0; t < P.n_dbtiles; ++t) {
+            for (int t = (G == 2 ? grp : 0); t < P.n_dbtiles; t += G) {
                 const int dt = (dt0 + t) % P.n_dbtiles;
                 long long w0 = SPHB_CLOCK();
                 ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
@@ -587,10 +597,37 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
                 __syncwarp();
                 SPHB_TRACE(P, qt, t, 9 + ew * 2);
                 if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * (as * MH + mhalf));
-                if (++as == 2) { as = 0; accphase ^= 1; }
+                if constexpr (G == 2) {
+                    accphase ^= 1;
+                } else {
+                    if (++as == 2) { as = 0; accphase ^= 1; }
+                }
             }
             const long long x0 = SPHB_CLOCK();
-            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
+            if constexpr (G == 2) {
+                // both groups prune their lists to at most cap/2 survivors each; group 1 hands its lengths over, group 0
+                // sorts the union, applies the joint band and exports.  Named barrier 1 + ew pairs the two warps of a row block.
+                constexpr int half_keep = cap / 2;
+                __syncwarp();
+                for (int L = 0; L < 32; ++L) {
+                    if (r - lane + L >= P.nq) break;
+                    compact_row_select<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, k, half_keep, lane, bc);
+                }
+                uint64_t* other_buf = P.cand + ((static_cast<size_t>(blockIdx.x) * G + 1) * (MH * BM) + (row_in_tile - lane)) * cap;
+                if (grp == 1) {
+                    xch[row_in_tile] = me.cnt | (me.ovf ? OVERFLOW_FLAG : 0);
+                    __threadfence_block();
+                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");  // lists + lengths visible to group 0
+                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");  // group 0 has read them
+                } else {
+                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");
+                    const int other = xch[row_in_tile];
+                    export_rows_merged<R>(me, other, r - lane, P.nq, warp_buf, other_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
+                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");
+                }
+            } else {
+                export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
+            }
             e_exp += SPHB_CLOCK() - x0;
         }
         if (P.prof && lane == 0) {
@@ -613,6 +650,272 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------
+// sweep, CTA-pair flavour (1 pass, d <= 256): the resident kernel on cta_group::2
+// ---------------------------------------------------------------------------
+// Two CTAs of a cluster (one TPC) share every MMA: M = 256 = 128 query rows from each CTA's resident tile,
+// N = 128 database rows of which each CTA stages 64.  Per SM and k-step the tensor core then reads 4 KB of A
+// and 2 KB of B from shared memory instead of 4 + 4 — the single-CTA kernel is bound by exactly that operand
+// bandwidth — and each database tile crosses L2 -> SM once per 512 query rows instead of 256.
+// Each CTA keeps MH = 2 resident halves (256 query rows) and runs its own epilogue on its own TMEM lanes.
+// smem per CTA: [A: 2 x DP64T chunks of 16 KB | ONES 16 KB | B ring: stages slots of 8 KB | barriers | tmem slot]
+// Barriers: full[s] (leader, 2 arrivals: each CTA's expect_tx), empty[s] / tfull[as][m] / aempty (one per CTA,
+// multicast commit), tempty[as][m] (leader, 8 arrivals: 4 epilogue warps of each CTA), afull (leader, 2 arrivals).
+namespace tcp {
+constexpr int SLOT_BYTES = 64 * 128;       // 64 database rows x 64 fp16
+constexpr int NORM_BYTES = 64 * 32;        // 64 database rows x 16 fp16 (SWIZZLE_32B)
+constexpr int NUM_THREADS = 64 + 256;
+}  // namespace tcp
+
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_bar), "r"(bytes) : "memory");
+}
+
+template <int R, int DP64T>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tcp::NUM_THREADS, 1)
+knn_sweep_pair(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, const __grid_constant__ CUtensorMap tmapN,
+               const __grid_constant__ CUtensorMap tmapO, const SweepParams P) {
+    using namespace tc;
+    using namespace tcp;
+    constexpr int MH = 2, BN = 128;
+    constexpr int ACC_COLS = MH * BN;
+    constexpr int TMEM_COLS = 2 * ACC_COLS;
+    constexpr int NB = DP64T + 1;  // ring slots per database tile
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    const int stages = P.stages;
+    const uint32_t smem_base = ptx::smem_u32(smem);
+    const uint32_t sA = smem_base;
+    const uint32_t sO = sA + MH * DP64T * CHUNK_BYTES;
+    const uint32_t sB = sO + CHUNK_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(MH * DP64T + 1) * CHUNK_BYTES + static_cast<size_t>(stages) * SLOT_BYTES);
+    const uint32_t bar_full = ptx::smem_u32(bars);
+    const uint32_t bar_empty = ptx::smem_u32(bars + stages);
+    const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * stages);
+    const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * stages + 4);
+    const uint32_t bar_afull = ptx::smem_u32(bars + 2 * stages + 8);
+    const uint32_t bar_aempty = ptx::smem_u32(bars + 2 * stages + 9);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 10);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    const int n_ptiles = (P.n_qtiles + 1) >> 1;  // pair tiles of 512 query rows
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmapA);
+        ptx::prefetch_tmap(&tmapB);
+        ptx::prefetch_tmap(&tmapN);
+        ptx::prefetch_tmap(&tmapO);
+        for (int s = 0; s < stages; ++s) {
+            ptx::mbar_init(bar_full + 8 * s, (P.pair_debug & 2) ? 1 : 2);
+            ptx::mbar_init(bar_empty + 8 * s, 1);
+        }
+        for (int s = 0; s < 2 * MH; ++s) {
+            ptx::mbar_init(bar_tfull + 8 * s, 1);
+            ptx::mbar_init(bar_tempty + 8 * s, (P.pair_debug & 1) ? 4 : 8);
+        }
+        ptx::mbar_init(bar_afull, 2);
+        ptx::mbar_init(bar_aempty, 1);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) {
+        ptx::tmem_alloc_pair(ptx::smem_u32(tmem_slot), TMEM_COLS);
+        ptx::tmem_relinquish_pair();
+    }
+    ptx::tc_fence_before();
+    ptx::cluster_sync();  // barrier inits of both CTAs visible before any remote arrive / multicast commit
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs; completion counted on the leader's barriers) =====================
+        const uint32_t afull_l = ptx::mapa(bar_afull, 0);
+        const uint32_t full_l = ptx::mapa(bar_full, 0);
+        int stage = 0;
+        uint32_t phase = 0, aphase = 0;
+        bool first = true;
+        long long pw = 0, pt0 = SPHB_CLOCK();
+        const bool solo_tx = (P.pair_debug & 2) != 0;  // debug: only the leader registers the bytes (of both CTAs)
+        const bool no_b = (P.pair_debug & 4) != 0;     // debug: no database loads at all (MMA issue rate on stale smem)
+        for (int pt = pair; pt < n_ptiles; pt += n_pairs) {
+            const int qt = 2 * pt + static_cast<int>(rank);  // this CTA's 256-row query tile (may be past the end: zero rows)
+            ptx::mbar_wait(bar_aempty, aphase ^ 1);
+            if (ptx::elect_one_sync()) {
+                mbar_expect_tx_cluster(afull_l, (MH * DP64T + (first ? 1 : 0)) * CHUNK_BYTES);
+                for (int m = 0; m < MH; ++m) {
+                    const int32_t qrow = static_cast<int32_t>(P.a_row0 + (static_cast<int64_t>(qt) * MH + m) * BM);
+                    for (int c = 0; c < DP64T; ++c) ptx::tma_load_2d_pair(sA + (m * DP64T + c) * CHUNK_BYTES, &tmapA, afull_l, c * BK, qrow);
+                }
+                if (first) ptx::tma_load_2d_pair(sO, &tmapO, afull_l, 0, 0);
+            }
+            __syncwarp();
+            first = false;
+            aphase ^= 1;
+            const int dt0 = sweep_start_at(P, static_cast<int64_t>(pt - pair) * (2 * MH * BM), 2 * pair, BN);
+            for (int t = 0; t < P.n_dbtiles; ++t) {
+                const int dt = (dt0 + t) % P.n_dbtiles;
+                const int32_t brow = dt * BN + static_cast<int32_t>(rank) * 64;
+#pragma unroll
+                for (int c = 0; c < NB; ++c) {
+                    if (no_b) break;
+                    const long long w0 = SPHB_CLOCK();
+                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    pw += SPHB_CLOCK() - w0;
+                    if (ptx::elect_one_sync()) {
+                        const uint32_t bytes = c < DP64T ? SLOT_BYTES : NORM_BYTES;
+                        if (!solo_tx) mbar_expect_tx_cluster(full_l + 8 * stage, bytes);
+                        else if (rank == 0) ptx::mbar_expect_tx(bar_full + 8 * stage, 2 * bytes);
+                        if (c < DP64T) ptx::tma_load_2d_pair(sB + stage * SLOT_BYTES, &tmapB, full_l + 8 * stage, c * BK, brow);
+                        else ptx::tma_load_2d_pair(sB + stage * SLOT_BYTES, &tmapN, full_l + 8 * stage, 0, brow);
+                    }
+                    __syncwarp();
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        if (P.prof && lane == 0) {
+            P.prof[blockIdx.x * 16 + 0] = pw;
+            P.prof[blockIdx.x * 16 + 1] = SPHB_CLOCK() - pt0;
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (rank == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_f16(2 * BM, BN);
+            constexpr uint32_t SLOT_DESC = SLOT_BYTES >> 4;
+            uint64_t adesc[MH][DP64T];
+#pragma unroll
+            for (int m = 0; m < MH; ++m)
+#pragma unroll
+                for (int c = 0; c < DP64T; ++c) adesc[m][c] = ptx::make_smem_desc_sw128(sA + (m * DP64T + c) * CHUNK_BYTES);
+            const uint64_t odesc = ptx::make_smem_desc_sw128(sO);
+            const uint64_t bdesc0 = ptx::make_smem_desc_sw128(sB);
+            const uint64_t ndesc0 = ptx::make_smem_desc_sw32(sB);
+            int stage = 0, as = 0;
+            uint32_t phase = 0, aphase = 0, accphase = 0;
+            long long mw_te = 0, mw_f = 0, mt0 = SPHB_CLOCK();
+            const bool no_b = (P.pair_debug & 4) != 0;
+            for (int pt = pair; pt < n_ptiles; pt += n_pairs) {
+                ptx::mbar_wait(bar_afull, aphase);
+                aphase ^= 1;
+                ptx::tc_fence_after();
+                for (int t = 0; t < P.n_dbtiles; ++t) {
+                    const uint32_t tmem_d = tmem_base + as * ACC_COLS;
+                    const bool last_tile = t == P.n_dbtiles - 1;
+#pragma unroll
+                    for (int m = 0; m < MH; ++m) {
+                        long long w0 = SPHB_CLOCK();
+                        ptx::mbar_wait(bar_tempty + 8 * (as * MH + m), accphase ^ 1);
+                        mw_te += SPHB_CLOCK() - w0;
+                        ptx::tc_fence_after();
+#pragma unroll
+                        for (int c = 0; c <= DP64T; ++c) {
+                            int st = stage + c;
+                            uint32_t ph = phase;
+                            if (st >= stages) { st -= stages; ph ^= 1; }
+                            if (m == 0 && !no_b) {
+                                w0 = SPHB_CLOCK();
+                                ptx::mbar_wait(bar_full + 8 * st, ph);
+                                mw_f += SPHB_CLOCK() - w0;
+                                ptx::tc_fence_after();
+                            }
+                            if (ptx::elect_one_sync()) {
+                                if (c < DP64T) {
+                                    const uint64_t bdesc = bdesc0 + static_cast<uint64_t>(st * SLOT_DESC);
+#pragma unroll
+                                    for (int kk = 0; kk < 4; ++kk)
+                                        ptx::umma_f16_pair(tmem_d + m * BN, adesc[m][c < DP64T ? c : 0] + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0 ? 1u : 0u);
+                                } else {
+                                    ptx::umma_f16_pair(tmem_d + m * BN, odesc, ndesc0 + static_cast<uint64_t>(st * SLOT_DESC), idesc, 1u);
+                                }
+                                if (m == MH - 1 && !no_b) ptx::umma_commit_pair(bar_empty + 8 * st, 3);
+                                if (c == DP64T) {
+                                    ptx::umma_commit_pair(bar_tfull + 8 * (as * MH + m), 3);
+                                    if (m == MH - 1 && last_tile) ptx::umma_commit_pair(bar_aempty, 3);
+                                }
+                            }
+                            __syncwarp();
+                        }
+                    }
+                    stage += NB;
+                    if (stage >= stages) { stage -= stages; phase ^= 1; }
+                    if (++as == 2) { as = 0; accphase ^= 1; }
+                }
+            }
+            if (P.prof && lane == 0) {
+                P.prof[blockIdx.x * 16 + 2] = mw_te;
+                P.prof[blockIdx.x * 16 + 3] = mw_f;
+                P.prof[blockIdx.x * 16 + 4] = SPHB_CLOCK() - mt0;
+            }
+        }
+    } else {
+        // ===================== epilogue (each CTA on its own 256 rows / TMEM lanes) =====================
+        const int ew = warp - 2;
+        const int quarter = warp & 3;
+        const int mhalf = ew >> 2;
+        constexpr int cap = 32 * R;
+        const int k = P.k, keep_max = P.keep_max;
+        const BandConsts bc = make_band_consts(P);
+        const uint32_t tempty_l = ptx::mapa(bar_tempty, 0);
+        int as = 0;
+        uint32_t accphase = 0;
+        unsigned long long n_compact = 0, n_accept = 0;
+        const uint32_t n32 = static_cast<uint32_t>(P.n);
+        long long e_cmp = 0, ew_tf = 0, et0 = SPHB_CLOCK();
+        for (int pt = pair; pt < n_ptiles; pt += n_pairs) {
+            const int qt = 2 * pt + static_cast<int>(rank);
+            const int row_in_tile = mhalf * BM + quarter * 32 + lane;
+            const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
+            const bool valid = r < P.nq;
+            uint64_t* warp_buf = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + (row_in_tile - lane)) * cap;
+            uint64_t* mybuf = warp_buf + static_cast<size_t>(lane) * cap;
+            RowList me;
+            init_row(me, P, r, valid);
+            const int dt0 = sweep_start_at(P, static_cast<int64_t>(pt - pair) * (2 * MH * BM), 2 * pair, BN);
+            for (int t = 0; t < P.n_dbtiles; ++t) {
+                const int dt = (dt0 + t) % P.n_dbtiles;
+                const long long w0 = SPHB_CLOCK();
+                ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
+                ew_tf += SPHB_CLOCK() - w0;
+                ptx::tc_fence_after();
+                const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
+#pragma unroll 1
+                for (int c = 0; c < (P.debug_skip_epilogue ? 0 : BN / 32); c += 2) {
+                    float v0[32], v1[32];
+                    ptx::tmem_ld_32x32(taddr + c * 32, v0);
+                    ptx::tmem_ld_32x32(taddr + c * 32 + 32, v1);
+                    ptx::tmem_ld_wait(v0);
+                    ptx::tmem_ld_wait(v1);
+                    filter_pair(v0, v1, jbase + c * 32, n32, me, mybuf, n_accept);
+                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
+                }
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0 && (rank == 0 || !(P.pair_debug & 1))) ptx::mbar_arrive_cluster(tempty_l + 8 * (as * MH + mhalf));
+                if (++as == 2) { as = 0; accphase ^= 1; }
+            }
+            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
+        }
+        if (P.prof && lane == 0) {
+            atomicAdd(P.prof + blockIdx.x * 16 + 5, static_cast<unsigned long long>(ew_tf));
+            atomicAdd(P.prof + blockIdx.x * 16 + 9, static_cast<unsigned long long>(SPHB_CLOCK() - et0));
+            atomicAdd(P.prof + blockIdx.x * 16 + 10, static_cast<unsigned long long>(e_cmp));
+        }
+        if (P.stats) {
+            n_accept = warp_sum(static_cast<double>(n_accept));
+            if (lane == 0) {
+                atomicAdd(P.stats + 0, n_compact);
+                atomicAdd(P.stats + 1, static_cast<unsigned long long>(n_accept));
+            }
+        }
+    }
+
+    ptx::tc_fence_before();
+    ptx::cluster_sync();  // no CTA leaves (or frees TMEM) while its peer can still signal its barriers
+    if (warp == 1) ptx::tmem_dealloc_pair(tmem_base, TMEM_COLS);
 }
 
 // ---------------------------------------------------------------------------
@@ -901,6 +1204,7 @@ struct KnnJob {
     DevBuf<__half> ones;
     bool narrow_norm;
     int64_t sum_compactions = 0, sum_accepted = 0;
+    bool used_pair = false;  // the main sweep ran on the CTA-pair kernel
 };
 
 int build_operands(KnnJob& J, Operands& op, int passes, int MH, const int64_t* d_rowlist, int64_t nlist, bool want_a, bool want_b) {
@@ -958,12 +1262,22 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     const int rows_per_cta = MH ? MH * BM : BM;
     const int n_qtiles = static_cast<int>((nq + rows_per_cta - 1) / rows_per_cta);
     const int n_dbtiles = static_cast<int>(J.np / bn);
-    const int grid = std::min(J.sms, n_qtiles);
+    // CTA-pair kernel (cta_group::2): 1 pass, resident MH = 2, cap 512, d <= 256
+    const bool lean = passes == 1 && MH == 2 && cap == 512 && !getenv("SPHB_KNN_GENERIC_ISSUE");
+    // (opt-in, SPHB_KNN_PAIR=1: it is exact but, with the present epilogue, slower than the single-CTA kernel — the two CTAs'
+    // epilogues gate each other's accumulator stages — see DESIGN.md §4.1)
+    const bool pair = lean && dp / 64 <= 4 && J.narrow_norm && J.sms >= 2 && getenv("SPHB_KNN_PAIR") && !getenv("SPHB_KNN_NO_PAIR");
+    // two epilogue groups (16 epilogue warps, one candidate list per group and row): needs k <= 192 so that the k smallest of
+    // each list survive the cap/2 pruning at export.
+    // (opt-in, SPHB_KNN_TWO_GROUPS=1: exact, but each list sees half the database, so twice the candidates are accepted and
+    // compacted, and at 18 warps the register file allows 96 registers per thread; measured slower than one group)
+    const int G = (lean && !pair && k <= 192 && getenv("SPHB_KNN_TWO_GROUPS")) ? 2 : 1;
+    const int grid = pair ? 2 * std::min(J.sms / 2, (n_qtiles + 1) / 2) : std::min(J.sms, n_qtiles);
 
     DevBuf<uint64_t> cand;
     DevBuf<uint32_t> cand_out;
     DevBuf<int> cnt_out;
-    SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * rows_per_cta * cap, stream));
+    SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * G * rows_per_cta * cap, stream));
     SPHB_CUDA(cand_out.alloc(static_cast<size_t>(nq) * keep_max, stream));
     SPHB_CUDA(cnt_out.alloc(nq, stream));
     SPHB_CUDA(cudaMemsetAsync(J.stats.p, 0, 2 * sizeof(unsigned long long), stream));
@@ -975,6 +1289,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     P.passes = passes;
     P.cand = cand.p; P.cand_out = cand_out.p; P.cnt_out = cnt_out.p; P.stats = J.stats.p;
     P.debug_skip_epilogue = getenv("SPHB_KNN_DEBUG_SKIP_EPI") ? 1 : 0;
+    P.pair_debug = getenv("SPHB_KNN_PAIR_DEBUG") ? atoi(getenv("SPHB_KNN_PAIR_DEBUG")) : 0;
     DevBuf<unsigned long long> prof;
 #ifdef SPHB_KNN_PROFILE
     const bool want_prof = getenv("SPHB_KNN_PROF") != nullptr;
@@ -1022,7 +1337,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
         if (int rc = make_tmap(&tmN, opB.N.p, J.np, opB.ldn, bn, opB.ldn == 16 ? 16 : 64)) return rc;
         const int dp64 = dp / 64;
         const int nA = (passes == 3 ? 2 : 1) * dp64;
-        const size_t fixed = static_cast<size_t>(MH * nA + 1) * CHUNK_BYTES + 256 + 1024;
+        const size_t fixed = static_cast<size_t>(MH * nA + 1) * CHUNK_BYTES + 256 + (G == 2 ? 1024 : 0) + 1024;
         int stages = 8;
         while (stages > 2 && fixed + static_cast<size_t>(stages) * CHUNK_BYTES > smem_limit) --stages;
         const size_t smem = fixed + static_cast<size_t>(stages) * CHUNK_BYTES;
@@ -1037,8 +1352,41 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
         SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<MH_, R_, DP_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
         knn_sweep_resident<MH_, R_, DP_><<<grid, 64 + 128 * MH_, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                              \
     } while (0)
-        const bool lean = passes == 1 && MH == 2 && cap == 512 && !getenv("SPHB_KNN_GENERIC_ISSUE");
-        if (lean && dp64 == 1) SPHB_LAUNCH_RESIDENT(2, 16, 1);
+        if (pair) {
+            if (!d_qrows) J.used_pair = true;
+            CUtensorMap tmB2, tmN2;
+            if (int rc = make_tmap(&tmB2, opB.B.p, J.np, opB.ldb, 64)) return rc;
+            if (int rc = make_tmap(&tmN2, opB.N.p, J.np, opB.ldn, 64, 16)) return rc;
+            const size_t pfixed = static_cast<size_t>(2 * dp64 + 1) * CHUNK_BYTES + 1024 + 1024;
+            int pstages = static_cast<int>((smem_limit - pfixed) / tcp::SLOT_BYTES);
+            pstages = std::min(pstages, 8 * (dp64 + 1));
+            if (pstages < 2 * (dp64 + 1)) return fail(5, "knn: shared memory budget exceeded for the pair kernel");
+            const size_t psmem = pfixed + static_cast<size_t>(pstages) * tcp::SLOT_BYTES;
+            P.stages = pstages;
+            P.half_major = 1;
+            P.norm_bytes = tcp::NORM_BYTES;
+#define SPHB_LAUNCH_PAIR(DP_)                                                                                                            \
+    do {                                                                                                                                 \
+        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_pair<16, DP_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(psmem))); \
+        knn_sweep_pair<16, DP_><<<grid, tcp::NUM_THREADS, psmem, stream>>>(tmA, tmB2, tmN2, tmO, P);                                     \
+    } while (0)
+            if (dp64 == 1) SPHB_LAUNCH_PAIR(1);
+            else if (dp64 == 2) SPHB_LAUNCH_PAIR(2);
+            else if (dp64 == 3) SPHB_LAUNCH_PAIR(3);
+            else SPHB_LAUNCH_PAIR(4);
+#undef SPHB_LAUNCH_PAIR
+        }
+#define SPHB_LAUNCH_RESIDENT2(DP_)                                                                                                                 \
+    do {                                                                                                                                           \
+        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<2, 16, DP_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
+        knn_sweep_resident<2, 16, DP_, 2><<<grid, 64 + 512, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                                      \
+    } while (0)
+        else if (G == 2 && dp64 == 1) SPHB_LAUNCH_RESIDENT2(1);
+        else if (G == 2 && dp64 == 2) SPHB_LAUNCH_RESIDENT2(2);
+        else if (G == 2 && dp64 == 3) SPHB_LAUNCH_RESIDENT2(3);
+        else if (G == 2) SPHB_LAUNCH_RESIDENT2(4);
+#undef SPHB_LAUNCH_RESIDENT2
+        else if (lean && dp64 == 1) SPHB_LAUNCH_RESIDENT(2, 16, 1);
         else if (lean && dp64 == 2) SPHB_LAUNCH_RESIDENT(2, 16, 2);
         else if (lean && dp64 == 3) SPHB_LAUNCH_RESIDENT(2, 16, 3);
         else if (lean && dp64 == 4) SPHB_LAUNCH_RESIDENT(2, 16, 4);
@@ -1256,7 +1604,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     g_knn_ms[3] = fallback_ms;
     const Operands& opm = rows_1pass > 0 ? op1 : op3;
     const int kexec = opm.MH ? ((opm.passes == 3 ? 3 : 1) * dp + 16) : opm.lda;
-    const int64_t st[8] = {1 + opm.MH, J.sum_compactions, J.sum_accepted, kexec, simt_rows, n_qtiles_total, rows_1pass > 0 ? 1 : 3, resweep_rows};
+    const int64_t st[8] = {(J.used_pair && rows_1pass > 0) ? 4 : 1 + opm.MH, J.sum_compactions, J.sum_accepted, kexec, simt_rows, n_qtiles_total, rows_1pass > 0 ? 1 : 3, resweep_rows};
     knn_set_stats(st);
     return 0;
 }

@@ -18,60 +18,116 @@ namespace sphb {
 // ---------------------------------------------------------------------------------------------
 // D3
 // ---------------------------------------------------------------------------------------------
-// One warp per row, rows of at most `cap` entries (cap power of two, shared memory).  top: k largest values, ties won
-// by the lower column (strict admission `back >= value -> reject`, arrival in column order); bottom: k smallest.
-// Values that are not strictly better than the deque's initial sentinel (FLT_MIN for top, FLT_MAX for bottom) are
-// never admitted.  Output column-sorted, fixed stride k, padded 0xFFFFFFFF.
+// One warp per row, rows of at most `cap` entries (cap power of two, shared memory).  The reference feeds the row, in
+// column order, through a fixed-size sorted deque that (i) admits a value only if it is STRICTLY better than the
+// current worst, (ii) places it in front of equal values, (iii) evicts from the back — among equal worst values the
+// one that arrived first.  Closed form of that process (T = the k-th best admissible value, "G" = better than T,
+// "E" = equal to T, subsequence = the G and E entries in column order):
+//   * every G is kept;
+//   * the first k entries of the subsequence are all admitted (the deque is not yet full of >= T values); after that
+//     every E is rejected and every G evicts the oldest E still held;
+//   * so the kept E's are the E's among the first k subsequence entries minus the first (lowest-column) n of them,
+//     n = number of G's beyond subsequence position k.
+// Values not strictly better than the deque's initial sentinel (FLT_MIN for top, FLT_MAX for bottom) are never
+// admitted.  Output column-sorted, fixed stride k, padded 0xFFFFFFFF.
 __global__ void __launch_bounds__(128) find_k_kernel(int64_t n, const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ col,
                                                      const float* __restrict__ val, int k, int top, int cap, uint32_t* __restrict__ out_cols,
                                                      float* __restrict__ out_vals, int32_t* __restrict__ row_nnz, int* __restrict__ err) {
     extern __shared__ uint64_t smem_keys[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
     uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
     const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
     const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
     for (int64_t r = gw; r < n; r += nw) {
         const int64_t b = rowptr[r];
-        const int64_t len = rowptr[r + 1] - b;
+        const int len = static_cast<int>(rowptr[r + 1] - b);
         if (len > cap) {
             if (lane == 0) atomicExch(err, 1);
             continue;
         }
+        auto admissible = [&](float v) { return top ? (v > FLT_MIN) : (v < FLT_MAX); };
+        // order value: ascending = best first
+        int n_adm = 0;
         for (int t = lane; t < cap; t += 32) {
             uint64_t key = ~0ull;
             if (t < len) {
                 const float v = val[b + t];
-                const bool admit = top ? (v > FLT_MIN) : (v < FLT_MAX);
-                if (admit) key = make_key(top ? -v : v, col[b + t]);  // ascending key order = best first, lower column first on ties
+                if (admissible(v)) { key = make_key(top ? -v : v, col[b + t]); ++n_adm; }
             }
             sm[t] = key;
         }
-        __syncwarp();
-        warp_bitonic_sort(sm, cap, lane);
-        // the first min(k, admitted) keys are the selection; re-key by column and sort again
-        int m = 0;
-        for (int t = lane; t < cap; t += 32) m += (t < k && sm[t] != ~0ull) ? 1 : 0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m += __shfl_xor_sync(0xffffffffu, m, o);
-        __syncwarp();
-        for (int t = lane; t < cap; t += 32) {
-            uint64_t key = ~0ull;
-            if (t < m) {
-                const uint64_t kk = sm[t];
-                float v = key_val(kk);
-                if (top) v = -v;
-                key = (static_cast<uint64_t>(key_idx(kk)) << 32) | __float_as_uint(v);
+        for (int o = 16; o > 0; o >>= 1) n_adm += __shfl_xor_sync(0xffffffffu, n_adm, o);
+        bool all = n_adm <= k;
+        float T = 0.f;  // order value of the k-th best
+        int later_g = 0;
+        if (!all) {
+            __syncwarp();
+            warp_bitonic_sort(sm, cap, lane);
+            T = key_val(sm[k - 1]);
+            // G's in total, and G's among the first k entries of the (G or E) subsequence in column order
+            int g = 0;
+            for (int t = lane; t < k; t += 32) g += key_val(sm[t]) < T ? 1 : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) g += __shfl_xor_sync(0xffffffffu, g, o);
+            int seen = 0, g_first = 0;
+            for (int base = 0; base < len && seen < k; base += 32) {
+                const int t = base + lane;
+                bool ge = false, isg = false;
+                if (t < len) {
+                    const float v = val[b + t];
+                    if (admissible(v)) {
+                        const float ov = top ? -v : v;
+                        ge = ov <= T;
+                        isg = ov < T;
+                    }
+                }
+                const unsigned mge = __ballot_sync(0xffffffffu, ge);
+                const int p = seen + __popc(mge & lt_mask) + 1;  // 1-based subsequence position
+                g_first += __popc(__ballot_sync(0xffffffffu, isg && p <= k));
+                seen += __popc(mge);
             }
-            sm[t] = key;
+            later_g = g - g_first;
         }
         __syncwarp();
-        warp_bitonic_sort(sm, cap, lane);
-        for (int t = lane; t < k; t += 32) {
-            const uint64_t key = sm[t];
-            out_cols[r * k + t] = t < m ? static_cast<uint32_t>(key >> 32) : 0xFFFFFFFFu;
-            out_vals[r * k + t] = t < m ? __uint_as_float(static_cast<uint32_t>(key)) : 0.f;
+        // selection pass in column order
+        int seen = 0, e_seen = 0, nout = 0;
+        for (int base = 0; base < len; base += 32) {
+            const int t = base + lane;
+            bool ge = false, isg = false;
+            float v = 0.f;
+            uint32_t c = 0;
+            if (t < len) {
+                v = val[b + t];
+                c = col[b + t];
+                if (admissible(v)) {
+                    const float ov = top ? -v : v;
+                    ge = all || ov <= T;
+                    isg = all || ov < T;
+                }
+            }
+            const unsigned mge = __ballot_sync(0xffffffffu, ge);
+            const int p = seen + __popc(mge & lt_mask) + 1;
+            const bool e_first = ge && !isg && p <= k;
+            const unsigned me = __ballot_sync(0xffffffffu, e_first);
+            const int q = e_seen + __popc(me & lt_mask) + 1;  // 1-based rank among the admitted E's
+            const bool keep = isg || (e_first && q > later_g);
+            const unsigned mk = __ballot_sync(0xffffffffu, keep);
+            if (keep) {
+                const int o = nout + __popc(mk & lt_mask);
+                out_cols[r * k + o] = c;
+                out_vals[r * k + o] = v;
+            }
+            seen += __popc(mge);
+            e_seen += __popc(me);
+            nout += __popc(mk);
         }
-        if (lane == 0) row_nnz[r] = m;
+        for (int t = nout + lane; t < k; t += 32) {
+            out_cols[r * k + t] = 0xFFFFFFFFu;
+            out_vals[r * k + t] = 0.f;
+        }
+        if (lane == 0) row_nnz[r] = nout;
         __syncwarp();
     }
 }

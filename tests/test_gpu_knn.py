@@ -54,10 +54,11 @@ def test_simt_duplicates_and_ties(capi, oracle):
 
 # paths (capi.force_knn_path): 2 auto (1-pass fp16 filter, 3-pass re-sweep of overflow rows), 3 streaming 3-pass,
 # 4 resident MH=1 3-pass, 5 3-pass auto flavour, 6 1-pass, 7 1-pass streaming.
-# flavour (stats["tensor_core"]): 1 streaming, 2 resident MH=1, 3 resident MH=2.
+# flavour (stats["tensor_core"]): 1 streaming, 2 resident MH=1, 3 resident MH=2, 4 CTA pair (cta_group::2).
 @pytest.mark.parametrize("n,d,k,path,flavour,passes", [
     (2048, 32, 16, 2, 3, 1), (4100, 128, 91, 2, 3, 1), (3000, 200, 91, 2, 3, 1), (2500, 21, 5, 2, 3, 1), (2300, 300, 40, 2, 2, 1),
-    (2100, 600, 20, 2, 1, 1), (4100, 128, 91, 6, 3, 1), (2500, 21, 5, 7, 1, 1), (2048, 64, 301, 6, 3, 1),
+    (2100, 600, 20, 2, 1, 1), (4100, 128, 91, 6, 3, 1), (2500, 21, 5, 7, 1, 1), (2048, 64, 301, 6, 3, 1), (70000, 256, 91, 6, 3, 1),
+    (1100, 140, 20, 6, 3, 1), (3000, 100, 192, 6, 3, 1), (3000, 100, 193, 6, 3, 1),
     (4100, 128, 91, 5, 3, 3), (3000, 200, 91, 5, 2, 3), (2300, 300, 40, 5, 1, 3),
     (4100, 128, 91, 3, 1, 3), (2500, 21, 5, 3, 1, 3), (3000, 100, 30, 4, 2, 3), (2048, 64, 301, 5, 3, 3),
 ])
@@ -68,6 +69,26 @@ def test_tc_matches_oracle(capi, oracle, n, d, k, path, flavour, passes):
     st = capi.knn_last_stats()
     assert st["tensor_core"] == flavour
     assert st["passes"] == passes
+
+
+@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (2048, 64, 301), (3000, 200, 91), (1100, 140, 20), (70000, 256, 91)])
+def test_tc_cta_pair_kernel(capi, oracle, n, d, k, monkeypatch):
+    # the cta_group::2 kernel (opt-in, SPHB_KNN_PAIR): two CTAs share every MMA, M = 256
+    monkeypatch.setenv("SPHB_KNN_PAIR", "1")
+    rng = np.random.default_rng(n + d)
+    x = (rng.standard_normal((n, d)) * 0.3 + rng.uniform(0, 1, (1, d))).astype(np.float32)
+    _check(capi, oracle, x, k, path=6)
+    assert capi.knn_last_stats()["tensor_core"] == 4
+
+
+@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (3000, 200, 91), (70000, 256, 91)])
+def test_tc_two_epilogue_groups(capi, oracle, n, d, k, monkeypatch):
+    # opt-in variant of the resident kernel: two epilogue groups (16 warps), two candidate lists per row merged at export
+    monkeypatch.setenv("SPHB_KNN_TWO_GROUPS", "1")
+    rng = np.random.default_rng(n + d)
+    x = (rng.standard_normal((n, d)) * 0.3 + rng.uniform(0, 1, (1, d))).astype(np.float32)
+    _check(capi, oracle, x, k, path=6)
+    assert capi.knn_last_stats()["tensor_core"] == 3
 
 
 @pytest.mark.parametrize("wide", ["0", "1"])
@@ -134,6 +155,19 @@ def test_tc_duplicates(capi, oracle):
     assert st["resweep_rows"] > 0 and st["overflow_rows"] > 0
     _check(capi, oracle, y, 100, path=5)
     assert capi.knn_last_stats()["overflow_rows"] > 0
+
+
+def test_tc_few_overflow_rows_segmented_fallback(capi, oracle):
+    # 2 x 600 identical points inside 7000 ordinary ones: 1200 rows overflow both filters; so few rows go through the
+    # database-segmented SIMT fallback (one warp per (row, segment) + merge)
+    rng = np.random.default_rng(11)
+    x = rng.standard_normal((8200, 24)).astype(np.float32)
+    x[1000:1600] = x[1000]
+    x[5000:5600] = x[5000]
+    _check(capi, oracle, x, 100, path=2)
+    st = capi.knn_last_stats()
+    assert 0 < st["overflow_rows"] <= 2300
+    _check(capi, oracle, x, 100, path=2, metric=0)
 
 
 def test_tc_equals_simt_on_device(capi):

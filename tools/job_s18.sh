@@ -1,0 +1,9 @@
+#!/bin/bash
+timeout 900 python -m pytest tests/test_gpu_knn.py -x -q 2>&1 | tail -6
+run() { echo "== $1"; shift; env "$@" PROBE_ITERS=3 timeout 300 python tools/knn_probe.py 2048 2048 128 91 151552 2>&1 | tail -1 | grep -o "resweep_rows.*"; }
+for rep in 1 2; do
+run "two groups" X=1
+run "one group" SPHB_KNN_ONE_GROUP=1
+done
+prof() { echo "== $1"; shift; env "$@" SPHB_LIB=$PWD/sph_b200/lib/libsphb200_prof.so SPHB_KNN_PROF=1 PROBE_ITERS=2 timeout 300 python tools/knn_probe.py 2048 2048 128 91 151552 2>&1 | grep -E "passes 1" | tail -1 | cut -c1-420; }
+prof "two groups" X=1
