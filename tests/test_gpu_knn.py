@@ -57,7 +57,7 @@ def test_simt_duplicates_and_ties(capi, oracle):
 # flavour (stats["tensor_core"]): 1 streaming, 2 resident MH=1, 3 resident MH=2, 4 CTA pair (cta_group::2).
 @pytest.mark.parametrize("n,d,k,path,flavour,passes", [
     (2048, 32, 16, 2, 3, 1), (4100, 128, 91, 2, 3, 1), (3000, 200, 91, 2, 3, 1), (2500, 21, 5, 2, 3, 1), (2300, 300, 40, 2, 2, 1),
-    (2100, 600, 20, 2, 1, 1), (4100, 128, 91, 6, 3, 1), (2500, 21, 5, 7, 1, 1), (2048, 64, 301, 6, 3, 1), (70000, 256, 91, 6, 3, 1),
+    (2100, 600, 20, 2, 1, 1), (4100, 128, 91, 6, 3, 1), (2500, 21, 5, 7, 1, 1), (2048, 64, 301, 6, 3, 1), (40000, 256, 91, 6, 3, 1),
     (1100, 140, 20, 6, 3, 1), (3000, 100, 192, 6, 3, 1), (3000, 100, 193, 6, 3, 1),
     (4100, 128, 91, 5, 3, 3), (3000, 200, 91, 5, 2, 3), (2300, 300, 40, 5, 1, 3),
     (4100, 128, 91, 3, 1, 3), (2500, 21, 5, 3, 1, 3), (3000, 100, 30, 4, 2, 3), (2048, 64, 301, 5, 3, 3),
@@ -71,7 +71,7 @@ def test_tc_matches_oracle(capi, oracle, n, d, k, path, flavour, passes):
     assert st["passes"] == passes
 
 
-@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (2048, 64, 301), (3000, 200, 91), (1100, 140, 20), (70000, 256, 91)])
+@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (2048, 64, 301), (3000, 200, 91), (1100, 140, 20), (40000, 256, 91)])
 def test_tc_cta_pair_kernel(capi, oracle, n, d, k, monkeypatch):
     # the cta_group::2 kernel (opt-in, SPHB_KNN_PAIR): two CTAs share every MMA, M = 256
     monkeypatch.setenv("SPHB_KNN_PAIR", "1")
@@ -81,7 +81,7 @@ def test_tc_cta_pair_kernel(capi, oracle, n, d, k, monkeypatch):
     assert capi.knn_last_stats()["tensor_core"] == 4
 
 
-@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (3000, 200, 91), (70000, 256, 91)])
+@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (3000, 200, 91), (40000, 256, 91)])
 def test_tc_two_epilogue_groups(capi, oracle, n, d, k, monkeypatch):
     # opt-in variant of the resident kernel: two epilogue groups (16 warps), two candidate lists per row merged at export
     monkeypatch.setenv("SPHB_KNN_TWO_GROUPS", "1")
