@@ -40,6 +40,7 @@ struct RowList {
     float dun;   // passes = 1: |u_i - fp16(u_i)|, rounded up
     int cnt;     // entries currently in the row's scratch list
     int ovf;     // overflow flag
+    int trig;    // compact when cnt exceeds this: min(cap - 64, survivors of the last compaction + BandConsts::step)
 };
 
 // Constants of the band computation, identical for every row of a launch.
@@ -50,6 +51,8 @@ struct BandConsts {
     float dvmax;   // max_j |v_j - fp16(v_j)|, rounded up
     float acc_c;   // accumulation-error coefficient (relative to 2|u||v| + |v|²)
     float sub_c;   // fp16 subnormal floor of a row's rounding-error norm: sqrt(d) * 2^-25
+    int step;      // appends between two compactions of a row (the threshold is stale in between: a short step means
+                   // fewer accepted candidates and cheaper, half-width compactions, but more of them)
 };
 
 // passes = 1.  Error of one computed G_ij against the true value, for |v_j| <= R:
@@ -163,6 +166,7 @@ __device__ __forceinline__ void compact_row_approx(RowList& me, int L, uint64_t*
         me.cnt = m;
         me.thr = limit;
         me.ovf |= ovf;
+        me.trig = min(32 * R - 64, m + bc.step);
     }
     __syncwarp();
 }
@@ -210,8 +214,8 @@ __device__ __forceinline__ void warp_bitonic_sort_regs32(uint32_t (&x)[R], int l
 }
 
 template <int R>
-__device__ __forceinline__ void compact_row_select(RowList& me, int L, uint64_t* __restrict__ buf_L, int k, int keep_max, int lane,
-                                                   const BandConsts& bc) {
+__device__ __forceinline__ void compact_row_select_n(RowList& me, int L, uint64_t* __restrict__ buf_L, int k, int keep_max, int cap, int lane,
+                                                     const BandConsts& bc) {
     const int cntL = __shfl_sync(0xffffffffu, me.cnt, L);
     uint64_t x[R];
     uint32_t v[R];
@@ -255,8 +259,22 @@ __device__ __forceinline__ void compact_row_select(RowList& me, int L, uint64_t*
         me.cnt = m;
         me.thr = limit;
         me.ovf |= ovf;
+        me.trig = min(cap - 64, m + bc.step);
     }
     __syncwarp();
+}
+// lists of at most half the capacity take the half-width network
+template <int R>
+__device__ __forceinline__ void compact_row_select(RowList& me, int L, uint64_t* __restrict__ buf_L, int k, int keep_max, int lane,
+                                                   const BandConsts& bc) {
+    const int cntL = __shfl_sync(0xffffffffu, me.cnt, L);
+    if constexpr (R >= 8) {
+        if (cntL <= 16 * R) {
+            compact_row_select_n<R / 2>(me, L, buf_L, k, keep_max, 32 * R, lane, bc);
+            return;
+        }
+    }
+    compact_row_select_n<R>(me, L, buf_L, k, keep_max, 32 * R, lane, bc);
 }
 
 // Filter one 32-column chunk of the accumulator tile held in v[] (columns jbase..jbase+31).
@@ -336,7 +354,7 @@ template <int R>
 __device__ __forceinline__ void compact_full_rows(RowList& me, uint64_t* __restrict__ warp_buf, int k, int keep_max, int lane,
                                                   const BandConsts& bc, unsigned long long& n_compact, long long& t_compact) {
     constexpr int cap = 32 * R;
-    unsigned full = __ballot_sync(0xffffffffu, me.cnt > cap - 64);  // room for one more filter_pair (<= 64 appends)
+    unsigned full = __ballot_sync(0xffffffffu, me.cnt > me.trig);  // trig <= cap - 64: room for one more filter_pair (<= 64 appends)
     if (full == 0) return;
     const long long c0 = SPHB_CLOCK();
     __syncwarp();  // the owner lanes' list appends must be visible to the whole warp

@@ -65,6 +65,7 @@ struct SweepParams {
     unsigned long long* stats;  // [0] compactions, [1] accepted candidates
     unsigned long long* progress;  // [1] zeroed: sum over CTAs of database tiles loaded (soft lock-step of the sweep, see sweep_pace)
     int pace_window;            // a CTA may run at most this many tiles ahead of the average (0: pacing off)
+    int compact_step;           // BandConsts::step
     int pair_debug;             // debug knobs of the CTA-pair kernel (SPHB_KNN_PAIR_DEBUG bit mask; timing experiments only)
     int debug_skip_epilogue;    // debug: epilogue releases the accumulator without reading it (pure MMA rate)
     unsigned long long* trace;  // optional (profile build): CTA 0, first query tile, database tiles [trace_t0, trace_t0+64): 32 clock stamps per tile
@@ -90,6 +91,7 @@ __device__ __forceinline__ BandConsts make_band_consts(const SweepParams& P) {
     bc.dvmax = P.passes == 1 ? __ldg(P.dvmax) : 0.f;
     bc.acc_c = P.acc_c;
     bc.sub_c = P.sub_c;
+    bc.step = P.compact_step;
     return bc;
 }
 
@@ -136,6 +138,7 @@ __device__ __forceinline__ void init_row(RowList& me, const SweepParams& P, int6
     me.dun = (valid && P.passes == 1) ? P.dun[gi] : 0.f;
     me.cnt = 0;
     me.ovf = 0;
+    me.trig = P.cap - 64;  // the first compaction happens on a full list (no threshold before it)
 }
 
 // First database tile of the sweep of query tile qt.  All CTAs of a wave (query tiles qt - blockIdx.x ...)
@@ -292,7 +295,7 @@ __global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [
 // straight-line code with pre-built descriptors; every hi chunk runs all 4 k-steps, the zero padding of
 // the operands makes that exact); DP64T = 0: generic (runtime chunk count, 1 or 3 passes, partial last chunk).
 template <int MH, int R, int DP64T, int G = 1>
-__global__ void __launch_bounds__(64 + 128 * MH * G) __maxnreg__(G == 2 ? 96 : (MH == 2 ? 168 : 255))
+__global__ void __launch_bounds__(64 + 128 * MH * G, 1)
 knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                    const __grid_constant__ CUtensorMap tmapN, const __grid_constant__ CUtensorMap tmapO, const SweepParams P,
                    const int k16_tail) {
@@ -1330,6 +1333,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     P.debug_skip_epilogue = getenv("SPHB_KNN_DEBUG_SKIP_EPI") ? 1 : 0;
     P.pair_debug = getenv("SPHB_KNN_PAIR_DEBUG") ? atoi(getenv("SPHB_KNN_PAIR_DEBUG")) : 0;
     P.progress = J.stats.p + 2;
+    P.compact_step = getenv("SPHB_KNN_COMPACT_STEP") ? std::max(32, atoi(getenv("SPHB_KNN_COMPACT_STEP"))) : cap;
     P.pace_window = (MH && !pair) ? (getenv("SPHB_KNN_PACE") ? atoi(getenv("SPHB_KNN_PACE")) : 256) : 0;
     DevBuf<unsigned long long> prof;
 #ifdef SPHB_KNN_PROFILE
