@@ -65,6 +65,7 @@ struct SweepParams {
     unsigned long long* stats;  // [0] compactions, [1] accepted candidates
     unsigned long long* progress;  // [1] zeroed: sum over CTAs of database tiles loaded (soft lock-step of the sweep, see sweep_pace)
     int pace_window;            // a CTA may run at most this many tiles ahead of the average (0: pacing off)
+    int l2_prefetch;            // producer prefetches the database tile this many steps ahead into L2 (0: off)
     int compact_step;           // BandConsts::step
     int pair_debug;             // debug knobs of the CTA-pair kernel (SPHB_KNN_PAIR_DEBUG bit mask; timing experiments only)
     int debug_skip_epilogue;    // debug: epilogue releases the accumulator without reading it (pure MMA rate)
@@ -294,8 +295,8 @@ __global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [
 // DP64T > 0: 1-pass specialisation with the chunk count known at compile time (the MMA issue loop is
 // straight-line code with pre-built descriptors; every hi chunk runs all 4 k-steps, the zero padding of
 // the operands makes that exact); DP64T = 0: generic (runtime chunk count, 1 or 3 passes, partial last chunk).
-template <int MH, int R, int DP64T, int G = 1>
-__global__ void __launch_bounds__(64 + 128 * MH * G, 1)
+template <int MH, int R, int DP64T, int G = 1, int H = 0>
+__global__ void __launch_bounds__(64 + 128 * MH * G + 32 * H, 1)
 knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                    const __grid_constant__ CUtensorMap tmapN, const __grid_constant__ CUtensorMap tmapO, const SweepParams P,
                    const int k16_tail) {
@@ -323,6 +324,18 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     const uint32_t bar_aempty = ptx::smem_u32(bars + 2 * stages + 9);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 10);
     int* xch = reinterpret_cast<int*>(bars + 2 * stages + 11);  // G = 2: [MH * BM] list lengths handed from group 1 to group 0 at export
+    // H > 0 (asynchronous compaction, H = MH helper warps): mailboxes between the filter lanes and the helpers
+    uint32_t* xw = reinterpret_cast<uint32_t*>(bars + 2 * stages + 11);
+    volatile uint32_t* hx_ring = xw;                                             // [MH][128] request ring per M half
+    volatile float* hx_thr = reinterpret_cast<volatile float*>(xw + 256);        // [256] threshold published by the helper
+    volatile uint32_t* hx_done = xw + 512;                                       // [256] requests completed per row
+    volatile int* hx_scnt = reinterpret_cast<volatile int*>(xw + 768);           // [256] survivors in S (| OVERFLOW_FLAG)
+    volatile float* hx_un = reinterpret_cast<volatile float*>(xw + 1024);        // [256] row constants for the band
+    volatile float* hx_dun = reinterpret_cast<volatile float*>(xw + 1280);
+    uint32_t* hx_ctl = xw + 1536;                                                // [0..MH) ring tails, [4] finished epilogue warps
+    if constexpr (H > 0) {
+        for (int i = threadIdx.x; i < 1536 + 8; i += blockDim.x) xw[i] = 0;
+    }
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // warps: 0 TMA producer, 1 MMA issuer, 2.. epilogue.  (A second issuer warp, one per M half, was measured: no gain —
@@ -376,9 +389,19 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             aphase ^= 1;
             const int dt0 = sweep_start(P, qt, MH * BM, BN);
             for (int t = 0; t < P.n_dbtiles; ++t) {
-                const int dt = (dt0 + t) % P.n_dbtiles;
+                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
                 if ((t & 15) == 0) sweep_pace(P, pace, lane);
                 ++pace.mine;
+                if (P.l2_prefetch > 0 && t + P.l2_prefetch < P.n_dbtiles) {
+                    // pull the tile this CTA needs l2_prefetch steps from now into L2: a miss then costs nothing on the
+                    // ring's critical path (the ring holds < 3 tiles, less than a DRAM round trip under load)
+                    const int pd = dt + P.l2_prefetch < P.n_dbtiles ? dt + P.l2_prefetch : dt + P.l2_prefetch - P.n_dbtiles;
+                    if (ptx::elect_one_sync()) {
+                        for (int c = 0; c < nB - 1; ++c) ptx::tma_prefetch_2d(&tmapB, c * BK, pd * BN);
+                        ptx::tma_prefetch_2d(&tmapN, 0, pd * BN);
+                    }
+                    __syncwarp();
+                }
                 for (int c = 0; c < nB; ++c) {
                     const long long w0 = SPHB_CLOCK();
                     ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
@@ -578,6 +601,152 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             P.prof[blockIdx.x * 16 + 4] = SPHB_CLOCK() - mt0;
         }
         }
+    } else if (H > 0 && warp >= 2 + 4 * MH * G) {
+        // ===================== compaction helper of M half hw =====================
+        const int hw = warp - (2 + 4 * MH * G);
+        const int k = P.k;
+        const BandConsts bc = make_band_consts(P);
+        uint32_t head = 0;
+        while (true) {
+            uint32_t e = 0;
+            while (true) {
+                e = hx_ring[hw * 128 + (head & 127)];
+                if (e & ASYNC_VALID) break;
+                if (*reinterpret_cast<volatile uint32_t*>(hx_ctl + 4) == 4 * MH * G) {
+                    e = hx_ring[hw * 128 + (head & 127)];  // a request posted before the last warp finished
+                    if (!(e & ASYNC_VALID)) e = 0;
+                    break;
+                }
+                __nanosleep(64);
+            }
+            e = __shfl_sync(0xffffffffu, e, 0);
+            if (e == 0) break;
+            __syncwarp();
+            if (lane == 0) hx_ring[hw * 128 + (head & 127)] = 0;
+            ++head;
+            __threadfence_block();
+            const int row = hw * BM + static_cast<int>((e >> 16) & 127u);
+            const int buf = static_cast<int>((e >> 30) & 1u);
+            const int count = static_cast<int>(e & 0xFFFFu);
+            uint64_t* S = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + row) * ASYNC_STRIDE;
+            const uint64_t* A = S + ASYNC_SC + buf * ASYNC_AC;
+            const int sc = hx_scnt[row] & ~OVERFLOW_FLAG;
+            const int so = hx_scnt[row] & OVERFLOW_FLAG;
+            const float un = hx_un[row], dun = hx_dun[row];
+            float thr_new;
+            int m;
+            if (sc + count <= 256) m = async_compact<8>(S, sc, A, count, k, un, dun, bc, lane, thr_new);
+            else m = async_compact<16>(S, sc, A, count, k, un, dun, bc, lane, thr_new);
+            __threadfence_block();
+            __syncwarp();
+            if (lane == 0) {
+                hx_scnt[row] = m | so;
+                hx_thr[row] = thr_new;
+                __threadfence_block();
+                hx_done[row] = hx_done[row] + 1;
+            }
+            __syncwarp();
+        }
+    } else if (H > 0) {
+        // ===================== epilogue, asynchronous compaction =====================
+        const int ew = warp - 2;
+        const int quarter = warp & 3;
+        const int mhalf = ew >> 2;
+        const int k = P.k, keep_max = P.keep_max;
+        const BandConsts bc = make_band_consts(P);
+        int as = 0;
+        uint32_t accphase = 0;
+        unsigned long long n_compact = 0, n_accept = 0;
+        const uint32_t n32 = static_cast<uint32_t>(P.n);
+        long long ew_tf = 0, e_ld = 0, e_filt = 0, e_exp = 0, e_stall = 0, et0 = SPHB_CLOCK();
+        const int row_in_tile = mhalf * BM + quarter * 32 + lane;
+        uint64_t* rowbase = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + row_in_tile) * ASYNC_STRIDE;
+        uint32_t posted = 0, seen = 0;  // requests posted by / thresholds absorbed from the helper for this lane's row
+        for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+            const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
+            const bool valid = r < P.nq;
+            RowList me;
+            init_row(me, P, r, valid);
+            int cur = 0;
+            uint64_t* mybuf = rowbase + ASYNC_SC;
+            hx_scnt[row_in_tile] = 0;  // no request of this row is in flight here
+            hx_un[row_in_tile] = me.un;
+            hx_dun[row_in_tile] = me.dun;
+            const int dt0 = sweep_start(P, qt, MH * BM, BN);
+            for (int t = 0; t < P.n_dbtiles; ++t) {
+                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
+                long long w0 = SPHB_CLOCK();
+                ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
+                ew_tf += SPHB_CLOCK() - w0;
+                ptx::tc_fence_after();
+                if (seen != posted && hx_done[row_in_tile] == posted) {  // the helper has a tighter threshold for this row
+                    me.thr = fminf(me.thr, hx_thr[row_in_tile]);
+                    seen = posted;
+                }
+                const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
+#pragma unroll 1
+                for (int c = 0; c < (P.debug_skip_epilogue ? 0 : BN / 32); c += 2) {
+                    float v0[32], v1[32];
+                    w0 = SPHB_CLOCK();
+                    ptx::tmem_ld_32x32(taddr + c * 32, v0);
+                    ptx::tmem_ld_32x32(taddr + c * 32 + 32, v1);
+                    ptx::tmem_ld_wait(v0);
+                    ptx::tmem_ld_wait(v1);
+                    const long long w1 = SPHB_CLOCK();
+                    e_ld += w1 - w0;
+                    filter_pair(v0, v1, jbase + c * 32, n32, me, mybuf, n_accept);
+                    if (me.cnt > ASYNC_AC - 64) {  // per lane: hand the buffer to the helper, continue in the other one
+                        const long long s0 = SPHB_CLOCK();
+                        while (hx_done[row_in_tile] != posted) __nanosleep(32);  // previous request of this row still in flight
+                        e_stall += SPHB_CLOCK() - s0;
+                        if (seen != posted) {
+                            me.thr = fminf(me.thr, hx_thr[row_in_tile]);
+                            seen = posted;
+                        }
+                        __threadfence_block();  // the appends are visible to the helper before the request is
+                        const uint32_t slot = atomicAdd(hx_ctl + mhalf, 1u) & 127u;
+                        hx_ring[mhalf * 128 + slot] = ASYNC_VALID | (static_cast<uint32_t>(cur) << 30) |
+                                                      (static_cast<uint32_t>(row_in_tile & 127) << 16) | static_cast<uint32_t>(me.cnt);
+                        ++posted;
+                        cur ^= 1;
+                        me.cnt = 0;
+                        mybuf = rowbase + ASYNC_SC + cur * ASYNC_AC;
+                        ++n_compact;
+                    }
+                    e_filt += SPHB_CLOCK() - w1;
+                }
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * (as * MH + mhalf));
+                if (++as == 2) { as = 0; accphase ^= 1; }
+            }
+            const long long x0 = SPHB_CLOCK();
+            while (hx_done[row_in_tile] != posted) __nanosleep(32);
+            seen = posted;
+            __threadfence_block();
+            export_rows_async<R>(me, cur, hx_scnt + (row_in_tile - lane), r - lane, P.nq, rowbase - static_cast<size_t>(lane) * ASYNC_STRIDE, k, keep_max,
+                                 P.cand_out, P.cnt_out, lane, bc);
+            e_exp += SPHB_CLOCK() - x0;
+        }
+        __syncwarp();
+        if (lane == 0) atomicAdd(hx_ctl + 4, 1u);  // this warp posts no more requests
+        if (P.prof && lane == 0) {
+            atomicAdd(P.prof + blockIdx.x * 16 + 5, static_cast<unsigned long long>(ew_tf));
+            atomicAdd(P.prof + blockIdx.x * 16 + 6, static_cast<unsigned long long>(e_ld));
+            atomicAdd(P.prof + blockIdx.x * 16 + 7, static_cast<unsigned long long>(e_filt));
+            atomicAdd(P.prof + blockIdx.x * 16 + 8, static_cast<unsigned long long>(e_exp));
+            atomicAdd(P.prof + blockIdx.x * 16 + 9, static_cast<unsigned long long>(SPHB_CLOCK() - et0));
+            atomicAdd(P.prof + blockIdx.x * 16 + 10, static_cast<unsigned long long>(e_stall));
+        }
+        if (P.stats) {
+            n_accept = warp_sum(static_cast<double>(n_accept));
+            n_compact = static_cast<unsigned long long>(warp_sum(static_cast<double>(n_compact)));
+            if (lane == 0) {
+                atomicAdd(P.stats + 0, n_compact);
+                atomicAdd(P.stats + 1, static_cast<unsigned long long>(n_accept));
+            }
+        }
     } else {
         // ===================== epilogue =====================
         // G = 2: two groups of 4*MH epilogue warps; group g owns accumulator stage g, i.e. the database tiles t with
@@ -606,7 +775,7 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             init_row(me, P, r, valid);
             const int dt0 = sweep_start(P, qt, MH * BM, BN);
             for (int t = (G == 2 ? grp : 0); t < P.n_dbtiles; t += G) {
-                const int dt = (dt0 + t) % P.n_dbtiles;
+                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
                 long long w0 = SPHB_CLOCK();
                 ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
                 ew_tf += SPHB_CLOCK() - w0;
@@ -798,7 +967,7 @@ knn_sweep_pair(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             aphase ^= 1;
             const int dt0 = sweep_start_at(P, static_cast<int64_t>(pt - pair) * (2 * MH * BM), 2 * pair, BN);
             for (int t = 0; t < P.n_dbtiles; ++t) {
-                const int dt = (dt0 + t) % P.n_dbtiles;
+                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
                 const int32_t brow = dt * BN + static_cast<int32_t>(rank) * 64;
 #pragma unroll
                 for (int c = 0; c < NB; ++c) {
@@ -917,7 +1086,7 @@ knn_sweep_pair(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             init_row(me, P, r, valid);
             const int dt0 = sweep_start_at(P, static_cast<int64_t>(pt - pair) * (2 * MH * BM), 2 * pair, BN);
             for (int t = 0; t < P.n_dbtiles; ++t) {
-                const int dt = (dt0 + t) % P.n_dbtiles;
+                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
                 const long long w0 = SPHB_CLOCK();
                 ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
                 ew_tf += SPHB_CLOCK() - w0;
@@ -1019,7 +1188,7 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                 const int32_t qrow = static_cast<int32_t>(P.a_row0 + static_cast<int64_t>(qt) * BM);
                 const int dt0 = sweep_start(P, qt, BM, BN);
                 for (int t = 0; t < P.n_dbtiles; ++t) {
-                    const int dt = (dt0 + t) % P.n_dbtiles;
+                    const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
                     for (int kc = 0; kc < P.kchunks; ++kc) {
                         ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                         const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -1079,7 +1248,7 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             init_row(me, P, r, valid);
             const int dt0 = sweep_start(P, qt, BM, BN);
             for (int t = 0; t < P.n_dbtiles; ++t) {
-                const int dt = (dt0 + t) % P.n_dbtiles;
+                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
                 ptx::mbar_wait(bar_tfull + 8 * as, accphase);
                 ptx::tc_fence_after();
                 const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
@@ -1314,12 +1483,14 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     // (opt-in, SPHB_KNN_TWO_GROUPS=1: exact, but each list sees half the database, so twice the candidates are accepted and
     // compacted, and at 18 warps the register file allows 96 registers per thread; measured slower than one group)
     const int G = (lean && !pair && k <= 192 && getenv("SPHB_KNN_TWO_GROUPS")) ? 2 : 1;
+    // asynchronous compaction by two helper warps (1-pass lean kernel, k <= 192 so that S holds the k smallest)
+    const bool async = lean && !pair && G == 1 && k <= 192 && getenv("SPHB_KNN_ASYNC") != nullptr;
     const int grid = pair ? 2 * std::min(J.sms / 2, (n_qtiles + 1) / 2) : std::min(J.sms, n_qtiles);
 
     DevBuf<uint64_t> cand;
     DevBuf<uint32_t> cand_out;
     DevBuf<int> cnt_out;
-    SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * G * rows_per_cta * cap, stream));
+    SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * G * rows_per_cta * (async ? ASYNC_STRIDE : cap), stream));
     SPHB_CUDA(cand_out.alloc(static_cast<size_t>(nq) * keep_max, stream));
     SPHB_CUDA(cnt_out.alloc(nq, stream));
     SPHB_CUDA(cudaMemsetAsync(J.stats.p, 0, 3 * sizeof(unsigned long long), stream));
@@ -1333,6 +1504,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     P.debug_skip_epilogue = getenv("SPHB_KNN_DEBUG_SKIP_EPI") ? 1 : 0;
     P.pair_debug = getenv("SPHB_KNN_PAIR_DEBUG") ? atoi(getenv("SPHB_KNN_PAIR_DEBUG")) : 0;
     P.progress = J.stats.p + 2;
+    P.l2_prefetch = getenv("SPHB_KNN_L2PF") ? atoi(getenv("SPHB_KNN_L2PF")) : 0;
     P.compact_step = getenv("SPHB_KNN_COMPACT_STEP") ? std::max(32, atoi(getenv("SPHB_KNN_COMPACT_STEP"))) : cap;
     P.pace_window = (MH && !pair) ? (getenv("SPHB_KNN_PACE") ? atoi(getenv("SPHB_KNN_PACE")) : 256) : 0;
     DevBuf<unsigned long long> prof;
@@ -1382,7 +1554,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
         if (int rc = make_tmap(&tmN, opB.N.p, J.np, opB.ldn, bn, opB.ldn == 16 ? 16 : 64)) return rc;
         const int dp64 = dp / 64;
         const int nA = (passes == 3 ? 2 : 1) * dp64;
-        const size_t fixed = static_cast<size_t>(MH * nA + 1) * CHUNK_BYTES + 256 + (G == 2 ? 1024 : 0) + 1024;
+        const size_t fixed = static_cast<size_t>(MH * nA + 1) * CHUNK_BYTES + 256 + (G == 2 ? 1024 : 0) + (async ? 6400 : 0) + 1024;
         int stages = 8;
         while (stages > 2 && fixed + static_cast<size_t>(stages) * CHUNK_BYTES > smem_limit) --stages;
         const size_t smem = fixed + static_cast<size_t>(stages) * CHUNK_BYTES;
@@ -1426,6 +1598,16 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
         SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<2, 16, DP_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
         knn_sweep_resident<2, 16, DP_, 2><<<grid, 64 + 512, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                                      \
     } while (0)
+#define SPHB_LAUNCH_ASYNC(DP_)                                                                                                                       \
+    do {                                                                                                                                             \
+        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<2, 16, DP_, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
+        knn_sweep_resident<2, 16, DP_, 1, 2><<<grid, 64 + 256 + 64, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                                \
+    } while (0)
+        else if (async && dp64 == 1) SPHB_LAUNCH_ASYNC(1);
+        else if (async && dp64 == 2) SPHB_LAUNCH_ASYNC(2);
+        else if (async && dp64 == 3) SPHB_LAUNCH_ASYNC(3);
+        else if (async) SPHB_LAUNCH_ASYNC(4);
+#undef SPHB_LAUNCH_ASYNC
         else if (G == 2 && dp64 == 1) SPHB_LAUNCH_RESIDENT2(1);
         else if (G == 2 && dp64 == 2) SPHB_LAUNCH_RESIDENT2(2);
         else if (G == 2 && dp64 == 3) SPHB_LAUNCH_RESIDENT2(3);

@@ -91,6 +91,16 @@ def test_tc_two_epilogue_groups(capi, oracle, n, d, k, monkeypatch):
     assert capi.knn_last_stats()["tensor_core"] == 3
 
 
+@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (3000, 200, 91), (1100, 140, 20), (40000, 256, 91), (2048, 32, 192)])
+def test_tc_async_compaction(capi, oracle, n, d, k, monkeypatch):
+    # variant of the resident kernel whose list compactions run on two helper warps (SPHB_KNN_ASYNC)
+    monkeypatch.setenv("SPHB_KNN_ASYNC", "1")
+    rng = np.random.default_rng(n + d)
+    x = (rng.standard_normal((n, d)) * 0.3 + rng.uniform(0, 1, (1, d))).astype(np.float32)
+    _check(capi, oracle, x, k, path=6)
+    assert capi.knn_last_stats()["tensor_core"] == 3
+
+
 @pytest.mark.parametrize("wide", ["0", "1"])
 def test_tc_norm_chunk_layouts(capi, oracle, wide, monkeypatch):
     # the |v|² chunk is a narrow (16-column, SWIZZLE_32B) or wide (64-column, SWIZZLE_128B) tile
