@@ -305,7 +305,8 @@ def main():
     prow_bytes = nq * (k * 12 + (k - 1) * 8)
     graph_pass = {"kernel": "prow_graph_kernel (perplexity rows, warp per row)", "bound": "hbm", "achieved": prow_bytes / (prow_ms * 1e-3) / 1e9,
                   "peak": peaks["hbm"], "unit": "GB/s", "frac": prow_bytes / (prow_ms * 1e-3) / 1e9 / peaks["hbm"], "kernel_ms": prow_ms,
-                  "algorithmic_bytes_per_launch": prow_bytes}
+                  "algorithmic_bytes_per_launch": prow_bytes,
+                  "note": "reported against the HBM peak; the kernel is FP64-exp bound (about 20 bisection steps x k fp64 exp per row), DESIGN.md 4.2"}
 
     # end to end through the host-buffer C ABI (pinned host memory; H2D + D2H inside the timed region)
     xh = torch.from_numpy(x).pin_memory()

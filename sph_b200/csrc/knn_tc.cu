@@ -1464,7 +1464,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
                      int64_t* d_ids, float* d_dist, int64_t* d_ovf_rows, int* d_ovf_count, int* n_ovf, float* sweep_ms, float* rerank_ms) {
     using namespace tc;
     cudaStream_t stream = J.stream;
-    const int passes = opB.passes, MH = opB.MH, d = J.d, k = J.k, dp = J.dp;
+    const int passes = opB.passes, MH = opA.MH, d = J.d, k = J.k, dp = J.dp;  // opA.MH: rows per CTA (the B layout is the same for MH 1 and 2)
     const int64_t nq = qb - qa;
     if (nq <= 0) { *n_ovf = 0; return 0; }
     const int cap = passes == 1 ? std::max(512, next_pow2_i(k + 160)) : std::max(256, next_pow2_i(k + 96));
@@ -1813,8 +1813,10 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         EventTimer tf;
         tf.start(stream);
         if (int rc = ensure_full(op3, 3)) return rc;
+        // few rows: 128-row query tiles (MH = 1) put twice as many CTAs to work, each with half the MMA work per database tile
+        const int mh_re = (op3.MH == 2 && (pending1 + BM - 1) / BM <= J.sms) ? 1 : op3.MH;
         Operands sub;
-        if (int rc = build_operands(J, sub, 3, op3.MH, ovf_rows.p, pending1, true, false)) return rc;
+        if (int rc = build_operands(J, sub, 3, mh_re, ovf_rows.p, pending1, true, false)) return rc;
         DevBuf<int> ovf2_count;
         DevBuf<int64_t> ovf2_rows;
         SPHB_CUDA(ovf2_count.alloc(1, stream));
