@@ -24,6 +24,7 @@
 
 #include <cuda_fp16.h>
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <vector>
@@ -1812,7 +1813,14 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         if (pending1 == 0) return 0;
         EventTimer tf;
         tf.start(stream);
+        const bool dbg = getenv("SPHB_KNN_TIMING") != nullptr;
+        auto now = [&]() { if (dbg) cudaStreamSynchronize(stream); return std::chrono::steady_clock::now(); };
+        auto ms_since = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+            return std::chrono::duration<double, std::milli>(b - a).count();
+        };
+        const auto t0 = now();
         if (int rc = ensure_full(op3, 3)) return rc;
+        const auto t1 = now();
         // few rows: 128-row query tiles (MH = 1) put twice as many CTAs to work, each with half the MMA work per database tile
         const int mh_re = (op3.MH == 2 && (pending1 + BM - 1) / BM <= J.sms) ? 1 : op3.MH;
         Operands sub;
@@ -1824,9 +1832,14 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         SPHB_CUDA(cudaMemsetAsync(ovf2_count.p, 0, sizeof(int), stream));
         float sm = 0.f, rm = 0.f;
         int hovf2 = 0;
+        const auto t2 = now();
         if (int rc = sweep_and_rerank(J, sub, op3, 0, pending1, ovf_rows.p, q0, d_ids, d_dist, ovf2_rows.p, ovf2_count.p, &hovf2, &sm, &rm)) return rc;
+        const auto t3 = now();
         resweep_rows += pending1;
         if (int rc = simt_rows_exact(ovf2_rows.p, ovf2_count.p, hovf2)) return rc;
+        if (dbg)
+            fprintf(stderr, "[knn timing] re-sweep of %d rows: 3-pass operands %.1f ms, gathered A %.1f ms, sweep+rerank %.1f ms (kernel %.1f + %.1f), simt %.1f ms\n",
+                    pending1, ms_since(t0, t1), ms_since(t1, t2), ms_since(t2, t3), sm, rm, ms_since(t3, now()));
         tf.stop(stream);
         fallback_ms += tf.ms();
         pending1 = 0;
