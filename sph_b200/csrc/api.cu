@@ -4,6 +4,7 @@
 
 #include <atomic>
 #include <mutex>
+#include <vector>
 #include <algorithm>
 
 namespace sphb {
@@ -23,6 +24,71 @@ void count_launch(int64_t n) { g_launches += n; }
 int ensure_init() {
     if (g_ctx.ready) return 0;
     return sphb_init(-1);
+}
+
+// ---- workspace cache (see common.cuh) -----------------------------------------------------------
+namespace {
+struct WsBlock {
+    void* p;
+    size_t bytes;
+    cudaStream_t stream;
+};
+std::mutex g_ws_mu;
+std::vector<WsBlock> g_ws_free;                     // idle blocks
+std::vector<WsBlock> g_ws_live;                     // blocks handed out (to find their size at release)
+size_t g_ws_idle_bytes = 0;
+constexpr size_t WS_IDLE_CAP = 64ull << 30;
+}  // namespace
+
+cudaError_t ws_alloc(void** p, size_t bytes, cudaStream_t stream) {
+    if (bytes == 0) { *p = nullptr; return cudaSuccess; }
+    {
+        std::lock_guard<std::mutex> lk(g_ws_mu);
+        int best = -1;
+        for (int i = 0; i < static_cast<int>(g_ws_free.size()); ++i) {
+            const WsBlock& b = g_ws_free[i];
+            if (b.stream != stream || b.bytes < bytes || b.bytes > bytes + bytes / 4 + (1u << 20)) continue;
+            if (best < 0 || b.bytes < g_ws_free[best].bytes) best = i;
+        }
+        if (best >= 0) {
+            WsBlock b = g_ws_free[best];
+            g_ws_free.erase(g_ws_free.begin() + best);
+            g_ws_idle_bytes -= b.bytes;
+            g_ws_live.push_back(b);
+            *p = b.p;
+            return cudaSuccess;
+        }
+    }
+    const cudaError_t e = cudaMallocAsync(p, bytes, stream);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lk(g_ws_mu);
+    g_ws_live.push_back({*p, bytes, stream});
+    return cudaSuccess;
+}
+
+void ws_free(void* p, cudaStream_t stream) {
+    if (!p) return;
+    std::lock_guard<std::mutex> lk(g_ws_mu);
+    for (size_t i = 0; i < g_ws_live.size(); ++i) {
+        if (g_ws_live[i].p != p) continue;
+        WsBlock b = g_ws_live[i];
+        g_ws_live.erase(g_ws_live.begin() + static_cast<long>(i));
+        if (b.stream == stream && g_ws_idle_bytes + b.bytes <= WS_IDLE_CAP) {
+            g_ws_free.push_back(b);
+            g_ws_idle_bytes += b.bytes;
+        } else {
+            cudaFreeAsync(p, stream);
+        }
+        return;
+    }
+    cudaFreeAsync(p, stream);  // not ours (should not happen)
+}
+
+void ws_trim() {
+    std::lock_guard<std::mutex> lk(g_ws_mu);
+    for (const WsBlock& b : g_ws_free) cudaFreeAsync(b.p, b.stream);
+    g_ws_free.clear();
+    g_ws_idle_bytes = 0;
 }
 
 // kernels / launchers implemented in the other translation units
@@ -62,7 +128,10 @@ SPHB_API int sphb_init(int device) {
     cudaDeviceProp prop;
     SPHB_CUDA(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) return fail(SPHB_ERR_UNSUPPORTED, std::string("sm_100a build, found ") + prop.name);
-    if (g_ctx.stream) cudaStreamDestroy(g_ctx.stream);
+    if (g_ctx.stream) {
+        sphb::ws_trim();  // cached blocks are tied to the stream they were released on
+        cudaStreamDestroy(g_ctx.stream);
+    }
     SPHB_CUDA(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
     // keep freed stream-ordered allocations cached in the pool between calls
     cudaMemPool_t pool;
@@ -79,6 +148,7 @@ SPHB_API int sphb_init(int device) {
 SPHB_API void sphb_shutdown(void) {
     if (!g_ctx.ready) return;
     cudaStreamSynchronize(g_ctx.stream);
+    sphb::ws_trim();
     cudaStreamDestroy(g_ctx.stream);
     g_ctx.stream = nullptr;
     cudaMemPool_t pool;

@@ -28,6 +28,14 @@ int ensure_init();
         }                                                                                          \
     } while (0)
 
+// Workspace cache (api.cu): device blocks released by the library are kept per stream and handed out again for
+// requests of a similar size on the same stream (stream order makes the reuse safe).  A call of the kNN path makes
+// ~20 stream-ordered allocations of up to several GB; going to cudaMallocAsync for each of them showed sporadic
+// stalls of 0.1-2 s (pool growth / remapping) between kernels.  Trimmed by sphb_shutdown and when more than 64 GB idle.
+cudaError_t ws_alloc(void** p, size_t bytes, cudaStream_t stream);
+void ws_free(void* p, cudaStream_t stream);
+void ws_trim();
+
 // RAII stream-ordered device buffer.
 template <class T>
 struct DevBuf {
@@ -42,10 +50,10 @@ struct DevBuf {
         s = stream;
         n = count;
         if (count == 0) return cudaSuccess;
-        return cudaMallocAsync(reinterpret_cast<void**>(&p), count * sizeof(T), stream);
+        return ws_alloc(reinterpret_cast<void**>(&p), count * sizeof(T), stream);
     }
     void release() {
-        if (p) cudaFreeAsync(p, s);
+        if (p) ws_free(p, s);
         p = nullptr;
     }
     ~DevBuf() { release(); }
