@@ -219,6 +219,9 @@ def main():
     if world > 1:
         import torch.distributed as dist
 
+        # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION) off it
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     capi.init(local_rank)
 
@@ -331,6 +334,9 @@ def main():
     d2h = n * (k * 12 + (k - 1) * 8)
     checksum = int(out_np[0][:, 1].sum() % (1 << 31))
 
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
 
