@@ -13,6 +13,8 @@ Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for every field.
 from __future__ import annotations
 
 import argparse
+import contextlib
+import ctypes
 import json
 import os
 import subprocess
@@ -152,6 +154,23 @@ def level1_p_wall_time(capi, synth):
             "walk_nnz": int(wrp[-1]), "merged_nnz": int(mrp[-1]), "p_nnz": int(orp[-1])}
 
 
+@contextlib.contextmanager
+def stdout_to_stderr():
+    """Route file descriptor 1 (Python's and the C library's stdout) to stderr inside the block."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        yield
+    finally:
+        try:
+            sys.stdout.flush()
+            ctypes.CDLL(None).fflush(None)
+        finally:
+            os.dup2(saved, 1)
+            os.close(saved)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -219,10 +238,12 @@ def main():
     if world > 1:
         import torch.distributed as dist
 
-        # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION) off it
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # stdout carries exactly one JSON line: NCCL prints its "NCCL version ..." banner on stdout when the communicator is
+        # created (NCCL_DEBUG=VERSION/WARN), so file descriptor 1 points at stderr until the first collective is through
+        with stdout_to_stderr():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
     capi.init(local_rank)
 
     x = synth.hyperspectral(h, w, d, endmembers=M, seed=seed)

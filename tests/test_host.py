@@ -121,3 +121,21 @@ def test_sharded_knn_world2_gloo(tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert r.stdout.count("ok") == 2
+
+
+def test_bench_stdout_guard(tmp_path):
+    # bench.py keeps its stdout to ONE JSON line: while NCCL creates its communicator, fd 1 points at stderr
+    code = (
+        "import ctypes, sys, bench\n"
+        "with bench.stdout_to_stderr():\n"
+        "    ctypes.CDLL(None).puts(b'banner from C')\n"
+        "    print('banner from python')\n"
+        "print('{\"ok\": 1}')\n"
+    )
+    import subprocess
+    import sys
+
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=str(ROOT), timeout=120)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout.strip() == '{"ok": 1}'
+    assert "banner from C" in r.stderr and "banner from python" in r.stderr
