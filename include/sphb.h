@@ -178,6 +178,53 @@ SPHB_API int sphb_find_k(int64_t n, const int64_t* rowptr, const uint32_t* col, 
 SPHB_API int sphb_neighbor_overlap(const int64_t* knn_ids, int64_t n, int k, int64_t ncomp, const int64_t* comp_ptr,
                                    const int64_t* comp_pix, const int64_t* pa, const int64_t* pb, int64_t npairs, float* out);
 
+/* ---- ragged-graph passes next to the kNN search and between levels -------- */
+/*
+ * A graph crosses the boundary as utils::Graph stores it (sph/utils/Graph.hpp:155-273): rowptr int64[n+1]
+ * (offsets + total), ids int64[nnz] (knnIndices), dist float[nnz] (knnDistances).  rowptr == NULL means a
+ * fixed-k graph (Graph::updateFixedNumNeighbors): row r is [r*k, (r+1)*k).
+ *
+ * Replaces utils::symmetrizeGraph (sph/utils/GraphUtils.cpp:197-317), the step NearestNeighbors::compute runs
+ * right after the search when symmetricNeighbors = true (sph/NearestNeighbors.cpp:176-183): for every stored
+ * (i, j) or (j, i) both rows get the entry, distance min(d_ij, d_ji) where both exist (first stored occurrence of
+ * each), rows ordered by (distance, index), then ensureClosestPointIsSelf (sph/utils/GraphUtils.cpp:23-95).
+ * Output capacity `cap` entries (2*nnz always suffices); *out_nnz receives the size.
+ */
+SPHB_API int sphb_symmetrize_graph(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist,
+                                   int64_t* out_rowptr, int64_t* out_ids, float* out_dist, int64_t cap, int64_t* out_nnz);
+/* utils::mergeGraphNodes (sph/utils/SparseMatrixAlgorithms.cpp:486-561): node r merges into parents[r]; the
+ * distance of (parent(r), parent(c)) is the minimum over the children; rows ordered by (distance, index), self first.
+ * cap: nnz of the input always suffices. */
+SPHB_API int sphb_merge_graph_nodes(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist,
+                                    const uint64_t* parents, int64_t n_merged,
+                                    int64_t* out_rowptr, int64_t* out_ids, float* out_dist, int64_t cap, int64_t* out_nnz);
+/* utils::mergeNodesDataDistances (sph/utils/SparseMatrixAlgorithms.cpp:443-484), the sparse-row form of the same
+ * merge: a stored or missing 0 counts as empty and is replaced by the next value, otherwise the smaller value stays. */
+SPHB_API int sphb_merge_data_distances(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                                       const uint64_t* parents, int64_t n_merged,
+                                       int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t cap, int64_t* out_nnz);
+/* useRandomWalksAsKnnDistances (sph/LevelSimilarities.cpp:346-389): every non-zero random-walk entry becomes a
+ * neighbour at distance 1 - value; rows stable-sorted by distance (ties keep column order).  out_ids/out_dist: nnz. */
+SPHB_API int sphb_rw_as_knn_distances(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                                      int64_t* out_rowptr, int64_t* out_ids, float* out_dist, int64_t* out_nnz);
+/* Zero removal of the level rows (sph/LevelSimilarities.cpp:566-581).  out_col/out_val: nnz. */
+SPHB_API int sphb_remove_zeros(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                               int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t* out_nnz);
+/* Exact level kNN in a random-walk component metric — LevelSimilarities' computeExactKnn
+ * (sph/LevelSimilarities.cpp:211-252) with NeighborWalksBhattacharyyaSpace (mode 0) or
+ * NeighborWalksSingleOverlapSpace (mode 1): distance = componentDistance = 0 if i == j else 1 - sim
+ * (sph/utils/Similarities.cpp:123-156, 374-396).  val is the level's random-walk matrix (n x n CSR).
+ * out: n*k, each row ordered by (distance, index); slots beyond n keep -1 / -1.0f. */
+SPHB_API int sphb_level_knn_walks(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int mode, int64_t k,
+                                  int64_t* out_ids, float* out_dist);
+/* Batched utils::euclidDistance (sph/utils/Similarities.cpp:414-483): symmetric Hausdorff distance
+ * (sph/utils/Math.cpp:167-172) of the all-pairs L2 matrix between the pixels of components pa[p] and pb[p]
+ * (comp_pix[comp_ptr[c] .. comp_ptr[c+1]), as Hierarchy::getRepresentedDataPoints lists them; single-pixel
+ * components give the level-0 branch).  The reference sub-samples components larger than numGeodesicSamples with an
+ * unseeded random_device (:455-474); the caller passes the sampled lists in that case. */
+SPHB_API int sphb_euclid_hausdorff(const float* x, int64_t n, int d, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix,
+                                   const int64_t* pa, const int64_t* pb, int64_t npairs, float* out);
+
 #ifdef __cplusplus
 }
 #endif

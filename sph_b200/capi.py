@@ -56,6 +56,13 @@ SIGNATURES = {
     "sphb_pair_sims": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, i64p, C.c_int64, C.c_int, f32p]),
     "sphb_find_k": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_int, u32p, f32p, i32p]),
     "sphb_neighbor_overlap": (C.c_int, [i64p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
+    "sphb_symmetrize_graph": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, i64p, f32p, C.c_int64, i64p]),
+    "sphb_merge_graph_nodes": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, u64p, C.c_int64, i64p, i64p, f32p, C.c_int64, i64p]),
+    "sphb_merge_data_distances": (C.c_int, [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, i64p, u32p, f32p, C.c_int64, i64p]),
+    "sphb_rw_as_knn_distances": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, i64p, f32p, i64p]),
+    "sphb_remove_zeros": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, u32p, f32p, i64p]),
+    "sphb_level_knn_walks": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int64, i64p, f32p]),
+    "sphb_euclid_hausdorff": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
 }
 
 
@@ -301,4 +308,117 @@ def neighbor_overlap(knn_ids, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
     n, k = knn_ids.shape
     _check(load().sphb_neighbor_overlap(_p(knn_ids, i64p), n, k, len(comp_ptr) - 1, _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p),
                                         _p(pb, i64p), len(pa), _p(out, f32p)))
+    return out
+
+
+# ------------------------------------------------------------------ ragged-graph passes
+def _graph_args(rowptr, ids, dist):
+    """(n, rowptr or None, k, ids, dist): a 2-D ids array is a fixed-k graph, otherwise rowptr gives the rows."""
+    ids = np.ascontiguousarray(ids, np.int64)
+    dist = np.ascontiguousarray(dist, np.float32)
+    if rowptr is None:
+        n, k = ids.shape
+        return n, None, k, ids, dist
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    return len(rowptr) - 1, rowptr, 0, ids, dist
+
+
+def symmetrize_graph(ids, dist, rowptr=None):
+    """utils::symmetrizeGraph: returns (rowptr, ids, dist) of the ragged symmetric graph."""
+    n, rp, k, ids, dist = _graph_args(rowptr, ids, dist)
+    cap = max(1, 2 * ids.size)
+    orp = np.zeros(n + 1, np.int64)
+    oi = np.zeros(cap, np.int64)
+    od = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_symmetrize_graph(n, _p(rp, i64p) if rp is not None else None, k, _p(ids, i64p), _p(dist, f32p), _p(orp, i64p), _p(oi, i64p),
+                                        _p(od, f32p), cap, _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oi[:m].copy(), od[:m].copy()
+
+
+def merge_graph_nodes(ids, dist, parents, n_merged: int, rowptr=None):
+    """utils::mergeGraphNodes: returns (rowptr, ids, dist) of the merged graph."""
+    n, rp, k, ids, dist = _graph_args(rowptr, ids, dist)
+    parents = np.ascontiguousarray(parents, np.uint64)
+    cap = max(1, ids.size)
+    orp = np.zeros(n_merged + 1, np.int64)
+    oi = np.zeros(cap, np.int64)
+    od = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_merge_graph_nodes(n, _p(rp, i64p) if rp is not None else None, k, _p(ids, i64p), _p(dist, f32p), _p(parents, u64p), n_merged,
+                                         _p(orp, i64p), _p(oi, i64p), _p(od, f32p), cap, _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oi[:m].copy(), od[:m].copy()
+
+
+def merge_data_distances(rowptr, col, val, parents, n_merged: int):
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    parents = np.ascontiguousarray(parents, np.uint64)
+    n = len(rowptr) - 1
+    cap = max(1, len(col))
+    orp = np.zeros(n_merged + 1, np.int64)
+    oc = np.zeros(cap, np.uint32)
+    ov = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_merge_data_distances(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(parents, u64p), n_merged, _p(orp, i64p),
+                                            _p(oc, u32p), _p(ov, f32p), cap, _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oc[:m].copy(), ov[:m].copy()
+
+
+def rw_as_knn_distances(rowptr, col, val):
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    cap = max(1, len(col))
+    orp = np.zeros(n + 1, np.int64)
+    oi = np.zeros(cap, np.int64)
+    od = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_rw_as_knn_distances(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(orp, i64p), _p(oi, i64p), _p(od, f32p), _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oi[:m].copy(), od[:m].copy()
+
+
+def remove_zeros(rowptr, col, val):
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    cap = max(1, len(col))
+    orp = np.zeros(n + 1, np.int64)
+    oc = np.zeros(cap, np.uint32)
+    ov = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_remove_zeros(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(orp, i64p), _p(oc, u32p), _p(ov, f32p), _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oc[:m].copy(), ov[:m].copy()
+
+
+def level_knn_walks(rowptr, col, val, k: int, mode: int = 0):
+    """Exact level kNN in the random-walk metric (mode 0 Bhattacharyya, 1 single overlap): (ids [n,k], dist [n,k])."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    ids = np.full((n, k), -1, np.int64)
+    dist = np.full((n, k), -1.0, np.float32)
+    _check(load().sphb_level_knn_walks(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), mode, k, _p(ids, i64p), _p(dist, f32p)))
+    return ids, dist
+
+
+def euclid_hausdorff(x, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
+    x = np.ascontiguousarray(x, np.float32)
+    comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+    comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+    pa = np.ascontiguousarray(pa, np.int64)
+    pb = np.ascontiguousarray(pb, np.int64)
+    out = np.zeros(len(pa), np.float32)
+    n, d = x.shape
+    _check(load().sphb_euclid_hausdorff(_p(x, f32p), n, d, len(comp_ptr) - 1, _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p),
+                                        len(pa), _p(out, f32p)))
     return out

@@ -67,6 +67,18 @@ class Oracle:
         L.orc_find_k.argtypes = [u32p, f32p, C.c_int, C.c_int, C.c_int, u32p, f32p]
         L.orc_pair_sims.argtypes = [C.c_int64, i64p, u32p, f32p, i64p, i64p, C.c_int64, C.c_int, f32p]
         L.orc_neighbor_overlap.argtypes = [i64p, C.c_int, i64p, i64p, i64p, i64p, C.c_int64, f32p]
+        L.orc_symmetrize_graph.argtypes = [C.c_int64, i64p, i64p, f32p, i64p, i64p, f32p, C.c_int64]
+        L.orc_symmetrize_graph.restype = C.c_int64
+        L.orc_merge_graph_nodes.argtypes = [C.c_int64, i64p, i64p, f32p, u64p, C.c_int64, i64p, i64p, f32p, C.c_int64]
+        L.orc_merge_graph_nodes.restype = C.c_int64
+        L.orc_merge_data_distances.argtypes = [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, i64p, u32p, f32p, C.c_int64]
+        L.orc_merge_data_distances.restype = C.c_int64
+        L.orc_rw_as_knn_distances.argtypes = [C.c_int64, i64p, u32p, f32p, i64p, i64p, f32p, C.c_int64]
+        L.orc_rw_as_knn_distances.restype = C.c_int64
+        L.orc_remove_zeros.argtypes = [C.c_int64, i64p, u32p, f32p, i64p, u32p, f32p]
+        L.orc_remove_zeros.restype = C.c_int64
+        L.orc_euclid_hausdorff.argtypes = [f32p, C.c_int, i64p, i64p, i64p, i64p, C.c_int64, f32p]
+        L.orc_level_knn_walks.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int64, i64p, f32p]
 
     # ---- Stage A
     def knn_exact(self, x, k, metric=1, rows=None):
@@ -259,6 +271,101 @@ class Oracle:
         out = np.zeros(len(pa), np.float32)
         self.lib.orc_neighbor_overlap(_p(knn_ids, i64p), knn_ids.shape[1], _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p))
         return out
+
+
+    # ---- ragged-graph passes
+    @staticmethod
+    def _graph(ids, dist, rowptr):
+        ids = np.ascontiguousarray(ids, np.int64)
+        dist = np.ascontiguousarray(dist, np.float32)
+        if rowptr is None:
+            n, k = ids.shape
+            rowptr = np.arange(n + 1, dtype=np.int64) * k
+        return np.ascontiguousarray(rowptr, np.int64), ids.reshape(-1), dist.reshape(-1)
+
+    def symmetrize_graph(self, ids, dist, rowptr=None):
+        rowptr, ids, dist = self._graph(ids, dist, rowptr)
+        n = len(rowptr) - 1
+        cap = max(1, 2 * len(ids))
+        orp = np.zeros(n + 1, np.int64)
+        oi = np.zeros(cap, np.int64)
+        od = np.zeros(cap, np.float32)
+        m = self.lib.orc_symmetrize_graph(n, _p(rowptr, i64p), _p(ids, i64p), _p(dist, f32p), _p(orp, i64p), _p(oi, i64p), _p(od, f32p), cap)
+        assert m >= 0
+        return orp, oi[:m].copy(), od[:m].copy()
+
+    def merge_graph_nodes(self, ids, dist, parents, n_merged, rowptr=None):
+        rowptr, ids, dist = self._graph(ids, dist, rowptr)
+        parents = np.ascontiguousarray(parents, np.uint64)
+        n = len(rowptr) - 1
+        cap = max(1, len(ids))
+        orp = np.zeros(n_merged + 1, np.int64)
+        oi = np.zeros(cap, np.int64)
+        od = np.zeros(cap, np.float32)
+        m = self.lib.orc_merge_graph_nodes(n, _p(rowptr, i64p), _p(ids, i64p), _p(dist, f32p), _p(parents, u64p), n_merged, _p(orp, i64p),
+                                           _p(oi, i64p), _p(od, f32p), cap)
+        assert m >= 0
+        return orp, oi[:m].copy(), od[:m].copy()
+
+    def merge_data_distances(self, rowptr, col, val, parents, n_merged):
+        rowptr = np.ascontiguousarray(rowptr, np.int64)
+        col = np.ascontiguousarray(col, np.uint32)
+        val = np.ascontiguousarray(val, np.float32)
+        parents = np.ascontiguousarray(parents, np.uint64)
+        n = len(rowptr) - 1
+        cap = max(1, len(col))
+        orp = np.zeros(n_merged + 1, np.int64)
+        oc = np.zeros(cap, np.uint32)
+        ov = np.zeros(cap, np.float32)
+        m = self.lib.orc_merge_data_distances(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(parents, u64p), n_merged, _p(orp, i64p),
+                                              _p(oc, u32p), _p(ov, f32p), cap)
+        assert m >= 0
+        return orp, oc[:m].copy(), ov[:m].copy()
+
+    def rw_as_knn_distances(self, rowptr, col, val):
+        rowptr = np.ascontiguousarray(rowptr, np.int64)
+        col = np.ascontiguousarray(col, np.uint32)
+        val = np.ascontiguousarray(val, np.float32)
+        n = len(rowptr) - 1
+        cap = max(1, len(col))
+        orp = np.zeros(n + 1, np.int64)
+        oi = np.zeros(cap, np.int64)
+        od = np.zeros(cap, np.float32)
+        m = self.lib.orc_rw_as_knn_distances(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(orp, i64p), _p(oi, i64p), _p(od, f32p), cap)
+        assert m >= 0
+        return orp, oi[:m].copy(), od[:m].copy()
+
+    def remove_zeros(self, rowptr, col, val):
+        rowptr = np.ascontiguousarray(rowptr, np.int64)
+        col = np.ascontiguousarray(col, np.uint32)
+        val = np.ascontiguousarray(val, np.float32)
+        n = len(rowptr) - 1
+        cap = max(1, len(col))
+        orp = np.zeros(n + 1, np.int64)
+        oc = np.zeros(cap, np.uint32)
+        ov = np.zeros(cap, np.float32)
+        m = self.lib.orc_remove_zeros(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), _p(orp, i64p), _p(oc, u32p), _p(ov, f32p))
+        return orp, oc[:m].copy(), ov[:m].copy()
+
+    def euclid_hausdorff(self, x, comp_ptr, comp_pix, pa, pb):
+        x = np.ascontiguousarray(x, np.float32)
+        comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+        comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+        pa = np.ascontiguousarray(pa, np.int64)
+        pb = np.ascontiguousarray(pb, np.int64)
+        out = np.zeros(len(pa), np.float32)
+        self.lib.orc_euclid_hausdorff(_p(x, f32p), x.shape[1], _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p))
+        return out
+
+    def level_knn_walks(self, rowptr, col, val, k, mode=0):
+        rowptr = np.ascontiguousarray(rowptr, np.int64)
+        col = np.ascontiguousarray(col, np.uint32)
+        val = np.ascontiguousarray(val, np.float32)
+        n = len(rowptr) - 1
+        ids = np.zeros((n, k), np.int64)
+        dist = np.zeros((n, k), np.float32)
+        self.lib.orc_level_knn_walks(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), mode, k, _p(ids, i64p), _p(dist, f32p))
+        return ids, dist
 
 
 _oracle = None

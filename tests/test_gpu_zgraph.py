@@ -1,0 +1,181 @@
+"""GPU parity tests of the ragged-graph passes (csrc/graph_merge.cu) through the C ABI vs the CPU oracle and the
+reference's golden vectors: symmetrizeGraph (F1), mergeGraphNodes / mergeNodesDataDistances (RW3),
+useRandomWalksAsKnnDistances (D9), zero removal (B7), exact level kNN in the random-walk metrics (D7),
+Euclid-Hausdorff component distance (D6).  All integer / index results bit-exact; fp32 values bit-exact too (every value
+is either copied or produced by the same fp32 / fp64 operation chain as the oracle's).
+
+STATUS: these kernels were written after round 1's GPU budget was spent — they cross-compile for sm_100a and their oracle
+is pinned against the reference goldens on the CPU, but they have not yet executed on hardware.  Until a GPU run
+confirms them the module is marked xfail(strict=False) so that a first-run defect cannot mask the verified suite
+(the file sorts last among the -m gpu tests); an XPASS here is the confirmation, after which the mark is to be removed.
+"""
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from oracle_lib import dense_to_csr
+
+pytestmark = [
+    pytest.mark.gpu,
+    pytest.mark.xfail(strict=False, reason="graph_merge.cu kernels not yet executed on a B200 (round-1 GPU budget spent before they were written)"),
+]
+GOLD = Path(__file__).resolve().parent / "golden"
+
+
+def gold(name):
+    return json.loads((GOLD / name).read_text())
+
+
+def eq3(a, b):
+    for x, y in zip(a, b):
+        np.testing.assert_array_equal(x, y)
+
+
+def random_knn_graph(n, k, seed, dup_frac=0.0):
+    """Fixed-k graph with self first, distances ascending; `dup_frac` of the points are exact duplicates of another
+    point (distance 0 to it), the situation ensureClosestPointIsSelf exists for."""
+    rng = np.random.default_rng(seed)
+    ids = np.empty((n, k), np.int64)
+    dist = np.empty((n, k), np.float32)
+    for i in range(n):
+        nb = rng.choice(np.delete(np.arange(n), i), k - 1, replace=False)
+        d = np.sort(rng.integers(1, 40, k - 1)).astype(np.float32) / 8  # many ties within and across rows
+        ids[i] = np.concatenate([[i], nb])
+        dist[i] = np.concatenate([[0], d])
+    for i in rng.choice(n, int(dup_frac * n), replace=False):
+        dist[i, 1] = 0.0  # a zero-distance neighbour with possibly smaller index than i
+    return ids, dist
+
+
+def random_stochastic(n, nnz_per_row, seed, diag=True):
+    rng = np.random.default_rng(seed)
+    rowptr = [0]
+    col, val = [], []
+    for i in range(n):
+        m = int(rng.integers(0, nnz_per_row + 1))
+        pool = np.arange(n) if diag else np.delete(np.arange(n), i)
+        c = np.sort(rng.choice(pool, size=min(m, len(pool)), replace=False))
+        w = rng.uniform(0.05, 1.0, len(c))
+        col.extend(c.tolist())
+        val.extend((w / max(w.sum(), 1e-9)).tolist())
+        rowptr.append(len(col))
+    return np.array(rowptr, np.int64), np.array(col, np.uint32), np.array(val, np.float32)
+
+
+# ---------------------------------------------------------------- F1
+def test_symmetrize_graph_golden(capi):
+    g = gold("symmetrize_graph_24.json")
+    ids = np.array(g["ids"], np.int64).reshape(-1, g["k"])
+    dist = np.array(g["dist"], np.float32).reshape(-1, g["k"])
+    rp, oi, od = capi.symmetrize_graph(ids, dist)
+    for p, exp in g["rows"].items():
+        p = int(p)
+        assert oi[rp[p]:rp[p + 1]].tolist() == exp
+
+
+@pytest.mark.parametrize("n,k,dup", [(24, 3, 0.0), (2000, 16, 0.05), (5000, 91, 0.01)])
+def test_symmetrize_graph_matches_oracle(capi, oracle, n, k, dup):
+    ids, dist = random_knn_graph(n, k, seed=n + k, dup_frac=dup)
+    eq3(capi.symmetrize_graph(ids, dist), oracle.symmetrize_graph(ids, dist))
+
+
+def test_symmetrize_graph_ragged_and_empty_rows(capi, oracle):
+    # ragged input (a symmetrised graph symmetrised again is a fixed point), rows without entries, self missing
+    ids, dist = random_knn_graph(300, 8, seed=2)
+    rp, oi, od = oracle.symmetrize_graph(ids, dist)
+    eq3(capi.symmetrize_graph(oi, od, rp), (rp, oi, od))
+    rp2 = np.array([0, 2, 2, 5, 6], np.int64)
+    ids2 = np.array([1, 2, 0, 2, 3, 3], np.int64)      # row 0 lacks itself (shift branch), row 1 is empty
+    dist2 = np.array([1, 2, 0.5, 0, 1, 0], np.float32)
+    eq3(capi.symmetrize_graph(ids2, dist2, rp2), oracle.symmetrize_graph(ids2, dist2, rp2))
+
+
+# ---------------------------------------------------------------- RW3
+def test_merge_graph_nodes_golden(capi):
+    g = gold("merge_graph_9to3.json")
+    ids = np.array(g["ids"], np.int64).reshape(-1, g["k"])
+    dist = np.array(g["dist"], np.float32).reshape(-1, g["k"])
+    rp, oi, od = capi.merge_graph_nodes(ids, dist, g["parents"], 3)
+    for m, exp in g["expected"].items():
+        m = int(m)
+        assert oi[rp[m]] == m and od[rp[m]] == 0
+        for t, (nid, nd) in enumerate(exp, start=1):
+            assert oi[rp[m] + t] == nid
+            np.testing.assert_allclose(od[rp[m] + t], nd, rtol=1e-6)
+
+
+@pytest.mark.parametrize("n,k,nm", [(9, 4, 3), (3000, 12, 700), (20000, 31, 9000)])
+def test_merge_graph_nodes_matches_oracle(capi, oracle, n, k, nm):
+    ids, dist = random_knn_graph(n, k, seed=n)
+    rng = np.random.default_rng(n + 1)
+    parents = rng.integers(0, nm, n).astype(np.uint64)
+    parents[:nm] = np.arange(nm)  # every merged node has a child
+    eq3(capi.merge_graph_nodes(ids, dist, parents, nm), oracle.merge_graph_nodes(ids, dist, parents, nm))
+
+
+def test_merge_data_distances_matches_oracle(capi, oracle):
+    rp, c, v = random_stochastic(2500, 20, seed=8)
+    v[::13] = 0.0  # stored zeros are "empty" for the reference's coeff() test
+    rng = np.random.default_rng(3)
+    parents = rng.integers(0, 600, 2500).astype(np.uint64)
+    parents[:600] = np.arange(600)
+    eq3(capi.merge_data_distances(rp, c, v, parents, 600), oracle.merge_data_distances(rp, c, v, parents, 600))
+
+
+# ---------------------------------------------------------------- D9 / B7
+def test_rw_as_knn_distances_matches_oracle(capi, oracle):
+    rp, c, v = random_stochastic(4000, 40, seed=12)
+    v[::11] = 0.0
+    v = (np.round(v * 16) / 16).astype(np.float32)  # heavy ties: the stable order is what is tested
+    eq3(capi.rw_as_knn_distances(rp, c, v), oracle.rw_as_knn_distances(rp, c, v))
+
+
+def test_remove_zeros_matches_oracle(capi, oracle):
+    rp, c, v = random_stochastic(4000, 40, seed=13)
+    v[::3] = 0.0
+    eq3(capi.remove_zeros(rp, c, v), oracle.remove_zeros(rp, c, v))
+    z = np.zeros_like(v)
+    orp, oc, ov = capi.remove_zeros(rp, c, z)
+    assert orp[-1] == 0 and len(oc) == 0 and (orp == 0).all()
+
+
+# ---------------------------------------------------------------- D7
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("n,per_row,k", [(50, 5, 12), (1500, 40, 31), (600, 3, 100)])
+def test_level_knn_walks_matches_oracle(capi, oracle, mode, n, per_row, k):
+    rp, c, v = random_stochastic(n, per_row, seed=n + mode)
+    ids, dist = capi.level_knn_walks(rp, c, v, k, mode)
+    rids, rdist = oracle.level_knn_walks(rp, c, v, k, mode)
+    np.testing.assert_array_equal(ids, rids)
+    np.testing.assert_array_equal(dist, rdist)  # same fp32 summation order as the per-pair loop
+
+
+def test_level_knn_walks_k_larger_than_n(capi, oracle):
+    rp, c, v = random_stochastic(20, 6, seed=1)
+    ids, dist = capi.level_knn_walks(rp, c, v, 33, 0)
+    rids, rdist = oracle.level_knn_walks(rp, c, v, 33, 0)
+    np.testing.assert_array_equal(ids, rids)
+    np.testing.assert_array_equal(dist, rdist)
+    assert (ids[:, 20:] == -1).all()
+
+
+# ---------------------------------------------------------------- D6
+@pytest.mark.parametrize("d", [3, 7, 128, 200])
+def test_euclid_hausdorff_matches_oracle(capi, oracle, d):
+    rng = np.random.default_rng(d)
+    n = 3000
+    x = rng.normal(size=(n, d)).astype(np.float32)
+    sizes = rng.integers(0, 60, 120)
+    sizes[0] = 1
+    sizes[1] = 1
+    comp_ptr = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    comp_pix = rng.integers(0, n, comp_ptr[-1]).astype(np.int64)
+    pa = rng.integers(0, 120, 500).astype(np.int64)
+    pb = rng.integers(0, 120, 500).astype(np.int64)
+    pa[:2], pb[:2] = [0, 0], [1, 0]  # level-0 style single-pixel pairs, one of them identical
+    out = capi.euclid_hausdorff(x, comp_ptr, comp_pix, pa, pb)
+    ref = oracle.euclid_hausdorff(x, comp_ptr, comp_pix, pa, pb)
+    np.testing.assert_array_equal(out, ref)
+    assert out[1] == 0

@@ -220,3 +220,122 @@ def test_random_walks_serial_reproducible_and_normalised(oracle):
     # un-normalised CONSTANT weighting: every walk step adds 1 -> raw row mass = W*L minus self hits
     raw = csr_to_dense(*oracle.random_walks(rp, c, v, 10, 3, weighting=0, seed=1, threads=1, remove_diagonal=False, normalize=False))
     np.testing.assert_allclose(raw.sum(1), 30.0)
+
+
+# ---------------------------------------------------------------- F1 symmetrizeGraph / RW3 mergeGraphNodes
+def _rows(rp, ids):
+    return [ids[rp[i]:rp[i + 1]].tolist() for i in range(len(rp) - 1)]
+
+
+def test_symmetrize_graph_golden(oracle):
+    g = gold("symmetrize_graph_24.json")
+    ids = np.array(g["ids"], np.int64).reshape(-1, g["k"])
+    dist = np.array(g["dist"], np.float32).reshape(-1, g["k"])
+    rp, oi, od = oracle.symmetrize_graph(ids, dist)
+    rows = _rows(rp, oi)
+    for p, exp in g["rows"].items():
+        assert rows[int(p)] == exp
+    # every edge is reachable from both ends (the isDirectNeighbor loop of the reference test), self first, distance 0
+    for p, row in enumerate(rows):
+        assert row[0] == p and od[rp[p]] == 0
+        for q in row:
+            assert p in rows[q]
+    # symmetric values: d(p, q) == d(q, p) == min of the stored directions
+    lut = {(p, int(oi[e])): float(od[e]) for p in range(len(rows)) for e in range(rp[p], rp[p + 1])}
+    for (p, q), v in lut.items():
+        assert lut[(q, p)] == v
+    assert lut[(0, 1)] == 0.5  # 0->1 stored 1, 1->0 stored 0.5
+
+
+def test_merge_graph_nodes_golden(oracle):
+    g = gold("merge_graph_9to3.json")
+    ids = np.array(g["ids"], np.int64).reshape(-1, g["k"])
+    dist = np.array(g["dist"], np.float32).reshape(-1, g["k"])
+    rp, oi, od = oracle.merge_graph_nodes(ids, dist, g["parents"], 3)
+    for m, exp in g["expected"].items():
+        m = int(m)
+        assert oi[rp[m]] == m and od[rp[m]] == 0  # self first
+        for t, (nid, nd) in enumerate(exp, start=1):
+            assert oi[rp[m] + t] == nid
+            np.testing.assert_allclose(od[rp[m] + t], nd, rtol=1e-6)
+    # the sparse form (mergeNodesDataDistances on convertGraphToEigenSparse) gives the same off-diagonal minima
+    n, k = ids.shape
+    dense = np.zeros((n, n), np.float32)
+    for i in range(n):
+        for t in range(k):
+            dense[i, ids[i, t]] = dist[i, t]
+    crp, cc, cv = dense_to_csr(dense)
+    mrp, mc, mv = oracle.merge_data_distances(crp, cc, cv, g["parents"], 3)
+    md = csr_to_dense(mrp, mc, mv, 3)
+    for m, exp in g["expected"].items():
+        for nid, nd in exp:
+            np.testing.assert_allclose(md[int(m), nid], nd, rtol=1e-6)
+
+
+def test_symmetrize_graph_self_repair_and_duplicates(oracle):
+    # row 1 lists a zero-distance duplicate pixel (0) before itself: ensureClosestPointIsSelf swaps, not shifts
+    rp = np.array([0, 2, 5, 6], np.int64)
+    ids = np.array([0, 1, 0, 1, 2, 2], np.int64)
+    dist = np.array([0, 0, 0, 0, 3, 0], np.float32)
+    orp, oi, od = oracle.symmetrize_graph(ids, dist, rp)
+    rows = _rows(orp, oi)
+    assert rows[0] == [0, 1] and rows[1] == [1, 0, 2] and rows[2] == [2, 1]
+    assert od.tolist() == [0, 0, 0, 0, 3, 0, 3]
+
+
+def test_rw_as_knn_distances_and_zero_removal(oracle):
+    m = np.array([[0.5, 0, 0.25, 0.25], [0, 0, 0, 0], [0.1, 0.1, 0.8, 0], [0, 1.0, 0, 0]], np.float32)
+    rp, c, v = dense_to_csr(m)
+    # an explicit zero must be dropped by both passes
+    c = np.concatenate([c, [2]]).astype(np.uint32)
+    v = np.concatenate([v, [0.0]]).astype(np.float32)
+    rp = rp.copy()
+    rp[-1] += 1
+    orp, oi, od = oracle.rw_as_knn_distances(rp, c, v)
+    assert orp.tolist() == [0, 3, 3, 6, 7]
+    assert oi.tolist() == [0, 2, 3, 2, 0, 1, 1]  # ties (0.75, 0.75) and (0.9, 0.9) keep column order
+    np.testing.assert_array_equal(od, np.array([0.5, 0.75, 0.75, 1 - np.float32(0.8), 0.9, 0.9, 0.0], np.float32))
+    zrp, zc, zv = oracle.remove_zeros(rp, c, v)
+    assert zrp.tolist() == [0, 3, 3, 6, 7] and zc.tolist() == [0, 2, 3, 0, 1, 2, 1]
+
+
+def test_euclid_hausdorff_matches_numpy(oracle):
+    rng = np.random.default_rng(5)
+    x = rng.normal(size=(60, 7)).astype(np.float32)
+    comp_ptr = np.array([0, 1, 5, 5, 20, 60], np.int64)  # sizes 1, 4, 0, 15, 40
+    comp_pix = rng.permutation(60).astype(np.int64)
+    pa = np.array([0, 1, 3, 4, 0, 2], np.int64)
+    pb = np.array([0, 3, 4, 1, 1, 3], np.int64)
+    out = oracle.euclid_hausdorff(x, comp_ptr, comp_pix, pa, pb)
+    for p in range(len(pa)):
+        a = comp_pix[comp_ptr[pa[p]]:comp_ptr[pa[p] + 1]]
+        b = comp_pix[comp_ptr[pb[p]]:comp_ptr[pb[p] + 1]]
+        if len(a) == 0 or len(b) == 0:
+            assert out[p] == 0
+            continue
+        dm = np.sqrt(((x[a, None, :].astype(np.float64) - x[None, b, :].astype(np.float64)) ** 2).sum(-1))
+        exp = max(dm.min(1).max(), dm.min(0).max())
+        np.testing.assert_allclose(out[p], exp, rtol=1e-6, atol=1e-7)  # testL2 pins utils::L2 to 1e-4 abs
+    assert out[0] == 0  # same single pixel
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_level_knn_walks_matches_pairwise(oracle, mode):
+    rng = np.random.default_rng(9 + mode)
+    n = 50
+    m = (rng.uniform(size=(n, n)) < 0.08) * rng.uniform(0.05, 1, size=(n, n))
+    m[7] = 0  # an empty row: everything but itself at distance 1
+    m /= np.maximum(m.sum(1, keepdims=True), 1e-9)
+    rp, c, v = dense_to_csr(m)
+    k = 12
+    ids, dist = oracle.level_knn_walks(rp, c, v, k, mode)
+    pa, pb = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    sim = oracle.pair_sims(rp, c, v, pa.ravel(), pb.ravel(), mode).reshape(n, n)
+    d = (np.float32(1) - sim).astype(np.float32)
+    d[np.arange(n), np.arange(n)] = 0
+    for i in range(n):
+        order = np.lexsort((np.arange(n), d[i]))[:k]
+        assert ids[i].tolist() == order.tolist()
+        np.testing.assert_array_equal(dist[i], d[i, order])
+    if mode == 0:  # nothing shares a column with the empty row: the lowest indices at distance exactly 1
+        assert ids[7, 0] == 7 and (dist[7, 1:] == 1).all() and ids[7, 1:].tolist() == [j for j in range(n) if j != 7][:k - 1]
