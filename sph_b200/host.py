@@ -88,6 +88,9 @@ class LevelSimilaritiesSettings:  # Settings.hpp:169-181 (the fields this path r
     weightTransitionBySize: bool = False
     normalizeProbDist: NormalizationScheme = NormalizationScheme.TSNE
     computeSymmetricProbDist: NormalizationScheme = NormalizationScheme.TSNE
+    componentSim: "ComponentSim | None" = None   # None: NEIGH_WALKS with MERGE_RW_ONLY (useRandomWalks)
+    knnFromWalkMetric: bool = False               # rwHandling == MERGE_RW_NEW_WALKS_AND_KNN: exact level kNN + useKnnDistances
+    forceComputeDistances: bool = False           # useRandomWalksAsKnnDistances
 
 
 @dataclass
@@ -110,6 +113,37 @@ class Graph:  # sph/utils/Graph.hpp:155-273 with a fixed number of neighbours
 
     def isValid(self) -> bool:
         return self.knnIndices.shape == self.knnDistances.shape and bool((self.knnIndices >= 0).all())
+
+
+@dataclass
+class RaggedGraph:  # sph/utils/Graph.hpp:155-273 with per-point neighbour counts (symmetrised / merged / level graphs)
+    rowptr: np.ndarray       # offsets + total
+    knnIndices: np.ndarray   # int64 [nnz]
+    knnDistances: np.ndarray  # float32 [nnz]
+    symmetric: bool = False
+
+    @property
+    def numPoints(self) -> int:
+        return len(self.rowptr) - 1
+
+    @property
+    def nns(self) -> np.ndarray:
+        return np.diff(self.rowptr)
+
+    def getNeighbors(self, p: int) -> np.ndarray:
+        return self.knnIndices[self.rowptr[p]:self.rowptr[p + 1]]
+
+    def getDistances(self, p: int) -> np.ndarray:
+        return self.knnDistances[self.rowptr[p]:self.rowptr[p + 1]]
+
+
+class ComponentSim(enum.IntEnum):  # sph/utils/Settings.hpp (ComponentSim)
+    NEIGH_OVERLAP = 0
+    GEO_CENTROID = 1
+    NEIGH_WALKS = 2
+    NEIGH_WALKS_SINGLE_OVERLAP = 3
+    EUCLID_CENTROID = 4
+    GEO_WALKS = 5
 
 
 @dataclass
@@ -162,6 +196,7 @@ class NearestNeighbors:
     def __init__(self, data: np.ndarray, knn_fn=None, prow_fn=None):
         self._data = np.ascontiguousarray(data, np.float32)
         self._graph: Graph | None = None
+        self._sym_graph: RaggedGraph | None = None
         self._nns = NearestNeighborsSettings()
         self._valid = False
         self._knn_fn = knn_fn  # injectable for the CPU multi-process tests (the product default is the C ABI)
@@ -195,6 +230,33 @@ class NearestNeighbors:
             dist = gather_rows(dist, n, group)
         self._graph = Graph(ids, dist)
         self._valid = checkAllNeighborsExist(ids) or n < s.numNearestNeighbors
+        self._sym_graph = None
+        if s.symmetricNeighbors and self._valid:
+            self.computeSymmetrizedNnGraph()
+
+    def computeSymmetrizedNnGraph(self):
+        """NearestNeighbors::computeSymmetrizedNnGraph (sph/NearestNeighbors.cpp:411-492) -> utils::symmetrizeGraph."""
+        if self._graph is None or self._graph.numPoints == 0:
+            log.warning("NearestNeighbors::computeSymmetrizedNnGraph: _knn graph is not computed yet, doing nothing")
+            return None
+        if not checkAllNeighborsExist(self._graph.knnIndices):
+            log.error("NearestNeighbors::computeSymmetrizedNnGraph: missing neighbours")
+            return None
+        try:
+            rp, ids, dist = self._symmetrize(self._graph.knnIndices, self._graph.knnDistances)
+        except Exception as e:
+            log.error("NearestNeighbors::computeSymmetrizedNnGraph failed: %s", e)
+            return None
+        self._sym_graph = RaggedGraph(rp, ids, dist, symmetric=True)
+        return self._sym_graph
+
+    def _symmetrize(self, ids, dist):
+        from . import capi
+
+        return capi.symmetrize_graph(ids, dist)
+
+    def getSymGraph(self):
+        return self._sym_graph
 
     def _knn(self, x, k, metric, l2sq, q0, q1):
         if self._knn_fn is not None:
@@ -290,6 +352,26 @@ class LevelSimilarities:
         self._prob: dict[int, SparseRows] = {}
         self._perplexities: list[float] = []
         self._ks: list[int] = []
+        self._distance_graphs: dict[int, object] = {}
+
+    def computeNearestNeighborOnLevel(self, level: int, lss: LevelSimilaritiesSettings):
+        """LevelSimilarities::computeNearestNeighborOnLevel (sph/LevelSimilarities.cpp:184-442) for the random-walk metrics:
+        exact kNN in the component metric (computeExactKnn, :211-252) or the walks themselves as distances (:346-389)."""
+        from . import capi
+
+        rw = self._rw[level]
+        k_l = min(self._ks[level], rw.n)
+        if lss.knnFromWalkMetric:
+            mode = 1 if lss.componentSim == ComponentSim.NEIGH_WALKS_SINGLE_OVERLAP else 0
+            ids, dist = capi.level_knn_walks(rw.rowptr, rw.col, rw.val, k_l, mode)
+            self._distance_graphs[level] = Graph(ids, dist)
+        elif lss.forceComputeDistances:
+            rp, ids, dist = capi.rw_as_knn_distances(rw.rowptr, rw.col, rw.val)
+            self._distance_graphs[level] = RaggedGraph(rp, ids, dist)
+        return self._distance_graphs.get(level)
+
+    def getSimilaritiesGraph(self, level: int):
+        return self._distance_graphs.get(level)
 
     def compute(self, lss: LevelSimilaritiesSettings | None = None) -> None:
         from . import capi
@@ -306,20 +388,26 @@ class LevelSimilarities:
                 self._prob[0] = normalizeKnnDistances(self._graph, NormalizationScheme.TSNE, self._perplexities[0])
                 continue
             rw = self._rw[level]
-            k_l, perp_l = self._ks[level], self._perplexities[level]
-            if lss.randomWalkPairSims:
-                cols, vals, nnz = capi.create_similarities(rw.rowptr, rw.col, rw.val, k_l, 1e-4)
+            k_l, perp_l = min(self._ks[level], rw.n), self._perplexities[level]
+            if lss.knnFromWalkMetric or lss.forceComputeDistances:
+                self.computeNearestNeighborOnLevel(level, lss)
+            if lss.knnFromWalkMetric:
+                # useKnnDistances (:510-515): flat Gaussian rows (tol 1e-5, ignore 0) scattered by neighbour id, skipping -1
+                g = self._distance_graphs[level]
+                temp = capi.prow_gaussian_flat(g.knnDistances, perp_l)
+                rowptr, c, v = scatter_flat_rows(g.knnIndices, temp)
             else:
-                raise NotImplementedError("randomWalkPairSims = false (top-k transition values) is not wired yet")
-            rowptr = np.concatenate([[0], np.cumsum(nnz, dtype=np.int64)])
-            keep = np.arange(cols.shape[1])[None, :] < nnz[:, None]
-            c, v = cols[keep], vals[keep]
-            if lss.normalizeProbDist == NormalizationScheme.TSNE:
-                v = capi.prow_gaussian_inplace(rowptr, v, perp_l, -1)
-            nz = v != 0  # erase exact zeros (:566-581)
-            counts = np.add.reduceat(nz.astype(np.int64), rowptr[:-1]) if len(v) else np.zeros(len(rowptr) - 1, np.int64)
-            counts[np.diff(rowptr) == 0] = 0
-            self._prob[level] = SparseRows(np.concatenate([[0], np.cumsum(counts)]).astype(np.int64), c[nz], v[nz])
+                if lss.randomWalkPairSims:
+                    cols, vals, nnz = capi.create_similarities(rw.rowptr, rw.col, rw.val, k_l, 1e-4)
+                else:  # convertEigenSparseVecToHDILibSparseVec: the k_l largest transition values per row (:481-486)
+                    cols, vals, nnz = capi.find_k(rw.rowptr, rw.col, rw.val, k_l, top=True)
+                rowptr = np.concatenate([[0], np.cumsum(nnz, dtype=np.int64)])
+                keep = np.arange(cols.shape[1])[None, :] < nnz[:, None]
+                c, v = cols[keep], vals[keep]
+                if lss.normalizeProbDist == NormalizationScheme.TSNE:
+                    v = capi.prow_gaussian_inplace(rowptr, v, perp_l, -1)
+            rp, c, v = capi.remove_zeros(rowptr, c, v)  # erase exact zeros (:566-581)
+            self._prob[level] = SparseRows(rp, c, v)
         self.symmetrizeOutput(lss.computeSymmetricProbDist)
 
     def symmetrizeOutput(self, scheme: NormalizationScheme) -> None:
@@ -341,6 +429,24 @@ class LevelSimilarities:
         return self._ks
 
 
+def scatter_flat_rows(ids: np.ndarray, temp: np.ndarray):
+    """The serial scatter of utils::computeGaussianDistributions (sph/utils/HDILibHelper.hpp:131-139): slots 1..k-1 of every
+    row go to `distribution[j][ids]` (a column-sorted map; a later duplicate id overwrites), ids == -1 are skipped."""
+    n, k = ids.shape
+    rowptr = [0]
+    cols, vals = [], []
+    for j in range(n):
+        row = {}
+        for t in range(1, k):
+            if ids[j, t] != -1:
+                row[int(ids[j, t])] = temp[j, t]
+        for cc in sorted(row):
+            cols.append(cc)
+            vals.append(row[cc])
+        rowptr.append(len(cols))
+    return np.array(rowptr, np.int64), np.array(cols, np.uint32), np.array(vals, np.float32)
+
+
 # ---- random walks (sph/utils/SparseMatrixAlgorithms.hpp:73,82) -----------------------------------
 def doRandomWalks(similarities: SparseRows, rws: RandomWalkSettings) -> SparseRows:
     from . import capi
@@ -355,3 +461,429 @@ def mergeNodesRandomWalks(walks: SparseRows, num_merged: int, parents, norm: boo
 
     rp, c, v = capi.rw_merge(walks.rowptr, walks.col, walks.val, parents, num_merged, norm, weight_by_size)
     return SparseRows(rp, c, v)
+
+
+def mergeGraphNodes(graph, num_merged: int, parents) -> RaggedGraph:
+    """utils::mergeGraphNodes (sph/utils/SparseMatrixAlgorithms.cpp:486-561)."""
+    from . import capi
+
+    rowptr = getattr(graph, "rowptr", None)
+    rp, ids, dist = capi.merge_graph_nodes(graph.knnIndices, graph.knnDistances, parents, num_merged, rowptr=rowptr)
+    return RaggedGraph(rp, ids, dist)
+
+
+def mergeNodesDataDistances(matrix: SparseRows, num_merged: int, parents) -> SparseRows:
+    """utils::mergeNodesDataDistances (sph/utils/SparseMatrixAlgorithms.cpp:443-484)."""
+    from . import capi
+
+    rp, c, v = capi.merge_data_distances(matrix.rowptr, matrix.col, matrix.val, parents, num_merged)
+    return SparseRows(rp, c, v)
+
+
+def symmetrizeGraph(graph) -> RaggedGraph:
+    """utils::symmetrizeGraph (sph/utils/GraphUtils.cpp:197-317)."""
+    from . import capi
+
+    rp, ids, dist = capi.symmetrize_graph(graph.knnIndices, graph.knnDistances, rowptr=getattr(graph, "rowptr", None))
+    return RaggedGraph(rp, ids, dist, symmetric=True)
+
+
+def euclidDistance(data: np.ndarray, comp_ptr, comp_pix, pairs_a, pairs_b) -> np.ndarray:
+    """Batched utils::euclidDistance (sph/utils/Similarities.cpp:414-483) over component pairs."""
+    from . import capi
+
+    return capi.euclid_hausdorff(data, comp_ptr, comp_pix, pairs_a, pairs_b)
+
+
+# ---- ImageHierarchy (sph/ImageHierarchy.hpp:46, .cpp:113-608) — the HOST merge loop ---------------
+class NeighConnection(enum.IntEnum):
+    FOUR = 0
+    EIGHT = 1
+
+
+class RandomWalkHandling(enum.IntEnum):
+    MERGE_RW_ONLY = 0
+    MERGE_RW_NEW_WALKS = 1
+    MERGE_RW_NEW_WALKS_AND_KNN = 2
+    MERGE_DATA_NEW_WALKS = 3
+
+
+class RandomWalkReduction(enum.IntEnum):
+    NONE = 0
+    PROPORTIONAL_COMPONENT_REDUCTION = 1
+    PROPORTIONAL_HALF = 2
+    PROPORTIONAL_DOUBLE = 3
+    CONSTANT = 4
+    CONSTANT_LOW = 5
+    CONSTANT_HIGH = 6
+
+
+class NormType(enum.IntEnum):
+    ONEDIM = 0
+    TWODIM = 1
+
+
+FLT_MAX = float(np.finfo(np.float32).max)
+
+
+@dataclass
+class ImageHierarchySettings:  # sph/utils/Settings.hpp:145-166
+    componentSim: ComponentSim = ComponentSim.NEIGH_OVERLAP
+    neighborConnection: NeighConnection = NeighConnection.FOUR
+    mergeMultiple: bool = False
+    usePercentile: bool = True
+    maxDist: float = 0.0
+    minNumComp: int = 1
+    minReduction: float = 99.99
+    numGeodesicSamples: int | None = None
+    maxLevels: int = -1
+    rwHandling: RandomWalkHandling = RandomWalkHandling.MERGE_RW_ONLY
+    rwReduction: RandomWalkReduction = RandomWalkReduction.PROPORTIONAL_COMPONENT_REDUCTION
+    normKnnDistances: NormalizationScheme = NormalizationScheme.TSNE
+    rwWeightMergeBySize: bool = True
+    rwNormSim: NormType = NormType.ONEDIM
+    rwRemoveSelfSimAfterMerging: bool = True
+
+    def isAlwaysMerge(self) -> bool:
+        return self.maxDist == -1.0
+
+
+class DeviceOps:
+    """The compute calls the merge loop makes, bound to the C ABI (the product path).  Tests substitute an object with the
+    same methods backed by the CPU oracle to pin the loop against the reference's hierarchy goldens without a GPU."""
+
+    def prow(self, graph: Graph, scheme: NormalizationScheme) -> SparseRows:
+        return normalizeKnnDistances(graph, scheme)
+
+    def random_walks(self, sims: SparseRows, rws: RandomWalkSettings) -> SparseRows:
+        return doRandomWalks(sims, rws)
+
+    def rw_merge(self, walks: SparseRows, parents, n_merged: int, norm: bool, weight_by_size: bool) -> SparseRows:
+        return mergeNodesRandomWalks(walks, n_merged, parents, norm, weight_by_size)
+
+    def pair_sims(self, walks: SparseRows, pa, pb, mode: int) -> np.ndarray:
+        from . import capi
+
+        return capi.pair_sims(walks.rowptr, walks.col, walks.val, pa, pb, mode)
+
+    def neighbor_overlap(self, knn_ids, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
+        from . import capi
+
+        return capi.neighbor_overlap(knn_ids, comp_ptr, comp_pix, pa, pb)
+
+    def euclid_hausdorff(self, data, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
+        from . import capi
+
+        return capi.euclid_hausdorff(data, comp_ptr, comp_pix, pa, pb)
+
+
+def pixelNeighborIDs(num_cols: int, num_rows: int, conn: NeighConnection, pid: int) -> list[int]:
+    """sph/utils/ImageHelper.cpp:8-29 with the direction tables of ImageHelper.hpp:13-19 (the order matters at level 0:
+    ties in distance keep it)."""
+    if conn == NeighConnection.EIGHT:
+        rd, cd = (-1, -1, -1, 0, 0, 1, 1, 1), (-1, 0, 1, -1, 1, -1, 0, 1)
+    else:
+        rd, cd = (-1, 0, 1, 0), (0, 1, 0, -1)
+    r, c = divmod(pid, num_cols)
+    out = []
+    for dr, dc in zip(rd, cd):
+        nr, nc = r + dr, c + dc
+        if 0 <= nr < num_rows and 0 <= nc < num_cols:
+            out.append(nr * num_cols + nc)
+    return out
+
+
+def labelWeakComponents(n: int, edges) -> tuple[int, np.ndarray]:
+    """utils::labelGraphWeakComponents (sph/utils/GraphUtils.cpp:371-392): boost::strong_components on the symmetrised
+    graph numbers the components in the order their lowest vertex is reached."""
+    parent = list(range(n))
+
+    def find(a):
+        while parent[a] != a:
+            parent[a] = parent[parent[a]]
+            a = parent[a]
+        return a
+
+    for a, b in edges:
+        ra, rb = find(a), find(b)
+        if ra != rb:
+            parent[max(ra, rb)] = min(ra, rb)
+    labels = np.empty(n, np.int64)
+    seen: dict[int, int] = {}
+    for v in range(n):
+        r = find(v)
+        if r not in seen:
+            seen[r] = len(seen)
+        labels[v] = seen[r]
+    return len(seen), labels
+
+
+def computeQuantile(data: np.ndarray, quantile: float, ignore=(), interpolation: int = 0) -> float:
+    """sph/utils/Math.cpp:133-165."""
+    d = np.asarray(data, np.float32)
+    for iv in ignore:
+        d = d[d != np.float32(iv)]
+    d = np.sort(d)
+    rank = np.float32(quantile) * np.float32(len(d) - 1)
+    lo, hi = int(np.floor(rank)), int(np.ceil(rank))
+    if lo == hi:
+        return float(d[lo])
+    frac = np.float32(rank - np.float32(lo))
+    if interpolation == 1:
+        return float(d[lo] + (d[hi] - d[lo]) * frac)
+    return float(np.float32(0.5) * (d[lo] + d[hi]))
+
+
+def _seq_sum_f32(v: np.ndarray) -> np.float32:  # Eigen's SparseVector::sum(): fp32, storage order
+    return np.cumsum(v, dtype=np.float32)[-1] if len(v) else np.float32(0)
+
+
+def removeDiagonalAndNormalize(m: SparseRows, remove_diagonal: bool, norm: NormType) -> SparseRows:
+    """Hierarchy::updateRandomWalks after the merge (sph/utils/Hierarchy.cpp:287-307): removeDiagonalElements(keepSingleEntry,
+    SparseMatrixAlgorithms.cpp:704-718), then per-row (ONEDIM) or whole-matrix (TWODIM) L1 normalisation."""
+    rowptr, cols, vals = [0], [], []
+    for i in range(m.n):
+        c, v = m.row(i)
+        if remove_diagonal and len(c) > 1:
+            keep = c != i
+            c, v = c[keep], v[keep]
+        cols.append(c)
+        vals.append(np.array(v, np.float32))
+        rowptr.append(rowptr[-1] + len(c))
+    if norm == NormType.ONEDIM:
+        vals = [v / _seq_sum_f32(v) if len(v) else v for v in vals]
+    else:
+        tot = np.float32(0)
+        for v in vals:
+            tot = np.float32(tot + _seq_sum_f32(v))
+        vals = [v / tot for v in vals]
+    return SparseRows(np.array(rowptr, np.int64), np.concatenate(cols).astype(np.uint32) if cols else np.zeros(0, np.uint32),
+                      np.concatenate(vals).astype(np.float32) if vals else np.zeros(0, np.float32))
+
+
+class ImageHierarchy:
+    """Borůvka-style superpixel merge loop (sph/ImageHierarchy.cpp:113-591) with the Hierarchy bookkeeping of
+    sph/utils/Hierarchy.cpp:134-390.  It stays on the host (BASELINE.json north_star); every data-parallel step it takes —
+    level-0 P rows, random walks, walk merges, component distances of all (component, spatial neighbour) pairs of a level —
+    is one batched call into `ops` (DeviceOps = the CUDA path through the C ABI)."""
+
+    def __init__(self, knn_graph: Graph, data: np.ndarray | None, num_rows: int, num_cols: int, ops=None):
+        self._graph = knn_graph
+        self._data = data
+        self._rows, self._cols = int(num_rows), int(num_cols)
+        self._ops = ops or DeviceOps()
+        self.ihs = ImageHierarchySettings()
+        self.rws = RandomWalkSettings()
+        self._clear()
+
+    def _clear(self):
+        self.numComponents: list[int] = []
+        self.parents: list[np.ndarray] = []
+        self.children: list[list[list[int]]] = []
+        self.spatialNeighbors: list[list[list[int]]] = []
+        self.pixelComponents: list[np.ndarray] = []
+        self.randomWalks: list[SparseRows] = []
+        self.notMergedNodes: list[list[int]] = []
+        self.reductionRates: list[float] = []
+        self.rwRandomWalkLengths: list[int] = []
+        self.dataLevelProbdist: SparseRows | None = None
+
+    # -- accessors named after the reference's
+    def getNumLevels(self) -> int:
+        return len(self.numComponents)
+
+    def pixelComponentsOn(self, level: int) -> np.ndarray:
+        return self.pixelComponents[level]
+
+    def parentsOn(self, level: int) -> np.ndarray:
+        return self.parents[level]
+
+    def childrenOn(self, level: int):
+        return self.children[level - 1]
+
+    def spatialNeighborsOn(self, level: int):
+        return self.spatialNeighbors[level - 1]
+
+    def getDataLevelProbdist(self) -> SparseRows:
+        return self.dataLevelProbdist
+
+    def getSpatialNeighbors(self, level: int, cid: int) -> list[int]:  # ImageHierarchy.cpp:594-605
+        if level == 0:
+            return pixelNeighborIDs(self._cols, self._rows, self.ihs.neighborConnection, cid)
+        return self.spatialNeighbors[level - 1][cid]
+
+    def representedDataPoints(self, level: int):
+        """(comp_ptr, comp_pix) of every component of `level` (Hierarchy::getRepresentedDataPoints, Hierarchy.cpp:27-73)."""
+        n = self.numComponents[level]
+        if level == 0:
+            return np.arange(n + 1, dtype=np.int64), np.arange(n, dtype=np.int64)
+        lists = [list(ch) for ch in self.children[level - 1]]
+        for lower in range(level - 1, 0, -1):
+            lists = [[g for c in comp for g in self.children[lower - 1][c]] for comp in lists]
+        ptr = np.concatenate([[0], np.cumsum([len(c) for c in lists])]).astype(np.int64)
+        return ptr, np.array([p for c in lists for p in c], np.int64)
+
+    def _uses_walks(self) -> bool:
+        return self.ihs.componentSim in (ComponentSim.NEIGH_WALKS, ComponentSim.NEIGH_WALKS_SINGLE_OVERLAP, ComponentSim.GEO_WALKS)
+
+    # -- compute
+    def compute(self, ihs: ImageHierarchySettings | None = None, rws: RandomWalkSettings | None = None) -> None:
+        if ihs is not None:
+            self.ihs = ihs
+        if rws is not None:
+            self.rws = rws
+        self._clear()
+        if self.ihs.componentSim in (ComponentSim.GEO_CENTROID, ComponentSim.GEO_WALKS):
+            log.error("ImageHierarchy::compute: geodesic component distances (A*/Dijkstra per pair) are host code outside this back-end")
+            return
+        if self.ihs.rwHandling == RandomWalkHandling.MERGE_DATA_NEW_WALKS and self._uses_walks():
+            log.error("ImageHierarchy::compute: MERGE_DATA_NEW_WALKS needs probability rows of a ragged graph; not wired")
+            return
+        try:
+            self._computePreparations()
+            self._computeBoruvkaHierarchy()
+        except Exception as e:  # reference convention: log + return
+            log.error("ImageHierarchy::compute failed: %s", e)
+            self._clear()
+
+    def _computePreparations(self):  # ImageHierarchy.cpp:149-190
+        if self.ihs.normKnnDistances in (NormalizationScheme.TSNE, NormalizationScheme.LINEAR):
+            self.dataLevelProbdist = self._ops.prow(self._graph, self.ihs.normKnnDistances)
+        n = self._graph.numPoints
+        self.numComponents = [n]
+        self.pixelComponents = [np.arange(n, dtype=np.int64)]
+        if self._uses_walks():
+            self.rwRandomWalkLengths.append(self.rws.singleWalkLength)
+            self.randomWalks.append(self._ops.random_walks(self.dataLevelProbdist, self.rws))
+
+    def computeDistances(self, level: int):
+        """ImageHierarchy::computeDistances (.cpp:192-249): rows [self, spatial neighbours...], componentDistance for every
+        pair in ONE batched call, rows stable-sorted by distance."""
+        n = self.numComponents[level]
+        neigh = [[c] + list(self.getSpatialNeighbors(level, c)) for c in range(n)]
+        rowptr = np.concatenate([[0], np.cumsum([len(r) for r in neigh])]).astype(np.int64)
+        ids = np.array([v for r in neigh for v in r], np.int64)
+        pa = np.repeat(np.arange(n, dtype=np.int64), np.diff(rowptr))
+        sim = self.ihs.componentSim
+        if sim == ComponentSim.NEIGH_OVERLAP:
+            ptr, pix = self.representedDataPoints(level)
+            dist = np.float32(1) - self._ops.neighbor_overlap(self._graph.knnIndices, ptr, pix, pa, ids)
+        elif sim in (ComponentSim.NEIGH_WALKS, ComponentSim.NEIGH_WALKS_SINGLE_OVERLAP):
+            mode = 1 if sim == ComponentSim.NEIGH_WALKS_SINGLE_OVERLAP else 0
+            dist = np.float32(1) - self._ops.pair_sims(self.randomWalks[level], pa, ids, mode)
+        elif sim == ComponentSim.EUCLID_CENTROID:
+            ptr, pix = self.representedDataPoints(level)
+            dist = self._ops.euclid_hausdorff(self._data, ptr, pix, pa, ids)
+        else:
+            raise NotImplementedError(sim)
+        dist = np.asarray(dist, np.float32).copy()
+        dist[pa == ids] = 0  # componentDistance: same id -> 0 (Similarities.cpp:127-128)
+        for c in range(n):  # synchronizedSort, stable (Algorithms.hpp:57-93)
+            b, e = rowptr[c], rowptr[c + 1]
+            order = np.argsort(dist[b:e], kind="stable")
+            dist[b:e] = dist[b:e][order]
+            ids[b:e] = ids[b:e][order]
+        return RaggedGraph(rowptr, ids, dist)
+
+    def _connectMostSimilarComponents(self, level: int):
+        """connectMostSimilarComponents + mergeMinBelow / mergeAllBelow (.cpp:260-407): the merge edges of one level."""
+        d = self.computeDistances(level)
+        s = self.ihs
+        thresh = np.float32(FLT_MAX)
+        if s.maxDist > 0:
+            thresh = np.float32(s.maxDist)
+            if s.usePercentile:
+                q = computeQuantile(d.knnDistances, s.maxDist, (0.0, -1.0, FLT_MAX))
+                thresh = np.float32(q if q >= 0 else FLT_MAX)
+        edges = []
+        rng = np.random.default_rng()
+        for c in range(d.numPoints):
+            ids, dist = d.getNeighbors(c), d.getDistances(c)
+            if s.mergeMultiple:
+                merge = []
+                for nid, dv in zip(ids[1:], dist[1:]):
+                    if dv < thresh:
+                        merge.append(int(nid))
+                    else:
+                        break
+                if not merge:
+                    merge = [int(ids[rng.integers(1, len(ids))])] if s.isAlwaysMerge() and len(ids) > 1 else [c]
+                edges.extend((c, m) for m in merge)
+            else:
+                merge, dmax = c, thresh
+                if len(ids) > 1 and dist[1] < dmax:  # distances are sorted: only the first neighbour can be the minimum
+                    dmax, merge = dist[1], int(ids[1])
+                if dmax == np.float32(FLT_MAX) and s.isAlwaysMerge() and len(ids) > 1:
+                    merge = int(ids[rng.integers(1, len(ids))])
+                if merge != c:
+                    edges.append((c, merge))
+        return edges
+
+    def _next_walk_length(self) -> None:  # .cpp:489-533
+        s = self.ihs
+        cur = self.rwRandomWalkLengths[-1]
+        rate = np.float32(self.reductionRates[-1]) / np.float32(100)
+        r = {RandomWalkReduction.NONE: np.float32(1), RandomWalkReduction.PROPORTIONAL_COMPONENT_REDUCTION: rate,
+             RandomWalkReduction.PROPORTIONAL_DOUBLE: rate * np.float32(2), RandomWalkReduction.PROPORTIONAL_HALF: rate * np.float32(0.5),
+             RandomWalkReduction.CONSTANT: np.float32(0.5), RandomWalkReduction.CONSTANT_LOW: np.float32(0.75),
+             RandomWalkReduction.CONSTANT_HIGH: np.float32(0.25)}[s.rwReduction]
+        r = min(max(r, np.float32(0)), np.float32(1))
+        nxt = int(np.float32(r * np.float32(cur)))
+        lo, hi = self.rws.minimumSingleWalkLength, self.rwRandomWalkLengths[0]
+        nxt = lo if nxt < lo else (hi if hi < nxt else nxt)  # std::clamp as libstdc++ evaluates it (lo may exceed hi)
+        self.rwRandomWalkLengths.append(nxt)
+
+    def _computeBoruvkaHierarchy(self):  # .cpp:409-591
+        s = self.ihs
+        num_trees = self.numComponents[0]
+        level = 0
+        while num_trees > s.minNumComp:
+            if s.maxLevels >= 0 and level >= s.maxLevels:
+                break
+            n_cur = self.numComponents[level]
+            edges = self._connectMostSimilarComponents(level)
+            n_next, labels = labelWeakComponents(n_cur, edges)
+            self.reductionRates.append(float(np.float32(100) * np.float32(n_next) / np.float32(n_cur)))
+            rr = self.reductionRates
+            if rr[-1] == 100.0 or (len(rr) > 2 and rr[-1] > s.minReduction and rr[-2] > s.minReduction):
+                break
+            if self._uses_walks() and s.rwHandling != RandomWalkHandling.MERGE_RW_ONLY:
+                self._next_walk_length()
+            self._addLevel(n_next, labels)
+            num_trees = n_next
+            level += 1
+
+    def _addLevel(self, n_next: int, labels: np.ndarray):  # Hierarchy::addLevel (Hierarchy.cpp:134-248)
+        n_pix = self.numComponents[0]
+        cur_level = len(self.numComponents) - 1
+        self.numComponents.append(int(n_next))
+        self.parents.append(labels.astype(np.uint64))
+        self.pixelComponents.append(labels[self.pixelComponents[cur_level]].astype(np.int64))
+        children = [[] for _ in range(n_next)]
+        for c, lab in enumerate(labels):
+            children[int(lab)].append(c)
+        self.children.append(children)
+        self.notMergedNodes.append([i for i, ch in enumerate(children) if len(ch) == 1])
+        pix = self.pixelComponents[-1]
+        sp = [set() for _ in range(n_next)]
+        for p in range(n_pix):
+            for q in pixelNeighborIDs(self._cols, self._rows, self.ihs.neighborConnection, p):
+                if pix[q] != pix[p]:
+                    sp[int(pix[p])].add(int(pix[q]))
+        self.spatialNeighbors.append([sorted(x) for x in sp])
+        if self._uses_walks():
+            self._updateRandomWalks(n_next)
+
+    def _updateRandomWalks(self, n_next: int):  # Hierarchy::updateRandomWalks (Hierarchy.cpp:250-390)
+        s = self.ihs
+        merged = self._ops.rw_merge(self.randomWalks[-1], self.parents[-1], n_next, False, s.rwWeightMergeBySize)
+        remove = s.rwRemoveSelfSimAfterMerging and merged.n > 1 and s.rwHandling != RandomWalkHandling.MERGE_RW_ONLY
+        merged = removeDiagonalAndNormalize(merged, remove, s.rwNormSim)
+        if s.rwHandling == RandomWalkHandling.MERGE_RW_ONLY:
+            out = merged
+        else:
+            rws = RandomWalkSettings(**{**self.rws.__dict__, "singleWalkLength": self.rwRandomWalkLengths[-1]})
+            out = self._ops.random_walks(merged, rws)
+        if out.n == 1 and len(out.col) == 0:  # a single top node keeps its self-similarity
+            out = SparseRows(np.array([0, 1], np.int64), np.zeros(1, np.uint32), np.ones(1, np.float32))
+        self.randomWalks.append(out)

@@ -380,6 +380,45 @@ def load() -> Oracle:
     return _oracle
 
 
+class OracleOps:
+    """The compute calls of sph_b200.host.ImageHierarchy served by the CPU oracle (same methods as host.DeviceOps) — lets the
+    host merge loop run here without a GPU so that the reference's full-hierarchy goldens pin the oracle."""
+
+    def __init__(self, oracle=None):
+        self.o = oracle or load()
+
+    def prow(self, graph, scheme):
+        from sph_b200 import host
+
+        n, k = graph.knnIndices.shape
+        if scheme == host.NormalizationScheme.TSNE:
+            cols, vals, _ = self.o.prow_gaussian_graph(graph.knnIndices, graph.knnDistances, 0.0)
+        else:
+            cols, vals = self.o.prow_linear_graph(graph.knnIndices, graph.knnDistances)
+        return host.SparseRows(np.arange(n + 1, dtype=np.int64) * (k - 1), cols.reshape(-1), vals.reshape(-1))
+
+    def random_walks(self, sims, rws):
+        from sph_b200 import host
+
+        rp, c, v = self.o.random_walks(sims.rowptr, sims.col, sims.val, rws.numRandomWalks, rws.singleWalkLength, int(rws.importanceWeighting),
+                                       rws.pruneValue, rws.pruneSteps, rws.randomSeed, 1, rws.removeDiagonal, rws.normalize)
+        return host.SparseRows(rp, c, v)
+
+    def rw_merge(self, walks, parents, n_merged, norm, weight_by_size):
+        from sph_b200 import host
+
+        return host.SparseRows(*self.o.rw_merge(walks.rowptr, walks.col, walks.val, parents, n_merged, norm, weight_by_size))
+
+    def pair_sims(self, walks, pa, pb, mode):
+        return self.o.pair_sims(walks.rowptr, walks.col, walks.val, pa, pb, mode)
+
+    def neighbor_overlap(self, knn_ids, comp_ptr, comp_pix, pa, pb):
+        return self.o.neighbor_overlap(knn_ids, comp_ptr, comp_pix, pa, pb)
+
+    def euclid_hausdorff(self, data, comp_ptr, comp_pix, pa, pb):
+        return self.o.euclid_hausdorff(data, comp_ptr, comp_pix, pa, pb)
+
+
 def dense_to_csr(m):
     m = np.asarray(m, np.float32)
     rowptr = [0]

@@ -179,3 +179,57 @@ def test_euclid_hausdorff_matches_oracle(capi, oracle, d):
     ref = oracle.euclid_hausdorff(x, comp_ptr, comp_pix, pa, pb)
     np.testing.assert_array_equal(out, ref)
     assert out[1] == 0
+
+
+# ---------------------------------------------------------------- host mirror on top of the new entry points
+def test_level_similarities_walk_knn_path(capi, oracle):
+    """LevelSimilarities with rwHandling = MERGE_RW_NEW_WALKS_AND_KNN: exact level kNN in the Bhattacharyya metric, then
+    useKnnDistances (flat Gaussian rows, tol 1e-5) and zero removal (sph/LevelSimilarities.cpp:211-252, 510-515, 566-581)."""
+    from sph_b200 import host
+
+    n0, k0 = 600, 31
+    ids, dist = random_knn_graph(n0, k0, seed=4)
+    rw1 = host.SparseRows(*random_stochastic(150, 25, seed=6))
+    ls = host.LevelSimilarities(host.Graph(ids, dist), [None, rw1])
+    lss = host.LevelSimilaritiesSettings(levelToCompute=1, knnFromWalkMetric=True, componentSim=host.ComponentSim.NEIGH_WALKS,
+                                         computeSymmetricProbDist=host.NormalizationScheme.NONE)
+    ls.compute(lss)
+    g = ls.getSimilaritiesGraph(1)
+    k1 = ls.getKs()[1]
+    rids, rdist = oracle.level_knn_walks(rw1.rowptr, rw1.col, rw1.val, k1, 0)
+    np.testing.assert_array_equal(g.knnIndices, rids)
+    np.testing.assert_array_equal(g.knnDistances, rdist)
+    temp = oracle.prow_gaussian_flat(rdist, ls.getPerplexities()[1])
+    rp, c, v = host.scatter_flat_rows(rids, temp)
+    zrp, zc, zv = oracle.remove_zeros(rp, c, v)
+    p = ls.getProbDist(1)
+    np.testing.assert_array_equal(p.rowptr, zrp)
+    np.testing.assert_array_equal(p.col, zc)
+    np.testing.assert_allclose(p.val, zv, rtol=1e-5, atol=1e-12)
+
+
+def test_level_similarities_topk_transition_path(capi, oracle):
+    """randomWalkPairSims = false: the k_l largest transition values per row, then the in-place Gaussian rows
+    (sph/LevelSimilarities.cpp:481-497)."""
+    from sph_b200 import host
+
+    ids, dist = random_knn_graph(600, 31, seed=5)
+    rw1 = host.SparseRows(*random_stochastic(150, 60, seed=7))
+    ls = host.LevelSimilarities(host.Graph(ids, dist), [None, rw1])
+    ls.compute(host.LevelSimilaritiesSettings(levelToCompute=1, randomWalkPairSims=False, computeSymmetricProbDist=host.NormalizationScheme.NONE))
+    k1, perp1 = ls.getKs()[1], ls.getPerplexities()[1]
+    rows_c, rows_v, rp = [], [], [0]
+    for i in range(rw1.n):
+        c, v = rw1.row(i)
+        oc, ov = oracle.find_k(c, v, k1, True)
+        rows_c.append(oc)
+        rows_v.append(ov)
+        rp.append(rp[-1] + len(oc))
+    rp = np.array(rp, np.int64)
+    c = np.concatenate(rows_c).astype(np.uint32)
+    v = oracle.prow_gaussian_inplace(rp, np.concatenate(rows_v).astype(np.float32), perp1, -1)
+    zrp, zc, zv = oracle.remove_zeros(rp, c, v)
+    p = ls.getProbDist(1)
+    np.testing.assert_array_equal(p.rowptr, zrp)
+    np.testing.assert_array_equal(p.col, zc)
+    np.testing.assert_allclose(p.val, zv, rtol=1e-5, atol=1e-12)

@@ -73,6 +73,43 @@ def test_nearest_neighbors_error_convention(caplog):
     assert not nn.isValid() and nn.getKnnGraph() is None
 
 
+def test_symmetric_neighbors_path(oracle, monkeypatch):
+    # NearestNeighbors::compute with symmetricNeighbors = true runs computeSymmetrizedNnGraph right after the search
+    # (sph/NearestNeighbors.cpp:176-177); the compute calls are injected with the checker (no GPU here)
+    from sph_b200 import host
+
+    rng = np.random.default_rng(2)
+    x = rng.standard_normal((120, 5)).astype(np.float32)
+
+    def knn(x, k, metric, l2sq, q0, q1):
+        return oracle.knn_reference_graph(x, k, l2_squared=l2sq, rows=np.arange(q0, q1), metric=metric)
+
+    nn = host.NearestNeighbors(x, knn_fn=knn)
+    monkeypatch.setattr(nn, "_symmetrize", lambda ids, dist: oracle.symmetrize_graph(ids, dist))
+    nn.compute(host.NearestNeighborsSettings(numNearestNeighbors=6, symmetricNeighbors=True))
+    g = nn.getSymGraph()
+    assert g is not None and g.symmetric and g.numPoints == 120
+    assert (g.nns >= 6).all()
+    for p in range(120):
+        assert g.getNeighbors(p)[0] == p
+        for q in g.getNeighbors(p):
+            assert p in g.getNeighbors(int(q))
+    nn2 = host.NearestNeighbors(x, knn_fn=knn)
+    nn2.compute(host.NearestNeighborsSettings(numNearestNeighbors=6))
+    assert nn2.getSymGraph() is None
+
+
+def test_scatter_flat_rows():
+    # sph/utils/HDILibHelper.hpp:131-139: slot 0 skipped, -1 skipped, later duplicate overwrites, rows column-sorted
+    from sph_b200 import host
+
+    ids = np.array([[0, 5, 2, -1], [1, 3, 3, 0]], np.int64)
+    temp = np.array([[9, .5, .25, .7], [9, .1, .2, .3]], np.float32)
+    rp, c, v = host.scatter_flat_rows(ids, temp)
+    assert rp.tolist() == [0, 2, 4] and c.tolist() == [2, 5, 0, 3]
+    np.testing.assert_array_equal(v, np.array([.25, .5, .3, .2], np.float32))
+
+
 WORKER = r'''
 import os, sys
 import numpy as np

@@ -339,3 +339,45 @@ def test_level_knn_walks_matches_pairwise(oracle, mode):
         np.testing.assert_array_equal(dist[i], d[i, order])
     if mode == 0:  # nothing shares a column with the empty row: the lowest indices at distance exactly 1
         assert ids[7, 0] == 7 and (dist[7, 1:] == 1).all() and ids[7, 1:].tolist() == [j for j in range(n) if j != 7][:k - 1]
+
+
+# ---------------------------------------------------------------- full hierarchies (host merge loop on the oracle)
+def run_hierarchy(g, ops):
+    from sph_b200 import host
+
+    n = g["rows"] * g["cols"]
+    ids = np.array(g["knn"], np.int64).reshape(n, g["k"])
+    dist = np.array(g.get("dist", [0.0] * (n * g["k"])), np.float32).reshape(n, g["k"])
+    ih = host.ImageHierarchy(host.Graph(ids, dist), None, g["rows"], g["cols"], ops=ops)
+    ihs = host.ImageHierarchySettings(componentSim=host.ComponentSim[g["sim"]], neighborConnection=host.NeighConnection.FOUR,
+                                      mergeMultiple=False, usePercentile=False)
+    rws = host.RandomWalkSettings()
+    if "num_walks" in g:
+        ihs.rwHandling = host.RandomWalkHandling.MERGE_RW_NEW_WALKS
+        ihs.normKnnDistances = host.NormalizationScheme.LINEAR
+        rws = host.RandomWalkSettings(numRandomWalks=g["num_walks"], singleWalkLength=g["walk_len"], randomSeed=g["seed"], parallel=False,
+                                      importanceWeighting=host.ImportanceWeighting.CONSTANT)
+    ih.compute(ihs, rws)
+    return ih
+
+
+def check_hierarchy(ih, g):
+    levels = len(g["pixel_components"])
+    assert ih.getNumLevels() == levels
+    for lvl in range(levels):
+        assert ih.pixelComponentsOn(lvl).tolist() == g["pixel_components"][lvl]
+    for lvl in range(levels - 1):
+        assert ih.parentsOn(lvl).tolist() == g["parents"][lvl]
+        assert ih.childrenOn(lvl + 1) == g["children"][lvl]
+        assert ih.spatialNeighborsOn(lvl + 1) == g["spatial_neighbors"][lvl]
+
+
+@pytest.mark.parametrize("name", ["hierarchy_overlap_4x4.json", "hierarchy_overlap_6x4.json", "hierarchy_walks_6x4.json"])
+def test_full_hierarchy_golden(oracle, name):
+    g = gold(name)
+    ih = run_hierarchy(g, oracle_lib.OracleOps(oracle))
+    check_hierarchy(ih, g)
+    if "num_walks" in g:  # testImageHierarchyWalks (:440-444): every random-walk row sums to 1
+        for rw in ih.randomWalks:
+            sums = np.add.reduceat(rw.val, rw.rowptr[:-1])
+            np.testing.assert_allclose(sums, 1.0, atol=1e-3)
