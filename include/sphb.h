@@ -211,12 +211,20 @@ SPHB_API int sphb_rw_as_knn_distances(int64_t n, const int64_t* rowptr, const ui
 SPHB_API int sphb_remove_zeros(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
                                int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t* out_nnz);
 /* Exact level kNN in a random-walk component metric — LevelSimilarities' computeExactKnn
- * (sph/LevelSimilarities.cpp:211-252) with NeighborWalksBhattacharyyaSpace (mode 0) or
- * NeighborWalksSingleOverlapSpace (mode 1): distance = componentDistance = 0 if i == j else 1 - sim
- * (sph/utils/Similarities.cpp:123-156, 374-396).  val is the level's random-walk matrix (n x n CSR).
- * out: n*k, each row ordered by (distance, index); slots beyond n keep -1 / -1.0f. */
+ * (sph/LevelSimilarities.cpp:211-252) in NeighborWalksBhattacharyyaSpace (mode 0,
+ * sph/utils/NeighborWalksBhattacharyyaSpace.hpp:28-41: distance 1 - randomWalksBhattacharyya(i, j)) or
+ * NeighborWalksSingleOverlapSpace (mode 1, sph/utils/NeighborWalksSingleOverlapSpace.hpp:26-36: distance 1 - A[i][j]);
+ * like the reference's spaces, j == i is not special-cased.  (rowptr, col, val) is the level's random-walk matrix
+ * (n x n CSR).  out: n*k, each row ordered by (distance, index) — the reference's unstable sort leaves ties unordered;
+ * slots beyond n keep -1 / -1.0f. */
 SPHB_API int sphb_level_knn_walks(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int mode, int64_t k,
                                   int64_t* out_ids, float* out_dist);
+/* The same exact level kNN in the neighbour-overlap metric (NeighborOverlapSpace, sph/utils/NeighborOverlapSpace.hpp:31-43;
+ * the default componentSim of LevelSimilaritiesSettings, sph/utils/Settings.hpp:170): distance 1 - simNeighborOverlap
+ * (sph/utils/Similarities.cpp:174-228) over the components' kNN-id unions; arguments as sphb_neighbor_overlap.
+ * out: ncomp*k, rows ordered by (distance, index). */
+SPHB_API int sphb_level_knn_overlap(const int64_t* knn_ids, int64_t n, int k_data, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix,
+                                    int64_t k, int64_t* out_ids, float* out_dist);
 /* Batched utils::euclidDistance (sph/utils/Similarities.cpp:414-483): symmetric Hausdorff distance
  * (sph/utils/Math.cpp:167-172) of the all-pairs L2 matrix between the pixels of components pa[p] and pb[p]
  * (comp_pix[comp_ptr[c] .. comp_ptr[c+1]), as Hierarchy::getRepresentedDataPoints lists them; single-pixel

@@ -213,28 +213,77 @@ ORC_API void orc_euclid_hausdorff(const float* x, int d, const int64_t* comp_ptr
     }
 }
 
-// D7 for the random-walk metrics (NeighborWalksBhattacharyyaSpace / NeighborWalksSingleOverlapSpace): distance of (i, j) =
-// componentDistance = 0 if i == j else 1 - sim(i, j) (sph/utils/Similarities.cpp:123-156), sim as in orc_pair_sims; the k
-// smallest per row.  The reference sorts with an unstable std::sort on the distance alone (ties unordered); the contract
-// here is (distance, index).
-extern "C" void orc_pair_sims(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, const int64_t* pa, const int64_t* pb,
-                              int64_t npairs, int mode, float* out);
+// D7 for the random-walk metrics.  The hnswlib spaces the reference searches in do NOT call componentDistance: the
+// distance of (i, j), i == j included, is 1 - randomWalksBhattacharyya(i, j) (mode 0,
+// sph/utils/NeighborWalksBhattacharyyaSpace.hpp:28-41) or 1 - randomWalksSingleOverlap(i, j) = 1 - A[i][j], row i only
+// (mode 1, sph/utils/NeighborWalksSingleOverlapSpace.hpp:26-36); per row the k smallest.  The reference sorts with an
+// unstable std::sort on the distance alone (ties unordered); the contract here is (distance, index).
 ORC_API void orc_level_knn_walks(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int mode, int64_t k, int64_t* out_ids,
                                  float* out_dist) {
+    auto coeff = [&](int64_t r, uint32_t c) -> float {
+        const uint32_t* b = col + rowptr[r];
+        const uint32_t* e = col + rowptr[r + 1];
+        const uint32_t* it = std::lower_bound(b, e, c);
+        return (it != e && *it == c) ? val[it - col] : 0.f;
+    };
 #pragma omp parallel
     {
-        std::vector<int64_t> pa(static_cast<size_t>(n)), pb(static_cast<size_t>(n));
-        std::vector<float> sim(static_cast<size_t>(n));
         std::vector<Pair> all(static_cast<size_t>(n));
 #pragma omp for schedule(dynamic, 4)
         for (int64_t i = 0; i < n; ++i) {
             for (int64_t j = 0; j < n; ++j) {
-                pa[j] = i;
-                pb[j] = j;
+                float sim;
+                if (mode == 1) sim = coeff(i, static_cast<uint32_t>(j));
+                else {
+                    sim = 0.f;
+                    for (int64_t e = rowptr[i]; e < rowptr[i + 1]; ++e) {
+                        const float v2 = coeff(j, col[e]);
+                        if (v2 > 0.0f) sim += std::sqrt(val[e] * v2);
+                    }
+                }
+                all[j] = {j, 1 - sim};
             }
-            orc_pair_sims(n, rowptr, col, val, pa.data(), pb.data(), n, mode, sim.data());
-            for (int64_t j = 0; j < n; ++j) all[j] = {j, i == j ? 0.f : 1.f - sim[j]};
             const int64_t kk = std::min(k, n);
+            std::partial_sort(all.begin(), all.begin() + kk, all.end(), pair_less);
+            for (int64_t t = 0; t < k; ++t) {
+                out_ids[i * k + t] = t < kk ? all[t].first : -1;
+                out_dist[i * k + t] = t < kk ? all[t].second : -1.f;
+            }
+        }
+    }
+}
+
+// D7 in the neighbour-overlap metric (NeighborOverlapSpace, sph/utils/NeighborOverlapSpace.hpp:31-43): distance of (i, j),
+// i == j included, = 1 - simNeighborOverlap (sph/utils/Similarities.cpp:174-228): U_c = sorted-unique union of the kNN
+// lists of the pixels of component c, sim = card(U_i ∩ U_j) / min(card U_i, card U_j) (0 when a union is empty).
+ORC_API void orc_level_knn_overlap(const int64_t* knn_ids, int k_data, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, int64_t k,
+                                   int64_t* out_ids, float* out_dist) {
+    std::vector<std::vector<uint64_t>> uni(static_cast<size_t>(ncomp));
+    for (int64_t c = 0; c < ncomp; ++c) {
+        auto& u = uni[c];
+        for (int64_t e = comp_ptr[c]; e < comp_ptr[c + 1]; ++e)
+            for (int t = 0; t < k_data; ++t) u.push_back(static_cast<uint64_t>(knn_ids[comp_pix[e] * k_data + t]));
+        std::sort(u.begin(), u.end());
+        u.erase(std::unique(u.begin(), u.end()), u.end());
+    }
+#pragma omp parallel
+    {
+        std::vector<Pair> all(static_cast<size_t>(ncomp));
+#pragma omp for schedule(dynamic, 4)
+        for (int64_t i = 0; i < ncomp; ++i) {
+            for (int64_t j = 0; j < ncomp; ++j) {
+                const auto &a = uni[i], &b = uni[j];
+                uint64_t cnt = 0;
+                for (size_t x = 0, y = 0; x < a.size() && y < b.size();) {
+                    if (a[x] < b[y]) ++x;
+                    else if (b[y] < a[x]) ++y;
+                    else { ++cnt; ++x; ++y; }
+                }
+                const size_t mn = a.size() <= b.size() ? a.size() : b.size();
+                const float sim = mn > 0 ? static_cast<float>(cnt) / mn : 0;
+                all[j] = {j, 1.f - sim};
+            }
+            const int64_t kk = std::min(k, ncomp);
             std::partial_sort(all.begin(), all.begin() + kk, all.end(), pair_less);
             for (int64_t t = 0; t < k; ++t) {
                 out_ids[i * k + t] = t < kk ? all[t].first : -1;

@@ -62,6 +62,7 @@ SIGNATURES = {
     "sphb_rw_as_knn_distances": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, i64p, f32p, i64p]),
     "sphb_remove_zeros": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, u32p, f32p, i64p]),
     "sphb_level_knn_walks": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int64, i64p, f32p]),
+    "sphb_level_knn_overlap": (C.c_int, [i64p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, C.c_int64, i64p, f32p]),
     "sphb_euclid_hausdorff": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
 }
 
@@ -408,6 +409,19 @@ def level_knn_walks(rowptr, col, val, k: int, mode: int = 0):
     ids = np.full((n, k), -1, np.int64)
     dist = np.full((n, k), -1.0, np.float32)
     _check(load().sphb_level_knn_walks(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), mode, k, _p(ids, i64p), _p(dist, f32p)))
+    return ids, dist
+
+
+def level_knn_overlap(knn_ids, comp_ptr, comp_pix, k: int):
+    """Exact level kNN in the neighbour-overlap metric: (ids [ncomp,k], dist [ncomp,k])."""
+    knn_ids = np.ascontiguousarray(knn_ids, np.int64)
+    comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+    comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+    n, kd = knn_ids.shape
+    ncomp = len(comp_ptr) - 1
+    ids = np.full((ncomp, k), -1, np.int64)
+    dist = np.full((ncomp, k), -1.0, np.float32)
+    _check(load().sphb_level_knn_overlap(_p(knn_ids, i64p), n, kd, ncomp, _p(comp_ptr, i64p), _p(comp_pix, i64p), k, _p(ids, i64p), _p(dist, f32p)))
     return ids, dist
 
 

@@ -450,9 +450,11 @@ int euclid_hausdorff_dev(const float* d_x, int d, const int64_t* d_comp_ptr, con
 
 // ---------------------------------------------------------------------------------------------
 // D7: exact level kNN in a random-walk component metric (LevelSimilarities.cpp:211-252 with
-// NeighborWalksBhattacharyyaSpace / NeighborWalksSingleOverlapSpace): d(i, j) = 0 if i == j else 1 - sim(i, j),
+// NeighborWalksBhattacharyyaSpace / NeighborWalksSingleOverlapSpace).  The spaces' distance functions do NOT go through
+// componentDistance: d(i, j) = 1 - sim(i, j) for every j, j == i included
 //   mode 0  sim = sum over the columns c of row i, in column order, of sqrt(A[i][c] * A[j][c]) where A[j][c] > 0
-//   mode 1  sim = max(A[i][j], A[j][i])
+//           (sph/utils/NeighborWalksBhattacharyyaSpace.hpp:28-41, Similarities.cpp:379-396)
+//   mode 1  sim = A[i][j], the stored entry of ROW i only (NeighborWalksSingleOverlapSpace.hpp:26-36, Similarities.cpp:374-377)
 // and per row the k smallest by (distance, index) (the reference's std::sort leaves ties unordered).
 // The reference evaluates all n² pairs; here row i is a Gustavson expansion through the transposed matrix: one CTA per
 // row walks the entries of row i IN ORDER (a barrier between columns), the threads of the CTA take the rows j of that
@@ -472,6 +474,10 @@ __global__ void lk_expand(int64_t n, const int64_t* __restrict__ rowptr, const u
             tkeys[e] = (static_cast<uint64_t>(col[e]) << 32) | static_cast<uint64_t>(r);
             tvals[e] = val[e];
         }
+}
+__global__ void lk_swap_halves(const uint64_t* __restrict__ in, int64_t num, uint64_t* __restrict__ out) {
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < num; t += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        out[t] = (in[t] << 32) | (in[t] >> 32);
 }
 __device__ __forceinline__ void lk_block_sort(uint64_t* sm, int cap) {
     for (int k2 = 2; k2 <= cap; k2 <<= 1) {
@@ -495,6 +501,7 @@ struct LkParams {
     const int64_t* rowptr;
     const uint32_t* col;
     const float* val;
+    const uint64_t* rowkeys; // mode 2: the rows as sorted (row << 32 | column) keys instead of (col, val)
     const int64_t* colptr;   // transpose: column c holds tkeys/tval[colptr[c] .. colptr[c+1]), row = low 32 bits of the key
     const uint64_t* tkeys;
     const float* tval;
@@ -538,7 +545,7 @@ __global__ void __launch_bounds__(LK_WARPS * 32) level_knn_walks_kernel(const Lk
                 }
                 __syncthreads();  // the next column may reach the same j from another thread
             }
-        } else {
+        } else if (P.mode == 1) {
             for (int64_t e = rb + threadIdx.x; e < re; e += blockDim.x) {
                 const float v = P.val[e];
                 if (v != 0.f) {
@@ -548,19 +555,19 @@ __global__ void __launch_bounds__(LK_WARPS * 32) level_knn_walks_kernel(const Lk
                 }
             }
             __syncthreads();
-            const int64_t cb = P.colptr[i], ce = P.colptr[i + 1];
-            for (int64_t f = cb + threadIdx.x; f < ce; f += blockDim.x) {
-                const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
-                const float v = P.tval[f], old = acc[j];
-                const float nv = fmaxf(old, v);
-                if (nv != old) acc[j] = nv;
-                if (old == 0.f && nv != 0.f) touched[atomicAdd(&s_touched, 1u)] = j;
+        } else {
+            // set intersection sizes: integer counts, the order of the additions is irrelevant (exact in fp32 below 2^24)
+            for (int64_t e = rb + warp; e < re; e += LK_WARPS) {
+                const uint32_t c = static_cast<uint32_t>(P.rowkeys[e]);
+                const int64_t cb = P.colptr[c], ce = P.colptr[c + 1];
+                for (int64_t f = cb + lane; f < ce; f += 32) {
+                    const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
+                    const float old = atomicAdd(acc + j, 1.f);
+                    if (old == 0.f) touched[atomicAdd(&s_touched, 1u)] = j;
+                }
             }
             __syncthreads();
         }
-        // the point itself is always a candidate (distance 0) whether or not its own row reaches it
-        if (threadIdx.x == 0 && acc[i] == 0.f) touched[s_touched++] = static_cast<uint32_t>(i);
-        __syncthreads();
         const unsigned int T = s_touched;
         // ---- 2. per-warp k smallest of (distance, index) over the touched rows
         int cnt = 0;
@@ -571,7 +578,12 @@ __global__ void __launch_bounds__(LK_WARPS * 32) level_knn_walks_kernel(const Lk
             uint64_t key = ~0ull;
             if (t < T) {
                 const uint32_t j = touched[t];
-                const float dv = static_cast<int64_t>(j) == i ? 0.f : __fsub_rn(1.f, acc[j]);
+                float sim = acc[j];
+                if (P.mode == 2) {  // card(U_i ∩ U_j) / min(card U_i, card U_j)  (Similarities.cpp:216-228)
+                    const int64_t lj = P.rowptr[j + 1] - P.rowptr[j];
+                    sim = __fdiv_rn(sim, static_cast<float>(static_cast<uint64_t>(min(re - rb, lj))));
+                }
+                const float dv = __fsub_rn(1.f, sim);
                 key = make_key(dv, j);
                 pass = key <= kth;
             }
@@ -620,7 +632,7 @@ __global__ void __launch_bounds__(LK_WARPS * 32) level_knn_walks_kernel(const Lk
             int o = nlt, li = nlt;
             int64_t j = 0;
             while (o < kk) {
-                while (j < P.n && (j == i || acc[j] != 0.f)) ++j;
+                while (j < P.n && acc[j] != 0.f) ++j;
                 const uint64_t key_u = j < P.n ? make_key(1.f, static_cast<uint32_t>(j)) : ~0ull;
                 const uint64_t key_l = li < nsel ? lk_keys[li] : ~0ull;
                 if (key_l == ~0ull && key_u == ~0ull) break;
@@ -678,6 +690,54 @@ int level_knn_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_co
     LkParams P{};
     P.n = n; P.rowptr = d_rowptr; P.col = d_col; P.val = d_val; P.colptr = colptr.p; P.tkeys = tk1.p; P.tval = tv1.p;
     P.mode = mode; P.k = static_cast<int>(k); P.cap = cap; P.acc = acc.p; P.touched = touched.p; P.out_ids = d_out_ids; P.out_dist = d_out_dist;
+    level_knn_walks_kernel<<<static_cast<unsigned>(grid), LK_WARPS * 32, smem, s>>>(P);
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return 0;
+}
+
+// D7 in the neighbour-overlap metric (NeighborOverlapSpace, sph/utils/NeighborOverlapSpace.hpp:31-43): the rows are the
+// sorted-unique unions U_c as (component << 32 | data id) keys (built by level_ops.cu for D5); distance 1 - |U_i ∩ U_j| /
+// min(|U_i|, |U_j|), per row the k smallest by (distance, index).
+int level_knn_sets_dev(int64_t nrows, int64_t ncols, const int64_t* d_rowptr, const uint64_t* d_rowkeys, int64_t nnz, int64_t k, int64_t* d_out_ids,
+                       float* d_out_dist, cudaStream_t s) {
+    if (nrows >= (1ll << 32) || ncols >= (1ll << 32)) return fail(SPHB_ERR_UNSUPPORTED, "level_knn: ids must fit 32 bits");
+    if (k > 992) return fail(SPHB_ERR_UNSUPPORTED, "level_knn: k > 992 unsupported");
+    if (nnz > 0x7fffffffll) return fail(SPHB_ERR_UNSUPPORTED, "level_knn: more than 2^31 - 1 set elements");
+    const int sms = ctx().num_sms;
+    DevBuf<int64_t> colptr;
+    DevBuf<uint64_t> tk0, tk1;
+    SPHB_CUDA(colptr.alloc(ncols + 1, s));
+    SPHB_CUDA(tk0.alloc(std::max<int64_t>(nnz, 1), s));
+    SPHB_CUDA(tk1.alloc(std::max<int64_t>(nnz, 1), s));
+    if (nnz > 0) {
+        lk_swap_halves<<<gm_grid(nnz, 256, sms), 256, 0, s>>>(d_rowkeys, nnz, tk0.p);
+        count_launch();
+        size_t bytes = 0;
+        const int end_bit = 32 + bits_for(static_cast<uint64_t>(ncols));
+        SPHB_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, bytes, tk0.p, tk1.p, static_cast<int>(nnz), 0, end_bit, s));
+        DevBuf<uint8_t> tmp;
+        SPHB_CUDA(tmp.alloc(bytes, s));
+        SPHB_CUDA(cub::DeviceRadixSort::SortKeys(tmp.p, bytes, tk0.p, tk1.p, static_cast<int>(nnz), 0, end_bit, s));
+        count_launch(3);
+    }
+    gm_rowptr_lower_bound<<<gm_grid(ncols + 1, 256, sms), 256, 0, s>>>(tk1.p, nnz, 32, ncols, colptr.p);
+    count_launch();
+    int cap = 64;
+    while (cap < k + 32) cap <<= 1;
+    const size_t smem = static_cast<size_t>(LK_WARPS) * cap * sizeof(uint64_t);
+    SPHB_CUDA(cudaFuncSetAttribute(level_knn_walks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int64_t grid = std::min<int64_t>(nrows, static_cast<int64_t>(sms) * 2);
+    while (grid > 1 && static_cast<double>(grid) * nrows * 8.0 > 8.0 * (1ull << 30)) grid /= 2;
+    DevBuf<float> acc;
+    DevBuf<uint32_t> touched;
+    SPHB_CUDA(acc.alloc(static_cast<size_t>(grid) * nrows, s));
+    SPHB_CUDA(touched.alloc(static_cast<size_t>(grid) * nrows, s));
+    SPHB_CUDA(cudaMemsetAsync(acc.p, 0, static_cast<size_t>(grid) * nrows * sizeof(float), s));
+    LkParams P{};
+    P.n = nrows; P.rowptr = d_rowptr; P.rowkeys = d_rowkeys; P.colptr = colptr.p; P.tkeys = tk1.p;
+    P.mode = 2; P.k = static_cast<int>(k); P.cap = cap; P.acc = acc.p; P.touched = touched.p; P.out_ids = d_out_ids; P.out_dist = d_out_dist;
     level_knn_walks_kernel<<<static_cast<unsigned>(grid), LK_WARPS * 32, smem, s>>>(P);
     count_launch();
     SPHB_CUDA(cudaGetLastError());

@@ -209,19 +209,13 @@ __global__ void overlap_pairs(const uint64_t* __restrict__ ukeys, const int64_t*
     }
 }
 
-int neighbor_overlap_dev(const int64_t* d_knn_ids, int64_t n, int k, int64_t ncomp, const int64_t* d_comp_ptr, const int64_t* d_comp_pix,
-                         int64_t npix, const int64_t* d_pa, const int64_t* d_pb, int64_t npairs, float* d_out, cudaStream_t s) {
-    if (npairs <= 0) return 0;
-    if (n >= (1ll << 32) || ncomp >= (1ll << 31)) return fail(SPHB_ERR_UNSUPPORTED, "neighbor_overlap: ids must fit 32 bits");
+// The sorted-unique unions U_c of ALL components: uk = sorted (component << 32 | id) keys, uptr[ncomp + 1].
+static int overlap_build_unions(const int64_t* d_knn_ids, int k, int64_t ncomp, const int64_t* d_comp_ptr, const int64_t* d_comp_pix, int64_t npix,
+                                DevBuf<uint64_t>& uk, DevBuf<int64_t>& uptr, int* total_out, cudaStream_t s) {
     const int sms = ctx().num_sms;
     const int64_t num = npix * k;
-    if (num == 0) {
-        SPHB_CUDA(cudaMemsetAsync(d_out, 0, npairs * sizeof(float), s));
-        return 0;
-    }
-    DevBuf<uint64_t> k0, k1, uk;
+    DevBuf<uint64_t> k0, k1;
     DevBuf<int> head, pos;
-    DevBuf<int64_t> uptr;
     SPHB_CUDA(k0.alloc(num, s));
     SPHB_CUDA(k1.alloc(num, s));
     SPHB_CUDA(head.alloc(num + 1, s));
@@ -251,10 +245,53 @@ int neighbor_overlap_dev(const int64_t* d_knn_ids, int64_t n, int k, int64_t nco
     SPHB_CUDA(uk.alloc(std::max(total, 1), s));
     overlap_compact<<<grid(num), 256, 0, s>>>(k1.p, head.p, pos.p, num, uk.p);
     overlap_rowptr<<<grid(ncomp + 1), 256, 0, s>>>(uk.p, total, ncomp, uptr.p);
-    overlap_pairs<<<grid(npairs * 32), 256, 0, s>>>(uk.p, uptr.p, d_pa, d_pb, npairs, d_out);
-    count_launch(3);
+    count_launch(2);
     SPHB_CUDA(cudaGetLastError());
+    SPHB_CUDA(cudaStreamSynchronize(s));  // k0 / k1 / head / pos are released on return
+    *total_out = total;
     return 0;
+}
+
+int neighbor_overlap_dev(const int64_t* d_knn_ids, int64_t n, int k, int64_t ncomp, const int64_t* d_comp_ptr, const int64_t* d_comp_pix,
+                         int64_t npix, const int64_t* d_pa, const int64_t* d_pb, int64_t npairs, float* d_out, cudaStream_t s) {
+    if (npairs <= 0) return 0;
+    if (n >= (1ll << 32) || ncomp >= (1ll << 31)) return fail(SPHB_ERR_UNSUPPORTED, "neighbor_overlap: ids must fit 32 bits");
+    const int sms = ctx().num_sms;
+    if (npix * k == 0) {
+        SPHB_CUDA(cudaMemsetAsync(d_out, 0, npairs * sizeof(float), s));
+        return 0;
+    }
+    DevBuf<uint64_t> uk;
+    DevBuf<int64_t> uptr;
+    int total = 0;
+    if (int rc = overlap_build_unions(d_knn_ids, k, ncomp, d_comp_ptr, d_comp_pix, npix, uk, uptr, &total, s)) return rc;
+    const unsigned grid = static_cast<unsigned>(std::max<int64_t>(1, std::min<int64_t>((npairs * 32 + 255) / 256, static_cast<int64_t>(sms) * 8)));
+    overlap_pairs<<<grid, 256, 0, s>>>(uk.p, uptr.p, d_pa, d_pb, npairs, d_out);
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return 0;
+}
+
+// implemented in graph_merge.cu
+int level_knn_sets_dev(int64_t nrows, int64_t ncols, const int64_t* d_rowptr, const uint64_t* d_rowkeys, int64_t nnz, int64_t k, int64_t* d_out_ids,
+                       float* d_out_dist, cudaStream_t s);
+
+// D7 in the neighbour-overlap metric: exact level kNN over the components' kNN-id unions.
+int level_knn_overlap_dev(const int64_t* d_knn_ids, int64_t n, int k_data, int64_t ncomp, const int64_t* d_comp_ptr, const int64_t* d_comp_pix,
+                          int64_t npix, int64_t k, int64_t* d_out_ids, float* d_out_dist, cudaStream_t s) {
+    if (n >= (1ll << 32) || ncomp >= (1ll << 31)) return fail(SPHB_ERR_UNSUPPORTED, "level_knn_overlap: ids must fit 32 bits");
+    DevBuf<uint64_t> uk;
+    DevBuf<int64_t> uptr;
+    int total = 0;
+    if (npix * k_data > 0) {
+        if (int rc = overlap_build_unions(d_knn_ids, k_data, ncomp, d_comp_ptr, d_comp_pix, npix, uk, uptr, &total, s)) return rc;
+    } else {
+        SPHB_CUDA(uptr.alloc(ncomp + 1, s));
+        SPHB_CUDA(uk.alloc(1, s));
+        SPHB_CUDA(cudaMemsetAsync(uptr.p, 0, (ncomp + 1) * sizeof(int64_t), s));
+    }
+    return level_knn_sets_dev(ncomp, n, uptr.p, uk.p, total, k, d_out_ids, d_out_dist, s);
 }
 
 }  // namespace sphb
@@ -292,6 +329,36 @@ SPHB_API int sphb_find_k(int64_t n, const int64_t* rowptr, const uint32_t* col, 
     SPHB_CUDA(cudaMemcpyAsync(out_cols, oc.p, n * k * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaMemcpyAsync(out_vals, ov.p, n * k * sizeof(float), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaMemcpyAsync(row_nnz, on.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_level_knn_overlap(const int64_t* knn_ids, int64_t n, int k_data, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix,
+                                    int64_t k, int64_t* out_ids, float* out_dist) {
+    if (int rc = ensure_init()) return rc;
+    if (!knn_ids || n <= 0 || k_data <= 0 || ncomp <= 0 || !comp_ptr || comp_ptr[0] != 0 || k <= 0 || !out_ids || !out_dist)
+        return fail(SPHB_ERR_INVALID, "level_knn_overlap: bad arguments");
+    const int64_t npix = comp_ptr[ncomp];
+    if (npix < 0 || (npix > 0 && !comp_pix)) return fail(SPHB_ERR_INVALID, "level_knn_overlap: bad arguments");
+    for (int64_t e = 0; e < npix; ++e)
+        if (comp_pix[e] < 0 || comp_pix[e] >= n) return fail(SPHB_ERR_INVALID, "level_knn_overlap: pixel id out of range");
+    for (int64_t e = 0; e < n * k_data; ++e)
+        if (knn_ids[e] < 0 || knn_ids[e] >= n) return fail(SPHB_ERR_INVALID, "level_knn_overlap: neighbour id out of range");
+    cudaStream_t s = ctx().stream;
+    DevBuf<int64_t> dk, dcp, dpx, oids;
+    DevBuf<float> odist;
+    const size_t nk = static_cast<size_t>(ncomp) * static_cast<size_t>(k);
+    SPHB_CUDA(dk.alloc(n * k_data, s));
+    SPHB_CUDA(dcp.alloc(ncomp + 1, s));
+    SPHB_CUDA(dpx.alloc(std::max<int64_t>(npix, 1), s));
+    SPHB_CUDA(oids.alloc(nk, s));
+    SPHB_CUDA(odist.alloc(nk, s));
+    SPHB_CUDA(cudaMemcpyAsync(dk.p, knn_ids, n * k_data * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    SPHB_CUDA(cudaMemcpyAsync(dcp.p, comp_ptr, (ncomp + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    if (npix) SPHB_CUDA(cudaMemcpyAsync(dpx.p, comp_pix, npix * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    if (int rc = level_knn_overlap_dev(dk.p, n, k_data, ncomp, dcp.p, dpx.p, npix, k, oids.p, odist.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(out_ids, oids.p, nk * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(out_dist, odist.p, nk * sizeof(float), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaStreamSynchronize(s));
     return SPHB_OK;
 }

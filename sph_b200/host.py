@@ -346,9 +346,10 @@ class LevelSimilarities:
     Bhattacharyya distances) or the top-k transition values, then the in-place Gaussian rows with ignore = -1,
     zero removal (:566-581) and symmetrizeOutput (:589-623)."""
 
-    def __init__(self, knn_graph: Graph, random_walks: list[SparseRows] | None = None):
+    def __init__(self, knn_graph: Graph, random_walks: list[SparseRows] | None = None, hierarchy=None):
         self._graph = knn_graph
-        self._rw = random_walks or []
+        self._rw = random_walks or (hierarchy.randomWalks if hierarchy is not None else [])
+        self._hierarchy = hierarchy  # an ImageHierarchy: component -> pixel maps for the neighbour-overlap metric
         self._prob: dict[int, SparseRows] = {}
         self._perplexities: list[float] = []
         self._ks: list[int] = []
@@ -359,6 +360,12 @@ class LevelSimilarities:
         exact kNN in the component metric (computeExactKnn, :211-252) or the walks themselves as distances (:346-389)."""
         from . import capi
 
+        if lss.componentSim == ComponentSim.NEIGH_OVERLAP:
+            ptr, pix = self._hierarchy.representedDataPoints(level)
+            k_l = min(self._ks[level], len(ptr) - 1)
+            ids, dist = capi.level_knn_overlap(self._graph.knnIndices, ptr, pix, k_l)
+            self._distance_graphs[level] = Graph(ids, dist)
+            return self._distance_graphs[level]
         rw = self._rw[level]
         k_l = min(self._ks[level], rw.n)
         if lss.knnFromWalkMetric:
@@ -377,7 +384,10 @@ class LevelSimilarities:
         from . import capi
 
         lss = lss or LevelSimilaritiesSettings()
-        sizes = [self._graph.numPoints] + [rw.n for rw in self._rw[1:]]
+        if self._hierarchy is not None:
+            sizes = list(self._hierarchy.numComponents)
+        else:
+            sizes = [self._graph.numPoints] + [rw.n for rw in self._rw[1:]]
         self._perplexities, self._ks = level_schedule(sizes, self._graph.knnIndices.shape[1])
         levels = range(len(sizes)) if lss.levelToCompute < 0 else [lss.levelToCompute]
         for level in levels:
@@ -387,11 +397,15 @@ class LevelSimilarities:
             if level == 0:
                 self._prob[0] = normalizeKnnDistances(self._graph, NormalizationScheme.TSNE, self._perplexities[0])
                 continue
-            rw = self._rw[level]
-            k_l, perp_l = min(self._ks[level], rw.n), self._perplexities[level]
-            if lss.knnFromWalkMetric or lss.forceComputeDistances:
+            overlap = lss.componentSim == ComponentSim.NEIGH_OVERLAP
+            if overlap and self._hierarchy is None:
+                log.error("LevelSimilarities::compute: NEIGH_OVERLAP needs the image hierarchy")
+                return
+            rw = None if overlap else self._rw[level]
+            k_l, perp_l = min(self._ks[level], sizes[level]), self._perplexities[level]
+            if overlap or lss.knnFromWalkMetric or lss.forceComputeDistances:
                 self.computeNearestNeighborOnLevel(level, lss)
-            if lss.knnFromWalkMetric:
+            if overlap or lss.knnFromWalkMetric:
                 # useKnnDistances (:510-515): flat Gaussian rows (tol 1e-5, ignore 0) scattered by neighbour id, skipping -1
                 g = self._distance_graphs[level]
                 temp = capi.prow_gaussian_flat(g.knnDistances, perp_l)

@@ -78,6 +78,7 @@ class Oracle:
         L.orc_remove_zeros.argtypes = [C.c_int64, i64p, u32p, f32p, i64p, u32p, f32p]
         L.orc_remove_zeros.restype = C.c_int64
         L.orc_euclid_hausdorff.argtypes = [f32p, C.c_int, i64p, i64p, i64p, i64p, C.c_int64, f32p]
+        L.orc_level_knn_overlap.argtypes = [i64p, C.c_int, C.c_int64, i64p, i64p, C.c_int64, i64p, f32p]
         L.orc_level_knn_walks.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int64, i64p, f32p]
 
     # ---- Stage A
@@ -356,6 +357,16 @@ class Oracle:
         out = np.zeros(len(pa), np.float32)
         self.lib.orc_euclid_hausdorff(_p(x, f32p), x.shape[1], _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p))
         return out
+
+    def level_knn_overlap(self, knn_ids, comp_ptr, comp_pix, k):
+        knn_ids = np.ascontiguousarray(knn_ids, np.int64)
+        comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+        comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+        ncomp = len(comp_ptr) - 1
+        ids = np.zeros((ncomp, k), np.int64)
+        dist = np.zeros((ncomp, k), np.float32)
+        self.lib.orc_level_knn_overlap(_p(knn_ids, i64p), knn_ids.shape[1], ncomp, _p(comp_ptr, i64p), _p(comp_pix, i64p), k, _p(ids, i64p), _p(dist, f32p))
+        return ids, dist
 
     def level_knn_walks(self, rowptr, col, val, k, mode=0):
         rowptr = np.ascontiguousarray(rowptr, np.int64)

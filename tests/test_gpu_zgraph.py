@@ -233,3 +233,53 @@ def test_level_similarities_topk_transition_path(capi, oracle):
     np.testing.assert_array_equal(p.rowptr, zrp)
     np.testing.assert_array_equal(p.col, zc)
     np.testing.assert_allclose(p.val, zv, rtol=1e-5, atol=1e-12)
+
+
+# ---------------------------------------------------------------- D7, neighbour-overlap metric (the default componentSim)
+def random_components(n, ncomp, seed):
+    rng = np.random.default_rng(seed)
+    lab = rng.integers(0, ncomp, n)
+    lab[:ncomp] = np.arange(ncomp)
+    order = np.argsort(lab, kind="stable")
+    ptr = np.concatenate([[0], np.cumsum(np.bincount(lab, minlength=ncomp))]).astype(np.int64)
+    return ptr, order.astype(np.int64)
+
+
+@pytest.mark.parametrize("n,kd,ncomp,k", [(24, 3, 9, 5), (3000, 12, 400, 31), (2000, 8, 1500, 64), (300, 6, 20, 33)])
+def test_level_knn_overlap_matches_oracle(capi, oracle, n, kd, ncomp, k):
+    ids, _ = random_knn_graph(n, kd, seed=n + kd)
+    ptr, pix = random_components(n, ncomp, seed=ncomp)
+    a = capi.level_knn_overlap(ids, ptr, pix, k)
+    b = oracle.level_knn_overlap(ids, ptr, pix, k)
+    np.testing.assert_array_equal(a[0], b[0])
+    np.testing.assert_array_equal(a[1], b[1])  # integer counts, one fp32 division and one subtraction: bit-exact
+
+
+def test_level_similarities_default_overlap_path(capi, oracle):
+    """The default configuration (componentSim = NEIGH_OVERLAP on both stages): hierarchy on the device, level-1 kNN in the
+    overlap metric, useKnnDistances (flat Gaussian rows, tol 1e-5), zero removal, symmetrizeTSNE — vs the oracle chain."""
+    import oracle_lib
+    from sph_b200 import host, synth
+
+    x = synth.hyperspectral(20, 16, 12, endmembers=4, seed=8)
+    ids, dist = capi.knn_exact(x, 9)
+    g = host.Graph(ids, dist)
+    ih = host.ImageHierarchy(g, x, 20, 16)
+    ih.compute(host.ImageHierarchySettings(componentSim=host.ComponentSim.NEIGH_OVERLAP, usePercentile=False))
+    assert ih.getNumLevels() >= 3
+    ls = host.LevelSimilarities(g, hierarchy=ih)
+    ls.compute(host.LevelSimilaritiesSettings(levelToCompute=1, componentSim=host.ComponentSim.NEIGH_OVERLAP))
+    ptr, pix = ih.representedDataPoints(1)
+    k1, perp1 = min(ls.getKs()[1], len(ptr) - 1), ls.getPerplexities()[1]
+    rids, rdist = oracle.level_knn_overlap(ids, ptr, pix, k1)
+    sg = ls.getSimilaritiesGraph(1)
+    np.testing.assert_array_equal(sg.knnIndices, rids)
+    np.testing.assert_array_equal(sg.knnDistances, rdist)
+    temp = oracle.prow_gaussian_flat(rdist, perp1)
+    rp, c, v = host.scatter_flat_rows(rids, temp)
+    rp, c, v = oracle.remove_zeros(rp, c, v)
+    orp, oc, ov = oracle.symmetrize(rp, c, v)
+    p = ls.getProbDist(1)
+    np.testing.assert_array_equal(p.rowptr, orp)
+    np.testing.assert_array_equal(p.col, oc)
+    np.testing.assert_allclose(p.val, ov, rtol=1e-5, atol=1e-12)

@@ -176,3 +176,93 @@ def test_bench_stdout_guard(tmp_path):
     assert r.returncode == 0, r.stderr
     assert r.stdout.strip() == '{"ok": 1}'
     assert "banner from C" in r.stderr and "banner from python" in r.stderr
+
+
+@pytest.fixture
+def capi_on_oracle(monkeypatch, oracle):
+    """Routes the ctypes entry points the host mirror calls to the CPU checker, so that the host-side control flow of
+    LevelSimilarities / ImageHierarchy can be exercised here without a GPU (test scaffolding only: the product binds the
+    CUDA library and has no such switch)."""
+    from sph_b200 import capi
+
+    o = oracle
+    monkeypatch.setattr(capi, "level_knn_overlap", lambda ids, ptr, pix, k: o.level_knn_overlap(ids, ptr, pix, k))
+    monkeypatch.setattr(capi, "level_knn_walks", lambda rp, c, v, k, mode=0: o.level_knn_walks(rp, c, v, k, mode))
+    monkeypatch.setattr(capi, "rw_as_knn_distances", lambda rp, c, v: o.rw_as_knn_distances(rp, c, v))
+    monkeypatch.setattr(capi, "prow_gaussian_flat", lambda d, p: o.prow_gaussian_flat(d, p))
+    monkeypatch.setattr(capi, "prow_gaussian_inplace", lambda rp, v, p=0.0, ig=-1: o.prow_gaussian_inplace(rp, v, p, ig))
+    monkeypatch.setattr(capi, "remove_zeros", lambda rp, c, v: o.remove_zeros(rp, c, v))
+    monkeypatch.setattr(capi, "symmetrize", lambda rp, c, v, umap=False: o.symmetrize(rp, c, v, umap=umap))
+    monkeypatch.setattr(capi, "create_similarities", lambda rp, c, v, k, pr=1e-4, variant=0, comp_sizes=None: o.create_similarities(rp, c, v, k, pr, variant, comp_sizes))
+
+    def find_k(rp, c, v, k, top):
+        n = len(rp) - 1
+        oc = np.full((n, k), 0xFFFFFFFF, np.uint32)
+        ov = np.zeros((n, k), np.float32)
+        nnz = np.zeros(n, np.int32)
+        for i in range(n):
+            cc, vv = o.find_k(c[rp[i]:rp[i + 1]], v[rp[i]:rp[i + 1]], k, top)
+            oc[i, :len(cc)], ov[i, :len(cc)], nnz[i] = cc, vv, len(cc)
+        return oc, ov, nnz
+
+    monkeypatch.setattr(capi, "find_k", find_k)
+    return capi
+
+
+def _toy_hierarchy(oracle):
+    import json
+
+    import oracle_lib
+    from sph_b200 import host
+
+    g = json.loads((ROOT / "tests" / "golden" / "hierarchy_walks_6x4.json").read_text())
+    ids = np.array(g["knn"], np.int64).reshape(24, 4)
+    dist = np.array(g["dist"], np.float32).reshape(24, 4)
+    graph = host.Graph(ids, dist)
+    return host, graph, oracle_lib.OracleOps(oracle)
+
+
+def test_level_similarities_overlap_control_flow(capi_on_oracle, oracle):
+    host, graph, ops = _toy_hierarchy(oracle)
+    ih = host.ImageHierarchy(graph, None, 6, 4, ops=ops)
+    ih.compute(host.ImageHierarchySettings(componentSim=host.ComponentSim.NEIGH_OVERLAP, usePercentile=False))
+    ls = host.LevelSimilarities(graph, hierarchy=ih)
+    ls.compute(host.LevelSimilaritiesSettings(levelToCompute=1, componentSim=host.ComponentSim.NEIGH_OVERLAP))
+    p = ls.getProbDist(1)
+    n1 = ih.numComponents[1]
+    assert p.n == n1 and ls.getSimilaritiesGraph(1).knnIndices.shape == (n1, min(ls.getKs()[1], n1))
+    dense = np.zeros((n1, n1), np.float32)
+    for i in range(n1):
+        c, v = p.row(i)
+        dense[i, c] = v
+    np.testing.assert_array_equal(dense, dense.T)          # symmetrizeTSNE ran
+    np.testing.assert_allclose(dense.sum(), n1, rtol=1e-4)  # rows were distributions before the symmetrisation
+    assert (p.val != 0).all()                               # zero removal
+
+
+@pytest.mark.parametrize("kind", ["pair_sims", "topk", "walk_knn", "rw_dist"])
+def test_level_similarities_walk_control_flow(capi_on_oracle, oracle, kind):
+    host, graph, ops = _toy_hierarchy(oracle)
+    ih = host.ImageHierarchy(graph, None, 6, 4, ops=ops)
+    ihs = host.ImageHierarchySettings(componentSim=host.ComponentSim.NEIGH_WALKS_SINGLE_OVERLAP, usePercentile=False,
+                                      rwHandling=host.RandomWalkHandling.MERGE_RW_NEW_WALKS, normKnnDistances=host.NormalizationScheme.LINEAR)
+    ih.compute(ihs, host.RandomWalkSettings(numRandomWalks=10, singleWalkLength=3, parallel=False))
+    assert ih.numComponents == [24, 9, 3, 1]
+    ls = host.LevelSimilarities(graph, hierarchy=ih)
+    lss = host.LevelSimilaritiesSettings(levelToCompute=1, componentSim=host.ComponentSim.NEIGH_WALKS_SINGLE_OVERLAP,
+                                         computeSymmetricProbDist=host.NormalizationScheme.NONE)
+    if kind == "topk":
+        lss.randomWalkPairSims = False
+    elif kind == "walk_knn":
+        lss.knnFromWalkMetric = True
+    elif kind == "rw_dist":
+        lss.forceComputeDistances = True
+    ls.compute(lss)
+    p = ls.getProbDist(1)
+    assert p.n == 9 and (np.diff(p.rowptr) >= 0).all() and (p.val != 0).all()
+    assert np.isfinite(p.val).all() and (p.val > 0).all()  # (rows need not sum to 1: with fewer entries than the perplexity the
+    # reference's search fails and falls back to 1 / (size - 1) per entry, sph/utils/HDILibHelper.hpp:98-104)
+    if kind == "walk_knn":
+        assert ls.getSimilaritiesGraph(1).knnIndices.shape[0] == 9
+    if kind == "rw_dist":
+        assert ls.getSimilaritiesGraph(1).numPoints == 9

@@ -330,15 +330,17 @@ def test_level_knn_walks_matches_pairwise(oracle, mode):
     k = 12
     ids, dist = oracle.level_knn_walks(rp, c, v, k, mode)
     pa, pb = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
-    sim = oracle.pair_sims(rp, c, v, pa.ravel(), pb.ravel(), mode).reshape(n, n)
+    if mode == 0:  # randomWalksBhattacharyya per pair, self included (the space does not special-case i == j)
+        sim = oracle.pair_sims(rp, c, v, pa.ravel(), pb.ravel(), 0).reshape(n, n)
+    else:          # randomWalksSingleOverlap(i, j) = A[i][j], one direction only
+        sim = csr_to_dense(rp, c, v)
     d = (np.float32(1) - sim).astype(np.float32)
-    d[np.arange(n), np.arange(n)] = 0
     for i in range(n):
         order = np.lexsort((np.arange(n), d[i]))[:k]
         assert ids[i].tolist() == order.tolist()
         np.testing.assert_array_equal(dist[i], d[i, order])
-    if mode == 0:  # nothing shares a column with the empty row: the lowest indices at distance exactly 1
-        assert ids[7, 0] == 7 and (dist[7, 1:] == 1).all() and ids[7, 1:].tolist() == [j for j in range(n) if j != 7][:k - 1]
+    # nothing shares a column with the empty row, itself included: the lowest indices at distance exactly 1
+    assert (dist[7] == 1).all() and ids[7].tolist() == list(range(k))
 
 
 # ---------------------------------------------------------------- full hierarchies (host merge loop on the oracle)
@@ -381,3 +383,25 @@ def test_full_hierarchy_golden(oracle, name):
         for rw in ih.randomWalks:
             sums = np.add.reduceat(rw.val, rw.rowptr[:-1])
             np.testing.assert_allclose(sums, 1.0, atol=1e-3)
+
+
+def test_level_knn_overlap_matches_pairwise(oracle):
+    # golden unions of testKnnOverlap (level-1 components) + the all-pairs definition through orc_neighbor_overlap
+    g = gold("knn_overlap.json")
+    knn = np.array(g["knn"], np.int64).reshape(-1, g["k"])
+    children = g["children_l1"]
+    ptr = np.concatenate([[0], np.cumsum([len(c) for c in children])]).astype(np.int64)
+    pix = np.array([p for c in children for p in c], np.int64)
+    n = len(children)
+    k = 5
+    ids, dist = oracle.level_knn_overlap(knn, ptr, pix, k)
+    pa, pb = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    sim = oracle.neighbor_overlap(knn, ptr, pix, pa.ravel(), pb.ravel()).reshape(n, n)
+    d = (np.float32(1) - sim).astype(np.float32)
+    for i in range(n):
+        order = np.lexsort((np.arange(n), d[i]))[:k]
+        assert ids[i].tolist() == order.tolist()
+        np.testing.assert_array_equal(dist[i], d[i, order])
+        assert ids[i, 0] == i and dist[i, 0] == 0  # a component overlaps itself completely
+    # golden: components 8 and 0 of level 1 share exactly one id out of min(5, 5) (tests/HierarchyTest.cpp:157-226)
+    assert d[8, 0] == np.float32(1) - np.float32(1) / np.float32(5)
