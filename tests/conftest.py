@@ -15,6 +15,10 @@ def pytest_configure(config):
 
 
 def _has_gpu() -> bool:
+    if os.environ.get("SPHB_EMULATE") == "1":
+        # tests/emu: the -m gpu tests of the CSR / graph passes run against the CPU emulation build of the same kernel
+        # sources (SPHB_LIB must point at tests/emu/_build/libsphb200_emu.so); a logic check, never a measurement
+        return True
     try:
         import torch
 
