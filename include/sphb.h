@@ -192,6 +192,12 @@ SPHB_API int sphb_neighbor_overlap(const int64_t* knn_ids, int64_t n, int k, int
  */
 SPHB_API int sphb_symmetrize_graph(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist,
                                    int64_t* out_rowptr, int64_t* out_ids, float* out_dist, int64_t cap, int64_t* out_nnz);
+/* Connected components of the kNN graph with edges taken as undirected — utils::labelGraphWeakComponents, and
+ * labelGraphStrongComponents on a symmetric graph (sph/utils/GraphUtils.cpp:371-423), as
+ * NearestNeighbors::computeConnectedComponents uses them (sph/NearestNeighbors.cpp:318-409).  labels[n]: component of
+ * every point, components numbered in ascending order of their lowest point (the order Boost reaches them);
+ * *num_components receives their number. */
+SPHB_API int sphb_weak_components(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, int64_t* labels, int64_t* num_components);
 /* utils::mergeGraphNodes (sph/utils/SparseMatrixAlgorithms.cpp:486-561): node r merges into parents[r]; the
  * distance of (parent(r), parent(c)) is the minimum over the children; rows ordered by (distance, index), self first.
  * cap: nnz of the input always suffices. */

@@ -292,3 +292,31 @@ ORC_API void orc_level_knn_overlap(const int64_t* knn_ids, int k_data, int64_t n
         }
     }
 }
+
+// F2.  Connected components with edges taken as undirected (utils::labelGraphWeakComponents, sph/utils/GraphUtils.cpp:371-407):
+// the reference symmetrises and runs boost::strong_components, whose DFS starts at vertex 0, 1, 2, ... and therefore numbers
+// the components in ascending order of their lowest vertex.  Returns the number of components.
+ORC_API int64_t orc_weak_components(int64_t n, const int64_t* rowptr, const int64_t* ids, int64_t* labels) {
+    std::vector<int64_t> parent(static_cast<size_t>(n));
+    for (int64_t v = 0; v < n; ++v) parent[v] = v;
+    auto find = [&](int64_t a) {
+        while (parent[a] != a) {
+            parent[a] = parent[parent[a]];
+            a = parent[a];
+        }
+        return a;
+    };
+    for (int64_t v = 0; v < n; ++v)
+        for (int64_t e = rowptr[v]; e < rowptr[v + 1]; ++e) {
+            const int64_t a = find(v), b = find(ids[e]);
+            if (a != b) parent[std::max(a, b)] = std::min(a, b);
+        }
+    int64_t next = 0;
+    std::vector<int64_t> number(static_cast<size_t>(n), -1);
+    for (int64_t v = 0; v < n; ++v) {
+        const int64_t r = find(v);
+        if (number[r] < 0) number[r] = next++;
+        labels[v] = number[r];
+    }
+    return next;
+}

@@ -57,6 +57,7 @@ SIGNATURES = {
     "sphb_find_k": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_int, u32p, f32p, i32p]),
     "sphb_neighbor_overlap": (C.c_int, [i64p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_symmetrize_graph": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, i64p, f32p, C.c_int64, i64p]),
+    "sphb_weak_components": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, i64p, i64p]),
     "sphb_merge_graph_nodes": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, u64p, C.c_int64, i64p, i64p, f32p, C.c_int64, i64p]),
     "sphb_merge_data_distances": (C.c_int, [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, i64p, u32p, f32p, C.c_int64, i64p]),
     "sphb_rw_as_knn_distances": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, i64p, f32p, i64p]),
@@ -336,6 +337,21 @@ def symmetrize_graph(ids, dist, rowptr=None):
                                         _p(od, f32p), cap, _p(nnz, i64p)))
     m = int(nnz[0])
     return orp, oi[:m].copy(), od[:m].copy()
+
+
+def weak_components(ids, rowptr=None):
+    """Connected components (edges undirected): (num_components, labels int64 [n])."""
+    ids = np.ascontiguousarray(ids, np.int64)
+    if rowptr is None:
+        n, k = ids.shape
+        rp = None
+    else:
+        rp = np.ascontiguousarray(rowptr, np.int64)
+        n, k = len(rp) - 1, 0
+    labels = np.zeros(max(n, 1), np.int64)
+    num = np.zeros(1, np.int64)
+    _check(load().sphb_weak_components(n, _p(rp, i64p) if rp is not None else None, k, _p(ids, i64p), _p(labels, i64p), _p(num, i64p)))
+    return int(num[0]), labels[:n]
 
 
 def merge_graph_nodes(ids, dist, parents, n_merged: int, rowptr=None):

@@ -745,6 +745,91 @@ int level_knn_sets_dev(int64_t nrows, int64_t ncols, const int64_t* d_rowptr, co
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// F2: connected components of the (symmetrised or plain) kNN graph — utils::labelGraphWeakComponents /
+// labelGraphStrongComponents on a symmetric graph (sph/utils/GraphUtils.cpp:371-423), the labelling behind
+// NearestNeighbors::computeConnectedComponents (sph/NearestNeighbors.cpp:318-409).  Edges are taken as undirected.
+// Min-label hooking + pointer jumping: label[x] <= x always (a forest of decreasing pointers), every edge hooks the
+// larger of its two labels under the smaller (atomicMin), jumping flattens the trees, repeat until no edge joins two
+// labels.  The root of a component is its lowest vertex; components are numbered in ascending order of that vertex,
+// which is the order boost::strong_components reaches them on a symmetric graph.
+// ---------------------------------------------------------------------------------------------
+namespace {
+__global__ void cc_init(int64_t n, unsigned int* __restrict__ label) {
+    for (int64_t v = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < n; v += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        label[v] = static_cast<unsigned int>(v);
+}
+__global__ void cc_hook(int64_t n, const int64_t* __restrict__ rowptr, const int64_t* __restrict__ ids, unsigned int* label, int* __restrict__ changed) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t v = warp; v < n; v += nwarps) {
+        for (int64_t e = rowptr[v] + lane; e < rowptr[v + 1]; e += 32) {
+            const unsigned int a = label[v], b = label[ids[e]];
+            if (a != b) {
+                atomicMin(label + max(a, b), min(a, b));
+                *changed = 1;
+            }
+        }
+    }
+}
+__global__ void cc_jump(int64_t n, unsigned int* label) {
+    for (int64_t v = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < n; v += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        unsigned int l = label[v];
+        while (true) {
+            const unsigned int ll = label[l];
+            if (ll == l) break;
+            l = ll;
+        }
+        label[v] = l;
+    }
+}
+__global__ void cc_flag_roots(int64_t n, const unsigned int* __restrict__ label, int* __restrict__ root) {
+    for (int64_t v = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v <= n; v += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        root[v] = (v < n && label[v] == static_cast<unsigned int>(v)) ? 1 : 0;
+}
+__global__ void cc_number(int64_t n, const unsigned int* __restrict__ label, const int* __restrict__ rank, int64_t* __restrict__ out) {
+    for (int64_t v = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < n; v += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        out[v] = rank[label[v]];
+}
+}  // namespace
+
+int weak_components_dev(int64_t n, const int64_t* d_rowptr, const int64_t* d_ids, int64_t* d_labels, int64_t* num_components, cudaStream_t s) {
+    if (n >= (1ll << 31)) return fail(SPHB_ERR_UNSUPPORTED, "weak_components: n must be < 2^31");
+    const int sms = ctx().num_sms;
+    DevBuf<unsigned int> label;
+    DevBuf<int> changed, root, rank;
+    SPHB_CUDA(label.alloc(n, s));
+    SPHB_CUDA(changed.alloc(1, s));
+    SPHB_CUDA(root.alloc(n + 1, s));
+    SPHB_CUDA(rank.alloc(n + 1, s));
+    cc_init<<<gm_grid(n, 256, sms), 256, 0, s>>>(n, label.p);
+    count_launch();
+    bool done = false;
+    for (int iter = 0; iter < 4096 && !done; ++iter) {  // each round at least halves the number of trees per component
+        SPHB_CUDA(cudaMemsetAsync(changed.p, 0, sizeof(int), s));
+        cc_hook<<<gm_grid(n * 32, 256, sms), 256, 0, s>>>(n, d_rowptr, d_ids, label.p, changed.p);
+        cc_jump<<<gm_grid(n, 256, sms), 256, 0, s>>>(n, label.p);
+        count_launch(2);
+        int h = 0;
+        SPHB_CUDA(cudaMemcpyAsync(&h, changed.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+        SPHB_CUDA(cudaStreamSynchronize(s));
+        done = h == 0;
+    }
+    if (!done) return fail(SPHB_ERR_CUDA, "weak_components: label propagation did not converge");
+    cc_flag_roots<<<gm_grid(n + 1, 256, sms), 256, 0, s>>>(n, label.p, root.p);
+    count_launch();
+    if (int rc = exclusive_sum<int>(root.p, rank.p, n + 1, s)) return rc;
+    cc_number<<<gm_grid(n, 256, sms), 256, 0, s>>>(n, label.p, rank.p, d_labels);
+    count_launch();
+    int total = 0;
+    SPHB_CUDA(cudaMemcpyAsync(&total, rank.p + n, sizeof(int), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaGetLastError());
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    *num_components = total;
+    return 0;
+}
+
 }  // namespace sphb
 
 using namespace sphb;
@@ -826,6 +911,32 @@ extern "C" {
 SPHB_API int sphb_symmetrize_graph(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, int64_t* out_rowptr,
                                    int64_t* out_ids, float* out_dist, int64_t cap, int64_t* out_nnz) {
     return graph_minmerge_host("symmetrize_graph", n, rowptr, k, ids, dist, nullptr, std::max<int64_t>(n, 1), out_rowptr, out_ids, out_dist, cap, out_nnz);
+}
+
+SPHB_API int sphb_weak_components(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, int64_t* labels, int64_t* num_components) {
+    if (int rc = ensure_init()) return rc;
+    std::vector<int64_t> tmp;
+    const int64_t* rp = nullptr;
+    if (n < 0 || !num_components || (n > 0 && !labels) || graph_rowptr(n, rowptr, k, tmp, &rp)) return fail(SPHB_ERR_INVALID, "weak_components: bad arguments");
+    if (n == 0) {
+        *num_components = 0;
+        return SPHB_OK;
+    }
+    const int64_t nnz = rp[n];
+    if (nnz > 0 && !ids) return fail(SPHB_ERR_INVALID, "weak_components: bad arguments");
+    for (int64_t e = 0; e < nnz; ++e)
+        if (ids[e] < 0 || ids[e] >= n) return fail(SPHB_ERR_INVALID, "weak_components: neighbour id out of range");
+    cudaStream_t s = ctx().stream;
+    DevBuf<int64_t> drp, dids, dl;
+    if (int rc = up(drp, rp, n + 1, s)) return rc;
+    if (int rc = up(dids, ids, nnz, s)) return rc;
+    SPHB_CUDA(dl.alloc(n, s));
+    int64_t nc = 0;
+    if (int rc = weak_components_dev(n, drp.p, dids.p, dl.p, &nc, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(labels, dl.p, n * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    *num_components = nc;
+    return SPHB_OK;
 }
 
 SPHB_API int sphb_merge_graph_nodes(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const uint64_t* parents,

@@ -197,6 +197,7 @@ class NearestNeighbors:
         self._data = np.ascontiguousarray(data, np.float32)
         self._graph: Graph | None = None
         self._sym_graph: RaggedGraph | None = None
+        self._cc = None
         self._nns = NearestNeighborsSettings()
         self._valid = False
         self._knn_fn = knn_fn  # injectable for the CPU multi-process tests (the product default is the C ABI)
@@ -233,6 +234,9 @@ class NearestNeighbors:
         self._sym_graph = None
         if s.symmetricNeighbors and self._valid:
             self.computeSymmetrizedNnGraph()
+        self._cc = None
+        if s.computeConnectComponents and self._valid:
+            self.computeConnectedComponents()
 
     def computeSymmetrizedNnGraph(self):
         """NearestNeighbors::computeSymmetrizedNnGraph (sph/NearestNeighbors.cpp:411-492) -> utils::symmetrizeGraph."""
@@ -249,6 +253,27 @@ class NearestNeighbors:
             return None
         self._sym_graph = RaggedGraph(rp, ids, dist, symmetric=True)
         return self._sym_graph
+
+    def computeConnectedComponents(self):
+        """NearestNeighbors::computeConnectedComponents (sph/NearestNeighbors.cpp:318-409): strong components of the symmetric
+        graph when it exists, else weak components of the kNN graph — both are the undirected components."""
+        from . import capi
+
+        if self._graph is None:
+            log.warning("NearestNeighbors::computeConnectedComponents: _knn graph is not computed yet, call compute() first")
+            return None
+        try:
+            if self._sym_graph is not None:
+                self._cc = capi.weak_components(self._sym_graph.knnIndices, self._sym_graph.rowptr)
+            else:
+                self._cc = capi.weak_components(self._graph.knnIndices)
+        except Exception as e:
+            log.error("NearestNeighbors::computeConnectedComponents failed: %s", e)
+            return None
+        return self._cc
+
+    def getConnectedComponents(self):
+        return self._cc
 
     def _symmetrize(self, ids, dist):
         from . import capi

@@ -78,6 +78,8 @@ class Oracle:
         L.orc_remove_zeros.argtypes = [C.c_int64, i64p, u32p, f32p, i64p, u32p, f32p]
         L.orc_remove_zeros.restype = C.c_int64
         L.orc_euclid_hausdorff.argtypes = [f32p, C.c_int, i64p, i64p, i64p, i64p, C.c_int64, f32p]
+        L.orc_weak_components.argtypes = [C.c_int64, i64p, i64p, i64p]
+        L.orc_weak_components.restype = C.c_int64
         L.orc_level_knn_overlap.argtypes = [i64p, C.c_int, C.c_int64, i64p, i64p, C.c_int64, i64p, f32p]
         L.orc_level_knn_walks.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int64, i64p, f32p]
 
@@ -357,6 +359,17 @@ class Oracle:
         out = np.zeros(len(pa), np.float32)
         self.lib.orc_euclid_hausdorff(_p(x, f32p), x.shape[1], _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p))
         return out
+
+    def weak_components(self, ids, rowptr=None):
+        ids = np.ascontiguousarray(ids, np.int64)
+        if rowptr is None:
+            n, k = ids.shape
+            rowptr = np.arange(n + 1, dtype=np.int64) * k
+        rowptr = np.ascontiguousarray(rowptr, np.int64)
+        n = len(rowptr) - 1
+        labels = np.zeros(max(n, 1), np.int64)
+        num = self.lib.orc_weak_components(n, _p(rowptr, i64p), _p(ids.reshape(-1), i64p), _p(labels, i64p))
+        return int(num), labels[:n]
 
     def level_knn_overlap(self, knn_ids, comp_ptr, comp_pix, k):
         knn_ids = np.ascontiguousarray(knn_ids, np.int64)

@@ -31,7 +31,7 @@ def test_overlap_hierarchy_matches_oracle_on_synthetic_image(capi, oracle):
     from sph_b200 import host, synth
 
     x = synth.hyperspectral(24, 20, 16, endmembers=4, seed=3)
-    ids, dist = capi.knn_exact(x, 9)
+    ids, dist = oracle.knn_reference_graph(x, 9)  # input only: the device kNN is bit-identical to it (test_gpu_knn.py)
     g = host.Graph(ids, dist)
     ihs = host.ImageHierarchySettings(componentSim=host.ComponentSim.NEIGH_OVERLAP, usePercentile=False)
     a = host.ImageHierarchy(g, x, 24, 20)

@@ -405,3 +405,16 @@ def test_level_knn_overlap_matches_pairwise(oracle):
         assert ids[i, 0] == i and dist[i, 0] == 0  # a component overlaps itself completely
     # golden: components 8 and 0 of level 1 share exactly one id out of min(5, 5) (tests/HierarchyTest.cpp:157-226)
     assert d[8, 0] == np.float32(1) - np.float32(1) / np.float32(5)
+
+
+def test_weak_components_golden(oracle):
+    g = gold("components_9.json")
+    num, labels = oracle.weak_components(np.array(g["ids"], np.int64).reshape(-1, g["k"]))
+    assert num == g["num_components"] and labels.tolist() == g["labels"]
+    # the 24-point kNN table of testSymmetrizeKnnGraph is one component once edges are undirected; numbering follows the lowest vertex
+    g2 = gold("symmetrize_graph_24.json")
+    num2, labels2 = oracle.weak_components(np.array(g2["ids"], np.int64).reshape(-1, g2["k"]))
+    assert num2 == 1 and (labels2 == 0).all()
+    ids = np.array([[0, 3], [1, 2], [2, 1], [3, 0], [4, 4]], np.int64)
+    num3, labels3 = oracle.weak_components(ids)
+    assert num3 == 3 and labels3.tolist() == [0, 1, 1, 0, 2]
