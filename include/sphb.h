@@ -120,6 +120,13 @@ SPHB_API int sphb_prow_gaussian_graph(const int64_t* ids, const float* dist, int
                                       uint32_t* cols, float* vals, double* sigma);
 SPHB_API int sphb_prow_gaussian_graph_dev(const int64_t* d_ids, const float* d_dist, int64_t n, int k, float perplexity,
                                           uint32_t* d_cols, float* d_vals, double* d_sigma, void* stream);
+/* The same two row builders for a RAGGED graph (utils::Graph with per-point neighbour counts — merged or symmetrised
+ * graphs; both reference functions take any GraphBaseInterface, sph/utils/GraphNormalization.cpp:191-411; reached with
+ * the merged data graph from Hierarchy::updateRandomWalks, sph/utils/Hierarchy.cpp:317-336).  rowptr int64[n+1], every row
+ * starts with the point itself; linear = 0 Gaussian (perplexity <= 0 means (k_p - 1) / 3 per row), 1 linear.
+ * out_rowptr[n+1] (row p holds k_p - 1 column-sorted entries), out_cols / out_vals: rowptr[n] - n entries. */
+SPHB_API int sphb_prow_graph_ragged(int64_t n, const int64_t* rowptr, const int64_t* ids, const float* dist, float perplexity, int linear,
+                                    int64_t* out_rowptr, uint32_t* out_cols, float* out_vals);
 /* utils::computeLinearDistributions (sph/utils/GraphNormalization.cpp:340-411). */
 SPHB_API int sphb_prow_linear_graph(const int64_t* ids, const float* dist, int64_t n, int k,
                                     uint32_t* cols, float* vals);

@@ -148,6 +148,32 @@ ORC_API void orc_prow_gaussian_flat(const float* dist, int64_t n, int k, double 
 }
 
 // B5: linear rows: p = normalise(1/(1+d)) over neighbours 1..k-1.
+// B2 / B5 on a ragged graph (any GraphBaseInterface, GraphNormalization.cpp:191-411): row p = [rowptr[p], rowptr[p+1]), the
+// point itself first; k_p - 1 column-sorted output entries per row starting at rowptr[p] - p.
+ORC_API void orc_prow_graph_ragged(int64_t n, const int64_t* rowptr, const int64_t* ids, const float* dist, float fixed_perplexity, int linear,
+                                   int64_t* out_rowptr, uint32_t* out_cols, float* out_vals) {
+    for (int64_t p = 0; p <= n; ++p) out_rowptr[p] = rowptr[p] - p;
+#pragma omp parallel for schedule(static)
+    for (int64_t p = 0; p < n; ++p) {
+        const int64_t b = rowptr[p];
+        const int nn = static_cast<int>(rowptr[p + 1] - b), nn_eff = nn - 1;
+        if (nn_eff <= 0) continue;
+        std::vector<float> condProb(nn, -1.f);
+        if (linear) {
+            for (int t = 1; t < nn; ++t) condProb[t] = 1.0f / (1.0f + dist[b + t]);
+            normalize_unit(condProb.data() + 1, nn_eff);
+        } else {
+            const float perplexity = fixed_perplexity > 0 ? fixed_perplexity : nn_eff / 3.f;
+            const double sigma = gaussian_fixed_perplexity(dist + b, condProb.data(), nn, perplexity, 200, 1e-6, 0);
+            if (sigma < 0.001) min_sigma_fallback(dist + b, condProb.data(), nn, true);
+        }
+        std::map<uint32_t, float> row;
+        for (int t = 1; t < nn; ++t) row[static_cast<uint32_t>(ids[b + t])] = condProb[t];
+        int64_t e = out_rowptr[p];
+        for (auto& kv : row) { out_cols[e] = kv.first; out_vals[e] = kv.second; ++e; }
+    }
+}
+
 ORC_API void orc_prow_linear_graph(const int64_t* ids, const float* dist, int64_t n, int k, uint32_t* out_cols, float* out_vals) {
 #pragma omp parallel for schedule(static)
     for (int64_t p = 0; p < n; ++p) {

@@ -57,6 +57,7 @@ SIGNATURES = {
     "sphb_find_k": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_int, u32p, f32p, i32p]),
     "sphb_neighbor_overlap": (C.c_int, [i64p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_symmetrize_graph": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, i64p, f32p, C.c_int64, i64p]),
+    "sphb_prow_graph_ragged": (C.c_int, [C.c_int64, i64p, i64p, f32p, C.c_float, C.c_int, i64p, u32p, f32p]),
     "sphb_weak_components": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, i64p, i64p]),
     "sphb_merge_graph_nodes": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, u64p, C.c_int64, i64p, i64p, f32p, C.c_int64, i64p]),
     "sphb_merge_data_distances": (C.c_int, [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, i64p, u32p, f32p, C.c_int64, i64p]),
@@ -337,6 +338,21 @@ def symmetrize_graph(ids, dist, rowptr=None):
                                         _p(od, f32p), cap, _p(nnz, i64p)))
     m = int(nnz[0])
     return orp, oi[:m].copy(), od[:m].copy()
+
+
+def prow_graph_ragged(rowptr, ids, dist, perplexity: float = 0.0, linear: bool = False):
+    """Gaussian / linear probability rows of a ragged graph: CSR (rowptr, cols, vals)."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    ids = np.ascontiguousarray(ids, np.int64)
+    dist = np.ascontiguousarray(dist, np.float32)
+    n = len(rowptr) - 1
+    m = max(int(rowptr[-1]) - n, 0)
+    orp = np.zeros(n + 1, np.int64)
+    oc = np.zeros(max(m, 1), np.uint32)
+    ov = np.zeros(max(m, 1), np.float32)
+    _check(load().sphb_prow_graph_ragged(n, _p(rowptr, i64p), _p(ids, i64p), _p(dist, f32p), perplexity, int(linear), _p(orp, i64p), _p(oc, u32p),
+                                         _p(ov, f32p)))
+    return orp, oc[:m].copy(), ov[:m].copy()
 
 
 def weak_components(ids, rowptr=None):

@@ -832,6 +832,11 @@ int weak_components_dev(int64_t n, const int64_t* d_rowptr, const int64_t* d_ids
 
 }  // namespace sphb
 
+namespace sphb {
+// implemented in prow.cu
+int prow_graph_ragged_launch(const int64_t* d_rowptr, const int64_t* d_ids, const float* d_dist, int64_t n, int max_k, float perplexity, int mode,
+                             uint32_t* d_cols, float* d_vals, cudaStream_t stream);
+}
 using namespace sphb;
 
 // ---------------------------------------------------------------------------------------------
@@ -911,6 +916,39 @@ extern "C" {
 SPHB_API int sphb_symmetrize_graph(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, int64_t* out_rowptr,
                                    int64_t* out_ids, float* out_dist, int64_t cap, int64_t* out_nnz) {
     return graph_minmerge_host("symmetrize_graph", n, rowptr, k, ids, dist, nullptr, std::max<int64_t>(n, 1), out_rowptr, out_ids, out_dist, cap, out_nnz);
+}
+
+SPHB_API int sphb_prow_graph_ragged(int64_t n, const int64_t* rowptr, const int64_t* ids, const float* dist, float perplexity, int linear,
+                                    int64_t* out_rowptr, uint32_t* out_cols, float* out_vals) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || !rowptr || rowptr[0] != 0 || !out_rowptr) return fail(SPHB_ERR_INVALID, "prow_graph_ragged: bad arguments");
+    int64_t max_k = 0;
+    for (int64_t p = 0; p < n; ++p) {
+        const int64_t kp = rowptr[p + 1] - rowptr[p];
+        if (kp < 1) return fail(SPHB_ERR_INVALID, "prow_graph_ragged: every row must hold at least the point itself");
+        max_k = std::max(max_k, kp);
+        out_rowptr[p] = rowptr[p] - p;
+    }
+    out_rowptr[n] = rowptr[n] - n;
+    const int64_t nnz = rowptr[n], onnz = nnz - n;
+    if (nnz > 0 && (!ids || !dist)) return fail(SPHB_ERR_INVALID, "prow_graph_ragged: bad arguments");
+    if (onnz <= 0) return SPHB_OK;
+    if (!out_cols || !out_vals) return fail(SPHB_ERR_INVALID, "prow_graph_ragged: bad arguments");
+    if (max_k > 1024) return fail(SPHB_ERR_UNSUPPORTED, "prow_graph_ragged: rows with more than 1024 neighbours unsupported");
+    cudaStream_t s = ctx().stream;
+    DevBuf<int64_t> drp, dids;
+    DevBuf<float> ddist, ov;
+    DevBuf<uint32_t> oc;
+    if (int rc = up(drp, rowptr, n + 1, s)) return rc;
+    if (int rc = up(dids, ids, nnz, s)) return rc;
+    if (int rc = up(ddist, dist, nnz, s)) return rc;
+    SPHB_CUDA(oc.alloc(onnz, s));
+    SPHB_CUDA(ov.alloc(onnz, s));
+    if (int rc = prow_graph_ragged_launch(drp.p, dids.p, ddist.p, n, static_cast<int>(max_k), perplexity, linear ? 1 : 0, oc.p, ov.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(out_cols, oc.p, onnz * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(out_vals, ov.p, onnz * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
 }
 
 SPHB_API int sphb_weak_components(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, int64_t* labels, int64_t* num_components) {

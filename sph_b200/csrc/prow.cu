@@ -240,6 +240,68 @@ __global__ void __launch_bounds__(128) prow_flat_kernel(const float* __restrict_
     }
 }
 
+// The same rows for a RAGGED graph (per-point neighbour counts: merged / symmetrised graphs,
+// computeGaussianDistributions / computeLinearDistributions take any GraphBaseInterface): row p is
+// [rowptr[p], rowptr[p+1]) with the point itself first, its k_p - 1 output entries start at rowptr[p] - p.
+template <int R>
+__global__ void __launch_bounds__(128) prow_graph_ragged_kernel(const int64_t* __restrict__ rowptr, const int64_t* __restrict__ ids,
+                                                                const float* __restrict__ dist, int64_t n, float fixed_perplexity, int mode,
+                                                                int cap, uint32_t* __restrict__ cols, float* __restrict__ vals) {
+    extern __shared__ uint64_t smem_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+    for (int64_t p = gw; p < n; p += nw) {
+        const int64_t b = rowptr[p];
+        const int k = static_cast<int>(rowptr[p + 1] - b);
+        const int ne = k - 1;
+        if (ne <= 0) continue;  // warp-uniform
+        const int64_t ob = b - p;
+        float dv[R], pv[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            dv[r] = idx < k ? dist[b + idx] : 0.f;
+            pv[r] = 0.f;
+        }
+        if (mode == 0) {
+            const float perplexity = fixed_perplexity > 0 ? fixed_perplexity : ne / 3.f;
+            const double sigma = perplexity_search<R>(dv, pv, k, lane, static_cast<double>(perplexity), 1e-6, 0);
+            if (sigma < 0.001) min_sigma_fallback<R>(dv, pv, k, lane, true);
+        } else {
+            double s = 0.0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int idx = lane + 32 * r;
+                pv[r] = (idx >= 1 && idx < k) ? 1.0f / (1.0f + dv[r]) : 0.f;
+                s += static_cast<double>(pv[r]);
+            }
+            s = warp_sum(s);
+#pragma unroll
+            for (int r = 0; r < R; ++r) pv[r] = static_cast<float>(static_cast<double>(pv[r]) / s);
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            if (idx < cap) {
+                uint64_t key = ~0ull;
+                if (idx >= 1 && idx < k) key = (static_cast<uint64_t>(static_cast<uint32_t>(ids[b + idx])) << 32) | __float_as_uint(pv[r]);
+                sm[idx] = key;
+            }
+        }
+        for (int t = 32 * R + lane; t < cap; t += 32) sm[t] = ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        for (int e = lane; e < ne; e += 32) {
+            const uint64_t key = sm[e];
+            cols[ob + e] = static_cast<uint32_t>(key >> 32);
+            vals[ob + e] = __uint_as_float(static_cast<uint32_t>(key));
+        }
+        __syncwarp();
+    }
+}
+
 static int pow2_at_least(int v) {
     int p = 32;
     while (p < v) p <<= 1;
@@ -270,6 +332,30 @@ int prow_graph_launch(const int64_t* d_ids, const float* d_dist, int64_t n, int 
     if (k <= 320) return launch_graph<10>(d_ids, d_dist, n, k, perplexity, mode, d_cols, d_vals, d_sigma, stream);
     if (k <= 1024) return launch_graph<32>(d_ids, d_dist, n, k, perplexity, mode, d_cols, d_vals, d_sigma, stream);
     return fail(5, "prow: k > 1024 unsupported");
+}
+
+template <int R>
+static int launch_graph_ragged(const int64_t* rowptr, const int64_t* ids, const float* dist, int64_t n, float perplexity, int mode, uint32_t* cols,
+                               float* vals, cudaStream_t stream) {
+    const int cap = pow2_at_least(32 * R);
+    const size_t smem = 4 * static_cast<size_t>(cap) * sizeof(uint64_t);
+    SPHB_CUDA(cudaFuncSetAttribute(prow_graph_ragged_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    const int64_t blocks = std::min<int64_t>((n + 3) / 4, static_cast<int64_t>(ctx().num_sms) * 16);
+    prow_graph_ragged_kernel<R><<<static_cast<unsigned>(blocks), 128, smem, stream>>>(rowptr, ids, dist, n, perplexity, mode, cap, cols, vals);
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int prow_graph_ragged_launch(const int64_t* d_rowptr, const int64_t* d_ids, const float* d_dist, int64_t n, int max_k, float perplexity, int mode,
+                             uint32_t* d_cols, float* d_vals, cudaStream_t stream) {
+    if (n <= 0 || max_k < 2) return 0;
+    if (max_k <= 32) return launch_graph_ragged<1>(d_rowptr, d_ids, d_dist, n, perplexity, mode, d_cols, d_vals, stream);
+    if (max_k <= 64) return launch_graph_ragged<2>(d_rowptr, d_ids, d_dist, n, perplexity, mode, d_cols, d_vals, stream);
+    if (max_k <= 128) return launch_graph_ragged<4>(d_rowptr, d_ids, d_dist, n, perplexity, mode, d_cols, d_vals, stream);
+    if (max_k <= 320) return launch_graph_ragged<10>(d_rowptr, d_ids, d_dist, n, perplexity, mode, d_cols, d_vals, stream);
+    if (max_k <= 1024) return launch_graph_ragged<32>(d_rowptr, d_ids, d_dist, n, perplexity, mode, d_cols, d_vals, stream);
+    return fail(5, "prow: rows with more than 1024 neighbours unsupported");
 }
 
 int prow_inplace_launch(int64_t n, const int64_t* d_rowptr, float* d_val, int max_nnz, float perplexity, int ignore, cudaStream_t stream) {

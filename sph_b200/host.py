@@ -605,6 +605,14 @@ class DeviceOps:
 
         return capi.pair_sims(walks.rowptr, walks.col, walks.val, pa, pb, mode)
 
+    def merge_graph_nodes(self, graph: RaggedGraph, parents, n_merged: int) -> RaggedGraph:
+        return mergeGraphNodes(graph, n_merged, parents)
+
+    def prow_ragged(self, graph: RaggedGraph, scheme: NormalizationScheme) -> SparseRows:
+        from . import capi
+
+        return SparseRows(*capi.prow_graph_ragged(graph.rowptr, graph.knnIndices, graph.knnDistances, 0.0, scheme == NormalizationScheme.LINEAR))
+
     def neighbor_overlap(self, knn_ids, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
         from . import capi
 
@@ -722,6 +730,7 @@ class ImageHierarchy:
         self.spatialNeighbors: list[list[list[int]]] = []
         self.pixelComponents: list[np.ndarray] = []
         self.randomWalks: list[SparseRows] = []
+        self.mergedDataGraphs: list[RaggedGraph] = []
         self.notMergedNodes: list[list[int]] = []
         self.reductionRates: list[float] = []
         self.rwRandomWalkLengths: list[int] = []
@@ -775,8 +784,8 @@ class ImageHierarchy:
         if self.ihs.componentSim in (ComponentSim.GEO_CENTROID, ComponentSim.GEO_WALKS):
             log.error("ImageHierarchy::compute: geodesic component distances (A*/Dijkstra per pair) are host code outside this back-end")
             return
-        if self.ihs.rwHandling == RandomWalkHandling.MERGE_DATA_NEW_WALKS and self._uses_walks():
-            log.error("ImageHierarchy::compute: MERGE_DATA_NEW_WALKS needs probability rows of a ragged graph; not wired")
+        if self.ihs.normKnnDistances not in (NormalizationScheme.TSNE, NormalizationScheme.LINEAR) and self._uses_walks():
+            log.error("ImageHierarchy::compute: %s rows are not built (UMAP rows are a 'next' item)", self.ihs.normKnnDistances.name)
             return
         try:
             self._computePreparations()
@@ -794,6 +803,10 @@ class ImageHierarchy:
         if self._uses_walks():
             self.rwRandomWalkLengths.append(self.rws.singleWalkLength)
             self.randomWalks.append(self._ops.random_walks(self.dataLevelProbdist, self.rws))
+            if self.ihs.rwHandling == RandomWalkHandling.MERGE_DATA_NEW_WALKS:  # keep the data distances for later merging (.cpp:176-177)
+                g = self._graph
+                k = g.knnIndices.shape[1]
+                self.mergedDataGraphs.append(RaggedGraph(np.arange(n + 1, dtype=np.int64) * k, g.knnIndices.reshape(-1), g.knnDistances.reshape(-1)))
 
     def computeDistances(self, level: int):
         """ImageHierarchy::computeDistances (.cpp:192-249): rows [self, spatial neighbours...], componentDistance for every
@@ -915,9 +928,14 @@ class ImageHierarchy:
 
     def _updateRandomWalks(self, n_next: int):  # Hierarchy::updateRandomWalks (Hierarchy.cpp:250-390)
         s = self.ihs
-        merged = self._ops.rw_merge(self.randomWalks[-1], self.parents[-1], n_next, False, s.rwWeightMergeBySize)
-        remove = s.rwRemoveSelfSimAfterMerging and merged.n > 1 and s.rwHandling != RandomWalkHandling.MERGE_RW_ONLY
-        merged = removeDiagonalAndNormalize(merged, remove, s.rwNormSim)
+        if s.rwHandling == RandomWalkHandling.MERGE_DATA_NEW_WALKS:  # Hierarchy.cpp:309-339: merge the data graph, rows from its distances
+            g = self._ops.merge_graph_nodes(self.mergedDataGraphs[-1], self.parents[-1], n_next)
+            merged = self._ops.prow_ragged(g, s.normKnnDistances)
+            self.mergedDataGraphs.append(g)
+        else:
+            merged = self._ops.rw_merge(self.randomWalks[-1], self.parents[-1], n_next, False, s.rwWeightMergeBySize)
+            remove = s.rwRemoveSelfSimAfterMerging and merged.n > 1 and s.rwHandling != RandomWalkHandling.MERGE_RW_ONLY
+            merged = removeDiagonalAndNormalize(merged, remove, s.rwNormSim)
         if s.rwHandling == RandomWalkHandling.MERGE_RW_ONLY:
             out = merged
         else:

@@ -78,6 +78,7 @@ class Oracle:
         L.orc_remove_zeros.argtypes = [C.c_int64, i64p, u32p, f32p, i64p, u32p, f32p]
         L.orc_remove_zeros.restype = C.c_int64
         L.orc_euclid_hausdorff.argtypes = [f32p, C.c_int, i64p, i64p, i64p, i64p, C.c_int64, f32p]
+        L.orc_prow_graph_ragged.argtypes = [C.c_int64, i64p, i64p, f32p, C.c_float, C.c_int, i64p, u32p, f32p]
         L.orc_weak_components.argtypes = [C.c_int64, i64p, i64p, i64p]
         L.orc_weak_components.restype = C.c_int64
         L.orc_level_knn_overlap.argtypes = [i64p, C.c_int, C.c_int64, i64p, i64p, C.c_int64, i64p, f32p]
@@ -360,6 +361,18 @@ class Oracle:
         self.lib.orc_euclid_hausdorff(_p(x, f32p), x.shape[1], _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p))
         return out
 
+    def prow_graph_ragged(self, rowptr, ids, dist, perplexity=0.0, linear=False):
+        rowptr = np.ascontiguousarray(rowptr, np.int64)
+        ids = np.ascontiguousarray(ids, np.int64)
+        dist = np.ascontiguousarray(dist, np.float32)
+        n = len(rowptr) - 1
+        m = max(int(rowptr[-1]) - n, 0)
+        orp = np.zeros(n + 1, np.int64)
+        oc = np.zeros(max(m, 1), np.uint32)
+        ov = np.zeros(max(m, 1), np.float32)
+        self.lib.orc_prow_graph_ragged(n, _p(rowptr, i64p), _p(ids, i64p), _p(dist, f32p), perplexity, int(linear), _p(orp, i64p), _p(oc, u32p), _p(ov, f32p))
+        return orp, oc[:m].copy(), ov[:m].copy()
+
     def weak_components(self, ids, rowptr=None):
         ids = np.ascontiguousarray(ids, np.int64)
         if rowptr is None:
@@ -435,6 +448,16 @@ class OracleOps:
 
     def pair_sims(self, walks, pa, pb, mode):
         return self.o.pair_sims(walks.rowptr, walks.col, walks.val, pa, pb, mode)
+
+    def merge_graph_nodes(self, graph, parents, n_merged):
+        from sph_b200 import host
+
+        return host.RaggedGraph(*self.o.merge_graph_nodes(graph.knnIndices, graph.knnDistances, parents, n_merged, rowptr=graph.rowptr))
+
+    def prow_ragged(self, graph, scheme):
+        from sph_b200 import host
+
+        return host.SparseRows(*self.o.prow_graph_ragged(graph.rowptr, graph.knnIndices, graph.knnDistances, 0.0, scheme == host.NormalizationScheme.LINEAR))
 
     def neighbor_overlap(self, knn_ids, comp_ptr, comp_pix, pa, pb):
         return self.o.neighbor_overlap(knn_ids, comp_ptr, comp_pix, pa, pb)

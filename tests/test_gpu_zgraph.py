@@ -322,3 +322,39 @@ def test_connected_components_of_symmetric_graph(capi, oracle):
     rnum, rlabels = oracle.weak_components(g.knnIndices, g.rowptr)
     assert num == rnum and num > 1
     np.testing.assert_array_equal(labels, rlabels)
+
+
+# ---------------------------------------------------------------- B2 / B5 on ragged graphs
+@pytest.mark.parametrize("linear", [False, True])
+def test_prow_graph_ragged_matches_oracle(capi, oracle, linear):
+    # the ragged graph a symmetrisation produces (rows of 8 .. ~40 neighbours), plus single-entry and two-entry rows
+    ids, dist = random_knn_graph(1200, 8, seed=21)
+    rp, oi, od = oracle.symmetrize_graph(ids, dist)
+    extra_ids = np.array([1200, 1201, 0], np.int64)
+    extra_dist = np.array([0, 0, 2.5], np.float32)
+    rp = np.concatenate([rp, [rp[-1] + 1, rp[-1] + 3]]).astype(np.int64)
+    oi = np.concatenate([oi, extra_ids])
+    od = np.concatenate([od, extra_dist])
+    a = capi.prow_graph_ragged(rp, oi, od, 0.0, linear)
+    b = oracle.prow_graph_ragged(rp, oi, od, 0.0, linear)
+    np.testing.assert_array_equal(a[0], b[0])
+    np.testing.assert_array_equal(a[1], b[1])
+    np.testing.assert_allclose(a[2], b[2], rtol=1e-5, atol=1e-12)
+
+
+def test_hierarchy_merge_data_new_walks_on_device(capi):
+    from sph_b200 import host
+
+    g = gold("hierarchy_walks_6x4.json")
+    ids = np.array(g["knn"], np.int64).reshape(24, 4)
+    dist = np.array(g["dist"], np.float32).reshape(24, 4)
+    ih = host.ImageHierarchy(host.Graph(ids, dist), None, 6, 4)
+    ihs = host.ImageHierarchySettings(componentSim=host.ComponentSim.NEIGH_WALKS, usePercentile=False,
+                                      rwHandling=host.RandomWalkHandling.MERGE_DATA_NEW_WALKS, normKnnDistances=host.NormalizationScheme.LINEAR)
+    ih.compute(ihs, host.RandomWalkSettings(numRandomWalks=10, singleWalkLength=3))
+    assert ih.getNumLevels() >= 2 and ih.numComponents[-1] == 1
+    for lvl, mg in enumerate(ih.mergedDataGraphs):
+        assert mg.numPoints == ih.numComponents[lvl]
+        assert (mg.knnIndices[mg.rowptr[:-1]] == np.arange(mg.numPoints)).all()
+    for rw in ih.randomWalks:
+        np.testing.assert_allclose(np.add.reduceat(rw.val, rw.rowptr[:-1]), 1.0, atol=1e-3)

@@ -418,3 +418,35 @@ def test_weak_components_golden(oracle):
     ids = np.array([[0, 3], [1, 2], [2, 1], [3, 0], [4, 4]], np.int64)
     num3, labels3 = oracle.weak_components(ids)
     assert num3 == 3 and labels3.tolist() == [0, 1, 1, 0, 2]
+
+
+def test_prow_graph_ragged_reduces_to_fixed_k(oracle):
+    rng = np.random.default_rng(4)
+    n, k = 40, 9
+    ids = np.stack([np.concatenate([[i], rng.choice(np.delete(np.arange(n), i), k - 1, replace=False)]) for i in range(n)]).astype(np.int64)
+    dist = np.concatenate([np.zeros((n, 1)), np.sort(rng.uniform(0.1, 3, (n, k - 1)), 1)], 1).astype(np.float32)
+    rp = np.arange(n + 1, dtype=np.int64) * k
+    for linear in (False, True):
+        orp, oc, ov = oracle.prow_graph_ragged(rp, ids.reshape(-1), dist.reshape(-1), 0.0, linear)
+        cols, vals = oracle.prow_linear_graph(ids, dist) if linear else oracle.prow_gaussian_graph(ids, dist, 0.0)[:2]
+        assert orp.tolist() == (np.arange(n + 1) * (k - 1)).tolist()
+        np.testing.assert_array_equal(oc, cols.reshape(-1))
+        np.testing.assert_array_equal(ov, vals.reshape(-1))
+
+
+def test_hierarchy_merge_data_new_walks_runs_on_oracle(oracle):
+    # MERGE_DATA_NEW_WALKS (sph/utils/Hierarchy.cpp:309-339): mergeGraphNodes + rows of the merged (ragged) data graph + new walks
+    from sph_b200 import host
+
+    g = gold("hierarchy_walks_6x4.json")
+    ids = np.array(g["knn"], np.int64).reshape(24, 4)
+    dist = np.array(g["dist"], np.float32).reshape(24, 4)
+    ih = host.ImageHierarchy(host.Graph(ids, dist), None, 6, 4, ops=oracle_lib.OracleOps(oracle))
+    ihs = host.ImageHierarchySettings(componentSim=host.ComponentSim.NEIGH_WALKS, usePercentile=False,
+                                      rwHandling=host.RandomWalkHandling.MERGE_DATA_NEW_WALKS, normKnnDistances=host.NormalizationScheme.LINEAR)
+    ih.compute(ihs, host.RandomWalkSettings(numRandomWalks=10, singleWalkLength=3, parallel=False))
+    assert ih.getNumLevels() >= 3 and ih.numComponents[-1] == 1
+    assert len(ih.mergedDataGraphs) == ih.getNumLevels()
+    for lvl, mg in enumerate(ih.mergedDataGraphs):
+        assert mg.numPoints == ih.numComponents[lvl]
+        assert (mg.knnIndices[mg.rowptr[:-1]] == np.arange(mg.numPoints)).all()  # self first on every level
