@@ -391,6 +391,25 @@ class LevelSimilarities:
             ids, dist = capi.level_knn_overlap(self._graph.knnIndices, ptr, pix, k_l)
             self._distance_graphs[level] = Graph(ids, dist)
             return self._distance_graphs[level]
+        if lss.componentSim == ComponentSim.EUCLID_CENTROID:
+            # EuclidDistSpace (sph/utils/EuclidDistSpace.hpp:29-39): Hausdorff distance of every component pair.  Not fused:
+            # row blocks of (i, j) pairs go through the batched D6 kernel, the k smallest per row are picked on the host
+            ptr, pix = self._hierarchy.representedDataPoints(level)
+            n_l = len(ptr) - 1
+            k_l = min(self._ks[level], n_l)
+            ids = np.empty((n_l, k_l), np.int64)
+            dist = np.empty((n_l, k_l), np.float32)
+            block = max(1, min(n_l, (1 << 22) // max(n_l, 1)))
+            cols = np.arange(n_l, dtype=np.int64)
+            for r0 in range(0, n_l, block):
+                r1 = min(n_l, r0 + block)
+                pa = np.repeat(np.arange(r0, r1, dtype=np.int64), n_l)
+                d = capi.euclid_hausdorff(self._hierarchy._data, ptr, pix, pa, np.tile(cols, r1 - r0)).reshape(r1 - r0, n_l)
+                for r in range(r0, r1):
+                    order = np.lexsort((cols, d[r - r0]))[:k_l]  # (distance, index); the reference's std::sort leaves ties unordered
+                    ids[r], dist[r] = order, d[r - r0, order]
+            self._distance_graphs[level] = Graph(ids, dist)
+            return self._distance_graphs[level]
         rw = self._rw[level]
         k_l = min(self._ks[level], rw.n)
         if lss.knnFromWalkMetric:
@@ -422,9 +441,9 @@ class LevelSimilarities:
             if level == 0:
                 self._prob[0] = normalizeKnnDistances(self._graph, NormalizationScheme.TSNE, self._perplexities[0])
                 continue
-            overlap = lss.componentSim == ComponentSim.NEIGH_OVERLAP
+            overlap = lss.componentSim in (ComponentSim.NEIGH_OVERLAP, ComponentSim.EUCLID_CENTROID)  # computeKnn + useKnnDistances
             if overlap and self._hierarchy is None:
-                log.error("LevelSimilarities::compute: NEIGH_OVERLAP needs the image hierarchy")
+                log.error("LevelSimilarities::compute: %s needs the image hierarchy", lss.componentSim.name)
                 return
             rw = None if overlap else self._rw[level]
             k_l, perp_l = min(self._ks[level], sizes[level]), self._perplexities[level]

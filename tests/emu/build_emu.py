@@ -69,22 +69,27 @@ def translate(text: str) -> str:
     return "".join(out)
 
 
-def build(verbose: bool = False) -> Path:
+def build(verbose: bool = False, asan: bool = False) -> Path:
+    """asan=True builds libsphb200_emu_asan.so with AddressSanitizer: every "device" buffer is a heap block, so an
+    out-of-bounds global-memory access of a kernel is reported (run with LD_PRELOAD=$(gcc -print-file-name=libasan.so)
+    ASAN_OPTIONS=detect_leaks=0:detect_stack_use_after_return=0)."""
     OUT.mkdir(exist_ok=True)
+    lib = OUT / "libsphb200_emu_asan.so" if asan else LIB
     srcs = []
     for name in SOURCES:
         dst = OUT / (Path(name).stem + "_emu.cpp")
         dst.write_text(f'#line 1 "{CSRC / name}"\n' + translate((CSRC / name).read_text()))
         srcs.append(dst)
     cmd = ["/usr/bin/g++", "-O1", "-g", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-fvisibility=hidden", "-D__CUDACC__",
-           "-w", f"-I{HERE / 'include'}", f"-I{CSRC}", "-o", str(LIB), *map(str, srcs), str(HERE / "emu_api.cpp")]
+           *(["-fsanitize=address", "-fno-omit-frame-pointer"] if asan else []),
+           "-w", f"-I{HERE / 'include'}", f"-I{CSRC}", "-o", str(lib), *map(str, srcs), str(HERE / "emu_api.cpp")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0 or verbose:
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode != 0:
         raise RuntimeError("emulation build failed")
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(verbose="-v" in sys.argv))
+    print(build(verbose="-v" in sys.argv, asan="--asan" in sys.argv))

@@ -187,6 +187,7 @@ def capi_on_oracle(monkeypatch, oracle):
 
     o = oracle
     monkeypatch.setattr(capi, "level_knn_overlap", lambda ids, ptr, pix, k: o.level_knn_overlap(ids, ptr, pix, k))
+    monkeypatch.setattr(capi, "euclid_hausdorff", lambda x, ptr, pix, pa, pb: o.euclid_hausdorff(x, ptr, pix, pa, pb))
     monkeypatch.setattr(capi, "level_knn_walks", lambda rp, c, v, k, mode=0: o.level_knn_walks(rp, c, v, k, mode))
     monkeypatch.setattr(capi, "rw_as_knn_distances", lambda rp, c, v: o.rw_as_knn_distances(rp, c, v))
     monkeypatch.setattr(capi, "prow_gaussian_flat", lambda d, p: o.prow_gaussian_flat(d, p))
@@ -266,3 +267,23 @@ def test_level_similarities_walk_control_flow(capi_on_oracle, oracle, kind):
         assert ls.getSimilaritiesGraph(1).knnIndices.shape[0] == 9
     if kind == "rw_dist":
         assert ls.getSimilaritiesGraph(1).numPoints == 9
+
+
+def test_level_similarities_euclid_control_flow(capi_on_oracle, oracle):
+    import oracle_lib
+    from sph_b200 import host
+
+    rng = np.random.default_rng(6)
+    x = rng.standard_normal((24, 5)).astype(np.float32)
+    ids, dist = oracle.knn_reference_graph(x, 4)
+    graph = host.Graph(ids, dist)
+    ih = host.ImageHierarchy(graph, x, 6, 4, ops=oracle_lib.OracleOps(oracle))
+    ih.compute(host.ImageHierarchySettings(componentSim=host.ComponentSim.EUCLID_CENTROID, usePercentile=False))
+    assert ih.getNumLevels() >= 3 and ih.numComponents[-1] == 1
+    ls = host.LevelSimilarities(graph, hierarchy=ih)
+    ls.compute(host.LevelSimilaritiesSettings(levelToCompute=1, componentSim=host.ComponentSim.EUCLID_CENTROID))
+    g = ls.getSimilaritiesGraph(1)
+    n1 = ih.numComponents[1]
+    assert g.knnIndices.shape[0] == n1 and (g.knnIndices[:, 0] == np.arange(n1)).all() and (g.knnDistances[:, 0] == 0).all()
+    assert (np.diff(g.knnDistances, axis=1) >= 0).all()
+    assert ls.getProbDist(1).n == n1
