@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 import oracle_lib
-from test_oracle_goldens import check_hierarchy, run_hierarchy
+from test_oracle_goldens import check_hierarchy, run_hierarchy, run_walks_4x4
 
 pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).resolve().parent / "golden"
@@ -54,3 +54,7 @@ def test_walk_hierarchy_invariants_on_device(capi):
     for rw in ih.randomWalks:  # testImageHierarchyWalks (:440-444)
         sums = np.add.reduceat(rw.val, rw.rowptr[:-1])
         np.testing.assert_allclose(sums, 1.0, atol=1e-3)
+
+
+def test_image_hierarchy_walks_row_sums_on_device(capi):
+    run_walks_4x4(None)  # tests/HierarchyTest.cpp:364-445 through the C ABI

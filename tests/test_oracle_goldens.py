@@ -450,3 +450,22 @@ def test_hierarchy_merge_data_new_walks_runs_on_oracle(oracle):
     for lvl, mg in enumerate(ih.mergedDataGraphs):
         assert mg.numPoints == ih.numComponents[lvl]
         assert (mg.knnIndices[mg.rowptr[:-1]] == np.arange(mg.numPoints)).all()  # self first on every level
+
+
+def run_walks_4x4(ops):
+    from sph_b200 import host
+
+    g = gold("hierarchy_walks_4x4_rowsums.json")
+    ids = np.array(g["knn"], np.int64).reshape(16, 4)
+    dist = np.array(g["dist"], np.float32).reshape(16, 4)
+    ih = host.ImageHierarchy(host.Graph(ids, dist), None, 4, 4, ops=ops)
+    ih.compute(host.ImageHierarchySettings(componentSim=host.ComponentSim.NEIGH_WALKS, rwHandling=host.RandomWalkHandling.MERGE_RW_NEW_WALKS))
+    assert ih.getNumLevels() >= 2 and len(ih.randomWalks) == ih.getNumLevels()
+    for rw in ih.randomWalks:
+        assert rw.n > 0 and (np.diff(rw.rowptr) > 0).all()
+        np.testing.assert_allclose(np.add.reduceat(rw.val, rw.rowptr[:-1]), 1.0, atol=g["row_sum_abs_tol"])
+    return ih
+
+
+def test_image_hierarchy_walks_row_sums(oracle):
+    run_walks_4x4(oracle_lib.OracleOps(oracle))
