@@ -152,6 +152,13 @@ SPHB_API int sphb_random_walks(int64_t n, const int64_t* rowptr, const uint32_t*
                                uint64_t num_walks, uint64_t walk_len, int weighting, float prune_value, uint64_t prune_steps,
                                uint64_t seed, int remove_diagonal, int normalize,
                                int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t cap, int64_t* out_nnz);
+/* The same for start points [q0, q1) only — the multi-GPU shard of doRandomWalks (start points are independent, the
+ * transition matrix is replicated; the RNG is keyed by the global start id, so slabs concatenate to the full result).
+ * out_rowptr: q1 - q0 + 1 entries relative to the slab. */
+SPHB_API int sphb_random_walks_slab(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                                    uint64_t num_walks, uint64_t walk_len, int weighting, float prune_value, uint64_t prune_steps,
+                                    uint64_t seed, int remove_diagonal, int normalize, int64_t q0, int64_t q1,
+                                    int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t cap, int64_t* out_nnz);
 /* utils::mergeNodesRandomWalks (sph/utils/SparseMatrixAlgorithms.hpp:82, .cpp:292-352). */
 SPHB_API int sphb_rw_merge(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
                            const uint64_t* parents, int64_t n_merged, int norm, int weight_by_size,

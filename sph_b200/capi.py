@@ -51,6 +51,8 @@ SIGNATURES = {
     "sphb_symmetrize": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
     "sphb_random_walks": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_uint64, C.c_uint64, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
                                     C.c_int, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
+    "sphb_random_walks_slab": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_uint64, C.c_uint64, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
+                                         C.c_int, C.c_int, C.c_int64, C.c_int64, i64p, u32p, f32p, C.c_int64, i64p]),
     "sphb_rw_merge": (C.c_int, [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, C.c_int, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
     "sphb_create_similarities": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, u32p, f32p, i32p]),
     "sphb_pair_sims": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, i64p, C.c_int64, C.c_int, f32p]),
@@ -241,6 +243,25 @@ def random_walks(rowptr, col, val, num_walks: int, walk_len: int, weighting: int
     nnz = np.zeros(1, np.int64)
     _check(load().sphb_random_walks(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), num_walks, walk_len, weighting, prune_value, prune_steps,
                                     seed, int(remove_diagonal), int(normalize), _p(orp, i64p), _p(oc, u32p), _p(ov, f32p), cap, _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oc[:m].copy(), ov[:m].copy()
+
+
+def random_walks_slab(rowptr, col, val, num_walks: int, walk_len: int, q0: int, q1: int, weighting: int = W_CONSTANT, prune_value: float = 0.0,
+                      prune_steps: int = 0, seed: int = 0, remove_diagonal: bool = True, normalize: bool = True, cap: int | None = None):
+    """Random walks of the start points [q0, q1) (multi-GPU shard): CSR of q1 - q0 rows."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    nq = q1 - q0
+    cap = max(1, nq * min(n, num_walks * walk_len)) if cap is None else int(cap)
+    orp = np.zeros(nq + 1, np.int64)
+    oc = np.zeros(cap, np.uint32)
+    ov = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_random_walks_slab(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), num_walks, walk_len, weighting, prune_value, prune_steps,
+                                         seed, int(remove_diagonal), int(normalize), q0, q1, _p(orp, i64p), _p(oc, u32p), _p(ov, f32p), cap, _p(nnz, i64p)))
     m = int(nnz[0])
     return orp, oc[:m].copy(), ov[:m].copy()
 

@@ -833,6 +833,10 @@ int weak_components_dev(int64_t n, const int64_t* d_rowptr, const int64_t* d_ids
 }  // namespace sphb
 
 namespace sphb {
+// implemented in walks.cu
+int random_walks_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, uint64_t num_walks, uint64_t walk_len,
+                          int weighting, float prune_value, uint64_t prune_steps, uint64_t seed, int remove_diagonal, int normalize, int64_t q0,
+                          int64_t q1, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s);
 // implemented in prow.cu
 int prow_graph_ragged_launch(const int64_t* d_rowptr, const int64_t* d_ids, const float* d_dist, int64_t n, int max_k, float perplexity, int mode,
                              uint32_t* d_cols, float* d_vals, cudaStream_t stream);
@@ -916,6 +920,37 @@ extern "C" {
 SPHB_API int sphb_symmetrize_graph(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, int64_t* out_rowptr,
                                    int64_t* out_ids, float* out_dist, int64_t cap, int64_t* out_nnz) {
     return graph_minmerge_host("symmetrize_graph", n, rowptr, k, ids, dist, nullptr, std::max<int64_t>(n, 1), out_rowptr, out_ids, out_dist, cap, out_nnz);
+}
+
+SPHB_API int sphb_random_walks_slab(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, uint64_t num_walks, uint64_t walk_len,
+                                    int weighting, float prune_value, uint64_t prune_steps, uint64_t seed, int remove_diagonal, int normalize,
+                                    int64_t q0, int64_t q1, int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t cap, int64_t* out_nnz) {
+    if (int rc = ensure_init()) return rc;
+    if (bad_csr_in(n, rowptr, col, val) || !out_rowptr || !out_nnz || cap < 0 || weighting < 0 || weighting > 4 || walk_len == 0 || q0 < 0 || q1 > n || q1 < q0)
+        return fail(SPHB_ERR_INVALID, "random_walks_slab: bad arguments");
+    const int64_t nnz = rowptr[n];
+    cudaStream_t s = ctx().stream;
+    DevBuf<int64_t> drp, orp;
+    DevBuf<uint32_t> dcol, oc;
+    DevBuf<float> dval, ov;
+    if (int rc = up(drp, rowptr, n + 1, s)) return rc;
+    if (int rc = up(dcol, col, nnz, s)) return rc;
+    if (int rc = up(dval, val, nnz, s)) return rc;
+    SPHB_CUDA(orp.alloc(q1 - q0 + 1, s));
+    SPHB_CUDA(oc.alloc(std::max<int64_t>(cap, 1), s));
+    SPHB_CUDA(ov.alloc(std::max<int64_t>(cap, 1), s));
+    int64_t m = 0;
+    if (int rc = random_walks_slab_dev(n, drp.p, dcol.p, dval.p, num_walks, walk_len, weighting, prune_value, prune_steps, seed, remove_diagonal, normalize,
+                                       q0, q1, orp.p, oc.p, ov.p, cap, &m, s))
+        return rc;
+    SPHB_CUDA(cudaMemcpyAsync(out_rowptr, orp.p, (q1 - q0 + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    if (m) {
+        SPHB_CUDA(cudaMemcpyAsync(out_col, oc.p, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        SPHB_CUDA(cudaMemcpyAsync(out_val, ov.p, m * sizeof(float), cudaMemcpyDeviceToHost, s));
+    }
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    *out_nnz = m;
+    return SPHB_OK;
 }
 
 SPHB_API int sphb_prow_graph_ragged(int64_t n, const int64_t* rowptr, const int64_t* ids, const float* dist, float perplexity, int linear,

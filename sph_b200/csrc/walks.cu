@@ -193,12 +193,16 @@ __global__ void widen_counts(const int* __restrict__ in, int64_t num, int64_t* _
         out[t] = t < num ? in[t] : 0;
 }
 
-int random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, uint64_t num_walks, uint64_t walk_len,
-                     int weighting, float prune_value, uint64_t prune_steps, uint64_t seed, int remove_diagonal, int normalize,
-                     int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s) {
+// Start points [q0, q1) only (the multi-GPU shard: every walk may read any row of the replicated matrix, the start points
+// are independent, and the counter-based RNG is keyed by the GLOBAL start id, so the slabs of a sharded run concatenate to
+// exactly the single-GPU result).  d_out_rowptr: q1 - q0 + 1 entries, relative to the slab.
+int random_walks_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, uint64_t num_walks, uint64_t walk_len,
+                          int weighting, float prune_value, uint64_t prune_steps, uint64_t seed, int remove_diagonal, int normalize, int64_t q0,
+                          int64_t q1, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s) {
     *out_nnz = 0;
-    SPHB_CUDA(cudaMemsetAsync(d_out_rowptr, 0, (n + 1) * sizeof(int64_t), s));
-    if (n == 0 || num_walks == 0) return 0;
+    if (q0 < 0 || q1 > n || q1 < q0) return fail(SPHB_ERR_INVALID, "random_walks: bad start-point range");
+    SPHB_CUDA(cudaMemsetAsync(d_out_rowptr, 0, (q1 - q0 + 1) * sizeof(int64_t), s));
+    if (n == 0 || num_walks == 0 || q1 == q0) return 0;
     const uint64_t total = num_walks * walk_len;
     if (total > 8192) return fail(SPHB_ERR_UNSUPPORTED, "random_walks: numRandomWalks * singleWalkLength > 8192 unsupported");
     if (weighting == SPHB_W_FIRST_VISIT && walk_len > FV_MAX_LEN) return fail(SPHB_ERR_UNSUPPORTED, "random_walks: FIRST_VISIT with walk length > 64 unsupported");
@@ -223,7 +227,7 @@ int random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, 
     const int tmp_stride = static_cast<int>(std::min<uint64_t>(total, static_cast<uint64_t>(n)));
     // chunk of start points per launch: bounded temp storage (<= 4 GiB), rows compacted chunk by chunk
     int64_t chunk = std::max<int64_t>(1024, (4ll << 30) / (static_cast<int64_t>(tmp_stride) * 8));
-    chunk = std::min<int64_t>(chunk, n);
+    chunk = std::min<int64_t>(chunk, q1 - q0);
     DevBuf<uint32_t> tcol;
     DevBuf<float> tval;
     DevBuf<int> cnt;
@@ -236,8 +240,8 @@ int random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, 
     if (warps == WARPS) SPHB_CUDA(cudaFuncSetAttribute(random_walk_kernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     else SPHB_CUDA(cudaFuncSetAttribute(random_walk_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     int64_t base = 0;
-    for (int64_t s0 = 0; s0 < n; s0 += chunk) {
-        const int64_t ns = std::min(chunk, n - s0);
+    for (int64_t s0 = q0; s0 < q1; s0 += chunk) {
+        const int64_t ns = std::min(chunk, q1 - s0);
         WalkParams P{};
         P.n = n; P.rowptr = d_rowptr; P.col = d_col; P.val = d_val;
         P.W = static_cast<uint32_t>(num_walks); P.L = static_cast<uint32_t>(walk_len);
@@ -253,7 +257,7 @@ int random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, 
         int64_t chunk_nnz = 0;
         SPHB_CUDA(cudaMemcpyAsync(&chunk_nnz, offs.p + ns, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
         walks_compact<<<static_cast<unsigned>(std::min<int64_t>((ns * 32 + 255) / 256, sms * 8)), 256, 0, s>>>(ns, tmp_stride, tcol.p, tval.p, offs.p, base, cap,
-                                                                                                              d_out_rowptr + s0, d_out_col, d_out_val);
+                                                                                                              d_out_rowptr + (s0 - q0), d_out_col, d_out_val);
         count_launch();
         SPHB_CUDA(cudaGetLastError());
         SPHB_CUDA(cudaStreamSynchronize(s));
@@ -262,6 +266,13 @@ int random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, 
     }
     *out_nnz = base;
     return 0;
+}
+
+int random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, uint64_t num_walks, uint64_t walk_len,
+                     int weighting, float prune_value, uint64_t prune_steps, uint64_t seed, int remove_diagonal, int normalize,
+                     int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s) {
+    return random_walks_slab_dev(n, d_rowptr, d_col, d_val, num_walks, walk_len, weighting, prune_value, prune_steps, seed, remove_diagonal, normalize, 0, n,
+                                 d_out_rowptr, d_out_col, d_out_val, cap, out_nnz, s);
 }
 
 }  // namespace sphb

@@ -506,9 +506,44 @@ def scatter_flat_rows(ids: np.ndarray, temp: np.ndarray):
 
 
 # ---- random walks (sph/utils/SparseMatrixAlgorithms.hpp:73,82) -----------------------------------
-def doRandomWalks(similarities: SparseRows, rws: RandomWalkSettings) -> SparseRows:
+def gather_csr(local: SparseRows, n: int, group=None) -> SparseRows:
+    """Concatenates the ranks' CSR row slabs (rank r holds rows shard_rows(n, world)[r], rowptr relative to its slab)."""
+    import torch
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return local
+    counts = gather_rows(np.diff(local.rowptr).astype(np.int64), n, group)
+    world = dist.get_world_size(group)
+    dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    slabs = shard_rows(n, world)
+    sizes = [int(counts[a:b].sum()) for a, b in slabs]
+    mx = max(max(sizes), 1)
+
+    def gather_flat(x, dtype):
+        buf = torch.zeros(mx, dtype=dtype, device=dev)
+        buf[: len(x)] = torch.from_numpy(np.ascontiguousarray(x).astype(np.int64 if dtype == torch.int64 else np.float32)).to(dev)
+        parts = [torch.empty_like(buf) for _ in range(world)]
+        dist.all_gather(parts, buf, group=group)
+        return np.concatenate([p[:sz].cpu().numpy() for p, sz in zip(parts, sizes)])
+
+    col = gather_flat(local.col, torch.int64).astype(np.uint32)
+    val = gather_flat(local.val, torch.float32).astype(np.float32)
+    return SparseRows(np.concatenate([[0], np.cumsum(counts)]).astype(np.int64), col, val)
+
+
+def doRandomWalks(similarities: SparseRows, rws: RandomWalkSettings, rank: int = 0, world: int = 1, group=None, walks_fn=None) -> SparseRows:
+    """utils::doRandomWalks; with world > 1 the start points are sharded over the ranks (SURVEY §8e: the transition matrix is
+    replicated, every rank walks its slab of start points, one gather of the ragged result)."""
     from . import capi
 
+    if world > 1:
+        q0, q1 = shard_rows(similarities.n, world)[rank]
+        fn = walks_fn or (lambda m, q0, q1: capi.random_walks_slab(m.rowptr, m.col, m.val, rws.numRandomWalks, rws.singleWalkLength, q0, q1,
+                                                                    int(rws.importanceWeighting), rws.pruneValue, rws.pruneSteps, rws.randomSeed,
+                                                                    rws.removeDiagonal, rws.normalize))
+        rp, c, v = fn(similarities, q0, q1)
+        return gather_csr(SparseRows(rp, c, v), similarities.n, group)
     rp, c, v = capi.random_walks(similarities.rowptr, similarities.col, similarities.val, rws.numRandomWalks, rws.singleWalkLength,
                                  int(rws.importanceWeighting), rws.pruneValue, rws.pruneSteps, rws.randomSeed, rws.removeDiagonal, rws.normalize)
     return SparseRows(rp, c, v)

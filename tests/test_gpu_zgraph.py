@@ -358,3 +358,16 @@ def test_hierarchy_merge_data_new_walks_on_device(capi):
         assert (mg.knnIndices[mg.rowptr[:-1]] == np.arange(mg.numPoints)).all()
     for rw in ih.randomWalks:
         np.testing.assert_allclose(np.add.reduceat(rw.val, rw.rowptr[:-1]), 1.0, atol=1e-3)
+
+
+# ---------------------------------------------------------------- RW1 sharded by start points
+def test_random_walk_slabs_concatenate_to_the_full_result(capi):
+    rp, c, v = random_stochastic(700, 12, seed=31, diag=False)
+    full = capi.random_walks(rp, c, v, 20, 6, capi.W_LINEAR, seed=5)
+    parts = [capi.random_walks_slab(rp, c, v, 20, 6, q0, q1, capi.W_LINEAR, seed=5) for q0, q1 in [(0, 233), (233, 234), (234, 700)]]
+    rowptr = np.concatenate([[0]] + [p[0][1:] + off for p, off in zip(parts, np.cumsum([0] + [len(p[1]) for p in parts[:-1]]))])
+    np.testing.assert_array_equal(rowptr, full[0])
+    np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), full[1])
+    np.testing.assert_array_equal(np.concatenate([p[2] for p in parts]), full[2])  # Philox keyed by the global start id
+    e = capi.random_walks_slab(rp, c, v, 20, 6, 100, 100, capi.W_LINEAR, seed=5)
+    assert e[0].tolist() == [0] and len(e[1]) == 0

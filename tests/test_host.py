@@ -139,6 +139,35 @@ print("rank", rank, "ok")
 '''
 
 
+WORKER_WALKS = r'''
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+import torch.distributed as dist
+from sph_b200 import host
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+n = 101
+rng = np.random.default_rng(3)
+counts = rng.integers(0, 7, n)
+counts[40:60] = 0                      # empty rows, also across the slab boundary
+rowptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+col = rng.integers(0, n, rowptr[-1]).astype(np.uint32)
+val = rng.uniform(size=rowptr[-1]).astype(np.float32)
+full = host.SparseRows(rowptr, col, val)
+def walks(m, q0, q1):                  # stand-in for the CUDA slab call: returns the slab of a fixed "result"
+    b, e = rowptr[q0], rowptr[q1]
+    return rowptr[q0:q1 + 1] - b, col[b:e], val[b:e]
+out = host.doRandomWalks(full, host.RandomWalkSettings(), rank=rank, world=world, walks_fn=walks)
+np.testing.assert_array_equal(out.rowptr, rowptr)
+np.testing.assert_array_equal(out.col, col)
+np.testing.assert_array_equal(out.val, val)
+dist.barrier()
+dist.destroy_process_group()
+print("rank", rank, "ok")
+'''
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -152,6 +181,19 @@ def test_sharded_knn_world2_gloo(tmp_path):
 
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1", "--master-port",
+           str(_free_port()), str(script), str(ROOT)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert r.stdout.count("ok") == 2
+
+
+def test_sharded_random_walks_world2_gloo(tmp_path):
+    import subprocess
+
+    script = tmp_path / "worker_walks.py"
+    script.write_text(WORKER_WALKS)
     env = dict(os.environ, OMP_NUM_THREADS="2")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1", "--master-port",
            str(_free_port()), str(script), str(ROOT)]
