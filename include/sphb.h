@@ -212,6 +212,11 @@ SPHB_API int sphb_symmetrize_graph(int64_t n, const int64_t* rowptr, int k, cons
  * every point, components numbered in ascending order of their lowest point (the order Boost reaches them);
  * *num_components receives their number. */
 SPHB_API int sphb_weak_components(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, int64_t* labels, int64_t* num_components);
+/* Device-pointer variant (graph resident in HBM, e.g. straight from sphb_knn_exact_dev); d_rowptr may be NULL for a
+ * fixed-k graph, nnz = number of stored entries; *out_nnz is written on the host (one stream synchronisation). */
+SPHB_API int sphb_symmetrize_graph_dev(int64_t n, const int64_t* d_rowptr, int k, const int64_t* d_ids, const float* d_dist, int64_t nnz,
+                                       int64_t* d_out_rowptr, int64_t* d_out_ids, float* d_out_dist, int64_t cap, int64_t* out_nnz,
+                                       void* stream);
 /* utils::mergeGraphNodes (sph/utils/SparseMatrixAlgorithms.cpp:486-561): node r merges into parents[r]; the
  * distance of (parent(r), parent(c)) is the minimum over the children; rows ordered by (distance, index), self first.
  * cap: nnz of the input always suffices. */

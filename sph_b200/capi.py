@@ -61,6 +61,8 @@ SIGNATURES = {
     "sphb_symmetrize_graph": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, i64p, f32p, C.c_int64, i64p]),
     "sphb_prow_graph_ragged": (C.c_int, [C.c_int64, i64p, i64p, f32p, C.c_float, C.c_int, i64p, u32p, f32p]),
     "sphb_weak_components": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, i64p, i64p]),
+    "sphb_symmetrize_graph_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_int64, i64p, C.c_void_p]),
     "sphb_merge_graph_nodes": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, u64p, C.c_int64, i64p, i64p, f32p, C.c_int64, i64p]),
     "sphb_merge_data_distances": (C.c_int, [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, i64p, u32p, f32p, C.c_int64, i64p]),
     "sphb_rw_as_knn_distances": (C.c_int, [C.c_int64, i64p, u32p, f32p, i64p, i64p, f32p, i64p]),
@@ -389,6 +391,15 @@ def weak_components(ids, rowptr=None):
     num = np.zeros(1, np.int64)
     _check(load().sphb_weak_components(n, _p(rp, i64p) if rp is not None else None, k, _p(ids, i64p), _p(labels, i64p), _p(num, i64p)))
     return int(num[0]), labels[:n]
+
+
+def symmetrize_graph_dev(n: int, rowptr_ptr: int, k: int, ids_ptr: int, dist_ptr: int, nnz: int, out_rowptr_ptr: int, out_ids_ptr: int,
+                         out_dist_ptr: int, cap: int, stream: int) -> int:
+    """Device-pointer symmetrizeGraph; returns the number of entries written."""
+    out = np.zeros(1, np.int64)
+    _check(load().sphb_symmetrize_graph_dev(n, rowptr_ptr or None, k, ids_ptr, dist_ptr, nnz, out_rowptr_ptr, out_ids_ptr, out_dist_ptr, cap,
+                                            _p(out, i64p), stream or None))
+    return int(out[0])
 
 
 def merge_graph_nodes(ids, dist, parents, n_merged: int, rowptr=None):

@@ -27,6 +27,9 @@ __global__ void gm_rowptr_lower_bound(const uint64_t* __restrict__ keys, int64_t
     for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; r <= nrows; r += static_cast<int64_t>(gridDim.x) * blockDim.x)
         rowptr[r] = lower_bound_u64(keys, num, static_cast<uint64_t>(r) << shift);
 }
+__global__ void gm_fixed_rowptr(int64_t n, int k, int64_t* __restrict__ rowptr) {
+    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; r <= n; r += static_cast<int64_t>(gridDim.x) * blockDim.x) rowptr[r] = r * k;
+}
 __global__ void gm_flag_heads(const uint64_t* __restrict__ keys, int64_t num, int* __restrict__ head) {
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t <= num; t += static_cast<int64_t>(gridDim.x) * blockDim.x)
         head[t] = t == num ? 0 : ((t == 0 || keys[t] != keys[t - 1]) ? 1 : 0);
@@ -1010,6 +1013,25 @@ SPHB_API int sphb_weak_components(int64_t n, const int64_t* rowptr, int k, const
     SPHB_CUDA(cudaStreamSynchronize(s));
     *num_components = nc;
     return SPHB_OK;
+}
+
+// Device-pointer variant for pipelines that keep the graph in HBM (sphb_knn_exact_dev -> here -> weak components / P rows).
+// d_rowptr may be NULL for a fixed-k graph.  *out_nnz is a HOST value (the call synchronises the stream once to size the output).
+SPHB_API int sphb_symmetrize_graph_dev(int64_t n, const int64_t* d_rowptr, int k, const int64_t* d_ids, const float* d_dist, int64_t nnz,
+                                       int64_t* d_out_rowptr, int64_t* d_out_ids, float* d_out_dist, int64_t cap, int64_t* out_nnz, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (n <= 0 || nnz < 0 || !d_out_rowptr || !out_nnz || cap < 0 || (!d_rowptr && (k <= 0 || nnz != n * static_cast<int64_t>(k))) ||
+        (nnz > 0 && (!d_ids || !d_dist || !d_out_ids || !d_out_dist)))
+        return fail(SPHB_ERR_INVALID, "symmetrize_graph_dev: bad arguments");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    DevBuf<int64_t> rp;
+    if (!d_rowptr) {
+        SPHB_CUDA(rp.alloc(n + 1, s));
+        gm_fixed_rowptr<<<gm_grid(n + 1, 256, ctx().num_sms), 256, 0, s>>>(n, k, rp.p);
+        count_launch();
+        d_rowptr = rp.p;
+    }
+    return graph_minmerge_dev(n, d_rowptr, d_ids, d_dist, nnz, nullptr, n, d_out_rowptr, d_out_ids, d_out_dist, cap, out_nnz, s);
 }
 
 SPHB_API int sphb_merge_graph_nodes(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const uint64_t* parents,

@@ -371,3 +371,32 @@ def test_random_walk_slabs_concatenate_to_the_full_result(capi):
     np.testing.assert_array_equal(np.concatenate([p[2] for p in parts]), full[2])  # Philox keyed by the global start id
     e = capi.random_walks_slab(rp, c, v, 20, 6, 100, 100, capi.W_LINEAR, seed=5)
     assert e[0].tolist() == [0] and len(e[1]) == 0
+
+
+def test_symmetrize_graph_dev_resident(capi, oracle):
+    """Device-pointer variant on buffers that stay on the device (torch tensors on a B200; plain host arrays under tests/emu,
+    where device memory is host memory)."""
+    import os
+
+    n, k = 3000, 12
+    ids, dist = random_knn_graph(n, k, seed=5, dup_frac=0.02)
+    cap = 2 * n * k
+    ref = oracle.symmetrize_graph(ids, dist)
+    if os.environ.get("SPHB_EMULATE") == "1":
+        orp, oi, od = np.zeros(n + 1, np.int64), np.zeros(cap, np.int64), np.zeros(cap, np.float32)
+        m = capi.symmetrize_graph_dev(n, 0, k, ids.ctypes.data, dist.ctypes.data, n * k, orp.ctypes.data, oi.ctypes.data, od.ctypes.data, cap, 0)
+        got = (orp, oi[:m], od[:m])
+    else:
+        import torch
+
+        capi.init(0)
+        d_ids, d_dist = torch.from_numpy(ids).cuda(), torch.from_numpy(dist).cuda()
+        orp = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+        oi = torch.zeros(cap, dtype=torch.int64, device="cuda")
+        od = torch.zeros(cap, dtype=torch.float32, device="cuda")
+        torch.cuda.synchronize()
+        m = capi.symmetrize_graph_dev(n, 0, k, d_ids.data_ptr(), d_dist.data_ptr(), n * k, orp.data_ptr(), oi.data_ptr(), od.data_ptr(), cap,
+                                      capi.stream_ptr())
+        torch.cuda.synchronize()
+        got = (orp.cpu().numpy(), oi[:m].cpu().numpy(), od[:m].cpu().numpy())
+    eq3(got, ref)
