@@ -100,6 +100,42 @@ __global__ void gm_widen(const uint32_t* __restrict__ in, int64_t num, uint64_t*
 }
 // One warp per output row: entries sorted by (distance, index) -> ids / dist with ensureClosestPointIsSelf fused
 // (swap / overwrite-last-then-swap / shift-right, sph/utils/GraphUtils.cpp:23-95).
+__device__ __forceinline__ void gm_write_row(const uint64_t* ent, int64_t len, int64_t p, int64_t* __restrict__ out_ids,
+                                             float* __restrict__ out_dist, int lane) {
+    int64_t s = -1;
+    bool allzero = true;
+    for (int64_t base = 0; base < len; base += 32) {
+        const int64_t t = base + lane;
+        bool hit = false, nz = false;
+        if (t < len) {
+            const uint64_t w = ent[t];
+            hit = static_cast<int64_t>(w & 0xffffffffull) == p;
+            nz = ord2f(static_cast<uint32_t>(w >> 32)) != 0.f;
+        }
+        const unsigned mh = __ballot_sync(0xffffffffu, hit);
+        if (__any_sync(0xffffffffu, nz)) allzero = false;
+        if (mh && s < 0) s = base + (__ffs(mh) - 1);
+    }
+    const int mode = s == 0 ? 0 : (s > 0 ? 1 : (allzero ? 2 : 3));
+    for (int64_t t = lane; t < len; t += 32) {
+        int64_t src = t;
+        if (mode == 1) src = t == 0 ? s : (t == s ? 0 : t);
+        else if (mode == 2) src = t == len - 1 ? 0 : t;
+        else if (mode == 3) src = t == 0 ? 0 : t - 1;
+        const uint64_t w = ent[src];
+        int64_t id = static_cast<int64_t>(w & 0xffffffffull);
+        float d = ord2f(static_cast<uint32_t>(w >> 32));
+        if (t == 0 && mode == 2) {
+            id = p;
+            d = ord2f(static_cast<uint32_t>(ent[len - 1] >> 32));
+        } else if (t == 0 && mode == 3) {
+            id = p;
+            d = 0.f;
+        }
+        out_ids[t] = id;
+        out_dist[t] = d;
+    }
+}
 __global__ void gm_write_rows(int64_t n, const int64_t* __restrict__ rowptr, const uint64_t* __restrict__ ent, int64_t* __restrict__ out_ids,
                               float* __restrict__ out_dist) {
     const int lane = threadIdx.x & 31;
@@ -108,40 +144,44 @@ __global__ void gm_write_rows(int64_t n, const int64_t* __restrict__ rowptr, con
     for (int64_t p = warp; p < n; p += nwarps) {
         const int64_t b = rowptr[p], len = rowptr[p + 1] - b;
         if (len <= 0) continue;
-        int64_t s = -1;
-        bool allzero = true;
-        for (int64_t base = 0; base < len; base += 32) {
-            const int64_t t = base + lane;
-            bool hit = false, nz = false;
-            if (t < len) {
-                const uint64_t w = ent[b + t];
-                hit = static_cast<int64_t>(w & 0xffffffffull) == p;
-                nz = ord2f(static_cast<uint32_t>(w >> 32)) != 0.f;
-            }
-            const unsigned mh = __ballot_sync(0xffffffffu, hit);
-            if (__any_sync(0xffffffffu, nz)) allzero = false;
-            if (mh && s < 0) s = base + (__ffs(mh) - 1);
-        }
-        const int mode = s == 0 ? 0 : (s > 0 ? 1 : (allzero ? 2 : 3));
-        for (int64_t t = lane; t < len; t += 32) {
-            int64_t src = t;
-            if (mode == 1) src = t == 0 ? s : (t == s ? 0 : t);
-            else if (mode == 2) src = t == len - 1 ? 0 : t;
-            else if (mode == 3) src = t == 0 ? 0 : t - 1;
-            const uint64_t w = ent[b + src];
-            int64_t id = static_cast<int64_t>(w & 0xffffffffull);
-            float d = ord2f(static_cast<uint32_t>(w >> 32));
-            if (t == 0 && mode == 2) {
-                id = p;
-                d = ord2f(static_cast<uint32_t>(ent[b + len - 1] >> 32));
-            } else if (t == 0 && mode == 3) {
-                id = p;
-                d = 0.f;
-            }
-            out_ids[b + t] = id;
-            out_dist[b + t] = d;
-        }
+        gm_write_row(ent + b, len, p, out_ids + b, out_dist + b, lane);
     }
+}
+// Short rows (the common case: <= 2k - 1 entries after a symmetrisation): the unique records come out of the reduction grouped
+// by row already, so each warp orders its row by (distance, index) in shared memory and writes it — no further global sort.
+constexpr int GM_SORT_WARPS = 4;
+__global__ void __launch_bounds__(GM_SORT_WARPS * 32) gm_sort_write_rows(int64_t n, const int64_t* __restrict__ rowptr, const uint64_t* __restrict__ ent,
+                                                                         int cap, int64_t* __restrict__ out_ids, float* __restrict__ out_dist) {
+    extern __shared__ uint64_t gm_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = gm_keys + static_cast<size_t>(warp) * cap;
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * GM_SORT_WARPS + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * GM_SORT_WARPS;
+    for (int64_t p = gw; p < n; p += nw) {
+        const int64_t b = rowptr[p], len = rowptr[p + 1] - b;
+        if (len <= 0) continue;  // warp-uniform
+        for (int t = lane; t < cap; t += 32) sm[t] = t < len ? ent[b + t] : ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        gm_write_row(sm, len, p, out_ids + b, out_dist + b, lane);
+        __syncwarp();
+    }
+}
+// row pointers of records grouped by an ascending uint32 row id; max_len receives the longest row
+__global__ void gm_rowptr_from_rows(const uint32_t* __restrict__ rows, int64_t num, int64_t nrows, int64_t* __restrict__ rowptr) {
+    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; r <= nrows; r += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        int64_t lo = 0, hi = num;
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (static_cast<int64_t>(rows[mid]) < r) lo = mid + 1;
+            else hi = mid;
+        }
+        rowptr[r] = lo;
+    }
+}
+__global__ void gm_max_row_len(int64_t nrows, const int64_t* __restrict__ rowptr, int* __restrict__ max_len) {
+    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; r < nrows; r += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        atomicMax(max_len, static_cast<int>(min(rowptr[r + 1] - rowptr[r], static_cast<int64_t>(0x7fffffff))));
 }
 
 }  // namespace
@@ -176,26 +216,50 @@ int graph_minmerge_dev(int64_t n, const int64_t* d_rowptr, const int64_t* d_ids,
     SPHB_CUDA(cudaMemcpyAsync(&total, pos.p + num, sizeof(int), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaStreamSynchronize(s));
     if (total > cap) return fail(SPHB_ERR_CAPACITY, "graph merge: output capacity too small (2*nnz for symmetrise, nnz for merge always suffices)");
-    // unique (row, col, min distance) records -> per-row order (distance, index): stable sort by (distance, col), then by row
-    DevBuf<uint64_t> e0, e1, r0, r1;
-    DevBuf<uint32_t> w0, w1;
+    // unique (row, col, min distance) records, emitted in (row, col) order: grouped by row already
+    DevBuf<uint64_t> e0;
+    DevBuf<uint32_t> w0;
+    DevBuf<int> maxlen;
     SPHB_CUDA(e0.alloc(total, s));
-    SPHB_CUDA(e1.alloc(total, s));
-    SPHB_CUDA(r0.alloc(total, s));
-    SPHB_CUDA(r1.alloc(total, s));
     SPHB_CUDA(w0.alloc(total, s));
-    SPHB_CUDA(w1.alloc(total, s));
+    SPHB_CUDA(maxlen.alloc(1, s));
+    SPHB_CUDA(cudaMemsetAsync(maxlen.p, 0, sizeof(int), s));
     gm_reduce<<<gm_grid(num, 256, sms), 256, 0, s>>>(k1.p, v1.p, head.p, pos.p, num, sym ? 1 : 0, e0.p, w0.p);
-    count_launch();
-    if (int rc = sort_pairs<uint32_t>(e0.p, e1.p, w0.p, w1.p, total, 64, s)) return rc;
-    gm_widen<<<gm_grid(total, 256, sms), 256, 0, s>>>(w1.p, total, r0.p);
-    count_launch();
-    if (int rc = sort_pairs<uint64_t>(r0.p, r1.p, e1.p, e0.p, total, bits_for(static_cast<uint64_t>(n_out)), s)) return rc;
-    gm_rowptr_lower_bound<<<gm_grid(n_out + 1, 256, sms), 256, 0, s>>>(r1.p, total, 0, n_out, d_out_rowptr);
-    gm_write_rows<<<gm_grid(n_out * 32, 256, sms), 256, 0, s>>>(n_out, d_out_rowptr, e0.p, d_out_ids, d_out_dist);
-    count_launch(2);
+    gm_rowptr_from_rows<<<gm_grid(n_out + 1, 256, sms), 256, 0, s>>>(w0.p, total, n_out, d_out_rowptr);
+    gm_max_row_len<<<gm_grid(n_out, 256, sms), 256, 0, s>>>(n_out, d_out_rowptr, maxlen.p);
+    count_launch(3);
+    int hmax = 0;
+    SPHB_CUDA(cudaMemcpyAsync(&hmax, maxlen.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    constexpr int GM_SHORT_ROW = 2048;
+    if (hmax <= GM_SHORT_ROW) {
+        // per-row order (distance, index) in shared memory, one warp per row
+        int cap = 32;
+        while (cap < hmax) cap <<= 1;
+        const size_t smem = static_cast<size_t>(GM_SORT_WARPS) * cap * sizeof(uint64_t);
+        SPHB_CUDA(cudaFuncSetAttribute(gm_sort_write_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        const unsigned grid = static_cast<unsigned>(std::max<int64_t>(1, std::min<int64_t>((n_out + GM_SORT_WARPS - 1) / GM_SORT_WARPS, static_cast<int64_t>(sms) * 8)));
+        gm_sort_write_rows<<<grid, GM_SORT_WARPS * 32, smem, s>>>(n_out, d_out_rowptr, e0.p, cap, d_out_ids, d_out_dist);
+        count_launch();
+    } else {
+        // long rows (a merged node that absorbed many children): stable sort by (distance, col), then by row
+        DevBuf<uint64_t> e1, r0, r1;
+        DevBuf<uint32_t> w1;
+        SPHB_CUDA(e1.alloc(total, s));
+        SPHB_CUDA(r0.alloc(total, s));
+        SPHB_CUDA(r1.alloc(total, s));
+        SPHB_CUDA(w1.alloc(total, s));
+        if (int rc = sort_pairs<uint32_t>(e0.p, e1.p, w0.p, w1.p, total, 64, s)) return rc;
+        gm_widen<<<gm_grid(total, 256, sms), 256, 0, s>>>(w1.p, total, r0.p);
+        count_launch();
+        if (int rc = sort_pairs<uint64_t>(r0.p, r1.p, e1.p, e0.p, total, bits_for(static_cast<uint64_t>(n_out)), s)) return rc;
+        gm_write_rows<<<gm_grid(n_out * 32, 256, sms), 256, 0, s>>>(n_out, d_out_rowptr, e0.p, d_out_ids, d_out_dist);
+        count_launch();
+        SPHB_CUDA(cudaGetLastError());
+        SPHB_CUDA(cudaStreamSynchronize(s));  // e1 / r0 / r1 / w1 are released at the end of this block
+    }
     SPHB_CUDA(cudaGetLastError());
-    SPHB_CUDA(cudaStreamSynchronize(s));  // e0 / r1 are released on return
+    SPHB_CUDA(cudaStreamSynchronize(s));  // e0 / w0 are released on return
     *out_nnz = total;
     return 0;
 }

@@ -261,6 +261,8 @@ template <class T>
 inline T atomicAdd(T* p, T v) { T o = *p; *p = o + v; return o; }
 inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { unsigned long long o = *p; *p = o + v; return o; }
 template <class T>
+inline T atomicMax(T* p, T v) { T o = *p; if (v > o) *p = v; return o; }
+template <class T>
 inline T atomicMin(T* p, T v) { T o = *p; if (v < o) *p = v; return o; }
 template <class T>
 inline T atomicExch(T* p, T v) { T o = *p; *p = v; return o; }

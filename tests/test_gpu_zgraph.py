@@ -400,3 +400,15 @@ def test_symmetrize_graph_dev_resident(capi, oracle):
         torch.cuda.synchronize()
         got = (orp.cpu().numpy(), oi[:m].cpu().numpy(), od[:m].cpu().numpy())
     eq3(got, ref)
+
+
+def test_merge_graph_nodes_long_row_path(capi, oracle):
+    # one merged node absorbs half of the graph: its row (> 2048 distinct neighbours) takes the global-sort path, the rest the
+    # shared-memory path is exercised by the other tests (rows <= 2048)
+    n = 6000
+    ids, dist = random_knn_graph(n, 12, seed=41)
+    parents = np.concatenate([np.zeros(3000), np.arange(1, 3001)]).astype(np.uint64)
+    a = capi.merge_graph_nodes(ids, dist, parents, 3001)
+    b = oracle.merge_graph_nodes(ids, dist, parents, 3001)
+    assert np.diff(b[0]).max() > 2048
+    eq3(a, b)
