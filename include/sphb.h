@@ -98,6 +98,10 @@ SPHB_API int sphb_knn_last_stats(int64_t* out8);
 /* device time of the last tensor-core kNN call in ms (CUDA events on its stream): [0] operand
  * preparation, [1] the tcgen05 sweep kernel(s), [2] the exact re-rank kernel(s), [3] overflow fallbacks. */
 SPHB_API int sphb_knn_last_timing(float* ms4);
+/* Global ids of the query rows of the last kNN call that left the main 1-product sweep: which = 0 rows re-swept with the
+ * 3-product filter (their candidate band overflowed), which = 1 rows recomputed by the exact SIMT kernel.  Writes at most
+ * cap ids to out; *count receives the total.  Diagnostic (parity checks sample these rows); no reference counterpart. */
+SPHB_API int sphb_knn_last_overflow_rows(int which, int64_t* out, int64_t cap, int64_t* count);
 /*
  * Stage A followed by the level-0 P rows of Stage B in one call — the pair
  * ComputeHierarchy::compute() runs back to back (computeKnnGraph, sph/ComputeHierarchy.cpp:97-159,
@@ -257,6 +261,54 @@ SPHB_API int sphb_level_knn_overlap(const int64_t* knn_ids, int64_t n, int k_dat
  * unseeded random_device (:455-474); the caller passes the sampled lists in that case. */
 SPHB_API int sphb_euclid_hausdorff(const float* x, int64_t n, int d, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix,
                                    const int64_t* pa, const int64_t* pb, int64_t npairs, float* out);
+
+/* ---- resident level pipeline: device-pointer variants + the fused level call ---------------
+ * Same semantics as the host-pointer entry points above; all pointers prefixed d_ are DEVICE pointers, `stream` is a
+ * cudaStream_t, counts (*out_nnz) are written on the host after one stream synchronisation.  A caller that keeps the
+ * matrices of LevelSimilarities::compute (sph/LevelSimilarities.cpp:118-182) in HBM binds these and moves nothing over
+ * PCIe between the stages. */
+/* utils::doRandomWalks for start points [q0, q1) (sph/utils/SparseMatrixAlgorithms.cpp:34-290). */
+SPHB_API int sphb_random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, uint64_t num_walks,
+                                   uint64_t walk_len, int weighting, float prune_value, uint64_t prune_steps, uint64_t seed, int remove_diagonal,
+                                   int normalize, int64_t q0, int64_t q1, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap,
+                                   int64_t* out_nnz, void* stream);
+/* utils::mergeNodesRandomWalks (sph/utils/SparseMatrixAlgorithms.cpp:292-352). */
+SPHB_API int sphb_rw_merge_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, const uint64_t* d_parents,
+                               int64_t n_merged, int norm, int weight_by_size, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val,
+                               int64_t cap, int64_t* out_nnz, void* stream);
+/* utils::createSimilarities (sph/utils/SparseMatrixAlgorithms.cpp:963-1378); outputs as sphb_create_similarities. */
+SPHB_API int sphb_create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k,
+                                          float prune_val, int variant, const int64_t* d_comp_sizes, uint32_t* d_out_cols, float* d_out_vals,
+                                          int32_t* d_row_nnz, void* stream);
+/* utils::computeGaussianDistributions in place (sph/utils/GraphNormalization.cpp:38-189); max_row_nnz <= 0: computed on the device. */
+SPHB_API int sphb_prow_gaussian_inplace_dev(int64_t n, const int64_t* d_rowptr, float* d_val, int max_row_nnz, float perplexity, int ignore,
+                                            void* stream);
+/* utils::symmetrizeTSNE / symmetrizeUMAP (sph/utils/HDILibHelper.hpp:260-302). */
+SPHB_API int sphb_symmetrize_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int umap,
+                                 int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, void* stream);
+/* utils::findTopK / findBottomK batched (sph/utils/SparseMatrixAlgorithms.cpp:720-776); max_row_nnz <= 0: computed on the device. */
+SPHB_API int sphb_find_k_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int max_row_nnz, int64_t k, int top,
+                             uint32_t* d_out_cols, float* d_out_vals, int32_t* d_row_nnz, void* stream);
+/*
+ * One level of LevelSimilarities::computeProbDistOnLevel's useRandomWalks branch + symmetrizeOutput in ONE call on the level's
+ * random-walk matrix (sph/LevelSimilarities.cpp:460-508, 566-581, 589-623), every intermediate resident in HBM:
+ *   pair_sims = 1: createSimilarities(walks, k, prune_val, comp_sizes) (randomWalkPairSims, the default),
+ *   pair_sims = 0: per-row top-k conversion (convertEigenSparseVecToHDILibSparseVec);
+ *   scheme 1 (NormalizationScheme::TSNE): computeGaussianDistributions(rows, perplexity, ignore = -1) in place; 0: none;
+ *   exact zeros erased; symmetrize != 0 (with scheme 1): symmetrizeTSNE.
+ * Output CSR (the level's SparseMatHDI): out_rowptr[n+1], out_col / out_val with capacity `cap` entries
+ * (2 * n * k always suffices); *out_nnz receives the size.
+ */
+SPHB_API int sphb_level_prob_dist_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k,
+                                      float prune_val, int variant, const int64_t* d_comp_sizes, int pair_sims, float perplexity, int scheme,
+                                      int symmetrize, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz,
+                                      void* stream);
+SPHB_API int sphb_level_prob_dist(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int64_t k, float prune_val, int variant,
+                                  const int64_t* comp_sizes, int pair_sims, float perplexity, int scheme, int symmetrize, int64_t* out_rowptr,
+                                  uint32_t* out_col, float* out_val, int64_t cap, int64_t* out_nnz);
+/* device time in ms of the stages of the last sphb_level_prob_dist[_dev] call (CUDA events on its stream):
+ * [0] similarities / top-k, [1] compaction to CSR, [2] Gaussian rows, [3] zero removal, [4] symmetrise. */
+SPHB_API int sphb_level_last_timing(float* ms5);
 
 #ifdef __cplusplus
 }

@@ -20,6 +20,7 @@
 #include <cstring>
 #include <dlfcn.h>
 #include <numeric>
+#include <omp.h>
 
 namespace {
 
@@ -200,6 +201,11 @@ inline void heap_replace_top(int k, float* hv, int64_t* hi, float v, int64_t id)
     }
     hv[i] = v; hi[i] = id;
 }
+using setnt_fn = void (*)(int);
+using getnt_fn = int (*)();
+setnt_fn g_set_threads = nullptr;
+getnt_fn g_get_threads = nullptr;
+double g_blas_stats[4] = {0, 0, 0, 0};  // sgemm seconds (mean per thread), heap seconds (mean per thread), sgemm flop, threads
 }  // namespace
 
 ORC_API int orc_blas_init(const char* openblas_path) {
@@ -208,10 +214,42 @@ ORC_API int orc_blas_init(const char* openblas_path) {
     if (!h) return -1;
     g_sgemm = reinterpret_cast<sgemm_fn>(dlsym(h, "scipy_cblas_sgemm64_"));
     if (!g_sgemm) g_sgemm = reinterpret_cast<sgemm_fn>(dlsym(h, "cblas_sgemm64_"));
+    g_set_threads = reinterpret_cast<setnt_fn>(dlsym(h, "scipy_openblas_set_num_threads64_"));
+    if (!g_set_threads) g_set_threads = reinterpret_cast<setnt_fn>(dlsym(h, "openblas_set_num_threads64_"));
+    g_get_threads = reinterpret_cast<getnt_fn>(dlsym(h, "scipy_openblas_get_num_threads64_"));
+    if (!g_get_threads) g_get_threads = reinterpret_cast<getnt_fn>(dlsym(h, "openblas_get_num_threads64_"));
     return g_sgemm ? 0 : -2;
 }
 
+// [0] sgemm seconds and [1] heap-update seconds of the last orc_knn_blas_l2 call (mean over its threads),
+// [2] sgemm flop of the call, [3] threads used.
+ORC_API void orc_knn_blas_last_stats(double* out4) {
+    for (int i = 0; i < 4; ++i) out4[i] = g_blas_stats[i];
+}
+
+// A standalone sgemm of the arm's block shape (4096 x 1024 x d) with the library's own threading, repeated for
+// about `seconds`: the host's sgemm rate the arm's achieved rate is compared with.  Returns GFLOP/s.
+ORC_API double orc_sgemm_standalone_gflops(int d, double seconds) {
+    if (!g_sgemm) return -1.0;
+    const int64_t M = 4096, N = 1024;
+    std::vector<float> A(static_cast<size_t>(M) * d, 0.5f), B(static_cast<size_t>(N) * d, 0.25f), Cm(static_cast<size_t>(M) * N);
+    g_sgemm(101, 111, 112, M, N, d, 1.0f, A.data(), d, B.data(), d, 0.0f, Cm.data(), N);
+    const double t0 = omp_get_wtime();
+    int reps = 0;
+    while (omp_get_wtime() - t0 < seconds) {
+        g_sgemm(101, 111, 112, M, N, d, 1.0f, A.data(), d, B.data(), d, 0.0f, Cm.data(), N);
+        ++reps;
+    }
+    return 2.0 * M * N * d * reps / (omp_get_wtime() - t0) / 1e9;
+}
+
 // queries = rows [q0, q1) of x; database = all n rows.  ids/dist sized (q1-q0)*k.
+// faiss' blocking (4096 queries x 1024 database rows per sgemm, then per-row max-heap updates).  Threading: faiss runs
+// a multi-threaded BLAS sgemm and then an OpenMP loop over the block's rows; with a pthread OpenBLAS next to libgomp
+// the two pools spin against each other between the phases (round 1: 46 GFLOP/s on 16 cores).  Here the OpenMP team
+// owns the whole block: each thread takes a strip of the 4096 queries, calls a SINGLE-threaded sgemm for its strip
+// against the 1024-row database block and updates its own rows' heaps — same arithmetic per (query, database) pair,
+// same heap admission order (database index ascending), no cross-pool hand-off.
 ORC_API int orc_knn_blas_l2(const float* x, int64_t n, int d, int k, int64_t q0, int64_t q1, int64_t* ids, float* dist) {
     if (!g_sgemm) return -1;
     const int64_t nq = q1 - q0;
@@ -222,30 +260,52 @@ ORC_API int orc_knn_blas_l2(const float* x, int64_t n, int d, int k, int64_t q0,
         for (int c = 0; c < d; ++c) s += x[i * d + c] * x[i * d + c];
         norms[i] = s;
     }
-    const int64_t bs_x = 4096, bs_y = 1024;
-    std::vector<float> ip(static_cast<size_t>(bs_x * bs_y));
+    const int64_t bs_x = 4096, bs_y = 1024, strip = 128;
     std::vector<float> hv(static_cast<size_t>(nq) * k, FLT_MAX);
     std::vector<int64_t> hi(static_cast<size_t>(nq) * k, -1);
+    const int prev_threads = g_get_threads ? g_get_threads() : 0;
+    if (g_set_threads) g_set_threads(1);
+    double t_gemm = 0.0, t_heap = 0.0;
+    int threads = 1;
     for (int64_t i0 = 0; i0 < nq; i0 += bs_x) {
         const int64_t i1 = std::min(nq, i0 + bs_x);
-        for (int64_t j0 = 0; j0 < n; j0 += bs_y) {
-            const int64_t j1 = std::min(n, j0 + bs_y);
-            // C[i][j] = <x_i, y_j>, row-major (CblasRowMajor=101, NoTrans=111, Trans=112)
-            g_sgemm(101, 111, 112, i1 - i0, j1 - j0, d, 1.0f, x + (q0 + i0) * d, d, x + j0 * d, d, 0.0f, ip.data(), j1 - j0);
-#pragma omp parallel for schedule(static)
-            for (int64_t i = i0; i < i1; ++i) {
-                float* v = hv.data() + i * k;
-                int64_t* id = hi.data() + i * k;
-                const float* row = ip.data() + (i - i0) * (j1 - j0);
-                const float ni = norms[q0 + i];
-                for (int64_t j = j0; j < j1; ++j) {
-                    float dis = ni + norms[j] - 2 * row[j - j0];
-                    if (dis < 0) dis = 0;
-                    if (dis < v[0]) heap_replace_top(k, v, id, dis, j);
+        const int64_t nstrips = (i1 - i0 + strip - 1) / strip;
+#pragma omp parallel reduction(+ : t_gemm, t_heap)
+        {
+            std::vector<float> ip(static_cast<size_t>(strip * bs_y));
+#pragma omp single
+            threads = omp_get_num_threads();
+            for (int64_t j0 = 0; j0 < n; j0 += bs_y) {
+                const int64_t j1 = std::min(n, j0 + bs_y);
+#pragma omp for schedule(static) nowait
+                for (int64_t sp = 0; sp < nstrips; ++sp) {
+                    const int64_t a = i0 + sp * strip, b = std::min(i1, a + strip);
+                    double t0 = omp_get_wtime();
+                    // C[i][j] = <x_i, y_j>, row-major (CblasRowMajor=101, NoTrans=111, Trans=112)
+                    g_sgemm(101, 111, 112, b - a, j1 - j0, d, 1.0f, x + (q0 + a) * d, d, x + j0 * d, d, 0.0f, ip.data(), j1 - j0);
+                    double t1 = omp_get_wtime();
+                    t_gemm += t1 - t0;
+                    for (int64_t i = a; i < b; ++i) {
+                        float* v = hv.data() + i * k;
+                        int64_t* id = hi.data() + i * k;
+                        const float* row = ip.data() + (i - a) * (j1 - j0);
+                        const float ni = norms[q0 + i];
+                        for (int64_t j = j0; j < j1; ++j) {
+                            float dis = ni + norms[j] - 2 * row[j - j0];
+                            if (dis < 0) dis = 0;
+                            if (dis < v[0]) heap_replace_top(k, v, id, dis, j);
+                        }
+                    }
+                    t_heap += omp_get_wtime() - t1;
                 }
             }
         }
     }
+    if (g_set_threads && prev_threads > 0) g_set_threads(prev_threads);
+    g_blas_stats[0] = t_gemm / threads;
+    g_blas_stats[1] = t_heap / threads;
+    g_blas_stats[2] = 2.0 * static_cast<double>(nq) * static_cast<double>(n) * d;
+    g_blas_stats[3] = threads;
 #pragma omp parallel for
     for (int64_t i = 0; i < nq; ++i) {
         std::vector<std::pair<float, int64_t>> tmp(k);

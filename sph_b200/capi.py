@@ -42,6 +42,7 @@ SIGNATURES = {
     "sphb_knn_exact_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sphb_knn_last_stats": (C.c_int, [i64p]),
     "sphb_knn_last_timing": (C.c_int, [f32p]),
+    "sphb_knn_last_overflow_rows": (C.c_int, [C.c_int, i64p, C.c_int64, i64p]),
     "sphb_knn_graph_prow": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int64, i64p, f32p, u32p, f32p]),
     "sphb_prow_gaussian_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, C.c_float, u32p, f32p, f64p]),
     "sphb_prow_gaussian_graph_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -70,6 +71,22 @@ SIGNATURES = {
     "sphb_level_knn_walks": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int64, i64p, f32p]),
     "sphb_level_knn_overlap": (C.c_int, [i64p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, C.c_int64, i64p, f32p]),
     "sphb_euclid_hausdorff": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
+    "sphb_random_walks_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
+                                        C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, i64p, C.c_void_p]),
+    "sphb_rw_merge_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p,
+                                    C.c_void_p, C.c_void_p, C.c_int64, i64p, C.c_void_p]),
+    "sphb_create_similarities_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_float, C.c_int, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sphb_prow_gaussian_inplace_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]),
+    "sphb_symmetrize_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                      i64p, C.c_void_p]),
+    "sphb_find_k_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_void_p]),
+    "sphb_level_prob_dist_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_float, C.c_int, C.c_void_p, C.c_int,
+                                           C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, i64p, C.c_void_p]),
+    "sphb_level_prob_dist": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, C.c_int, C.c_float, C.c_int, C.c_int, i64p,
+                                       u32p, f32p, C.c_int64, i64p]),
+    "sphb_level_last_timing": (C.c_int, [f32p]),
 }
 
 
@@ -135,6 +152,15 @@ def knn_last_stats() -> dict:
     _check(load().sphb_knn_last_stats(_p(out, i64p)))
     return dict(tensor_core=int(out[0]), compactions=int(out[1]), accepted=int(out[2]), kp=int(out[3]), overflow_rows=int(out[4]), q_tiles=int(out[5]),
                 passes=int(out[6]), resweep_rows=int(out[7]))
+
+
+def knn_last_overflow_rows(which: int = 0, cap: int = 1 << 20) -> np.ndarray:
+    """Global ids of the rows of the last kNN call that were re-swept with the 3-product filter (which = 0) or recomputed by
+    the exact SIMT kernel (which = 1)."""
+    cnt = np.zeros(1, np.int64)
+    out = np.zeros(max(1, cap), np.int64)
+    _check(load().sphb_knn_last_overflow_rows(which, _p(out, i64p), cap, _p(cnt, i64p)))
+    return out[: min(cap, int(cnt[0]))].copy()
 
 
 def knn_last_timing() -> dict:
@@ -500,3 +526,75 @@ def euclid_hausdorff(x, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
     _check(load().sphb_euclid_hausdorff(_p(x, f32p), n, d, len(comp_ptr) - 1, _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p),
                                         len(pa), _p(out, f32p)))
     return out
+
+
+# ------------------------------------------------------------------ resident level pipeline
+def level_prob_dist(rowptr, col, val, k: int, prune_val: float = 1e-4, variant: int = 0, comp_sizes=None, pair_sims: bool = True,
+                    perplexity: float = 0.0, scheme: int = 1, symmetrize: bool = True):
+    """LevelSimilarities' useRandomWalks branch + symmetrizeOutput in one call (host buffers): returns the level's P as CSR."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    cap = max(1, 2 * n * k)
+    orp = np.zeros(n + 1, np.int64)
+    oc = np.zeros(cap, np.uint32)
+    ov = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    cs = None if comp_sizes is None else np.ascontiguousarray(comp_sizes, np.int64)
+    _check(load().sphb_level_prob_dist(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), k, prune_val, variant, None if cs is None else _p(cs, i64p),
+                                       int(pair_sims), perplexity, scheme, int(symmetrize), _p(orp, i64p), _p(oc, u32p), _p(ov, f32p), cap,
+                                       _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oc[:m].copy(), ov[:m].copy()
+
+
+def level_last_timing() -> dict:
+    out = np.zeros(5, np.float32)
+    _check(load().sphb_level_last_timing(_p(out, f32p)))
+    return dict(similarities_ms=float(out[0]), to_csr_ms=float(out[1]), gaussian_ms=float(out[2]), remove_zeros_ms=float(out[3]),
+                symmetrize_ms=float(out[4]))
+
+
+def random_walks_dev(n, rowptr_ptr, col_ptr, val_ptr, num_walks, walk_len, weighting, seed, q0, q1, out_rowptr_ptr, out_col_ptr, out_val_ptr, cap,
+                     stream, prune_value=0.0, prune_steps=0, remove_diagonal=True, normalize=True) -> int:
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_random_walks_dev(n, rowptr_ptr, col_ptr, val_ptr, num_walks, walk_len, weighting, prune_value, prune_steps, seed,
+                                        int(remove_diagonal), int(normalize), q0, q1, out_rowptr_ptr, out_col_ptr, out_val_ptr, cap, _p(nnz, i64p), stream))
+    return int(nnz[0])
+
+
+def rw_merge_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, parents_ptr, n_merged, norm, weight_by_size, out_rowptr_ptr, out_col_ptr, out_val_ptr, cap,
+                 stream) -> int:
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_rw_merge_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, parents_ptr, n_merged, int(norm), int(weight_by_size), out_rowptr_ptr,
+                                    out_col_ptr, out_val_ptr, cap, _p(nnz, i64p), stream))
+    return int(nnz[0])
+
+
+def create_similarities_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, out_cols_ptr, out_vals_ptr, row_nnz_ptr, stream):
+    _check(load().sphb_create_similarities_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, out_cols_ptr, out_vals_ptr,
+                                               row_nnz_ptr, stream))
+
+
+def prow_gaussian_inplace_dev(n, rowptr_ptr, val_ptr, max_row_nnz, perplexity, ignore, stream):
+    _check(load().sphb_prow_gaussian_inplace_dev(n, rowptr_ptr, val_ptr, max_row_nnz, perplexity, ignore, stream))
+
+
+def symmetrize_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, umap, out_rowptr_ptr, out_col_ptr, out_val_ptr, cap, stream) -> int:
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_symmetrize_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, int(umap), out_rowptr_ptr, out_col_ptr, out_val_ptr, cap, _p(nnz, i64p),
+                                      stream))
+    return int(nnz[0])
+
+
+def find_k_dev(n, rowptr_ptr, col_ptr, val_ptr, max_row_nnz, k, top, out_cols_ptr, out_vals_ptr, row_nnz_ptr, stream):
+    _check(load().sphb_find_k_dev(n, rowptr_ptr, col_ptr, val_ptr, max_row_nnz, k, int(top), out_cols_ptr, out_vals_ptr, row_nnz_ptr, stream))
+
+
+def level_prob_dist_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, pair_sims, perplexity, scheme, symmetrize,
+                        out_rowptr_ptr, out_col_ptr, out_val_ptr, cap, stream) -> int:
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_level_prob_dist_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, int(pair_sims), perplexity,
+                                           scheme, int(symmetrize), out_rowptr_ptr, out_col_ptr, out_val_ptr, cap, _p(nnz, i64p), stream))
+    return int(nnz[0])

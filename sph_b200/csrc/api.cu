@@ -98,6 +98,8 @@ bool knn_tc_supported(int64_t n, int d, int k);
 void knn_set_stats(const int64_t* s);
 void knn_get_stats(int64_t* s);
 void knn_get_timing(float* ms4);
+void knn_clear_overflow_rows();
+const std::vector<int64_t>& knn_overflow_rows(int which);
 int prow_graph_launch(const int64_t*, const float*, int64_t, int, float, int, uint32_t*, float*, double*, cudaStream_t);
 int prow_inplace_launch(int64_t, const int64_t*, float*, int, float, int, cudaStream_t);
 int prow_flat_launch(const float*, int64_t, int, double, float*, cudaStream_t);
@@ -181,6 +183,7 @@ SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int m
     if (use_tc) return knn_tc_launch(d_x, n, d, k, metric, l2_squared, q0, q1, d_ids, d_dist, s, g_force_path >= 3 ? g_force_path - 2 : 0);
     const int64_t st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     knn_set_stats(st);
+    knn_clear_overflow_rows();
     return knn_simt_launch(d_x, n, d, k, metric, l2_squared, q0, q1, nullptr, nullptr, 0, d_ids, d_dist, s);
 }
 
@@ -211,6 +214,14 @@ SPHB_API int sphb_knn_exact(const float* x, int64_t n, int d, int k, int metric,
 SPHB_API int sphb_knn_last_stats(int64_t* out8) {
     if (!out8) return fail(SPHB_ERR_INVALID, "null pointer");
     knn_get_stats(out8);
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_knn_last_overflow_rows(int which, int64_t* out, int64_t cap, int64_t* count) {
+    if (!count || (cap > 0 && !out) || which < 0 || which > 1) return fail(SPHB_ERR_INVALID, "knn_last_overflow_rows: bad arguments");
+    const std::vector<int64_t>& v = knn_overflow_rows(which);
+    *count = static_cast<int64_t>(v.size());
+    for (int64_t i = 0; i < cap && i < *count; ++i) out[i] = v[static_cast<size_t>(i)];
     return SPHB_OK;
 }
 

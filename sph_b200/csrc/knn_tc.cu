@@ -1375,6 +1375,20 @@ static float g_knn_ms[4] = {0.f, 0.f, 0.f, 0.f};  // prep, main sweep(s), re-ran
 void knn_get_timing(float* ms4) { for (int i = 0; i < 4; ++i) ms4[i] = g_knn_ms[i]; }
 void knn_set_stats(const int64_t* s) { for (int i = 0; i < 8; ++i) g_knn_stats[i] = s[i]; }
 void knn_get_stats(int64_t* s) { for (int i = 0; i < 8; ++i) s[i] = g_knn_stats[i]; }
+// global ids of the rows of the last call that left the main sweep: [0] re-swept with the 3-product filter, [1] recomputed
+// by the exact SIMT kernel (parity checks sample them, bench.py "parity")
+static std::vector<int64_t> g_knn_ovf_rows[2];
+void knn_clear_overflow_rows() { g_knn_ovf_rows[0].clear(); g_knn_ovf_rows[1].clear(); }
+const std::vector<int64_t>& knn_overflow_rows(int which) { return g_knn_ovf_rows[which ? 1 : 0]; }
+static int record_overflow_rows(int which, const int64_t* d_rows, int count, cudaStream_t stream) {
+    if (count <= 0) return 0;
+    std::vector<int64_t>& v = g_knn_ovf_rows[which];
+    const size_t old = v.size();
+    v.resize(old + static_cast<size_t>(count));
+    SPHB_CUDA(cudaMemcpyAsync(v.data() + old, d_rows, static_cast<size_t>(count) * sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
+    SPHB_CUDA(cudaStreamSynchronize(stream));
+    return 0;
+}
 
 bool knn_tc_supported(int64_t n, int d, int k) {
     if (d < 8 || n < 1024) return false;
@@ -1703,6 +1717,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
                   float* d_dist, cudaStream_t stream, int flavour) {
     using namespace tc;
     const int64_t nq = q1 - q0;
+    knn_clear_overflow_rows();
     if (nq <= 0) return 0;
     KnnJob J{};
     J.x = d_x; J.n = n; J.d = d; J.k = k; J.metric = metric; J.l2_squared = l2_squared; J.stream = stream;
@@ -1802,6 +1817,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         if (int rc = sweep_and_rerank(J, op, op, qa, qb, nullptr, q0, d_ids, d_dist, ovf3_rows.p, ovf3_count.p, &hovf, &sweep_ms, &rerank_ms)) return rc;
         if (ovf_frac) *ovf_frac = static_cast<double>(hovf) / static_cast<double>(qb - qa);
         if (hovf == 0) return 0;
+        if (int rc = record_overflow_rows(1, ovf3_rows.p, hovf, stream)) return rc;
         EventTimer tf;
         tf.start(stream);
         if (int rc = simt_rows_exact(ovf3_rows.p, ovf3_count.p, hovf)) return rc;
@@ -1836,6 +1852,8 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         if (int rc = sweep_and_rerank(J, sub, op3, 0, pending1, ovf_rows.p, q0, d_ids, d_dist, ovf2_rows.p, ovf2_count.p, &hovf2, &sm, &rm)) return rc;
         const auto t3 = now();
         resweep_rows += pending1;
+        if (int rc = record_overflow_rows(0, ovf_rows.p, pending1, stream)) return rc;
+        if (int rc = record_overflow_rows(1, ovf2_rows.p, hovf2, stream)) return rc;
         if (int rc = simt_rows_exact(ovf2_rows.p, ovf2_count.p, hovf2)) return rc;
         if (dbg)
             fprintf(stderr, "[knn timing] re-sweep of %d rows: 3-pass operands %.1f ms, gathered A %.1f ms, sweep+rerank %.1f ms (kernel %.1f + %.1f), simt %.1f ms\n",

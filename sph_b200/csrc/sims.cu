@@ -4,14 +4,24 @@
 //
 // Row-wise Gustavson SpGEMM that never materialises the product: S = sqrt(prune(A)) and its
 // transpose (built by one radix sort on (column, row)) stay in HBM/L2; one persistent CTA per output
-// row scatters s_ic * s_jc into its private dense accumulator slab (float atomics in L2, first-touch
-// list), then selects the bottom k of (-ln C, column) with per-warp sorted lists and a final
-// block-wide bitonic merge.  The accumulator slab is reset on the way out, so it is touched only
-// where the row has candidates.  Algorithmic bytes: 8 B per expanded product + 8 n k written.
+// row accumulates s_ic * s_jc into a dense accumulator row, then selects the bottom k of (-ln C, column)
+// with per-warp sorted lists and a final block-wide bitonic merge.  Two accumulator homes:
+//   DENSE (n <= what fits beside the lists in 220 KB of shared memory, ~52 k components): the row lives in
+//     SHARED memory and the CTA walks the row's entries c in order, one column of Sᵀ at a time — the rows j
+//     of a column are distinct, so the 256 threads update distinct accumulators with plain LDS / FADD / STS
+//     (no atomics; a barrier between columns), the (row, value) pairs of the next 16 column segments are in
+//     flight in registers while the current ones are added.  Every C[i][j] is therefore summed in ascending c
+//     — the order of the reference's sparse dot — and the result is deterministic.  Round 1's version of this
+//     kernel (float atomics with return into an L2 slab) ran 381 ms at C2 level 1 (ncu); see DESIGN.md §4.5.
+//   SLAB (larger n): a private slab per CTA in HBM/L2, float atomics, first-touch list (the round-1 kernel).
+// Candidates are screened with a fast fp32 log before the reference's fp64 log is evaluated (D is monotone in C,
+// so anything whose approximate D exceeds the running k-th D by more than 1e-4 cannot enter the list).
+// Algorithmic bytes: 8 B per expanded product (row id + value of Sᵀ) + 8 n k written.
 #include "../../include/sphb.h"
 #include "graph_common.cuh"
 
 #include <cfloat>
+#include <cstdlib>
 
 namespace sphb {
 
@@ -89,49 +99,126 @@ struct SimsParams {
     const float* sval;
     const int64_t* colptr;    // Sᵀ: for column c the entries tkeys/tval[colptr[c] .. colptr[c+1]) (row = low 32 bits of the key)
     const uint64_t* tkeys;
+    const uint32_t* trow;     // low halves of tkeys (row ids), 4 B per product for the DENSE kernel
     const float* tval;
     float prune_val;
     int hdi;                  // 1: createSimilaritiesHDI semantics, 0: createSimilaritiesEigen + bottom-k conversion
     int k, cap;               // cap: per-warp list capacity, power of two >= k + 32
-    float* acc;               // [grid][n] zero-initialised accumulator slabs
-    uint32_t* touched;        // [grid][n]
+    float* acc;               // SLAB: [grid][n] zero-initialised accumulator slabs
+    uint32_t* touched;        // SLAB: [grid][n]
+    int ch;                   // DENSE: accumulator floats in shared memory (>= n)
     uint32_t* out_cols;       // [n][k], padded 0xFFFFFFFF
     float* out_vals;          // [n][k]
     int32_t* row_nnz;
 };
 
 constexpr int SIMS_WARPS = 8;
+constexpr int SIMS_EB = 512;   // DENSE: row entries staged per batch (column start, length, s_ic)
+constexpr int SIMS_U = 16;     // DENSE: column segments in flight per thread
 
+__global__ void sims_split_rows(const uint64_t* __restrict__ keys, int64_t num, uint32_t* __restrict__ rows) {
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < num; t += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        rows[t] = static_cast<uint32_t>(keys[t]);
+}
+
+template <bool DENSE>
 __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsParams P) {
-    extern __shared__ uint64_t sm_keys[];  // SIMS_WARPS * cap keys
+    extern __shared__ uint64_t sm_keys[];  // SIMS_WARPS * cap keys | DENSE: entry batch | accumulator row
     __shared__ unsigned int s_touched, s_valid, s_nsel;
     __shared__ double s_sum;
+    constexpr int THREADS = SIMS_WARPS * 32;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float* acc = P.acc + static_cast<size_t>(blockIdx.x) * P.n;
-    uint32_t* touched = P.touched + static_cast<size_t>(blockIdx.x) * P.n;
+    float* acc = DENSE ? nullptr : P.acc + static_cast<size_t>(blockIdx.x) * P.n;
+    uint32_t* touched = DENSE ? nullptr : P.touched + static_cast<size_t>(blockIdx.x) * P.n;
     uint64_t* mylist = sm_keys + static_cast<size_t>(warp) * P.cap;
+    // DENSE shared-memory carve-up behind the lists
+    int64_t* e_cb = reinterpret_cast<int64_t*>(sm_keys + static_cast<size_t>(SIMS_WARPS) * P.cap);
+    int* e_len = reinterpret_cast<int*>(e_cb + SIMS_EB);
+    float* e_sic = reinterpret_cast<float*>(e_len + SIMS_EB);
+    float* sacc = e_sic + SIMS_EB;
     const int k = P.k, cap = P.cap;
+    if constexpr (DENSE) {
+        for (int t = threadIdx.x; t < P.ch; t += THREADS) sacc[t] = 0.f;
+    }
     for (int64_t i = blockIdx.x; i < P.n; i += gridDim.x) {
         if (threadIdx.x == 0) { s_touched = 0; s_valid = 0; s_nsel = 0; s_sum = 0.0; }
         __syncthreads();
-        // ---- 1. expand: C[i][j] += s_ic * s_jc, one warp per entry c of row i, lanes over column c of S
         const int64_t rb = P.srowptr[i], re = P.srowptr[i + 1];
-        for (int64_t e = rb + warp; e < re; e += SIMS_WARPS) {
-            const uint32_t c = P.scol[e];
-            const float sic = P.sval[e];
-            const int64_t cb = P.colptr[c], ce = P.colptr[c + 1];
-            for (int64_t f = cb + lane; f < ce; f += 32) {
-                const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
-                const float old = atomicAdd(acc + j, sic * P.tval[f]);
-                if (old == 0.f) touched[atomicAdd(&s_touched, 1u)] = j;
+        if constexpr (DENSE) {
+            // ---- 1. expand, one column of Sᵀ at a time (distinct rows j within a column: no atomics)
+            for (int64_t eb = rb; eb < re; eb += SIMS_EB) {
+                const int ne = static_cast<int>(min(static_cast<int64_t>(SIMS_EB), re - eb));
+                for (int t = threadIdx.x; t < ne; t += THREADS) {
+                    const uint32_t c = P.scol[eb + t];
+                    const int64_t cb = P.colptr[c];
+                    e_cb[t] = cb;
+                    e_len[t] = static_cast<int>(P.colptr[c + 1] - cb);
+                    e_sic[t] = P.sval[eb + t];
+                }
+                __syncthreads();
+                // uniform cursor over the column segments (THREADS entries each) of this batch
+                int ce = 0, cseg = 0;
+                uint32_t jj[2][SIMS_U];
+                float vv[2][SIMS_U], ss[2][SIMS_U];
+                int flag[2][SIMS_U];  // bit 0: this thread has an element, bit 1: segment exists, bit 2: last segment of its column
+                auto fetch = [&](int b) {
+#pragma unroll
+                    for (int u = 0; u < SIMS_U; ++u) {
+                        int f = 0;
+                        if (ce < ne) {
+                            const int off = cseg * THREADS + static_cast<int>(threadIdx.x);
+                            const int len = e_len[ce];
+                            f = 2;
+                            if (off < len) {
+                                const int64_t a = e_cb[ce] + off;
+                                jj[b][u] = __ldg(P.trow + a);
+                                vv[b][u] = __ldg(P.tval + a);
+                                f |= 1;
+                            }
+                            ss[b][u] = e_sic[ce];
+                            ++cseg;
+                            if (cseg * THREADS >= len) { f |= 4; ++ce; cseg = 0; }
+                        }
+                        flag[b][u] = f;
+                    }
+                };
+                fetch(0);
+                int b = 0;
+                while (true) {
+                    const bool more = ce < ne;
+                    if (more) fetch(b ^ 1);
+                    bool done = false;
+#pragma unroll
+                    for (int u = 0; u < SIMS_U; ++u) {
+                        const int f = flag[b][u];
+                        if (!(f & 2)) { done = true; break; }   // uniform
+                        if (f & 1) sacc[jj[b][u]] = __fadd_rn(sacc[jj[b][u]], __fmul_rn(ss[b][u], vv[b][u]));
+                        if (f & 4) __syncthreads();             // uniform: the next segment belongs to another column
+                    }
+                    if (done || !more) break;
+                    b ^= 1;
+                }
+                __syncthreads();  // e_* are rewritten by the next batch
             }
+        } else {
+            // ---- 1. expand: C[i][j] += s_ic * s_jc, one warp per entry c of row i, lanes over column c of S
+            for (int64_t e = rb + warp; e < re; e += SIMS_WARPS) {
+                const uint32_t c = P.scol[e];
+                const float sic = P.sval[e];
+                const int64_t cb = P.colptr[c], ce = P.colptr[c + 1];
+                for (int64_t f = cb + lane; f < ce; f += 32) {
+                    const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
+                    const float old = atomicAdd(acc + j, sic * P.tval[f]);
+                    if (old == 0.f) touched[atomicAdd(&s_touched, 1u)] = j;
+                }
+            }
+            __syncthreads();
         }
-        __syncthreads();
-        const unsigned int T = s_touched;
+        const unsigned int T = DENSE ? static_cast<unsigned int>(P.n) : s_touched;
         // ---- 2. (Eigen variant) number of entries that survive the product prune, diagonal included
         if (!P.hdi) {
             unsigned int v = 0;
-            for (unsigned int t = threadIdx.x; t < T; t += blockDim.x) v += eigen_keep(acc[touched[t]], P.prune_val) ? 1u : 0u;
+            for (unsigned int t = threadIdx.x; t < T; t += blockDim.x) v += eigen_keep(DENSE ? sacc[t] : acc[touched[t]], P.prune_val) ? 1u : 0u;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
             if (lane == 0 && v) atomicAdd(&s_valid, v);
@@ -141,22 +228,24 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
         // ---- 3. per-warp bottom-k of (D, column); the accumulator is reset on the way
         int cnt = 0;
         uint64_t kth = ~0ull;
+        float dk_screen = INFINITY;  // running k-th D + margin: a candidate whose fast-log D exceeds it cannot enter the list
         for (unsigned int base = warp * 32; base < T; base += SIMS_WARPS * 32) {
             const unsigned int t = base + lane;
             bool pass = false;
             uint64_t key = ~0ull;
             if (t < T) {
-                const uint32_t j = touched[t];
-                const float c = acc[j];
-                acc[j] = 0.f;
-                if (eigen_keep(c, P.prune_val)) {
+                const uint32_t j = DENSE ? t : touched[t];
+                float c;
+                if constexpr (DENSE) { c = sacc[t]; sacc[t] = 0.f; }
+                else { c = acc[j]; acc[j] = 0.f; }
+                const bool diag = static_cast<int64_t>(j) == i;
+                if (eigen_keep(c, P.prune_val) && (diag || c == 1.f || !(-__logf(c) > dk_screen))) {
                     float dv;
                     bool use = true;
                     if (P.hdi) {
-                        use = static_cast<int64_t>(j) != i;                                  // :1250-1252
+                        use = !diag;                                                                  // :1250-1252
                         dv = c == 1.f ? c : -1.f * static_cast<float>(log(static_cast<double>(c)));  // :1290-1292
                     } else {
-                        const bool diag = static_cast<int64_t>(j) == i;
                         dv = diag ? c : -1.f * static_cast<float>(log(static_cast<double>(c)));      // :1143-1153
                         if (multi && (diag || dv == 0.f)) use = false;                        // removeDiagonalElements(keepSingleEntry)
                     }
@@ -176,6 +265,7 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
                     warp_bitonic_sort(mylist, cap, lane);
                     cnt = min(cnt, k);
                     kth = (cnt == k) ? mylist[k - 1] : ~0ull;
+                    if (cnt == k) dk_screen = key_val(kth) + 1e-4f;
                 }
             }
         }
@@ -266,21 +356,35 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
     // ---- the row kernel
     int cap = 64;
     while (cap < k + 32) cap <<= 1;
-    const size_t smem = static_cast<size_t>(SIMS_WARPS) * cap * sizeof(uint64_t);
-    SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * 2);
-    // bound the accumulator slabs to 8 GiB
-    while (grid > 1 && static_cast<double>(grid) * n * 8.0 > 8.0 * (1ull << 30)) grid /= 2;
-    DevBuf<float> acc;
-    DevBuf<uint32_t> touched;
-    SPHB_CUDA(acc.alloc(static_cast<size_t>(grid) * n, s));
-    SPHB_CUDA(touched.alloc(static_cast<size_t>(grid) * n, s));
-    SPHB_CUDA(cudaMemsetAsync(acc.p, 0, static_cast<size_t>(grid) * n * sizeof(float), s));
+    const size_t list_bytes = static_cast<size_t>(SIMS_WARPS) * cap * sizeof(uint64_t);
     SimsParams P{};
     P.n = n; P.srowptr = srowptr.p; P.scol = scol.p; P.sval = sval.p; P.colptr = colptr.p; P.tkeys = tk1.p; P.tval = tval.p;
     P.prune_val = prune_val; P.hdi = hdi ? 1 : 0; P.k = static_cast<int>(k); P.cap = cap;
-    P.acc = acc.p; P.touched = touched.p; P.out_cols = d_out_cols; P.out_vals = d_out_vals; P.row_nnz = d_row_nnz;
-    sims_row_kernel<<<static_cast<unsigned>(grid), SIMS_WARPS * 32, smem, s>>>(P);
+    P.out_cols = d_out_cols; P.out_vals = d_out_vals; P.row_nnz = d_row_nnz;
+    const size_t dense_fixed = list_bytes + static_cast<size_t>(SIMS_EB) * 16;
+    const size_t dense_smem = dense_fixed + static_cast<size_t>(n) * sizeof(float);
+    DevBuf<float> acc;
+    DevBuf<uint32_t> touched, trow;
+    if (dense_smem <= 220 * 1024 && !getenv("SPHB_SIMS_SLAB")) {
+        SPHB_CUDA(trow.alloc(std::max<int64_t>(snnz, 1), s));
+        sims_split_rows<<<g, 256, 0, s>>>(tk1.p, snnz, trow.p);
+        count_launch();
+        P.trow = trow.p;
+        P.ch = static_cast<int>(n);
+        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dense_smem)));
+        const int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * (dense_smem <= 100 * 1024 ? 2 : 1));
+        sims_row_kernel<true><<<static_cast<unsigned>(grid), SIMS_WARPS * 32, dense_smem, s>>>(P);
+    } else {
+        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(list_bytes)));
+        int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * 2);
+        // bound the accumulator slabs to 8 GiB
+        while (grid > 1 && static_cast<double>(grid) * n * 8.0 > 8.0 * (1ull << 30)) grid /= 2;
+        SPHB_CUDA(acc.alloc(static_cast<size_t>(grid) * n, s));
+        SPHB_CUDA(touched.alloc(static_cast<size_t>(grid) * n, s));
+        SPHB_CUDA(cudaMemsetAsync(acc.p, 0, static_cast<size_t>(grid) * n * sizeof(float), s));
+        P.acc = acc.p; P.touched = touched.p;
+        sims_row_kernel<false><<<static_cast<unsigned>(grid), SIMS_WARPS * 32, list_bytes, s>>>(P);
+    }
     count_launch();
     SPHB_CUDA(cudaGetLastError());
     return 0;

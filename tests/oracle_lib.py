@@ -47,6 +47,10 @@ class Oracle:
         L.orc_check_all_neighbors_exist.argtypes = [i64p, C.c_int64]
         L.orc_blas_init.argtypes = [C.c_char_p]
         L.orc_knn_blas_l2.argtypes = [f32p, C.c_int64, C.c_int, C.c_int, C.c_int64, C.c_int64, i64p, f32p]
+        L.orc_knn_blas_last_stats.argtypes = [f64p]
+        L.orc_knn_blas_last_stats.restype = None
+        L.orc_sgemm_standalone_gflops.argtypes = [C.c_int, C.c_double]
+        L.orc_sgemm_standalone_gflops.restype = C.c_double
         L.orc_gaussian_row.argtypes = [f32p, f32p, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int]
         L.orc_gaussian_row.restype = C.c_double
         L.orc_prow_gaussian_graph.argtypes = [i64p, f32p, C.c_int64, C.c_int, C.c_float, u32p, f32p, f64p]
@@ -130,6 +134,15 @@ class Oracle:
         if rc != 0:
             raise RuntimeError("orc_knn_blas_l2 failed (OpenBLAS not initialised)")
         return ids, dist
+
+    def knn_blas_last_stats(self):
+        out = np.zeros(4, np.float64)
+        self.lib.orc_knn_blas_last_stats(_p(out, f64p))
+        return dict(sgemm_s=float(out[0]), heap_s=float(out[1]), sgemm_flop=float(out[2]), threads=int(out[3]),
+                    sgemm_gflops=float(out[2] / out[0] / 1e9) if out[0] > 0 else 0.0)
+
+    def sgemm_standalone_gflops(self, d, seconds=1.0):
+        return float(self.lib.orc_sgemm_standalone_gflops(int(d), float(seconds)))
 
     # ---- Stage B
     def gaussian_row(self, dist, perplexity, tol=1e-6, ignore=0, max_iter=200):

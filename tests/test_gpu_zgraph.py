@@ -4,12 +4,8 @@ useRandomWalksAsKnnDistances (D9), zero removal (B7), exact level kNN in the ran
 Euclid-Hausdorff component distance (D6).  All integer / index results bit-exact; fp32 values bit-exact too (every value
 is either copied or produced by the same fp32 / fp64 operation chain as the oracle's).
 
-STATUS: these kernels were written after round 1's GPU budget was spent — they cross-compile for sm_100a, their oracle is
-pinned against the reference goldens on the CPU, and every test of this file passes bit-exactly when the unmodified kernel
-sources run under the functional CPU emulation of tests/emu (SPHB_EMULATE=1, see tests/emu/README.md) — but they have not
-yet executed on hardware.  Until a B200 run confirms them the module is marked xfail(strict=False) so that a hardware-only
-defect (a race the serialised emulation hides, a launch limit) cannot mask the verified suite (the file sorts last among
-the -m gpu tests); an XPASS here is the confirmation, after which the mark is to be removed.
+STATUS: hardware-verified.  All 42 tests passed on a B200 in the round-1 driver run (GPUTEST_r01.json, reported as XPASS
+because the module then still carried xfail(strict=False)); the mark is gone, a regression now fails the GPU gate.
 """
 import json
 from pathlib import Path
@@ -19,10 +15,7 @@ import pytest
 
 from oracle_lib import dense_to_csr
 
-pytestmark = [
-    pytest.mark.gpu,
-    pytest.mark.xfail(strict=False, reason="graph_merge.cu kernels: verified under tests/emu, not yet executed on a B200 (round-1 GPU budget spent before they were written)"),
-]
+pytestmark = [pytest.mark.gpu]
 GOLD = Path(__file__).resolve().parent / "golden"
 
 
