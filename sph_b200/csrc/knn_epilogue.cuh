@@ -263,11 +263,86 @@ __device__ __forceinline__ void compact_row_select_n(RowList& me, int L, uint64_
     }
     __syncwarp();
 }
+// ---- in-sweep compaction, round 2: selection by bisection on the ordered 32-bit values ---------------------
+// The sorting network above costs ~2.5 k dependent warp instructions (10.6 k cycles measured) per compaction; with one
+// compaction per ~20 database tiles somewhere in the CTA and only two accumulator stages per M half to absorb it, those
+// cycles were the MMA issuer's whole wait for a free accumulator (26 % of the sweep, profiles/r02_sweep_prof.txt).
+// What a compaction needs is ANY upper bound T of the row's k-th smallest value (thr = T + band(T) then still keeps every
+// true neighbour; a looser T only keeps a few more candidates): bisect the ordered-u32 value range, counting the
+// list's values <= pivot with one compare per register and a REDUX per probe, and stop as soon as the count lies in
+// [k, k + 8].  ~15 probes of ~40 independent instructions instead of a 45-stage network.
+template <int R>
+__device__ __forceinline__ void compact_row_bisect_n(RowList& me, int L, uint64_t* __restrict__ buf_L, int k, int keep_max, int cap, int lane,
+                                                     const BandConsts& bc) {
+    const int cntL = __shfl_sync(0xffffffffu, me.cnt, L);
+    uint64_t x[R];
+    uint32_t v[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int e = r * 32 + lane;  // coalesced
+        x[r] = (e < cntL) ? buf_L[e] : ~0ull;
+        v[r] = static_cast<uint32_t>(x[r] >> 32);
+    }
+    int m = cntL;
+    float limit = INFINITY;
+    int ovf = 0;
+    if (cntL >= k) {
+        uint32_t lo = 0xffffffffu, hi = 0u;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            lo = min(lo, v[r]);
+            hi = max(hi, (r * 32 + lane < cntL) ? v[r] : 0u);
+        }
+        lo = __reduce_min_sync(0xffffffffu, lo);
+        hi = __reduce_max_sync(0xffffffffu, hi);  // count(v <= hi) = cntL >= k: the invariant of the search
+        while (lo < hi) {
+            const uint32_t mid = lo + ((hi - lo) >> 1);
+            int c = 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) c += (v[r] <= mid) ? 1 : 0;  // padding is 0xffffffff > mid (mid < hi)
+            c = __reduce_add_sync(0xffffffffu, c);
+            if (c >= k) {
+                hi = mid;
+                if (c <= k + 8) break;
+            } else {
+                lo = mid + 1;
+            }
+        }
+        const float gk = ord2f(hi);  // >= the k-th smallest value of the list
+        const float band = bc.passes == 3 ? me.eps2 : band_1pass(gk, me.un, me.dun, bc);
+        limit = __fadd_ru(gk, __shfl_sync(0xffffffffu, band, L));
+        const uint32_t lim = f2ord(limit);
+        const unsigned lt = (1u << lane) - 1u;
+        int base = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool keep = (r * 32 + lane < cntL) && v[r] <= lim;
+            const unsigned mk = __ballot_sync(0xffffffffu, keep);
+            const int pos = base + __popc(mk & lt);
+            if (keep && pos < keep_max) buf_L[pos] = x[r];  // pos <= r*32 + lane: never ahead of an unread slot (all reads are done)
+            base += __popc(mk);
+        }
+        m = base;
+        if (m > keep_max) {
+            m = keep_max;
+            ovf = 1;
+        }
+    }
+    if (lane == L) {
+        me.cnt = m;
+        me.thr = limit;
+        me.ovf |= ovf;
+        me.trig = min(cap - 64, m + bc.step);
+    }
+    __syncwarp();
+}
+
 // lists of at most half the capacity take the half-width network
 template <int R>
 __device__ __forceinline__ void compact_row_select(RowList& me, int L, uint64_t* __restrict__ buf_L, int k, int keep_max, int lane,
                                                    const BandConsts& bc) {
     const int cntL = __shfl_sync(0xffffffffu, me.cnt, L);
+#ifdef SPHB_COMPACT_SORT_SELECT
     if constexpr (R >= 8) {
         if (cntL <= 16 * R) {
             compact_row_select_n<R / 2>(me, L, buf_L, k, keep_max, 32 * R, lane, bc);
@@ -275,6 +350,15 @@ __device__ __forceinline__ void compact_row_select(RowList& me, int L, uint64_t*
         }
     }
     compact_row_select_n<R>(me, L, buf_L, k, keep_max, 32 * R, lane, bc);
+#else
+    if constexpr (R >= 8) {
+        if (cntL <= 16 * R) {
+            compact_row_bisect_n<R / 2>(me, L, buf_L, k, keep_max, 32 * R, lane, bc);
+            return;
+        }
+    }
+    compact_row_bisect_n<R>(me, L, buf_L, k, keep_max, 32 * R, lane, bc);
+#endif
 }
 
 // Filter one 32-column chunk of the accumulator tile held in v[] (columns jbase..jbase+31).

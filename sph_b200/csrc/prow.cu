@@ -14,6 +14,17 @@ namespace sphb {
 
 // Returns sigma (0 when not found).  On return p[] holds the fp32 probabilities
 // exactly as the reference leaves them (normalised if found, uniform if not).
+//
+// The iterate sequence is the reference's (sph/utils/HDILibHelper.hpp:40-93: fp64 beta, doubling / halving until bracketed,
+// then bisection), and every decision that can depend on fp64 detail is taken by the reference's own fp64 evaluation.
+// What changed against round 1 (ncu: issue slots 79 % busy, fp64 pipe 41 % — instruction bound, ~25 fp64 instructions
+// per exp): an iteration first evaluates H in fp32 on SHIFTED exponents x_j = beta (d_j - d_min) >= 0 (H is invariant
+// under the shift, and the shifted sum lies in [1, n], so nothing over- or underflows), together with a rigorous bound
+// on |H_fp32 - H_reference|:  dH = sum_j p_j e_j (x_j - E + 1) for relative errors e_j of the terms,
+// |e_j| <= 2e-7 x_j + 5e-7 (fp32 product, ex2.approx, the reference's own fp32 round trip of p), hence
+// |dH| <= 2e-7 (E[x²] + E (E + 1)) + 5e-7 (2 E + 1) with E = E_p[x]; E[x²] is accumulated in the same pass.  If
+// |H_fp32 - ln(perplexity)| exceeds four times that bound plus the tolerance, the branch the reference takes is
+// certain and the fp64 evaluation is skipped; near convergence (the last ~6 of ~30 steps) every step is fp64 as before.
 template <int R>
 __device__ __forceinline__ double perplexity_search(const float (&dist)[R], float (&p)[R], int nn, int lane, double perplexity, double tol,
                                                     int ignore) {
@@ -22,43 +33,101 @@ __device__ __forceinline__ double perplexity_search(const float (&dist)[R], floa
     double min_beta = -DBL_MAX, max_beta = DBL_MAX;
     double sum = DBL_MIN;
     const double logp = log(perplexity);
+    // fp32 screen: shifted distances
+    float dd[R];
+    float dmin = INFINITY, dmax = -INFINITY;
+    int nvalid = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int idx = lane + 32 * r;
+        if (idx < nn && idx != ignore) {
+            dmin = fminf(dmin, dist[r]);
+            dmax = fmaxf(dmax, dist[r]);
+            ++nvalid;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        dmin = fminf(dmin, __shfl_xor_sync(0xffffffffu, dmin, o));
+        dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+        nvalid += __shfl_xor_sync(0xffffffffu, nvalid, o);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int idx = lane + 32 * r;
+        dd[r] = (idx < nn && idx != ignore) ? dist[r] - dmin : INFINITY;  // excluded slots contribute exp(-inf) = 0
+    }
+    const bool screen_ok = nvalid >= 2 && dmin >= 0.f && dmax < 1.0e30f;
+    const float logp_f = static_cast<float>(logp);
+    const float tol_f = static_cast<float>(tol) * 1.01f + 1.0e-6f;  // + the fp32 rounding of log(s), E and ln(perplexity)
     int iter = 0;
     while (!found && iter < 200) {
-        double s = 0.0;
+        bool decided = false, up = false;  // up: H > ln(perplexity), beta must grow
+        if (screen_ok && beta < 1.0e30 && beta > 1.0e-30) {
+            const float bf = static_cast<float>(beta);
+            float s = 0.f, h = 0.f, q = 0.f;
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int idx = lane + 32 * r;
-            if (idx < nn) {
-                if (idx == ignore) {
-                    p[r] = 0.f;
-                } else {
-                    const double v = exp(-beta * static_cast<double>(dist[r]));
-                    p[r] = static_cast<float>(v);
-                    s += v;
-                }
+            for (int r = 0; r < R; ++r) {
+                const float x = bf * dd[r];              // +inf for excluded slots (bf > 0)
+                const float v = __expf(-x);              // ex2.approx(-x log2 e); 0 for x = +inf
+                const float xv = (v > 0.f) ? x * v : 0.f;  // inf * 0 guarded
+                s += v;
+                h += xv;
+                q = fmaf(xv, (v > 0.f) ? x : 0.f, q);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                s += __shfl_xor_sync(0xffffffffu, s, o);
+                h += __shfl_xor_sync(0xffffffffu, h, o);
+                q += __shfl_xor_sync(0xffffffffu, q, o);
+            }
+            const float E = h / s, E2 = q / s;
+            const float Hd = (E + logf(s)) - logp_f;
+            const float err = 4.f * (2.0e-7f * (E2 + E * (E + 1.f)) + 5.0e-7f * (2.f * E + 1.f)) + tol_f;
+            if (fabsf(Hd) > err) {  // false for NaN: falls through to the fp64 evaluation
+                decided = true;
+                up = Hd > 0.f;
             }
         }
-        s = warp_sum(s);
-        sum = DBL_MIN + s;
-        double h = 0.0;
+        if (!decided) {
+            double s = 0.0;
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int idx = lane + 32 * r;
-            if (idx < nn && idx != ignore) h += beta * static_cast<double>(dist[r] * p[r]);
+            for (int r = 0; r < R; ++r) {
+                const int idx = lane + 32 * r;
+                if (idx < nn) {
+                    if (idx == ignore) {
+                        p[r] = 0.f;
+                    } else {
+                        const double v = exp(-beta * static_cast<double>(dist[r]));
+                        p[r] = static_cast<float>(v);
+                        s += v;
+                    }
+                }
+            }
+            s = warp_sum(s);
+            sum = DBL_MIN + s;
+            double h = 0.0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int idx = lane + 32 * r;
+                if (idx < nn && idx != ignore) h += beta * static_cast<double>(dist[r] * p[r]);
+            }
+            h = warp_sum(h);
+            const double H = (h / sum) + log(sum);
+            const double Hdiff = H - logp;
+            if (Hdiff < tol && -Hdiff < tol) found = true;
+            else up = Hdiff > 0;
         }
-        h = warp_sum(h);
-        const double H = (h / sum) + log(sum);
-        const double Hdiff = H - logp;
-        if (Hdiff < tol && -Hdiff < tol) {
-            found = true;
-        } else if (Hdiff > 0) {
-            min_beta = beta;
-            if (max_beta == DBL_MAX || max_beta == -DBL_MAX) beta *= 2.0;
-            else beta = (beta + max_beta) / 2.0;
-        } else {
-            max_beta = beta;
-            if (min_beta == -DBL_MAX || min_beta == DBL_MAX) beta /= 2.0;
-            else beta = (beta + min_beta) / 2.0;
+        if (!found) {
+            if (up) {
+                min_beta = beta;
+                if (max_beta == DBL_MAX || max_beta == -DBL_MAX) beta *= 2.0;
+                else beta = (beta + max_beta) / 2.0;
+            } else {
+                max_beta = beta;
+                if (min_beta == -DBL_MAX || min_beta == DBL_MAX) beta /= 2.0;
+                else beta = (beta + min_beta) / 2.0;
+            }
         }
         ++iter;
     }

@@ -116,6 +116,12 @@ constexpr int SIMS_WARPS = 8;
 constexpr int SIMS_EB = 512;   // DENSE: row entries staged per batch (column start, length, s_ic)
 constexpr int SIMS_U = 16;     // DENSE: column segments in flight per thread
 
+struct SegBuf {
+    uint32_t j[SIMS_U];
+    float v[SIMS_U], s[SIMS_U];
+    int f[SIMS_U];
+};
+
 __global__ void sims_split_rows(const uint64_t* __restrict__ keys, int64_t num, uint32_t* __restrict__ rows) {
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < num; t += static_cast<int64_t>(gridDim.x) * blockDim.x)
         rows[t] = static_cast<uint32_t>(keys[t]);
@@ -156,12 +162,12 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
                     e_sic[t] = P.sval[eb + t];
                 }
                 __syncthreads();
-                // uniform cursor over the column segments (THREADS entries each) of this batch
+                // uniform cursor over the column segments (THREADS entries each) of this batch; two register buffers of
+                // SIMS_U segments each, addressed statically (a runtime buffer index would put a select behind every
+                // load and serialise them)
                 int ce = 0, cseg = 0;
-                uint32_t jj[2][SIMS_U];
-                float vv[2][SIMS_U], ss[2][SIMS_U];
-                int flag[2][SIMS_U];  // bit 0: this thread has an element, bit 1: segment exists, bit 2: last segment of its column
-                auto fetch = [&](int b) {
+                SegBuf b0, b1;
+                auto fetch = [&](SegBuf& B) {
 #pragma unroll
                     for (int u = 0; u < SIMS_U; ++u) {
                         int f = 0;
@@ -171,32 +177,36 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
                             f = 2;
                             if (off < len) {
                                 const int64_t a = e_cb[ce] + off;
-                                jj[b][u] = __ldg(P.trow + a);
-                                vv[b][u] = __ldg(P.tval + a);
+                                B.j[u] = __ldg(P.trow + a);
+                                B.v[u] = __ldg(P.tval + a);
                                 f |= 1;
                             }
-                            ss[b][u] = e_sic[ce];
+                            B.s[u] = e_sic[ce];
                             ++cseg;
                             if (cseg * THREADS >= len) { f |= 4; ++ce; cseg = 0; }
                         }
-                        flag[b][u] = f;
+                        B.f[u] = f;
                     }
                 };
-                fetch(0);
-                int b = 0;
-                while (true) {
-                    const bool more = ce < ne;
-                    if (more) fetch(b ^ 1);
-                    bool done = false;
+                // returns true when the buffer ended before its last slot (no more segments)
+                auto consume = [&](const SegBuf& B) -> bool {
 #pragma unroll
                     for (int u = 0; u < SIMS_U; ++u) {
-                        const int f = flag[b][u];
-                        if (!(f & 2)) { done = true; break; }   // uniform
-                        if (f & 1) sacc[jj[b][u]] = __fadd_rn(sacc[jj[b][u]], __fmul_rn(ss[b][u], vv[b][u]));
-                        if (f & 4) __syncthreads();             // uniform: the next segment belongs to another column
+                        const int f = B.f[u];
+                        if (!(f & 2)) return true;                // uniform
+                        if (f & 1) sacc[B.j[u]] = __fadd_rn(sacc[B.j[u]], __fmul_rn(B.s[u], B.v[u]));
+                        if (f & 4) __syncthreads();               // uniform: the next segment belongs to another column
                     }
-                    if (done || !more) break;
-                    b ^= 1;
+                    return false;
+                };
+                fetch(b0);
+                while (true) {
+                    bool more = ce < ne;
+                    if (more) fetch(b1);
+                    if (consume(b0) || !more) break;
+                    more = ce < ne;
+                    if (more) fetch(b0);
+                    if (consume(b1) || !more) break;
                 }
                 __syncthreads();  // e_* are rewritten by the next batch
             }
