@@ -112,14 +112,13 @@ struct SimsParams {
     int32_t* row_nnz;
 };
 
-constexpr int SIMS_WARPS = 8;
+constexpr int SIMS_WARPS = 16;
 constexpr int SIMS_EB = 512;   // DENSE: row entries staged per batch (column start, length, s_ic)
-constexpr int SIMS_U = 16;     // DENSE: column segments in flight per thread
+constexpr int SIMS_D = 8;      // DENSE: columns per register group (two groups: one being added, one in flight)
 
-struct SegBuf {
-    uint32_t j[SIMS_U];
-    float v[SIMS_U], s[SIMS_U];
-    int f[SIMS_U];
+struct ColGroup {
+    uint32_t j[SIMS_D][2];
+    float v[SIMS_D][2], s[SIMS_D];
 };
 
 __global__ void sims_split_rows(const uint64_t* __restrict__ keys, int64_t num, uint32_t* __restrict__ rows) {
@@ -162,51 +161,58 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
                     e_sic[t] = P.sval[eb + t];
                 }
                 __syncthreads();
-                // uniform cursor over the column segments (THREADS entries each) of this batch; two register buffers of
-                // SIMS_U segments each, addressed statically (a runtime buffer index would put a select behind every
-                // load and serialise them)
-                int ce = 0, cseg = 0;
-                SegBuf b0, b1;
-                auto fetch = [&](SegBuf& B) {
+                // register-staged software pipeline over the columns of this batch: while group A (SIMS_D columns) is
+                // added, the (row, value) pairs of group B are in flight.  A thread holds the first two elements of
+                // every column of a group (columns longer than 2 * THREADS finish with direct loads); the two groups
+                // are separate objects so that every register is addressed statically.  (The first version of this
+                // loop drove a flag-per-slot cursor: ncu counted 111 warp instructions per 32 products, issue-bound.)
+                ColGroup ga, gb;
+                auto load_group = [&](ColGroup& G, int c0) {
 #pragma unroll
-                    for (int u = 0; u < SIMS_U; ++u) {
-                        int f = 0;
-                        if (ce < ne) {
-                            const int off = cseg * THREADS + static_cast<int>(threadIdx.x);
-                            const int len = e_len[ce];
-                            f = 2;
-                            if (off < len) {
-                                const int64_t a = e_cb[ce] + off;
-                                B.j[u] = __ldg(P.trow + a);
-                                B.v[u] = __ldg(P.tval + a);
-                                f |= 1;
+                    for (int d = 0; d < SIMS_D; ++d) {
+                        const int c = c0 + d;
+                        if (c < ne) {  // uniform
+                            const int len = e_len[c];
+                            const int64_t cb = e_cb[c];
+                            G.s[d] = e_sic[c];
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int off = e * THREADS + static_cast<int>(threadIdx.x);
+                                if (off < len) {
+                                    G.j[d][e] = __ldg(P.trow + cb + off);
+                                    G.v[d][e] = __ldg(P.tval + cb + off);
+                                }
                             }
-                            B.s[u] = e_sic[ce];
-                            ++cseg;
-                            if (cseg * THREADS >= len) { f |= 4; ++ce; cseg = 0; }
                         }
-                        B.f[u] = f;
                     }
                 };
-                // returns true when the buffer ended before its last slot (no more segments)
-                auto consume = [&](const SegBuf& B) -> bool {
+                auto consume_group = [&](const ColGroup& G, int c0) {
 #pragma unroll
-                    for (int u = 0; u < SIMS_U; ++u) {
-                        const int f = B.f[u];
-                        if (!(f & 2)) return true;                // uniform
-                        if (f & 1) sacc[B.j[u]] = __fadd_rn(sacc[B.j[u]], __fmul_rn(B.s[u], B.v[u]));
-                        if (f & 4) __syncthreads();               // uniform: the next segment belongs to another column
+                    for (int d = 0; d < SIMS_D; ++d) {
+                        const int c = c0 + d;
+                        if (c >= ne) break;  // uniform
+                        const int len = e_len[c];
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int off = e * THREADS + static_cast<int>(threadIdx.x);
+                            if (off < len) sacc[G.j[d][e]] = __fadd_rn(sacc[G.j[d][e]], __fmul_rn(G.s[d], G.v[d][e]));
+                        }
+                        if (len > 2 * THREADS) {  // uniform; the rows of one column are distinct, no barrier inside a column
+                            const int64_t cb = e_cb[c];
+                            for (int off = 2 * THREADS + static_cast<int>(threadIdx.x); off < len; off += THREADS) {
+                                const uint32_t j = __ldg(P.trow + cb + off);
+                                sacc[j] = __fadd_rn(sacc[j], __fmul_rn(G.s[d], __ldg(P.tval + cb + off)));
+                            }
+                        }
+                        __syncthreads();  // the next column may hit the same rows from other threads
                     }
-                    return false;
                 };
-                fetch(b0);
-                while (true) {
-                    bool more = ce < ne;
-                    if (more) fetch(b1);
-                    if (consume(b0) || !more) break;
-                    more = ce < ne;
-                    if (more) fetch(b0);
-                    if (consume(b1) || !more) break;
+                load_group(ga, 0);
+                for (int c0 = 0; c0 < ne; c0 += 2 * SIMS_D) {
+                    load_group(gb, c0 + SIMS_D);
+                    consume_group(ga, c0);
+                    load_group(ga, c0 + 2 * SIMS_D);
+                    consume_group(gb, c0 + SIMS_D);
                 }
                 __syncthreads();  // e_* are rewritten by the next batch
             }

@@ -54,6 +54,11 @@ def main():
         res[f"fused_stage_ms_rep{r}"] = capi.level_last_timing()
         res[f"fused_equals_staged_rep{r}"] = bool(np.array_equal(frp, orp) and np.array_equal(fc, oc) and np.array_equal(fv, ov))
         res[f"wall_ms_rep{r}"] = {a: 1e3 * b for a, b in t.items()}
+    keepm = mv > 1e-4 * 1e-5
+    lens = np.bincount(mc[keepm].astype(np.int64), minlength=n1).astype(np.float64)
+    res["sims_products"] = float((lens ** 2).sum())
+    res["sims_col_len_max"] = float(lens.max())
+    res["sims_col_len_mean"] = float(lens.mean())
     res.update(walk_nnz=int(wrp[-1]), merged_nnz=int(mrp[-1]), sim_nnz=int(prp[-1]), p_nnz=int(orp[-1]))
     print(json.dumps(res))
 
