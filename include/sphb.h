@@ -112,6 +112,20 @@ SPHB_API int sphb_knn_last_overflow_rows(int which, int64_t* out, int64_t cap, i
 SPHB_API int sphb_knn_graph_prow(const float* x, int64_t n, int d, int k, int metric, int l2_squared, float perplexity,
                                  int64_t q0, int64_t q1, int64_t* ids, float* dist, uint32_t* cols, float* vals);
 
+/*
+ * Exact kNN of an explicit list of query rows WITHOUT any device allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same result contract as sphb_knn_exact (fp64 pair keys, (distance, index) order,
+ * fused post-passes); output row r holds the neighbours of point d_rows[r].  All pointers are DEVICE pointers.
+ * The scratch (per-segment candidate lists) is a fixed 8 MiB device array inside the library, held by every GPU that
+ * loads the library until exit.  Limits: nrows <= 256 and k <= 128 per call (SPHB_ERR_CAPACITY beyond).  The call makes no
+ * cudaMalloc / cudaFree / allocating library call; the first call on a device looks up the array's address once
+ * (cudaGetSymbolAddress) and, if sphb_init was not called yet, creates the library stream — make one call before a
+ * graph capture.  All calls share the array: calls that overlap on the GPU (two streams, two threads) race.
+ */
+SPHB_API int sphb_knn_rows_noalloc_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, const int64_t* d_rows,
+                                       int64_t nrows, int64_t* d_ids, float* d_dist, void* stream);
+
 /* ---- Stage B: perplexity-calibrated probability rows -------------------- */
 /*
  * Replaces utils::computeGaussianDistributions(const GraphBaseInterface&, vector<T>&, float)

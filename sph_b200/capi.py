@@ -42,6 +42,8 @@ SIGNATURES = {
     "sphb_knn_exact_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sphb_knn_last_stats": (C.c_int, [i64p]),
     "sphb_knn_last_timing": (C.c_int, [f32p]),
+    "sphb_knn_rows_noalloc_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                            C.c_void_p]),
     "sphb_knn_last_overflow_rows": (C.c_int, [C.c_int, i64p, C.c_int64, i64p]),
     "sphb_knn_graph_prow": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int64, i64p, f32p, u32p, f32p]),
     "sphb_prow_gaussian_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, C.c_float, u32p, f32p, f64p]),
@@ -598,3 +600,9 @@ def level_prob_dist_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, v
     _check(load().sphb_level_prob_dist_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, int(pair_sims), perplexity,
                                            scheme, int(symmetrize), out_rowptr_ptr, out_col_ptr, out_val_ptr, cap, _p(nnz, i64p), stream))
     return int(nnz[0])
+
+
+def knn_rows_noalloc_dev(x_ptr: int, n: int, d: int, k: int, metric: int, l2_squared: bool, rows_ptr: int, nrows: int, ids_ptr: int, dist_ptr: int,
+                         stream: int):
+    """Exact kNN of a list of <= 256 query rows (k <= 128) with the library's fixed scratch: no device allocation."""
+    _check(load().sphb_knn_rows_noalloc_dev(x_ptr, n, d, k, metric, int(l2_squared), rows_ptr, nrows, ids_ptr, dist_ptr, stream))

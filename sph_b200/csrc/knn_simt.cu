@@ -3,6 +3,7 @@
 // Used where the tensor-core sweep does not pay: tiny n, very small d (the
 // 3-channel RGB configuration is FP64/ALU bound) — and as the
 // on-device cross-check of the tcgen05 path in the GPU tests.
+#include "../../include/sphb.h"
 #include "knn_common.cuh"
 
 namespace sphb {
@@ -182,4 +183,115 @@ int knn_simt_launch(const float* d_x, int64_t n, int d, int k, int metric, int l
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// No-allocation variant of the segmented exact search (sphb_knn_rows_noalloc_dev, include/sphb.h).
+// No counterpart in the reference; added for callers that cannot
+// allocate device memory (CUDA graph capture, tight serving loops).  The scratch of knn_simt_seg_kernel —
+// the per-(row, segment) sorted lists — lives in a file-scope device array of fixed size instead of a
+// stream-ordered allocation.  Every GPU that loads the library holds the array until exit; all calls share
+// it (calls that overlap on the GPU race), and it keeps the last call's contents (every slot a call reads is
+// written by the same call first; the row count slot is set per call).
+// ---------------------------------------------------------------------------------------------
+constexpr int NOALLOC_MAX_ROWS = 256;   // query rows per call
+constexpr int NOALLOC_MAX_K = 128;      // neighbours per row
+constexpr int NOALLOC_SEGMENTS = 32;    // database segments per row
+constexpr size_t NOALLOC_LIST_WORDS = static_cast<size_t>(NOALLOC_MAX_ROWS) * NOALLOC_SEGMENTS * NOALLOC_MAX_K;  // 1 Mi u64 = 8 MiB
+// [0, 32): header (word 0 holds the row count as an int), then the segment lists
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[32 + NOALLOC_LIST_WORDS];
+
+__global__ void knn_noalloc_set_count(int* count, int v) { *count = v; }
+
+// merge of the segment lists; output row = position in the row list (the existing merge kernel writes to row id - q0)
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) knn_simt_merge_list_kernel(const uint64_t* __restrict__ tmp, int S, int k, int cap, int metric,
+                                                                         int l2_squared, const int64_t* __restrict__ rowlist,
+                                                                         const int* __restrict__ rowcount, int64_t* __restrict__ ids,
+                                                                         float* __restrict__ dist) {
+    extern __shared__ uint64_t smem_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
+    const int64_t nq = *rowcount;
+    for (int64_t rr = static_cast<int64_t>(blockIdx.x) * WARPS + warp; rr < nq; rr += static_cast<int64_t>(gridDim.x) * WARPS) {
+        const int64_t i = rowlist[rr];
+        const uint64_t* src = tmp + rr * S * k;
+        const int total = S * k;
+        int cnt = 0;
+        uint64_t kth = ~0ull;
+        for (int base = 0; base < total; base += 32) {
+            const int t = base + lane;
+            const uint64_t key = t < total ? src[t] : ~0ull;
+            const bool pass = key != ~0ull && key <= kth;
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (m) {
+                if (pass) sm[cnt + __popc(m & ((1u << lane) - 1u))] = key;
+                cnt += __popc(m);
+                if (cnt + 32 > cap) {
+                    for (int u = cnt + lane; u < cap; u += 32) sm[u] = ~0ull;
+                    __syncwarp();
+                    warp_bitonic_sort(sm, cap, lane);
+                    cnt = min(cnt, k);
+                    kth = (cnt == k) ? sm[k - 1] : ~0ull;
+                }
+            }
+        }
+        for (int t = cnt + lane; t < cap; t += 32) sm[t] = ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        cnt = min(cnt, k);
+        write_row(sm, cnt, k, i, metric, l2_squared, ids + rr * k, dist + rr * k, lane);
+        __syncwarp();
+    }
+}
+
+namespace {
+// device address of the scratch array per device ordinal (the array's name is a host-side stand-in in host code)
+constexpr int NOALLOC_MAX_DEVICES = 64;
+unsigned long long* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+int noalloc_scratch_ptr(unsigned long long** out) {
+    int dev = -1;
+    SPHB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(SPHB_ERR_UNSUPPORTED, "knn_rows_noalloc: device ordinal out of range");
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        SPHB_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));  // once per device, with that device current
+        g_noalloc_ptr[dev] = static_cast<unsigned long long*>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+}  // namespace
+
 }  // namespace sphb
+
+using namespace sphb;
+
+extern "C" SPHB_API int sphb_knn_rows_noalloc_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, const int64_t* d_rows,
+                                                  int64_t nrows, int64_t* d_ids, float* d_dist, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (!d_x || !d_rows || !d_ids || !d_dist || n <= 0 || d <= 0 || k <= 0 || nrows < 0) return fail(SPHB_ERR_INVALID, "knn_rows_noalloc: bad arguments");
+    if (metric != SPHB_METRIC_L2 && metric != SPHB_METRIC_INNER_PRODUCT) return fail(SPHB_ERR_INVALID, "knn_rows_noalloc: unknown metric");
+    if (nrows > NOALLOC_MAX_ROWS) return fail(SPHB_ERR_CAPACITY, "knn_rows_noalloc: more than 256 query rows per call (fixed scratch); split the call");
+    if (k > NOALLOC_MAX_K) return fail(SPHB_ERR_CAPACITY, "knn_rows_noalloc: k > 128 exceeds the fixed scratch; use sphb_knn_exact_dev");
+    if (n >= (1ll << 32) - 1) return fail(SPHB_ERR_UNSUPPORTED, "knn_rows_noalloc: n must fit in uint32");
+    if (nrows == 0) return SPHB_OK;
+    unsigned long long* scratch = nullptr;
+    if (int rc = noalloc_scratch_ptr(&scratch)) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    constexpr int WARPS = 4;
+    int cap = 1;
+    while (cap < k + 64) cap <<= 1;  // <= 256: 8 KB of dynamic shared memory, below the 48 KB default limit
+    const size_t smem = static_cast<size_t>(WARPS) * cap * sizeof(uint64_t);
+    int S = static_cast<int>(std::min<int64_t>(NOALLOC_SEGMENTS, std::max<int64_t>(1, n / 1024)));
+    const int64_t seglen = ((n + S - 1) / S + 31) / 32 * 32;
+    int* d_count = reinterpret_cast<int*>(scratch);
+    uint64_t* lists = reinterpret_cast<uint64_t*>(scratch + 32);
+    knn_noalloc_set_count<<<1, 1, 0, s>>>(d_count, static_cast<int>(nrows));
+    const int64_t b1 = std::min<int64_t>((nrows * S + WARPS - 1) / WARPS, static_cast<int64_t>(ctx().num_sms) * 16);
+    knn_simt_seg_kernel<WARPS><<<static_cast<unsigned>(b1), WARPS * 32, smem, s>>>(d_x, n, d, k, cap, metric, d_rows, d_count, S, seglen, lists);
+    const int64_t b2 = (nrows + WARPS - 1) / WARPS;
+    knn_simt_merge_list_kernel<WARPS><<<static_cast<unsigned>(b2), WARPS * 32, smem, s>>>(lists, S, k, cap, metric, l2_squared, d_rows, d_count, d_ids, d_dist);
+    count_launch(3);
+    SPHB_CUDA(cudaGetLastError());
+    return SPHB_OK;
+}
