@@ -260,7 +260,9 @@ ORC_API int orc_knn_blas_l2(const float* x, int64_t n, int d, int k, int64_t q0,
         for (int c = 0; c < d; ++c) s += x[i * d + c] * x[i * d + c];
         norms[i] = s;
     }
-    const int64_t bs_x = 4096, bs_y = 1024, strip = 128;
+    const int64_t bs_x = 4096, bs_y = 1024;
+    // strip of queries per single-threaded sgemm: every thread of the team gets one (32..128 rows)
+    const int64_t strip = std::max<int64_t>(32, std::min<int64_t>(128, ((std::min(nq, bs_x) + omp_get_max_threads() - 1) / omp_get_max_threads() + 15) / 16 * 16));
     std::vector<float> hv(static_cast<size_t>(nq) * k, FLT_MAX);
     std::vector<int64_t> hi(static_cast<size_t>(nq) * k, -1);
     const int prev_threads = g_get_threads ? g_get_threads() : 0;

@@ -94,9 +94,10 @@ SparseMat sqrt_rows(const SparseMat& in, float pruneVal, bool eigen_prune, const
 }
 }  // namespace
 
-// D1.  variant: 0 = auto (n > 5000 -> HDI else Eigen), 1 = force HDI, 2 = force Eigen.
+// D1, first restatement (explicit merge dot per candidate pair; kept as the cross-check of the row-wise form below).
+// variant: 0 = auto (n > 5000 -> HDI else Eigen), 1 = force HDI, 2 = force Eigen.
 // Output: fixed stride k per row (cols padded 0xFFFFFFFF), row_nnz[n].
-ORC_API void orc_create_similarities(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+ORC_API void orc_create_similarities_mergedot(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
                                      int64_t k, float pruneVal, int variant, const int64_t* comp_sizes,
                                      uint32_t* out_cols, float* out_vals, int32_t* row_nnz) {
     const SparseMat in = from_csr(n, rowptr, col, val);
@@ -147,6 +148,76 @@ ORC_API void orc_create_similarities(int64_t n, const int64_t* rowptr, const uin
             out_vals[i * k + t] = t < static_cast<int64_t>(sel.size()) ? sel[t].second : 0.f;
         }
     }
+}
+
+// D1, row-wise (Gustavson) form for the rows [row0, row1): C[i][j] accumulated over the columns c of row i in ascending
+// order through the transposed matrix — the products and their fp32 addition order are exactly those of the merge dot
+// above (ascending shared column), so both forms are bit-identical; this one costs one multiply-add per expanded product,
+// as the reference's blocked Eigen SpGEMM does (sph/utils/SparseMatrixAlgorithms.cpp:1214-1282), which makes it the fair
+// CPU baseline of bench.py.  out_*: (row1 - row0) rows of stride k.
+ORC_API void orc_create_similarities_rows(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                                          int64_t k, float pruneVal, int variant, const int64_t* comp_sizes, int64_t row0, int64_t row1,
+                                          uint32_t* out_cols, float* out_vals, int32_t* row_nnz) {
+    const SparseMat in = from_csr(n, rowptr, col, val);
+    const SparseMat s = sqrt_rows(in, pruneVal, true, comp_sizes);
+    const bool hdi = variant == 1 || (variant == 0 && n > 5000);
+    std::vector<std::vector<std::pair<uint32_t, float>>> st(static_cast<size_t>(n));  // S transposed: column -> (row, value), rows ascending
+    for (int64_t i = 0; i < n; ++i)
+        for (auto& p : s[i]) st[p.first].emplace_back(static_cast<uint32_t>(i), p.second);
+#pragma omp parallel
+    {
+        std::vector<float> acc(static_cast<size_t>(n), 0.f);
+        std::vector<uint8_t> seen(static_cast<size_t>(n), 0);
+        std::vector<uint32_t> touched;
+#pragma omp for schedule(dynamic, 16)
+        for (int64_t i = row0; i < row1; ++i) {
+            touched.clear();
+            for (auto& p : s[i]) {
+                const float sic = p.second;
+                for (auto& q : st[p.first]) {
+                    if (!seen[q.first]) { seen[q.first] = 1; touched.push_back(q.first); }
+                    acc[q.first] += sic * q.second;
+                }
+            }
+            std::sort(touched.begin(), touched.end());
+            SparseRow drow;  // ascending column
+            for (uint32_t j : touched) {
+                const float c = acc[j];
+                acc[j] = 0.f;
+                seen[j] = 0;
+                if (!eigen_pruned_keep(c, pruneVal)) continue;
+                if (hdi) {
+                    if (static_cast<int64_t>(j) == i) continue;              // :1250-1252
+                    drow.emplace_back(j, c == 1.f ? c : -1.f * std::log(c));  // :1290-1292
+                } else {
+                    drow.emplace_back(j, static_cast<int64_t>(j) == i ? c : -1.f * std::log(c));  // :1143-1153
+                }
+            }
+            if (!hdi && drow.size() > 1) {  // removeDiagonalElements(keepSingleEntry=true) (:704-718)
+                for (auto& p : drow) if (static_cast<int64_t>(p.first) == i) p.second = 0.f;
+                drow.erase(std::remove_if(drow.begin(), drow.end(), [](auto& p) { return p.second == 0.f; }), drow.end());
+            }
+            SparseRow sel = select_k<MinDeque>(drow, static_cast<size_t>(k));
+            double sum = 0;
+            for (auto& e : sel) sum += e.second;
+            if (hdi || sum > 0)
+                for (auto& e : sel) e.second /= static_cast<float>(sum);
+            const int64_t o = i - row0;
+            row_nnz[o] = static_cast<int32_t>(sel.size());
+            for (int64_t t = 0; t < k; ++t) {
+                out_cols[o * k + t] = t < static_cast<int64_t>(sel.size()) ? sel[t].first : 0xFFFFFFFFu;
+                out_vals[o * k + t] = t < static_cast<int64_t>(sel.size()) ? sel[t].second : 0.f;
+            }
+        }
+    }
+}
+
+// D1.  variant: 0 = auto (n > 5000 -> HDI else Eigen), 1 = force HDI, 2 = force Eigen.
+// Output: fixed stride k per row (cols padded 0xFFFFFFFF), row_nnz[n].
+ORC_API void orc_create_similarities(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
+                                     int64_t k, float pruneVal, int variant, const int64_t* comp_sizes,
+                                     uint32_t* out_cols, float* out_vals, int32_t* row_nnz) {
+    orc_create_similarities_rows(n, rowptr, col, val, k, pruneVal, variant, comp_sizes, 0, n, out_cols, out_vals, row_nnz);
 }
 
 // D2: createSimilaritiesSPH — full (unpruned-to-k) symmetric -log(sqrt(a_i)·sqrt(a_j)) matrix, CSR out.

@@ -1,0 +1,88 @@
+"""One process per GPU: Stage A + level-0 P rows with the query rows sharded over the ranks.
+
+The database is replicated through NCCL, not through PCIe: every rank uploads only ITS N/G rows of the image stack from
+(pinned) host memory and one all-gather over NVLink assembles the full stack on every GPU ("each rank H2D-copies its own
+1/G and ncclAllGather"), so the host-to-device traffic of a call is N*d*4 bytes in total, independent
+of the number of GPUs.  Each rank then searches its slab of query rows against the full database
+(sphb_knn_exact_dev), builds its P rows (sphb_prow_gaussian_graph_dev) and copies its four result slabs into its
+range of the caller's host buffers — no collective on the result side.
+
+torch is used for device buffers, streams and torch.distributed (NCCL) only; the kernels are the C-ABI library's.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import capi
+
+
+def slab_bounds(n: int, rank: int, world: int) -> tuple[int, int, int]:
+    """(q0, q1, chunk): rank r owns rows [r*chunk, min(n, (r+1)*chunk)), chunk = ceil(n / world)."""
+    chunk = (n + world - 1) // world
+    q0 = min(n, rank * chunk)
+    return q0, min(n, q0 + chunk), chunk
+
+
+class ShardedKnnProw:
+    """Reusable buffers for repeated calls on stacks of one shape (n, d, k)."""
+
+    def __init__(self, n: int, d: int, k: int, rank: int, world: int, group=None):
+        import torch
+
+        self.n, self.d, self.k, self.rank, self.world, self.group = n, d, k, rank, world, group
+        self.q0, self.q1, self.chunk = slab_bounds(n, rank, world)
+        nq = self.q1 - self.q0
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.x_all = torch.empty((world * self.chunk, d), dtype=torch.float32, device=dev)  # the replicated database (rows >= n: padding)
+        self.x_mine = self.x_all[rank * self.chunk:(rank + 1) * self.chunk]
+        self.ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
+        self.dist = torch.empty((nq, k), dtype=torch.float32, device=dev)
+        self.cols = torch.empty((nq, k - 1), dtype=torch.int32, device=dev)
+        self.vals = torch.empty((nq, k - 1), dtype=torch.float32, device=dev)
+
+    def replicate(self, x_host) -> None:
+        """x_host: torch CPU tensor [n, d] (pinned for full PCIe rate).  Uploads this rank's rows, all-gathers the rest."""
+        import torch
+        import torch.distributed as dist
+
+        nq = self.q1 - self.q0
+        if nq > 0:
+            self.x_mine[:nq].copy_(x_host[self.q0:self.q1], non_blocking=True)
+        if nq < self.chunk:
+            self.x_mine[nq:].zero_()
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.x_all, self.x_mine.clone(), group=self.group)  # clone: input must not alias the output
+        _ = torch
+
+    def compute(self, perplexity: float = 0.0, metric: int = capi.METRIC_L2, l2_squared: bool = False) -> None:
+        import torch
+
+        s = torch.cuda.current_stream().cuda_stream
+        nq = self.q1 - self.q0
+        if nq == 0:
+            return
+        capi.knn_exact_dev(self.x_all.data_ptr(), self.n, self.d, self.k, metric, l2_squared, self.q0, self.q1, self.ids.data_ptr(),
+                           self.dist.data_ptr(), s)
+        capi.prow_gaussian_graph_dev(self.ids.data_ptr(), self.dist.data_ptr(), nq, self.k, perplexity, self.cols.data_ptr(), self.vals.data_ptr(), s)
+
+    def download(self, out) -> None:
+        """out = (ids, dist, cols, vals): torch CPU tensors for THIS rank's slab (pinned for full rate), e.g. views of shared buffers."""
+        for dst, src in zip(out, (self.ids, self.dist, self.cols, self.vals)):
+            dst.copy_(src, non_blocking=True)
+
+    def __call__(self, x_host, out, perplexity: float = 0.0) -> None:
+        self.replicate(x_host)
+        self.compute(perplexity)
+        self.download(out)
+
+
+def knn_graph_prow_sharded(x: np.ndarray, k: int, rank: int, world: int, perplexity: float = 0.0, group=None):
+    """Convenience form: numpy in, this rank's (ids, dist, cols, vals) slabs out."""
+    import torch
+
+    n, d = x.shape
+    job = ShardedKnnProw(n, d, k, rank, world, group)
+    job.replicate(torch.from_numpy(x))
+    job.compute(perplexity)
+    torch.cuda.synchronize()
+    return job.ids.cpu().numpy(), job.dist.cpu().numpy(), job.cols.cpu().numpy().view(np.uint32), job.vals.cpu().numpy()

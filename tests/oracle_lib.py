@@ -66,6 +66,8 @@ class Oracle:
         L.orc_rw_merge.argtypes = [C.c_int64, i64p, u32p, f32p, u64p, C.c_int64, C.c_int, C.c_int, i64p, u32p, f32p, C.c_int64]
         L.orc_rw_merge.restype = C.c_int64
         L.orc_create_similarities.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, u32p, f32p, i32p]
+        L.orc_create_similarities_mergedot.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, u32p, f32p, i32p]
+        L.orc_create_similarities_rows.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, C.c_int64, C.c_int64, u32p, f32p, i32p]
         L.orc_create_similarities_sph.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_float, i64p, u32p, f32p, C.c_int64]
         L.orc_create_similarities_sph.restype = C.c_int64
         L.orc_find_k.argtypes = [u32p, f32p, C.c_int, C.c_int, C.c_int, u32p, f32p]
@@ -246,6 +248,28 @@ class Oracle:
         cs = None if comp_sizes is None else np.ascontiguousarray(comp_sizes, np.int64)
         self.lib.orc_create_similarities(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), k, prune_val, variant, _p(cs, i64p), _p(oc, u32p),
                                          _p(ov, f32p), _p(nnz, i32p))
+        return oc, ov, nnz
+
+    def create_similarities_rows(self, rowptr, col, val, k, row0, row1, prune_val=1e-4, variant=0, comp_sizes=None, mergedot=False):
+        """rows [row0, row1) only (the bounded CPU-baseline sample); mergedot=True: the first restatement, all rows."""
+        rowptr = np.ascontiguousarray(rowptr, np.int64)
+        col = np.ascontiguousarray(col, np.uint32)
+        val = np.ascontiguousarray(val, np.float32)
+        n = len(rowptr) - 1
+        if mergedot:
+            row0, row1 = 0, n
+        m = row1 - row0
+        oc = np.zeros((m, k), np.uint32)
+        ov = np.zeros((m, k), np.float32)
+        nnz = np.zeros(m, np.int32)
+        cs = None if comp_sizes is None else np.ascontiguousarray(comp_sizes, np.int64)
+        csp = _p(cs, i64p) if cs is not None else None
+        if mergedot:
+            self.lib.orc_create_similarities_mergedot(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), k, prune_val, variant, csp, _p(oc, u32p),
+                                                      _p(ov, f32p), _p(nnz, i32p))
+        else:
+            self.lib.orc_create_similarities_rows(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), k, prune_val, variant, csp, row0, row1,
+                                                  _p(oc, u32p), _p(ov, f32p), _p(nnz, i32p))
         return oc, ov, nnz
 
     def create_similarities_sph(self, rowptr, col, val, prune_val=1e-4):
