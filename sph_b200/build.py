@@ -45,7 +45,7 @@ def build(force: bool = False, verbose: bool = False, profile: bool = False, tag
     (-DSPHB_KNN_PROFILE; select it with SPHB_LIB=<path>, enable with SPHB_KNN_PROF=1)."""
     LIBDIR.mkdir(exist_ok=True)
     tag = tag or ("_prof" if profile else "")
-    defines = list(defines) + (["-DSPHB_KNN_PROFILE"] if profile else [])
+    defines = list(defines) + (["-DSPHB_KNN_PROFILE", "-DSPHB_KNN_TUNING"] if profile else [])
     lib = LIBDIR / f"libsphb200{tag}.so"
     stamp = LIBDIR / f"build{tag}.stamp"
     dig = _digest()

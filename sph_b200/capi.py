@@ -115,6 +115,8 @@ def load():
     # testing hook, not part of the public header
     lib.sphb_debug_force_knn_path.restype = None
     lib.sphb_debug_force_knn_path.argtypes = [C.c_int]
+    lib.sphb_debug_force_sims_slab.restype = None
+    lib.sphb_debug_force_sims_slab.argtypes = [C.c_int]
     _lib = lib
     return lib
 
@@ -147,6 +149,11 @@ def stream_ptr() -> int:
 def force_knn_path(path: int):
     """0 auto, 1 SIMT exact kernel, 2 tcgen05 (auto), 3 streaming 3-pass, 4 resident MH=1 3-pass, 5 3-pass (auto flavour), 6 1-pass, 7 1-pass streaming (tests only)."""
     load().sphb_debug_force_knn_path(path)
+
+
+def force_sims_slab(on: bool):
+    """createSimilarities: run the L2-slab accumulator kernel even where the shared-memory row fits (tests only)."""
+    load().sphb_debug_force_sims_slab(int(on))
 
 
 def knn_last_stats() -> dict:

@@ -457,10 +457,12 @@ __device__ __forceinline__ void compact_full_rows(RowList& me, uint64_t* __restr
 }
 
 // End of sweep: final compaction of the warp's 32 rows and export of the candidate ids.
-//   r0: slab-row of lane 0; cand_out [nq, keep_max] uint32, cnt_out [nq] (bit 30 = overflow).
+//   r0: slab-row of lane 0; list of row r goes to slot r * out_mul + out_add of cand_out [slots, keep_max] uint32 and
+//   cnt_out [slots] (bit 30 = overflow) — out_mul = database segments per row, out_add = this item's segment.
 template <int R>
 __device__ __forceinline__ void export_rows(RowList& me, int64_t r0, int64_t nq, uint64_t* __restrict__ warp_buf, int k, int keep_max,
-                                            uint32_t* __restrict__ cand_out, int* __restrict__ cnt_out, int lane, const BandConsts& bc) {
+                                            uint32_t* __restrict__ cand_out, int* __restrict__ cnt_out, int lane, const BandConsts& bc,
+                                            int out_mul = 1, int out_add = 0) {
     constexpr int cap = 32 * R;
     __syncwarp();
     for (int L = 0; L < 32; ++L) {
@@ -473,174 +475,9 @@ __device__ __forceinline__ void export_rows(RowList& me, int64_t r0, int64_t nq,
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int e = lane * R + r;
-            if (e < m) cand_out[rL * keep_max + e] = key_idx(x[r]);
+            if (e < m) cand_out[(rL * out_mul + out_add) * keep_max + e] = key_idx(x[r]);
         }
-        if (lane == 0) cnt_out[rL] = m | (ovf ? OVERFLOW_FLAG : 0);
-        __syncwarp();
-    }
-}
-
-// Export for the two-group epilogue: lane L's row has mA = me.cnt survivors in bufA_L and mB (other & ~flag)
-// survivors in bufB_L (both unsorted, each pruned against its own list's k-th value + band, mA, mB <= cap/2).  A true
-// neighbour is among the k smallest of the half of the database its list saw, so it survived there; the union is
-// sorted, pruned against the k-th value of the union + band, and exported like export_rows does.
-template <int R>
-__device__ __forceinline__ void export_rows_merged(RowList& me, int other, int64_t r0, int64_t nq, uint64_t* __restrict__ warp_bufA,
-                                                   uint64_t* __restrict__ warp_bufB, int k, int keep_max, uint32_t* __restrict__ cand_out,
-                                                   int* __restrict__ cnt_out, int lane, const BandConsts& bc) {
-    constexpr int cap = 32 * R;
-    __syncwarp();
-    for (int L = 0; L < 32; ++L) {
-        const int64_t rL = r0 + L;
-        if (rL >= nq) break;
-        const int mA = __shfl_sync(0xffffffffu, me.cnt, L);
-        const int oB = __shfl_sync(0xffffffffu, other, L);
-        const int mB = oB & ~OVERFLOW_FLAG;
-        int ovf = __shfl_sync(0xffffffffu, me.ovf, L) | ((oB & OVERFLOW_FLAG) ? 1 : 0);
-        const uint64_t* bufA = warp_bufA + static_cast<size_t>(L) * cap;
-        const uint64_t* bufB = warp_bufB + static_cast<size_t>(L) * cap;
-        uint64_t x[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int e = lane * R + r;
-            x[r] = e < mA ? bufA[e] : (e < mA + mB ? bufB[e - mA] : ~0ull);
-        }
-        warp_bitonic_sort_regs<R>(x, lane);
-        int m = mA + mB;
-        if (m >= k) {
-            uint64_t kth = 0;
-            const int kr = (k - 1) % R;
-#pragma unroll
-            for (int r = 0; r < R; ++r) kth = (r == kr) ? x[r] : kth;
-            kth = __shfl_sync(0xffffffffu, kth, (k - 1) / R);
-            const float band = bc.passes == 3 ? me.eps2 : band_1pass(key_val(kth), me.un, me.dun, bc);
-            const float limit = __fadd_ru(key_val(kth), __shfl_sync(0xffffffffu, band, L));
-            int c = 0;
-#pragma unroll
-            for (int r = 0; r < R; ++r) c += (lane * R + r < m && key_val(x[r]) <= limit) ? 1 : 0;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-            m = c;
-            if (m > keep_max) {
-                m = keep_max;
-                ovf = 1;
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int e = lane * R + r;
-            if (e < m) cand_out[rL * keep_max + e] = key_idx(x[r]);
-        }
-        if (lane == 0) cnt_out[rL] = m | (ovf ? OVERFLOW_FLAG : 0);
-        __syncwarp();
-    }
-}
-
-// ---- asynchronous compaction (helper warps) -------------------------------------------------------------
-// Row scratch layout: [S: ASYNC_SC survivors | A0: ASYNC_AC appends | A1: ASYNC_AC appends] u64 keys.  The filter lane
-// appends to A[cur]; when that buffer is nearly full it posts (row, cur, count) to the helper warp of its M half and
-// carries on in the other buffer with its old threshold.  The helper merges S and the posted buffer, selects the k-th
-// value, prunes into S and publishes the new threshold; the lane picks it up at the next tile.  The accumulator
-// pipeline never waits for a compaction unless a row's previous request is still in flight when its next buffer fills.
-constexpr int ASYNC_SC = 256, ASYNC_AC = 256, ASYNC_STRIDE = ASYNC_SC + 2 * ASYNC_AC;
-constexpr uint32_t ASYNC_VALID = 0x80000000u;
-
-// Helper side: merge S[0, sc) and buf[0, count) of one row.  RR*32 >= sc + count.  Returns the new survivor count
-// (| OVERFLOW_FLAG) and the new threshold (INFINITY while fewer than k values are known).
-template <int RR>
-__device__ __forceinline__ int async_compact(uint64_t* __restrict__ S, int sc, const uint64_t* __restrict__ buf, int count, int k, float un,
-                                             float dun, const BandConsts& bc, int lane, float& thr_out) {
-    const int total = sc + count;
-    uint64_t x[RR];
-    uint32_t v[RR];
-#pragma unroll
-    for (int r = 0; r < RR; ++r) {
-        const int e = r * 32 + lane;
-        x[r] = e < sc ? __ldcg(S + e) : (e < total ? __ldcg(buf + (e - sc)) : ~0ull);
-        v[r] = static_cast<uint32_t>(x[r] >> 32);
-    }
-    thr_out = INFINITY;
-    if (total < k) {  // nothing to prune yet: move the appends behind the survivors (total < k <= ASYNC_SC)
-#pragma unroll
-        for (int r = 0; r < RR; ++r) {
-            const int e = r * 32 + lane;
-            if (e >= sc && e < total) __stcg(S + e, x[r]);
-        }
-        return total;
-    }
-    warp_bitonic_sort_regs32<RR>(v, lane);
-    uint32_t kth = 0;
-    const int kr = (k - 1) % RR;
-#pragma unroll
-    for (int r = 0; r < RR; ++r) kth = (r == kr) ? v[r] : kth;
-    kth = __shfl_sync(0xffffffffu, kth, (k - 1) / RR);
-    const float gk = ord2f(kth);
-    const float limit = __fadd_ru(gk, band_1pass(gk, un, dun, bc));
-    thr_out = limit;
-    const uint32_t lim = f2ord(limit);
-    const unsigned lt = (1u << lane) - 1u;
-    int base = 0;
-#pragma unroll
-    for (int r = 0; r < RR; ++r) {
-        const bool keep = (r * 32 + lane < total) && static_cast<uint32_t>(x[r] >> 32) <= lim;
-        const unsigned mk = __ballot_sync(0xffffffffu, keep);
-        const int pos = base + __popc(mk & lt);
-        if (keep && pos < ASYNC_SC) __stcg(S + pos, x[r]);
-        base += __popc(mk);
-    }
-    return base > ASYNC_SC ? (ASYNC_SC | OVERFLOW_FLAG) : base;
-}
-
-// Export of one warp's 32 rows at the end of a query tile: union of S (sA entries, from the helper's table) and the
-// current append buffer, sorted, pruned against the k-th value of the union + band, written like export_rows does.
-template <int R>
-__device__ __forceinline__ void export_rows_async(const RowList& me, int cur, const volatile int* s_cnt_warp, int64_t r0, int64_t nq,
-                                                  uint64_t* __restrict__ warp_base, int k, int keep_max, uint32_t* __restrict__ cand_out,
-                                                  int* __restrict__ cnt_out, int lane, const BandConsts& bc) {
-    __syncwarp();
-    for (int L = 0; L < 32; ++L) {
-        const int64_t rL = r0 + L;
-        if (rL >= nq) break;
-        const int sA = s_cnt_warp[L];
-        const int mA = sA & ~OVERFLOW_FLAG;
-        const int mB = __shfl_sync(0xffffffffu, me.cnt, L);
-        const int curL = __shfl_sync(0xffffffffu, cur, L);
-        int ovf = __shfl_sync(0xffffffffu, me.ovf, L) | ((sA & OVERFLOW_FLAG) ? 1 : 0);
-        const uint64_t* bufA = warp_base + static_cast<size_t>(L) * ASYNC_STRIDE;
-        const uint64_t* bufB = bufA + ASYNC_SC + curL * ASYNC_AC;
-        uint64_t x[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int e = lane * R + r;
-            x[r] = e < mA ? __ldcg(bufA + e) : (e < mA + mB ? bufB[e - mA] : ~0ull);
-        }
-        warp_bitonic_sort_regs<R>(x, lane);
-        int m = mA + mB;
-        if (m >= k) {
-            uint64_t kth = 0;
-            const int kr = (k - 1) % R;
-#pragma unroll
-            for (int r = 0; r < R; ++r) kth = (r == kr) ? x[r] : kth;
-            kth = __shfl_sync(0xffffffffu, kth, (k - 1) / R);
-            const float band = band_1pass(key_val(kth), me.un, me.dun, bc);
-            const float limit = __fadd_ru(key_val(kth), __shfl_sync(0xffffffffu, band, L));
-            int c = 0;
-#pragma unroll
-            for (int r = 0; r < R; ++r) c += (lane * R + r < m && key_val(x[r]) <= limit) ? 1 : 0;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-            m = c;
-            if (m > keep_max) {
-                m = keep_max;
-                ovf = 1;
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int e = lane * R + r;
-            if (e < m) cand_out[rL * keep_max + e] = key_idx(x[r]);
-        }
-        if (lane == 0) cnt_out[rL] = m | (ovf ? OVERFLOW_FLAG : 0);
+        if (lane == 0) cnt_out[rL * out_mul + out_add] = m | (ovf ? OVERFLOW_FLAG : 0);
         __syncwarp();
     }
 }

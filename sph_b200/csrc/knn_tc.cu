@@ -51,6 +51,7 @@ struct SweepParams {
     int64_t q0, nq;        // query slab (q0 = first global row when qrows is null)
     int64_t a_row0;        // row of the A operand matrix that holds query 0 of this launch
     int n_qtiles, n_dbtiles;
+    int nseg, seg_tiles;   // resident flavour: database segments per query tile (0 / 1: none) and tiles per segment, see sweep_item
     int dp64;              // resident flavour: padded d / 64
     int passes;            // 1: single fp16 product, 3: split fp16 (hi·hi + lo·hi + hi·lo)
     int half_major;        // resident lean issue loop: all chunks for M half 0, then for half 1 (needs stages >= 2 chunks-per-tile)
@@ -68,22 +69,10 @@ struct SweepParams {
     int pace_window;            // a CTA may run at most this many tiles ahead of the average (0: pacing off)
     int l2_prefetch;            // producer prefetches the database tile this many steps ahead into L2 (0: off)
     int compact_step;           // BandConsts::step
-    int pair_debug;             // debug knobs of the CTA-pair kernel (SPHB_KNN_PAIR_DEBUG bit mask; timing experiments only)
     int debug_skip_epilogue;    // debug: epilogue releases the accumulator without reading it (pure MMA rate)
-    unsigned long long* trace;  // optional (profile build): CTA 0, first query tile, database tiles [trace_t0, trace_t0+64): 32 clock stamps per tile
-    int trace_t0;
     unsigned long long* prof;   // optional [grid][16] cycle counters (build -DSPHB_KNN_PROFILE, run SPHB_KNN_PROF=1)
 };
 
-#ifdef SPHB_KNN_PROFILE
-#define SPHB_TRACE(P, qt, t, slot)                                                                                   \
-    do {                                                                                                             \
-        if ((P).trace && blockIdx.x == 0 && (qt) == 0 && (t) >= (P).trace_t0 && (t) < (P).trace_t0 + 64 && (threadIdx.x & 31) == 0) \
-            (P).trace[((t) - (P).trace_t0) * 32 + (slot)] = clock64();                                                   \
-    } while (0)
-#else
-#define SPHB_TRACE(P, qt, t, slot) do { } while (0)
-#endif
 
 __device__ __forceinline__ BandConsts make_band_consts(const SweepParams& P) {
     BandConsts bc;
@@ -106,6 +95,7 @@ __device__ __forceinline__ BandConsts make_band_consts(const SweepParams& P) {
 // publishes the progress of a complete run.
 struct SweepPace {
     long long mine = 0, published = 0;
+    bool off = false;  // this CTA gave up waiting (no global progress for ~5 ms: some CTA of the grid is not running)
 };
 __device__ __forceinline__ void sweep_pace(const SweepParams& P, SweepPace& sp, int lane) {
     if (P.pace_window > 0 && lane == 0) {
@@ -114,9 +104,16 @@ __device__ __forceinline__ void sweep_pace(const SweepParams& P, SweepPace& sp, 
             sp.published = sp.mine;
         }
         const long long g = gridDim.x;
-        while (true) {
+        // The wait is bounded: the host only enables pacing when the whole grid fits the device (occupancy query), but a
+        // CTA that is not scheduled all the same (MPS limit, another long kernel on the SMs) must not hang the others —
+        // after ~5 ms without ANY global progress this CTA stops pacing itself for the rest of the launch.
+        unsigned long long last = ~0ull;
+        int idle = 0;
+        while (!sp.off) {
             const unsigned long long tot = *reinterpret_cast<volatile unsigned long long*>(P.progress);
             if (sp.mine * g <= static_cast<long long>(tot) + static_cast<long long>(P.pace_window) * g) break;
+            if (tot != last) { last = tot; idle = 0; }
+            else if (++idle > 20000) sp.off = true;
             __nanosleep(256);
         }
     }
@@ -296,8 +293,40 @@ __global__ void knn_prep_ones(__half* __restrict__ ones) {  // [128, 64]: rows [
 // DP64T > 0: 1-pass specialisation with the chunk count known at compile time (the MMA issue loop is
 // straight-line code with pre-built descriptors; every hi chunk runs all 4 k-steps, the zero padding of
 // the operands makes that exact); DP64T = 0: generic (runtime chunk count, 1 or 3 passes, partial last chunk).
-template <int MH, int R, int DP64T, int G = 1, int H = 0>
-__global__ void __launch_bounds__(64 + 128 * MH * G + 32 * H, 1)
+//
+// Work items.  A launch processes n_qtiles * nseg items; item w = (query tile qt, database segment seg).
+// nseg = 1 (every main sweep): an item is one query tile against the whole database, rotated to start near the
+// tile's own rows.  nseg > 1 (the re-sweep of the few rows whose 1-pass band overflowed): the database is cut into
+// nseg segments of seg_tiles tiles, so that a handful of query tiles still fills all SMs — each (tile, segment)
+// keeps its own candidate lists (every true neighbour is among the k nearest of ITS segment, so the per-segment
+// band argument holds unchanged) and the re-rank merges the nseg lists of a row.  Round 1 ran such a re-sweep as one
+// database pass per query tile: 65 ms for 0.8 % of the rows at C4, however few rows a rank had.
+struct SweepItem {
+    int qt, seg, tile0, ntiles;
+};
+__device__ __forceinline__ SweepItem sweep_item(const SweepParams& P, int w) {
+    SweepItem it;
+    if (P.nseg <= 1) {
+        it.qt = w; it.seg = 0; it.tile0 = 0; it.ntiles = P.n_dbtiles;
+        return it;
+    }
+    it.seg = w / P.n_qtiles;  // segment-major: the CTAs of a wave read the same part of the database
+    it.qt = w - it.seg * P.n_qtiles;
+    it.tile0 = it.seg * P.seg_tiles;
+    it.ntiles = min(P.seg_tiles, P.n_dbtiles - it.tile0);
+    return it;
+}
+__device__ __forceinline__ int sweep_item_start(const SweepParams& P, const SweepItem& it, int rows_per_cta, int bn) {
+    return P.nseg <= 1 ? sweep_start(P, it.qt, rows_per_cta, bn) : 0;
+}
+// database tile of step t of an item (dt0 from sweep_item_start)
+__device__ __forceinline__ int sweep_tile(const SweepParams& P, const SweepItem& it, int dt0, int t) {
+    if (P.nseg > 1) return it.tile0 + t;
+    return dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;
+}
+
+template <int MH, int R, int DP64T>
+__global__ void __launch_bounds__(64 + 128 * MH, 1)
 knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                    const __grid_constant__ CUtensorMap tmapN, const __grid_constant__ CUtensorMap tmapO, const SweepParams P,
                    const int k16_tail) {
@@ -311,6 +340,7 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     const bool three = P.passes == 3;
     const int nA = three ? 2 * dp64 : dp64;  // A chunks per M half
     const int nB = nA + 1;                   // B chunks per database tile (the last one is the norm chunk)
+    const int n_items = P.n_qtiles * (P.nseg > 1 ? P.nseg : 1);
     const uint32_t smem_base = ptx::smem_u32(smem);
     const uint32_t sA = smem_base;                                   // [m][c] -> sA + (m*nA + c)*CHUNK_BYTES
     const uint32_t sO = sA + MH * nA * CHUNK_BYTES;
@@ -324,19 +354,6 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     const uint32_t bar_afull = ptx::smem_u32(bars + 2 * stages + 8);
     const uint32_t bar_aempty = ptx::smem_u32(bars + 2 * stages + 9);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 10);
-    int* xch = reinterpret_cast<int*>(bars + 2 * stages + 11);  // G = 2: [MH * BM] list lengths handed from group 1 to group 0 at export
-    // H > 0 (asynchronous compaction, H = MH helper warps): mailboxes between the filter lanes and the helpers
-    uint32_t* xw = reinterpret_cast<uint32_t*>(bars + 2 * stages + 11);
-    volatile uint32_t* hx_ring = xw;                                             // [MH][128] request ring per M half
-    volatile float* hx_thr = reinterpret_cast<volatile float*>(xw + 256);        // [256] threshold published by the helper
-    volatile uint32_t* hx_done = xw + 512;                                       // [256] requests completed per row
-    volatile int* hx_scnt = reinterpret_cast<volatile int*>(xw + 768);           // [256] survivors in S (| OVERFLOW_FLAG)
-    volatile float* hx_un = reinterpret_cast<volatile float*>(xw + 1024);        // [256] row constants for the band
-    volatile float* hx_dun = reinterpret_cast<volatile float*>(xw + 1280);
-    uint32_t* hx_ctl = xw + 1536;                                                // [0..MH) ring tails, [4] finished epilogue warps
-    if constexpr (H > 0) {
-        for (int i = threadIdx.x; i < 1536 + 8; i += blockDim.x) xw[i] = 0;
-    }
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // warps: 0 TMA producer, 1 MMA issuer, 2.. epilogue.  (A second issuer warp, one per M half, was measured: no gain —
@@ -375,12 +392,13 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         bool first = true;
         long long pw = 0, pt0 = SPHB_CLOCK();
         SweepPace pace;
-        for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+        for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+            const SweepItem it = sweep_item(P, w);
             ptx::mbar_wait(bar_aempty, aphase ^ 1);  // previous query tile fully consumed
             if (ptx::elect_one_sync()) {
                 ptx::mbar_expect_tx(bar_afull, (MH * nA + (first ? 1 : 0)) * CHUNK_BYTES);
                 for (int m = 0; m < MH; ++m) {
-                    const int32_t qrow = static_cast<int32_t>(P.a_row0 + (static_cast<int64_t>(qt) * MH + m) * BM);
+                    const int32_t qrow = static_cast<int32_t>(P.a_row0 + (static_cast<int64_t>(it.qt) * MH + m) * BM);
                     for (int c = 0; c < nA; ++c) ptx::tma_load_2d(sA + (m * nA + c) * CHUNK_BYTES, &tmapA, bar_afull, c * BK, qrow);
                 }
                 if (first) ptx::tma_load_2d(sO, &tmapO, bar_afull, 0, 0);
@@ -388,15 +406,14 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             __syncwarp();
             first = false;
             aphase ^= 1;
-            const int dt0 = sweep_start(P, qt, MH * BM, BN);
-            for (int t = 0; t < P.n_dbtiles; ++t) {
-                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
+            const int dt0 = sweep_item_start(P, it, MH * BM, BN);
+            for (int t = 0; t < it.ntiles; ++t) {
+                const int dt = sweep_tile(P, it, dt0, t);
                 if ((t & 15) == 0) sweep_pace(P, pace, lane);
                 ++pace.mine;
-                if (P.l2_prefetch > 0 && t + P.l2_prefetch < P.n_dbtiles) {
-                    // pull the tile this CTA needs l2_prefetch steps from now into L2: a miss then costs nothing on the
-                    // ring's critical path (the ring holds < 3 tiles, less than a DRAM round trip under load)
-                    const int pd = dt + P.l2_prefetch < P.n_dbtiles ? dt + P.l2_prefetch : dt + P.l2_prefetch - P.n_dbtiles;
+                if (P.l2_prefetch > 0 && t + P.l2_prefetch < it.ntiles) {
+                    // pull the tile this CTA needs l2_prefetch steps from now into L2
+                    const int pd = sweep_tile(P, it, dt0, t + P.l2_prefetch);
                     if (ptx::elect_one_sync()) {
                         for (int c = 0; c < nB - 1; ++c) ptx::tma_prefetch_2d(&tmapB, c * BK, pd * BN);
                         ptx::tma_prefetch_2d(&tmapN, 0, pd * BN);
@@ -442,13 +459,14 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             int stage = 0, as = 0;
             uint32_t phase = 0, aphase = 0, accphase = 0;
             long long mw_te = 0, mw_f = 0, mt0 = SPHB_CLOCK();
-            for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+            for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+                const SweepItem it = sweep_item(P, w);
                 ptx::mbar_wait(bar_afull, aphase);
                 aphase ^= 1;
                 ptx::tc_fence_after();
-                for (int t = 0; t < P.n_dbtiles; ++t) {
+                for (int t = 0; t < it.ntiles; ++t) {
                     const uint32_t tmem_d = tmem_base + as * ACC_COLS;
-                    const bool last_tile = t == P.n_dbtiles - 1;
+                    const bool last_tile = t == it.ntiles - 1;
                     if (P.half_major) {
                         // all chunks for M half 0, then for half 1: the epilogue warps of half 0 start while half 1 is
                         // still being multiplied, and a slow warp of one half only delays that half's next tile
@@ -457,7 +475,6 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
                             long long w0 = SPHB_CLOCK();
                             ptx::mbar_wait(bar_tempty + 8 * (as * MH + m), accphase ^ 1);
                             mw_te += SPHB_CLOCK() - w0;
-                            SPHB_TRACE(P, qt, t, m * 2);
                             ptx::tc_fence_after();
 #pragma unroll
                             for (int c = 0; c <= DP64T; ++c) {
@@ -487,7 +504,6 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
                                 }
                                 __syncwarp();
                             }
-                            SPHB_TRACE(P, qt, t, m * 2 + 1);
                         }
                         stage += DP64T + 1;
                         if (stage >= stages) { stage -= stages; phase ^= 1; }
@@ -542,11 +558,12 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         const uint64_t odesc = ptx::make_smem_desc_sw128(sO);
         const bool narrow = P.norm_bytes != CHUNK_BYTES;
         long long mw_te = 0, mw_f = 0, mt0 = SPHB_CLOCK();
-        for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+        for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+            const SweepItem it = sweep_item(P, w);
             ptx::mbar_wait(bar_afull, aphase);
             aphase ^= 1;
             ptx::tc_fence_after();
-            for (int t = 0; t < P.n_dbtiles; ++t) {
+            for (int t = 0; t < it.ntiles; ++t) {
                 long long w0 = SPHB_CLOCK();
 #pragma unroll
                 for (int m = 0; m < MH; ++m) ptx::mbar_wait(bar_tempty + 8 * (as * MH + m), accphase ^ 1);
@@ -588,7 +605,7 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
 #pragma unroll
                             for (int m = 0; m < MH; ++m) ptx::umma_commit(bar_tfull + 8 * (as * MH + m));
                         }
-                        if (c == nB - 1 && t == P.n_dbtiles - 1) ptx::umma_commit(bar_aempty);  // query tile consumed
+                        if (c == nB - 1 && t == it.ntiles - 1) ptx::umma_commit(bar_aempty);  // query tile consumed
                     }
                     __syncwarp();
                     if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -602,185 +619,35 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
             P.prof[blockIdx.x * 16 + 4] = SPHB_CLOCK() - mt0;
         }
         }
-    } else if (H > 0 && warp >= 2 + 4 * MH * G) {
-        // ===================== compaction helper of M half hw =====================
-        const int hw = warp - (2 + 4 * MH * G);
-        const int k = P.k;
-        const BandConsts bc = make_band_consts(P);
-        uint32_t head = 0;
-        while (true) {
-            uint32_t e = 0;
-            while (true) {
-                e = hx_ring[hw * 128 + (head & 127)];
-                if (e & ASYNC_VALID) break;
-                if (*reinterpret_cast<volatile uint32_t*>(hx_ctl + 4) == 4 * MH * G) {
-                    e = hx_ring[hw * 128 + (head & 127)];  // a request posted before the last warp finished
-                    if (!(e & ASYNC_VALID)) e = 0;
-                    break;
-                }
-                __nanosleep(64);
-            }
-            e = __shfl_sync(0xffffffffu, e, 0);
-            if (e == 0) break;
-            __syncwarp();
-            if (lane == 0) hx_ring[hw * 128 + (head & 127)] = 0;
-            ++head;
-            __threadfence_block();
-            const int row = hw * BM + static_cast<int>((e >> 16) & 127u);
-            const int buf = static_cast<int>((e >> 30) & 1u);
-            const int count = static_cast<int>(e & 0xFFFFu);
-            uint64_t* S = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + row) * ASYNC_STRIDE;
-            const uint64_t* A = S + ASYNC_SC + buf * ASYNC_AC;
-            const int sc = hx_scnt[row] & ~OVERFLOW_FLAG;
-            const int so = hx_scnt[row] & OVERFLOW_FLAG;
-            const float un = hx_un[row], dun = hx_dun[row];
-            float thr_new;
-            int m;
-            if (sc + count <= 256) m = async_compact<8>(S, sc, A, count, k, un, dun, bc, lane, thr_new);
-            else m = async_compact<16>(S, sc, A, count, k, un, dun, bc, lane, thr_new);
-            __threadfence_block();
-            __syncwarp();
-            if (lane == 0) {
-                hx_scnt[row] = m | so;
-                hx_thr[row] = thr_new;
-                __threadfence_block();
-                hx_done[row] = hx_done[row] + 1;
-            }
-            __syncwarp();
-        }
-    } else if (H > 0) {
-        // ===================== epilogue, asynchronous compaction =====================
-        const int ew = warp - 2;
-        const int quarter = warp & 3;
+    } else {
+        // ===================== epilogue: 4 warps per M half, one thread per query row =====================
+        const int ew = warp - 2;       // 0 .. 4*MH-1
+        const int quarter = warp & 3;  // TMEM lane quarter this warp may access
         const int mhalf = ew >> 2;
+        constexpr int cap = 32 * R;
         const int k = P.k, keep_max = P.keep_max;
+        const int out_mul = P.nseg > 1 ? P.nseg : 1;
         const BandConsts bc = make_band_consts(P);
         int as = 0;
         uint32_t accphase = 0;
         unsigned long long n_compact = 0, n_accept = 0;
         const uint32_t n32 = static_cast<uint32_t>(P.n);
-        long long ew_tf = 0, e_ld = 0, e_filt = 0, e_exp = 0, e_stall = 0, et0 = SPHB_CLOCK();
-        const int row_in_tile = mhalf * BM + quarter * 32 + lane;
-        uint64_t* rowbase = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + row_in_tile) * ASYNC_STRIDE;
-        uint32_t posted = 0, seen = 0;  // requests posted by / thresholds absorbed from the helper for this lane's row
-        for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
-            const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
-            const bool valid = r < P.nq;
-            RowList me;
-            init_row(me, P, r, valid);
-            int cur = 0;
-            uint64_t* mybuf = rowbase + ASYNC_SC;
-            hx_scnt[row_in_tile] = 0;  // no request of this row is in flight here
-            hx_un[row_in_tile] = me.un;
-            hx_dun[row_in_tile] = me.dun;
-            const int dt0 = sweep_start(P, qt, MH * BM, BN);
-            for (int t = 0; t < P.n_dbtiles; ++t) {
-                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
-                long long w0 = SPHB_CLOCK();
-                ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
-                ew_tf += SPHB_CLOCK() - w0;
-                ptx::tc_fence_after();
-                if (seen != posted && hx_done[row_in_tile] == posted) {  // the helper has a tighter threshold for this row
-                    me.thr = fminf(me.thr, hx_thr[row_in_tile]);
-                    seen = posted;
-                }
-                const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
-                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
-#pragma unroll 1
-                for (int c = 0; c < (P.debug_skip_epilogue ? 0 : BN / 32); c += 2) {
-                    float v0[32], v1[32];
-                    w0 = SPHB_CLOCK();
-                    ptx::tmem_ld_32x32(taddr + c * 32, v0);
-                    ptx::tmem_ld_32x32(taddr + c * 32 + 32, v1);
-                    ptx::tmem_ld_wait(v0);
-                    ptx::tmem_ld_wait(v1);
-                    const long long w1 = SPHB_CLOCK();
-                    e_ld += w1 - w0;
-                    filter_pair(v0, v1, jbase + c * 32, n32, me, mybuf, n_accept);
-                    if (me.cnt > ASYNC_AC - 64) {  // per lane: hand the buffer to the helper, continue in the other one
-                        const long long s0 = SPHB_CLOCK();
-                        while (hx_done[row_in_tile] != posted) __nanosleep(32);  // previous request of this row still in flight
-                        e_stall += SPHB_CLOCK() - s0;
-                        if (seen != posted) {
-                            me.thr = fminf(me.thr, hx_thr[row_in_tile]);
-                            seen = posted;
-                        }
-                        __threadfence_block();  // the appends are visible to the helper before the request is
-                        const uint32_t slot = atomicAdd(hx_ctl + mhalf, 1u) & 127u;
-                        hx_ring[mhalf * 128 + slot] = ASYNC_VALID | (static_cast<uint32_t>(cur) << 30) |
-                                                      (static_cast<uint32_t>(row_in_tile & 127) << 16) | static_cast<uint32_t>(me.cnt);
-                        ++posted;
-                        cur ^= 1;
-                        me.cnt = 0;
-                        mybuf = rowbase + ASYNC_SC + cur * ASYNC_AC;
-                        ++n_compact;
-                    }
-                    e_filt += SPHB_CLOCK() - w1;
-                }
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * (as * MH + mhalf));
-                if (++as == 2) { as = 0; accphase ^= 1; }
-            }
-            const long long x0 = SPHB_CLOCK();
-            while (hx_done[row_in_tile] != posted) __nanosleep(32);
-            seen = posted;
-            __threadfence_block();
-            export_rows_async<R>(me, cur, hx_scnt + (row_in_tile - lane), r - lane, P.nq, rowbase - static_cast<size_t>(lane) * ASYNC_STRIDE, k, keep_max,
-                                 P.cand_out, P.cnt_out, lane, bc);
-            e_exp += SPHB_CLOCK() - x0;
-        }
-        __syncwarp();
-        if (lane == 0) atomicAdd(hx_ctl + 4, 1u);  // this warp posts no more requests
-        if (P.prof && lane == 0) {
-            atomicAdd(P.prof + blockIdx.x * 16 + 5, static_cast<unsigned long long>(ew_tf));
-            atomicAdd(P.prof + blockIdx.x * 16 + 6, static_cast<unsigned long long>(e_ld));
-            atomicAdd(P.prof + blockIdx.x * 16 + 7, static_cast<unsigned long long>(e_filt));
-            atomicAdd(P.prof + blockIdx.x * 16 + 8, static_cast<unsigned long long>(e_exp));
-            atomicAdd(P.prof + blockIdx.x * 16 + 9, static_cast<unsigned long long>(SPHB_CLOCK() - et0));
-            atomicAdd(P.prof + blockIdx.x * 16 + 10, static_cast<unsigned long long>(e_stall));
-        }
-        if (P.stats) {
-            n_accept = warp_sum(static_cast<double>(n_accept));
-            n_compact = static_cast<unsigned long long>(warp_sum(static_cast<double>(n_compact)));
-            if (lane == 0) {
-                atomicAdd(P.stats + 0, n_compact);
-                atomicAdd(P.stats + 1, static_cast<unsigned long long>(n_accept));
-            }
-        }
-    } else {
-        // ===================== epilogue =====================
-        // G = 2: two groups of 4*MH epilogue warps; group g owns accumulator stage g, i.e. the database tiles t with
-        // t % 2 == g (n_dbtiles is even), and keeps its own candidate list and threshold per row.  A warp alone is
-        // latency bound (dependent min trees, TMEM loads, list appends); twice the warps hide twice the latency, and a
-        // group has two MMA tile times per tile.  The two lists of a row are merged at export.
-        const int grp = (warp - 2) / (4 * MH);
-        const int ew = (warp - 2) % (4 * MH);  // 0 .. 4*MH-1
-        const int quarter = warp & 3;          // TMEM lane quarter this warp may access
-        const int mhalf = ew >> 2;
-        constexpr int cap = 32 * R;
-        const int k = P.k, keep_max = P.keep_max;
-        const BandConsts bc = make_band_consts(P);
-        int as = G == 2 ? grp : 0;
-        uint32_t accphase = 0;
-        unsigned long long n_compact = 0, n_accept = 0;
-        const uint32_t n32 = static_cast<uint32_t>(P.n);
         long long ew_tf = 0, e_ld = 0, e_filt = 0, e_exp = 0, e_cmp = 0, et0 = SPHB_CLOCK();
-        for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
+        for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+            const SweepItem it = sweep_item(P, w);
             const int row_in_tile = mhalf * BM + quarter * 32 + lane;
-            const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
+            const int64_t r = static_cast<int64_t>(it.qt) * (MH * BM) + row_in_tile;
             const bool valid = r < P.nq;
-            uint64_t* warp_buf = P.cand + ((static_cast<size_t>(blockIdx.x) * G + grp) * (MH * BM) + (row_in_tile - lane)) * cap;
+            uint64_t* warp_buf = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + (row_in_tile - lane)) * cap;
             uint64_t* mybuf = warp_buf + static_cast<size_t>(lane) * cap;
             RowList me;
             init_row(me, P, r, valid);
-            const int dt0 = sweep_start(P, qt, MH * BM, BN);
-            for (int t = (G == 2 ? grp : 0); t < P.n_dbtiles; t += G) {
-                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
+            const int dt0 = sweep_item_start(P, it, MH * BM, BN);
+            for (int t = 0; t < it.ntiles; ++t) {
+                const int dt = sweep_tile(P, it, dt0, t);
                 long long w0 = SPHB_CLOCK();
                 ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
                 ew_tf += SPHB_CLOCK() - w0;
-                SPHB_TRACE(P, qt, t, 8 + ew * 2);
                 ptx::tc_fence_after();
                 const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
@@ -794,52 +661,17 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
                     ptx::tmem_ld_wait(v1);
                     const long long w1 = SPHB_CLOCK();
                     e_ld += w1 - w0;
-#ifdef SPHB_FILTER_SINGLE
-                    filter_chunk(v0, jbase + c * 32, n32, me, mybuf, n_accept);
-                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
-                    filter_chunk(v1, jbase + c * 32 + 32, n32, me, mybuf, n_accept);
-                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
-#else
                     filter_pair(v0, v1, jbase + c * 32, n32, me, mybuf, n_accept);
                     compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
-#endif
                     e_filt += SPHB_CLOCK() - w1;
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
-                SPHB_TRACE(P, qt, t, 9 + ew * 2);
                 if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * (as * MH + mhalf));
-                if constexpr (G == 2) {
-                    accphase ^= 1;
-                } else {
-                    if (++as == 2) { as = 0; accphase ^= 1; }
-                }
+                if (++as == 2) { as = 0; accphase ^= 1; }
             }
             const long long x0 = SPHB_CLOCK();
-            if constexpr (G == 2) {
-                // both groups prune their lists to at most cap/2 survivors each; group 1 hands its lengths over, group 0
-                // sorts the union, applies the joint band and exports.  Named barrier 1 + ew pairs the two warps of a row block.
-                constexpr int half_keep = cap / 2;
-                __syncwarp();
-                for (int L = 0; L < 32; ++L) {
-                    if (r - lane + L >= P.nq) break;
-                    compact_row_select<R>(me, L, warp_buf + static_cast<size_t>(L) * cap, k, half_keep, lane, bc);
-                }
-                uint64_t* other_buf = P.cand + ((static_cast<size_t>(blockIdx.x) * G + 1) * (MH * BM) + (row_in_tile - lane)) * cap;
-                if (grp == 1) {
-                    xch[row_in_tile] = me.cnt | (me.ovf ? OVERFLOW_FLAG : 0);
-                    __threadfence_block();
-                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");  // lists + lengths visible to group 0
-                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");  // group 0 has read them
-                } else {
-                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");
-                    const int other = xch[row_in_tile];
-                    export_rows_merged<R>(me, other, r - lane, P.nq, warp_buf, other_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
-                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");
-                }
-            } else {
-                export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
-            }
+            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc, out_mul, it.seg);
             e_exp += SPHB_CLOCK() - x0;
         }
         if (P.prof && lane == 0) {
@@ -862,272 +694,6 @@ knn_sweep_resident(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
-}
-
-// ---------------------------------------------------------------------------
-// sweep, CTA-pair flavour (1 pass, d <= 256): the resident kernel on cta_group::2
-// ---------------------------------------------------------------------------
-// Two CTAs of a cluster (one TPC) share every MMA: M = 256 = 128 query rows from each CTA's resident tile,
-// N = 128 database rows of which each CTA stages 64.  Per SM and k-step the tensor core then reads 4 KB of A
-// and 2 KB of B from shared memory instead of 4 + 4 — the single-CTA kernel is bound by exactly that operand
-// bandwidth — and each database tile crosses L2 -> SM once per 512 query rows instead of 256.
-// Each CTA keeps MH = 2 resident halves (256 query rows) and runs its own epilogue on its own TMEM lanes.
-// smem per CTA: [A: 2 x DP64T chunks of 16 KB | ONES 16 KB | B ring: stages slots of 8 KB | barriers | tmem slot]
-// Barriers: full[s] (leader, 2 arrivals: each CTA's expect_tx), empty[s] / tfull[as][m] / aempty (one per CTA,
-// multicast commit), tempty[as][m] (leader, 8 arrivals: 4 epilogue warps of each CTA), afull (leader, 2 arrivals).
-namespace tcp {
-constexpr int SLOT_BYTES = 64 * 128;       // 64 database rows x 64 fp16
-constexpr int NORM_BYTES = 64 * 32;        // 64 database rows x 16 fp16 (SWIZZLE_32B)
-constexpr int NUM_THREADS = 64 + 256;
-}  // namespace tcp
-
-__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_bar), "r"(bytes) : "memory");
-}
-
-template <int R, int DP64T>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tcp::NUM_THREADS, 1)
-knn_sweep_pair(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, const __grid_constant__ CUtensorMap tmapN,
-               const __grid_constant__ CUtensorMap tmapO, const SweepParams P) {
-    using namespace tc;
-    using namespace tcp;
-    constexpr int MH = 2, BN = 128;
-    constexpr int ACC_COLS = MH * BN;
-    constexpr int TMEM_COLS = 2 * ACC_COLS;
-    constexpr int NB = DP64T + 1;  // ring slots per database tile
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int stages = P.stages;
-    const uint32_t smem_base = ptx::smem_u32(smem);
-    const uint32_t sA = smem_base;
-    const uint32_t sO = sA + MH * DP64T * CHUNK_BYTES;
-    const uint32_t sB = sO + CHUNK_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(MH * DP64T + 1) * CHUNK_BYTES + static_cast<size_t>(stages) * SLOT_BYTES);
-    const uint32_t bar_full = ptx::smem_u32(bars);
-    const uint32_t bar_empty = ptx::smem_u32(bars + stages);
-    const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * stages);
-    const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * stages + 4);
-    const uint32_t bar_afull = ptx::smem_u32(bars + 2 * stages + 8);
-    const uint32_t bar_aempty = ptx::smem_u32(bars + 2 * stages + 9);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 10);
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t rank = ptx::cluster_ctarank();
-    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
-    const int n_ptiles = (P.n_qtiles + 1) >> 1;  // pair tiles of 512 query rows
-
-    if (warp == 0 && lane == 0) {
-        ptx::prefetch_tmap(&tmapA);
-        ptx::prefetch_tmap(&tmapB);
-        ptx::prefetch_tmap(&tmapN);
-        ptx::prefetch_tmap(&tmapO);
-        for (int s = 0; s < stages; ++s) {
-            ptx::mbar_init(bar_full + 8 * s, (P.pair_debug & 2) ? 1 : 2);
-            ptx::mbar_init(bar_empty + 8 * s, 1);
-        }
-        for (int s = 0; s < 2 * MH; ++s) {
-            ptx::mbar_init(bar_tfull + 8 * s, 1);
-            ptx::mbar_init(bar_tempty + 8 * s, (P.pair_debug & 1) ? 4 : 8);
-        }
-        ptx::mbar_init(bar_afull, 2);
-        ptx::mbar_init(bar_aempty, 1);
-        ptx::fence_barrier_init();
-    }
-    if (warp == 1) {
-        ptx::tmem_alloc_pair(ptx::smem_u32(tmem_slot), TMEM_COLS);
-        ptx::tmem_relinquish_pair();
-    }
-    ptx::tc_fence_before();
-    ptx::cluster_sync();  // barrier inits of both CTAs visible before any remote arrive / multicast commit
-    ptx::tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-
-    if (warp == 0) {
-        // ===================== TMA producer (both CTAs; completion counted on the leader's barriers) =====================
-        const uint32_t afull_l = ptx::mapa(bar_afull, 0);
-        const uint32_t full_l = ptx::mapa(bar_full, 0);
-        int stage = 0;
-        uint32_t phase = 0, aphase = 0;
-        bool first = true;
-        long long pw = 0, pt0 = SPHB_CLOCK();
-        const bool solo_tx = (P.pair_debug & 2) != 0;  // debug: only the leader registers the bytes (of both CTAs)
-        const bool no_b = (P.pair_debug & 4) != 0;     // debug: no database loads at all (MMA issue rate on stale smem)
-        for (int pt = pair; pt < n_ptiles; pt += n_pairs) {
-            const int qt = 2 * pt + static_cast<int>(rank);  // this CTA's 256-row query tile (may be past the end: zero rows)
-            ptx::mbar_wait(bar_aempty, aphase ^ 1);
-            if (ptx::elect_one_sync()) {
-                mbar_expect_tx_cluster(afull_l, (MH * DP64T + (first ? 1 : 0)) * CHUNK_BYTES);
-                for (int m = 0; m < MH; ++m) {
-                    const int32_t qrow = static_cast<int32_t>(P.a_row0 + (static_cast<int64_t>(qt) * MH + m) * BM);
-                    for (int c = 0; c < DP64T; ++c) ptx::tma_load_2d_pair(sA + (m * DP64T + c) * CHUNK_BYTES, &tmapA, afull_l, c * BK, qrow);
-                }
-                if (first) ptx::tma_load_2d_pair(sO, &tmapO, afull_l, 0, 0);
-            }
-            __syncwarp();
-            first = false;
-            aphase ^= 1;
-            const int dt0 = sweep_start_at(P, static_cast<int64_t>(pt - pair) * (2 * MH * BM), 2 * pair, BN);
-            for (int t = 0; t < P.n_dbtiles; ++t) {
-                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
-                const int32_t brow = dt * BN + static_cast<int32_t>(rank) * 64;
-#pragma unroll
-                for (int c = 0; c < NB; ++c) {
-                    if (no_b) break;
-                    const long long w0 = SPHB_CLOCK();
-                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                    pw += SPHB_CLOCK() - w0;
-                    if (ptx::elect_one_sync()) {
-                        const uint32_t bytes = c < DP64T ? SLOT_BYTES : NORM_BYTES;
-                        if (!solo_tx) mbar_expect_tx_cluster(full_l + 8 * stage, bytes);
-                        else if (rank == 0) ptx::mbar_expect_tx(bar_full + 8 * stage, 2 * bytes);
-                        if (c < DP64T) ptx::tma_load_2d_pair(sB + stage * SLOT_BYTES, &tmapB, full_l + 8 * stage, c * BK, brow);
-                        else ptx::tma_load_2d_pair(sB + stage * SLOT_BYTES, &tmapN, full_l + 8 * stage, 0, brow);
-                    }
-                    __syncwarp();
-                    if (++stage == stages) { stage = 0; phase ^= 1; }
-                }
-            }
-        }
-        if (P.prof && lane == 0) {
-            P.prof[blockIdx.x * 16 + 0] = pw;
-            P.prof[blockIdx.x * 16 + 1] = SPHB_CLOCK() - pt0;
-        }
-    } else if (warp == 1) {
-        // ===================== MMA issuer (leader CTA only) =====================
-        if (rank == 0) {
-            constexpr uint32_t idesc = ptx::make_idesc_f16(2 * BM, BN);
-            constexpr uint32_t SLOT_DESC = SLOT_BYTES >> 4;
-            uint64_t adesc[MH][DP64T];
-#pragma unroll
-            for (int m = 0; m < MH; ++m)
-#pragma unroll
-                for (int c = 0; c < DP64T; ++c) adesc[m][c] = ptx::make_smem_desc_sw128(sA + (m * DP64T + c) * CHUNK_BYTES);
-            const uint64_t odesc = ptx::make_smem_desc_sw128(sO);
-            const uint64_t bdesc0 = ptx::make_smem_desc_sw128(sB);
-            const uint64_t ndesc0 = ptx::make_smem_desc_sw32(sB);
-            int stage = 0, as = 0;
-            uint32_t phase = 0, aphase = 0, accphase = 0;
-            long long mw_te = 0, mw_f = 0, mt0 = SPHB_CLOCK();
-            const bool no_b = (P.pair_debug & 4) != 0;
-            for (int pt = pair; pt < n_ptiles; pt += n_pairs) {
-                ptx::mbar_wait(bar_afull, aphase);
-                aphase ^= 1;
-                ptx::tc_fence_after();
-                for (int t = 0; t < P.n_dbtiles; ++t) {
-                    const uint32_t tmem_d = tmem_base + as * ACC_COLS;
-                    const bool last_tile = t == P.n_dbtiles - 1;
-#pragma unroll
-                    for (int m = 0; m < MH; ++m) {
-                        long long w0 = SPHB_CLOCK();
-                        ptx::mbar_wait(bar_tempty + 8 * (as * MH + m), accphase ^ 1);
-                        mw_te += SPHB_CLOCK() - w0;
-                        ptx::tc_fence_after();
-#pragma unroll
-                        for (int c = 0; c <= DP64T; ++c) {
-                            int st = stage + c;
-                            uint32_t ph = phase;
-                            if (st >= stages) { st -= stages; ph ^= 1; }
-                            if (m == 0 && !no_b) {
-                                w0 = SPHB_CLOCK();
-                                ptx::mbar_wait(bar_full + 8 * st, ph);
-                                mw_f += SPHB_CLOCK() - w0;
-                                ptx::tc_fence_after();
-                            }
-                            if (ptx::elect_one_sync()) {
-                                if (c < DP64T) {
-                                    const uint64_t bdesc = bdesc0 + static_cast<uint64_t>(st * SLOT_DESC);
-#pragma unroll
-                                    for (int kk = 0; kk < 4; ++kk)
-                                        ptx::umma_f16_pair(tmem_d + m * BN, adesc[m][c < DP64T ? c : 0] + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0 ? 1u : 0u);
-                                } else {
-                                    ptx::umma_f16_pair(tmem_d + m * BN, odesc, ndesc0 + static_cast<uint64_t>(st * SLOT_DESC), idesc, 1u);
-                                }
-                                if (m == MH - 1 && !no_b) ptx::umma_commit_pair(bar_empty + 8 * st, 3);
-                                if (c == DP64T) {
-                                    ptx::umma_commit_pair(bar_tfull + 8 * (as * MH + m), 3);
-                                    if (m == MH - 1 && last_tile) ptx::umma_commit_pair(bar_aempty, 3);
-                                }
-                            }
-                            __syncwarp();
-                        }
-                    }
-                    stage += NB;
-                    if (stage >= stages) { stage -= stages; phase ^= 1; }
-                    if (++as == 2) { as = 0; accphase ^= 1; }
-                }
-            }
-            if (P.prof && lane == 0) {
-                P.prof[blockIdx.x * 16 + 2] = mw_te;
-                P.prof[blockIdx.x * 16 + 3] = mw_f;
-                P.prof[blockIdx.x * 16 + 4] = SPHB_CLOCK() - mt0;
-            }
-        }
-    } else {
-        // ===================== epilogue (each CTA on its own 256 rows / TMEM lanes) =====================
-        const int ew = warp - 2;
-        const int quarter = warp & 3;
-        const int mhalf = ew >> 2;
-        constexpr int cap = 32 * R;
-        const int k = P.k, keep_max = P.keep_max;
-        const BandConsts bc = make_band_consts(P);
-        const uint32_t tempty_l = ptx::mapa(bar_tempty, 0);
-        int as = 0;
-        uint32_t accphase = 0;
-        unsigned long long n_compact = 0, n_accept = 0;
-        const uint32_t n32 = static_cast<uint32_t>(P.n);
-        long long e_cmp = 0, ew_tf = 0, et0 = SPHB_CLOCK();
-        for (int pt = pair; pt < n_ptiles; pt += n_pairs) {
-            const int qt = 2 * pt + static_cast<int>(rank);
-            const int row_in_tile = mhalf * BM + quarter * 32 + lane;
-            const int64_t r = static_cast<int64_t>(qt) * (MH * BM) + row_in_tile;
-            const bool valid = r < P.nq;
-            uint64_t* warp_buf = P.cand + (static_cast<size_t>(blockIdx.x) * (MH * BM) + (row_in_tile - lane)) * cap;
-            uint64_t* mybuf = warp_buf + static_cast<size_t>(lane) * cap;
-            RowList me;
-            init_row(me, P, r, valid);
-            const int dt0 = sweep_start_at(P, static_cast<int64_t>(pt - pair) * (2 * MH * BM), 2 * pair, BN);
-            for (int t = 0; t < P.n_dbtiles; ++t) {
-                const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
-                const long long w0 = SPHB_CLOCK();
-                ptx::mbar_wait(bar_tfull + 8 * (as * MH + mhalf), accphase);
-                ew_tf += SPHB_CLOCK() - w0;
-                ptx::tc_fence_after();
-                const uint32_t jbase = static_cast<uint32_t>(dt) * BN;
-                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * ACC_COLS + mhalf * BN;
-#pragma unroll 1
-                for (int c = 0; c < (P.debug_skip_epilogue ? 0 : BN / 32); c += 2) {
-                    float v0[32], v1[32];
-                    ptx::tmem_ld_32x32(taddr + c * 32, v0);
-                    ptx::tmem_ld_32x32(taddr + c * 32 + 32, v1);
-                    ptx::tmem_ld_wait(v0);
-                    ptx::tmem_ld_wait(v1);
-                    filter_pair(v0, v1, jbase + c * 32, n32, me, mybuf, n_accept);
-                    compact_full_rows<R>(me, warp_buf, k, keep_max, lane, bc, n_compact, e_cmp);
-                }
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0 && (rank == 0 || !(P.pair_debug & 1))) ptx::mbar_arrive_cluster(tempty_l + 8 * (as * MH + mhalf));
-                if (++as == 2) { as = 0; accphase ^= 1; }
-            }
-            export_rows<R>(me, r - lane, P.nq, warp_buf, k, keep_max, P.cand_out, P.cnt_out, lane, bc);
-        }
-        if (P.prof && lane == 0) {
-            atomicAdd(P.prof + blockIdx.x * 16 + 5, static_cast<unsigned long long>(ew_tf));
-            atomicAdd(P.prof + blockIdx.x * 16 + 9, static_cast<unsigned long long>(SPHB_CLOCK() - et0));
-            atomicAdd(P.prof + blockIdx.x * 16 + 10, static_cast<unsigned long long>(e_cmp));
-        }
-        if (P.stats) {
-            n_accept = warp_sum(static_cast<double>(n_accept));
-            if (lane == 0) {
-                atomicAdd(P.stats + 0, n_compact);
-                atomicAdd(P.stats + 1, static_cast<unsigned long long>(n_accept));
-            }
-        }
-    }
-
-    ptx::tc_fence_before();
-    ptx::cluster_sync();  // no CTA leaves (or frees TMEM) while its peer can still signal its barriers
-    if (warp == 1) ptx::tmem_dealloc_pair(tmem_base, TMEM_COLS);
 }
 
 // ---------------------------------------------------------------------------
@@ -1295,7 +861,8 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
 // exact re-rank of the surviving candidates (one warp per query row)
 // ---------------------------------------------------------------------------
 // Row r of this launch is point gi = qrows ? qrows[r] : q0 + r; it is written to output row gi - out_q0.
-__global__ void __launch_bounds__(256) knn_rerank_kernel(const float* __restrict__ X, int d, int k, int cap, int keep_max, int metric,
+// nseg > 1: the row's candidates are the union of its nseg per-segment lists (disjoint database ranges, sweep_item).
+__global__ void __launch_bounds__(256) knn_rerank_kernel(const float* __restrict__ X, int d, int k, int cap, int keep_max, int nseg, int metric,
                                                          int l2_squared, int64_t q0, int64_t nq, const int64_t* __restrict__ qrows,
                                                          int64_t out_q0, const uint32_t* __restrict__ cand, const int* __restrict__ cnt,
                                                          int64_t* __restrict__ ids, float* __restrict__ dist,
@@ -1306,21 +873,24 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(const float* __restrict
     const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
     const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
     for (int64_t r = gw; r < nq; r += nw) {
-        const int c = cnt[r];
         const int64_t gi = qrows ? qrows[r] : q0 + r;
-        if (c & OVERFLOW_FLAG) {
+        bool ovf = false;
+        for (int sg = 0; sg < nseg; ++sg) ovf |= (cnt[r * nseg + sg] & OVERFLOW_FLAG) != 0;
+        if (ovf) {
             if (lane == 0) ovf_rows[atomicAdd(ovf_count, 1)] = gi;
             continue;
         }
-        const int m = c;
-        for (int t = lane; t < cap; t += 32) {
-            uint64_t key = ~0ull;
-            if (t < m) {
-                const uint32_t j = cand[r * keep_max + t];
-                key = make_key(exact_key(X, gi, static_cast<int64_t>(j), d, metric), j);
+        int m = 0;
+        for (int sg = 0; sg < nseg; ++sg) {
+            const int c = cnt[r * nseg + sg];
+            const uint32_t* src = cand + (r * nseg + sg) * keep_max;
+            for (int t = lane; t < c; t += 32) {
+                const uint32_t j = src[t];
+                sm[m + t] = make_key(exact_key(X, gi, static_cast<int64_t>(j), d, metric), j);
             }
-            sm[t] = key;
+            m += c;
         }
+        for (int t = m + lane; t < cap; t += 32) sm[t] = ~0ull;
         __syncwarp();
         warp_bitonic_sort(sm, cap, lane);
         const int64_t orow = gi - out_q0;
@@ -1430,7 +1000,6 @@ struct KnnJob {
     DevBuf<__half> ones;
     bool narrow_norm;
     int64_t sum_compactions = 0, sum_accepted = 0;
-    bool used_pair = false;  // the main sweep ran on the CTA-pair kernel
 };
 
 int build_operands(KnnJob& J, Operands& op, int passes, int MH, const int64_t* d_rowlist, int64_t nlist, bool want_a, bool want_b) {
@@ -1472,6 +1041,17 @@ int build_operands(KnnJob& J, Operands& op, int passes, int MH, const int64_t* d
     return 0;
 }
 
+// Tuning knobs of the sweep.  Release builds use the defaults; the environment is read only in builds with
+// -DSPHB_KNN_TUNING (the profile build), so the library adds no public switches.
+static int tune(const char* name, int def) {
+#ifdef SPHB_KNN_TUNING
+    if (const char* e = getenv(name)) return atoi(e);
+#else
+    (void)name;
+#endif
+    return def;
+}
+
 // One sweep + exact re-rank of query rows: either the slab [qa, qb) (A rows taken from the full operand
 // matrix) or the explicit list d_qrows[0..nq) (A rows from the gathered matrix opA).  Rows whose band
 // overflowed are appended to ovf_rows / ovf_count (device) and their number is returned in *n_ovf.
@@ -1488,64 +1068,56 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     const int rows_per_cta = MH ? MH * BM : BM;
     const int n_qtiles = static_cast<int>((nq + rows_per_cta - 1) / rows_per_cta);
     const int n_dbtiles = static_cast<int>(J.np / bn);
-    // CTA-pair kernel (cta_group::2): 1 pass, resident MH = 2, cap 512, d <= 256
-    const bool lean = passes == 1 && MH == 2 && cap == 512 && !getenv("SPHB_KNN_GENERIC_ISSUE");
-    // (opt-in, SPHB_KNN_PAIR=1: it is exact but, with the present epilogue, slower than the single-CTA kernel — the two CTAs'
-    // epilogues gate each other's accumulator stages — see DESIGN.md §4.1)
-    const bool pair = lean && dp / 64 <= 4 && J.narrow_norm && J.sms >= 2 && getenv("SPHB_KNN_PAIR") && !getenv("SPHB_KNN_NO_PAIR");
-    // two epilogue groups (16 epilogue warps, one candidate list per group and row): needs k <= 192 so that the k smallest of
-    // each list survive the cap/2 pruning at export.
-    // (opt-in, SPHB_KNN_TWO_GROUPS=1: exact, but each list sees half the database, so twice the candidates are accepted and
-    // compacted, and at 18 warps the register file allows 96 registers per thread; measured slower than one group)
-    const int G = (lean && !pair && k <= 192 && getenv("SPHB_KNN_TWO_GROUPS")) ? 2 : 1;
-    // asynchronous compaction by two helper warps (1-pass lean kernel, k <= 192 so that S holds the k smallest)
-    const bool async = lean && !pair && G == 1 && k <= 192 && getenv("SPHB_KNN_ASYNC") != nullptr;
-    const int grid = pair ? 2 * std::min(J.sms / 2, (n_qtiles + 1) / 2) : std::min(J.sms, n_qtiles);
+    const bool lean = passes == 1 && MH == 2 && cap == 512 && !tune("SPHB_KNN_GENERIC_ISSUE", 0);
+    // Database segments (resident flavour, re-sweep of a row list): enough (tile, segment) items for ~4 per SM, at most
+    // what the re-rank's shared-memory sort holds (2048 keys per row) and segments of at least 32 tiles.
+    int nseg = 1, seg_tiles = n_dbtiles;
+    if (MH && d_qrows) {
+        const int want = (4 * J.sms + n_qtiles - 1) / n_qtiles;
+        nseg = std::max(1, std::min({want, 2048 / keep_max, n_dbtiles / 32, tune("SPHB_KNN_MAX_SEG", 64)}));
+        seg_tiles = (n_dbtiles + nseg - 1) / nseg;
+        nseg = (n_dbtiles + seg_tiles - 1) / seg_tiles;  // every segment holds at least one tile
+    }
+    const int n_items = n_qtiles * nseg;
+    const int grid = std::min(J.sms, n_items);
 
     DevBuf<uint64_t> cand;
     DevBuf<uint32_t> cand_out;
     DevBuf<int> cnt_out;
-    SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * G * rows_per_cta * (async ? ASYNC_STRIDE : cap), stream));
-    SPHB_CUDA(cand_out.alloc(static_cast<size_t>(nq) * keep_max, stream));
-    SPHB_CUDA(cnt_out.alloc(nq, stream));
+    SPHB_CUDA(cand.alloc(static_cast<size_t>(grid) * rows_per_cta * cap, stream));
+    SPHB_CUDA(cand_out.alloc(static_cast<size_t>(nq) * nseg * keep_max, stream));
+    SPHB_CUDA(cnt_out.alloc(static_cast<size_t>(nq) * nseg, stream));
     SPHB_CUDA(cudaMemsetAsync(J.stats.p, 0, 3 * sizeof(unsigned long long), stream));
 
     SweepParams P{};
     P.un2 = J.un2.p; P.dun = J.dun.p; P.dvmax = reinterpret_cast<const float*>(J.dvmax.p); P.qrows = d_qrows;
     P.n = J.n; P.k = k; P.cap = cap; P.keep_max = keep_max; P.metric = J.metric;
     P.q0 = qa; P.nq = nq; P.a_row0 = d_qrows ? 0 : qa; P.n_qtiles = n_qtiles; P.n_dbtiles = n_dbtiles;
+    P.nseg = nseg; P.seg_tiles = seg_tiles;
     P.passes = passes;
     P.cand = cand.p; P.cand_out = cand_out.p; P.cnt_out = cnt_out.p; P.stats = J.stats.p;
-    P.debug_skip_epilogue = getenv("SPHB_KNN_DEBUG_SKIP_EPI") ? 1 : 0;
-    P.pair_debug = getenv("SPHB_KNN_PAIR_DEBUG") ? atoi(getenv("SPHB_KNN_PAIR_DEBUG")) : 0;
+    P.debug_skip_epilogue = tune("SPHB_KNN_DEBUG_SKIP_EPI", 0);
     P.progress = J.stats.p + 2;
-    P.l2_prefetch = getenv("SPHB_KNN_L2PF") ? atoi(getenv("SPHB_KNN_L2PF")) : 0;
-    P.compact_step = getenv("SPHB_KNN_COMPACT_STEP") ? std::max(32, atoi(getenv("SPHB_KNN_COMPACT_STEP"))) : cap;
-    P.pace_window = (MH && !pair) ? (getenv("SPHB_KNN_PACE") ? atoi(getenv("SPHB_KNN_PACE")) : 256) : 0;
+    P.l2_prefetch = tune("SPHB_KNN_L2PF", 0);
+    P.compact_step = std::max(32, tune("SPHB_KNN_COMPACT_STEP", cap));
+    // soft lock-step of the CTAs' sweeps (sweep_pace): only for whole-database items, and only when every CTA of the grid is
+    // resident at once (one CTA per SM by shared memory; the occupancy query below guards partitioned / shared devices)
+    P.pace_window = (MH && nseg == 1) ? tune("SPHB_KNN_PACE", 256) : 0;
     DevBuf<unsigned long long> prof;
 #ifdef SPHB_KNN_PROFILE
     const bool want_prof = getenv("SPHB_KNN_PROF") != nullptr;
 #else
     const bool want_prof = false;
 #endif
-    DevBuf<unsigned long long> trace;
     if (want_prof) {
-        SPHB_CUDA(trace.alloc(64 * 32, stream));
-        SPHB_CUDA(cudaMemsetAsync(trace.p, 0, 64 * 32 * sizeof(unsigned long long), stream));
-        P.trace = trace.p;
-        P.trace_t0 = getenv("SPHB_KNN_TRACE_T0") ? atoi(getenv("SPHB_KNN_TRACE_T0")) : 2000;
         SPHB_CUDA(prof.alloc(static_cast<size_t>(grid) * 16, stream));
         SPHB_CUDA(cudaMemsetAsync(prof.p, 0, static_cast<size_t>(grid) * 16 * sizeof(unsigned long long), stream));
         P.prof = prof.p;
     }
-    {
-        // CTA b starts its database sweep b*stagger tiles in: the CTAs then read different lines at any
-        // moment (no L2 hot lines) while the union of their positions stays inside an L2-sized window.
-        const char* e = getenv("SPHB_KNN_STAGGER");
-        P.stagger = e ? atoi(e) : 4;
-        const char* l = getenv("SPHB_KNN_LEAD_ROWS");
-        P.lead = (l ? atoi(l) : 16384) / bn;
-    }
+    // CTA b starts its database sweep b*stagger tiles in: the CTAs then read different lines at any
+    // moment (no L2 hot lines) while the union of their positions stays inside an L2-sized window.
+    P.stagger = tune("SPHB_KNN_STAGGER", 4);
+    P.lead = tune("SPHB_KNN_LEAD_ROWS", 16384) / bn;
     // Error models.  3 passes: split truncation 6·2^-22 + accumulation (one 2^-22 per
     // k-step), times the magnitude (2|u||v| + |v|²), plus the fp16 subnormal floor; safety factor 2.
     // 1 pass: operand rounding is bounded from the measured |u - fp16(u)| norms (knn_epilogue.cuh); the
@@ -1569,66 +1141,29 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
         if (int rc = make_tmap(&tmN, opB.N.p, J.np, opB.ldn, bn, opB.ldn == 16 ? 16 : 64)) return rc;
         const int dp64 = dp / 64;
         const int nA = (passes == 3 ? 2 : 1) * dp64;
-        const size_t fixed = static_cast<size_t>(MH * nA + 1) * CHUNK_BYTES + 256 + (G == 2 ? 1024 : 0) + (async ? 6400 : 0) + 1024;
+        const size_t fixed = static_cast<size_t>(MH * nA + 1) * CHUNK_BYTES + 256 + 1024;
         int stages = 8;
         while (stages > 2 && fixed + static_cast<size_t>(stages) * CHUNK_BYTES > smem_limit) --stages;
         const size_t smem = fixed + static_cast<size_t>(stages) * CHUNK_BYTES;
         if (smem > smem_limit) return fail(5, "knn: shared memory budget exceeded for the resident kernel");
         P.dp64 = dp64; P.stages = stages;
-        P.half_major = (stages >= 2 * (nA + 1) && !getenv("SPHB_KNN_CHUNK_MAJOR")) ? 1 : 0;
+        P.half_major = (stages >= 2 * (nA + 1) && !tune("SPHB_KNN_CHUNK_MAJOR", 0)) ? 1 : 0;
         P.norm_bytes = opB.ldn == 16 ? 128 * 32 : CHUNK_BYTES;
         const int tail = d - 64 * (dp64 - 1);
         const int k16_tail = (tail + 15) / 16;
 #define SPHB_LAUNCH_RESIDENT(MH_, R_, DP_)                                                                                                      \
     do {                                                                                                                                        \
-        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<MH_, R_, DP_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
-        knn_sweep_resident<MH_, R_, DP_><<<grid, 64 + 128 * MH_, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                              \
+        auto kern = knn_sweep_resident<MH_, R_, DP_>;                                                                                           \
+        SPHB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));                             \
+        if (P.pace_window > 0) {                                                                                                                \
+            /* the pacing spin needs every CTA of the grid resident: check what the device can host right now */                   \
+            int per_sm = 0;                                                                                                                     \
+            SPHB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 64 + 128 * MH_, smem));                                      \
+            if (static_cast<int64_t>(per_sm) * J.sms < grid) P.pace_window = 0;                                                                 \
+        }                                                                                                                                       \
+        kern<<<grid, 64 + 128 * MH_, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                                                          \
     } while (0)
-        if (pair) {
-            if (!d_qrows) J.used_pair = true;
-            CUtensorMap tmB2, tmN2;
-            if (int rc = make_tmap(&tmB2, opB.B.p, J.np, opB.ldb, 64)) return rc;
-            if (int rc = make_tmap(&tmN2, opB.N.p, J.np, opB.ldn, 64, 16)) return rc;
-            const size_t pfixed = static_cast<size_t>(2 * dp64 + 1) * CHUNK_BYTES + 1024 + 1024;
-            int pstages = static_cast<int>((smem_limit - pfixed) / tcp::SLOT_BYTES);
-            pstages = std::min(pstages, 8 * (dp64 + 1));
-            if (pstages < 2 * (dp64 + 1)) return fail(5, "knn: shared memory budget exceeded for the pair kernel");
-            const size_t psmem = pfixed + static_cast<size_t>(pstages) * tcp::SLOT_BYTES;
-            P.stages = pstages;
-            P.half_major = 1;
-            P.norm_bytes = tcp::NORM_BYTES;
-#define SPHB_LAUNCH_PAIR(DP_)                                                                                                            \
-    do {                                                                                                                                 \
-        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_pair<16, DP_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(psmem))); \
-        knn_sweep_pair<16, DP_><<<grid, tcp::NUM_THREADS, psmem, stream>>>(tmA, tmB2, tmN2, tmO, P);                                     \
-    } while (0)
-            if (dp64 == 1) SPHB_LAUNCH_PAIR(1);
-            else if (dp64 == 2) SPHB_LAUNCH_PAIR(2);
-            else if (dp64 == 3) SPHB_LAUNCH_PAIR(3);
-            else SPHB_LAUNCH_PAIR(4);
-#undef SPHB_LAUNCH_PAIR
-        }
-#define SPHB_LAUNCH_RESIDENT2(DP_)                                                                                                                 \
-    do {                                                                                                                                           \
-        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<2, 16, DP_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
-        knn_sweep_resident<2, 16, DP_, 2><<<grid, 64 + 512, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                                      \
-    } while (0)
-#define SPHB_LAUNCH_ASYNC(DP_)                                                                                                                       \
-    do {                                                                                                                                             \
-        SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_resident<2, 16, DP_, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
-        knn_sweep_resident<2, 16, DP_, 1, 2><<<grid, 64 + 256 + 64, smem, stream>>>(tmA, tmB, tmN, tmO, P, k16_tail);                                \
-    } while (0)
-        else if (async && dp64 == 1) SPHB_LAUNCH_ASYNC(1);
-        else if (async && dp64 == 2) SPHB_LAUNCH_ASYNC(2);
-        else if (async && dp64 == 3) SPHB_LAUNCH_ASYNC(3);
-        else if (async) SPHB_LAUNCH_ASYNC(4);
-#undef SPHB_LAUNCH_ASYNC
-        else if (G == 2 && dp64 == 1) SPHB_LAUNCH_RESIDENT2(1);
-        else if (G == 2 && dp64 == 2) SPHB_LAUNCH_RESIDENT2(2);
-        else if (G == 2 && dp64 == 3) SPHB_LAUNCH_RESIDENT2(3);
-        else if (G == 2) SPHB_LAUNCH_RESIDENT2(4);
-#undef SPHB_LAUNCH_RESIDENT2
-        else if (lean && dp64 == 1) SPHB_LAUNCH_RESIDENT(2, 16, 1);
+        if (lean && dp64 == 1) SPHB_LAUNCH_RESIDENT(2, 16, 1);
         else if (lean && dp64 == 2) SPHB_LAUNCH_RESIDENT(2, 16, 2);
         else if (lean && dp64 == 3) SPHB_LAUNCH_RESIDENT(2, 16, 3);
         else if (lean && dp64 == 4) SPHB_LAUNCH_RESIDENT(2, 16, 4);
@@ -1664,11 +1199,12 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
 
     trerank.start(stream);
     {
-        const size_t smem = 8 * static_cast<size_t>(cap) * sizeof(uint64_t);
+        const int cap_sort = next_pow2_i(std::max(cap, nseg * keep_max));
+        const size_t smem = 8 * static_cast<size_t>(cap_sort) * sizeof(uint64_t);
         SPHB_CUDA(cudaFuncSetAttribute(knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         const int64_t blocks = std::min<int64_t>((nq + 7) / 8, static_cast<int64_t>(J.sms) * 8);
-        knn_rerank_kernel<<<static_cast<unsigned>(blocks), 256, smem, stream>>>(J.x, d, k, cap, keep_max, J.metric, J.l2_squared, qa, nq, d_qrows,
-                                                                                 out_q0, cand_out.p, cnt_out.p, d_ids, d_dist, d_ovf_rows,
+        knn_rerank_kernel<<<static_cast<unsigned>(blocks), 256, smem, stream>>>(J.x, d, k, cap_sort, keep_max, nseg, J.metric, J.l2_squared, qa, nq,
+                                                                                 d_qrows, out_q0, cand_out.p, cnt_out.p, d_ids, d_dist, d_ovf_rows,
                                                                                  d_ovf_count);
         count_launch();
         SPHB_CUDA(cudaGetLastError());
@@ -1689,21 +1225,11 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
         double acc[16] = {0};
         for (int b = 0; b < grid; ++b)
             for (int i = 0; i < 16; ++i) acc[i] += static_cast<double>(hp[b * 16 + i]) / grid;
-        if (const char* tf = passes == 1 && !d_qrows ? getenv("SPHB_KNN_TRACE_FILE") : nullptr) {
-            std::vector<unsigned long long> ht(64 * 32);
-            cudaMemcpy(ht.data(), trace.p, ht.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
-            if (FILE* f = fopen(tf, "w")) {
-                for (int t = 0; t < 64; ++t) {
-                    for (int sl = 0; sl < 32; ++sl) fprintf(f, "%llu%c", ht[t * 32 + sl], sl == 31 ? '\n' : ' ');
-                }
-                fclose(f);
-            }
-        }
         const int ew = MH ? 4 * MH : 4;
         fprintf(stderr,
-                "[knn prof] passes %d mean cycles per CTA: producer wait_empty %.3g of %.3g | mma wait_tempty %.3g wait_full %.3g of %.3g | "
+                "[knn prof] passes %d nseg %d mean cycles per CTA: producer wait_empty %.3g of %.3g | mma wait_tempty %.3g wait_full %.3g of %.3g | "
                 "epilogue(per warp) wait_tfull %.3g ld %.3g filter+compact %.3g (compact %.3g) export %.3g of %.3g | sweep %.2f ms\n",
-                passes, acc[0], acc[1], acc[2], acc[3], acc[4], acc[5] / ew, acc[6] / ew, acc[7] / ew, acc[10] / ew, acc[8] / ew, acc[9] / ew,
+                passes, nseg, acc[0], acc[1], acc[2], acc[3], acc[4], acc[5] / ew, acc[6] / ew, acc[7] / ew, acc[10] / ew, acc[8] / ew, acc[9] / ew,
                 tsweep.ms());
     }
     return 0;
@@ -1725,15 +1251,12 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     J.sms = ctx().num_sms;
     J.dp = (d + 63) / 64 * 64;
     J.np = (n + 255) / 256 * 256;
-    {
-        const char* e = getenv("SPHB_KNN_NORM_WIDE");
-        J.narrow_norm = !(e && atoi(e) != 0);
-    }
+    J.narrow_norm = tune("SPHB_KNN_NORM_WIDE", 0) == 0;
     const int dp = J.dp, sms = J.sms;
 
     // ---- which kernel: passes and flavour
     int passes_first = (flavour >= 1 && flavour <= 3) ? 3 : 1;
-    if (const char* e = getenv("SPHB_KNN_PASSES")) { if (flavour == 0) passes_first = atoi(e) == 3 ? 3 : 1; }
+    if (flavour == 0 && tune("SPHB_KNN_PASSES", 1) == 3) passes_first = 3;
     auto pick_mh = [&](int passes) {
         if (flavour == 1 || flavour == 5) return 0;
         if (passes == 3) return dp <= 128 ? (flavour == 2 ? 1 : 2) : (dp <= 256 ? 1 : 0);
@@ -1766,9 +1289,17 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     SPHB_CUDA(cudaGetLastError());
 
     Operands op1, op3;  // full operand sets (A and B) for 1 pass / 3 passes, built on demand
-    auto ensure_full = [&](Operands& op, int passes) -> int {
-        if (op.built_b) return 0;
-        return build_operands(J, op, passes, pick_mh(passes), nullptr, 0, true, true);
+    // need_a = false: only the database side (B, norms) is wanted — the re-sweep of a row list brings its own gathered A
+    auto ensure_full = [&](Operands& op, int passes, bool need_a = true) -> int {
+        if (op.built_b && (op.A.p || !need_a)) return 0;
+        if (op.built_b) {  // B exists, A does not: build A alone
+            Operands tmp;
+            if (int rc = build_operands(J, tmp, passes, pick_mh(passes), nullptr, 0, true, false)) return rc;
+            op.A.p = tmp.A.p; op.A.s = tmp.A.s; op.A.n = tmp.A.n; op.a_rows = tmp.a_rows;
+            tmp.A.p = nullptr;
+            return 0;
+        }
+        return build_operands(J, op, passes, pick_mh(passes), nullptr, 0, need_a, true);
     };
     if (int rc = ensure_full(passes_first == 1 ? op1 : op3, passes_first)) return rc;
     tprep.stop(stream);
@@ -1829,13 +1360,13 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         if (pending1 == 0) return 0;
         EventTimer tf;
         tf.start(stream);
-        const bool dbg = getenv("SPHB_KNN_TIMING") != nullptr;
+        const bool dbg = tune("SPHB_KNN_TIMING", 0) != 0;
         auto now = [&]() { if (dbg) cudaStreamSynchronize(stream); return std::chrono::steady_clock::now(); };
         auto ms_since = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
             return std::chrono::duration<double, std::milli>(b - a).count();
         };
         const auto t0 = now();
-        if (int rc = ensure_full(op3, 3)) return rc;
+        if (int rc = ensure_full(op3, 3, false)) return rc;
         const auto t1 = now();
         // few rows: 128-row query tiles (MH = 1) put twice as many CTAs to work, each with half the MMA work per database tile
         const int mh_re = (op3.MH == 2 && (pending1 + BM - 1) / BM <= J.sms) ? 1 : op3.MH;
@@ -1887,7 +1418,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
     g_knn_ms[3] = fallback_ms;
     const Operands& opm = rows_1pass > 0 ? op1 : op3;
     const int kexec = opm.MH ? ((opm.passes == 3 ? 3 : 1) * dp + 16) : opm.lda;
-    const int64_t st[8] = {(J.used_pair && rows_1pass > 0) ? 4 : 1 + opm.MH, J.sum_compactions, J.sum_accepted, kexec, simt_rows, n_qtiles_total, rows_1pass > 0 ? 1 : 3, resweep_rows};
+    const int64_t st[8] = {1 + opm.MH, J.sum_compactions, J.sum_accepted, kexec, simt_rows, n_qtiles_total, rows_1pass > 0 ? 1 : 3, resweep_rows};
     knn_set_stats(st);
     return 0;
 }

@@ -112,6 +112,10 @@ struct SimsParams {
     int32_t* row_nnz;
 };
 
+// testing hook (sphb_debug_force_sims_slab, not in the public header): run the L2-slab kernel where the shared-memory row would fit
+static int g_force_slab = 0;
+void sims_force_slab(int on) { g_force_slab = on; }
+
 constexpr int SIMS_WARPS = 16;
 constexpr int SIMS_EB = 512;   // DENSE: row entries staged per batch (column start, length, s_ic)
 constexpr int SIMS_D = 8;      // DENSE: columns per register group (two groups: one being added, one in flight)
@@ -381,7 +385,7 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
     const size_t dense_smem = dense_fixed + static_cast<size_t>(n) * sizeof(float);
     DevBuf<float> acc;
     DevBuf<uint32_t> touched, trow;
-    if (dense_smem <= 220 * 1024 && !getenv("SPHB_SIMS_SLAB")) {
+    if (dense_smem <= 220 * 1024 && !g_force_slab) {
         SPHB_CUDA(trow.alloc(std::max<int64_t>(snnz, 1), s));
         sims_split_rows<<<g, 256, 0, s>>>(tk1.p, snnz, trow.p);
         count_launch();

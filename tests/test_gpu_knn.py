@@ -71,43 +71,27 @@ def test_tc_matches_oracle(capi, oracle, n, d, k, path, flavour, passes):
     assert st["passes"] == passes
 
 
-@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (2048, 64, 301), (3000, 200, 91), (1100, 140, 20), (40000, 256, 91)])
-def test_tc_cta_pair_kernel(capi, oracle, n, d, k, monkeypatch):
-    # the cta_group::2 kernel (opt-in, SPHB_KNN_PAIR): two CTAs share every MMA, M = 256
-    monkeypatch.setenv("SPHB_KNN_PAIR", "1")
-    rng = np.random.default_rng(n + d)
-    x = (rng.standard_normal((n, d)) * 0.3 + rng.uniform(0, 1, (1, d))).astype(np.float32)
-    _check(capi, oracle, x, k, path=6)
-    assert capi.knn_last_stats()["tensor_core"] == 4
-
-
-@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (3000, 200, 91), (40000, 256, 91)])
-def test_tc_two_epilogue_groups(capi, oracle, n, d, k, monkeypatch):
-    # opt-in variant of the resident kernel: two epilogue groups (16 warps), two candidate lists per row merged at export
-    monkeypatch.setenv("SPHB_KNN_TWO_GROUPS", "1")
-    rng = np.random.default_rng(n + d)
-    x = (rng.standard_normal((n, d)) * 0.3 + rng.uniform(0, 1, (1, d))).astype(np.float32)
-    _check(capi, oracle, x, k, path=6)
-    assert capi.knn_last_stats()["tensor_core"] == 3
-
-
-@pytest.mark.parametrize("n,d,k", [(4100, 128, 91), (3000, 200, 91), (1100, 140, 20), (40000, 256, 91), (2048, 32, 192)])
-def test_tc_async_compaction(capi, oracle, n, d, k, monkeypatch):
-    # variant of the resident kernel whose list compactions run on two helper warps (SPHB_KNN_ASYNC)
-    monkeypatch.setenv("SPHB_KNN_ASYNC", "1")
-    rng = np.random.default_rng(n + d)
-    x = (rng.standard_normal((n, d)) * 0.3 + rng.uniform(0, 1, (1, d))).astype(np.float32)
-    _check(capi, oracle, x, k, path=6)
-    assert capi.knn_last_stats()["tensor_core"] == 3
-
-
-@pytest.mark.parametrize("wide", ["0", "1"])
-def test_tc_norm_chunk_layouts(capi, oracle, wide, monkeypatch):
-    # the |v|² chunk is a narrow (16-column, SWIZZLE_32B) or wide (64-column, SWIZZLE_128B) tile
-    monkeypatch.setenv("SPHB_KNN_NORM_WIDE", wide)
+def test_tc_norm_chunk_layout(capi, oracle):
+    # the |v|² chunk is a narrow (16-column, SWIZZLE_32B) tile next to the 64-column data chunks, 1-pass and 3-pass sweeps
     x = synth.hyperspectral(64, 64, 96, endmembers=8, seed=21)
     _check(capi, oracle, x, 31, path=6)
     _check(capi, oracle, x, 31, path=5)
+
+
+def test_tc_resweep_database_segments(capi, oracle):
+    """Few overflow rows against a database of many tiles: the re-sweep cuts the database into segments (sweep_item), the
+    re-rank merges the per-segment candidate lists; rows sit on both sides of segment borders."""
+    rng = np.random.default_rng(5)
+    n, d, k = 60000, 64, 40
+    x = (rng.standard_normal((n, d)) * 0.3).astype(np.float32)
+    # three tight clusters far from the mean, spread over the index range: their rows overflow the 1-pass band
+    for c0 in (100, 29990, 59000):
+        x[c0:c0 + 700] = (5.0 + rng.standard_normal((1, d)) + 1e-3 * rng.standard_normal((700, d))).astype(np.float32)
+    rows = np.concatenate([np.arange(90, 140), np.arange(29980, 30050), np.arange(59600, 59710), rng.choice(n, 200, replace=False)])
+    _check(capi, oracle, x, k, path=2, rows=np.unique(rows))
+    st = capi.knn_last_stats()
+    assert st["resweep_rows"] > 0
+    assert len(capi.knn_last_overflow_rows(0)) == st["resweep_rows"]
 
 
 def test_tc_one_pass_overflow_resweep(capi, oracle):

@@ -105,13 +105,15 @@ def _sims_equal_up_to_ties(gc, gv, gn, oc, ov, on):
 
 
 @pytest.mark.parametrize("variant", [1, 2])
-def test_similarities_slab_and_dense_agree(capi, oracle, variant, monkeypatch):
+def test_similarities_slab_and_dense_agree(capi, oracle, variant):
     """the shared-memory row (default when it fits) and the L2-slab kernel (large levels) compute the same rows"""
     rp, c, v = walk_like_rows(1500, seed=31 + variant)
     dense = capi.create_similarities(rp, c, v, 31, 1e-4, variant)
-    monkeypatch.setenv("SPHB_SIMS_SLAB", "1")
-    slab = capi.create_similarities(rp, c, v, 31, 1e-4, variant)
-    monkeypatch.delenv("SPHB_SIMS_SLAB")
+    capi.force_sims_slab(True)
+    try:
+        slab = capi.create_similarities(rp, c, v, 31, 1e-4, variant)
+    finally:
+        capi.force_sims_slab(False)
     ref = oracle.create_similarities(rp, c, v, 31, 1e-4, variant)
     _sims_equal_up_to_ties(*dense, *ref)
     _sims_equal_up_to_ties(*slab, *ref)
