@@ -102,12 +102,19 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(self.samples)}
 
 
-def load_oracle():
-    """The CPU checker / baseline (oracle/): only the parity block, the cpu_baseline legs and --impl reference use it."""
+def load_oracle(threads=None):
+    """The CPU checker / baseline (oracle/): only the parity block, the cpu_baseline legs and --impl reference use it.
+    threads: OpenMP team size of this process (torchrun exports OMP_NUM_THREADS=1; the ranks share the host cores)."""
     sys.path.insert(0, str(ROOT / "tests"))
     import oracle_lib
 
-    return oracle_lib.load()
+    orc = oracle_lib.load()
+    if threads:
+        try:
+            ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(threads))
+        except OSError:
+            pass
+    return orc
 
 
 def cpu_reference_step(orc, x, k, q0, q1):
@@ -356,8 +363,6 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if world > 1:  # the oracle's OpenMP teams of the ranks share the host cores
-        os.environ.setdefault("OMP_NUM_THREADS", str(max(1, (os.cpu_count() or 1) // world)))
 
     from sph_b200 import synth
 
@@ -469,7 +474,7 @@ def main():
     parity = None
     orc = None
     if args.parity_rows > 0:
-        orc = load_oracle()
+        orc = load_oracle(threads=max(1, (os.cpu_count() or 1) // world))
         rows, n_re, n_simt, tot_re, tot_simt = parity_rows(capi, n, q0, q1, args.parity_rows, 4242 + rank)
         sel = torch.from_numpy(rows - q0).cuda()
         got = (job.ids[sel].cpu().numpy(), job.dist[sel].cpu().numpy(), job.cols[sel].cpu().numpy().view(np.uint32), job.vals[sel].cpu().numpy())

@@ -117,6 +117,8 @@ def load():
     lib.sphb_debug_force_knn_path.argtypes = [C.c_int]
     lib.sphb_debug_force_sims_slab.restype = None
     lib.sphb_debug_force_sims_slab.argtypes = [C.c_int]
+    lib.sphb_debug_force_walk_scan.restype = None
+    lib.sphb_debug_force_walk_scan.argtypes = [C.c_int]
     _lib = lib
     return lib
 
@@ -154,6 +156,11 @@ def force_knn_path(path: int):
 def force_sims_slab(on: bool):
     """createSimilarities: run the L2-slab accumulator kernel even where the shared-memory row fits (tests only)."""
     load().sphb_debug_force_sims_slab(int(on))
+
+
+def force_walk_scan(on: bool):
+    """doRandomWalks: run the serial-scan kernel instead of the binary-search kernel (tests only)."""
+    load().sphb_debug_force_walk_scan(int(on))
 
 
 def knn_last_stats() -> dict:

@@ -104,6 +104,7 @@ int prow_graph_launch(const int64_t*, const float*, int64_t, int, float, int, ui
 int prow_inplace_launch(int64_t, const int64_t*, float*, int, float, int, cudaStream_t);
 int prow_flat_launch(const float*, int64_t, int, double, float*, cudaStream_t);
 void sims_force_slab(int on);
+void walks_force_scan(int on);
 
 // testing hook: 0 auto, 1 SIMT, 2 tensor core (auto), 3 tc streaming 3-pass, 4 tc resident MH=1 3-pass, 5 tc 3-pass (auto flavour),
 // 6 tc 1-pass (resident when d allows), 7 tc 1-pass streaming
@@ -168,6 +169,7 @@ SPHB_API void* sphb_stream(void) { return g_ctx.ready ? static_cast<void*>(g_ctx
 // testing hooks (not in the public header): 0 auto, 1 force SIMT, 2 force tensor-core path; D1 accumulator home
 SPHB_API void sphb_debug_force_knn_path(int path) { g_force_path = path; }
 SPHB_API void sphb_debug_force_sims_slab(int on) { sphb::sims_force_slab(on); }
+SPHB_API void sphb_debug_force_walk_scan(int on) { sphb::walks_force_scan(on); }
 
 // ---------------------------------------------------------------- Stage A
 SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, int64_t q0, int64_t q1,

@@ -63,7 +63,10 @@ __device__ __forceinline__ double perplexity_search(const float (&dist)[R], floa
     int iter = 0;
     while (!found && iter < 200) {
         bool decided = false, up = false;  // up: H > ln(perplexity), beta must grow
-        if (screen_ok && beta < 1.0e30 && beta > 1.0e-30) {
+        // beta * d_min <= 60: the reference's UNSHIFTED exp(-beta d) then stays >= 1e-26 for the nearest entry, so every term that its
+        // fp32 round trip of p flushes to a denormal or zero weighs < 1e-12 of the sum and the error model above holds; beyond that
+        // (p underflows for the whole row and the reference's H collapses to log(sum)) only the fp64 replica below is trusted
+        if (screen_ok && beta < 1.0e30 && beta > 1.0e-30 && beta * static_cast<double>(dmin) <= 60.0) {
             const float bf = static_cast<float>(beta);
             float s = 0.f, h = 0.f, q = 0.f;
 #pragma unroll

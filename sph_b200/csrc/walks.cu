@@ -21,6 +21,7 @@ struct WalkParams {
     const int64_t* rowptr;
     const uint32_t* col;
     const float* val;
+    const double* cum;  // SEARCH kernel: per-entry running fp64 sum of the row (sequential order), see walk_build_cum
     uint32_t W, L;
     int weighting;
     float prune_value;
@@ -47,9 +48,38 @@ __device__ __forceinline__ float step_weight(int weighting, uint32_t step, uint3
     }
 }
 
+// testing hook (sphb_debug_force_walk_scan, not in the public header): always run the serial-scan kernel
+static int g_force_scan = 0;
+void walks_force_scan(int on) { g_force_scan = on; }
+
 constexpr int FV_MAX_LEN = 64;  // FIRST_VISIT keeps the visited set of a walk in registers/local memory
 
-template <int WARPS>
+// Running sums of every row, fp64, accumulated in storage (ascending column) order exactly as the reference's scan does
+// (`inc += val[e]`, SparseMatrixAlgorithms.cpp:129-135) — one thread per row, sequential.  With them a step is a binary
+// search for the first entry with u < cum instead of a serial scan of half the row: the same entry for every u as long as
+// the sums are non-decreasing, i.e. no value is negative (flagged otherwise; the scan kernel then runs).
+__global__ void walk_build_cum(int64_t n, const int64_t* __restrict__ rowptr, const float* __restrict__ val, double* __restrict__ cum,
+                               int* __restrict__ negative) {
+    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; r < n; r += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        double inc = 0.0;
+        bool neg = false;
+        for (int64_t e = rowptr[r]; e < rowptr[r + 1]; ++e) {
+            const float v = val[e];
+            neg |= v < 0.f;
+            inc += static_cast<double>(v);
+            cum[e] = inc;
+        }
+        if (neg) atomicExch(negative, 1);
+    }
+}
+
+constexpr int WALK_CHAINS = 3;  // SEARCH kernel: independent walks per lane in flight (96 walks per warp pass; W = 90 fits one pass)
+
+// SEARCH = true: lane = WALK_CHAINS interleaved walks, every step a binary search in the row's running sums (7 dependent
+// 8-byte probes for a 90-entry row instead of a serial scan of ~45 entries; the chains of a lane hide each other's
+// latency).  SEARCH = false: the serial scan (rows with negative values, FIRST_VISIT weighting which keeps a visited set).
+// Both draw the same Philox uniform per (start, walk, step) and pick the same entry, so their results are identical.
+template <int WARPS, bool SEARCH>
 __global__ void __launch_bounds__(WARPS * 32) random_walk_kernel(const WalkParams P) {
     extern __shared__ uint64_t smem_ev[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -60,6 +90,62 @@ __global__ void __launch_bounds__(WARPS * 32) random_walk_kernel(const WalkParam
     for (int64_t s = static_cast<int64_t>(blockIdx.x) * WARPS + warp; s < P.nstarts; s += static_cast<int64_t>(gridDim.x) * WARPS) {
         const int64_t start = P.start0 + s;
         // ---- 1. the walks
+        if constexpr (SEARCH) {
+            for (uint32_t w0 = 0; w0 < W; w0 += 32 * WALK_CHAINS) {
+                int64_t cur[WALK_CHAINS];
+                bool live[WALK_CHAINS];
+#pragma unroll
+                for (int c = 0; c < WALK_CHAINS; ++c) {
+                    cur[c] = start;
+                    live[c] = w0 + c * 32 + lane < W;
+                }
+                for (uint32_t step = 0; step < L; ++step) {
+                    double u[WALK_CHAINS];
+                    int64_t lo[WALK_CHAINS], hi[WALK_CHAINS], e1[WALK_CHAINS];
+#pragma unroll
+                    for (int c = 0; c < WALK_CHAINS; ++c) {
+                        const uint32_t w = w0 + c * 32 + lane;
+                        const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(start), static_cast<uint32_t>(start >> 32), w, step), key);
+                        u[c] = u01_from_bits(r.x, r.y);
+                        lo[c] = live[c] ? __ldg(P.rowptr + cur[c]) : 0;
+                        e1[c] = live[c] ? __ldg(P.rowptr + cur[c] + 1) : 0;
+                        hi[c] = e1[c];
+                    }
+                    // first entry with u < cum (lower bound on a non-decreasing array); the chains advance together
+                    while (true) {
+                        bool any = false;
+                        double cm[WALK_CHAINS];
+                        int64_t mid[WALK_CHAINS];
+#pragma unroll
+                        for (int c = 0; c < WALK_CHAINS; ++c) {
+                            mid[c] = (lo[c] + hi[c]) >> 1;
+                            if (lo[c] < hi[c]) {
+                                cm[c] = __ldg(P.cum + mid[c]);
+                                any = true;
+                            }
+                        }
+                        if (!any) break;
+#pragma unroll
+                        for (int c = 0; c < WALK_CHAINS; ++c) {
+                            if (lo[c] < hi[c]) {
+                                if (u[c] < cm[c]) hi[c] = mid[c];
+                                else lo[c] = mid[c] + 1;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int c = 0; c < WALK_CHAINS; ++c) {
+                        if (!live[c]) continue;
+                        const uint32_t w = w0 + c * 32 + lane;
+                        const int64_t next = lo[c] < e1[c] ? static_cast<int64_t>(__ldg(P.col + lo[c])) : cur[c];  // never found: stays put
+                        const bool record = P.weighting == SPHB_W_ONLYLAST ? step == L - 1 : true;
+                        const uint32_t order = w * L + step;
+                        ev[order] = record ? ((static_cast<uint64_t>(next) << 32) | order) : ~0ull;
+                        cur[c] = next;
+                    }
+                }
+            }
+        } else {
         for (uint32_t w = lane; w < W; w += 32) {
             int64_t cur = start;
             uint32_t visited[FV_MAX_LEN + 1];
@@ -90,6 +176,7 @@ __global__ void __launch_bounds__(WARPS * 32) random_walk_kernel(const WalkParam
                 ev[order] = record ? ((static_cast<uint64_t>(next) << 32) | order) : ~0ull;
                 cur = next;
             }
+        }
         }
         for (int t = total + lane; t < P.cap_ev; t += 32) ev[t] = ~0ull;
         __syncwarp();
@@ -237,8 +324,28 @@ int random_walks_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_
     SPHB_CUDA(cnt.alloc(chunk, s));
     SPHB_CUDA(cnt64.alloc(chunk + 1, s));
     SPHB_CUDA(offs.alloc(chunk + 1, s));
-    if (warps == WARPS) SPHB_CUDA(cudaFuncSetAttribute(random_walk_kernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    else SPHB_CUDA(cudaFuncSetAttribute(random_walk_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    // running sums for the binary-search kernel (8 B per entry); FIRST_VISIT and matrices with negative entries use the scan kernel
+    DevBuf<double> cum;
+    bool search = weighting != SPHB_W_FIRST_VISIT && !g_force_scan;
+    if (search) {
+        int64_t nnz_in = 0;
+        SPHB_CUDA(cudaMemcpyAsync(&nnz_in, d_rowptr + n, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+        SPHB_CUDA(cudaStreamSynchronize(s));
+        DevBuf<int> negative;
+        SPHB_CUDA(negative.alloc(1, s));
+        SPHB_CUDA(cudaMemsetAsync(negative.p, 0, sizeof(int), s));
+        SPHB_CUDA(cum.alloc(static_cast<size_t>(std::max<int64_t>(nnz_in, 1)), s));
+        walk_build_cum<<<static_cast<unsigned>(std::max<int64_t>(1, std::min<int64_t>((n + 127) / 128, static_cast<int64_t>(sms) * 16))), 128, 0, s>>>(
+            n, d_rowptr, d_val, cum.p, negative.p);
+        count_launch();
+        int hneg = 0;
+        SPHB_CUDA(cudaMemcpyAsync(&hneg, negative.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+        SPHB_CUDA(cudaStreamSynchronize(s));
+        if (hneg) search = false;
+    }
+    auto set_attr = [&](auto kern) { return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)); };
+    if (warps == WARPS) SPHB_CUDA(search ? set_attr(random_walk_kernel<WARPS, true>) : set_attr(random_walk_kernel<WARPS, false>));
+    else SPHB_CUDA(search ? set_attr(random_walk_kernel<1, true>) : set_attr(random_walk_kernel<1, false>));
     int64_t base = 0;
     for (int64_t s0 = q0; s0 < q1; s0 += chunk) {
         const int64_t ns = std::min(chunk, q1 - s0);
@@ -247,10 +354,12 @@ int random_walks_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_
         P.W = static_cast<uint32_t>(num_walks); P.L = static_cast<uint32_t>(walk_len);
         P.weighting = weighting; P.prune_value = pv; P.seed = seed; P.remove_diagonal = remove_diagonal; P.normalize = normalize;
         P.cap_ev = cap_ev; P.start0 = s0; P.nstarts = ns; P.tmp_stride = tmp_stride;
-        P.tmp_col = tcol.p; P.tmp_val = tval.p; P.row_nnz = cnt.p;
+        P.tmp_col = tcol.p; P.tmp_val = tval.p; P.row_nnz = cnt.p; P.cum = cum.p;
         const int64_t blocks = std::min<int64_t>((ns + warps - 1) / warps, static_cast<int64_t>(sms) * 16);
-        if (warps == WARPS) random_walk_kernel<WARPS><<<static_cast<unsigned>(blocks), WARPS * 32, smem, s>>>(P);
-        else random_walk_kernel<1><<<static_cast<unsigned>(blocks), 32, smem, s>>>(P);
+        if (warps == WARPS && search) random_walk_kernel<WARPS, true><<<static_cast<unsigned>(blocks), WARPS * 32, smem, s>>>(P);
+        else if (warps == WARPS) random_walk_kernel<WARPS, false><<<static_cast<unsigned>(blocks), WARPS * 32, smem, s>>>(P);
+        else if (search) random_walk_kernel<1, true><<<static_cast<unsigned>(blocks), 32, smem, s>>>(P);
+        else random_walk_kernel<1, false><<<static_cast<unsigned>(blocks), 32, smem, s>>>(P);
         widen_counts<<<static_cast<unsigned>(std::min<int64_t>((ns + 256) / 256, sms * 8)), 256, 0, s>>>(cnt.p, ns, cnt64.p);
         count_launch(2);
         if (int rc = exclusive_sum<int64_t>(cnt64.p, offs.p, ns + 1, s)) return rc;

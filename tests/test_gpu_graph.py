@@ -285,3 +285,28 @@ def test_neighbor_overlap_matches_oracle(capi, oracle):
     a = capi.neighbor_overlap(knn, comp_ptr, order, pa, pb)
     b = oracle.neighbor_overlap(knn, comp_ptr, order, pa, pb)
     np.testing.assert_array_equal(a, b)
+
+
+# ---------------------------------------------------------------- RW1: binary-search kernel == serial-scan kernel
+@pytest.mark.parametrize("weighting", [0, 1, 2, 3])
+def test_random_walks_search_equals_scan(capi, weighting):
+    """The step of the production kernel is a binary search in the rows' fp64 running sums; the serial scan of the reference
+    (`inc += val[e]; if (u < inc)`, SparseMatrixAlgorithms.cpp:129-135) picks the same entry for the same uniform, so the two
+    kernels must agree bit for bit — rows of 1..60 entries, an empty row (walk stays put) and rows that do not sum to 1."""
+    rp, c, v = random_stochastic(1500, 60, seed=33)
+    v = v.copy()
+    v[rp[7]:rp[8]] *= 0.5                      # defective row: u beyond the last running sum -> stays put
+    lens = np.diff(rp)
+    keep = np.ones(len(c), bool)
+    keep[rp[11]:rp[12]] = False                # empty row
+    rp2 = np.concatenate([[0], np.cumsum(np.where(np.arange(1500) == 11, 0, lens))]).astype(np.int64)
+    c2, v2 = c[keep], v[keep]
+    W, L = 90, 15
+    a = capi.random_walks(rp2, c2, v2, W, L, weighting, seed=3)
+    capi.force_walk_scan(True)
+    try:
+        b = capi.random_walks(rp2, c2, v2, W, L, weighting, seed=3)
+    finally:
+        capi.force_walk_scan(False)
+    for x, y in zip(a, b):
+        np.testing.assert_array_equal(x, y)

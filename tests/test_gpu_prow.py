@@ -80,3 +80,29 @@ def test_gaussian_flat(capi, oracle):
     out = capi.prow_gaussian_flat(dist, 30.0)
     ref = oracle.prow_gaussian_flat(dist, 30.0)
     np.testing.assert_allclose(out, ref, rtol=RTOL, atol=1e-12)
+
+
+def test_search_ends_at_the_reference_beta(capi, oracle):
+    """The search screens every iterate in fp32 (with a proven error band) before falling back to the reference's fp64 evaluation:
+    every branch it takes must be the reference's, so the final beta — returned as sigma = sqrt(1 / 2 beta) — is bit-identical.
+    20 000 rows over 12 decades of distance scale, large offsets (beta * d_min beyond the fp32 underflow of p), near-constant rows,
+    heavy ties, perplexities from 2 to k - 2."""
+    rng = np.random.default_rng(123)
+    n, k = 20000, 91
+    base = np.sort(rng.gamma(2.0, 1.0, size=(n, k)).astype(np.float32), axis=1)
+    scale = (10.0 ** rng.uniform(-6, 6, size=(n, 1))).astype(np.float32)
+    dist = base * scale
+    off = np.where(rng.uniform(size=(n, 1)) < 0.3, 10.0 ** rng.uniform(-3, 3, size=(n, 1)), 0.0).astype(np.float32)
+    dist = dist + off * scale
+    dist[:2000] = np.round(dist[:2000] / scale[:2000] * 2) / 2 * scale[:2000]      # ties
+    dist[2000:3000, 1:] = dist[2000:3000, 1:2] * (1 + 1e-6 * rng.uniform(size=(1000, k - 1))).astype(np.float32)  # near-constant
+    dist = np.sort(dist, axis=1)
+    dist[:, 0] = 0
+    offs = 1 + np.argsort(rng.random((n, 400)), axis=1)[:, :k - 1]   # distinct neighbours per row, as in a kNN graph
+    ids = np.concatenate([np.arange(n)[:, None], (np.arange(n)[:, None] + offs) % n], axis=1).astype(np.int64)
+    for perp in (0.0, 2.0, 50.0, 89.0):
+        cols, vals, sigma = capi.prow_gaussian_graph(ids, dist, perp, want_sigma=True)
+        rcols, rvals, rsigma = oracle.prow_gaussian_graph(ids, dist, perp)
+        np.testing.assert_array_equal(sigma, rsigma)
+        np.testing.assert_array_equal(cols, rcols)
+        np.testing.assert_allclose(vals, rvals, rtol=RTOL, atol=1e-12)
