@@ -27,7 +27,8 @@ struct WalkParams {
     float prune_value;
     uint64_t seed;
     int remove_diagonal, normalize;
-    int cap_ev;         // events per start, power of two >= W*L
+    int cap_ev;         // events per start: scan kernel power of two >= W*L; search kernel W*L rounded up to 32
+    int col_bits, radix_bits;  // search kernel: bits of a column id, digit width of the radix passes
     int64_t start0, nstarts;
     int tmp_stride;     // entries per start in the temp buffers
     uint32_t* tmp_col;
@@ -75,11 +76,10 @@ __global__ void walk_build_cum(int64_t n, const int64_t* __restrict__ rowptr, co
 
 constexpr int WALK_CHAINS = 3;  // SEARCH kernel: independent walks per lane in flight (96 walks per warp pass; W = 90 fits one pass)
 
-// SEARCH = true: lane = WALK_CHAINS interleaved walks, every step a binary search in the row's running sums (7 dependent
-// 8-byte probes for a 90-entry row instead of a serial scan of ~45 entries; the chains of a lane hide each other's
-// latency).  SEARCH = false: the serial scan (rows with negative values, FIRST_VISIT weighting which keeps a visited set).
-// Both draw the same Philox uniform per (start, walk, step) and pick the same entry, so their results are identical.
-template <int WARPS, bool SEARCH>
+// The serial-scan kernel: lane = walk, every step scans the current row until u < inc.  Runs for matrices with negative
+// values and for FIRST_VISIT weighting (which keeps a visited set per walk); everything else takes random_walk_search_kernel
+// below.  Both draw the same Philox uniform per (start, walk, step) and pick the same entry, so their results are identical.
+template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) random_walk_kernel(const WalkParams P) {
     extern __shared__ uint64_t smem_ev[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -90,62 +90,6 @@ __global__ void __launch_bounds__(WARPS * 32) random_walk_kernel(const WalkParam
     for (int64_t s = static_cast<int64_t>(blockIdx.x) * WARPS + warp; s < P.nstarts; s += static_cast<int64_t>(gridDim.x) * WARPS) {
         const int64_t start = P.start0 + s;
         // ---- 1. the walks
-        if constexpr (SEARCH) {
-            for (uint32_t w0 = 0; w0 < W; w0 += 32 * WALK_CHAINS) {
-                int64_t cur[WALK_CHAINS];
-                bool live[WALK_CHAINS];
-#pragma unroll
-                for (int c = 0; c < WALK_CHAINS; ++c) {
-                    cur[c] = start;
-                    live[c] = w0 + c * 32 + lane < W;
-                }
-                for (uint32_t step = 0; step < L; ++step) {
-                    double u[WALK_CHAINS];
-                    int64_t lo[WALK_CHAINS], hi[WALK_CHAINS], e1[WALK_CHAINS];
-#pragma unroll
-                    for (int c = 0; c < WALK_CHAINS; ++c) {
-                        const uint32_t w = w0 + c * 32 + lane;
-                        const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(start), static_cast<uint32_t>(start >> 32), w, step), key);
-                        u[c] = u01_from_bits(r.x, r.y);
-                        lo[c] = live[c] ? __ldg(P.rowptr + cur[c]) : 0;
-                        e1[c] = live[c] ? __ldg(P.rowptr + cur[c] + 1) : 0;
-                        hi[c] = e1[c];
-                    }
-                    // first entry with u < cum (lower bound on a non-decreasing array); the chains advance together
-                    while (true) {
-                        bool any = false;
-                        double cm[WALK_CHAINS];
-                        int64_t mid[WALK_CHAINS];
-#pragma unroll
-                        for (int c = 0; c < WALK_CHAINS; ++c) {
-                            mid[c] = (lo[c] + hi[c]) >> 1;
-                            if (lo[c] < hi[c]) {
-                                cm[c] = __ldg(P.cum + mid[c]);
-                                any = true;
-                            }
-                        }
-                        if (!any) break;
-#pragma unroll
-                        for (int c = 0; c < WALK_CHAINS; ++c) {
-                            if (lo[c] < hi[c]) {
-                                if (u[c] < cm[c]) hi[c] = mid[c];
-                                else lo[c] = mid[c] + 1;
-                            }
-                        }
-                    }
-#pragma unroll
-                    for (int c = 0; c < WALK_CHAINS; ++c) {
-                        if (!live[c]) continue;
-                        const uint32_t w = w0 + c * 32 + lane;
-                        const int64_t next = lo[c] < e1[c] ? static_cast<int64_t>(__ldg(P.col + lo[c])) : cur[c];  // never found: stays put
-                        const bool record = P.weighting == SPHB_W_ONLYLAST ? step == L - 1 : true;
-                        const uint32_t order = w * L + step;
-                        ev[order] = record ? ((static_cast<uint64_t>(next) << 32) | order) : ~0ull;
-                        cur[c] = next;
-                    }
-                }
-            }
-        } else {
         for (uint32_t w = lane; w < W; w += 32) {
             int64_t cur = start;
             uint32_t visited[FV_MAX_LEN + 1];
@@ -176,7 +120,6 @@ __global__ void __launch_bounds__(WARPS * 32) random_walk_kernel(const WalkParam
                 ev[order] = record ? ((static_cast<uint64_t>(next) << 32) | order) : ~0ull;
                 cur = next;
             }
-        }
         }
         for (int t = total + lane; t < P.cap_ev; t += 32) ev[t] = ~0ull;
         __syncwarp();
@@ -252,6 +195,227 @@ __global__ void __launch_bounds__(WARPS * 32) random_walk_kernel(const WalkParam
             oc[t] = static_cast<uint32_t>(k >> 32);
             const float v = __uint_as_float(static_cast<uint32_t>(k));
             ov[t] = P.normalize ? v / nv : v;
+        }
+        if (lane == 0) P.row_nnz[s] = m;
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// The production kernel.  lane = WALK_CHAINS interleaved walks; every step is a binary search in the row's running sums
+// (7 dependent 8-byte probes for a 90-entry row instead of a serial scan of ~45 entries; the chains of a lane hide each
+// other's latency).  The events of a start are kept as (column u32, step u16) in event order — the array index IS the
+// event order — and grouped by column with a STABLE LSD radix sort in shared memory (digits of <= 9 bits; per 32-event chunk
+// a match.any gives the rank among equal digits), so every run of equal columns is still in event order and its fp32 sum is
+// the reference's `hits[next] += stepWeight` sequence.  Step weights come from a table built once per block.
+// (ncu on the first version — u64 keys, bitonic sort of 2048, expf per event: 90 k warp instructions per start, half of them
+// the sort, a third the weights; profiles/r02_walk_*.)
+// Shared memory per warp: colA, colB u32[cap] | stepA, stepB u16[cap] | cnt u32[512]; per block: wt float[L].
+// ---------------------------------------------------------------------------------------------
+constexpr int WALK_RADIX_BITS = 9;
+
+__device__ __forceinline__ void warp_radix_pass(const uint32_t* __restrict__ ksrc, const uint16_t* __restrict__ psrc, uint32_t* __restrict__ kdst,
+                                                uint16_t* __restrict__ pdst, uint32_t* __restrict__ cnt, int nev, int shift, int bits, int lane) {
+    const int bins = 1 << bits;
+    const uint32_t dmask = static_cast<uint32_t>(bins - 1);
+    for (int b = lane; b < bins; b += 32) cnt[b] = 0;
+    __syncwarp();
+    for (int t = lane; t < nev; t += 32) atomicAdd(&cnt[(ksrc[t] >> shift) & dmask], 1u);
+    __syncwarp();
+    // exclusive scan of the bins: lane owns bins [lane * per, (lane + 1) * per)
+    const int per = bins >> 5;  // bins >= 32
+    uint32_t local = 0;
+    for (int b = 0; b < per; ++b) local += cnt[lane * per + b];
+    uint32_t incl = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+    }
+    uint32_t run = incl - local;
+    for (int b = 0; b < per; ++b) {
+        const uint32_t c = cnt[lane * per + b];
+        cnt[lane * per + b] = run;
+        run += c;
+    }
+    __syncwarp();
+    // stable scatter, chunk by chunk in event order
+    for (int base = 0; base < nev; base += 32) {
+        const int t = base + lane;
+        const bool valid = t < nev;
+        const uint32_t key = valid ? ksrc[t] : 0u;
+        const uint16_t pay = valid ? psrc[t] : static_cast<uint16_t>(0);
+        const uint32_t dg = valid ? ((key >> shift) & dmask) : static_cast<uint32_t>(bins + lane);  // invalid lanes group with nobody
+        const unsigned peers = __match_any_sync(0xffffffffu, dg);
+        const uint32_t off = valid ? cnt[dg] : 0u;
+        __syncwarp();
+        if (valid && (__ffs(peers) - 1) == lane) cnt[dg] = off + __popc(peers);
+        __syncwarp();
+        if (valid) {
+            const uint32_t pos = off + __popc(peers & ((1u << lane) - 1u));
+            kdst[pos] = key;
+            pdst[pos] = pay;
+        }
+    }
+    __syncwarp();
+}
+
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) random_walk_search_kernel(const WalkParams P) {
+    extern __shared__ uint64_t smem_ev[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t W = P.W, L = P.L;
+    const bool all_steps = P.weighting != SPHB_W_ONLYLAST;       // ONLYLAST records one event per walk
+    const int nev = static_cast<int>(all_steps ? W * L : W);
+    const int cap = P.cap_ev;                                     // >= nev, multiple of 32
+    uint8_t* base8 = reinterpret_cast<uint8_t*>(smem_ev) + static_cast<size_t>(warp) * (static_cast<size_t>(cap) * 12 + 2048);
+    uint32_t* colA = reinterpret_cast<uint32_t*>(base8);
+    uint32_t* colB = colA + cap;
+    uint16_t* stepA = reinterpret_cast<uint16_t*>(colB + cap);
+    uint16_t* stepB = stepA + cap;
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(stepB + cap);
+    float* wt = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(smem_ev) + static_cast<size_t>(WARPS) * (static_cast<size_t>(cap) * 12 + 2048));
+    for (uint32_t t = threadIdx.x; t < L; t += WARPS * 32) wt[t] = step_weight(P.weighting, t, L);
+    __syncthreads();
+    const uint2 key = make_uint2(static_cast<uint32_t>(P.seed), static_cast<uint32_t>(P.seed >> 32));
+    for (int64_t s = static_cast<int64_t>(blockIdx.x) * WARPS + warp; s < P.nstarts; s += static_cast<int64_t>(gridDim.x) * WARPS) {
+        const int64_t start = P.start0 + s;
+        // ---- 1. the walks
+        for (uint32_t w0 = 0; w0 < W; w0 += 32 * WALK_CHAINS) {
+            int64_t cur[WALK_CHAINS];
+            bool live[WALK_CHAINS];
+#pragma unroll
+            for (int c = 0; c < WALK_CHAINS; ++c) {
+                cur[c] = start;
+                live[c] = w0 + c * 32 + lane < W;
+            }
+            for (uint32_t step = 0; step < L; ++step) {
+                double u[WALK_CHAINS];
+                int64_t lo[WALK_CHAINS], hi[WALK_CHAINS], e1[WALK_CHAINS];
+#pragma unroll
+                for (int c = 0; c < WALK_CHAINS; ++c) {
+                    const uint32_t w = w0 + c * 32 + lane;
+                    const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(start), static_cast<uint32_t>(start >> 32), w, step), key);
+                    u[c] = u01_from_bits(r.x, r.y);
+                    lo[c] = live[c] ? __ldg(P.rowptr + cur[c]) : 0;
+                    e1[c] = live[c] ? __ldg(P.rowptr + cur[c] + 1) : 0;
+                    hi[c] = e1[c];
+                }
+                // first entry with u < cum (lower bound on a non-decreasing array); the chains advance together
+                while (true) {
+                    bool any = false;
+                    double cm[WALK_CHAINS];
+                    int64_t mid[WALK_CHAINS];
+#pragma unroll
+                    for (int c = 0; c < WALK_CHAINS; ++c) {
+                        mid[c] = (lo[c] + hi[c]) >> 1;
+                        if (lo[c] < hi[c]) {
+                            cm[c] = __ldg(P.cum + mid[c]);
+                            any = true;
+                        }
+                    }
+                    if (!any) break;
+#pragma unroll
+                    for (int c = 0; c < WALK_CHAINS; ++c) {
+                        if (lo[c] < hi[c]) {
+                            if (u[c] < cm[c]) hi[c] = mid[c];
+                            else lo[c] = mid[c] + 1;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < WALK_CHAINS; ++c) {
+                    if (!live[c]) continue;
+                    const uint32_t w = w0 + c * 32 + lane;
+                    const int64_t next = lo[c] < e1[c] ? static_cast<int64_t>(__ldg(P.col + lo[c])) : cur[c];  // never found: stays put
+                    if (all_steps) {
+                        colA[w * L + step] = static_cast<uint32_t>(next);
+                        stepA[w * L + step] = static_cast<uint16_t>(step);
+                    } else if (step == L - 1) {
+                        colA[w] = static_cast<uint32_t>(next);
+                        stepA[w] = static_cast<uint16_t>(step);
+                    }
+                    cur[c] = next;
+                }
+            }
+        }
+        __syncwarp();
+        // ---- 2. group by column, stable (event order survives inside every run)
+        uint32_t* ck = colA;
+        uint16_t* cp = stepA;
+        uint32_t* ok = colB;
+        uint16_t* op = stepB;
+        for (int shift = 0; shift < P.col_bits; shift += P.radix_bits) {
+            int bits = min(P.radix_bits, P.col_bits - shift);
+            if (bits < 5) bits = 5;  // at least 32 bins (one per lane in the scan); the extra digit bits are zero
+            warp_radix_pass(ck, cp, ok, op, cnt, nev, shift, bits, lane);
+            uint32_t* tk = ck; ck = ok; ok = tk;
+            uint16_t* tp = cp; cp = op; op = tp;
+        }
+        // ---- 3. reduce every run of equal columns in event order; (column, value) -> (ok, float view of ck) compacted in place
+        float* vout = reinterpret_cast<float*>(ck);
+        int m = 0;
+        uint32_t prev_col = 0xffffffffu;
+        bool have_prev = false;
+        for (int base = 0; base < nev; base += 32) {
+            const int t = base + lane;
+            const bool valid = t < nev;
+            const uint32_t c = valid ? ck[t] : 0xffffffffu;
+            uint32_t pc = __shfl_up_sync(0xffffffffu, c, 1);
+            bool pv = __shfl_up_sync(0xffffffffu, valid ? 1 : 0, 1) != 0;
+            if (lane == 0) { pc = prev_col; pv = have_prev; }
+            const bool head = valid && !(pv && pc == c);
+            float sum = 0.f;
+            if (head) {
+                for (int u = t; u < nev && ck[u] == c; ++u) sum += all_steps ? wt[cp[u]] : 1.f;
+            }
+            bool keep = head;
+            if (keep && P.prune_value > 0.f && (sum <= P.prune_value || sum == 0.f)) keep = false;
+            prev_col = __shfl_sync(0xffffffffu, c, 31);
+            have_prev = __shfl_sync(0xffffffffu, valid ? 1 : 0, 31) != 0;
+            const unsigned mask = __ballot_sync(0xffffffffu, keep);
+            __syncwarp();  // all reads of this chunk (and the forward run scans) are done before the in-place writes
+            if (keep) {
+                const int o = m + __popc(mask & ((1u << lane) - 1u));
+                ok[o] = c;
+                vout[o] = sum;
+            }
+            m += __popc(mask);
+            __syncwarp();
+        }
+        // ---- 4. removeDiagonalElements(keepSingleEntry = true): with more than one entry, drop the diagonal and every exact zero
+        if (P.remove_diagonal && m > 1) {
+            int m2 = 0;
+            for (int base = 0; base < m; base += 32) {
+                const int t = base + lane;
+                const uint32_t c = t < m ? ok[t] : 0u;
+                const float v = t < m ? vout[t] : 0.f;
+                const bool keep = t < m && static_cast<int64_t>(c) != start && v != 0.f;
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                __syncwarp();
+                if (keep) {
+                    const int o = m2 + __popc(mask & ((1u << lane) - 1u));
+                    ok[o] = c;
+                    vout[o] = v;
+                }
+                m2 += __popc(mask);
+                __syncwarp();
+            }
+            m = m2;
+        }
+        // ---- 5. L1 normalisation: fp32 sum in column order (Eigen sum()), then the single write of the row
+        float nv = 1.f;
+        if (P.normalize) {
+            float acc = 0.f;
+            if (lane == 0)
+                for (int t = 0; t < m; ++t) acc += vout[t];
+            nv = __shfl_sync(0xffffffffu, acc, 0);
+        }
+        uint32_t* oc = P.tmp_col + s * P.tmp_stride;
+        float* ov = P.tmp_val + s * P.tmp_stride;
+        for (int t = lane; t < m; t += 32) {
+            oc[t] = ok[t];
+            ov[t] = P.normalize ? vout[t] / nv : vout[t];
         }
         if (lane == 0) P.row_nnz[s] = m;
         __syncwarp();
@@ -343,9 +507,22 @@ int random_walks_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_
         SPHB_CUDA(cudaStreamSynchronize(s));
         if (hneg) search = false;
     }
+    // shared memory: scan kernel u64 events (power of two for the bitonic sort); search kernel (col u32, step u16) x 2 buffers + 512 radix
+    // counters per warp + the step-weight table
+    int cap_s = 0, col_bits = 0, radix_bits = 0;
+    if (search) {
+        const int nev = static_cast<int>(weighting == SPHB_W_ONLYLAST ? num_walks : total);
+        cap_s = (nev + 31) / 32 * 32;
+        smem = static_cast<size_t>(WARPS) * (static_cast<size_t>(cap_s) * 12 + 2048) + walk_len * sizeof(float);
+        warps = WARPS;
+        if (smem > 200 * 1024) { warps = 1; smem = static_cast<size_t>(cap_s) * 12 + 2048 + walk_len * sizeof(float); }
+        col_bits = std::max(5, bits_for(static_cast<uint64_t>(n)));
+        const int passes = (col_bits + WALK_RADIX_BITS - 1) / WALK_RADIX_BITS;
+        radix_bits = (col_bits + passes - 1) / passes;
+    }
     auto set_attr = [&](auto kern) { return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)); };
-    if (warps == WARPS) SPHB_CUDA(search ? set_attr(random_walk_kernel<WARPS, true>) : set_attr(random_walk_kernel<WARPS, false>));
-    else SPHB_CUDA(search ? set_attr(random_walk_kernel<1, true>) : set_attr(random_walk_kernel<1, false>));
+    if (warps == WARPS) SPHB_CUDA(search ? set_attr(random_walk_search_kernel<WARPS>) : set_attr(random_walk_kernel<WARPS>));
+    else SPHB_CUDA(search ? set_attr(random_walk_search_kernel<1>) : set_attr(random_walk_kernel<1>));
     int64_t base = 0;
     for (int64_t s0 = q0; s0 < q1; s0 += chunk) {
         const int64_t ns = std::min(chunk, q1 - s0);
@@ -355,11 +532,12 @@ int random_walks_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_
         P.weighting = weighting; P.prune_value = pv; P.seed = seed; P.remove_diagonal = remove_diagonal; P.normalize = normalize;
         P.cap_ev = cap_ev; P.start0 = s0; P.nstarts = ns; P.tmp_stride = tmp_stride;
         P.tmp_col = tcol.p; P.tmp_val = tval.p; P.row_nnz = cnt.p; P.cum = cum.p;
+        if (search) { P.cap_ev = cap_s; P.col_bits = col_bits; P.radix_bits = radix_bits; }
         const int64_t blocks = std::min<int64_t>((ns + warps - 1) / warps, static_cast<int64_t>(sms) * 16);
-        if (warps == WARPS && search) random_walk_kernel<WARPS, true><<<static_cast<unsigned>(blocks), WARPS * 32, smem, s>>>(P);
-        else if (warps == WARPS) random_walk_kernel<WARPS, false><<<static_cast<unsigned>(blocks), WARPS * 32, smem, s>>>(P);
-        else if (search) random_walk_kernel<1, true><<<static_cast<unsigned>(blocks), 32, smem, s>>>(P);
-        else random_walk_kernel<1, false><<<static_cast<unsigned>(blocks), 32, smem, s>>>(P);
+        if (warps == WARPS && search) random_walk_search_kernel<WARPS><<<static_cast<unsigned>(blocks), WARPS * 32, smem, s>>>(P);
+        else if (warps == WARPS) random_walk_kernel<WARPS><<<static_cast<unsigned>(blocks), WARPS * 32, smem, s>>>(P);
+        else if (search) random_walk_search_kernel<1><<<static_cast<unsigned>(blocks), 32, smem, s>>>(P);
+        else random_walk_kernel<1><<<static_cast<unsigned>(blocks), 32, smem, s>>>(P);
         widen_counts<<<static_cast<unsigned>(std::min<int64_t>((ns + 256) / 256, sms * 8)), 256, 0, s>>>(cnt.p, ns, cnt64.p);
         count_launch(2);
         if (int rc = exclusive_sum<int64_t>(cnt64.p, offs.p, ns + 1, s)) return rc;
