@@ -20,6 +20,14 @@
  *     SPHB_ERR_NO_DEVICE;
  *   - single caller at a time per process (the reference facade is sequential,
  *     sph/ComputeHierarchy.cpp:262-276).
+ *   - size limits (exceeding one returns SPHB_ERR_UNSUPPORTED / SPHB_ERR_CAPACITY with a message, never a truncated result):
+ *       kNN: n < 2^31 points on the tensor-core path (2^32 - 1 on the SIMT path), k <= 864 on the tensor-core path
+ *            (next_pow2(k + 160) <= 1024), any d >= 1 (d < 8 or n < 1024 run the exact SIMT kernel);
+ *       P rows: k <= 1024 per row (graph, ragged and in-place variants);
+ *       random walks: numRandomWalks * singleWalkLength <= 8192 events per start point, FIRST_VISIT walk length <= 64;
+ *       createSimilarities / level kNN: k <= 992, n < 2^32; findTopK / findBottomK: rows of at most 4096 entries;
+ *       every sort-based pass (symmetrize, rw_merge, symmetrize_graph, merge_*): at most 2^31 - 1 records per call
+ *       (symmetrize expands to 2 * nnz records);
  *   - sparse matrices cross the boundary as CSR: int64 rowptr[n+1],
  *     uint32 col[nnz] (column-sorted within a row), float val[nnz] — the flat
  *     form of SparseMatSPH / SparseMatHDI (sph/utils/CommonDefinitions.hpp:87-93).
@@ -50,7 +58,10 @@ enum {
 
 /* faiss::MetricType values used at the reference call sites
  * (sph/NearestNeighbors.cpp:81-96): METRIC_INNER_PRODUCT = 0, METRIC_L2 = 1. */
-enum { SPHB_METRIC_INNER_PRODUCT = 0, SPHB_METRIC_L2 = 1 };
+enum { SPHB_METRIC_INNER_PRODUCT = 0, SPHB_METRIC_L2 = 1,
+       /* KnnMetric::COSINE (sph/utils/Settings.hpp; NearestNeighbors::setMetric + initFaissData, sph/NearestNeighbors.cpp:81-96, 208-222):
+        * not a faiss value — the back-end L2-normalises a device copy of the rows and searches it with the inner product */
+       SPHB_METRIC_COSINE = 2 };
 
 /* sph::utils::ImportanceWeighting (sph/utils/Settings.hpp, used at
  * sph/utils/SparseMatrixAlgorithms.cpp:137-161). */
@@ -89,6 +100,10 @@ SPHB_API int sphb_knn_exact_slab(const float* x, int64_t n, int d, int k, int me
                                  int64_t q0, int64_t q1, int64_t* ids, float* dist);
 SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared,
                                 int64_t q0, int64_t q1, int64_t* d_ids, float* d_dist, void* stream);
+/* faiss::fvec_renorm_L2 on a copy, the COSINE preparation of NearestNeighbors::initFaissData (sph/NearestNeighbors.cpp:208-222):
+ * out[i] = x[i] / sqrt(fp32 sum of x[i][c]^2 in column order); all-zero rows are copied.  (sphb_knn_exact* with
+ * SPHB_METRIC_COSINE does this on the device by itself; this entry point serves callers that keep the normalised copy.) */
+SPHB_API int sphb_renorm_l2(const float* x, int64_t n, int d, float* out);
 /* kNN statistics of the last call: [0] path (0 SIMT, 1 tcgen05 streaming, 2 tcgen05 resident MH=1,
  * 3 tcgen05 resident MH=2, 4 tcgen05 CTA pair (cta_group::2)), [1] candidate-list compactions, [2] candidates accepted by the filter,
  * [3] executed GEMM K extent per pair of the main sweep, [4] rows recomputed by the exact SIMT kernel
@@ -253,6 +268,15 @@ SPHB_API int sphb_rw_as_knn_distances(int64_t n, const int64_t* rowptr, const ui
 /* Zero removal of the level rows (sph/LevelSimilarities.cpp:566-581).  out_col/out_val: nnz. */
 SPHB_API int sphb_remove_zeros(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val,
                                int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t* out_nnz);
+/* The post-merge step of Hierarchy::updateRandomWalks (sph/utils/Hierarchy.cpp:287-307) on the merged walks:
+ * remove_diagonal != 0: removeDiagonalElements(keepSingleEntry = true) (sph/utils/SparseMatrixAlgorithms.cpp:704-718) — a row with more
+ * than one entry loses its diagonal and every stored exact zero; norm: 0 none, 1 NormType::ONEDIM (every row / its fp32 sum,
+ * normalizeUnitSparseVector :666-673), 2 NormType::TWODIM (every value / the fp32 sum over all rows, normalizeSparseMatrix :617-628).
+ * out_col / out_val: nnz of the input suffices. */
+SPHB_API int sphb_rw_post_merge(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int remove_diagonal, int norm,
+                                int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t* out_nnz);
+SPHB_API int sphb_rw_post_merge_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int remove_diagonal, int norm,
+                                    int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t* out_nnz, void* stream);
 /* Exact level kNN in a random-walk component metric — LevelSimilarities' computeExactKnn
  * (sph/LevelSimilarities.cpp:211-252) in NeighborWalksBhattacharyyaSpace (mode 0,
  * sph/utils/NeighborWalksBhattacharyyaSpace.hpp:28-41: distance 1 - randomWalksBhattacharyya(i, j)) or

@@ -19,6 +19,7 @@ _lib = None
 
 METRIC_INNER_PRODUCT = 0
 METRIC_L2 = 1
+METRIC_COSINE = 2
 W_CONSTANT, W_LINEAR, W_NORMAL, W_ONLYLAST, W_FIRST_VISIT = range(5)
 
 i64p = C.POINTER(C.c_int64)
@@ -40,6 +41,10 @@ SIGNATURES = {
     "sphb_knn_exact": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, i64p, f32p]),
     "sphb_knn_exact_slab": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, i64p, f32p]),
     "sphb_knn_exact_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sphb_renorm_l2": (C.c_int, [f32p, C.c_int64, C.c_int, f32p]),
+    "sphb_rw_post_merge": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int, i64p, u32p, f32p, i64p]),
+    "sphb_rw_post_merge_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, i64p,
+                                         C.c_void_p]),
     "sphb_knn_last_stats": (C.c_int, [i64p]),
     "sphb_knn_last_timing": (C.c_int, [f32p]),
     "sphb_knn_rows_noalloc_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
@@ -620,3 +625,28 @@ def knn_rows_noalloc_dev(x_ptr: int, n: int, d: int, k: int, metric: int, l2_squ
                          stream: int):
     """Exact kNN of a list of <= 256 query rows (k <= 128) with the library's fixed scratch: no device allocation."""
     _check(load().sphb_knn_rows_noalloc_dev(x_ptr, n, d, k, metric, int(l2_squared), rows_ptr, nrows, ids_ptr, dist_ptr, stream))
+
+
+def renorm_l2(x: np.ndarray) -> np.ndarray:
+    """COSINE preparation (faiss::fvec_renorm_L2 on a copy, sph/NearestNeighbors.cpp:208-222) on the device."""
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.empty_like(x)
+    _check(load().sphb_renorm_l2(_p(x, f32p), x.shape[0], x.shape[1], _p(out, f32p)))
+    return out
+
+
+def rw_post_merge(rowptr, col, val, remove_diagonal: bool, norm: int):
+    """Hierarchy::updateRandomWalks after the merge: diagonal / zero removal, then norm 0 none, 1 ONEDIM, 2 TWODIM."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    cap = max(1, len(col))
+    orp = np.zeros(n + 1, np.int64)
+    oc = np.zeros(cap, np.uint32)
+    ov = np.zeros(cap, np.float32)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_rw_post_merge(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), int(remove_diagonal), int(norm), _p(orp, i64p), _p(oc, u32p),
+                                     _p(ov, f32p), _p(nnz, i64p)))
+    m = int(nnz[0])
+    return orp, oc[:m].copy(), ov[:m].copy()

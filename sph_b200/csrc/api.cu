@@ -110,6 +110,35 @@ void walks_force_scan(int on);
 // 6 tc 1-pass (resident when d allows), 7 tc 1-pass streaming
 static int g_force_path = 0;
 
+// COSINE preparation (NearestNeighbors::initFaissData, sph/NearestNeighbors.cpp:208-222: copy + faiss::fvec_renorm_L2): one warp per
+// row; the squared norm is the fp32 sum of x[c] * x[c] taken in column order (the published faiss scalar loop) — the lanes hold
+// the row, the running sum is formed in order through shuffles.
+__global__ void renorm_l2_kernel(const float* __restrict__ x, int64_t n, int d, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const float* xr = x + r * d;
+        float nr = 0.f;
+        for (int c0 = 0; c0 < d; c0 += 32) {
+            const float v = c0 + lane < d ? xr[c0 + lane] : 0.f;
+            const float sq = __fmul_rn(v, v);
+            const int m = min(32, d - c0);
+            for (int t = 0; t < m; ++t) nr = __fadd_rn(nr, __shfl_sync(0xffffffffu, sq, t));
+        }
+        const float inv = nr > 0.f ? 1.0f / sqrtf(nr) : 1.f;
+        for (int c = lane; c < d; c += 32) out[r * d + c] = nr > 0.f ? __fmul_rn(xr[c], inv) : xr[c];
+    }
+}
+
+int renorm_l2_dev(const float* d_x, int64_t n, int d, float* d_out, cudaStream_t s) {
+    const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>((n * 32 + 255) / 256, static_cast<int64_t>(ctx().num_sms) * 16));
+    renorm_l2_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(d_x, n, d, d_out);
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
 }  // namespace sphb
 
 using namespace sphb;
@@ -176,9 +205,18 @@ SPHB_API int sphb_knn_exact_dev(const float* d_x, int64_t n, int d, int k, int m
                                 int64_t* d_ids, float* d_dist, void* stream) {
     if (int rc = ensure_init()) return rc;
     if (n <= 0 || d <= 0 || k <= 0 || q0 < 0 || q1 > n || q0 > q1) return fail(SPHB_ERR_INVALID, "knn: bad sizes");
-    if (metric != SPHB_METRIC_L2 && metric != SPHB_METRIC_INNER_PRODUCT) return fail(SPHB_ERR_INVALID, "knn: unknown metric");
+    if (metric != SPHB_METRIC_L2 && metric != SPHB_METRIC_INNER_PRODUCT && metric != SPHB_METRIC_COSINE) return fail(SPHB_ERR_INVALID, "knn: unknown metric");
     if (n >= (1ll << 32) - 1) return fail(SPHB_ERR_UNSUPPORTED, "knn: n must fit in uint32");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (metric == SPHB_METRIC_COSINE) {
+        // KnnMetric::COSINE (sph/NearestNeighbors.cpp:81-96, 208-222): rows L2-normalised into a device copy, then inner product
+        DevBuf<float> xn;
+        SPHB_CUDA(xn.alloc(static_cast<size_t>(n) * d, s));
+        if (int rc = renorm_l2_dev(d_x, n, d, xn.p, s)) return rc;
+        const int rc = sphb_knn_exact_dev(xn.p, n, d, k, SPHB_METRIC_INNER_PRODUCT, 0, q0, q1, d_ids, d_dist, stream);
+        SPHB_CUDA(cudaStreamSynchronize(s));  // the copy is released on return
+        return rc;
+    }
     bool use_tc = knn_tc_supported(n, d, k);
     if (g_force_path == 1) use_tc = false;
     if (g_force_path >= 2) {
@@ -213,6 +251,22 @@ SPHB_API int sphb_knn_exact_slab(const float* x, int64_t n, int d, int k, int me
 
 SPHB_API int sphb_knn_exact(const float* x, int64_t n, int d, int k, int metric, int l2_squared, int64_t* ids, float* dist) {
     return sphb_knn_exact_slab(x, n, d, k, metric, l2_squared, 0, n, ids, dist);
+}
+
+SPHB_API int sphb_renorm_l2(const float* x, int64_t n, int d, float* out) {
+    if (int rc = ensure_init()) return rc;
+    if (!x || !out || n < 0 || d <= 0) return fail(SPHB_ERR_INVALID, "renorm_l2: bad arguments");
+    if (n == 0) return SPHB_OK;
+    cudaStream_t s = g_ctx.stream;
+    DevBuf<float> dx, dout;
+    const size_t cnt = static_cast<size_t>(n) * d;
+    SPHB_CUDA(dx.alloc(cnt, s));
+    SPHB_CUDA(dout.alloc(cnt, s));
+    SPHB_CUDA(cudaMemcpyAsync(dx.p, x, cnt * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (int rc = renorm_l2_dev(dx.p, n, d, dout.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(out, dout.p, cnt * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
 }
 
 SPHB_API int sphb_knn_last_stats(int64_t* out8) {

@@ -461,6 +461,113 @@ int remove_zeros_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, 
 }
 
 // ---------------------------------------------------------------------------------------------
+// RW4: the post-merge step of Hierarchy::updateRandomWalks (sph/utils/Hierarchy.cpp:287-307):
+//   removeDiagonalElements(keepSingleEntry = true) (sph/utils/SparseMatrixAlgorithms.cpp:704-718) — a row with more than one
+//   entry loses its diagonal AND every stored exact zero (removeElement: coeffRef(i) = 0, then prune(0, eps)), then
+//   ONEDIM: every row / its fp32 storage-order sum (normalizeUnitSparseVector :666-673)
+//   TWODIM: every value / the fp32 sum of the row sums taken in row order (normalizeSparseMatrix :617-628).
+// ---------------------------------------------------------------------------------------------
+namespace {
+__global__ void rd_count(int64_t n, const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ col, const float* __restrict__ val, int remove,
+                         int64_t* __restrict__ cnt) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = warp; r <= n; r += nwarps) {
+        int c = 0;
+        if (r < n) {
+            const int64_t b = rowptr[r], e1 = rowptr[r + 1];
+            const bool strip = remove && e1 - b > 1;
+            for (int64_t e = b + lane; e < e1; e += 32) c += (strip && (static_cast<int64_t>(col[e]) == r || val[e] == 0.f)) ? 0 : 1;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        if (lane == 0) cnt[r] = c;
+    }
+}
+__global__ void rd_scatter(int64_t n, const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ col, const float* __restrict__ val, int remove,
+                           const int64_t* __restrict__ out_rowptr, uint32_t* __restrict__ out_col, float* __restrict__ out_val) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        int64_t out = out_rowptr[r];
+        const int64_t b = rowptr[r], end = rowptr[r + 1];
+        const bool strip = remove && end - b > 1;
+        for (int64_t base = b; base < end; base += 32) {
+            const int64_t e = base + lane;
+            const bool keep = e < end && !(strip && (static_cast<int64_t>(col[e]) == r || val[e] == 0.f));
+            const unsigned mask = __ballot_sync(0xffffffffu, keep);
+            if (keep) {
+                const int64_t o = out + __popc(mask & ((1u << lane) - 1u));
+                out_col[o] = col[e];
+                out_val[o] = val[e];
+            }
+            out += __popc(mask);
+        }
+    }
+}
+// fp32 storage-order sum of every row (Eigen SparseVector::sum()); ONEDIM divides in place
+__global__ void rd_row_sums(int64_t n, const int64_t* __restrict__ rowptr, float* __restrict__ val, int divide, float* __restrict__ sums) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const int64_t b = rowptr[r], e1 = rowptr[r + 1];
+        float sacc = 0.f;
+        if (lane == 0)
+            for (int64_t e = b; e < e1; ++e) sacc += val[e];
+        sacc = __shfl_sync(0xffffffffu, sacc, 0);
+        if (sums && lane == 0) sums[r] = sacc;
+        if (divide)
+            for (int64_t e = b + lane; e < e1; e += 32) val[e] = val[e] / sacc;
+    }
+}
+__global__ void rd_total(int64_t n, const float* __restrict__ sums, float* __restrict__ total) {  // one thread: the reference's row-order fp32 sum
+    float t = 0.f;
+    for (int64_t r = 0; r < n; ++r) t += sums[r];
+    *total = t;
+}
+__global__ void rd_scale(int64_t nnz, float* __restrict__ val, const float* __restrict__ total) {
+    const float t = *total;
+    for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < nnz; e += static_cast<int64_t>(gridDim.x) * blockDim.x) val[e] = val[e] / t;
+}
+}  // namespace
+
+// norm: 0 none, 1 ONEDIM, 2 TWODIM
+int rw_post_merge_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int remove_diagonal, int norm,
+                      int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t* out_nnz, cudaStream_t s) {
+    const int sms = ctx().num_sms;
+    DevBuf<int64_t> cnt;
+    SPHB_CUDA(cnt.alloc(n + 1, s));
+    rd_count<<<gm_grid((n + 1) * 32, 256, sms), 256, 0, s>>>(n, d_rowptr, d_col, d_val, remove_diagonal, cnt.p);
+    count_launch();
+    if (int rc = exclusive_sum<int64_t>(cnt.p, d_out_rowptr, n + 1, s)) return rc;
+    int64_t kept = 0;
+    SPHB_CUDA(cudaMemcpyAsync(&kept, d_out_rowptr + n, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    *out_nnz = kept;
+    if (kept == 0) return 0;
+    rd_scatter<<<gm_grid(n * 32, 256, sms), 256, 0, s>>>(n, d_rowptr, d_col, d_val, remove_diagonal, d_out_rowptr, d_out_col, d_out_val);
+    count_launch();
+    if (norm == 1) {
+        rd_row_sums<<<gm_grid(n * 32, 256, sms), 256, 0, s>>>(n, d_out_rowptr, d_out_val, 1, nullptr);
+        count_launch();
+    } else if (norm == 2) {
+        DevBuf<float> sums, total;
+        SPHB_CUDA(sums.alloc(n, s));
+        SPHB_CUDA(total.alloc(1, s));
+        rd_row_sums<<<gm_grid(n * 32, 256, sms), 256, 0, s>>>(n, d_out_rowptr, d_out_val, 0, sums.p);
+        rd_total<<<1, 1, 0, s>>>(n, sums.p, total.p);
+        rd_scale<<<gm_grid(kept, 256, sms), 256, 0, s>>>(kept, d_out_val, total.p);
+        count_launch(3);
+        SPHB_CUDA(cudaStreamSynchronize(s));  // sums / total are released on return
+    }
+    SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // D6: symmetric Hausdorff distance between the pixel sets of two components, one CTA per pair.
 // Every pixel-pair distance is the Stage-A contract distance (fp64 FMA chain, one rounding, sqrtf), so a pair of
 // single-pixel components is the plain L2 distance of the level-0 branch.  The distance matrix is never stored: the
@@ -1192,6 +1299,44 @@ SPHB_API int sphb_remove_zeros(int64_t n, const int64_t* rowptr, const uint32_t*
     SPHB_CUDA(cudaStreamSynchronize(s));
     *out_nnz = m;
     return SPHB_OK;
+}
+
+SPHB_API int sphb_rw_post_merge(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int remove_diagonal, int norm,
+                                int64_t* out_rowptr, uint32_t* out_col, float* out_val, int64_t* out_nnz) {
+    if (int rc = ensure_init()) return rc;
+    if (!rowptr || !out_rowptr || !out_nnz || n < 0 || norm < 0 || norm > 2) return fail(SPHB_ERR_INVALID, "rw_post_merge: bad arguments");
+    *out_nnz = 0;
+    if (n == 0) return SPHB_OK;
+    cudaStream_t s = ctx().stream;
+    const int64_t nnz = rowptr[n];
+    DevBuf<int64_t> drp, orp;
+    DevBuf<uint32_t> dcol, oc;
+    DevBuf<float> dval, ov;
+    if (int rc = up(drp, rowptr, n + 1, s)) return rc;
+    if (int rc = up(dcol, col, nnz, s)) return rc;
+    if (int rc = up(dval, val, nnz, s)) return rc;
+    SPHB_CUDA(orp.alloc(n + 1, s));
+    SPHB_CUDA(oc.alloc(std::max<int64_t>(nnz, 1), s));
+    SPHB_CUDA(ov.alloc(std::max<int64_t>(nnz, 1), s));
+    int64_t m = 0;
+    if (int rc = rw_post_merge_dev(n, drp.p, dcol.p, dval.p, remove_diagonal, norm, orp.p, oc.p, ov.p, &m, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(out_rowptr, orp.p, (n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    if (m > 0) {
+        SPHB_CUDA(cudaMemcpyAsync(out_col, oc.p, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        SPHB_CUDA(cudaMemcpyAsync(out_val, ov.p, m * sizeof(float), cudaMemcpyDeviceToHost, s));
+    }
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    *out_nnz = m;
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_rw_post_merge_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int remove_diagonal, int norm,
+                                    int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t* out_nnz, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (!d_rowptr || !d_out_rowptr || !out_nnz || n < 0 || norm < 0 || norm > 2) return fail(SPHB_ERR_INVALID, "rw_post_merge_dev: bad arguments");
+    *out_nnz = 0;
+    if (n == 0) return SPHB_OK;
+    return rw_post_merge_dev(n, d_rowptr, d_col, d_val, remove_diagonal, norm, d_out_rowptr, d_out_col, d_out_val, out_nnz, static_cast<cudaStream_t>(stream));
 }
 
 SPHB_API int sphb_level_knn_walks(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int mode, int64_t k, int64_t* out_ids,

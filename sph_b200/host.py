@@ -219,7 +219,7 @@ class NearestNeighbors:
         if s.knnMetric in (KnnMetric.COSINE, KnnMetric.INNER_PRODUCT):
             metric, l2sq = 0, False  # setMetric: IP / COSINE force L2squared = false (:81-96)
             if s.knnMetric == KnnMetric.COSINE:
-                x = renorm_l2(x)
+                metric = 2  # SPHB_METRIC_COSINE: the back-end normalises a device copy of the rows (initFaissData) and searches by inner product
         q0, q1 = shard_rows(n, world)[rank]
         try:
             ids, dist = self._knn(x, int(s.numNearestNeighbors), metric, l2sq, q0, q1)
@@ -285,6 +285,8 @@ class NearestNeighbors:
 
     def _knn(self, x, k, metric, l2sq, q0, q1):
         if self._knn_fn is not None:
+            if metric == 2:  # an injected search (tests: the CPU oracle) gets the normalised copy + inner product, as faiss does
+                x, metric = renorm_l2(x), 0
             return self._knn_fn(x, k, metric, l2sq, q0, q1)
         from . import capi
 
@@ -654,6 +656,11 @@ class DeviceOps:
     def rw_merge(self, walks: SparseRows, parents, n_merged: int, norm: bool, weight_by_size: bool) -> SparseRows:
         return mergeNodesRandomWalks(walks, n_merged, parents, norm, weight_by_size)
 
+    def rw_post_merge(self, merged: SparseRows, remove_diagonal: bool, norm) -> SparseRows:
+        from . import capi
+
+        return SparseRows(*capi.rw_post_merge(merged.rowptr, merged.col, merged.val, remove_diagonal, 1 if norm == NormType.ONEDIM else 2))
+
     def pair_sims(self, walks: SparseRows, pa, pb, mode: int) -> np.ndarray:
         from . import capi
 
@@ -746,7 +753,7 @@ def removeDiagonalAndNormalize(m: SparseRows, remove_diagonal: bool, norm: NormT
     for i in range(m.n):
         c, v = m.row(i)
         if remove_diagonal and len(c) > 1:
-            keep = c != i
+            keep = (c != i) & (v != 0)  # removeElement: coeffRef(i) = 0, then prune(0, eps) drops every exact zero of the row
             c, v = c[keep], v[keep]
         cols.append(c)
         vals.append(np.array(v, np.float32))
@@ -989,7 +996,7 @@ class ImageHierarchy:
         else:
             merged = self._ops.rw_merge(self.randomWalks[-1], self.parents[-1], n_next, False, s.rwWeightMergeBySize)
             remove = s.rwRemoveSelfSimAfterMerging and merged.n > 1 and s.rwHandling != RandomWalkHandling.MERGE_RW_ONLY
-            merged = removeDiagonalAndNormalize(merged, remove, s.rwNormSim)
+            merged = self._ops.rw_post_merge(merged, remove, s.rwNormSim)
         if s.rwHandling == RandomWalkHandling.MERGE_RW_ONLY:
             out = merged
         else:

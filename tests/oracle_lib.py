@@ -483,6 +483,11 @@ class OracleOps:
 
         return host.SparseRows(*self.o.rw_merge(walks.rowptr, walks.col, walks.val, parents, n_merged, norm, weight_by_size))
 
+    def rw_post_merge(self, merged, remove_diagonal, norm):
+        from sph_b200 import host
+
+        return host.removeDiagonalAndNormalize(merged, remove_diagonal, norm)
+
     def pair_sims(self, walks, pa, pb, mode):
         return self.o.pair_sims(walks.rowptr, walks.col, walks.val, pa, pb, mode)
 

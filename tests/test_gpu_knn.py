@@ -192,3 +192,20 @@ def test_invalid_arguments(capi):
         capi.knn_exact(x, 0)
     with pytest.raises(capi.SphbError):
         capi.knn_exact(x, 3, q0=5, q1=20)
+
+
+def test_cosine_metric_on_device(capi, oracle):
+    """KnnMetric::COSINE: the back-end normalises a device copy of the rows (initFaissData, sph/NearestNeighbors.cpp:208-222) and
+    searches by inner product; the normalised copy is bit-identical to the oracle's fvec_renorm_L2 restatement."""
+    import ctypes as C
+
+    rng = np.random.default_rng(77)
+    x = (rng.standard_normal((3000, 40)) * rng.uniform(0.1, 10, (3000, 1))).astype(np.float32)
+    x[17] = 0  # all-zero row: copied unchanged
+    ref = np.empty_like(x)
+    oracle.lib.orc_renorm_l2(x.ctypes.data_as(C.POINTER(C.c_float)), x.shape[0], x.shape[1], ref.ctypes.data_as(C.POINTER(C.c_float)))
+    np.testing.assert_array_equal(capi.renorm_l2(x), ref)
+    ids, dist = capi.knn_exact(x, 21, metric=capi.METRIC_COSINE)
+    rids, rdist = oracle.knn_reference_graph(ref, 21, metric=0)
+    np.testing.assert_array_equal(ids, rids)
+    np.testing.assert_array_equal(dist, rdist)

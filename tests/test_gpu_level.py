@@ -215,3 +215,21 @@ def test_dev_entry_points_match_host(capi):
     np.testing.assert_array_equal(prp_.cpu().numpy(), hp[0])
     np.testing.assert_array_equal(pc_[:pm].cpu().numpy().view(np.uint32), hp[1])
     np.testing.assert_array_equal(pv_[:pm].cpu().numpy(), hp[2])
+
+
+@pytest.mark.parametrize("norm", [1, 2])
+@pytest.mark.parametrize("remove", [True, False])
+def test_rw_post_merge_matches_host_restatement(capi, norm, remove):
+    """RW4 after the merge (Hierarchy::updateRandomWalks, sph/utils/Hierarchy.cpp:287-307): diagonal + exact-zero removal with
+    keepSingleEntry, ONEDIM / TWODIM normalisation in the reference's fp32 summation order — against the literal host loop."""
+    from sph_b200 import host
+
+    rp, c, v = walk_like_rows(700, seed=91, lo=1, hi=40, window=30)
+    v = v.copy()
+    v[::17] = 0.0                      # stored zeros (removed together with the diagonal in rows with > 1 entries)
+    rows = host.SparseRows(rp, c, v)
+    want = host.removeDiagonalAndNormalize(rows, remove, host.NormType.ONEDIM if norm == 1 else host.NormType.TWODIM)
+    got = capi.rw_post_merge(rp, c, v, remove, norm)
+    np.testing.assert_array_equal(got[0], want.rowptr)
+    np.testing.assert_array_equal(got[1], want.col)
+    np.testing.assert_array_equal(got[2], want.val)
