@@ -169,6 +169,26 @@ SPHB_API int sphb_prow_gaussian_inplace(int64_t n, const int64_t* rowptr, float*
 /* utils::computeGaussianDistributions(dist², idx, nn, rows, params) flat variant
  *   (sph/utils/HDILibHelper.hpp:112-140; tol 1e-5): fills temp[n*k]; the caller scatters. */
 SPHB_API int sphb_prow_gaussian_flat(const float* dist, int64_t n, int k, double perplexity, float* temp);
+/* SURVEY 8(f)-3 — utils::computeExponentialDistributions (sph/utils/GraphNormalization.hpp:29-32, .cpp:413-593): the
+ * UMAP-flavoured rows (NormalizationScheme::UMAP, sph/LevelSimilarities.cpp:499-503,532-533).  The reference passes each
+ * row to umappp::neighbor_similarities (libscran-umappp 3.2.0, default options, fp32): rho = first non-zero distance,
+ * sigma from sum_j [d_j > rho ? exp(-(d_j - rho)/sigma) : 1] = log2(n_neighbours + 1) (|sum - target| < 1e-5, <= 64
+ * evaluations), sigma >= 1e-3 * mean(d), w_j = d_j > rho ? exp(-(d_j - rho)/sigma) : 1.  umappp is not part of the
+ * reference tree, so the arithmetic follows the published algorithm; results agree with any conforming implementation to
+ * the search tolerance (parity unpinned).
+ *  _graph: (graphView, rows) overload (.cpp:508-593) on a fixed-k graph, neighbour 0 (the point itself) skipped; cols/vals:
+ *          n*(k-1); sort_cols = 0 keeps the neighbour order (T = MapMemEff, storage.emplace_back .cpp:566-569), 1 sorts each
+ *          row by column (T = SparseVecSPH, insert .cpp:559-562).
+ *  _inplace: (rows, ignore) overload (.cpp:413-506) on CSR rows, values overwritten; an entry whose COLUMN equals `ignore`
+ *          (>= 0; the reference calls it with -1) is left out of the row and keeps its value; col may be NULL when ignore < 0.
+ *          Rows of at most 1024 entries. */
+SPHB_API int sphb_prow_exponential_graph(const int64_t* ids, const float* dist, int64_t n, int k, int sort_cols,
+                                         uint32_t* cols, float* vals);
+SPHB_API int sphb_prow_exponential_graph_dev(const int64_t* d_ids, const float* d_dist, int64_t n, int k, int sort_cols,
+                                             uint32_t* d_cols, float* d_vals, void* stream);
+SPHB_API int sphb_prow_exponential_inplace(int64_t n, const int64_t* rowptr, const uint32_t* col, float* val, int ignore);
+SPHB_API int sphb_prow_exponential_inplace_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, float* d_val,
+                                               int max_row_nnz, int ignore, void* stream);
 /* utils::symmetrizeTSNE / symmetrizeUMAP (sph/utils/HDILibHelper.hpp:260-302).
  * out_* capacity `cap` entries (2*nnz always suffices); *out_nnz receives the size. */
 SPHB_API int sphb_symmetrize(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int umap,
@@ -245,6 +265,29 @@ SPHB_API int sphb_symmetrize_graph(int64_t n, const int64_t* rowptr, int k, cons
  * every point, components numbered in ascending order of their lowest point (the order Boost reaches them);
  * *num_components receives their number. */
 SPHB_API int sphb_weak_components(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, int64_t* labels, int64_t* num_components);
+/* SURVEY 8(f)-2 — component bridging, the device parts of NearestNeighbors::connectComponents
+ * (sph/NearestNeighbors.cpp:494-861; forced by GEO_CENTROID configurations, sph/ComputeHierarchy.cpp:41-42).
+ * labels[n] in [0, num_components) as sphb_weak_components writes them.
+ *  sphb_component_centers: centre of mass of every component (computeCentersOfMass :655-680 with utils::computeMean,
+ *    sph/utils/Math.hpp:29-48): fp64 sums in ascending point order, divided by the count, rounded to fp32 — bit-identical
+ *    to the reference's sequential sums.  centers: num_components * d.
+ *  sphb_bridge_components: for every edge (edges[2e] = component A, edges[2e+1] = component B — the source and target of
+ *    an edge of the minimum spanning tree the host builds over the centres, :682-708) the pair the reference connects
+ *    (insertConnectionsBetweenComponents :592-653): for every point of B its nearest point of A, then the closest such
+ *    pair; ids_a[e] / ids_b[e] = global point ids, dist[e] = their SQUARED L2 distance (what faiss::IndexFlat returns and
+ *    the reference inserts into the graph as is).  Exact: ties resolve to the lowest point of B, then of A.  The reference
+ *    switches to the approximate IndexIVFFlat (nlist 100, nprobe 10) when A holds more than 3900 points (:607-626); this
+ *    entry point is exact at every size, so its distance is <= the reference's there.  Only SPHB_METRIC_L2.
+ *    The host keeps the MST (Kruskal over num_components^2 / 2 centre distances) and the row insertions (:547-572);
+ *    sph_b200/host.py NearestNeighbors.connectComponents is that mirror.  `edges` is always a HOST array. */
+SPHB_API int sphb_component_centers(const float* x, int64_t n, int d, const int64_t* labels, int64_t num_components, float* centers);
+SPHB_API int sphb_component_centers_dev(const float* d_x, int64_t n, int d, const int64_t* d_labels, int64_t num_components,
+                                        float* d_centers, void* stream);
+SPHB_API int sphb_bridge_components(const float* x, int64_t n, int d, int metric, const int64_t* labels, int64_t num_components,
+                                    const int64_t* edges, int64_t num_edges, int64_t* ids_a, int64_t* ids_b, float* dist);
+SPHB_API int sphb_bridge_components_dev(const float* d_x, int64_t n, int d, int metric, const int64_t* d_labels,
+                                        int64_t num_components, const int64_t* edges, int64_t num_edges, int64_t* d_ids_a,
+                                        int64_t* d_ids_b, float* d_dist, void* stream);
 /* Device-pointer variant (graph resident in HBM, e.g. straight from sphb_knn_exact_dev); d_rowptr may be NULL for a
  * fixed-k graph, nnz = number of stored entries; *out_nnz is written on the host (one stream synchronisation). */
 SPHB_API int sphb_symmetrize_graph_dev(int64_t n, const int64_t* d_rowptr, int k, const int64_t* d_ids, const float* d_dist, int64_t nnz,

@@ -320,3 +320,55 @@ ORC_API int64_t orc_weak_components(int64_t n, const int64_t* rowptr, const int6
     }
     return next;
 }
+
+// F3.  Component bridging, NearestNeighbors::connectComponents (sph/NearestNeighbors.cpp:494-861) — the two loops the device
+// replaces, restated literally (sequential, brute force).
+// computeCentersOfMass (:655-680) with utils::computeMean (sph/utils/Math.hpp:29-48): fp64 sums over the component's points
+// in ascending id order (getComponentValues :574-590), / count, cast to float.
+ORC_API void orc_component_centers(const float* x, int64_t n, int d, const int64_t* labels, int64_t ncomp, float* centers) {
+    std::vector<double> sum(static_cast<size_t>(ncomp) * d, 0.0);
+    std::vector<int64_t> cnt(static_cast<size_t>(ncomp), 0);
+    for (int64_t i = 0; i < n; ++i) {
+        const int64_t c = labels[i];
+        ++cnt[c];
+        for (int t = 0; t < d; ++t) sum[c * d + t] += static_cast<double>(x[i * d + t]);
+    }
+    for (int64_t c = 0; c < ncomp; ++c)
+        for (int t = 0; t < d; ++t) centers[c * d + t] = cnt[c] ? static_cast<float>(sum[c * d + t] / static_cast<double>(cnt[c])) : 0.f;
+}
+
+// insertConnectionsBetweenComponents (:592-653) with an exact per-point search (faiss::IndexFlat, the npA <= 3900 branch :607-616;
+// the distance of a pair is the Stage-A contract value: fp64 FMA chain rounded once to fp32, squared L2 as faiss returns it):
+// for every point of B (ascending id) its nearest point of A (ties: lowest id), then the first B point with the strictly
+// smallest distance (:628-636).
+ORC_API void orc_bridge_components(const float* x, int64_t n, int d, const int64_t* labels, const int64_t* edges, int64_t m, int64_t* ids_a,
+                                   int64_t* ids_b, float* dist) {
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t e = 0; e < m; ++e) {
+        const int64_t ca = edges[2 * e], cb = edges[2 * e + 1];
+        std::vector<int64_t> A, B;
+        for (int64_t i = 0; i < n; ++i) {
+            if (labels[i] == ca) A.push_back(i);
+            if (labels[i] == cb) B.push_back(i);
+        }
+        float best = std::numeric_limits<float>::max();
+        int64_t ba = -1, bb = -1;
+        for (int64_t b : B) {
+            float nearest = std::numeric_limits<float>::infinity();
+            int64_t na = -1;
+            for (int64_t a : A) {
+                double acc = 0.0;
+                for (int c = 0; c < d; ++c) {
+                    const double diff = static_cast<double>(x[b * d + c]) - static_cast<double>(x[a * d + c]);
+                    acc = std::fma(diff, diff, acc);
+                }
+                const float v = static_cast<float>(acc);
+                if (v < nearest) { nearest = v; na = a; }
+            }
+            if (nearest < best) { best = nearest; ba = na; bb = b; }
+        }
+        ids_a[e] = ba;
+        ids_b[e] = bb;
+        dist[e] = best;
+    }
+}

@@ -7,6 +7,7 @@
 //   B5 sph/utils/GraphNormalization.cpp:340-411  linear rows
 //   B6 sph/utils/HDILibHelper.hpp:260-302        symmetrizeTSNE / symmetrizeUMAP
 //   B8 sph/LevelSimilarities.cpp:83-115          k / perplexity schedule
+//   §8(f)-3 sph/utils/GraphNormalization.cpp:413-593  exponential (UMAP) rows — parity unpinned, see below
 #include "oracle_common.hpp"
 
 #include <algorithm>
@@ -239,5 +240,86 @@ ORC_API void orc_level_schedule(const int64_t* level_sizes, int num_levels, int6
         pl = std::min(dataPerplexity, pl);
         perplexities[l] = pl;
         ks[l] = std::min<int64_t>(static_cast<int64_t>(pl) * 3 + 1, level_sizes[l]);
+    }
+}
+
+// ---- §8(f)-3: UMAP-flavoured rows -------------------------------------------------------------------------------------
+// utils::computeExponentialDistributions (sph/utils/GraphNormalization.cpp:413-593) hands each row to
+// umappp::neighbor_similarities (libscran-umappp 3.2.0, vcpkg.json:146-147; NOT vendored under /root/reference and absent
+// from this image) with default options: local_connectivity 1, bandwidth 1, Float_ = float (NeighborList<int64_t, float>,
+// :418,514).  PARITY UNPINNED for the arithmetic below: the reference holds no golden vector for these rows and the
+// library source is not available here, so this is a restatement of the published algorithm the library implements
+// (UMAP's smooth_knn_dist, McInnes et al. 2018 Alg. 3 + the reference Python implementation's constants):
+//   rho    = distance of the first neighbour with a non-zero distance (local_connectivity = 1: index 1, no interpolation),
+//            0 when all distances are zero;
+//   sigma  = root of  sum_j [ d_j > rho ? exp(-(d_j - rho) / sigma) : 1 ] = log2(n_neighbours + 1) * bandwidth
+//            (the +1 is the point itself, which the neighbour list does not hold), found from sigma = 1 by doubling while no
+//            upper bound is known and bisection afterwards, at most 64 evaluations, stop at |sum - target| < 1e-5;
+//   sigma  = max(sigma, 1e-3 * mean of the row's distances)        (min_k_dist_scale);
+//   w_j    = d_j > rho ? exp(-(d_j - rho) / sigma) : 1.
+// All arithmetic in fp32 like the library's Float_.  Any conforming implementation (umappp refines the same root with
+// Newton steps inside the same bracket) agrees with this to the search tolerance, not bit for bit; tests compare the CUDA
+// kernel with THIS function at rtol 1e-4 and check the defining equation sum_j w_j = log2(n + 1) directly.
+static void umap_row_weights(const float* dist, float* out, int nn) {
+    if (nn <= 0) return;
+    float rho = 0.f;
+    for (int j = 0; j < nn; ++j)
+        if (dist[j] != 0.f) { rho = dist[j]; break; }
+    int num_le = 0;
+    float total = 0.f;
+    for (int j = 0; j < nn; ++j) { num_le += !(dist[j] > rho); total += dist[j]; }
+    if (num_le == nn) {
+        for (int j = 0; j < nn; ++j) out[j] = 1.f;
+        return;
+    }
+    const float target = std::log2(static_cast<float>(nn + 1));
+    constexpr float fmax = std::numeric_limits<float>::max();
+    float sigma = 1.f, lo = 0.f, hi = fmax;
+    for (int iter = 0; iter < 64; ++iter) {
+        float val = static_cast<float>(num_le);
+        for (int j = 0; j < nn; ++j)
+            if (dist[j] > rho) val += std::exp(-(dist[j] - rho) / sigma);
+        if (std::fabs(val - target) < 1e-5f) break;
+        if (val > target) { hi = sigma; sigma = (lo + hi) / 2.f; }
+        else { lo = sigma; sigma = (hi == fmax) ? sigma * 2.f : (lo + hi) / 2.f; }
+    }
+    sigma = std::max(sigma, 1e-3f * (total / static_cast<float>(nn)));
+    for (int j = 0; j < nn; ++j) out[j] = dist[j] > rho ? std::exp(-(dist[j] - rho) / sigma) : 1.f;
+}
+
+// computeExponentialDistributions(const GraphBaseInterface&, vector<T>&) (GraphNormalization.cpp:508-593): neighbours 1..k-1
+// of every point (the point itself, neighbour 0, is skipped :523), weights stored in NEIGHBOUR order for T = MapMemEff
+// (storage.emplace_back :566-569; sort_cols = 0) and in column order for T = SparseVecSPH (insert :559-562; sort_cols = 1).
+ORC_API void orc_prow_exponential_graph(const int64_t* ids, const float* dist, int64_t n, int k, int sort_cols, uint32_t* out_cols,
+                                        float* out_vals) {
+    const int ne = k - 1;
+#pragma omp parallel for schedule(static)
+    for (int64_t p = 0; p < n; ++p) {
+        std::vector<float> w(static_cast<size_t>(std::max(ne, 0)));
+        umap_row_weights(dist + p * k + 1, w.data(), ne);
+        std::vector<std::pair<uint32_t, float>> row(w.size());
+        for (int t = 0; t < ne; ++t) row[t] = {static_cast<uint32_t>(ids[p * k + 1 + t]), w[t]};
+        if (sort_cols) std::stable_sort(row.begin(), row.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+        for (int t = 0; t < ne; ++t) { out_cols[p * ne + t] = row[t].first; out_vals[p * ne + t] = row[t].second; }
+    }
+}
+
+// computeExponentialDistributions(vector<T>&, int ignore) in place on sparse rows (GraphNormalization.cpp:413-506): the
+// entries of a row in STORED (column) order are the "neighbours" (:430-447; they are not sorted by value, so rho is the first
+// non-zero stored value), an entry whose COLUMN equals `ignore` is left out and keeps its value (SparseVecSPH write-back by
+// id :472-475).  Called with ignore = -1 (sph/LevelSimilarities.cpp:502).
+ORC_API void orc_prow_exponential_inplace(int64_t n, const int64_t* rowptr, const uint32_t* col, float* val, int ignore) {
+#pragma omp parallel for schedule(static)
+    for (int64_t p = 0; p < n; ++p) {
+        std::vector<float> d, w;
+        std::vector<int64_t> pos;
+        for (int64_t e = rowptr[p]; e < rowptr[p + 1]; ++e) {
+            if (ignore >= 0 && col && col[e] == static_cast<uint32_t>(ignore)) continue;
+            d.push_back(val[e]);
+            pos.push_back(e);
+        }
+        w.resize(d.size());
+        umap_row_weights(d.data(), w.data(), static_cast<int>(d.size()));
+        for (size_t t = 0; t < d.size(); ++t) val[pos[t]] = w[t];
     }
 }

@@ -56,6 +56,15 @@ SIGNATURES = {
     "sphb_prow_linear_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, u32p, f32p]),
     "sphb_prow_gaussian_inplace": (C.c_int, [C.c_int64, i64p, f32p, C.c_float, C.c_int]),
     "sphb_prow_gaussian_flat": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_double, f32p]),
+    "sphb_component_centers": (C.c_int, [f32p, C.c_int64, C.c_int, i64p, C.c_int64, f32p]),
+    "sphb_component_centers_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "sphb_bridge_components": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, i64p, C.c_int64, i64p, C.c_int64, i64p, i64p, f32p]),
+    "sphb_bridge_components_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_int64, i64p, C.c_int64, C.c_void_p,
+                                             C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sphb_prow_exponential_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, C.c_int, u32p, f32p]),
+    "sphb_prow_exponential_graph_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sphb_prow_exponential_inplace": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int]),
+    "sphb_prow_exponential_inplace_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "sphb_symmetrize": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
     "sphb_random_walks": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_uint64, C.c_uint64, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
                                     C.c_int, C.c_int, i64p, u32p, f32p, C.c_int64, i64p]),
@@ -255,6 +264,34 @@ def prow_gaussian_inplace(rowptr: np.ndarray, val: np.ndarray, perplexity: float
     return out
 
 
+def prow_exponential_graph(ids: np.ndarray, dist: np.ndarray, sort_cols: bool = False):
+    """utils::computeExponentialDistributions(graph, rows): UMAP membership rows of neighbours 1..k-1 -> (cols, vals) [n, k-1]."""
+    ids = np.ascontiguousarray(ids, np.int64)
+    dist = np.ascontiguousarray(dist, np.float32)
+    n, k = ids.shape
+    cols = np.zeros((n, k - 1), np.uint32)
+    vals = np.zeros((n, k - 1), np.float32)
+    _check(load().sphb_prow_exponential_graph(_p(ids, i64p), _p(dist, f32p), n, k, int(sort_cols), _p(cols, u32p), _p(vals, f32p)))
+    return cols, vals
+
+
+def prow_exponential_graph_dev(ids_ptr: int, dist_ptr: int, n: int, k: int, sort_cols: bool, cols_ptr: int, vals_ptr: int, stream: int):
+    _check(load().sphb_prow_exponential_graph_dev(ids_ptr, dist_ptr, n, k, int(sort_cols), cols_ptr, vals_ptr, stream))
+
+
+def prow_exponential_inplace(rowptr: np.ndarray, val: np.ndarray, col: np.ndarray | None = None, ignore: int = -1) -> np.ndarray:
+    """utils::computeExponentialDistributions(rows, ignore) on CSR rows; returns the new values."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    out = np.array(val, np.float32, copy=True)
+    colp = _p(np.ascontiguousarray(col, np.uint32), u32p) if col is not None else None
+    _check(load().sphb_prow_exponential_inplace(len(rowptr) - 1, _p(rowptr, i64p), colp, _p(out, f32p), ignore))
+    return out
+
+
+def prow_exponential_inplace_dev(n, rowptr_ptr, col_ptr, val_ptr, max_row_nnz, ignore, stream):
+    _check(load().sphb_prow_exponential_inplace_dev(n, rowptr_ptr, col_ptr, val_ptr, max_row_nnz, ignore, stream))
+
+
 def prow_gaussian_flat(dist: np.ndarray, perplexity: float) -> np.ndarray:
     dist = np.ascontiguousarray(dist, np.float32)
     n, k = dist.shape
@@ -394,6 +431,31 @@ def _graph_args(rowptr, ids, dist):
         return n, None, k, ids, dist
     rowptr = np.ascontiguousarray(rowptr, np.int64)
     return len(rowptr) - 1, rowptr, 0, ids, dist
+
+
+def component_centers(x: np.ndarray, labels: np.ndarray, num_components: int) -> np.ndarray:
+    """Centre of mass of every connected component (connectComponents' computeCentersOfMass): [num_components, d] float32."""
+    x = np.ascontiguousarray(x, np.float32)
+    labels = np.ascontiguousarray(labels, np.int64)
+    n, d = x.shape
+    centers = np.zeros((num_components, d), np.float32)
+    _check(load().sphb_component_centers(_p(x, f32p), n, d, _p(labels, i64p), num_components, _p(centers, f32p)))
+    return centers
+
+
+def bridge_components(x: np.ndarray, labels: np.ndarray, num_components: int, edges: np.ndarray, metric: int = METRIC_L2):
+    """Closest pair (point of A, point of B, squared L2) for every (component A, component B) edge: (ids_a, ids_b, dist)."""
+    x = np.ascontiguousarray(x, np.float32)
+    labels = np.ascontiguousarray(labels, np.int64)
+    edges = np.ascontiguousarray(edges, np.int64).reshape(-1, 2)
+    n, d = x.shape
+    m = len(edges)
+    ia = np.full(m, -1, np.int64)
+    ib = np.full(m, -1, np.int64)
+    dist = np.zeros(m, np.float32)
+    _check(load().sphb_bridge_components(_p(x, f32p), n, d, metric, _p(labels, i64p), num_components, _p(edges, i64p), m, _p(ia, i64p),
+                                         _p(ib, i64p), _p(dist, f32p)))
+    return ia, ib, dist
 
 
 def symmetrize_graph(ids, dist, rowptr=None):

@@ -103,6 +103,10 @@ const std::vector<int64_t>& knn_overflow_rows(int which);
 int prow_graph_launch(const int64_t*, const float*, int64_t, int, float, int, uint32_t*, float*, double*, cudaStream_t);
 int prow_inplace_launch(int64_t, const int64_t*, float*, int, float, int, cudaStream_t);
 int prow_flat_launch(const float*, int64_t, int, double, float*, cudaStream_t);
+int component_centers_dev(const float*, int64_t, int, const int64_t*, int64_t, float*, cudaStream_t);
+int bridge_components_dev(const float*, int64_t, int, const int64_t*, int64_t, const int64_t*, int64_t, int64_t*, int64_t*, float*, cudaStream_t);
+int prow_exponential_graph_launch(const int64_t*, const float*, int64_t, int, int, uint32_t*, float*, cudaStream_t);
+int prow_exponential_inplace_launch(int64_t, const int64_t*, const uint32_t*, float*, int, int, cudaStream_t);
 void sims_force_slab(int on);
 void walks_force_scan(int on);
 
@@ -377,6 +381,134 @@ SPHB_API int sphb_prow_gaussian_inplace(int64_t n, const int64_t* rowptr, float*
     SPHB_CUDA(cudaMemcpyAsync(drp.p, rowptr, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
     SPHB_CUDA(cudaMemcpyAsync(dval.p, val, nnz * sizeof(float), cudaMemcpyHostToDevice, s));
     if (int rc = prow_inplace_launch(n, drp.p, dval.p, static_cast<int>(max_nnz), perplexity, ignore, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(val, dval.p, nnz * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+// §8(f)-2: NearestNeighbors::connectComponents (sph/NearestNeighbors.cpp:494-861), device parts
+SPHB_API int sphb_component_centers_dev(const float* d_x, int64_t n, int d, const int64_t* d_labels, int64_t num_components, float* d_centers,
+                                        void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || d <= 0 || num_components < 0 || (n > 0 && (!d_x || !d_labels)) || (num_components > 0 && !d_centers))
+        return fail(SPHB_ERR_INVALID, "component_centers_dev: bad arguments");
+    if (num_components > 0x7fffffff) return fail(SPHB_ERR_UNSUPPORTED, "component_centers: more than 2^31 - 1 components");
+    return component_centers_dev(d_x, n, d, d_labels, num_components, d_centers, static_cast<cudaStream_t>(stream));
+}
+
+SPHB_API int sphb_bridge_components_dev(const float* d_x, int64_t n, int d, int metric, const int64_t* d_labels, int64_t num_components,
+                                        const int64_t* edges, int64_t num_edges, int64_t* d_ids_a, int64_t* d_ids_b, float* d_dist, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || d <= 0 || num_components < 0 || num_edges < 0 || (n > 0 && (!d_x || !d_labels)) ||
+        (num_edges > 0 && (!edges || !d_ids_a || !d_ids_b || !d_dist)))
+        return fail(SPHB_ERR_INVALID, "bridge_components_dev: bad arguments");
+    if (metric != SPHB_METRIC_L2) return fail(SPHB_ERR_UNSUPPORTED, "bridge_components: only SPHB_METRIC_L2 (squared distances, as faiss returns them)");
+    return bridge_components_dev(d_x, n, d, d_labels, num_components, edges, num_edges, d_ids_a, d_ids_b, d_dist, static_cast<cudaStream_t>(stream));
+}
+
+SPHB_API int sphb_component_centers(const float* x, int64_t n, int d, const int64_t* labels, int64_t num_components, float* centers) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || d <= 0 || num_components < 0 || (n > 0 && (!x || !labels)) || (num_components > 0 && !centers))
+        return fail(SPHB_ERR_INVALID, "component_centers: bad arguments");
+    if (num_components == 0) return SPHB_OK;
+    cudaStream_t s = g_ctx.stream;
+    DevBuf<float> dx, dc;
+    DevBuf<int64_t> dl;
+    SPHB_CUDA(dx.alloc(static_cast<size_t>(n) * d, s));
+    SPHB_CUDA(dl.alloc(n, s));
+    SPHB_CUDA(dc.alloc(static_cast<size_t>(num_components) * d, s));
+    SPHB_CUDA(cudaMemcpyAsync(dx.p, x, static_cast<size_t>(n) * d * sizeof(float), cudaMemcpyHostToDevice, s));
+    SPHB_CUDA(cudaMemcpyAsync(dl.p, labels, n * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    if (int rc = sphb_component_centers_dev(dx.p, n, d, dl.p, num_components, dc.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(centers, dc.p, static_cast<size_t>(num_components) * d * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_bridge_components(const float* x, int64_t n, int d, int metric, const int64_t* labels, int64_t num_components, const int64_t* edges,
+                                    int64_t num_edges, int64_t* ids_a, int64_t* ids_b, float* dist) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || d <= 0 || num_edges < 0 || (n > 0 && (!x || !labels)) || (num_edges > 0 && (!edges || !ids_a || !ids_b || !dist)))
+        return fail(SPHB_ERR_INVALID, "bridge_components: bad arguments");
+    if (num_edges == 0) return SPHB_OK;
+    cudaStream_t s = g_ctx.stream;
+    DevBuf<float> dx, dd;
+    DevBuf<int64_t> dl, da, db;
+    SPHB_CUDA(dx.alloc(static_cast<size_t>(n) * d, s));
+    SPHB_CUDA(dl.alloc(n, s));
+    SPHB_CUDA(da.alloc(num_edges, s));
+    SPHB_CUDA(db.alloc(num_edges, s));
+    SPHB_CUDA(dd.alloc(num_edges, s));
+    SPHB_CUDA(cudaMemcpyAsync(dx.p, x, static_cast<size_t>(n) * d * sizeof(float), cudaMemcpyHostToDevice, s));
+    SPHB_CUDA(cudaMemcpyAsync(dl.p, labels, n * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    if (int rc = sphb_bridge_components_dev(dx.p, n, d, metric, dl.p, num_components, edges, num_edges, da.p, db.p, dd.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(ids_a, da.p, num_edges * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(ids_b, db.p, num_edges * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(dist, dd.p, num_edges * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+// §8(f)-3: utils::computeExponentialDistributions(graph, rows) (sph/utils/GraphNormalization.cpp:508-593)
+SPHB_API int sphb_prow_exponential_graph_dev(const int64_t* d_ids, const float* d_dist, int64_t n, int k, int sort_cols, uint32_t* d_cols,
+                                             float* d_vals, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || k < 2 || (n > 0 && (!d_ids || !d_dist || !d_cols || !d_vals))) return fail(SPHB_ERR_INVALID, "prow_exponential_graph_dev: bad arguments");
+    return prow_exponential_graph_launch(d_ids, d_dist, n, k, sort_cols, d_cols, d_vals, static_cast<cudaStream_t>(stream));
+}
+
+SPHB_API int sphb_prow_exponential_graph(const int64_t* ids, const float* dist, int64_t n, int k, int sort_cols, uint32_t* cols, float* vals) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || k < 2 || (n > 0 && (!ids || !dist || !cols || !vals))) return fail(SPHB_ERR_INVALID, "prow_exponential_graph: bad arguments");
+    if (n == 0) return SPHB_OK;
+    cudaStream_t s = g_ctx.stream;
+    const size_t nk = static_cast<size_t>(n) * k, ne = static_cast<size_t>(n) * (k - 1);
+    DevBuf<int64_t> dids;
+    DevBuf<float> ddist, dvals;
+    DevBuf<uint32_t> dcols;
+    SPHB_CUDA(dids.alloc(nk, s));
+    SPHB_CUDA(ddist.alloc(nk, s));
+    SPHB_CUDA(dcols.alloc(ne, s));
+    SPHB_CUDA(dvals.alloc(ne, s));
+    SPHB_CUDA(cudaMemcpyAsync(dids.p, ids, nk * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    SPHB_CUDA(cudaMemcpyAsync(ddist.p, dist, nk * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (int rc = prow_exponential_graph_launch(dids.p, ddist.p, n, k, sort_cols, dcols.p, dvals.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(cols, dcols.p, ne * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(vals, dvals.p, ne * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+// §8(f)-3: utils::computeExponentialDistributions(rows, ignore) in place (sph/utils/GraphNormalization.cpp:413-506)
+SPHB_API int sphb_prow_exponential_inplace_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, float* d_val, int max_row_nnz, int ignore,
+                                               void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || (n > 0 && (!d_rowptr || !d_val)) || (ignore >= 0 && !d_col)) return fail(SPHB_ERR_INVALID, "prow_exponential_inplace_dev: bad arguments");
+    if (max_row_nnz <= 0 || max_row_nnz > 1024) return fail(SPHB_ERR_UNSUPPORTED, "prow_exponential_inplace_dev: max_row_nnz must be in 1..1024");
+    return prow_exponential_inplace_launch(n, d_rowptr, d_col, d_val, max_row_nnz, ignore, static_cast<cudaStream_t>(stream));
+}
+
+SPHB_API int sphb_prow_exponential_inplace(int64_t n, const int64_t* rowptr, const uint32_t* col, float* val, int ignore) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || !rowptr || (!val && n > 0 && rowptr[n] > 0) || (ignore >= 0 && !col)) return fail(SPHB_ERR_INVALID, "prow_exponential_inplace: bad arguments");
+    if (n == 0 || rowptr[n] == 0) return SPHB_OK;
+    cudaStream_t s = g_ctx.stream;
+    const int64_t nnz = rowptr[n];
+    int64_t max_nnz = 0;
+    for (int64_t i = 0; i < n; ++i) max_nnz = std::max(max_nnz, rowptr[i + 1] - rowptr[i]);
+    if (max_nnz > 1024) return fail(SPHB_ERR_UNSUPPORTED, "prow_exponential_inplace: rows with more than 1024 entries unsupported");
+    DevBuf<int64_t> drp;
+    DevBuf<uint32_t> dcol;
+    DevBuf<float> dval;
+    SPHB_CUDA(drp.alloc(n + 1, s));
+    SPHB_CUDA(dval.alloc(nnz, s));
+    SPHB_CUDA(cudaMemcpyAsync(drp.p, rowptr, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    SPHB_CUDA(cudaMemcpyAsync(dval.p, val, nnz * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (ignore >= 0) {
+        SPHB_CUDA(dcol.alloc(nnz, s));
+        SPHB_CUDA(cudaMemcpyAsync(dcol.p, col, nnz * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+    }
+    if (int rc = prow_exponential_inplace_launch(n, drp.p, ignore >= 0 ? dcol.p : nullptr, dval.p, static_cast<int>(max_nnz), ignore, s)) return rc;
     SPHB_CUDA(cudaMemcpyAsync(val, dval.p, nnz * sizeof(float), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaStreamSynchronize(s));
     return SPHB_OK;

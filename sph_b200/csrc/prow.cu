@@ -4,6 +4,7 @@
 //   B3 sph/utils/GraphNormalization.cpp:38-189   in place on sparse rows (+ the 1e-10 cursor quirk)
 //   B4 sph/utils/HDILibHelper.hpp:112-140        flat variant, tol 1e-5
 //   B5 sph/utils/GraphNormalization.cpp:340-411  linear rows
+//   §8(f)-3 sph/utils/GraphNormalization.cpp:413-593  exponential (UMAP) rows, at the end of this file
 // Distances live in registers (R values per lane), all reductions are warp shuffles,
 // the beta loop never touches memory.  HBM traffic is the one read of (ids, dist)
 // and the one write of (cols, vals).
@@ -458,6 +459,215 @@ int prow_flat_launch(const float* d_dist, int64_t n, int k, double perplexity, f
     else return fail(5, "prow_flat: k > 1024 unsupported");
     count_launch();
     SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+
+// ---- §8(f)-3: UMAP-flavoured rows, utils::computeExponentialDistributions (sph/utils/GraphNormalization.cpp:413-593) ----
+// The reference hands each row to umappp::neighbor_similarities (libscran-umappp 3.2.0, default options: local_connectivity 1,
+// bandwidth 1, fp32).  Per row: rho = first non-zero distance in stored order; sigma solves
+//   sum_j [ d_j > rho ? exp(-(d_j - rho) / sigma) : 1 ] = log2(n_neighbours + 1)
+// (doubling from 1 until bracketed, then bisection, <= 64 evaluations, |sum - target| < 1e-5), is clamped from below by
+// 1e-3 * mean(d), and the row becomes w_j = d_j > rho ? exp(-(d_j - rho) / sigma) : 1.  Same shape as the Gaussian rows: one
+// warp per row, the distances in registers, warp-shuffle sums, no memory traffic inside the search.
+// vm: bit r set <=> register r of this lane holds a row entry.
+template <int R>
+__device__ __forceinline__ void umap_row_weights(const float (&d)[R], float (&w)[R], uint32_t vm, int lane) {
+    int first = 0x7fffffff, nn = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const bool v = (vm >> r) & 1u;
+        nn += v;
+        if (v && d[r] != 0.f) first = min(first, lane + 32 * r);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+        nn += __shfl_xor_sync(0xffffffffu, nn, o);
+    }
+    float rho = 0.f;
+    if (first != 0x7fffffff) {
+        float c = 0.f;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (r == (first >> 5)) c = d[r];
+        rho = __shfl_sync(0xffffffffu, c, first & 31);
+    }
+    int num_le = 0;
+    float total = 0.f;
+    float delta[R];  // > 0 for the entries beyond rho, 0 marks "not active"
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const bool v = (vm >> r) & 1u;
+        const bool act = v && d[r] > rho;
+        num_le += v && !act;
+        total += v ? d[r] : 0.f;
+        delta[r] = act ? d[r] - rho : 0.f;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        num_le += __shfl_xor_sync(0xffffffffu, num_le, o);
+        total += __shfl_xor_sync(0xffffffffu, total, o);
+    }
+    if (num_le == nn) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) w[r] = 1.f;
+        return;
+    }
+    const float target = log2f(static_cast<float>(nn + 1));
+    float sigma = 1.f, lo = 0.f, hi = FLT_MAX;
+    for (int iter = 0; iter < 64; ++iter) {
+        float part = 0.f;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (delta[r] > 0.f) part += expf(-delta[r] / sigma);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        const float val = static_cast<float>(num_le) + part;
+        if (fabsf(val - target) < 1e-5f) break;
+        if (val > target) {
+            hi = sigma;
+            sigma = (lo + hi) / 2.f;
+        } else {
+            lo = sigma;
+            sigma = (hi == FLT_MAX) ? sigma * 2.f : (lo + hi) / 2.f;
+        }
+    }
+    sigma = fmaxf(sigma, 1e-3f * (total / static_cast<float>(nn)));
+#pragma unroll
+    for (int r = 0; r < R; ++r) w[r] = delta[r] > 0.f ? expf(-delta[r] / sigma) : 1.f;
+}
+
+// Graph form (GraphNormalization.cpp:508-593): neighbours 1..k-1 of a fixed-k graph; sort_cols = 0 keeps the neighbour order
+// (T = MapMemEff: storage.emplace_back), 1 sorts the row by column (T = SparseVecSPH: insert).
+template <int R>
+__global__ void __launch_bounds__(128) prow_exponential_graph_kernel(const int64_t* __restrict__ ids, const float* __restrict__ dist, int64_t n,
+                                                                     int k, int sort_cols, int cap, uint32_t* __restrict__ cols,
+                                                                     float* __restrict__ vals) {
+    extern __shared__ uint64_t smem_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+    const int ne = k - 1;
+    for (int64_t p = gw; p < n; p += nw) {
+        float dv[R], wv[R];
+        uint32_t vm = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            dv[r] = idx < ne ? dist[p * k + 1 + idx] : 0.f;
+            vm |= (idx < ne ? 1u : 0u) << r;
+        }
+        umap_row_weights<R>(dv, wv, vm, lane);
+        if (!sort_cols) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int idx = lane + 32 * r;
+                if (idx < ne) {
+                    cols[p * ne + idx] = static_cast<uint32_t>(ids[p * k + 1 + idx]);
+                    vals[p * ne + idx] = wv[r];
+                }
+            }
+            continue;
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            if (idx < cap)
+                sm[idx] = idx < ne ? (static_cast<uint64_t>(static_cast<uint32_t>(ids[p * k + 1 + idx])) << 32) | __float_as_uint(wv[r]) : ~0ull;
+        }
+        for (int t = 32 * R + lane; t < cap; t += 32) sm[t] = ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        for (int e = lane; e < ne; e += 32) {
+            const uint64_t key = sm[e];
+            cols[p * ne + e] = static_cast<uint32_t>(key >> 32);
+            vals[p * ne + e] = __uint_as_float(static_cast<uint32_t>(key));
+        }
+        __syncwarp();
+    }
+}
+
+// In-place form on CSR rows (GraphNormalization.cpp:413-506): the stored entries of a row are its "neighbours", an entry whose
+// COLUMN equals `ignore` (>= 0) is left out and keeps its value.
+template <int R>
+__global__ void __launch_bounds__(128) prow_exponential_inplace_kernel(int64_t n, const int64_t* __restrict__ rowptr,
+                                                                       const uint32_t* __restrict__ col, float* __restrict__ val, int ignore,
+                                                                       int* __restrict__ err) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+    for (int64_t p = gw; p < n; p += nw) {
+        const int64_t b = rowptr[p];
+        const int64_t nn64 = rowptr[p + 1] - b;
+        if (nn64 <= 0) continue;
+        if (nn64 > 32 * R) {
+            if (lane == 0) atomicExch(err, 1);
+            continue;
+        }
+        const int nn = static_cast<int>(nn64);
+        float dv[R], wv[R];
+        uint32_t vm = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int idx = lane + 32 * r;
+            const bool v = idx < nn && !(ignore >= 0 && col != nullptr && col[b + (idx < nn ? idx : 0)] == static_cast<uint32_t>(ignore));
+            dv[r] = v ? val[b + idx] : 0.f;
+            vm |= (v ? 1u : 0u) << r;
+        }
+        umap_row_weights<R>(dv, wv, vm, lane);
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if ((vm >> r) & 1u) val[b + lane + 32 * r] = wv[r];
+    }
+}
+
+template <int R>
+static int launch_exponential_graph(const int64_t* ids, const float* dist, int64_t n, int k, int sort_cols, uint32_t* cols, float* vals,
+                                    cudaStream_t stream) {
+    const int cap = pow2_at_least(32 * R);
+    const size_t smem = sort_cols ? 4 * static_cast<size_t>(cap) * sizeof(uint64_t) : 0;
+    SPHB_CUDA(cudaFuncSetAttribute(prow_exponential_graph_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    const int64_t blocks = std::min<int64_t>((n + 3) / 4, static_cast<int64_t>(ctx().num_sms) * 16);
+    prow_exponential_graph_kernel<R><<<static_cast<unsigned>(blocks), 128, smem, stream>>>(ids, dist, n, k, sort_cols, cap, cols, vals);
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int prow_exponential_graph_launch(const int64_t* d_ids, const float* d_dist, int64_t n, int k, int sort_cols, uint32_t* d_cols, float* d_vals,
+                                  cudaStream_t stream) {
+    if (n <= 0) return 0;
+    if (k < 2) return fail(2, "prow_exponential: k must be >= 2");
+    const int ne = k - 1;
+    if (ne <= 32) return launch_exponential_graph<1>(d_ids, d_dist, n, k, sort_cols, d_cols, d_vals, stream);
+    if (ne <= 64) return launch_exponential_graph<2>(d_ids, d_dist, n, k, sort_cols, d_cols, d_vals, stream);
+    if (ne <= 96) return launch_exponential_graph<3>(d_ids, d_dist, n, k, sort_cols, d_cols, d_vals, stream);
+    if (ne <= 128) return launch_exponential_graph<4>(d_ids, d_dist, n, k, sort_cols, d_cols, d_vals, stream);
+    if (ne <= 320) return launch_exponential_graph<10>(d_ids, d_dist, n, k, sort_cols, d_cols, d_vals, stream);
+    if (ne <= 1024) return launch_exponential_graph<32>(d_ids, d_dist, n, k, sort_cols, d_cols, d_vals, stream);
+    return fail(5, "prow_exponential: k > 1025 unsupported");
+}
+
+int prow_exponential_inplace_launch(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, float* d_val, int max_nnz, int ignore,
+                                    cudaStream_t stream) {
+    if (n <= 0) return 0;
+    DevBuf<int> err;
+    SPHB_CUDA(err.alloc(1, stream));
+    SPHB_CUDA(cudaMemsetAsync(err.p, 0, sizeof(int), stream));
+    const int64_t blocks = std::min<int64_t>((n + 3) / 4, static_cast<int64_t>(ctx().num_sms) * 16);
+    const unsigned g = static_cast<unsigned>(blocks);
+    if (max_nnz <= 128) prow_exponential_inplace_kernel<4><<<g, 128, 0, stream>>>(n, d_rowptr, d_col, d_val, ignore, err.p);
+    else if (max_nnz <= 320) prow_exponential_inplace_kernel<10><<<g, 128, 0, stream>>>(n, d_rowptr, d_col, d_val, ignore, err.p);
+    else if (max_nnz <= 1024) prow_exponential_inplace_kernel<32><<<g, 128, 0, stream>>>(n, d_rowptr, d_col, d_val, ignore, err.p);
+    else return fail(5, "prow_exponential_inplace: rows with more than 1024 entries unsupported");
+    count_launch();
+    SPHB_CUDA(cudaGetLastError());
+    int herr = 0;
+    SPHB_CUDA(cudaMemcpyAsync(&herr, err.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    SPHB_CUDA(cudaStreamSynchronize(stream));
+    if (herr) return fail(5, "prow_exponential_inplace: row longer than the dispatched register tile");
     return 0;
 }
 

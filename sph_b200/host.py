@@ -188,6 +188,112 @@ def gather_rows(local: np.ndarray, n: int, group=None) -> np.ndarray:
     return np.concatenate([p[: b - a].cpu().numpy() for p, (a, b) in zip(parts, slabs)], axis=0)
 
 
+# ---- host parts of NearestNeighbors::connectComponents (sph/NearestNeighbors.cpp:494-861) ----------------------------
+def centroid_spanning_tree(centers: np.ndarray) -> np.ndarray:
+    """computeSpanningTree (:682-708): minimum spanning tree of the complete graph over the component centres, edge weight
+    utils::L2 (sqrt of the fp32 squared distance, sph/utils/Distances.hpp:40-43).  Returns int64 [ncomp-1, 2]: (source, target)
+    with source < target — Boost stores the edge (i, j) as added in the i < j loop (:690-694) — in ascending order of weight,
+    the order kruskal_minimum_spanning_tree emits them.  With pairwise distinct weights the tree is unique; among exactly equal
+    weights Boost's priority queue order is unspecified, here ties go to the lower (source, target).  Prim over on-the-fly
+    distance rows: O(ncomp^2 d) time, O(ncomp) memory (the reference materialises all ncomp^2 / 2 Boost edges)."""
+    c = np.ascontiguousarray(centers, np.float32)
+    m = len(c)
+    if m <= 1:
+        return np.zeros((0, 2), np.int64)
+    in_tree = np.zeros(m, bool)
+    best = np.full(m, np.inf, np.float32)
+    link = np.full(m, -1, np.int64)
+    out = []
+    v = 0
+    for _ in range(m - 1):
+        in_tree[v] = True
+        diff = c - c[v]
+        w = np.sqrt(np.einsum("ij,ij->i", diff, diff, dtype=np.float32))
+        upd = ~in_tree & ((w < best) | ((w == best) & (v < link)))
+        best[upd] = w[upd]
+        link[upd] = v
+        cand = np.where(in_tree, np.inf, best)
+        v = int(np.argmin(cand))
+        a, b = (int(link[v]), v) if link[v] < v else (v, int(link[v]))
+        out.append((float(best[v]), a, b))
+    out.sort()
+    return np.array([(a, b) for _, a, b in out], np.int64).reshape(-1, 2)
+
+
+def insert_graph_edges(rowptr, ids, dist, ids_a, ids_b, dd):
+    """insertDistance (:547-572) for (a, b, d) and (b, a, d) of every bridge, in the given order: skipped when a == b or b is
+    already a neighbour of a; otherwise inserted behind the last distance <= d (std::upper_bound), never at position 0."""
+    touched: dict[int, tuple[list, list]] = {}
+
+    def row(a):
+        if a not in touched:
+            b0, b1 = int(rowptr[a]), int(rowptr[a + 1])
+            touched[a] = (ids[b0:b1].tolist(), dist[b0:b1].tolist())
+        return touched[a]
+
+    def insert(a, b, d):
+        if a == b or a < 0 or b < 0 or a >= len(rowptr) - 1:
+            return
+        rid, rd = row(a)
+        if b in rid:
+            return
+        pos = int(np.searchsorted(np.asarray(rd, np.float32), np.float32(d), side="right"))
+        pos = max(pos, 1)
+        rid.insert(pos, b)
+        rd.insert(pos, float(np.float32(d)))
+
+    for a, b, d in zip(ids_a.tolist(), ids_b.tolist(), dd.tolist()):
+        insert(a, b, d)
+        insert(b, a, d)
+    if not touched:
+        return rowptr, ids, dist
+    n = len(rowptr) - 1
+    nns = np.diff(rowptr)
+    for a, (rid, _) in touched.items():
+        nns[a] = len(rid)
+    new_rowptr = np.concatenate([[0], np.cumsum(nns)]).astype(np.int64)
+    new_ids = np.empty(new_rowptr[-1], np.int64)
+    new_dist = np.empty(new_rowptr[-1], np.float32)
+    keep = np.ones(n, bool)
+    keep[list(touched)] = False
+    # untouched rows move as blocks: every old entry shifts by the growth of the rows before it
+    shift = np.repeat(new_rowptr[:-1] - rowptr[:-1], np.diff(rowptr))
+    mask = np.repeat(keep, np.diff(rowptr))
+    dst = (np.arange(len(ids), dtype=np.int64) + shift)[mask]
+    new_ids[dst] = ids[mask]
+    new_dist[dst] = dist[mask]
+    for a, (rid, rd) in touched.items():
+        b0 = int(new_rowptr[a])
+        new_ids[b0:b0 + len(rid)] = rid
+        new_dist[b0:b0 + len(rd)] = rd
+    return new_rowptr, new_ids, new_dist
+
+
+def ensureClosestPointIsSelf(g) -> int:
+    """utils::ensureClosestPointIsSelf (sph/utils/GraphUtils.cpp:23-95) on a RaggedGraph, in place; returns the number of adjusted rows.
+    (Stage A and symmetrizeGraph apply it on the device; this host form serves the connected graph, where it is a no-op unless an
+    upstream row was already broken.)"""
+    first = g.knnIndices[g.rowptr[:-1]] if g.numPoints else np.zeros(0, np.int64)
+    bad = np.nonzero((first != np.arange(g.numPoints)) & (np.diff(g.rowptr) > 0))[0]
+    for p in bad.tolist():
+        b0, b1 = int(g.rowptr[p]), int(g.rowptr[p + 1])
+        nb, ds = g.knnIndices[b0:b1], g.knnDistances[b0:b1]
+        hit = np.nonzero(nb == p)[0]
+        if hit.size:
+            sp = int(hit[0])
+        elif (ds == 0).all():
+            sp = len(nb) - 1
+            nb[sp] = p
+        else:
+            nb[1:] = nb[:-1].copy()
+            ds[1:] = ds[:-1].copy()
+            sp = 0
+            nb[0], ds[0] = p, 0.0
+        nb[0], nb[sp] = nb[sp], nb[0]
+        ds[0], ds[sp] = ds[sp], ds[0]
+    return int(bad.size)
+
+
 # ---- NearestNeighbors (sph/NearestNeighbors.hpp:32-125, .cpp:98-189) ----------------------------
 class NearestNeighbors:
     """Data-level exact kNN graph.  `compute()` follows NearestNeighbors::compute: metric setup (:81-96),
@@ -274,6 +380,46 @@ class NearestNeighbors:
 
     def getConnectedComponents(self):
         return self._cc
+
+    def connectComponents(self, bridge_ops=None):
+        """NearestNeighbors::connectComponents (sph/NearestNeighbors.cpp:494-861): one extra bidirectional edge per edge of the
+        minimum spanning tree over the component centres, between the closest pair of points of the two components.
+        Device: centres of mass and the closest pairs of ALL tree edges (sphb_component_centers, sphb_bridge_components);
+        host: the tree itself (:682-708) and the row insertions (:547-572), as SURVEY §8(f)-2 splits it.
+        bridge_ops: object with component_centers / bridge_components (tests inject the CPU oracle); default the C ABI."""
+        if self._graph is None:
+            log.warning("NearestNeighbors::connectComponents: _knn graph is not computed yet, call compute() first")
+            return None
+        if self._cc is None and self.computeConnectedComponents() is None:
+            return None
+        if bridge_ops is None:
+            from . import capi as bridge_ops
+        num, labels = self._cc
+        if self._sym_graph is not None:
+            g = self._sym_graph
+            rowptr, ids, dist, sym = g.rowptr.copy(), g.knnIndices.copy(), g.knnDistances.copy(), True
+        else:
+            n, k = self._graph.knnIndices.shape
+            rowptr = np.arange(n + 1, dtype=np.int64) * k
+            ids, dist, sym = self._graph.knnIndices.reshape(-1).copy(), self._graph.knnDistances.reshape(-1).copy(), False
+        if num > 1:
+            if self._nns.knnMetric != KnnMetric.L2:
+                log.error("NearestNeighbors::connectComponents: only the L2 metric is served by the device search")
+                return None
+            try:
+                centers = bridge_ops.component_centers(self._data, labels, num)
+                edges = centroid_spanning_tree(centers)
+                ia, ib, dd = bridge_ops.bridge_components(self._data, labels, num, edges)
+            except Exception as e:
+                log.error("NearestNeighbors::connectComponents failed: %s", e)
+                return None
+            rowptr, ids, dist = insert_graph_edges(rowptr, ids, dist, ia, ib, dd)
+        self._connected_graph = RaggedGraph(rowptr, ids, dist, symmetric=sym)
+        ensureClosestPointIsSelf(self._connected_graph)
+        return self._connected_graph
+
+    def getConnectedGraph(self):
+        return getattr(self, "_connected_graph", None)
 
     def _symmetrize(self, ids, dist):
         from . import capi

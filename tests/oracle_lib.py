@@ -57,6 +57,8 @@ class Oracle:
         L.orc_prow_gaussian_inplace.argtypes = [C.c_int64, i64p, f32p, C.c_float, C.c_int]
         L.orc_prow_gaussian_flat.argtypes = [f32p, C.c_int64, C.c_int, C.c_double, f32p]
         L.orc_prow_linear_graph.argtypes = [i64p, f32p, C.c_int64, C.c_int, u32p, f32p]
+        L.orc_prow_exponential_graph.argtypes = [i64p, f32p, C.c_int64, C.c_int, C.c_int, u32p, f32p]
+        L.orc_prow_exponential_inplace.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int]
         L.orc_symmetrize.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int, i64p, u32p, f32p, C.c_int64]
         L.orc_symmetrize.restype = C.c_int64
         L.orc_level_schedule.argtypes = [i64p, C.c_int, C.c_int64, f32p, i64p]
@@ -87,6 +89,8 @@ class Oracle:
         L.orc_prow_graph_ragged.argtypes = [C.c_int64, i64p, i64p, f32p, C.c_float, C.c_int, i64p, u32p, f32p]
         L.orc_weak_components.argtypes = [C.c_int64, i64p, i64p, i64p]
         L.orc_weak_components.restype = C.c_int64
+        L.orc_component_centers.argtypes = [f32p, C.c_int64, C.c_int, i64p, C.c_int64, f32p]
+        L.orc_bridge_components.argtypes = [f32p, C.c_int64, C.c_int, i64p, i64p, C.c_int64, i64p, i64p, f32p]
         L.orc_level_knn_overlap.argtypes = [i64p, C.c_int, C.c_int64, i64p, i64p, C.c_int64, i64p, f32p]
         L.orc_level_knn_walks.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int64, i64p, f32p]
 
@@ -175,6 +179,22 @@ class Oracle:
         temp = np.zeros((n, k), np.float32)
         self.lib.orc_prow_gaussian_flat(_p(dist, f32p), n, k, perplexity, _p(temp, f32p))
         return temp
+
+    def prow_exponential_graph(self, ids, dist, sort_cols=False):
+        ids = np.ascontiguousarray(ids, np.int64)
+        dist = np.ascontiguousarray(dist, np.float32)
+        n, k = ids.shape
+        cols = np.zeros((n, k - 1), np.uint32)
+        vals = np.zeros((n, k - 1), np.float32)
+        self.lib.orc_prow_exponential_graph(_p(ids, i64p), _p(dist, f32p), n, k, int(sort_cols), _p(cols, u32p), _p(vals, f32p))
+        return cols, vals
+
+    def prow_exponential_inplace(self, rowptr, val, col=None, ignore=-1):
+        rowptr = np.ascontiguousarray(rowptr, np.int64)
+        out = np.array(val, np.float32, copy=True)
+        colp = _p(np.ascontiguousarray(col, np.uint32), u32p) if col is not None else None
+        self.lib.orc_prow_exponential_inplace(len(rowptr) - 1, _p(rowptr, i64p), colp, _p(out, f32p), ignore)
+        return out
 
     def prow_linear_graph(self, ids, dist):
         ids = np.ascontiguousarray(ids, np.int64)
@@ -409,6 +429,26 @@ class Oracle:
         ov = np.zeros(max(m, 1), np.float32)
         self.lib.orc_prow_graph_ragged(n, _p(rowptr, i64p), _p(ids, i64p), _p(dist, f32p), perplexity, int(linear), _p(orp, i64p), _p(oc, u32p), _p(ov, f32p))
         return orp, oc[:m].copy(), ov[:m].copy()
+
+    def component_centers(self, x, labels, num_components):
+        x = np.ascontiguousarray(x, np.float32)
+        labels = np.ascontiguousarray(labels, np.int64)
+        n, d = x.shape
+        centers = np.zeros((num_components, d), np.float32)
+        self.lib.orc_component_centers(_p(x, f32p), n, d, _p(labels, i64p), num_components, _p(centers, f32p))
+        return centers
+
+    def bridge_components(self, x, labels, num_components, edges, metric=1):
+        x = np.ascontiguousarray(x, np.float32)
+        labels = np.ascontiguousarray(labels, np.int64)
+        edges = np.ascontiguousarray(edges, np.int64).reshape(-1, 2)
+        n, d = x.shape
+        m = len(edges)
+        ia = np.full(m, -1, np.int64)
+        ib = np.full(m, -1, np.int64)
+        dist = np.zeros(m, np.float32)
+        self.lib.orc_bridge_components(_p(x, f32p), n, d, _p(labels, i64p), _p(edges, i64p), m, _p(ia, i64p), _p(ib, i64p), _p(dist, f32p))
+        return ia, ib, dist
 
     def weak_components(self, ids, rowptr=None):
         ids = np.ascontiguousarray(ids, np.int64)

@@ -106,3 +106,66 @@ def test_search_ends_at_the_reference_beta(capi, oracle):
         np.testing.assert_array_equal(sigma, rsigma)
         np.testing.assert_array_equal(cols, rcols)
         np.testing.assert_allclose(vals, rvals, rtol=RTOL, atol=1e-12)
+
+
+# ---- UMAP-flavoured rows (utils::computeExponentialDistributions, sph/utils/GraphNormalization.cpp:413-593) ----
+# fp32 search on both sides (umappp's Float_ is float); the device sums in warp-tree order and uses CUDA's expf, so a search may stop
+# one bisection step apart from the oracle's: |sum - target| < 1e-5 on a sum of log2(k) bounds the effect on a weight well below 1e-4.
+URTOL = 1e-4
+
+
+@pytest.mark.parametrize("k,sort_cols", [(91, False), (91, True), (16, False), (31, True), (130, False), (301, True), (1025, False)])
+def test_exponential_graph(capi, oracle, k, sort_cols):
+    ids, dist = _graph(300, k, seed=1000 + k, scale=0.5 if k % 2 else 3.0)
+    cols, vals = capi.prow_exponential_graph(ids, dist, sort_cols)
+    rcols, rvals = oracle.prow_exponential_graph(ids, dist, sort_cols)
+    np.testing.assert_array_equal(cols, rcols)
+    np.testing.assert_allclose(vals, rvals, rtol=URTOL, atol=1e-7)
+    np.testing.assert_allclose(vals.sum(axis=1), np.log2(k), atol=3e-5 * k)  # the defining equation of the rows
+
+
+def test_exponential_graph_edge_rows(capi, oracle):
+    k = 9
+    ids = np.tile(np.arange(k, dtype=np.int64), (6, 1))
+    dist = np.zeros((6, k), np.float32)
+    dist[1, 1:] = 2.5
+    dist[2, 1:] = [0, 1, 2, 3, 4, 5, 6, 7]
+    dist[3, 1:] = [1, 1, 1, 1, 1, 1, 1, 1e6]
+    dist[4, 1:] = [1e-3, 1, 1, 1, 1, 1, 1, 1]
+    dist[5, 1:] = [0, 0, 0, 0, 0, 0, 0, 4]
+    cols, vals = capi.prow_exponential_graph(ids, dist)
+    rcols, rvals = oracle.prow_exponential_graph(ids, dist)
+    np.testing.assert_array_equal(cols, rcols)
+    np.testing.assert_allclose(vals, rvals, rtol=URTOL, atol=1e-7)
+    assert (vals[0] == 1).all() and (vals[1] == 1).all() and (vals[5] == 1).all() and vals[3, 7] == 0.0
+
+
+def test_exponential_inplace(capi, oracle):
+    rng = np.random.default_rng(77)
+    lens = np.concatenate([rng.integers(0, 130, size=300), [0, 1, 2, 128, 129, 320, 321, 1024]])
+    rowptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    col = np.concatenate([np.sort(rng.choice(4096, size=m, replace=False)) for m in lens]).astype(np.uint32)
+    val = rng.gamma(2.0, 1.0, size=rowptr[-1]).astype(np.float32)
+    val[rng.random(val.size) < 0.02] = 0.0  # stored zeros in the middle of a row
+    got = capi.prow_exponential_inplace(rowptr, val)
+    ref = oracle.prow_exponential_inplace(rowptr, val)
+    np.testing.assert_allclose(got, ref, rtol=URTOL, atol=1e-7)
+    got7 = capi.prow_exponential_inplace(rowptr, val, col=col, ignore=7)
+    ref7 = oracle.prow_exponential_inplace(rowptr, val, col=col, ignore=7)
+    np.testing.assert_allclose(got7, ref7, rtol=URTOL, atol=1e-7)
+    assert (got7[col == 7] == val[col == 7]).all() and (col == 7).sum() > 0
+
+
+def test_exponential_rows_feed_symmetrize_umap(capi, oracle):
+    """The UMAP branch of LevelSimilarities::computeProbDist (sph/LevelSimilarities.cpp:499-503 + symmetrizeOutput :566-600):
+    exponential rows, then the fuzzy union a + b - ab."""
+    n, k = 500, 16
+    rng = np.random.default_rng(3)
+    x = rng.normal(size=(n, 6)).astype(np.float32)
+    ids, dist = capi.knn_exact(x, k)
+    cols, vals = capi.prow_exponential_graph(ids, dist, sort_cols=True)
+    rowptr = np.arange(n + 1, dtype=np.int64) * (k - 1)
+    got = capi.symmetrize(rowptr, cols.ravel(), vals.ravel(), umap=True)
+    ref = oracle.symmetrize(rowptr, cols.ravel(), vals.ravel(), umap=True)
+    for g, r in zip(got, ref):
+        np.testing.assert_array_equal(g, r)
