@@ -899,6 +899,118 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(const float* __restrict
     }
 }
 
+// The same re-rank with the candidate rows STAGED through shared memory (d % 4 == 0).  In knn_rerank_kernel every lane walks
+// its own candidate row in global memory: per 4 channels one LDG.128 whose 32 lanes touch 32 different rows (32 L1 wavefronts).
+// Here a group of 32 candidates is fetched chunk by chunk (32 channels = 128 B per row): one LDG.128 covers four rows with eight
+// lanes each (4 wavefronts), the chunk lands in shared memory (row stride 36 floats: the quarter-warps of an LDS.128 hit disjoint
+// banks), and lane l runs the exact fp64 chain of candidate l; the query chunk is converted to fp64 once and read as a broadcast.
+// Same chain, same order (c = 0 .. d-1, one accumulator per candidate) as exact_key — bit-identical keys.  About 9 KB of shared
+// memory per warp, so 24 warps per SM stay resident to cover the latency of the dependent DFMA chain.
+constexpr int RR_DCH = 32;
+constexpr int RR_LD = RR_DCH + 4;
+constexpr int RR_WARPS = 8;
+__host__ __device__ constexpr size_t rerank_staged_smem_per_warp(int cap) {
+    return static_cast<size_t>(cap) * 8 + RR_DCH * 8 + 32 * RR_LD * 4;
+}
+
+__global__ void __launch_bounds__(RR_WARPS * 32, 3) knn_rerank_staged_kernel(const float* __restrict__ X, int d, int k, int cap, int keep_max, int nseg,
+                                                                          int metric, int l2_squared, int64_t q0, int64_t nq,
+                                                                          const int64_t* __restrict__ qrows, int64_t out_q0,
+                                                                          const uint32_t* __restrict__ cand, const int* __restrict__ cnt,
+                                                                          int64_t* __restrict__ ids, float* __restrict__ dist,
+                                                                          int64_t* __restrict__ ovf_rows, int* __restrict__ ovf_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned char* base = smem_raw + static_cast<size_t>(warp) * rerank_staged_smem_per_warp(cap);
+    uint64_t* sm = reinterpret_cast<uint64_t*>(base);
+    double* qd = reinterpret_cast<double*>(base + static_cast<size_t>(cap) * 8);
+    float* stage = reinterpret_cast<float*>(base + static_cast<size_t>(cap) * 8 + RR_DCH * 8);
+    const int sub = lane >> 3, col4 = (lane & 7) * 4;  // staging role: row 4c + sub, channels col4 .. col4 + 3 of the chunk
+    const int64_t gw = static_cast<int64_t>(blockIdx.x) * RR_WARPS + warp;
+    const int64_t nw = static_cast<int64_t>(gridDim.x) * RR_WARPS;
+    for (int64_t r = gw; r < nq; r += nw) {
+        const int64_t gi = qrows ? qrows[r] : q0 + r;
+        bool ovf = false;
+        for (int sg = 0; sg < nseg; ++sg) ovf |= (cnt[r * nseg + sg] & OVERFLOW_FLAG) != 0;
+        if (ovf) {
+            if (lane == 0) ovf_rows[atomicAdd(ovf_count, 1)] = gi;
+            continue;
+        }
+        int m = 0;
+        for (int sg = 0; sg < nseg; ++sg) {
+            const int c = cnt[r * nseg + sg];
+            const uint32_t* src = cand + (r * nseg + sg) * keep_max;
+            for (int t = lane; t < c; t += 32) sm[m + t] = src[t];  // ids first; the keys replace them group by group
+            m += c;
+        }
+        __syncwarp();
+        const float* xq = X + gi * d;
+        for (int g0 = 0; g0 < m; g0 += 32) {
+            const int t = g0 + lane;
+            const int nv = min(32, m - g0);
+            const uint32_t jm = t < m ? static_cast<uint32_t>(sm[t]) : 0u;
+            const float* xr[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) xr[c] = X + static_cast<int64_t>(__shfl_sync(0xffffffffu, jm, 4 * c + sub)) * d + col4;
+            double acc = 0.0;
+            for (int c0 = 0; c0 < d; c0 += RR_DCH) {
+                const bool in = c0 + col4 < d;
+                if (sub == 0 && in) {
+                    const float4 q = __ldg(reinterpret_cast<const float4*>(xq + c0 + col4));
+                    qd[col4] = q.x; qd[col4 + 1] = q.y; qd[col4 + 2] = q.z; qd[col4 + 3] = q.w;
+                }
+                float4 v[8];
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    if (in && 4 * c + sub < nv) v[c] = __ldg(reinterpret_cast<const float4*>(xr[c] + c0));
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    if (in && 4 * c + sub < nv) *reinterpret_cast<float4*>(stage + (4 * c + sub) * RR_LD + col4) = v[c];
+                __syncwarp();
+                if (lane < nv) {
+                    const float* mine = stage + lane * RR_LD;
+                    const int len = min(RR_DCH, d - c0);
+                    if (metric == METRIC_L2) {
+#pragma unroll
+                        for (int e = 0; e < RR_DCH; e += 4) {
+                            if (e < len) {
+                                const float4 w = *reinterpret_cast<const float4*>(mine + e);
+                                const double2 qa = *reinterpret_cast<const double2*>(qd + e), qb = *reinterpret_cast<const double2*>(qd + e + 2);
+                                double tt;
+                                tt = qa.x - static_cast<double>(w.x); acc = fma(tt, tt, acc);
+                                tt = qa.y - static_cast<double>(w.y); acc = fma(tt, tt, acc);
+                                tt = qb.x - static_cast<double>(w.z); acc = fma(tt, tt, acc);
+                                tt = qb.y - static_cast<double>(w.w); acc = fma(tt, tt, acc);
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < RR_DCH; e += 4) {
+                            if (e < len) {
+                                const float4 w = *reinterpret_cast<const float4*>(mine + e);
+                                const double2 qa = *reinterpret_cast<const double2*>(qd + e), qb = *reinterpret_cast<const double2*>(qd + e + 2);
+                                acc = fma(qa.x, static_cast<double>(w.x), acc);
+                                acc = fma(qa.y, static_cast<double>(w.y), acc);
+                                acc = fma(qb.x, static_cast<double>(w.z), acc);
+                                acc = fma(qb.y, static_cast<double>(w.w), acc);
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            const float v32 = static_cast<float>(acc);
+            if (t < m) sm[t] = make_key(metric == METRIC_L2 ? v32 : -v32, jm);
+        }
+        for (int t = m + lane; t < cap; t += 32) sm[t] = ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        const int64_t orow = gi - out_q0;
+        write_row(sm, min(m, k), k, gi, metric, l2_squared, ids + orow * k, dist + orow * k, lane);
+        __syncwarp();
+    }
+}
+
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
@@ -1200,12 +1312,21 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     trerank.start(stream);
     {
         const int cap_sort = next_pow2_i(std::max(cap, nseg * keep_max));
-        const size_t smem = 8 * static_cast<size_t>(cap_sort) * sizeof(uint64_t);
-        SPHB_CUDA(cudaFuncSetAttribute(knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        const int64_t blocks = std::min<int64_t>((nq + 7) / 8, static_cast<int64_t>(J.sms) * 8);
-        knn_rerank_kernel<<<static_cast<unsigned>(blocks), 256, smem, stream>>>(J.x, d, k, cap_sort, keep_max, nseg, J.metric, J.l2_squared, qa, nq,
-                                                                                 d_qrows, out_q0, cand_out.p, cnt_out.p, d_ids, d_dist, d_ovf_rows,
-                                                                                 d_ovf_count);
+        const size_t smem_staged = RR_WARPS * rerank_staged_smem_per_warp(cap_sort);
+        if ((d & 3) == 0 && smem_staged <= 200 * 1024 && tune("SPHB_KNN_RERANK_STAGED", 1)) {
+            SPHB_CUDA(cudaFuncSetAttribute(knn_rerank_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_staged)));
+            const int64_t blocks = std::min<int64_t>((nq + RR_WARPS - 1) / RR_WARPS, static_cast<int64_t>(J.sms) * 6);
+            knn_rerank_staged_kernel<<<static_cast<unsigned>(blocks), RR_WARPS * 32, smem_staged, stream>>>(
+                J.x, d, k, cap_sort, keep_max, nseg, J.metric, J.l2_squared, qa, nq, d_qrows, out_q0, cand_out.p, cnt_out.p, d_ids, d_dist,
+                d_ovf_rows, d_ovf_count);
+        } else {
+            const size_t smem = 8 * static_cast<size_t>(cap_sort) * sizeof(uint64_t);
+            SPHB_CUDA(cudaFuncSetAttribute(knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+            const int64_t blocks = std::min<int64_t>((nq + 7) / 8, static_cast<int64_t>(J.sms) * 8);
+            knn_rerank_kernel<<<static_cast<unsigned>(blocks), 256, smem, stream>>>(J.x, d, k, cap_sort, keep_max, nseg, J.metric, J.l2_squared, qa,
+                                                                                     nq, d_qrows, out_q0, cand_out.p, cnt_out.p, d_ids, d_dist,
+                                                                                     d_ovf_rows, d_ovf_count);
+        }
         count_launch();
         SPHB_CUDA(cudaGetLastError());
     }
@@ -1366,6 +1487,34 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
             return std::chrono::duration<double, std::milli>(b - a).count();
         };
         const auto t0 = now();
+        // Optional first stage: the overflow rows once more through the 1-PRODUCT filter, database split into segments with a list
+        // per (row, segment) — the lists of a row together hold nseg times the candidates of the main sweep at a third of the
+        // 3-product sweep's tensor work.  What still overflows goes on to the 3-product stage below.
+        if (tune("SPHB_KNN_RESWEEP_1PASS", 1) && op1.passes == 1 && op1.MH) {
+            const int mh1 = (op1.MH == 2 && (pending1 + BM - 1) / BM <= J.sms) ? 1 : op1.MH;
+            Operands sub1;
+            if (int rc = build_operands(J, sub1, 1, mh1, ovf_rows.p, pending1, true, false)) return rc;
+            DevBuf<int> ovfb_count;
+            DevBuf<int64_t> ovfb_rows;
+            SPHB_CUDA(ovfb_count.alloc(1, stream));
+            SPHB_CUDA(ovfb_rows.alloc(pending1, stream));
+            SPHB_CUDA(cudaMemsetAsync(ovfb_count.p, 0, sizeof(int), stream));
+            float sm1 = 0.f, rm1 = 0.f;
+            int hovfb = 0;
+            if (int rc = sweep_and_rerank(J, sub1, op1, 0, pending1, ovf_rows.p, q0, d_ids, d_dist, ovfb_rows.p, ovfb_count.p, &hovfb, &sm1, &rm1)) return rc;
+            if (dbg) fprintf(stderr, "[knn timing] 1-product re-sweep of %d rows: %d still overflow (kernel %.1f + %.1f ms)\n", pending1, hovfb, sm1, rm1);
+            if (int rc = record_overflow_rows(0, ovf_rows.p, pending1, stream)) return rc;
+            resweep_rows += pending1;
+            if (hovfb == 0) {
+                tf.stop(stream);
+                fallback_ms += tf.ms();
+                pending1 = 0;
+                return 0;
+            }
+            SPHB_CUDA(cudaMemcpyAsync(ovf_rows.p, ovfb_rows.p, static_cast<size_t>(hovfb) * sizeof(int64_t), cudaMemcpyDeviceToDevice, stream));
+            pending1 = hovfb;
+            resweep_rows -= pending1;  // counted again below
+        }
         if (int rc = ensure_full(op3, 3, false)) return rc;
         const auto t1 = now();
         // few rows: 128-row query tiles (MH = 1) put twice as many CTAs to work, each with half the MMA work per database tile
