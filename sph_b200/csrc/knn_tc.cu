@@ -1487,7 +1487,8 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
             return std::chrono::duration<double, std::milli>(b - a).count();
         };
         const auto t0 = now();
-        // Optional first stage: the overflow rows once more through the 1-PRODUCT filter, database split into segments with a list
+        bool recorded = false;  // the rows of this call's re-sweep are reported once (sphb_knn_last_overflow_rows), whatever stages they pass
+        // First stage: the overflow rows once more through the 1-PRODUCT filter, database split into segments with a list
         // per (row, segment) — the lists of a row together hold nseg times the candidates of the main sweep at a third of the
         // 3-product sweep's tensor work.  What still overflows goes on to the 3-product stage below.
         if (tune("SPHB_KNN_RESWEEP_1PASS", 1) && op1.passes == 1 && op1.MH) {
@@ -1504,6 +1505,7 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
             if (int rc = sweep_and_rerank(J, sub1, op1, 0, pending1, ovf_rows.p, q0, d_ids, d_dist, ovfb_rows.p, ovfb_count.p, &hovfb, &sm1, &rm1)) return rc;
             if (dbg) fprintf(stderr, "[knn timing] 1-product re-sweep of %d rows: %d still overflow (kernel %.1f + %.1f ms)\n", pending1, hovfb, sm1, rm1);
             if (int rc = record_overflow_rows(0, ovf_rows.p, pending1, stream)) return rc;
+            recorded = true;
             resweep_rows += pending1;
             if (hovfb == 0) {
                 tf.stop(stream);
@@ -1532,7 +1534,8 @@ int knn_tc_launch(const float* d_x, int64_t n, int d, int k, int metric, int l2_
         if (int rc = sweep_and_rerank(J, sub, op3, 0, pending1, ovf_rows.p, q0, d_ids, d_dist, ovf2_rows.p, ovf2_count.p, &hovf2, &sm, &rm)) return rc;
         const auto t3 = now();
         resweep_rows += pending1;
-        if (int rc = record_overflow_rows(0, ovf_rows.p, pending1, stream)) return rc;
+        if (!recorded)
+            if (int rc = record_overflow_rows(0, ovf_rows.p, pending1, stream)) return rc;
         if (int rc = record_overflow_rows(1, ovf2_rows.p, hovf2, stream)) return rc;
         if (int rc = simt_rows_exact(ovf2_rows.p, ovf2_count.p, hovf2)) return rc;
         if (dbg)
