@@ -27,6 +27,20 @@ int sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const V* vals_in, V*
     return 0;
 }
 
+// The same on bits [begin_bit, end_bit) only (input already ordered on the lower bits: LSD sorts are stable).
+template <class V>
+int sort_pairs_bits(const uint64_t* keys_in, uint64_t* keys_out, const V* vals_in, V* vals_out, int64_t num, int begin_bit, int end_bit, cudaStream_t s) {
+    if (num <= 0) return 0;
+    if (num > 0x7fffffffll) return fail(5, "sort_pairs: more than 2^31 - 1 records");
+    size_t bytes = 0;
+    SPHB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, bytes, keys_in, keys_out, vals_in, vals_out, static_cast<int>(num), begin_bit, end_bit, s));
+    DevBuf<uint8_t> tmp;
+    SPHB_CUDA(tmp.alloc(bytes, s));
+    SPHB_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, bytes, keys_in, keys_out, vals_in, vals_out, static_cast<int>(num), begin_bit, end_bit, s));
+    count_launch(3);
+    return 0;
+}
+
 template <class T>
 int exclusive_sum(const T* in, T* out, int64_t num, cudaStream_t s) {
     if (num <= 0) return 0;

@@ -116,13 +116,13 @@ struct SimsParams {
 static int g_force_slab = 0;
 void sims_force_slab(int on) { g_force_slab = on; }
 
-constexpr int SIMS_WARPS = 16;
 constexpr int SIMS_EB = 512;   // DENSE: row entries staged per batch (column start, length, s_ic)
-constexpr int SIMS_D = 8;      // DENSE: columns per register group (two groups: one being added, one in flight)
 
+// DENSE: SIMS_D columns per register group (two groups: one being added, one in flight), E entries of every column per thread
+template <int SIMS_D, int E>
 struct ColGroup {
-    uint32_t j[SIMS_D][2];
-    float v[SIMS_D][2], s[SIMS_D];
+    uint32_t j[SIMS_D][E];
+    float v[SIMS_D][E], s[SIMS_D];
 };
 
 __global__ void sims_split_rows(const uint64_t* __restrict__ keys, int64_t num, uint32_t* __restrict__ rows) {
@@ -130,7 +130,7 @@ __global__ void sims_split_rows(const uint64_t* __restrict__ keys, int64_t num, 
         rows[t] = static_cast<uint32_t>(keys[t]);
 }
 
-template <bool DENSE>
+template <bool DENSE, int SIMS_WARPS, int E, int SIMS_D>
 __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsParams P) {
     extern __shared__ uint64_t sm_keys[];  // SIMS_WARPS * cap keys | DENSE: entry batch | accumulator row
     __shared__ unsigned int s_touched, s_valid, s_nsel;
@@ -170,8 +170,8 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
                 // every column of a group (columns longer than 2 * THREADS finish with direct loads); the two groups
                 // are separate objects so that every register is addressed statically.  (The first version of this
                 // loop drove a flag-per-slot cursor: ncu counted 111 warp instructions per 32 products, issue-bound.)
-                ColGroup ga, gb;
-                auto load_group = [&](ColGroup& G, int c0) {
+                ColGroup<SIMS_D, E> ga, gb;
+                auto load_group = [&](ColGroup<SIMS_D, E>& G, int c0) {
 #pragma unroll
                     for (int d = 0; d < SIMS_D; ++d) {
                         const int c = c0 + d;
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
                             const int64_t cb = e_cb[c];
                             G.s[d] = e_sic[c];
 #pragma unroll
-                            for (int e = 0; e < 2; ++e) {
+                            for (int e = 0; e < E; ++e) {
                                 const int off = e * THREADS + static_cast<int>(threadIdx.x);
                                 if (off < len) {
                                     G.j[d][e] = __ldg(P.trow + cb + off);
@@ -190,20 +190,20 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
                         }
                     }
                 };
-                auto consume_group = [&](const ColGroup& G, int c0) {
+                auto consume_group = [&](const ColGroup<SIMS_D, E>& G, int c0) {
 #pragma unroll
                     for (int d = 0; d < SIMS_D; ++d) {
                         const int c = c0 + d;
                         if (c >= ne) break;  // uniform
                         const int len = e_len[c];
 #pragma unroll
-                        for (int e = 0; e < 2; ++e) {
+                        for (int e = 0; e < E; ++e) {
                             const int off = e * THREADS + static_cast<int>(threadIdx.x);
                             if (off < len) sacc[G.j[d][e]] = __fadd_rn(sacc[G.j[d][e]], __fmul_rn(G.s[d], G.v[d][e]));
                         }
-                        if (len > 2 * THREADS) {  // uniform; the rows of one column are distinct, no barrier inside a column
+                        if (len > E * THREADS) {  // uniform; the rows of one column are distinct, no barrier inside a column
                             const int64_t cb = e_cb[c];
-                            for (int off = 2 * THREADS + static_cast<int>(threadIdx.x); off < len; off += THREADS) {
+                            for (int off = E * THREADS + static_cast<int>(threadIdx.x); off < len; off += THREADS) {
                                 const uint32_t j = __ldg(P.trow + cb + off);
                                 sacc[j] = __fadd_rn(sacc[j], __fmul_rn(G.s[d], __ldg(P.tval + cb + off)));
                             }
@@ -340,6 +340,342 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
     }
 }
 
+// ---- DENSE, class-partitioned (round 2, second version) -------------------------------------------------------------------
+// The column-at-a-time kernel above needs a block barrier after every column of Sᵀ (two columns may hit the same row j from
+// different threads) and is latency-bound by them: 1 233 cycles per column at C2 level 1, issue slots 35 % busy, more warps
+// help, fewer hurt (16 warps 90 ms, 8 warps 109-140 ms).  Here the rows j are split into 16 CLASSES (j mod 16), warp w owns
+// class w: Sᵀ is stored class-major (one radix sort on (class, column, row)), so the entries of column c that belong to class
+// w are one contiguous segment, and warp w walks the columns of row i in order adding only its own segment into its own
+// accumulator sub-array acc[w][j >> 4].  No two warps ever touch the same accumulator, so there is NO block barrier inside a
+// row's expansion; inside a warp a column's rows are distinct and columns are processed in order (a __syncwarp between them),
+// so every C[i][j] is still summed in ascending c — bit-identical to the kernel above, deterministic.
+constexpr int SC_WARPS = 16;
+constexpr int SC_D = 4;   // columns per register group
+constexpr int SC_E = 2;   // entries of a (column, class) segment per lane held in registers (segments average n_col / 16)
+
+struct ClassGroup {
+    uint32_t j[SC_D][SC_E];
+    float v[SC_D][SC_E], s[SC_D];
+    int len[SC_D];
+    int64_t b[SC_D];
+};
+
+__global__ void sims_class_ptr(const uint64_t* __restrict__ keys, int64_t num, int64_t n, int cbits, int64_t* __restrict__ cptr) {
+    const int64_t total = static_cast<int64_t>(SC_WARPS) * (n + 1);
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t w = t / (n + 1), c = t - w * (n + 1);
+        cptr[t] = lower_bound_u64(keys, num, (static_cast<uint64_t>(w) << (32 + cbits)) | (static_cast<uint64_t>(c) << 32));
+    }
+}
+__global__ void sims_class_keys(const uint64_t* __restrict__ tkeys, int64_t num, int cbits, uint64_t* __restrict__ out) {
+    // (column, row) -> (row mod 16, column, row)
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < num; t += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const uint64_t k = tkeys[t];
+        out[t] = ((k & 15ull) << (32 + cbits)) | k;
+    }
+}
+
+__global__ void __launch_bounds__(SC_WARPS * 32) sims_class_kernel(const SimsParams P, const int64_t* __restrict__ cptr, int CH) {
+    extern __shared__ uint64_t sm_keys[];  // SC_WARPS * cap keys | entry batch | SC_WARPS * CH accumulators
+    __shared__ unsigned int s_valid, s_nsel, s_ncand, s_bin, s_above, s_nreg;
+    __shared__ double s_sum;
+    constexpr int THREADS = SC_WARPS * 32;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* mylist = sm_keys + static_cast<size_t>(warp) * P.cap;
+    uint32_t* e_c = reinterpret_cast<uint32_t*>(sm_keys + static_cast<size_t>(SC_WARPS) * P.cap);
+    float* e_sic = reinterpret_cast<float*>(e_c + SIMS_EB);
+    float* sacc = e_sic + SIMS_EB;
+    float* myacc = sacc + static_cast<size_t>(warp) * CH;
+    const int64_t* myptr = cptr + static_cast<int64_t>(warp) * (P.n + 1);
+    const int k = P.k, cap = P.cap;
+    for (int t = threadIdx.x; t < SC_WARPS * CH; t += THREADS) sacc[t] = 0.f;
+    if (threadIdx.x == 0) s_nreg = 0;
+    for (int64_t i = blockIdx.x; i < P.n; i += gridDim.x) {
+        if (threadIdx.x == 0) { s_valid = 0; s_nsel = 0; s_sum = 0.0; }
+        __syncthreads();
+        const int64_t rb = P.srowptr[i], re = P.srowptr[i + 1];
+        // ---- 1. expand: warp w adds the class-w segment of every column of row i, columns in order
+        for (int64_t eb = rb; eb < re; eb += SIMS_EB) {
+            const int ne = static_cast<int>(min(static_cast<int64_t>(SIMS_EB), re - eb));
+            for (int t = threadIdx.x; t < ne; t += THREADS) {
+                e_c[t] = P.scol[eb + t];
+                e_sic[t] = P.sval[eb + t];
+            }
+            __syncthreads();
+            for (int t0 = 0; t0 < ne; t0 += 32) {
+                // lane l looks up the segment of column t0 + l once; the columns are then consumed in order via shuffles
+                int64_t b_l = 0;
+                int len_l = 0;
+                float s_l = 0.f;
+                if (t0 + lane < ne) {
+                    const uint32_t c = e_c[t0 + lane];
+                    b_l = __ldg(myptr + c);
+                    len_l = static_cast<int>(__ldg(myptr + c + 1) - b_l);
+                    s_l = e_sic[t0 + lane];
+                }
+                const int nc = min(32, ne - t0);
+                ClassGroup ga, gb;
+                auto load_group = [&](ClassGroup& G, int tt0) {
+#pragma unroll
+                    for (int d = 0; d < SC_D; ++d) {
+                        const int tt = tt0 + d;  // warp-uniform
+                        G.len[d] = 0;
+                        if (tt < nc) {
+                            G.b[d] = __shfl_sync(0xffffffffu, b_l, tt);
+                            G.len[d] = __shfl_sync(0xffffffffu, len_l, tt);
+                            G.s[d] = __shfl_sync(0xffffffffu, s_l, tt);
+#pragma unroll
+                            for (int e = 0; e < SC_E; ++e) {
+                                const int off = e * 32 + lane;
+                                if (off < G.len[d]) {
+                                    G.j[d][e] = __ldg(P.trow + G.b[d] + off);
+                                    G.v[d][e] = __ldg(P.tval + G.b[d] + off);
+                                }
+                            }
+                        }
+                    }
+                };
+                auto consume_group = [&](const ClassGroup& G) {
+#pragma unroll
+                    for (int d = 0; d < SC_D; ++d) {
+                        const int len = G.len[d];  // warp-uniform
+                        if (len == 0) continue;
+#pragma unroll
+                        for (int e = 0; e < SC_E; ++e) {
+                            const int off = e * 32 + lane;
+                            if (off < len) {
+                                const uint32_t q = G.j[d][e] >> 4;
+                                myacc[q] = __fadd_rn(myacc[q], __fmul_rn(G.s[d], G.v[d][e]));
+                            }
+                        }
+                        for (int off = SC_E * 32 + lane; off < len; off += 32) {  // long segments: the rows of one column are distinct
+                            const uint32_t q = __ldg(P.trow + G.b[d] + off) >> 4;
+                            myacc[q] = __fadd_rn(myacc[q], __fmul_rn(G.s[d], __ldg(P.tval + G.b[d] + off)));
+                        }
+                        __syncwarp();  // the next column may hit the same rows from other lanes
+                    }
+                };
+                load_group(ga, 0);
+                for (int tt0 = 0; tt0 < nc; tt0 += 2 * SC_D) {
+                    load_group(gb, tt0 + SC_D);
+                    consume_group(ga);
+                    load_group(ga, tt0 + 2 * SC_D);
+                    consume_group(gb);
+                }
+            }
+            __syncthreads();  // e_* are rewritten by the next batch; after the last batch: all classes complete
+        }
+        // ---- 2. (Eigen variant) number of entries that survive the product prune, diagonal included
+        if (!P.hdi) {
+            unsigned int v = 0;
+            for (int t = threadIdx.x; t < SC_WARPS * CH; t += THREADS) v += eigen_keep(sacc[t], P.prune_val) ? 1u : 0u;  // padding slots are 0
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0 && v) atomicAdd(&s_valid, v);
+            __syncthreads();
+        }
+        const bool multi = s_valid > 1;
+        // ---- 3. candidates for the bottom-k of (D, column).  D = -ln C falls with C, so the row's k entries are among the k largest
+        // C plus the few "special" entries whose D does not follow C (the diagonal, C == 1).  Two histogram levels over the
+        // float bits of C (10 bits each: exponent + 12 mantissa bits) locate a threshold with at least k regular entries above it;
+        // everything above (1 - 1e-5) of the threshold is a candidate (entries whose D could tie with the k-th after the fp32
+        // rounding of the logarithm differ from it by less than 2e-6 in C, D <= 21), typically k + a few.  Only candidates pay the
+        // fp64 logarithm and the sort.  (The per-warp sorted lists this replaces were 32 % of the kernel's instructions.)
+        unsigned int* hist = reinterpret_cast<unsigned int*>(sm_keys);        // 1024 bins
+        uint64_t* cand = sm_keys + 512;                                       // up to SIMS_NCAND keys behind the histogram
+        const int SIMS_NCAND = min(1024, SC_WARPS * cap - 512);  // keys that fit behind the histogram (cap >= 64)
+        auto is_special = [&](uint32_t j, float c) { return static_cast<int64_t>(j) == i || c == 1.f; };
+        auto top_bin = [&](unsigned int need) -> unsigned int {  // highest bin B with (entries in bins >= B) >= need; warp 0, result in s_bin / s_above
+            unsigned int above = 0, found = 0xffffffffu;
+            for (int base = 1024 - 32; base >= 0 && found == 0xffffffffu; base -= 32) {
+                const unsigned int h = hist[base + 31 - lane];  // lane 0 holds the highest bin of the chunk
+                unsigned int incl = h;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const unsigned int up = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += up;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, above + incl >= need);
+                if (m) {
+                    const int l = __ffs(m) - 1;
+                    found = static_cast<unsigned int>(base + 31 - l);
+                    above += __shfl_sync(0xffffffffu, incl, l) - __shfl_sync(0xffffffffu, h, l);  // entries strictly above the bin
+                } else {
+                    above += __shfl_sync(0xffffffffu, incl, 31);
+                }
+            }
+            if (lane == 0) { s_bin = found; s_above = above; }
+            return found;
+        };
+        for (int t = threadIdx.x; t < 1024; t += THREADS) hist[t] = 0;
+        if (threadIdx.x == 0) { s_ncand = 0; s_bin = 0xffffffffu; s_above = 0; }
+        __syncthreads();
+        {
+            unsigned int nreg = 0;
+            for (int q = lane; q < CH; q += 32) {
+                const float c = myacc[q];
+                const uint32_t j = (static_cast<uint32_t>(q) << 4) | static_cast<uint32_t>(warp);
+                if (eigen_keep(c, P.prune_val) && c > 0.f && !is_special(j, c)) {
+                    atomicAdd(&hist[(__float_as_uint(c) >> 21) & 1023u], 1u);
+                    ++nreg;
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) nreg += __shfl_xor_sync(0xffffffffu, nreg, o);
+            if (lane == 0 && nreg) atomicAdd(&s_nreg, nreg);
+        }
+        __syncthreads();
+        const unsigned int nreg_all = s_nreg;
+        uint32_t thr_bits = 0;  // 0: every regular entry is a candidate
+        if (nreg_all > static_cast<unsigned int>(k)) {
+            if (warp == 0) top_bin(static_cast<unsigned int>(k));
+            __syncthreads();
+            const unsigned int b1 = s_bin, above1 = s_above;
+            for (int t = threadIdx.x; t < 1024; t += THREADS) hist[t] = 0;
+            __syncthreads();
+            for (int q = lane; q < CH; q += 32) {
+                const float c = myacc[q];
+                const uint32_t j = (static_cast<uint32_t>(q) << 4) | static_cast<uint32_t>(warp);
+                const uint32_t bits = __float_as_uint(c);
+                if (eigen_keep(c, P.prune_val) && c > 0.f && !is_special(j, c) && ((bits >> 21) & 1023u) == b1) atomicAdd(&hist[(bits >> 11) & 1023u], 1u);
+            }
+            __syncthreads();
+            if (warp == 0) top_bin(static_cast<unsigned int>(k) - above1);
+            __syncthreads();
+            thr_bits = (b1 << 21) | (s_bin << 11);
+        }
+        const float thr = __uint_as_float(thr_bits) * (1.f - 1e-5f);
+        // collect + reset
+        for (int q = lane; q < CH; q += 32) {
+            const float c = myacc[q];
+            const uint32_t j = (static_cast<uint32_t>(q) << 4) | static_cast<uint32_t>(warp);
+            if (eigen_keep(c, P.prune_val)) {
+                const bool diag = static_cast<int64_t>(j) == i;
+                if (diag || c == 1.f || !(c > 0.f) || c >= thr) {
+                    float dv;
+                    bool use = true;
+                    if (P.hdi) {
+                        use = !diag;                                                                  // :1250-1252
+                        dv = c == 1.f ? c : -1.f * static_cast<float>(log(static_cast<double>(c)));  // :1290-1292
+                    } else {
+                        dv = diag ? c : -1.f * static_cast<float>(log(static_cast<double>(c)));      // :1143-1153
+                        if (multi && (diag || dv == 0.f)) use = false;                        // removeDiagonalElements(keepSingleEntry)
+                    }
+                    if (use) {
+                        const unsigned int slot = atomicAdd(&s_ncand, 1u);
+                        if (slot < static_cast<unsigned int>(SIMS_NCAND)) cand[slot] = make_key(dv, j);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        const unsigned int ncand = s_ncand;
+        if (threadIdx.x == 0) s_nreg = 0;
+        if (ncand <= static_cast<unsigned int>(SIMS_NCAND)) {
+            for (int q = lane; q < CH; q += 32) myacc[q] = 0.f;
+            int capc = 32;
+            while (capc < static_cast<int>(ncand)) capc <<= 1;
+            for (int t = static_cast<int>(ncand) + threadIdx.x; t < capc; t += THREADS) cand[t] = ~0ull;
+            __syncthreads();
+            block_bitonic_sort(cand, capc);
+            for (int t = threadIdx.x; t < capc && t < k; t += THREADS) sm_keys[t] = cand[t];  // dst index = src index - 512: a thread's second read follows its first write
+            __syncthreads();
+            for (int t = capc + threadIdx.x; t < k; t += THREADS) sm_keys[t] = ~0ull;
+            __syncthreads();
+        } else {
+        // more candidates than the list holds (massive ties at the threshold): the per-warp sorted lists of the first version
+        int cnt = 0;
+        uint64_t kth = ~0ull;
+        float dk_screen = INFINITY;
+        for (int base = 0; base < CH; base += 32) {
+            const int q = base + lane;
+            bool pass = false;
+            uint64_t key = ~0ull;
+            if (q < CH) {
+                const uint32_t j = (static_cast<uint32_t>(q) << 4) | static_cast<uint32_t>(warp);
+                const float c = myacc[q];
+                myacc[q] = 0.f;
+                const bool diag = static_cast<int64_t>(j) == i;
+                if (eigen_keep(c, P.prune_val) && (diag || c == 1.f || !(-__logf(c) > dk_screen))) {
+                    float dv;
+                    bool use = true;
+                    if (P.hdi) {
+                        use = !diag;
+                        dv = c == 1.f ? c : -1.f * static_cast<float>(log(static_cast<double>(c)));
+                    } else {
+                        dv = diag ? c : -1.f * static_cast<float>(log(static_cast<double>(c)));
+                        if (multi && (diag || dv == 0.f)) use = false;
+                    }
+                    if (use) {
+                        key = make_key(dv, j);
+                        pass = key <= kth;
+                    }
+                }
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (m) {
+                if (pass) mylist[cnt + __popc(m & ((1u << lane) - 1u))] = key;
+                cnt += __popc(m);
+                if (cnt + 32 > cap) {
+                    for (int u = cnt + lane; u < cap; u += 32) mylist[u] = ~0ull;
+                    __syncwarp();
+                    warp_bitonic_sort(mylist, cap, lane);
+                    cnt = min(cnt, k);
+                    kth = (cnt == k) ? mylist[k - 1] : ~0ull;
+                    if (cnt == k) dk_screen = key_val(kth) + 1e-4f;
+                }
+            }
+        }
+        for (int u = cnt + lane; u < cap; u += 32) mylist[u] = ~0ull;
+        __syncthreads();
+        // ---- 4. merge the warps' lists: block-wide sort of all SC_WARPS * cap keys, the first k are the row
+        block_bitonic_sort(sm_keys, SC_WARPS * cap);
+        }
+        int m = 0;
+        for (int t = threadIdx.x; t < k; t += blockDim.x) m += sm_keys[t] != ~0ull ? 1 : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m += __shfl_xor_sync(0xffffffffu, m, o);
+        if (lane == 0 && m) atomicAdd(&s_nsel, static_cast<unsigned int>(m));
+        __syncthreads();
+        const int nsel = static_cast<int>(s_nsel);
+        if (warp == 0) {
+            double sum = 0.0;
+            for (int t = lane; t < nsel; t += 32) sum += static_cast<double>(key_val(sm_keys[t]));
+            sum = warp_sum(sum);
+            if (lane == 0) s_sum = sum;
+        }
+        __syncthreads();
+        int cap2 = 32;
+        while (cap2 < k) cap2 <<= 1;
+        for (int t = threadIdx.x; t < cap2; t += blockDim.x) {
+            uint64_t key = ~0ull;
+            if (t < nsel) {
+                const uint64_t kk = sm_keys[t];
+                key = (static_cast<uint64_t>(key_idx(kk)) << 32) | __float_as_uint(key_val(kk));
+            }
+            sm_keys[t] = key;
+        }
+        __syncthreads();
+        block_bitonic_sort(sm_keys, cap2);
+        const double sum = s_sum;
+        const bool divide = P.hdi || sum > 0.0;
+        for (int t = threadIdx.x; t < k; t += blockDim.x) {
+            uint32_t oc = 0xFFFFFFFFu;
+            float ov = 0.f;
+            if (t < nsel) {
+                const uint64_t key = sm_keys[t];
+                oc = static_cast<uint32_t>(key >> 32);
+                ov = __uint_as_float(static_cast<uint32_t>(key));
+                if (divide) ov /= static_cast<float>(sum);
+            }
+            P.out_cols[i * k + t] = oc;
+            P.out_vals[i * k + t] = ov;
+        }
+        if (threadIdx.x == 0) P.row_nnz[i] = nsel;
+        __syncthreads();
+    }
+}
+
 int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
                             int variant, const int64_t* d_comp_sizes, uint32_t* d_out_cols, float* d_out_vals, int32_t* d_row_nnz, cudaStream_t s) {
     if (n >= (1ll << 32)) return fail(SPHB_ERR_UNSUPPORTED, "create_similarities: n must be < 2^32");
@@ -376,26 +712,71 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
     // ---- the row kernel
     int cap = 64;
     while (cap < k + 32) cap <<= 1;
-    const size_t list_bytes = static_cast<size_t>(SIMS_WARPS) * cap * sizeof(uint64_t);
     SimsParams P{};
     P.n = n; P.srowptr = srowptr.p; P.scol = scol.p; P.sval = sval.p; P.colptr = colptr.p; P.tkeys = tk1.p; P.tval = tval.p;
     P.prune_val = prune_val; P.hdi = hdi ? 1 : 0; P.k = static_cast<int>(k); P.cap = cap;
     P.out_cols = d_out_cols; P.out_vals = d_out_vals; P.row_nnz = d_row_nnz;
-    const size_t dense_fixed = list_bytes + static_cast<size_t>(SIMS_EB) * 16;
-    const size_t dense_smem = dense_fixed + static_cast<size_t>(n) * sizeof(float);
     DevBuf<float> acc;
     DevBuf<uint32_t> touched, trow;
+    int dense_cfg = 0;
+#ifdef SPHB_KNN_TUNING
+    if (const char* e = getenv("SPHB_SIMS_CFG")) dense_cfg = atoi(e);
+#endif
+    const int cbits = bits_for(static_cast<uint64_t>(n));
+    const int CH = static_cast<int>((n + SC_WARPS - 1) / SC_WARPS);
+    const size_t class_smem = static_cast<size_t>(SC_WARPS) * cap * sizeof(uint64_t) + static_cast<size_t>(SIMS_EB) * 8 +
+                              static_cast<size_t>(SC_WARPS) * CH * sizeof(float);
+    if (dense_cfg == 0 && class_smem <= 220 * 1024 && cbits <= 28 && !g_force_slab) {
+        // class-major transpose: (row mod 16, column, row)
+        DevBuf<uint64_t> ck0, ck1;
+        DevBuf<float> cval;
+        DevBuf<int64_t> cptr;
+        SPHB_CUDA(ck0.alloc(std::max<int64_t>(snnz, 1), s));
+        SPHB_CUDA(ck1.alloc(std::max<int64_t>(snnz, 1), s));
+        SPHB_CUDA(cval.alloc(std::max<int64_t>(snnz, 1), s));
+        SPHB_CUDA(cptr.alloc(static_cast<size_t>(SC_WARPS) * (n + 1), s));
+        SPHB_CUDA(trow.alloc(std::max<int64_t>(snnz, 1), s));
+        sims_class_keys<<<g, 256, 0, s>>>(tk1.p, snnz, cbits, ck0.p);
+        count_launch();
+        // tk1 / tval are (column, row)-sorted already, so a stable sort on the 4 class bits alone finishes the job
+        if (int rc = sort_pairs_bits<float>(ck0.p, ck1.p, tval.p, cval.p, snnz, 32 + cbits, 36 + cbits, s)) return rc;
+        sims_class_ptr<<<g, 256, 0, s>>>(ck1.p, snnz, n, cbits, cptr.p);
+        sims_split_rows<<<g, 256, 0, s>>>(ck1.p, snnz, trow.p);
+        count_launch(2);
+        P.trow = trow.p;
+        P.tval = cval.p;
+        SPHB_CUDA(cudaFuncSetAttribute(sims_class_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(class_smem)));
+        const int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * (class_smem <= 100 * 1024 ? 2 : 1));
+        sims_class_kernel<<<static_cast<unsigned>(grid), SC_WARPS * 32, class_smem, s>>>(P, cptr.p, CH);
+        count_launch();
+        SPHB_CUDA(cudaGetLastError());
+        SPHB_CUDA(cudaStreamSynchronize(s));  // the class-major buffers are released on return
+        return 0;
+    }
+    const int dense_warps = dense_cfg == 3 ? 4 : ((dense_cfg == 0 || dense_cfg == 10) ? 16 : 8);
+    const size_t dense_smem = static_cast<size_t>(dense_warps) * cap * sizeof(uint64_t) + static_cast<size_t>(SIMS_EB) * 16 + static_cast<size_t>(n) * sizeof(float);
     if (dense_smem <= 220 * 1024 && !g_force_slab) {
         SPHB_CUDA(trow.alloc(std::max<int64_t>(snnz, 1), s));
         sims_split_rows<<<g, 256, 0, s>>>(tk1.p, snnz, trow.p);
         count_launch();
         P.trow = trow.p;
         P.ch = static_cast<int>(n);
-        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dense_smem)));
         const int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * (dense_smem <= 100 * 1024 ? 2 : 1));
-        sims_row_kernel<true><<<static_cast<unsigned>(grid), SIMS_WARPS * 32, dense_smem, s>>>(P);
+#define SIMS_DENSE_LAUNCH(W_, E_, D_)                                                                                                        \
+    do {                                                                                                                                      \
+        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<true, W_, E_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dense_smem))); \
+        sims_row_kernel<true, W_, E_, D_><<<static_cast<unsigned>(grid), W_ * 32, dense_smem, s>>>(P);                                       \
+    } while (0)
+        if (dense_cfg == 1) SIMS_DENSE_LAUNCH(8, 4, 4);
+        else if (dense_cfg == 2) SIMS_DENSE_LAUNCH(8, 3, 6);
+        else if (dense_cfg == 3) SIMS_DENSE_LAUNCH(4, 6, 3);
+        else if (dense_cfg == 4) SIMS_DENSE_LAUNCH(8, 2, 8);
+        else SIMS_DENSE_LAUNCH(16, 2, 8);
+#undef SIMS_DENSE_LAUNCH
     } else {
-        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(list_bytes)));
+        constexpr int SLAB_WARPS = 16;
+        const size_t list_bytes = static_cast<size_t>(SLAB_WARPS) * cap * sizeof(uint64_t);
+        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<false, SLAB_WARPS, 2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(list_bytes)));
         int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * 2);
         // bound the accumulator slabs to 8 GiB
         while (grid > 1 && static_cast<double>(grid) * n * 8.0 > 8.0 * (1ull << 30)) grid /= 2;
@@ -403,7 +784,7 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
         SPHB_CUDA(touched.alloc(static_cast<size_t>(grid) * n, s));
         SPHB_CUDA(cudaMemsetAsync(acc.p, 0, static_cast<size_t>(grid) * n * sizeof(float), s));
         P.acc = acc.p; P.touched = touched.p;
-        sims_row_kernel<false><<<static_cast<unsigned>(grid), SIMS_WARPS * 32, list_bytes, s>>>(P);
+        sims_row_kernel<false, SLAB_WARPS, 2, 8><<<static_cast<unsigned>(grid), SLAB_WARPS * 32, list_bytes, s>>>(P);
     }
     count_launch();
     SPHB_CUDA(cudaGetLastError());
