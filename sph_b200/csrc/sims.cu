@@ -4,15 +4,12 @@
 //
 // Row-wise Gustavson SpGEMM that never materialises the product: S = sqrt(prune(A)) and its
 // transpose (built by one radix sort on (column, row)) stay in HBM/L2; one persistent CTA per output
-// row accumulates s_ic * s_jc into a dense accumulator row, then selects the bottom k of (-ln C, column)
-// with per-warp sorted lists and a final block-wide bitonic merge.  Two accumulator homes:
-//   DENSE (n <= what fits beside the lists in 220 KB of shared memory, ~52 k components): the row lives in
-//     SHARED memory and the CTA walks the row's entries c in order, one column of Sᵀ at a time — the rows j
-//     of a column are distinct, so the 256 threads update distinct accumulators with plain LDS / FADD / STS
-//     (no atomics; a barrier between columns), the (row, value) pairs of the next 16 column segments are in
-//     flight in registers while the current ones are added.  Every C[i][j] is therefore summed in ascending c
-//     — the order of the reference's sparse dot — and the result is deterministic.  Round 1's version of this
-//     kernel (float atomics with return into an L2 slab) ran 381 ms at C2 level 1 (ncu); see DESIGN.md §4.5.
+// row accumulates s_ic * s_jc into a dense accumulator row, then selects the bottom k of (-ln C, column).  Two accumulator homes:
+//   CLASS (n up to ~52 k components: 16 x ceil(n / 16) floats beside the lists in 220 KB of SHARED memory): sims_class_kernel
+//     below — rows j split into 16 classes (j mod 16), one warp per class, class-major transpose, no block barrier and no
+//     atomics inside a row; every C[i][j] is summed in ascending c (the order of the reference's sparse dot), deterministic.
+//     History at C2 level 1: L2 float atomics 381 ms (round 1) -> one column at a time with a block barrier per column 137 ->
+//     register pipeline 91 -> class-partitioned 85 -> histogram candidate selection 56 -> 8-byte (row, value) records 52 ms.
 //   SLAB (larger n): a private slab per CTA in HBM/L2, float atomics, first-touch list (the round-1 kernel).
 // Candidates are screened with a fast fp32 log before the reference's fp64 log is evaluated (D is monotone in C,
 // so anything whose approximate D exceeds the running k-th D by more than 1e-4 cannot enter the list).
@@ -99,14 +96,12 @@ struct SimsParams {
     const float* sval;
     const int64_t* colptr;    // Sᵀ: for column c the entries tkeys/tval[colptr[c] .. colptr[c+1]) (row = low 32 bits of the key)
     const uint64_t* tkeys;
-    const uint32_t* trow;     // low halves of tkeys (row ids), 4 B per product for the DENSE kernel
     const float* tval;
     float prune_val;
     int hdi;                  // 1: createSimilaritiesHDI semantics, 0: createSimilaritiesEigen + bottom-k conversion
     int k, cap;               // cap: per-warp list capacity, power of two >= k + 32
     float* acc;               // SLAB: [grid][n] zero-initialised accumulator slabs
     uint32_t* touched;        // SLAB: [grid][n]
-    int ch;                   // DENSE: accumulator floats in shared memory (>= n)
     uint32_t* out_cols;       // [n][k], padded 0xFFFFFFFF
     float* out_vals;          // [n][k]
     int32_t* row_nnz;
@@ -116,129 +111,43 @@ struct SimsParams {
 static int g_force_slab = 0;
 void sims_force_slab(int on) { g_force_slab = on; }
 
-constexpr int SIMS_EB = 512;   // DENSE: row entries staged per batch (column start, length, s_ic)
+constexpr int SIMS_EB = 512;   // class kernel: row entries staged per batch (column, s_ic)
 
-// DENSE: SIMS_D columns per register group (two groups: one being added, one in flight), E entries of every column per thread
-template <int SIMS_D, int E>
-struct ColGroup {
-    uint32_t j[SIMS_D][E];
-    float v[SIMS_D][E], s[SIMS_D];
-};
 
-__global__ void sims_split_rows(const uint64_t* __restrict__ keys, int64_t num, uint32_t* __restrict__ rows) {
-    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < num; t += static_cast<int64_t>(gridDim.x) * blockDim.x)
-        rows[t] = static_cast<uint32_t>(keys[t]);
-}
+constexpr int SIMS_WARPS = 16;
 
-template <bool DENSE, int SIMS_WARPS, int E, int SIMS_D>
+// SLAB flavour (n too large for a shared-memory accumulator row): a private slab per CTA in HBM/L2, float atomics with return,
+// first-touch list.
 __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsParams P) {
-    extern __shared__ uint64_t sm_keys[];  // SIMS_WARPS * cap keys | DENSE: entry batch | accumulator row
+    extern __shared__ uint64_t sm_keys[];  // SIMS_WARPS * cap keys
     __shared__ unsigned int s_touched, s_valid, s_nsel;
     __shared__ double s_sum;
-    constexpr int THREADS = SIMS_WARPS * 32;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float* acc = DENSE ? nullptr : P.acc + static_cast<size_t>(blockIdx.x) * P.n;
-    uint32_t* touched = DENSE ? nullptr : P.touched + static_cast<size_t>(blockIdx.x) * P.n;
+    float* acc = P.acc + static_cast<size_t>(blockIdx.x) * P.n;
+    uint32_t* touched = P.touched + static_cast<size_t>(blockIdx.x) * P.n;
     uint64_t* mylist = sm_keys + static_cast<size_t>(warp) * P.cap;
-    // DENSE shared-memory carve-up behind the lists
-    int64_t* e_cb = reinterpret_cast<int64_t*>(sm_keys + static_cast<size_t>(SIMS_WARPS) * P.cap);
-    int* e_len = reinterpret_cast<int*>(e_cb + SIMS_EB);
-    float* e_sic = reinterpret_cast<float*>(e_len + SIMS_EB);
-    float* sacc = e_sic + SIMS_EB;
     const int k = P.k, cap = P.cap;
-    if constexpr (DENSE) {
-        for (int t = threadIdx.x; t < P.ch; t += THREADS) sacc[t] = 0.f;
-    }
     for (int64_t i = blockIdx.x; i < P.n; i += gridDim.x) {
         if (threadIdx.x == 0) { s_touched = 0; s_valid = 0; s_nsel = 0; s_sum = 0.0; }
         __syncthreads();
         const int64_t rb = P.srowptr[i], re = P.srowptr[i + 1];
-        if constexpr (DENSE) {
-            // ---- 1. expand, one column of Sᵀ at a time (distinct rows j within a column: no atomics)
-            for (int64_t eb = rb; eb < re; eb += SIMS_EB) {
-                const int ne = static_cast<int>(min(static_cast<int64_t>(SIMS_EB), re - eb));
-                for (int t = threadIdx.x; t < ne; t += THREADS) {
-                    const uint32_t c = P.scol[eb + t];
-                    const int64_t cb = P.colptr[c];
-                    e_cb[t] = cb;
-                    e_len[t] = static_cast<int>(P.colptr[c + 1] - cb);
-                    e_sic[t] = P.sval[eb + t];
-                }
-                __syncthreads();
-                // register-staged software pipeline over the columns of this batch: while group A (SIMS_D columns) is
-                // added, the (row, value) pairs of group B are in flight.  A thread holds the first two elements of
-                // every column of a group (columns longer than 2 * THREADS finish with direct loads); the two groups
-                // are separate objects so that every register is addressed statically.  (The first version of this
-                // loop drove a flag-per-slot cursor: ncu counted 111 warp instructions per 32 products, issue-bound.)
-                ColGroup<SIMS_D, E> ga, gb;
-                auto load_group = [&](ColGroup<SIMS_D, E>& G, int c0) {
-#pragma unroll
-                    for (int d = 0; d < SIMS_D; ++d) {
-                        const int c = c0 + d;
-                        if (c < ne) {  // uniform
-                            const int len = e_len[c];
-                            const int64_t cb = e_cb[c];
-                            G.s[d] = e_sic[c];
-#pragma unroll
-                            for (int e = 0; e < E; ++e) {
-                                const int off = e * THREADS + static_cast<int>(threadIdx.x);
-                                if (off < len) {
-                                    G.j[d][e] = __ldg(P.trow + cb + off);
-                                    G.v[d][e] = __ldg(P.tval + cb + off);
-                                }
-                            }
-                        }
-                    }
-                };
-                auto consume_group = [&](const ColGroup<SIMS_D, E>& G, int c0) {
-#pragma unroll
-                    for (int d = 0; d < SIMS_D; ++d) {
-                        const int c = c0 + d;
-                        if (c >= ne) break;  // uniform
-                        const int len = e_len[c];
-#pragma unroll
-                        for (int e = 0; e < E; ++e) {
-                            const int off = e * THREADS + static_cast<int>(threadIdx.x);
-                            if (off < len) sacc[G.j[d][e]] = __fadd_rn(sacc[G.j[d][e]], __fmul_rn(G.s[d], G.v[d][e]));
-                        }
-                        if (len > E * THREADS) {  // uniform; the rows of one column are distinct, no barrier inside a column
-                            const int64_t cb = e_cb[c];
-                            for (int off = E * THREADS + static_cast<int>(threadIdx.x); off < len; off += THREADS) {
-                                const uint32_t j = __ldg(P.trow + cb + off);
-                                sacc[j] = __fadd_rn(sacc[j], __fmul_rn(G.s[d], __ldg(P.tval + cb + off)));
-                            }
-                        }
-                        __syncthreads();  // the next column may hit the same rows from other threads
-                    }
-                };
-                load_group(ga, 0);
-                for (int c0 = 0; c0 < ne; c0 += 2 * SIMS_D) {
-                    load_group(gb, c0 + SIMS_D);
-                    consume_group(ga, c0);
-                    load_group(ga, c0 + 2 * SIMS_D);
-                    consume_group(gb, c0 + SIMS_D);
-                }
-                __syncthreads();  // e_* are rewritten by the next batch
+        // ---- 1. expand: C[i][j] += s_ic * s_jc, one warp per entry c of row i, lanes over column c of S
+        for (int64_t e = rb + warp; e < re; e += SIMS_WARPS) {
+            const uint32_t c = P.scol[e];
+            const float sic = P.sval[e];
+            const int64_t cb = P.colptr[c], ce = P.colptr[c + 1];
+            for (int64_t f = cb + lane; f < ce; f += 32) {
+                const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
+                const float old = atomicAdd(acc + j, sic * P.tval[f]);
+                if (old == 0.f) touched[atomicAdd(&s_touched, 1u)] = j;
             }
-        } else {
-            // ---- 1. expand: C[i][j] += s_ic * s_jc, one warp per entry c of row i, lanes over column c of S
-            for (int64_t e = rb + warp; e < re; e += SIMS_WARPS) {
-                const uint32_t c = P.scol[e];
-                const float sic = P.sval[e];
-                const int64_t cb = P.colptr[c], ce = P.colptr[c + 1];
-                for (int64_t f = cb + lane; f < ce; f += 32) {
-                    const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
-                    const float old = atomicAdd(acc + j, sic * P.tval[f]);
-                    if (old == 0.f) touched[atomicAdd(&s_touched, 1u)] = j;
-                }
-            }
-            __syncthreads();
         }
-        const unsigned int T = DENSE ? static_cast<unsigned int>(P.n) : s_touched;
+        __syncthreads();
+        const unsigned int T = s_touched;
         // ---- 2. (Eigen variant) number of entries that survive the product prune, diagonal included
         if (!P.hdi) {
             unsigned int v = 0;
-            for (unsigned int t = threadIdx.x; t < T; t += blockDim.x) v += eigen_keep(DENSE ? sacc[t] : acc[touched[t]], P.prune_val) ? 1u : 0u;
+            for (unsigned int t = threadIdx.x; t < T; t += blockDim.x) v += eigen_keep(acc[touched[t]], P.prune_val) ? 1u : 0u;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
             if (lane == 0 && v) atomicAdd(&s_valid, v);
@@ -254,10 +163,9 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
             bool pass = false;
             uint64_t key = ~0ull;
             if (t < T) {
-                const uint32_t j = DENSE ? t : touched[t];
-                float c;
-                if constexpr (DENSE) { c = sacc[t]; sacc[t] = 0.f; }
-                else { c = acc[j]; acc[j] = 0.f; }
+                const uint32_t j = touched[t];
+                const float c = acc[j];
+                acc[j] = 0.f;
                 const bool diag = static_cast<int64_t>(j) == i;
                 if (eigen_keep(c, P.prune_val) && (diag || c == 1.f || !(-__logf(c) > dk_screen))) {
                     float dv;
@@ -354,11 +262,16 @@ constexpr int SC_D = 4;   // columns per register group
 constexpr int SC_E = 2;   // entries of a (column, class) segment per lane held in registers (segments average n_col / 16)
 
 struct ClassGroup {
-    uint32_t j[SC_D][SC_E];
-    float v[SC_D][SC_E], s[SC_D];
+    uint2 r[SC_D][SC_E];  // (row j, value bits) records of the class-major transpose
+    float s[SC_D];
     int len[SC_D];
     int64_t b[SC_D];
 };
+
+__global__ void sims_zip_records(const uint64_t* __restrict__ keys, const float* __restrict__ val, int64_t num, uint2* __restrict__ rec) {
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < num; t += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        rec[t] = make_uint2(static_cast<uint32_t>(keys[t]), __float_as_uint(val[t]));
+}
 
 __global__ void sims_class_ptr(const uint64_t* __restrict__ keys, int64_t num, int64_t n, int cbits, int64_t* __restrict__ cptr) {
     const int64_t total = static_cast<int64_t>(SC_WARPS) * (n + 1);
@@ -375,7 +288,11 @@ __global__ void sims_class_keys(const uint64_t* __restrict__ tkeys, int64_t num,
     }
 }
 
-__global__ void __launch_bounds__(SC_WARPS * 32) sims_class_kernel(const SimsParams P, const int64_t* __restrict__ cptr, int CH) {
+// Two deeper-prefetch variants of the expansion were tried and lost against the register pipeline below (52 ms at C2 level 1):
+// one cp.async.bulk + mbarrier per segment into a per-warp byte ring (139 ms: 300-byte bulk copies are far too small for the
+// TMA unit) and 16-byte cp.async copies into a three-stage per-warp buffer (81 ms: the bookkeeping per stage costs more than the
+// extra bytes in flight gain).  Both are deleted; tools/r02_sims_ab.sh holds the A/B.
+__global__ void __launch_bounds__(SC_WARPS * 32) sims_class_kernel(const SimsParams P, const int64_t* __restrict__ cptr, const uint2* __restrict__ trec, int CH) {
     extern __shared__ uint64_t sm_keys[];  // SC_WARPS * cap keys | entry batch | SC_WARPS * CH accumulators
     __shared__ unsigned int s_valid, s_nsel, s_ncand, s_bin, s_above, s_nreg;
     __shared__ double s_sum;
@@ -427,10 +344,7 @@ __global__ void __launch_bounds__(SC_WARPS * 32) sims_class_kernel(const SimsPar
 #pragma unroll
                             for (int e = 0; e < SC_E; ++e) {
                                 const int off = e * 32 + lane;
-                                if (off < G.len[d]) {
-                                    G.j[d][e] = __ldg(P.trow + G.b[d] + off);
-                                    G.v[d][e] = __ldg(P.tval + G.b[d] + off);
-                                }
+                                if (off < G.len[d]) G.r[d][e] = __ldg(trec + G.b[d] + off);
                             }
                         }
                     }
@@ -444,13 +358,13 @@ __global__ void __launch_bounds__(SC_WARPS * 32) sims_class_kernel(const SimsPar
                         for (int e = 0; e < SC_E; ++e) {
                             const int off = e * 32 + lane;
                             if (off < len) {
-                                const uint32_t q = G.j[d][e] >> 4;
-                                myacc[q] = __fadd_rn(myacc[q], __fmul_rn(G.s[d], G.v[d][e]));
+                                const uint32_t q = G.r[d][e].x >> 4;
+                                myacc[q] = __fadd_rn(myacc[q], __fmul_rn(G.s[d], __uint_as_float(G.r[d][e].y)));
                             }
                         }
                         for (int off = SC_E * 32 + lane; off < len; off += 32) {  // long segments: the rows of one column are distinct
-                            const uint32_t q = __ldg(P.trow + G.b[d] + off) >> 4;
-                            myacc[q] = __fadd_rn(myacc[q], __fmul_rn(G.s[d], __ldg(P.tval + G.b[d] + off)));
+                            const uint2 r = __ldg(trec + G.b[d] + off);
+                            myacc[r.x >> 4] = __fadd_rn(myacc[r.x >> 4], __fmul_rn(G.s[d], __uint_as_float(r.y)));
                         }
                         __syncwarp();  // the next column may hit the same rows from other lanes
                     }
@@ -717,16 +631,12 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
     P.prune_val = prune_val; P.hdi = hdi ? 1 : 0; P.k = static_cast<int>(k); P.cap = cap;
     P.out_cols = d_out_cols; P.out_vals = d_out_vals; P.row_nnz = d_row_nnz;
     DevBuf<float> acc;
-    DevBuf<uint32_t> touched, trow;
-    int dense_cfg = 0;
-#ifdef SPHB_KNN_TUNING
-    if (const char* e = getenv("SPHB_SIMS_CFG")) dense_cfg = atoi(e);
-#endif
+    DevBuf<uint32_t> touched;
     const int cbits = bits_for(static_cast<uint64_t>(n));
     const int CH = static_cast<int>((n + SC_WARPS - 1) / SC_WARPS);
     const size_t class_smem = static_cast<size_t>(SC_WARPS) * cap * sizeof(uint64_t) + static_cast<size_t>(SIMS_EB) * 8 +
                               static_cast<size_t>(SC_WARPS) * CH * sizeof(float);
-    if (dense_cfg == 0 && class_smem <= 220 * 1024 && cbits <= 28 && !g_force_slab) {
+    if (class_smem <= 220 * 1024 && cbits <= 28 && !g_force_slab) {
         // class-major transpose: (row mod 16, column, row)
         DevBuf<uint64_t> ck0, ck1;
         DevBuf<float> cval;
@@ -735,48 +645,26 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
         SPHB_CUDA(ck1.alloc(std::max<int64_t>(snnz, 1), s));
         SPHB_CUDA(cval.alloc(std::max<int64_t>(snnz, 1), s));
         SPHB_CUDA(cptr.alloc(static_cast<size_t>(SC_WARPS) * (n + 1), s));
-        SPHB_CUDA(trow.alloc(std::max<int64_t>(snnz, 1), s));
+        DevBuf<uint2> trec;
+        SPHB_CUDA(trec.alloc(std::max<int64_t>(snnz, 1), s));
         sims_class_keys<<<g, 256, 0, s>>>(tk1.p, snnz, cbits, ck0.p);
         count_launch();
         // tk1 / tval are (column, row)-sorted already, so a stable sort on the 4 class bits alone finishes the job
         if (int rc = sort_pairs_bits<float>(ck0.p, ck1.p, tval.p, cval.p, snnz, 32 + cbits, 36 + cbits, s)) return rc;
         sims_class_ptr<<<g, 256, 0, s>>>(ck1.p, snnz, n, cbits, cptr.p);
-        sims_split_rows<<<g, 256, 0, s>>>(ck1.p, snnz, trow.p);
+        sims_zip_records<<<g, 256, 0, s>>>(ck1.p, cval.p, snnz, trec.p);
         count_launch(2);
-        P.trow = trow.p;
-        P.tval = cval.p;
         SPHB_CUDA(cudaFuncSetAttribute(sims_class_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(class_smem)));
         const int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * (class_smem <= 100 * 1024 ? 2 : 1));
-        sims_class_kernel<<<static_cast<unsigned>(grid), SC_WARPS * 32, class_smem, s>>>(P, cptr.p, CH);
+        sims_class_kernel<<<static_cast<unsigned>(grid), SC_WARPS * 32, class_smem, s>>>(P, cptr.p, trec.p, CH);
         count_launch();
         SPHB_CUDA(cudaGetLastError());
         SPHB_CUDA(cudaStreamSynchronize(s));  // the class-major buffers are released on return
         return 0;
     }
-    const int dense_warps = dense_cfg == 3 ? 4 : ((dense_cfg == 0 || dense_cfg == 10) ? 16 : 8);
-    const size_t dense_smem = static_cast<size_t>(dense_warps) * cap * sizeof(uint64_t) + static_cast<size_t>(SIMS_EB) * 16 + static_cast<size_t>(n) * sizeof(float);
-    if (dense_smem <= 220 * 1024 && !g_force_slab) {
-        SPHB_CUDA(trow.alloc(std::max<int64_t>(snnz, 1), s));
-        sims_split_rows<<<g, 256, 0, s>>>(tk1.p, snnz, trow.p);
-        count_launch();
-        P.trow = trow.p;
-        P.ch = static_cast<int>(n);
-        const int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * (dense_smem <= 100 * 1024 ? 2 : 1));
-#define SIMS_DENSE_LAUNCH(W_, E_, D_)                                                                                                        \
-    do {                                                                                                                                      \
-        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<true, W_, E_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dense_smem))); \
-        sims_row_kernel<true, W_, E_, D_><<<static_cast<unsigned>(grid), W_ * 32, dense_smem, s>>>(P);                                       \
-    } while (0)
-        if (dense_cfg == 1) SIMS_DENSE_LAUNCH(8, 4, 4);
-        else if (dense_cfg == 2) SIMS_DENSE_LAUNCH(8, 3, 6);
-        else if (dense_cfg == 3) SIMS_DENSE_LAUNCH(4, 6, 3);
-        else if (dense_cfg == 4) SIMS_DENSE_LAUNCH(8, 2, 8);
-        else SIMS_DENSE_LAUNCH(16, 2, 8);
-#undef SIMS_DENSE_LAUNCH
-    } else {
-        constexpr int SLAB_WARPS = 16;
-        const size_t list_bytes = static_cast<size_t>(SLAB_WARPS) * cap * sizeof(uint64_t);
-        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<false, SLAB_WARPS, 2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(list_bytes)));
+    {
+        const size_t list_bytes = static_cast<size_t>(SIMS_WARPS) * cap * sizeof(uint64_t);
+        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(list_bytes)));
         int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * 2);
         // bound the accumulator slabs to 8 GiB
         while (grid > 1 && static_cast<double>(grid) * n * 8.0 > 8.0 * (1ull << 30)) grid /= 2;
@@ -784,7 +672,7 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
         SPHB_CUDA(touched.alloc(static_cast<size_t>(grid) * n, s));
         SPHB_CUDA(cudaMemsetAsync(acc.p, 0, static_cast<size_t>(grid) * n * sizeof(float), s));
         P.acc = acc.p; P.touched = touched.p;
-        sims_row_kernel<false, SLAB_WARPS, 2, 8><<<static_cast<unsigned>(grid), SLAB_WARPS * 32, list_bytes, s>>>(P);
+        sims_row_kernel<<<static_cast<unsigned>(grid), SIMS_WARPS * 32, list_bytes, s>>>(P);
     }
     count_launch();
     SPHB_CUDA(cudaGetLastError());
