@@ -141,6 +141,16 @@ SPHB_API int sphb_knn_graph_prow(const float* x, int64_t n, int d, int k, int me
 SPHB_API int sphb_knn_rows_noalloc_dev(const float* d_x, int64_t n, int d, int k, int metric, int l2_squared, const int64_t* d_rows,
                                        int64_t nrows, int64_t* d_ids, float* d_dist, void* stream);
 
+/* Single process, several GPUs: the same result as sphb_knn_graph_prow over the whole stack (q0 = 0, q1 = n), computed on the
+ * `num_devices` GPUs listed in `devices` from ONE call of one host thread — the form a drop-in for the single-threaded
+ * ComputeHierarchy::compute() (sph/ComputeHierarchy.cpp:262-276) needs on a multi-GPU box.  One worker thread per device:
+ * worker g uploads rows [g*ceil(n/G), (g+1)*ceil(n/G)) from `x`, the workers exchange their slabs device to device
+ * (cudaMemcpyPeerAsync; NVLink where peer access exists) so that every GPU holds the whole database, each searches its slab of
+ * query rows and writes its range of ids / dist / cols / vals.  Host-to-device traffic N*d*4 bytes in total.  Contexts are per
+ * host thread: the calling thread's own context (sphb_init, sphb_knn_last_stats, ...) is not touched by this call. */
+SPHB_API int sphb_knn_graph_prow_multi(const float* x, int64_t n, int d, int k, int metric, int l2_squared, float perplexity,
+                                       const int* devices, int num_devices, int64_t* ids, float* dist, uint32_t* cols, float* vals);
+
 /* ---- Stage B: perplexity-calibrated probability rows -------------------- */
 /*
  * Replaces utils::computeGaussianDistributions(const GraphBaseInterface&, vector<T>&, float)

@@ -51,6 +51,8 @@ SIGNATURES = {
                                             C.c_void_p]),
     "sphb_knn_last_overflow_rows": (C.c_int, [C.c_int, i64p, C.c_int64, i64p]),
     "sphb_knn_graph_prow": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int64, i64p, f32p, u32p, f32p]),
+    "sphb_knn_graph_prow_multi": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.POINTER(C.c_int), C.c_int, i64p, f32p, u32p,
+                                            f32p]),
     "sphb_prow_gaussian_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, C.c_float, u32p, f32p, f64p]),
     "sphb_prow_gaussian_graph_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sphb_prow_linear_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, u32p, f32p]),
@@ -214,6 +216,19 @@ def knn_graph_prow(x: np.ndarray, k: int, perplexity: float = 0.0, metric: int =
 
 
 # ------------------------------------------------------------------ Stage A
+def knn_graph_prow_multi(x: np.ndarray, k: int, devices, perplexity: float = 0.0, metric: int = METRIC_L2, l2_squared: bool = False, out=None):
+    """Stage A + level-0 P rows of the whole stack on the listed GPUs from one call (one worker thread per device)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, d = x.shape
+    if out is None:
+        out = (np.full((n, k), -1, np.int64), np.full((n, k), -1.0, np.float32), np.zeros((n, k - 1), np.uint32), np.zeros((n, k - 1), np.float32))
+    ids, dist, cols, vals = out
+    dev = (C.c_int * len(devices))(*devices)
+    _check(load().sphb_knn_graph_prow_multi(_p(x, f32p), n, d, k, metric, int(l2_squared), perplexity, dev, len(devices), _p(ids, i64p), _p(dist, f32p),
+                                            _p(cols, u32p), _p(vals, f32p)))
+    return ids, dist, cols, vals
+
+
 def knn_exact(x: np.ndarray, k: int, metric: int = METRIC_L2, l2_squared: bool = False, q0: int = 0, q1: int | None = None):
     """Exact kNN of rows [q0,q1) of x against all rows; returns (ids int64 [nq,k], dist float32 [nq,k])."""
     x = np.ascontiguousarray(x, dtype=np.float32)

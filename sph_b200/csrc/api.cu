@@ -3,14 +3,18 @@
 #include "common.cuh"
 
 #include <atomic>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
 #include <vector>
 #include <algorithm>
 
 namespace sphb {
 
-static Context g_ctx;
-static std::string g_err;
+// One context per HOST THREAD: a thread binds a device with sphb_init (or lazily to the current device) and owns a stream; the
+// multi-device entry point below drives every GPU from its own worker thread, each with its own context.
+static thread_local Context g_ctx;
+static thread_local std::string g_err;
 static std::atomic<int64_t> g_launches{0};
 
 Context& ctx() { return g_ctx; }
@@ -90,6 +94,20 @@ void ws_trim() {
     g_ws_free.clear();
     g_ws_idle_bytes = 0;
 }
+// only the idle blocks of one stream (a thread shutting down its own context leaves the other threads' caches alone)
+static void ws_trim_stream(cudaStream_t stream) {
+    std::lock_guard<std::mutex> lk(g_ws_mu);
+    size_t w = 0;
+    for (size_t i = 0; i < g_ws_free.size(); ++i) {
+        if (g_ws_free[i].stream == stream) {
+            cudaFreeAsync(g_ws_free[i].p, stream);
+            g_ws_idle_bytes -= g_ws_free[i].bytes;
+        } else {
+            g_ws_free[w++] = g_ws_free[i];
+        }
+    }
+    g_ws_free.resize(w);
+}
 
 // kernels / launchers implemented in the other translation units
 int knn_simt_launch(const float*, int64_t, int, int, int, int, int64_t, int64_t, const int64_t*, const int*, int64_t, int64_t*, float*, cudaStream_t);
@@ -166,7 +184,8 @@ SPHB_API int sphb_init(int device) {
     SPHB_CUDA(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) return fail(SPHB_ERR_UNSUPPORTED, std::string("sm_100a build, found ") + prop.name);
     if (g_ctx.stream) {
-        sphb::ws_trim();  // cached blocks are tied to the stream they were released on
+        sphb::ws_trim_stream(g_ctx.stream);  // cached blocks are tied to the stream they were released on
+        cudaStreamSynchronize(g_ctx.stream);
         cudaStreamDestroy(g_ctx.stream);
     }
     SPHB_CUDA(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
@@ -185,7 +204,8 @@ SPHB_API int sphb_init(int device) {
 SPHB_API void sphb_shutdown(void) {
     if (!g_ctx.ready) return;
     cudaStreamSynchronize(g_ctx.stream);
-    sphb::ws_trim();
+    sphb::ws_trim_stream(g_ctx.stream);
+    cudaStreamSynchronize(g_ctx.stream);
     cudaStreamDestroy(g_ctx.stream);
     g_ctx.stream = nullptr;
     cudaMemPool_t pool;
@@ -527,6 +547,123 @@ SPHB_API int sphb_prow_gaussian_flat(const float* dist, int64_t n, int k, double
     if (int rc = prow_flat_launch(dd.p, n, k, perplexity, dt.p, s)) return rc;
     SPHB_CUDA(cudaMemcpyAsync(temp, dt.p, nk * sizeof(float), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+
+// ---------------------------------------------------------------- single process, several GPUs
+// The reference calls ComputeHierarchy::compute() from ONE host thread (sph/ComputeHierarchy.cpp:262-276); a drop-in for that
+// thread cannot ask it to become one process per GPU.  sphb_knn_graph_prow_multi takes the same host buffers as
+// sphb_knn_graph_prow plus a device list and runs one worker thread per device: worker g uploads ONLY its N/G rows of the stack
+// from host memory, the workers exchange their slabs device to device (cudaMemcpyPeerAsync: NVLink where peer access exists) so
+// that every GPU holds the whole database, then each searches its slab of query rows, builds its P rows and copies its four
+// result slabs into its range of the caller's buffers.  Host-to-device traffic is N*d*4 bytes in total, as in the
+// one-process-per-GPU path (sph_b200/multigpu.py), and there is no data-path collective on the result side.
+namespace {
+struct MultiBarrier {
+    std::mutex mu;
+    std::condition_variable cv;
+    int count = 0, generation = 0, parties;
+    explicit MultiBarrier(int p) : parties(p) {}
+    void wait() {
+        std::unique_lock<std::mutex> lk(mu);
+        const int gen = generation;
+        if (++count == parties) {
+            count = 0;
+            ++generation;
+            cv.notify_all();
+        } else {
+            cv.wait(lk, [&] { return gen != generation; });
+        }
+    }
+};
+}  // namespace
+
+SPHB_API int sphb_knn_graph_prow_multi(const float* x, int64_t n, int d, int k, int metric, int l2_squared, float perplexity, const int* devices,
+                                       int num_devices, int64_t* ids, float* dist, uint32_t* cols, float* vals) {
+    if (!x || !ids || !dist || !cols || !vals || !devices) return fail(SPHB_ERR_INVALID, "knn_graph_prow_multi: null pointer");
+    if (n <= 0 || d <= 0 || k < 2 || num_devices < 1 || num_devices > 64) return fail(SPHB_ERR_INVALID, "knn_graph_prow_multi: bad sizes");
+    const int G = num_devices;
+    const int64_t chunk = (n + G - 1) / G;
+    std::vector<float*> dx(G, nullptr);
+    std::vector<cudaStream_t> streams(G, nullptr);
+    std::vector<int> rcs(G, SPHB_OK);
+    std::vector<std::string> errs(G);
+    MultiBarrier bar(G);
+    auto worker = [&](int g) {
+        int rc = sphb_init(devices[g]);
+        const int64_t q0 = std::min<int64_t>(n, g * chunk), q1 = std::min<int64_t>(n, q0 + chunk), nq = q1 - q0;
+        DevBuf<float> xall, dd, dv;
+        DevBuf<int64_t> di;
+        DevBuf<uint32_t> dc;
+        cudaStream_t s = nullptr;
+        auto check = [&](cudaError_t e, const char* what) {
+            if (rc == SPHB_OK && e != cudaSuccess) rc = fail(SPHB_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+        };
+        if (rc == SPHB_OK) {
+            s = g_ctx.stream;
+            check(xall.alloc(static_cast<size_t>(n) * d, s), "alloc stack");
+            if (rc == SPHB_OK && nq > 0)
+                check(cudaMemcpyAsync(xall.p + q0 * d, x + q0 * d, static_cast<size_t>(nq) * d * sizeof(float), cudaMemcpyHostToDevice, s), "H2D slab");
+            check(cudaStreamSynchronize(s), "H2D slab");
+        }
+        dx[g] = xall.p;
+        streams[g] = s;
+        bar.wait();  // every worker's slab is in place (or it failed: rcs is checked after the exchange barrier)
+        rcs[g] = rc;
+        bar.wait();
+        bool all_ok = true;
+        for (int p = 0; p < G; ++p) all_ok &= rcs[p] == SPHB_OK;
+        if (all_ok) {
+            // all-gather by peer copies: pull every other worker's slab
+            for (int o = 1; o < G && rc == SPHB_OK; ++o) {
+                const int p = (g + o) % G;
+                const int64_t p0 = std::min<int64_t>(n, p * chunk), p1 = std::min<int64_t>(n, p0 + chunk);
+                if (p1 <= p0) continue;
+                if (devices[p] != devices[g]) {
+                    int can = 0;
+                    cudaDeviceCanAccessPeer(&can, devices[g], devices[p]);
+                    if (can) {
+                        const cudaError_t e = cudaDeviceEnablePeerAccess(devices[p], 0);
+                        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) check(e, "enable peer access");
+                        cudaGetLastError();
+                    }
+                }
+                check(cudaMemcpyPeerAsync(xall.p + p0 * d, devices[g], dx[p] + p0 * d, devices[p], static_cast<size_t>(p1 - p0) * d * sizeof(float), s),
+                      "peer copy");
+            }
+            check(cudaStreamSynchronize(s), "peer copy");
+        }
+        bar.wait();  // nobody releases its copy of the stack while a peer still reads it
+        if (all_ok && rc == SPHB_OK && nq > 0) {
+            const size_t nk = static_cast<size_t>(nq) * k, ne = static_cast<size_t>(nq) * (k - 1);
+            check(di.alloc(nk, s), "alloc");
+            check(dd.alloc(nk, s), "alloc");
+            check(dc.alloc(ne, s), "alloc");
+            check(dv.alloc(ne, s), "alloc");
+            if (rc == SPHB_OK) rc = sphb_knn_exact_dev(xall.p, n, d, k, metric, l2_squared, q0, q1, di.p, dd.p, s);
+            if (rc == SPHB_OK) rc = prow_graph_launch(di.p, dd.p, nq, k, perplexity, 0, dc.p, dv.p, nullptr, s);
+            if (rc == SPHB_OK) {
+                check(cudaMemcpyAsync(ids + q0 * k, di.p, nk * sizeof(int64_t), cudaMemcpyDeviceToHost, s), "D2H");
+                check(cudaMemcpyAsync(dist + q0 * k, dd.p, nk * sizeof(float), cudaMemcpyDeviceToHost, s), "D2H");
+                check(cudaMemcpyAsync(cols + q0 * (k - 1), dc.p, ne * sizeof(uint32_t), cudaMemcpyDeviceToHost, s), "D2H");
+                check(cudaMemcpyAsync(vals + q0 * (k - 1), dv.p, ne * sizeof(float), cudaMemcpyDeviceToHost, s), "D2H");
+                check(cudaStreamSynchronize(s), "D2H");
+            }
+        }
+        if (rc != SPHB_OK) errs[g] = g_err;
+        rcs[g] = rc;
+        // buffers are released here (stream-ordered), the worker's context stays cached in its thread and dies with it
+        xall.release(); di.release(); dd.release(); dc.release(); dv.release();
+        if (s) cudaStreamSynchronize(s);
+        sphb_shutdown();
+    };
+    std::vector<std::thread> threads;
+    threads.reserve(G);
+    for (int g = 0; g < G; ++g) threads.emplace_back(worker, g);
+    for (auto& t : threads) t.join();
+    for (int g = 0; g < G; ++g)
+        if (rcs[g] != SPHB_OK) return fail(rcs[g], "knn_graph_prow_multi: device " + std::to_string(devices[g]) + ": " + errs[g]);
     return SPHB_OK;
 }
 

@@ -1052,14 +1052,15 @@ static int next_pow2_i(int v) {
     return p;
 }
 
-static int64_t g_knn_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-static float g_knn_ms[4] = {0.f, 0.f, 0.f, 0.f};  // prep, main sweep(s), re-rank(s), fallback (CUDA events on the launching stream)
+// per host thread, like the context (api.cu): the workers of sphb_knn_graph_prow_multi run this file concurrently
+static thread_local int64_t g_knn_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+static thread_local float g_knn_ms[4] = {0.f, 0.f, 0.f, 0.f};  // prep, main sweep(s), re-rank(s), fallback (CUDA events on the launching stream)
 void knn_get_timing(float* ms4) { for (int i = 0; i < 4; ++i) ms4[i] = g_knn_ms[i]; }
 void knn_set_stats(const int64_t* s) { for (int i = 0; i < 8; ++i) g_knn_stats[i] = s[i]; }
 void knn_get_stats(int64_t* s) { for (int i = 0; i < 8; ++i) s[i] = g_knn_stats[i]; }
 // global ids of the rows of the last call that left the main sweep: [0] re-swept with the 3-product filter, [1] recomputed
 // by the exact SIMT kernel (parity checks sample them, bench.py "parity")
-static std::vector<int64_t> g_knn_ovf_rows[2];
+static thread_local std::vector<int64_t> g_knn_ovf_rows[2];
 void knn_clear_overflow_rows() { g_knn_ovf_rows[0].clear(); g_knn_ovf_rows[1].clear(); }
 const std::vector<int64_t>& knn_overflow_rows(int which) { return g_knn_ovf_rows[which ? 1 : 0]; }
 static int record_overflow_rows(int which, const int64_t* d_rows, int count, cudaStream_t stream) {

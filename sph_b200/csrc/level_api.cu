@@ -75,7 +75,7 @@ int max_row_len(int64_t n, const int64_t* d_rowptr, int* out, cudaStream_t s) {
 }
 
 // per-stage device times of the last sphb_level_prob_dist[_dev] call (CUDA events on its stream)
-float g_level_ms[5] = {0, 0, 0, 0, 0};
+thread_local float g_level_ms[5] = {0, 0, 0, 0, 0};
 
 struct StageTimer {
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

@@ -118,15 +118,24 @@ constexpr int SIMS_WARPS = 16;
 
 // SLAB flavour (n too large for a shared-memory accumulator row): a private slab per CTA in HBM/L2, float atomics with return,
 // first-touch list.
+// BITMAP (n bits fit beside the lists in shared memory, n up to ~1.6 M): the products are fire-and-forget reductions
+// (red.global.add.f32, no return value to wait for) and the rows touched are recorded in a shared-memory bitmap that is turned
+// into the first-touch list afterwards.  Without it (larger n) every product is an atomic WITH return whose old value tells the
+// first touch — the returning atomics bound the round-1 kernel at 1.8e10 products/s whatever the number of CTAs.
+template <bool BITMAP>
 __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsParams P) {
-    extern __shared__ uint64_t sm_keys[];  // SIMS_WARPS * cap keys
+    extern __shared__ uint64_t sm_keys[];  // SIMS_WARPS * cap keys | BITMAP: ceil(n / 32) words
     __shared__ unsigned int s_touched, s_valid, s_nsel;
     __shared__ double s_sum;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* acc = P.acc + static_cast<size_t>(blockIdx.x) * P.n;
     uint32_t* touched = P.touched + static_cast<size_t>(blockIdx.x) * P.n;
     uint64_t* mylist = sm_keys + static_cast<size_t>(warp) * P.cap;
+    uint32_t* bm = reinterpret_cast<uint32_t*>(sm_keys + static_cast<size_t>(SIMS_WARPS) * P.cap);
+    const int nwords = static_cast<int>((P.n + 31) >> 5);
     const int k = P.k, cap = P.cap;
+    if constexpr (BITMAP)
+        for (int t = threadIdx.x; t < nwords; t += blockDim.x) bm[t] = 0u;
     for (int64_t i = blockIdx.x; i < P.n; i += gridDim.x) {
         if (threadIdx.x == 0) { s_touched = 0; s_valid = 0; s_nsel = 0; s_sum = 0.0; }
         __syncthreads();
@@ -136,10 +145,35 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
             const uint32_t c = P.scol[e];
             const float sic = P.sval[e];
             const int64_t cb = P.colptr[c], ce = P.colptr[c + 1];
-            for (int64_t f = cb + lane; f < ce; f += 32) {
-                const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
-                const float old = atomicAdd(acc + j, sic * P.tval[f]);
-                if (old == 0.f) touched[atomicAdd(&s_touched, 1u)] = j;
+            if constexpr (BITMAP) {
+#pragma unroll 4
+                for (int64_t f = cb + lane; f < ce; f += 32) {
+                    const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
+                    atomicAdd(acc + j, sic * P.tval[f]);  // result unused: RED
+                    const uint32_t bit = 1u << (j & 31u);
+                    if (!(bm[j >> 5] & bit)) atomicOr(&bm[j >> 5], bit);
+                }
+            } else {
+                for (int64_t f = cb + lane; f < ce; f += 32) {
+                    const uint32_t j = static_cast<uint32_t>(P.tkeys[f]);
+                    const float old = atomicAdd(acc + j, sic * P.tval[f]);
+                    if (old == 0.f) touched[atomicAdd(&s_touched, 1u)] = j;
+                }
+            }
+        }
+        if constexpr (BITMAP) {
+            __threadfence();  // the reductions of this thread are performed before the accumulators are read back
+            __syncthreads();
+            for (int wi = threadIdx.x; wi < nwords; wi += blockDim.x) {
+                uint32_t bits = bm[wi];
+                if (bits) {
+                    bm[wi] = 0u;
+                    unsigned int at = atomicAdd(&s_touched, static_cast<unsigned int>(__popc(bits)));
+                    while (bits) {
+                        touched[at++] = (static_cast<uint32_t>(wi) << 5) | static_cast<uint32_t>(__ffs(bits) - 1);
+                        bits &= bits - 1;
+                    }
+                }
             }
         }
         __syncthreads();
@@ -147,7 +181,7 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
         // ---- 2. (Eigen variant) number of entries that survive the product prune, diagonal included
         if (!P.hdi) {
             unsigned int v = 0;
-            for (unsigned int t = threadIdx.x; t < T; t += blockDim.x) v += eigen_keep(acc[touched[t]], P.prune_val) ? 1u : 0u;
+            for (unsigned int t = threadIdx.x; t < T; t += blockDim.x) v += eigen_keep(__ldcg(acc + touched[t]), P.prune_val) ? 1u : 0u;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
             if (lane == 0 && v) atomicAdd(&s_valid, v);
@@ -164,7 +198,7 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
             uint64_t key = ~0ull;
             if (t < T) {
                 const uint32_t j = touched[t];
-                const float c = acc[j];
+                const float c = __ldcg(acc + j);
                 acc[j] = 0.f;
                 const bool diag = static_cast<int64_t>(j) == i;
                 if (eigen_keep(c, P.prune_val) && (diag || c == 1.f || !(-__logf(c) > dk_screen))) {
@@ -664,15 +698,24 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
     }
     {
         const size_t list_bytes = static_cast<size_t>(SIMS_WARPS) * cap * sizeof(uint64_t);
-        SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(list_bytes)));
+        const size_t bitmap_bytes = static_cast<size_t>((n + 31) / 32) * 4;
+        bool bitmap = list_bytes + bitmap_bytes <= 200 * 1024;
+#ifdef SPHB_KNN_TUNING
+        if (const char* e = getenv("SPHB_SIMS_BITMAP")) bitmap = bitmap && atoi(e) != 0;
+#endif
+        const size_t slab_smem = list_bytes + (bitmap ? bitmap_bytes : 0);
+        if (bitmap) SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(slab_smem)));
+        else SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(slab_smem)));
         int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * 2);
-        // bound the accumulator slabs to 8 GiB
+        // bound the accumulator slabs to 8 GiB.  (Keeping the slabs L2-resident by running fewer CTAs does not help: 768 x 768 x 128
+        // level 1, 296 / 136 / 68 CTAs: 9.2 / 10.4 / 11.6 s — the returning atomics, not L2 misses, were the bound.)
         while (grid > 1 && static_cast<double>(grid) * n * 8.0 > 8.0 * (1ull << 30)) grid /= 2;
         SPHB_CUDA(acc.alloc(static_cast<size_t>(grid) * n, s));
         SPHB_CUDA(touched.alloc(static_cast<size_t>(grid) * n, s));
         SPHB_CUDA(cudaMemsetAsync(acc.p, 0, static_cast<size_t>(grid) * n * sizeof(float), s));
         P.acc = acc.p; P.touched = touched.p;
-        sims_row_kernel<<<static_cast<unsigned>(grid), SIMS_WARPS * 32, list_bytes, s>>>(P);
+        if (bitmap) sims_row_kernel<true><<<static_cast<unsigned>(grid), SIMS_WARPS * 32, slab_smem, s>>>(P);
+        else sims_row_kernel<false><<<static_cast<unsigned>(grid), SIMS_WARPS * 32, slab_smem, s>>>(P);
     }
     count_launch();
     SPHB_CUDA(cudaGetLastError());

@@ -31,12 +31,17 @@ def main():
     ap.add_argument("--band-rows", type=int, default=64, help="image rows per band (even)")
     ap.add_argument("--parity-rows", type=int, default=256)
     ap.add_argument("--out", default="")
+    ap.add_argument("--shape", default="", help="h,w,d,endmembers,seed instead of a named workload")
+    ap.add_argument("--skip-knn-timing", action="store_true")
     args = ap.parse_args()
 
     import torch
     from sph_b200 import capi, host, synth
     import bench
 
+    if args.shape:
+        bench.SHAPES["custom"] = tuple(int(v) for v in args.shape.split(","))
+        args.workload = "custom"
     h, w, d, M, seed = bench.SHAPES[args.workload]
     k = bench.K_NEIGHBOURS
     n = h * w
@@ -88,7 +93,7 @@ def main():
     mrp_b = torch.empty(n1 + 1, dtype=torch.int64, device="cuda")
     mc_b = torch.empty(cap_w, dtype=torch.int32, device="cuda")
     mv_b = torch.empty(cap_w, dtype=torch.float32, device="cuda")
-    est = int(min(n1 * 1400, 2 ** 31 - 1))  # the level call counts entries in 32 bits
+    est = int(n1 * 4 * 1350 // 2)  # a merged row holds at most 4 x W x L entries; half of that is ample
     mc = torch.empty(est, dtype=torch.int32, device="cuda")
     mv = torch.empty(est, dtype=torch.float32, device="cuda")
     mrp = torch.zeros(n1 + 1, dtype=torch.int64, device="cuda")
@@ -117,6 +122,27 @@ def main():
     del wc, wv, mc_b, mv_b, wrp_full, wrp_b, mrp_b
     torch.cuda.empty_cache()
 
+    # column lengths of the merged matrix -> product count of the Gustavson expansion (D1's work)
+    lens = torch.zeros(n1, dtype=torch.int64, device="cuda")
+    for c0 in range(0, merged, 1 << 28):
+        lens += torch.bincount(mc[c0: min(merged, c0 + (1 << 28))].long(), minlength=n1)
+    products = float((lens.double() ** 2).sum())
+    del lens
+    out = {"workload": f"{args.workload}: {h}x{w}x{d}, k = {k}; level 1 = 2x2 pixel blocks ({n1} components), k_1 = {k1}, walks W={W} L={L} NORMAL, "
+                       f"RW1/RW2 in bands of {args.band_rows} image rows, resident in HBM",
+           "knn_ms": knn_ms, "prow_level0_ms": prow_ms, "random_walks_level0_ms": rw_ms, "rw_merge_ms": mg_ms,
+           "walk_nnz": int(walk_nnz), "merged_nnz": int(merged), "merged_entries_per_component": merged / n1, "d1_products": products,
+           "walk_steps": n * W * L, "walk_steps_per_s": n * W * L / (rw_ms * 1e-3)}
+    if merged >= 2 ** 31:
+        out["level1_prob_dist_ms"] = None
+        out["note"] = ("the merged walk matrix holds more than 2^31 - 1 entries: createSimilarities (D1) counts records in 32 bits and is not run; "
+                       f"its Gustavson expansion would be {products:.3g} products")
+        line = json.dumps(out)
+        print(line)
+        if args.out:
+            with open(args.out, "w") as f:
+                f.write(line + "\n")
+        return
     # ---- the level: D1 -> CSR -> B3 -> B7 -> B6 in one call
     cap_p = 2 * n1 * k1
     prp = torch.empty(n1 + 1, dtype=torch.int64, device="cuda")
@@ -125,12 +151,7 @@ def main():
     lv_ms, pnnz = timed(lambda: capi.level_prob_dist_dev(n1, mrp.data_ptr(), mc.data_ptr(), mv.data_ptr(), merged, k1, 1e-4, 0, None, True, 0.0, 1, True,
                                                          prp.data_ptr(), pc.data_ptr(), pv.data_ptr(), cap_p, s))
     stage = dict(capi.level_last_timing())
-    out = {"workload": f"{args.workload}: {h}x{w}x{d}, k = {k}; level 1 = 2x2 pixel blocks ({n1} components), k_1 = {k1}, walks W={W} L={L} NORMAL, "
-                       f"RW1/RW2 in bands of {args.band_rows} image rows, resident in HBM",
-           "knn_ms": knn_ms, "prow_level0_ms": prow_ms, "random_walks_level0_ms": rw_ms, "rw_merge_ms": mg_ms, "level1_prob_dist_ms": lv_ms,
-           "level1_stages_ms": stage, "total_ms": knn_ms + prow_ms + rw_ms + mg_ms + lv_ms,
-           "walk_nnz": int(walk_nnz), "merged_nnz": int(merged), "p_nnz": int(pnnz), "walk_steps": n * W * L,
-           "walk_steps_per_s": n * W * L / (rw_ms * 1e-3)}
+    out.update({"level1_prob_dist_ms": lv_ms, "level1_stages_ms": stage, "total_ms": knn_ms + prow_ms + rw_ms + mg_ms + lv_ms, "p_nnz": int(pnnz)})
 
     # ---- parity of D1 + B3 on sampled rows against the oracle (same merged matrix)
     if args.parity_rows > 0:
