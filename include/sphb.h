@@ -20,6 +20,10 @@
  *     SPHB_ERR_NO_DEVICE;
  *   - single caller at a time per process (the reference facade is sequential,
  *     sph/ComputeHierarchy.cpp:262-276).
+ *   - threading: a context (device, stream, last error, last-call statistics) belongs to the HOST THREAD that created it;
+ *     different threads may call concurrently (each on its own context), one thread's calls are sequential.  Transient device
+ *     buffers are cached per stream between calls (also for a caller's stream passed to a _dev entry point): call
+ *     sphb_shutdown() in the thread that used a stream before destroying that stream.
  *   - size limits (exceeding one returns SPHB_ERR_UNSUPPORTED / SPHB_ERR_CAPACITY with a message, never a truncated result):
  *       kNN: n < 2^31 points on the tensor-core path (2^32 - 1 on the SIMT path), k <= 864 on the tensor-core path
  *            (next_pow2(k + 160) <= 1024), any d >= 1 (d < 8 or n < 1024 run the exact SIMT kernel);

@@ -63,7 +63,17 @@ cudaError_t ws_alloc(void** p, size_t bytes, cudaStream_t stream) {
             return cudaSuccess;
         }
     }
-    const cudaError_t e = cudaMallocAsync(p, bytes, stream);
+    cudaError_t e = cudaMallocAsync(p, bytes, stream);
+    if (e == cudaErrorMemoryAllocation) {
+        // the idle blocks of the cache (any stream, any size class) may be what is missing: give them back and try once more
+        cudaGetLastError();
+        ws_trim();
+        cudaStreamSynchronize(stream);
+        int dev = 0;
+        cudaMemPool_t pool;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+        e = cudaMallocAsync(p, bytes, stream);
+    }
     if (e != cudaSuccess) return e;
     std::lock_guard<std::mutex> lk(g_ws_mu);
     g_ws_live.push_back({*p, bytes, stream});

@@ -44,6 +44,7 @@ int sort_pairs_bits(const uint64_t* keys_in, uint64_t* keys_out, const V* vals_i
 template <class T>
 int exclusive_sum(const T* in, T* out, int64_t num, cudaStream_t s) {
     if (num <= 0) return 0;
+    if (num > 0x7fffffffll) return fail(5, "exclusive_sum: more than 2^31 - 1 items");
     size_t bytes = 0;
     SPHB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, static_cast<int>(num), s));
     DevBuf<uint8_t> tmp;
