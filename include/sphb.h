@@ -343,6 +343,12 @@ SPHB_API int sphb_rw_post_merge_dev(int64_t n, const int64_t* d_rowptr, const ui
  * slots beyond n keep -1 / -1.0f. */
 SPHB_API int sphb_level_knn_walks(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int mode, int64_t k,
                                   int64_t* out_ids, float* out_dist);
+/* The same exact level kNN in the Euclid metric (EuclidDistSpace, sph/utils/EuclidDistSpace.hpp:29-39; computeExactKnn
+ * sph/LevelSimilarities.cpp:211-252 as reached from :414): the symmetric Hausdorff distance (sphb_euclid_hausdorff) of every
+ * component against every component, the k smallest (distance, index) of every row selected on the device.
+ * out: ncomp*k, rows ordered by (distance, index); k <= ncomp. */
+SPHB_API int sphb_level_knn_euclid(const float* x, int64_t n, int d, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, int64_t k,
+                                   int64_t* out_ids, float* out_dist);
 /* The same exact level kNN in the neighbour-overlap metric (NeighborOverlapSpace, sph/utils/NeighborOverlapSpace.hpp:31-43;
  * the default componentSim of LevelSimilaritiesSettings, sph/utils/Settings.hpp:170): distance 1 - simNeighborOverlap
  * (sph/utils/Similarities.cpp:174-228) over the components' kNN-id unions; arguments as sphb_neighbor_overlap.

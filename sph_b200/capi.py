@@ -63,6 +63,7 @@ SIGNATURES = {
     "sphb_bridge_components": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int, i64p, C.c_int64, i64p, C.c_int64, i64p, i64p, f32p]),
     "sphb_bridge_components_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_int64, i64p, C.c_int64, C.c_void_p,
                                              C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sphb_level_knn_euclid": (C.c_int, [f32p, C.c_int64, C.c_int, C.c_int64, i64p, i64p, C.c_int64, i64p, f32p]),
     "sphb_prow_exponential_graph": (C.c_int, [i64p, f32p, C.c_int64, C.c_int, C.c_int, u32p, f32p]),
     "sphb_prow_exponential_graph_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sphb_prow_exponential_inplace": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int]),
@@ -446,6 +447,19 @@ def _graph_args(rowptr, ids, dist):
         return n, None, k, ids, dist
     rowptr = np.ascontiguousarray(rowptr, np.int64)
     return len(rowptr) - 1, rowptr, 0, ids, dist
+
+
+def level_knn_euclid(x: np.ndarray, comp_ptr, comp_pix, k: int):
+    """Exact level kNN in the Euclid (Hausdorff) component metric: (ids int64 [ncomp, k], dist float32 [ncomp, k])."""
+    x = np.ascontiguousarray(x, np.float32)
+    comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+    comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+    n, d = x.shape
+    ncomp = len(comp_ptr) - 1
+    ids = np.full((ncomp, k), -1, np.int64)
+    dist = np.full((ncomp, k), -1.0, np.float32)
+    _check(load().sphb_level_knn_euclid(_p(x, f32p), n, d, ncomp, _p(comp_ptr, i64p), _p(comp_pix, i64p), k, _p(ids, i64p), _p(dist, f32p)))
+    return ids, dist
 
 
 def component_centers(x: np.ndarray, labels: np.ndarray, num_components: int) -> np.ndarray:

@@ -622,6 +622,84 @@ int euclid_hausdorff_dev(const float* d_x, int d, const int64_t* d_comp_ptr, con
     return 0;
 }
 
+// D7 in the Euclid metric (computeExactKnn with EuclidDistSpace, sph/LevelSimilarities.cpp:211-252, :414;
+// sph/utils/EuclidDistSpace.hpp:29-39): every component against every component through the Hausdorff kernel above, row block
+// by row block, and the k smallest (distance, index) of every row picked on the device — no host round trip per block.
+__global__ void eh_block_pairs(int64_t r0, int64_t rows, int64_t ncomp, int64_t* __restrict__ pa, int64_t* __restrict__ pb) {
+    const int64_t total = rows * ncomp;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        pa[t] = r0 + t / ncomp;
+        pb[t] = t % ncomp;
+    }
+}
+
+constexpr int BK_WARPS = 4;
+__global__ void __launch_bounds__(BK_WARPS * 32) bottomk_rows_kernel(const float* __restrict__ dmat, int64_t rows, int64_t ncols, int k, int cap,
+                                                                     int64_t* __restrict__ ids, float* __restrict__ dist) {
+    extern __shared__ uint64_t smem_keys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t* sm = smem_keys + static_cast<size_t>(warp) * cap;
+    for (int64_t r = static_cast<int64_t>(blockIdx.x) * BK_WARPS + warp; r < rows; r += static_cast<int64_t>(gridDim.x) * BK_WARPS) {
+        const float* row = dmat + r * ncols;
+        int cnt = 0;
+        uint64_t kth = ~0ull;
+        for (int64_t base = 0; base < ncols; base += 32) {
+            const int64_t j = base + lane;
+            const uint64_t key = j < ncols ? make_key(row[j], static_cast<uint32_t>(j)) : ~0ull;
+            const bool pass = j < ncols && key <= kth;
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (m) {
+                if (pass) sm[cnt + __popc(m & ((1u << lane) - 1u))] = key;
+                cnt += __popc(m);
+                if (cnt + 32 > cap) {
+                    for (int t = cnt + lane; t < cap; t += 32) sm[t] = ~0ull;
+                    __syncwarp();
+                    warp_bitonic_sort(sm, cap, lane);
+                    cnt = min(cnt, k);
+                    kth = (cnt == k) ? sm[k - 1] : ~0ull;
+                }
+            }
+        }
+        for (int t = cnt + lane; t < cap; t += 32) sm[t] = ~0ull;
+        __syncwarp();
+        warp_bitonic_sort(sm, cap, lane);
+        for (int t = lane; t < k; t += 32) {
+            const uint64_t key = sm[t];
+            ids[r * k + t] = key == ~0ull ? -1 : static_cast<int64_t>(key_idx(key));
+            dist[r * k + t] = key == ~0ull ? -1.0f : key_val(key);
+        }
+        __syncwarp();
+    }
+}
+
+int level_knn_euclid_dev(const float* d_x, int d, int64_t ncomp, const int64_t* d_comp_ptr, const int64_t* d_comp_pix, int k, int64_t* d_ids,
+                         float* d_dist, cudaStream_t s) {
+    if (ncomp <= 0) return 0;
+    int cap = 64;
+    while (cap < k + 32) cap <<= 1;
+    const size_t smem = static_cast<size_t>(BK_WARPS) * cap * sizeof(uint64_t);
+    if (smem > 200 * 1024) return fail(SPHB_ERR_UNSUPPORTED, "level_knn_euclid: k too large");
+    SPHB_CUDA(cudaFuncSetAttribute(bottomk_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    const int64_t block = std::max<int64_t>(1, std::min<int64_t>(ncomp, (int64_t{1} << 24) / ncomp));  // <= 16 M pairs per block
+    DevBuf<int64_t> pa, pb;
+    DevBuf<float> dm;
+    SPHB_CUDA(pa.alloc(block * ncomp, s));
+    SPHB_CUDA(pb.alloc(block * ncomp, s));
+    SPHB_CUDA(dm.alloc(block * ncomp, s));
+    const int sms = ctx().num_sms;
+    for (int64_t r0 = 0; r0 < ncomp; r0 += block) {
+        const int64_t rows = std::min<int64_t>(block, ncomp - r0);
+        eh_block_pairs<<<gm_grid(rows * ncomp, 256, sms), 256, 0, s>>>(r0, rows, ncomp, pa.p, pb.p);
+        count_launch();
+        if (int rc = euclid_hausdorff_dev(d_x, d, d_comp_ptr, d_comp_pix, pa.p, pb.p, rows * ncomp, dm.p, s)) return rc;
+        bottomk_rows_kernel<<<static_cast<unsigned>(std::min<int64_t>((rows + BK_WARPS - 1) / BK_WARPS, static_cast<int64_t>(sms) * 16)), BK_WARPS * 32, smem,
+                              s>>>(dm.p, rows, ncomp, k, cap, d_ids + r0 * k, d_dist + r0 * k);
+        count_launch();
+    }
+    SPHB_CUDA(cudaGetLastError());
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // D7: exact level kNN in a random-walk component metric (LevelSimilarities.cpp:211-252 with
 // NeighborWalksBhattacharyyaSpace / NeighborWalksSingleOverlapSpace).  The spaces' distance functions do NOT go through
@@ -1389,6 +1467,34 @@ SPHB_API int sphb_euclid_hausdorff(const float* x, int64_t n, int d, int64_t nco
     SPHB_CUDA(dout.alloc(npairs, s));
     if (int rc = euclid_hausdorff_dev(dx.p, d, dptr.p, dpix.p, da.p, db.p, npairs, dout.p, s)) return rc;
     SPHB_CUDA(cudaMemcpyAsync(out, dout.p, npairs * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+
+SPHB_API int sphb_level_knn_euclid(const float* x, int64_t n, int d, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, int64_t k,
+                                   int64_t* out_ids, float* out_dist) {
+    if (int rc = ensure_init()) return rc;
+    if (!x || n <= 0 || d <= 0 || ncomp <= 0 || !comp_ptr || comp_ptr[0] != 0 || k <= 0 || k > ncomp || !out_ids || !out_dist)
+        return fail(SPHB_ERR_INVALID, "level_knn_euclid: bad arguments");
+    if (k > 992) return fail(SPHB_ERR_UNSUPPORTED, "level_knn_euclid: k > 992 unsupported");
+    const int64_t npix = comp_ptr[ncomp];
+    if (npix < 0 || (npix > 0 && !comp_pix)) return fail(SPHB_ERR_INVALID, "level_knn_euclid: bad arguments");
+    for (int64_t c = 0; c < ncomp; ++c)
+        if (comp_ptr[c + 1] < comp_ptr[c]) return fail(SPHB_ERR_INVALID, "level_knn_euclid: comp_ptr not monotone");
+    for (int64_t i = 0; i < npix; ++i)
+        if (comp_pix[i] < 0 || comp_pix[i] >= n) return fail(SPHB_ERR_INVALID, "level_knn_euclid: pixel id out of range");
+    cudaStream_t s = ctx().stream;
+    DevBuf<float> dx, dd;
+    DevBuf<int64_t> dptr, dpix, di;
+    if (int rc = up(dx, x, n * d, s)) return rc;
+    if (int rc = up(dptr, comp_ptr, ncomp + 1, s)) return rc;
+    if (int rc = up(dpix, comp_pix, npix, s)) return rc;
+    SPHB_CUDA(di.alloc(ncomp * k, s));
+    SPHB_CUDA(dd.alloc(ncomp * k, s));
+    if (int rc = level_knn_euclid_dev(dx.p, d, ncomp, dptr.p, dpix.p, static_cast<int>(k), di.p, dd.p, s)) return rc;
+    SPHB_CUDA(cudaMemcpyAsync(out_ids, di.p, ncomp * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(out_dist, dd.p, ncomp * k * sizeof(float), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaStreamSynchronize(s));
     return SPHB_OK;
 }

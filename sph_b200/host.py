@@ -540,22 +540,12 @@ class LevelSimilarities:
             self._distance_graphs[level] = Graph(ids, dist)
             return self._distance_graphs[level]
         if lss.componentSim == ComponentSim.EUCLID_CENTROID:
-            # EuclidDistSpace (sph/utils/EuclidDistSpace.hpp:29-39): Hausdorff distance of every component pair.  Not fused:
-            # row blocks of (i, j) pairs go through the batched D6 kernel, the k smallest per row are picked on the host
+            # EuclidDistSpace (sph/utils/EuclidDistSpace.hpp:29-39): Hausdorff distance of every component pair, the k smallest
+            # (distance, index) per row selected on the device (sphb_level_knn_euclid)
             ptr, pix = self._hierarchy.representedDataPoints(level)
             n_l = len(ptr) - 1
             k_l = min(self._ks[level], n_l)
-            ids = np.empty((n_l, k_l), np.int64)
-            dist = np.empty((n_l, k_l), np.float32)
-            block = max(1, min(n_l, (1 << 22) // max(n_l, 1)))
-            cols = np.arange(n_l, dtype=np.int64)
-            for r0 in range(0, n_l, block):
-                r1 = min(n_l, r0 + block)
-                pa = np.repeat(np.arange(r0, r1, dtype=np.int64), n_l)
-                d = capi.euclid_hausdorff(self._hierarchy._data, ptr, pix, pa, np.tile(cols, r1 - r0)).reshape(r1 - r0, n_l)
-                for r in range(r0, r1):
-                    order = np.lexsort((cols, d[r - r0]))[:k_l]  # (distance, index); the reference's std::sort leaves ties unordered
-                    ids[r], dist[r] = order, d[r - r0, order]
+            ids, dist = capi.level_knn_euclid(self._hierarchy._data, ptr, pix, k_l)
             self._distance_graphs[level] = Graph(ids, dist)
             return self._distance_graphs[level]
         rw = self._rw[level]

@@ -176,6 +176,28 @@ def test_euclid_hausdorff_matches_oracle(capi, oracle, d):
     assert out[1] == 0
 
 
+@pytest.mark.parametrize("d,ncomp,k", [(3, 200, 31), (64, 150, 150), (16, 5000, 12)])
+def test_level_knn_euclid_matches_all_pairs(capi, oracle, d, ncomp, k):
+    """D7 in the Euclid metric: every component against every component, k smallest (distance, index) per row — against the
+    oracle's Hausdorff distance over all pairs (rows sampled where ncomp^2 is large)."""
+    rng = np.random.default_rng(ncomp + d)
+    n = 4 * ncomp
+    x = rng.normal(size=(n, d)).astype(np.float32)
+    x[n // 2:] = x[:n - n // 2]            # duplicated pixels: zero distances and ties
+    sizes = rng.integers(1, 6, ncomp)
+    comp_ptr = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    comp_pix = rng.integers(0, n, comp_ptr[-1]).astype(np.int64)
+    ids, dist = capi.level_knn_euclid(x, comp_ptr, comp_pix, k)
+    cols = np.arange(ncomp, dtype=np.int64)
+    rows = np.arange(ncomp) if ncomp <= 200 else rng.choice(ncomp, 40, replace=False)
+    for r in rows:
+        dr = oracle.euclid_hausdorff(x, comp_ptr, comp_pix, np.full(ncomp, r, np.int64), cols)
+        order = np.lexsort((cols, dr))[:k]
+        np.testing.assert_array_equal(ids[r], order)
+        np.testing.assert_array_equal(dist[r], dr[order])
+    assert (np.diff(dist, axis=1) >= 0).all()
+
+
 # ---------------------------------------------------------------- host mirror on top of the new entry points
 def test_level_similarities_walk_knn_path(capi, oracle):
     """LevelSimilarities with rwHandling = MERGE_RW_NEW_WALKS_AND_KNN: exact level kNN in the Bhattacharyya metric, then

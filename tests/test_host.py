@@ -231,6 +231,19 @@ def capi_on_oracle(monkeypatch, oracle):
     monkeypatch.setattr(capi, "level_knn_overlap", lambda ids, ptr, pix, k: o.level_knn_overlap(ids, ptr, pix, k))
     monkeypatch.setattr(capi, "euclid_hausdorff", lambda x, ptr, pix, pa, pb: o.euclid_hausdorff(x, ptr, pix, pa, pb))
     monkeypatch.setattr(capi, "level_knn_walks", lambda rp, c, v, k, mode=0: o.level_knn_walks(rp, c, v, k, mode))
+
+    def level_knn_euclid(x, ptr, pix, k):  # all pairs through the checker's Hausdorff distance, rows ordered by (distance, index)
+        n_l = len(ptr) - 1
+        cols = np.arange(n_l, dtype=np.int64)
+        ids = np.empty((n_l, k), np.int64)
+        dist = np.empty((n_l, k), np.float32)
+        for r in range(n_l):
+            dr = o.euclid_hausdorff(x, ptr, pix, np.full(n_l, r, np.int64), cols)
+            order = np.lexsort((cols, dr))[:k]
+            ids[r], dist[r] = order, dr[order]
+        return ids, dist
+
+    monkeypatch.setattr(capi, "level_knn_euclid", level_knn_euclid)
     monkeypatch.setattr(capi, "rw_as_knn_distances", lambda rp, c, v: o.rw_as_knn_distances(rp, c, v))
     monkeypatch.setattr(capi, "prow_gaussian_flat", lambda d, p: o.prow_gaussian_flat(d, p))
     monkeypatch.setattr(capi, "prow_gaussian_inplace", lambda rp, v, p=0.0, ig=-1: o.prow_gaussian_inplace(rp, v, p, ig))
