@@ -211,7 +211,7 @@ SPHB_API int sphb_init(int device) {
     return SPHB_OK;
 }
 
-SPHB_API void sphb_shutdown(void) {
+static void shutdown_context(bool trim_pool) {
     if (!g_ctx.ready) return;
     cudaStreamSynchronize(g_ctx.stream);
     sphb::ws_trim_stream(g_ctx.stream);
@@ -219,9 +219,11 @@ SPHB_API void sphb_shutdown(void) {
     cudaStreamDestroy(g_ctx.stream);
     g_ctx.stream = nullptr;
     cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, g_ctx.device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+    if (trim_pool && cudaDeviceGetDefaultMemPool(&pool, g_ctx.device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
     g_ctx.ready = false;
 }
+
+SPHB_API void sphb_shutdown(void) { shutdown_context(true); }
 
 SPHB_API const char* sphb_last_error(void) { return g_err.c_str(); }
 SPHB_API int sphb_version(void) { return 100; }
@@ -666,7 +668,7 @@ SPHB_API int sphb_knn_graph_prow_multi(const float* x, int64_t n, int d, int k, 
         // buffers are released here (stream-ordered), the worker's context stays cached in its thread and dies with it
         xall.release(); di.release(); dd.release(); dc.release(); dv.release();
         if (s) cudaStreamSynchronize(s);
-        sphb_shutdown();
+        shutdown_context(false);  // the device's memory pool keeps the freed blocks for the next call
     };
     std::vector<std::thread> threads;
     threads.reserve(G);
