@@ -710,6 +710,9 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
         // bound the accumulator slabs to 8 GiB.  (Keeping the slabs L2-resident by running fewer CTAs does not help: 768 x 768 x 128
         // level 1, 296 / 136 / 68 CTAs: 9.2 / 10.4 / 11.6 s — the returning atomics, not L2 misses, were the bound.)
         while (grid > 1 && static_cast<double>(grid) * n * 8.0 > 8.0 * (1ull << 30)) grid /= 2;
+#ifdef SPHB_KNN_TUNING
+        if (const char* e = getenv("SPHB_SIMS_SLAB_CTAS")) grid = std::max<int64_t>(1, std::min<int64_t>(n, atoi(e)));
+#endif
         SPHB_CUDA(acc.alloc(static_cast<size_t>(grid) * n, s));
         SPHB_CUDA(touched.alloc(static_cast<size_t>(grid) * n, s));
         SPHB_CUDA(cudaMemsetAsync(acc.p, 0, static_cast<size_t>(grid) * n * sizeof(float), s));
