@@ -4,6 +4,7 @@
 
 #include <atomic>
 #include <condition_variable>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -175,6 +176,54 @@ int renorm_l2_dev(const float* d_x, int64_t n, int d, float* d_out, cudaStream_t
 
 using namespace sphb;
 
+namespace {
+// Persistent worker threads of the multi-device entry point: worker g keeps its context (device, stream, cached workspace
+// blocks, enabled peer access) between calls, so a steady-state call makes no cudaMallocAsync call and creates no stream.
+struct MultiWorker {
+    std::thread th;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::function<void()> job;
+    bool has_job = false, done = true;
+    MultiWorker() {
+        th = std::thread([this] {
+            for (;;) {
+                std::function<void()> j;
+                {
+                    std::unique_lock<std::mutex> lk(mu);
+                    cv.wait(lk, [&] { return has_job; });
+                    j = std::move(job);
+                }
+                j();
+                {
+                    std::lock_guard<std::mutex> lk(mu);
+                    has_job = false;
+                    done = true;
+                }
+                cv.notify_all();
+            }
+        });
+        th.detach();  // lives until the process exits
+    }
+    void post(std::function<void()> j) {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            job = std::move(j);
+            has_job = true;
+            done = false;
+        }
+        cv.notify_all();
+    }
+    void wait() {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return done; });
+    }
+};
+std::mutex g_multi_call_mu;             // one multi-device call at a time
+std::vector<MultiWorker*> g_multi_pool;  // never destroyed: the threads are detached
+
+}  // namespace
+
 extern "C" {
 
 SPHB_API int sphb_init(int device) {
@@ -223,7 +272,17 @@ static void shutdown_context(bool trim_pool) {
     g_ctx.ready = false;
 }
 
-SPHB_API void sphb_shutdown(void) { shutdown_context(true); }
+SPHB_API void sphb_shutdown(void) {
+    shutdown_context(true);
+    // the worker threads of sphb_knn_graph_prow_multi hold contexts of their own
+    std::vector<MultiWorker*> pool;
+    {
+        std::lock_guard<std::mutex> call_lock(g_multi_call_mu);
+        pool = g_multi_pool;
+        for (MultiWorker* w : pool) w->post([] { shutdown_context(true); });
+        for (MultiWorker* w : pool) w->wait();
+    }
+}
 
 SPHB_API const char* sphb_last_error(void) { return g_err.c_str(); }
 SPHB_API int sphb_version(void) { return 100; }
@@ -665,15 +724,16 @@ SPHB_API int sphb_knn_graph_prow_multi(const float* x, int64_t n, int d, int k, 
         }
         if (rc != SPHB_OK) errs[g] = g_err;
         rcs[g] = rc;
-        // buffers are released here (stream-ordered), the worker's context stays cached in its thread and dies with it
+        // buffers go back to the workspace cache of the worker's stream
         xall.release(); di.release(); dd.release(); dc.release(); dv.release();
-        if (s) cudaStreamSynchronize(s);
-        shutdown_context(false);  // the device's memory pool keeps the freed blocks for the next call
+        if (s) cudaStreamSynchronize(s);  // the context stays with the worker thread: its workspace cache serves the next call
     };
-    std::vector<std::thread> threads;
-    threads.reserve(G);
-    for (int g = 0; g < G; ++g) threads.emplace_back(worker, g);
-    for (auto& t : threads) t.join();
+    {
+        std::lock_guard<std::mutex> call_lock(g_multi_call_mu);
+        while (static_cast<int>(g_multi_pool.size()) < G) g_multi_pool.push_back(new MultiWorker());
+        for (int g = 0; g < G; ++g) g_multi_pool[g]->post([&worker, g] { worker(g); });
+        for (int g = 0; g < G; ++g) g_multi_pool[g]->wait();
+    }
     for (int g = 0; g < G; ++g)
         if (rcs[g] != SPHB_OK) return fail(rcs[g], "knn_graph_prow_multi: device " + std::to_string(devices[g]) + ": " + errs[g]);
     return SPHB_OK;
