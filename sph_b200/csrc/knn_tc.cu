@@ -97,6 +97,26 @@ struct SweepPace {
     long long mine = 0, published = 0;
     bool off = false;  // this CTA gave up waiting (no global progress for ~5 ms: some CTA of the grid is not running)
 };
+__device__ __forceinline__ void sweep_pace(const SweepParams& P, SweepPace& sp, int lane);
+// the same for a producer that is a single thread (streaming flavour)
+__device__ __forceinline__ void sweep_pace_one(const SweepParams& P, SweepPace& sp) {
+    if (P.pace_window > 0) {
+        if (sp.mine > sp.published) {
+            atomicAdd(P.progress, static_cast<unsigned long long>(sp.mine - sp.published));
+            sp.published = sp.mine;
+        }
+        const long long g = gridDim.x;
+        unsigned long long last = ~0ull;
+        int idle = 0;
+        while (!sp.off) {
+            const unsigned long long tot = *reinterpret_cast<volatile unsigned long long*>(P.progress);
+            if (sp.mine * g <= static_cast<long long>(tot) + static_cast<long long>(P.pace_window) * g) break;
+            if (tot != last) { last = tot; idle = 0; }
+            else if (++idle > 20000) sp.off = true;
+            __nanosleep(256);
+        }
+    }
+}
 __device__ __forceinline__ void sweep_pace(const SweepParams& P, SweepPace& sp, int lane) {
     if (P.pace_window > 0 && lane == 0) {
         if (sp.mine > sp.published) {
@@ -751,11 +771,17 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            // Soft lock-step as in the resident kernel (sweep_pace): a database tile of this flavour is 256 rows x ~2 KB, the L2
+            // holds ~240 of them, and without coupling the CTAs drift apart until every CTA streams the database from DRAM on its
+            // own (full C5: 582 TFLOP/s, HBM-bound; a short 8-wave slab, where they cannot drift far, reaches 984).
+            SweepPace pace;
             for (int qt = blockIdx.x; qt < P.n_qtiles; qt += gridDim.x) {
                 const int32_t qrow = static_cast<int32_t>(P.a_row0 + static_cast<int64_t>(qt) * BM);
                 const int dt0 = sweep_start(P, qt, BM, BN);
                 for (int t = 0; t < P.n_dbtiles; ++t) {
                     const int dt = dt0 + t < P.n_dbtiles ? dt0 + t : dt0 + t - P.n_dbtiles;  // dt0, t < n_dbtiles
+                    if ((t & 3) == 0) sweep_pace_one(P, pace);
+                    ++pace.mine;
                     for (int kc = 0; kc < P.kchunks; ++kc) {
                         ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                         const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -765,6 +791,11 @@ knn_sweep_stream(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                         if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
                 }
+            }
+            if (P.pace_window > 0) {  // a CTA that has finished publishes the progress of a complete run
+                const long long waves = (P.n_qtiles + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+                const long long all = waves * P.n_dbtiles;
+                if (all > pace.published) atomicAdd(P.progress, static_cast<unsigned long long>(all - pace.published));
             }
         }
     } else if (warp == 1) {
@@ -1215,7 +1246,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     P.compact_step = std::max(32, tune("SPHB_KNN_COMPACT_STEP", cap));
     // soft lock-step of the CTAs' sweeps (sweep_pace): only for whole-database items, and only when every CTA of the grid is
     // resident at once (one CTA per SM by shared memory; the occupancy query below guards partitioned / shared devices)
-    P.pace_window = (MH && nseg == 1) ? tune("SPHB_KNN_PACE", 256) : 0;
+    P.pace_window = (MH && nseg == 1) ? tune("SPHB_KNN_PACE", 256) : (!MH ? tune("SPHB_KNN_STREAM_PACE", 16) : 0);
     DevBuf<unsigned long long> prof;
 #ifdef SPHB_KNN_PROFILE
     const bool want_prof = getenv("SPHB_KNN_PROF") != nullptr;
@@ -1229,7 +1260,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     }
     // CTA b starts its database sweep b*stagger tiles in: the CTAs then read different lines at any
     // moment (no L2 hot lines) while the union of their positions stays inside an L2-sized window.
-    P.stagger = tune("SPHB_KNN_STAGGER", 4);
+    P.stagger = MH ? tune("SPHB_KNN_STAGGER", 4) : tune("SPHB_KNN_STREAM_STAGGER", 0);  // streaming tiles are 256 rows x the whole K extent (516 KB at C5): any stagger spreads the CTAs over more than L2 holds
     P.lead = tune("SPHB_KNN_LEAD_ROWS", 16384) / bn;
     // Error models.  3 passes: split truncation 6·2^-22 + accumulation (one 2^-22 per
     // k-step), times the magnitude (2|u||v| + |v|²), plus the fp16 subnormal floor; safety factor 2.
@@ -1299,6 +1330,11 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
 #define SPHB_LAUNCH_STREAM(R_)                                                                                                         \
     do {                                                                                                                               \
         SPHB_CUDA(cudaFuncSetAttribute(knn_sweep_stream<R_>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));     \
+        if (P.pace_window > 0) { /* the pacing spin needs every CTA of the grid resident */                                             \
+            int per_sm = 0;                                                                                                            \
+            SPHB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_sweep_stream<R_>, tcs::NUM_THREADS, smem));            \
+            if (static_cast<int64_t>(per_sm) * J.sms < grid) P.pace_window = 0;                                                         \
+        }                                                                                                                              \
         knn_sweep_stream<R_><<<grid, tcs::NUM_THREADS, smem, stream>>>(tmA, tmB, P);                                                   \
     } while (0)
         if (cap == 256) SPHB_LAUNCH_STREAM(8);
