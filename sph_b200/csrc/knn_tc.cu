@@ -1246,7 +1246,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     P.compact_step = std::max(32, tune("SPHB_KNN_COMPACT_STEP", cap));
     // soft lock-step of the CTAs' sweeps (sweep_pace): only for whole-database items, and only when every CTA of the grid is
     // resident at once (one CTA per SM by shared memory; the occupancy query below guards partitioned / shared devices)
-    P.pace_window = (MH && nseg == 1) ? tune("SPHB_KNN_PACE", 256) : (!MH ? tune("SPHB_KNN_STREAM_PACE", 16) : 0);
+    P.pace_window = (MH && nseg == 1) ? tune("SPHB_KNN_PACE", 64) : (!MH ? tune("SPHB_KNN_STREAM_PACE", 16) : 0);
     DevBuf<unsigned long long> prof;
 #ifdef SPHB_KNN_PROFILE
     const bool want_prof = getenv("SPHB_KNN_PROF") != nullptr;
@@ -1260,7 +1260,7 @@ int sweep_and_rerank(KnnJob& J, const Operands& opA, const Operands& opB, int64_
     }
     // CTA b starts its database sweep b*stagger tiles in: the CTAs then read different lines at any
     // moment (no L2 hot lines) while the union of their positions stays inside an L2-sized window.
-    P.stagger = MH ? tune("SPHB_KNN_STAGGER", 4) : tune("SPHB_KNN_STREAM_STAGGER", 0);  // streaming tiles are 256 rows x the whole K extent (516 KB at C5): any stagger spreads the CTAs over more than L2 holds
+    P.stagger = MH ? tune("SPHB_KNN_STAGGER", 0) : tune("SPHB_KNN_STREAM_STAGGER", 0);  // streaming tiles are 256 rows x the whole K extent (516 KB at C5): any stagger spreads the CTAs over more than L2 holds
     P.lead = tune("SPHB_KNN_LEAD_ROWS", 16384) / bn;
     // Error models.  3 passes: split truncation 6·2^-22 + accumulation (one 2^-22 per
     // k-step), times the magnitude (2|u||v| + |v|²), plus the fp16 subnormal floor; safety factor 2.
