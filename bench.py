@@ -300,10 +300,10 @@ def level1_p_matrix(capi, synth, orc, peaks, workload="C2", cpu=True):
         return e
 
     passes = [
-        entry("RW1 doRandomWalks", "random_walk_kernel (+ compaction)", rw_ms, n * W * L * 8.0 * (k - 1) / 2 + 8.0 * wnnz,
+        entry("RW1 doRandomWalks", "random_walk_search_kernel (binary search in fp64 running sums, radix grouping) + compaction", rw_ms, n * W * L * 8.0 * (k - 1) / 2 + 8.0 * wnnz,
               "360 B per step (half a 90-entry row of (col, val) pairs) + 8 B per output entry, SURVEY §8d"),
         entry("RW2 mergeNodesRandomWalks", "merge_expand + radix sort + merge_reduce", mg_ms, 8.0 * wnnz + 8.0 * mnnz + 8.0 * n),
-        entry("D1 createSimilarities", "sims_row_kernel<DENSE>", stage["similarities_ms"], 8.0 * products + 8.0 * n1 * k1,
+        entry("D1 createSimilarities", "sims_class_kernel (class-partitioned shared-memory accumulators; SLAB flavour above ~52 k components) + transpose sorts", stage["similarities_ms"], 8.0 * products + 8.0 * n1 * k1,
               "8 B per expanded product (row id + value of the transposed matrix) + 8 B per output slot"),
         entry("B3 Gaussian rows in place", "prow_inplace_kernel", stage["gaussian_ms"], 8.0 * n1 * k1 + 8.0 * n1),
         entry("B6 symmetrizeTSNE", "sym_expand + radix sort + sym_combine", stage["symmetrize_ms"], 8.0 * n1 * k1 + 8.0 * pnnz),
@@ -509,7 +509,7 @@ def main():
         step_ms = e0.elapsed_time(e1) / args.steps
         sm_mhz = (clocks.summary().get("sm_mhz") or 1700.0)
         peak_pairs = 148 * 128 * sm_mhz * 1e6
-        roofline = {"bound": "fp32-issue", "kernel": "knn_simt_kernel (fp64 pair keys, warp per row)", "achieved": pairs / (step_ms * 1e-3),
+        roofline = {"bound": "fp32-issue", "kernel": "knn_simt_kernel (fp32 screen + exact fp64 keys, warp per row)", "achieved": pairs / (step_ms * 1e-3),
                     "peak": peak_pairs, "unit": "pairs/s", "frac": pairs / (step_ms * 1e-3) / peak_pairs, "traffic": None,
                     "peak_source": "148 SMs x 128 lanes x sampled SM clock (one pair evaluation per lane-cycle)", "kernel_ms": step_ms}
 
