@@ -403,13 +403,45 @@ SPHB_API int sphb_knn_graph_prow(const float* x, int64_t n, int d, int k, int me
     SPHB_CUDA(dvals.alloc(nq * (k - 1), s));
     SPHB_CUDA(cudaMemcpyAsync(dx.p, x, static_cast<size_t>(n) * d * sizeof(float), cudaMemcpyHostToDevice, s));
     if (int rc = sphb_knn_exact_dev(dx.p, n, d, k, metric, l2_squared, q0, q1, dids.p, ddist.p, s)) return rc;
+    // The graph goes back to the host on a second stream WHILE the P-row kernel runs (it only reads ids / dist): the kernel's
+    // 36 ms at C4 disappear behind the 4.6 GB copy.
+    cudaStream_t cs = nullptr;
+    cudaEvent_t graph_done = nullptr, copies_done = nullptr;
+    const bool overlap = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) == cudaSuccess &&
+                         cudaEventCreateWithFlags(&graph_done, cudaEventDisableTiming) == cudaSuccess &&
+                         cudaEventCreateWithFlags(&copies_done, cudaEventDisableTiming) == cudaSuccess;
+    auto cleanup = [&]() {
+        if (graph_done) cudaEventDestroy(graph_done);
+        if (copies_done) cudaEventDestroy(copies_done);
+        if (cs) cudaStreamDestroy(cs);
+    };
+    cudaStream_t gs = overlap ? cs : s;  // stream of the graph copies
+    cudaError_t e = cudaSuccess;
+    if (overlap) {
+        e = cudaEventRecord(graph_done, s);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(cs, graph_done, 0);
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ids, dids.p, nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, gs);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dist, ddist.p, nq * k * sizeof(float), cudaMemcpyDeviceToHost, gs);
+    if (e != cudaSuccess) {
+        cudaStreamSynchronize(gs);
+        cleanup();
+        return fail(SPHB_ERR_CUDA, std::string("knn_graph_prow: ") + cudaGetErrorString(e));
+    }
     // the rows of a slab are points q0.., but prow only uses ids for the column labels, so the slab graph can be fed as is
-    if (int rc = prow_graph_launch(dids.p, ddist.p, static_cast<int64_t>(nq), k, perplexity, 0, dcols.p, dvals.p, nullptr, s)) return rc;
-    SPHB_CUDA(cudaMemcpyAsync(ids, dids.p, nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
-    SPHB_CUDA(cudaMemcpyAsync(dist, ddist.p, nq * k * sizeof(float), cudaMemcpyDeviceToHost, s));
-    SPHB_CUDA(cudaMemcpyAsync(cols, dcols.p, nq * (k - 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-    SPHB_CUDA(cudaMemcpyAsync(vals, dvals.p, nq * (k - 1) * sizeof(float), cudaMemcpyDeviceToHost, s));
-    SPHB_CUDA(cudaStreamSynchronize(s));
+    int rc = prow_graph_launch(dids.p, ddist.p, static_cast<int64_t>(nq), k, perplexity, 0, dcols.p, dvals.p, nullptr, s);
+    if (rc == SPHB_OK) {
+        e = cudaMemcpyAsync(cols, dcols.p, nq * (k - 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(vals, dvals.p, nq * (k - 1) * sizeof(float), cudaMemcpyDeviceToHost, s);
+    }
+    if (overlap) {  // the graph buffers go back to the workspace cache of s only after the other stream is done with them
+        cudaEventRecord(copies_done, cs);
+        cudaStreamWaitEvent(s, copies_done, 0);
+    }
+    const cudaError_t e2 = cudaStreamSynchronize(s);
+    cleanup();
+    if (rc != SPHB_OK) return rc;
+    if (e != cudaSuccess || e2 != cudaSuccess) return fail(SPHB_ERR_CUDA, std::string("knn_graph_prow: ") + cudaGetErrorString(e != cudaSuccess ? e : e2));
     return SPHB_OK;
 }
 

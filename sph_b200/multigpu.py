@@ -70,10 +70,30 @@ class ShardedKnnProw:
         for dst, src in zip(out, (self.ids, self.dist, self.cols, self.vals)):
             dst.copy_(src, non_blocking=True)
 
-    def __call__(self, x_host, out, perplexity: float = 0.0) -> None:
+    def __call__(self, x_host, out, perplexity: float = 0.0, metric: int = capi.METRIC_L2, l2_squared: bool = False) -> None:
+        """replicate -> search -> P rows -> download; the graph (ids, dist) goes back to the host on a side stream while the P-row
+        kernel runs, as in sphb_knn_graph_prow."""
+        import torch
+
         self.replicate(x_host)
-        self.compute(perplexity)
-        self.download(out)
+        nq = self.q1 - self.q0
+        if nq == 0:
+            return
+        main = torch.cuda.current_stream()
+        s = main.cuda_stream
+        capi.knn_exact_dev(self.x_all.data_ptr(), self.n, self.d, self.k, metric, l2_squared, self.q0, self.q1, self.ids.data_ptr(), self.dist.data_ptr(), s)
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream()
+        graph_done = torch.cuda.Event()
+        graph_done.record(main)
+        self._side.wait_event(graph_done)
+        with torch.cuda.stream(self._side):
+            out[0].copy_(self.ids, non_blocking=True)
+            out[1].copy_(self.dist, non_blocking=True)
+        capi.prow_gaussian_graph_dev(self.ids.data_ptr(), self.dist.data_ptr(), nq, self.k, perplexity, self.cols.data_ptr(), self.vals.data_ptr(), s)
+        out[2].copy_(self.cols, non_blocking=True)
+        out[3].copy_(self.vals, non_blocking=True)
+        main.wait_stream(self._side)  # a synchronize on the current stream covers all four copies
 
 
 def knn_graph_prow_sharded(x: np.ndarray, k: int, rank: int, world: int, perplexity: float = 0.0, group=None):

@@ -42,3 +42,29 @@ def test_multi_reports_errors(capi):
     x = np.zeros((100, 4), np.float32)
     with pytest.raises(Exception, match="device"):
         capi.knn_graph_prow_multi(x, 5, [0, 99])
+
+
+def test_sharded_call_overlapped_download(capi):
+    """multigpu.ShardedKnnProw.__call__ (the N > 1 bench path) on one rank: the graph is copied back on a side stream while the P-row
+    kernel runs; the host buffers must hold exactly what sphb_knn_graph_prow returns."""
+    import torch
+
+    from sph_b200 import multigpu
+
+    x = synth.hyperspectral(80, 80, 32, endmembers=6, seed=11)
+    n, d = x.shape
+    k = 21
+    ref = capi.knn_graph_prow(x, k, 0.0)
+    job = multigpu.ShardedKnnProw(n, d, k, rank=0, world=1)
+    out = (torch.empty((n, k), dtype=torch.int64).pin_memory(), torch.empty((n, k), dtype=torch.float32).pin_memory(),
+           torch.empty((n, k - 1), dtype=torch.int32).pin_memory(), torch.empty((n, k - 1), dtype=torch.float32).pin_memory())
+    xh = torch.from_numpy(x).pin_memory()
+    for _ in range(2):
+        for o in out:
+            o.zero_()
+        job(xh, out)
+        torch.cuda.current_stream().synchronize()
+        np.testing.assert_array_equal(out[0].numpy(), ref[0])
+        np.testing.assert_array_equal(out[1].numpy(), ref[1])
+        np.testing.assert_array_equal(out[2].numpy().view(np.uint32), ref[2])
+        np.testing.assert_array_equal(out[3].numpy(), ref[3])
