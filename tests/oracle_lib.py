@@ -93,6 +93,10 @@ class Oracle:
         L.orc_bridge_components.argtypes = [f32p, C.c_int64, C.c_int, i64p, i64p, C.c_int64, i64p, i64p, f32p]
         L.orc_level_knn_overlap.argtypes = [i64p, C.c_int, C.c_int64, i64p, i64p, C.c_int64, i64p, f32p]
         L.orc_level_knn_walks.argtypes = [C.c_int64, i64p, u32p, f32p, C.c_int, C.c_int64, i64p, f32p]
+        L.orc_shortest_paths.argtypes = [C.c_int64, i64p, i64p, f32p, i64p, C.c_int64, i64p, i64p, f32p]
+        L.orc_sssp.argtypes = [C.c_int64, i64p, i64p, f32p, C.c_int64, f32p]
+        L.orc_astar.argtypes = [C.c_int64, C.c_int, i64p, f32p, f32p, C.c_int, C.c_int64, i64p, i64p, f32p]
+        L.orc_geodesic_hausdorff.argtypes = [C.c_int64, i64p, i64p, f32p, i64p, i64p, i64p, i64p, i64p, C.c_int64, f32p]
 
     # ---- Stage A
     def knn_exact(self, x, k, metric=1, rows=None):
@@ -416,6 +420,55 @@ class Oracle:
         pb = np.ascontiguousarray(pb, np.int64)
         out = np.zeros(len(pa), np.float32)
         self.lib.orc_euclid_hausdorff(_p(x, f32p), x.shape[1], _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p))
+        return out
+
+    # ---- 8(f)-4 geodesic distances (oracle_geodesic.cpp); graphs as (rowptr, ids, dist), rowptr None = fixed k from ids.shape
+    @staticmethod
+    def _graph_csr(rowptr, ids, dist):
+        ids = np.ascontiguousarray(ids, np.int64)
+        dist = np.ascontiguousarray(dist, np.float32)
+        if rowptr is None:
+            n, k = ids.shape
+            rowptr = np.arange(n + 1, dtype=np.int64) * k
+        return np.ascontiguousarray(rowptr, np.int64), ids.reshape(-1), dist.reshape(-1)
+
+    def shortest_paths(self, rowptr, ids, dist, start, end, labels=None):
+        rowptr, ids, dist = self._graph_csr(rowptr, ids, dist)
+        start = np.ascontiguousarray(start, np.int64)
+        end = np.ascontiguousarray(end, np.int64)
+        lab = None if labels is None else np.ascontiguousarray(labels, np.int64)
+        out = np.zeros(len(start), np.float32)
+        self.lib.orc_shortest_paths(len(rowptr) - 1, _p(rowptr, i64p), _p(ids, i64p), _p(dist, f32p), None if lab is None else _p(lab, i64p), len(start),
+                                    _p(start, i64p), _p(end, i64p), _p(out, f32p))
+        return out
+
+    def sssp(self, rowptr, ids, dist, src):
+        rowptr, ids, dist = self._graph_csr(rowptr, ids, dist)
+        out = np.zeros(len(rowptr) - 1, np.float32)
+        self.lib.orc_sssp(len(rowptr) - 1, _p(rowptr, i64p), _p(ids, i64p), _p(dist, f32p), int(src), _p(out, f32p))
+        return out
+
+    def astar(self, ids, dist, x, start, end):
+        ids = np.ascontiguousarray(ids, np.int64)
+        dist = np.ascontiguousarray(dist, np.float32)
+        x = np.ascontiguousarray(x, np.float32)
+        start = np.ascontiguousarray(start, np.int64)
+        end = np.ascontiguousarray(end, np.int64)
+        out = np.zeros(len(start), np.float32)
+        self.lib.orc_astar(ids.shape[0], ids.shape[1], _p(ids, i64p), _p(dist, f32p), _p(x, f32p), x.shape[1], len(start), _p(start, i64p), _p(end, i64p),
+                           _p(out, f32p))
+        return out
+
+    def geodesic_hausdorff(self, rowptr, ids, dist, comp_ptr, comp_pix, pa, pb, labels=None):
+        rowptr, ids, dist = self._graph_csr(rowptr, ids, dist)
+        comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+        comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+        pa = np.ascontiguousarray(pa, np.int64)
+        pb = np.ascontiguousarray(pb, np.int64)
+        lab = None if labels is None else np.ascontiguousarray(labels, np.int64)
+        out = np.zeros(len(pa), np.float32)
+        self.lib.orc_geodesic_hausdorff(len(rowptr) - 1, _p(rowptr, i64p), _p(ids, i64p), _p(dist, f32p), None if lab is None else _p(lab, i64p),
+                                        _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p))
         return out
 
     def prow_graph_ragged(self, rowptr, ids, dist, perplexity=0.0, linear=False):
