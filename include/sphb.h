@@ -349,6 +349,30 @@ SPHB_API int sphb_level_knn_walks(int64_t n, const int64_t* rowptr, const uint32
  * out: ncomp*k, rows ordered by (distance, index); k <= ncomp. */
 SPHB_API int sphb_level_knn_euclid(const float* x, int64_t n, int d, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, int64_t k,
                                    int64_t* out_ids, float* out_dist);
+/* SURVEY 8(f)-4 — geodesic component distances, the metric of GEO_CENTROID / GEO_WALKS: utils::geodesicDistance
+ * (sph/utils/Similarities.cpp:234-309) over utils::computeShortestPath (sph/utils/ShortestPath.cpp:100-171), batched.
+ * The graph is the data-level kNN graph the reference hands to createBoostGraph (sph/utils/AStarBoost.cpp:104-133; with
+ * GEO_* the connected graph, sph/ComputeHierarchy.cpp:135): rowptr int64[n+1] or NULL for a fixed-k graph (ids / dist n*k),
+ * one directed edge per stored (point, neighbour != point, distance); distances must be non-negative.  labels (may be NULL):
+ * connected-component label of every point (sph/ComputeHierarchy.cpp:143) — points with different labels have no path.
+ * Per (start, end): different labels -> no path; end stored in start's row -> the stored distance of the first such slot;
+ * else the shortest-path distance, i.e. the minimum over the paths of the left-to-right fp32 sum of the edge weights (what
+ * dijkstraBoost settles, AStarBoost.cpp:241-257, and what astarBoost returns with an admissible heuristic — true L2 edge
+ * weights, L2squared = false).  One single-source search per distinct start point of a call, on the device.
+ *
+ * sphb_geodesic_distances: computeShortestPath for npairs point pairs, -1 where there is no path.
+ * sphb_geodesic_hausdorff: geodesicDistance for npairs component pairs (pa[p], pb[p]), components as in
+ * sphb_euclid_hausdorff: symmetric Hausdorff distance (sph/utils/Math.cpp:167-172) of the matrix of computeShortestPath
+ * values from the points of pa[p] to the points of pb[p], "no path" entering as FLT_MAX (:278-281); single-point components
+ * give the level-0 branch (:245-252).  The sub-sampled branch (:288-303) draws from an unseeded random_device: the caller
+ * passes the sampled lists.  sphb_geodesic_last_stats: {vertices expanded, bitmap passes, searches run, sources} of the
+ * calling thread's last call. */
+SPHB_API int sphb_geodesic_distances(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const int64_t* labels,
+                                     const int64_t* start, const int64_t* end, int64_t npairs, float* out);
+SPHB_API int sphb_geodesic_hausdorff(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const int64_t* labels,
+                                     int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, const int64_t* pa, const int64_t* pb,
+                                     int64_t npairs, float* out);
+SPHB_API int sphb_geodesic_last_stats(int64_t* out4);
 /* The same exact level kNN in the neighbour-overlap metric (NeighborOverlapSpace, sph/utils/NeighborOverlapSpace.hpp:31-43;
  * the default componentSim of LevelSimilaritiesSettings, sph/utils/Settings.hpp:170): distance 1 - simNeighborOverlap
  * (sph/utils/Similarities.cpp:174-228) over the components' kNN-id unions; arguments as sphb_neighbor_overlap.

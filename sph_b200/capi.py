@@ -106,6 +106,9 @@ SIGNATURES = {
     "sphb_level_prob_dist": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, C.c_int, C.c_float, C.c_int, C.c_int, i64p,
                                        u32p, f32p, C.c_int64, i64p]),
     "sphb_level_last_timing": (C.c_int, [f32p]),
+    "sphb_geodesic_distances": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, i64p, i64p, C.c_int64, f32p]),
+    "sphb_geodesic_hausdorff": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
+    "sphb_geodesic_last_stats": (C.c_int, [i64p]),
 }
 
 
@@ -638,6 +641,48 @@ def euclid_hausdorff(x, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
     _check(load().sphb_euclid_hausdorff(_p(x, f32p), n, d, len(comp_ptr) - 1, _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p),
                                         len(pa), _p(out, f32p)))
     return out
+
+
+def _geo_graph(ids, dist, rowptr):
+    ids = np.ascontiguousarray(ids, np.int64)
+    dist = np.ascontiguousarray(dist, np.float32)
+    if rowptr is None:
+        n, k = ids.shape
+        return n, None, k, ids, dist
+    rp = np.ascontiguousarray(rowptr, np.int64)
+    return len(rp) - 1, rp, 0, ids, dist
+
+
+def geodesic_distances(ids, dist, start, end, rowptr=None, labels=None) -> np.ndarray:
+    """computeShortestPath (sph/utils/ShortestPath.cpp:100-171) for point pairs; -1 where there is no path."""
+    n, rp, k, ids, dist = _geo_graph(ids, dist, rowptr)
+    start = np.ascontiguousarray(start, np.int64)
+    end = np.ascontiguousarray(end, np.int64)
+    lab = None if labels is None else np.ascontiguousarray(labels, np.int64)
+    out = np.zeros(len(start), np.float32)
+    _check(load().sphb_geodesic_distances(n, None if rp is None else _p(rp, i64p), k, _p(ids, i64p), _p(dist, f32p), None if lab is None else _p(lab, i64p),
+                                          _p(start, i64p), _p(end, i64p), len(start), _p(out, f32p)))
+    return out
+
+
+def geodesic_hausdorff(ids, dist, comp_ptr, comp_pix, pa, pb, rowptr=None, labels=None) -> np.ndarray:
+    """geodesicDistance (sph/utils/Similarities.cpp:234-309) for component pairs."""
+    n, rp, k, ids, dist = _geo_graph(ids, dist, rowptr)
+    comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+    comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+    pa = np.ascontiguousarray(pa, np.int64)
+    pb = np.ascontiguousarray(pb, np.int64)
+    lab = None if labels is None else np.ascontiguousarray(labels, np.int64)
+    out = np.zeros(len(pa), np.float32)
+    _check(load().sphb_geodesic_hausdorff(n, None if rp is None else _p(rp, i64p), k, _p(ids, i64p), _p(dist, f32p), None if lab is None else _p(lab, i64p),
+                                          len(comp_ptr) - 1, _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p)))
+    return out
+
+
+def geodesic_last_stats() -> dict:
+    out = np.zeros(4, np.int64)
+    _check(load().sphb_geodesic_last_stats(_p(out, i64p)))
+    return dict(expanded=int(out[0]), passes=int(out[1]), searches=int(out[2]), sources=int(out[3]))
 
 
 # ------------------------------------------------------------------ resident level pipeline

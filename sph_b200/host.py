@@ -91,6 +91,7 @@ class LevelSimilaritiesSettings:  # Settings.hpp:169-181 (the fields this path r
     componentSim: "ComponentSim | None" = None   # None: NEIGH_WALKS with MERGE_RW_ONLY (useRandomWalks)
     knnFromWalkMetric: bool = False               # rwHandling == MERGE_RW_NEW_WALKS_AND_KNN: exact level kNN + useKnnDistances
     forceComputeDistances: bool = False           # useRandomWalksAsKnnDistances
+    componentLabels: np.ndarray | None = None     # GEO_CENTROID: connected-component label per point (sph/ComputeHierarchy.cpp:144)
 
 
 @dataclass
@@ -548,6 +549,19 @@ class LevelSimilarities:
             ids, dist = capi.level_knn_euclid(self._hierarchy._data, ptr, pix, k_l)
             self._distance_graphs[level] = Graph(ids, dist)
             return self._distance_graphs[level]
+        if lss.componentSim == ComponentSim.GEO_CENTROID:
+            # GeodesicPathSpace (sph/utils/GeodesicPathSpace.hpp:38-49): geodesicDistance of every component pair — one batched
+            # device call — then the k smallest (distance, index) per row
+            ptr, pix = self._hierarchy.representedDataPoints(level)
+            n_l = len(ptr) - 1
+            k_l = min(self._ks[level], n_l)
+            pa = np.repeat(np.arange(n_l, dtype=np.int64), n_l)
+            pb = np.tile(np.arange(n_l, dtype=np.int64), n_l)
+            sptr, spix, spa, spb = subsampleComponentPairs(ptr, pix, pa, pb, self._hierarchy.ihs.numGeodesicSamples)
+            dm = geodesicDistance(self._graph, sptr, spix, spa, spb, lss.componentLabels).reshape(n_l, n_l)
+            order = np.lexsort((pb.reshape(n_l, n_l), dm), axis=1)[:, :k_l]
+            self._distance_graphs[level] = Graph(order.astype(np.int64), np.take_along_axis(dm, order, 1).astype(np.float32))
+            return self._distance_graphs[level]
         rw = self._rw[level]
         k_l = min(self._ks[level], rw.n)
         if lss.knnFromWalkMetric:
@@ -570,16 +584,27 @@ class LevelSimilarities:
             sizes = list(self._hierarchy.numComponents)
         else:
             sizes = [self._graph.numPoints] + [rw.n for rw in self._rw[1:]]
-        self._perplexities, self._ks = level_schedule(sizes, self._graph.knnIndices.shape[1])
+        if lss.ks:  # _lss.ks[0] is the number of data-level neighbours (LevelSimilarities.cpp:96-98)
+            k0 = int(lss.ks[0])
+        elif self._graph.knnIndices.ndim == 2:
+            k0 = self._graph.knnIndices.shape[1]
+        else:
+            log.error("LevelSimilarities::compute: a ragged data graph needs lss.ks[0], the number of data-level neighbours")
+            return
+        self._perplexities, self._ks = level_schedule(sizes, k0)
         levels = range(len(sizes)) if lss.levelToCompute < 0 else [lss.levelToCompute]
         for level in levels:
             if level >= len(sizes):
                 log.error("LevelSimilarities::compute: level %d does not exist", level)
                 return
             if level == 0:
-                self._prob[0] = normalizeKnnDistances(self._graph, NormalizationScheme.TSNE, self._perplexities[0])
+                if isinstance(self._graph, RaggedGraph):
+                    g = self._graph
+                    self._prob[0] = SparseRows(*capi.prow_graph_ragged(g.rowptr, g.knnIndices, g.knnDistances, self._perplexities[0], False))
+                else:
+                    self._prob[0] = normalizeKnnDistances(self._graph, NormalizationScheme.TSNE, self._perplexities[0])
                 continue
-            overlap = lss.componentSim in (ComponentSim.NEIGH_OVERLAP, ComponentSim.EUCLID_CENTROID)  # computeKnn + useKnnDistances
+            overlap = lss.componentSim in (ComponentSim.NEIGH_OVERLAP, ComponentSim.EUCLID_CENTROID, ComponentSim.GEO_CENTROID)  # computeKnn + useKnnDistances
             if overlap and self._hierarchy is None:
                 log.error("LevelSimilarities::compute: %s needs the image hierarchy", lss.componentSim.name)
                 return
@@ -726,6 +751,45 @@ def euclidDistance(data: np.ndarray, comp_ptr, comp_pix, pairs_a, pairs_b) -> np
     return capi.euclid_hausdorff(data, comp_ptr, comp_pix, pairs_a, pairs_b)
 
 
+def geodesicDistance(graph, comp_ptr, comp_pix, pairs_a, pairs_b, labels=None) -> np.ndarray:
+    """Batched utils::geodesicDistance (sph/utils/Similarities.cpp:234-309) over component pairs: one single-source search on the
+    device per point of every first component (sphb_geodesic_hausdorff)."""
+    from . import capi
+
+    return capi.geodesic_hausdorff(graph.knnIndices, graph.knnDistances, comp_ptr, comp_pix, pairs_a, pairs_b, rowptr=getattr(graph, "rowptr", None),
+                                   labels=labels)
+
+
+def subsampleComponentPairs(comp_ptr, comp_pix, pairs_a, pairs_b, num_samples: int | None, rng=None):
+    """The sub-sampling branch of geodesicDistance / euclidDistance (sph/utils/Similarities.cpp:283-303, :455-474): a pair with more
+    than numGeodesicSamples^2 point combinations is evaluated on numGeodesicSamples points drawn WITH replacement from either
+    component (the reference seeds from random_device, so its draws are not reproducible; `rng` makes ours so).  Returns
+    (comp_ptr, comp_pix, pairs_a, pairs_b) with the sampled lists appended as extra components."""
+    comp_ptr = np.asarray(comp_ptr, np.int64)
+    comp_pix = np.asarray(comp_pix, np.int64)
+    pairs_a = np.array(pairs_a, np.int64)
+    pairs_b = np.array(pairs_b, np.int64)
+    if num_samples is None:
+        return comp_ptr, comp_pix, pairs_a, pairs_b
+    sizes = np.diff(comp_ptr)
+    big = np.nonzero(sizes[pairs_a] * sizes[pairs_b] > num_samples * num_samples)[0]
+    if len(big) == 0:
+        return comp_ptr, comp_pix, pairs_a, pairs_b
+    rng = rng or np.random.default_rng()
+    extra = []
+    ncomp = len(comp_ptr) - 1
+    for p in big:
+        for side in (pairs_a, pairs_b):
+            c = side[p]
+            lst = comp_pix[comp_ptr[c]:comp_ptr[c + 1]]
+            extra.append(lst[rng.integers(0, len(lst), num_samples)])
+            side[p] = ncomp
+            ncomp += 1
+    comp_pix = np.concatenate([comp_pix] + extra)
+    comp_ptr = np.concatenate([comp_ptr, comp_ptr[-1] + num_samples * np.arange(1, len(extra) + 1, dtype=np.int64)])
+    return comp_ptr, comp_pix, pairs_a, pairs_b
+
+
 # ---- ImageHierarchy (sph/ImageHierarchy.hpp:46, .cpp:113-608) — the HOST merge loop ---------------
 class NeighConnection(enum.IntEnum):
     FOUR = 0
@@ -774,6 +838,7 @@ class ImageHierarchySettings:  # sph/utils/Settings.hpp:145-166
     rwWeightMergeBySize: bool = True
     rwNormSim: NormType = NormType.ONEDIM
     rwRemoveSelfSimAfterMerging: bool = True
+    componentLabels: np.ndarray | None = None  # connected-component label per point (GEO_*: sph/ComputeHierarchy.cpp:143)
 
     def isAlwaysMerge(self) -> bool:
         return self.maxDist == -1.0
@@ -819,6 +884,9 @@ class DeviceOps:
         from . import capi
 
         return capi.euclid_hausdorff(data, comp_ptr, comp_pix, pa, pb)
+
+    def geodesic_hausdorff(self, graph, comp_ptr, comp_pix, pa, pb, labels=None) -> np.ndarray:
+        return geodesicDistance(graph, comp_ptr, comp_pix, pa, pb, labels)
 
 
 def pixelNeighborIDs(num_cols: int, num_rows: int, conn: NeighConnection, pid: int) -> list[int]:
@@ -978,9 +1046,6 @@ class ImageHierarchy:
         if rws is not None:
             self.rws = rws
         self._clear()
-        if self.ihs.componentSim in (ComponentSim.GEO_CENTROID, ComponentSim.GEO_WALKS):
-            log.error("ImageHierarchy::compute: geodesic component distances (A*/Dijkstra per pair) are host code outside this back-end")
-            return
         if self.ihs.normKnnDistances not in (NormalizationScheme.TSNE, NormalizationScheme.LINEAR) and self._uses_walks():
             log.error("ImageHierarchy::compute: %s rows are not built (UMAP rows are a 'next' item)", self.ihs.normKnnDistances.name)
             return
@@ -993,7 +1058,10 @@ class ImageHierarchy:
 
     def _computePreparations(self):  # ImageHierarchy.cpp:149-190
         if self.ihs.normKnnDistances in (NormalizationScheme.TSNE, NormalizationScheme.LINEAR):
-            self.dataLevelProbdist = self._ops.prow(self._graph, self.ihs.normKnnDistances)
+            if isinstance(self._graph, RaggedGraph):  # the connected / symmetrised graph of the GEO_* configurations
+                self.dataLevelProbdist = self._ops.prow_ragged(self._graph, self.ihs.normKnnDistances)
+            else:
+                self.dataLevelProbdist = self._ops.prow(self._graph, self.ihs.normKnnDistances)
         n = self._graph.numPoints
         self.numComponents = [n]
         self.pixelComponents = [np.arange(n, dtype=np.int64)]
@@ -1002,8 +1070,11 @@ class ImageHierarchy:
             self.randomWalks.append(self._ops.random_walks(self.dataLevelProbdist, self.rws))
             if self.ihs.rwHandling == RandomWalkHandling.MERGE_DATA_NEW_WALKS:  # keep the data distances for later merging (.cpp:176-177)
                 g = self._graph
-                k = g.knnIndices.shape[1]
-                self.mergedDataGraphs.append(RaggedGraph(np.arange(n + 1, dtype=np.int64) * k, g.knnIndices.reshape(-1), g.knnDistances.reshape(-1)))
+                if isinstance(g, RaggedGraph):
+                    self.mergedDataGraphs.append(g)
+                else:
+                    k = g.knnIndices.shape[1]
+                    self.mergedDataGraphs.append(RaggedGraph(np.arange(n + 1, dtype=np.int64) * k, g.knnIndices.reshape(-1), g.knnDistances.reshape(-1)))
 
     def computeDistances(self, level: int):
         """ImageHierarchy::computeDistances (.cpp:192-249): rows [self, spatial neighbours...], componentDistance for every
@@ -1022,7 +1093,12 @@ class ImageHierarchy:
             dist = np.float32(1) - self._ops.pair_sims(self.randomWalks[level], pa, ids, mode)
         elif sim == ComponentSim.EUCLID_CENTROID:
             ptr, pix = self.representedDataPoints(level)
-            dist = self._ops.euclid_hausdorff(self._data, ptr, pix, pa, ids)
+            sptr, spix, spa, spb = subsampleComponentPairs(ptr, pix, pa, ids, self.ihs.numGeodesicSamples)
+            dist = self._ops.euclid_hausdorff(self._data, sptr, spix, spa, spb)
+        elif sim in (ComponentSim.GEO_CENTROID, ComponentSim.GEO_WALKS):  # geodesicDistance (Similarities.cpp:142,146)
+            ptr, pix = self.representedDataPoints(level)
+            sptr, spix, spa, spb = subsampleComponentPairs(ptr, pix, pa, ids, self.ihs.numGeodesicSamples)
+            dist = self._ops.geodesic_hausdorff(self._graph, sptr, spix, spa, spb, self.ihs.componentLabels)
         else:
             raise NotImplementedError(sim)
         dist = np.asarray(dist, np.float32).copy()

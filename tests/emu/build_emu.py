@@ -15,7 +15,7 @@ ROOT = HERE.parent.parent
 CSRC = ROOT / "sph_b200" / "csrc"
 OUT = HERE / "_build"
 LIB = OUT / "libsphb200_emu.so"
-SOURCES = ["graph_merge.cu", "graph_ops.cu", "level_ops.cu", "sims.cu", "walks.cu", "prow.cu"]
+SOURCES = ["graph_merge.cu", "graph_ops.cu", "level_ops.cu", "sims.cu", "walks.cu", "prow.cu", "geodesic.cu", "level_api.cu"]
 
 
 def _split_top(s: str) -> list[str]:
@@ -69,20 +69,20 @@ def translate(text: str) -> str:
     return "".join(out)
 
 
-def build(verbose: bool = False, asan: bool = False) -> Path:
+def build(verbose: bool = False, asan: bool = False, defines: tuple = (), tag: str = "") -> Path:
     """asan=True builds libsphb200_emu_asan.so with AddressSanitizer: every "device" buffer is a heap block, so an
     out-of-bounds global-memory access of a kernel is reported (run with LD_PRELOAD=$(gcc -print-file-name=libasan.so)
     ASAN_OPTIONS=detect_leaks=0:detect_stack_use_after_return=0)."""
     OUT.mkdir(exist_ok=True)
-    lib = OUT / "libsphb200_emu_asan.so" if asan else LIB
+    lib = OUT / "libsphb200_emu_asan.so" if asan else (OUT / f"libsphb200_emu{tag}.so" if tag else LIB)
     srcs = []
     for name in SOURCES:
         dst = OUT / (Path(name).stem + "_emu.cpp")
         dst.write_text(f'#line 1 "{CSRC / name}"\n' + translate((CSRC / name).read_text()))
         srcs.append(dst)
     cmd = ["/usr/bin/g++", "-O1", "-g", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-fvisibility=hidden", "-D__CUDACC__",
-           *(["-fsanitize=address", "-fno-omit-frame-pointer"] if asan else []),
-           "-w", f"-I{HERE / 'include'}", f"-I{CSRC}", "-o", str(lib), *map(str, srcs), str(HERE / "emu_api.cpp")]
+           *(["-fsanitize=address", "-fno-omit-frame-pointer"] if asan else []), *defines,
+           "-w", f"-I{HERE / 'include'}", f"-I{CSRC}", "-o", str(lib), *map(str, srcs), str(HERE / "emu_api.cpp"), str(HERE / "emu_stubs.cpp")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0 or verbose:
         sys.stderr.write(r.stdout + r.stderr)

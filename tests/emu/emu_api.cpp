@@ -21,6 +21,8 @@ cudaError_t ws_alloc(void** p, size_t bytes, cudaStream_t) {
 }
 void ws_free(void* p, cudaStream_t) { std::free(p); }
 void ws_trim() {}
+void sims_force_slab(int on);
+void walks_force_scan(int on);
 int prow_graph_launch(const int64_t*, const float*, int64_t, int, float, int, uint32_t*, float*, double*, cudaStream_t);
 int prow_inplace_launch(int64_t, const int64_t*, float*, int, float, int, cudaStream_t);
 int prow_flat_launch(const float*, int64_t, int, double, float*, cudaStream_t);
@@ -43,6 +45,8 @@ SPHB_API int64_t sphb_launch_count(void) { return g_launches; }
 SPHB_API void sphb_reset_launch_count(void) { g_launches = 0; }
 SPHB_API void* sphb_stream(void) { return nullptr; }
 SPHB_API void sphb_debug_force_knn_path(int) {}
+SPHB_API void sphb_debug_force_sims_slab(int on) { sims_force_slab(on); }
+SPHB_API void sphb_debug_force_walk_scan(int on) { walks_force_scan(on); }
 SPHB_API int sphb_knn_exact(const float*, int64_t, int, int, int, int, int64_t*, float*) { return unsupported(); }
 SPHB_API int sphb_knn_exact_slab(const float*, int64_t, int, int, int, int, int64_t, int64_t, int64_t*, float*) { return unsupported(); }
 SPHB_API int sphb_knn_exact_dev(const float*, int64_t, int, int, int, int, int64_t, int64_t, int64_t*, float*, void*) { return unsupported(); }

@@ -36,6 +36,12 @@ inline cudaError_t cudaMemsetAsync(void* d, int v, size_t n, cudaStream_t) {
     return cudaSuccess;
 }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
+typedef void* cudaEvent_t;
+inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = nullptr; return cudaSuccess; }
+inline cudaError_t cudaEventDestroy(cudaEvent_t) { return cudaSuccess; }
+inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return cudaSuccess; }
+inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }
+inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0.f; return cudaSuccess; }
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 template <class F>
 inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute, int) { return cudaSuccess; }
@@ -244,6 +250,9 @@ inline int __all_sync(unsigned m, int pred) {
     return __ballot_sync(m, pred) == full;
 }
 
+// fast-math intrinsics: glibc declares (but does not export) these names
+#define __logf logf
+#define __expf expf
 inline int __popc(unsigned v) { return __builtin_popcount(v); }
 inline int __ffs(unsigned v) { return __builtin_ffs(static_cast<int>(v)); }
 inline unsigned __float_as_uint(float f) { return emu::from_bits<unsigned>(emu::to_bits(f)); }
@@ -255,6 +264,19 @@ inline float __fdiv_rn(float a, float b) { return a / b; }
 inline unsigned __umulhi(unsigned a, unsigned b) { return static_cast<unsigned>((static_cast<uint64_t>(a) * b) >> 32); }
 template <class T>
 inline T __ldg(const T* p) { return *p; }
+template <class T>
+inline T __ldcg(const T* p) { return *p; }
+inline void __threadfence() {}
+inline void __threadfence_block() {}
+template <class T>
+inline unsigned __match_any_sync(unsigned, T v) {
+    uint64_t o[32];
+    emu::warp_exchange(emu::to_bits(v), o);
+    const unsigned tid = emu::B().cur->tid, lanes = std::min(32u, emu::B().nthreads - (tid & ~31u));
+    unsigned m = 0;
+    for (unsigned l = 0; l < lanes; ++l) m |= (o[l] == o[emu::lane_id()]) ? (1u << l) : 0u;
+    return m;
+}
 
 // single OS thread: atomics are plain read-modify-writes
 template <class T>
@@ -266,6 +288,10 @@ template <class T>
 inline T atomicMin(T* p, T v) { T o = *p; if (v < o) *p = v; return o; }
 template <class T>
 inline T atomicExch(T* p, T v) { T o = *p; *p = v; return o; }
+template <class T>
+inline T atomicOr(T* p, T v) { T o = *p; *p = o | v; return o; }
+template <class T>
+inline T atomicAnd(T* p, T v) { T o = *p; *p = o & v; return o; }
 
 using std::max;
 using std::min;

@@ -600,6 +600,14 @@ class OracleOps:
     def euclid_hausdorff(self, data, comp_ptr, comp_pix, pa, pb):
         return self.o.euclid_hausdorff(data, comp_ptr, comp_pix, pa, pb)
 
+    def geodesic_hausdorff(self, graph, comp_ptr, comp_pix, pa, pb, labels=None):
+        return self.o.geodesic_hausdorff(getattr(graph, "rowptr", None), graph.knnIndices, graph.knnDistances, comp_ptr, comp_pix, pa, pb, labels=labels)
+
+    def prow_ragged(self, graph, scheme):
+        from sph_b200 import host
+
+        return host.SparseRows(*self.o.prow_graph_ragged(graph.rowptr, graph.knnIndices, graph.knnDistances, 0.0, scheme == host.NormalizationScheme.LINEAR))
+
 
 def dense_to_csr(m):
     m = np.asarray(m, np.float32)

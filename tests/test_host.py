@@ -231,6 +231,9 @@ def capi_on_oracle(monkeypatch, oracle):
     monkeypatch.setattr(capi, "level_knn_overlap", lambda ids, ptr, pix, k: o.level_knn_overlap(ids, ptr, pix, k))
     monkeypatch.setattr(capi, "euclid_hausdorff", lambda x, ptr, pix, pa, pb: o.euclid_hausdorff(x, ptr, pix, pa, pb))
     monkeypatch.setattr(capi, "level_knn_walks", lambda rp, c, v, k, mode=0: o.level_knn_walks(rp, c, v, k, mode))
+    monkeypatch.setattr(capi, "geodesic_hausdorff",
+                        lambda ids, dist, ptr, pix, pa, pb, rowptr=None, labels=None: o.geodesic_hausdorff(rowptr, ids, dist, ptr, pix, pa, pb, labels=labels))
+    monkeypatch.setattr(capi, "prow_graph_ragged", lambda rp, ids, dist, perp=0.0, linear=False: o.prow_graph_ragged(rp, ids, dist, perp, linear))
 
     def level_knn_euclid(x, ptr, pix, k):  # all pairs through the checker's Hausdorff distance, rows ordered by (distance, index)
         n_l = len(ptr) - 1
@@ -342,3 +345,100 @@ def test_level_similarities_euclid_control_flow(capi_on_oracle, oracle):
     assert g.knnIndices.shape[0] == n1 and (g.knnIndices[:, 0] == np.arange(n1)).all() and (g.knnDistances[:, 0] == 0).all()
     assert (np.diff(g.knnDistances, axis=1) >= 0).all()
     assert ls.getProbDist(1).n == n1
+
+
+def _l2_graph(oracle, x, k):
+    ids, dist = oracle.knn_reference_graph(x, k)
+    return ids, np.sqrt(dist).astype(np.float32)  # L2squared = false: true L2 distances (sph/NearestNeighbors.cpp:224-231)
+
+
+@pytest.mark.parametrize("sim", ["GEO_CENTROID", "GEO_WALKS"])
+def test_image_hierarchy_geodesic_control_flow(capi_on_oracle, oracle, sim):
+    """GEO_CENTROID / GEO_WALKS (sph/ImageHierarchy.cpp:192-249 -> componentDistance -> geodesicDistance): the merge loop asks
+    for the geodesic distance of every (component, spatial neighbour) pair of a level in one batched call."""
+    import oracle_lib
+    from sph_b200 import host
+
+    rng = np.random.default_rng(12)
+    x = rng.standard_normal((30, 4)).astype(np.float32)
+    ids, dist = _l2_graph(oracle, x, 5)
+    graph = host.Graph(ids, dist)
+    ih = host.ImageHierarchy(graph, x, 6, 5, ops=oracle_lib.OracleOps(oracle))
+    ih.compute(host.ImageHierarchySettings(componentSim=getattr(host.ComponentSim, sim), usePercentile=False))
+    assert ih.getNumLevels() >= 3 and ih.numComponents[-1] == 1
+    # level-0 distances are computeShortestPath values of the 4-neighbour pairs, rows sorted, self first
+    d0 = ih.computeDistances(0)
+    for c in (0, 7, 29):
+        nb = d0.getNeighbors(c)
+        dd = d0.getDistances(c)
+        assert nb[0] == c and dd[0] == 0 and (np.diff(dd) >= 0).all()
+        ref = oracle.shortest_paths(None, ids, dist, np.full(len(nb), c), nb)
+        ref[ref < 0] = np.finfo(np.float32).max
+        assert np.array_equal(dd, ref)
+    # a higher level: the Hausdorff distance over the represented points
+    d1 = ih.computeDistances(1)
+    ptr, pix = ih.representedDataPoints(1)
+    nb = d1.getNeighbors(0)
+    ref = oracle.geodesic_hausdorff(None, ids, dist, ptr, pix, np.zeros(len(nb), np.int64), nb)
+    ref[nb == 0] = 0
+    assert np.array_equal(np.sort(ref), d1.getDistances(0))
+
+
+def test_image_hierarchy_geodesic_ragged_graph_and_labels(capi_on_oracle, oracle):
+    """The GEO_* configurations run on the connected (ragged) graph with the component labels (sph/ComputeHierarchy.cpp:135-144)."""
+    import oracle_lib
+    from sph_b200 import host
+
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((24, 3)).astype(np.float32)
+    x[12:] += 40  # two components
+    ids, dist = _l2_graph(oracle, x, 4)
+    rp, sid, sdist = oracle.symmetrize_graph(ids, dist)
+    graph = host.RaggedGraph(rp, sid, sdist, symmetric=True)
+    labels = (np.arange(24) >= 12).astype(np.int64)
+    ih = host.ImageHierarchy(graph, x, 6, 4, ops=oracle_lib.OracleOps(oracle))
+    ih.compute(host.ImageHierarchySettings(componentSim=host.ComponentSim.GEO_CENTROID, usePercentile=False, componentLabels=labels))
+    assert ih.getNumLevels() >= 2
+    d0 = ih.computeDistances(0)
+    # pixel 11 (row 2, col 3) and pixel 15 (row 3, col 3) are spatial neighbours in different components: no path
+    nb, dd = d0.getNeighbors(11), d0.getDistances(11)
+    assert dd[list(nb).index(15)] == np.finfo(np.float32).max
+
+
+def test_level_similarities_geodesic_knn(capi_on_oracle, oracle):
+    """LevelSimilarities with GEO_CENTROID: exact level kNN in GeodesicPathSpace, then useKnnDistances (LevelSimilarities.cpp:405-407, :558-561)."""
+    import oracle_lib
+    from sph_b200 import host
+
+    rng = np.random.default_rng(6)
+    x = rng.standard_normal((24, 5)).astype(np.float32)
+    ids, dist = _l2_graph(oracle, x, 4)
+    graph = host.Graph(ids, dist)
+    ih = host.ImageHierarchy(graph, x, 6, 4, ops=oracle_lib.OracleOps(oracle))
+    ih.compute(host.ImageHierarchySettings(componentSim=host.ComponentSim.GEO_CENTROID, usePercentile=False))
+    ls = host.LevelSimilarities(graph, hierarchy=ih)
+    ls.compute(host.LevelSimilaritiesSettings(levelToCompute=1, componentSim=host.ComponentSim.GEO_CENTROID))
+    g = ls.getSimilaritiesGraph(1)
+    n1 = ih.numComponents[1]
+    assert g.knnIndices.shape[0] == n1 and (g.knnIndices[:, 0] == np.arange(n1)).all() and (g.knnDistances[:, 0] == 0).all()
+    assert (np.diff(g.knnDistances, axis=1) >= 0).all()
+    ptr, pix = ih.representedDataPoints(1)
+    row = oracle.geodesic_hausdorff(None, ids, dist, ptr, pix, np.full(n1, 2, np.int64), np.arange(n1))
+    order = np.lexsort((np.arange(n1), row))[:g.knnIndices.shape[1]]
+    assert np.array_equal(g.knnIndices[2], order) and np.array_equal(g.knnDistances[2], row[order])
+    assert ls.getProbDist(1).n == n1
+
+
+def test_subsample_component_pairs():
+    from sph_b200 import host
+
+    ptr = np.array([0, 2, 12, 30], np.int64)
+    pix = np.arange(30, dtype=np.int64)
+    sptr, spix, spa, spb = host.subsampleComponentPairs(ptr, pix, [0, 1, 2], [1, 2, 2], 5, rng=np.random.default_rng(0))
+    assert list(spa[:1]) == [0] and list(spb[:1]) == [1]            # 2 x 10 <= 25: untouched
+    assert spa[1] >= 3 and spb[1] >= 3 and spa[2] >= 3 and spb[2] >= 3  # 10 x 18 and 18 x 18: both sides replaced by samples
+    for c, src in ((spa[1], 1), (spb[1], 2), (spa[2], 2), (spb[2], 2)):
+        lst = spix[sptr[c]:sptr[c + 1]]
+        assert len(lst) == 5 and set(lst) <= set(pix[ptr[src]:ptr[src + 1]])
+    same = host.subsampleComponentPairs(ptr, pix, [0, 1], [1, 2], None)
+    assert same[0] is not None and len(same[0]) == 4
