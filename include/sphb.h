@@ -373,6 +373,28 @@ SPHB_API int sphb_geodesic_hausdorff(int64_t n, const int64_t* rowptr, int k, co
                                      int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, const int64_t* pa, const int64_t* pb,
                                      int64_t npairs, float* out);
 SPHB_API int sphb_geodesic_last_stats(int64_t* out4);
+/* SURVEY 8(f)-4, cache blobs — the reference's stage-cache files (sph/utils/FileIO.hpp:165-291, 523-640; FileIO.cpp:586-618,
+ * 620-799, 895-937, 1274-1460), written and read on the HOST so that results of this back-end can be dropped into the
+ * reference's cache directory and loaded by it, and the reverse.  Blocks are LZ4 block format (LZ4_compress_default /
+ * LZ4_decompress_safe); files above INT_MAX bytes use the reference's chunked layout.
+ *   vec:   writeCompressedVecToBinary<T> / loadCompressedVecFromBinary<T> (connected-component labels, spanning-tree ids, ...)
+ *   graph: writeCompressedGraphToBinary / loadCompressedGraphFromBinary — <base>Distances.cache, <base>Indices.cache,
+ *          <base>NNs.cache, <base>Symmetric.cache (kNN / symmetric / connected graphs, sph/NearestNeighbors.cpp:1011-1017; level
+ *          graphs, sph/LevelSimilarities.cpp:744); rowptr NULL = fixed k
+ *   prob:  writeCompressedSparseMatHDIToBinary / loadCompressedSparseMatHDIFromBinary — a P matrix as CSR
+ *          (_lls_probDist<level>.cache, sph/LevelSimilarities.cpp:763-787)
+ * Readers called with NULL output arrays fill only the sizes (*count / *n, *nnz). */
+SPHB_API int64_t sphb_lz4_compress_bound(int64_t n);
+SPHB_API int64_t sphb_lz4_compress(const void* src, int64_t n, void* dst, int64_t cap);   /* bytes written, -1 on failure */
+SPHB_API int64_t sphb_lz4_decompress(const void* src, int64_t n, void* dst, int64_t cap); /* bytes written, -1 on a malformed block */
+SPHB_API int sphb_cache_write_vec(const char* path, const void* data, int64_t count, int elem_size);
+SPHB_API int sphb_cache_read_vec(const char* path, void* out, int64_t cap, int elem_size, int64_t* count);
+SPHB_API int sphb_cache_write_graph(const char* base, int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, int symmetric);
+SPHB_API int sphb_cache_read_graph(const char* base, int64_t cap_n, int64_t cap_nnz, int64_t* n, int64_t* nnz, int64_t* nns, int64_t* ids,
+                                   float* dist, int* symmetric);
+SPHB_API int sphb_cache_write_prob(const char* path, int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val);
+SPHB_API int sphb_cache_read_prob(const char* path, int64_t cap_n, int64_t cap_nnz, int64_t* n, int64_t* nnz, int64_t* rowptr, uint32_t* col,
+                                  float* val);
 /* The same exact level kNN in the neighbour-overlap metric (NeighborOverlapSpace, sph/utils/NeighborOverlapSpace.hpp:31-43;
  * the default componentSim of LevelSimilaritiesSettings, sph/utils/Settings.hpp:170): distance 1 - simNeighborOverlap
  * (sph/utils/Similarities.cpp:174-228) over the components' kNN-id unions; arguments as sphb_neighbor_overlap.

@@ -109,6 +109,15 @@ SIGNATURES = {
     "sphb_geodesic_distances": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_geodesic_hausdorff": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_geodesic_last_stats": (C.c_int, [i64p]),
+    "sphb_lz4_compress_bound": (C.c_int64, [C.c_int64]),
+    "sphb_lz4_compress": (C.c_int64, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
+    "sphb_lz4_decompress": (C.c_int64, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
+    "sphb_cache_write_vec": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int64, C.c_int]),
+    "sphb_cache_read_vec": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int64, C.c_int, i64p]),
+    "sphb_cache_write_graph": (C.c_int, [C.c_char_p, C.c_int64, i64p, C.c_int, i64p, f32p, C.c_int]),
+    "sphb_cache_read_graph": (C.c_int, [C.c_char_p, C.c_int64, C.c_int64, i64p, i64p, i64p, i64p, f32p, C.POINTER(C.c_int)]),
+    "sphb_cache_write_prob": (C.c_int, [C.c_char_p, C.c_int64, i64p, u32p, f32p]),
+    "sphb_cache_read_prob": (C.c_int, [C.c_char_p, C.c_int64, C.c_int64, i64p, i64p, i64p, u32p, f32p]),
 }
 
 
@@ -139,6 +148,8 @@ def load():
     lib.sphb_debug_force_sims_slab.argtypes = [C.c_int]
     lib.sphb_debug_force_walk_scan.restype = None
     lib.sphb_debug_force_walk_scan.argtypes = [C.c_int]
+    lib.sphb_debug_cache_chunk_limit.restype = None
+    lib.sphb_debug_cache_chunk_limit.argtypes = [C.c_int64]
     _lib = lib
     return lib
 
@@ -683,6 +694,87 @@ def geodesic_last_stats() -> dict:
     out = np.zeros(4, np.int64)
     _check(load().sphb_geodesic_last_stats(_p(out, i64p)))
     return dict(expanded=int(out[0]), passes=int(out[1]), searches=int(out[2]), sources=int(out[3]))
+
+
+# ------------------------------------------------------------------ the reference's cache blobs (host code, no GPU needed)
+def cache_chunk_limit(nbytes: int):
+    """Byte limit above which the chunked layouts are written (INT_MAX in the reference; tests lower it).  0 restores the default."""
+    load().sphb_debug_cache_chunk_limit(int(nbytes))
+
+
+def lz4_compress(data: bytes) -> bytes:
+    L = load()
+    cap = int(L.sphb_lz4_compress_bound(len(data)))
+    dst = C.create_string_buffer(cap)
+    m = int(L.sphb_lz4_compress(data, len(data), dst, cap))
+    if m < 0:
+        raise SphbError("lz4_compress failed")
+    return dst.raw[:m]
+
+
+def lz4_decompress(block: bytes, size: int) -> bytes:
+    dst = C.create_string_buffer(max(size, 1))
+    m = int(load().sphb_lz4_decompress(block, len(block), dst, size))
+    if m < 0:
+        raise SphbError("lz4_decompress: malformed block or output too small")
+    return dst.raw[:m]
+
+
+def cache_write_vec(path, vec: np.ndarray):
+    """writeCompressedVecToBinary<T> (sph/utils/FileIO.hpp:279-291)."""
+    vec = np.ascontiguousarray(vec)
+    _check(load().sphb_cache_write_vec(str(path).encode(), vec.ctypes.data_as(C.c_void_p), vec.size, vec.dtype.itemsize))
+
+
+def cache_read_vec(path, dtype) -> np.ndarray:
+    """loadCompressedVecFromBinary<T> (sph/utils/FileIO.hpp:523-640)."""
+    dtype = np.dtype(dtype)
+    cnt = np.zeros(1, np.int64)
+    _check(load().sphb_cache_read_vec(str(path).encode(), None, 0, dtype.itemsize, _p(cnt, i64p)))
+    out = np.zeros(max(int(cnt[0]), 1), dtype)
+    _check(load().sphb_cache_read_vec(str(path).encode(), out.ctypes.data_as(C.c_void_p), len(out), dtype.itemsize, _p(cnt, i64p)))
+    return out[: int(cnt[0])]
+
+
+def cache_write_graph(base, ids, dist, rowptr=None, symmetric: bool = False):
+    """writeCompressedGraphToBinary (sph/utils/FileIO.cpp:586-618): <base>{Distances,Indices,NNs,Symmetric}.cache."""
+    n, rp, k, ids, dist = _geo_graph(ids, dist, rowptr)
+    _check(load().sphb_cache_write_graph(str(base).encode(), n, None if rp is None else _p(rp, i64p), k, _p(ids, i64p), _p(dist, f32p), int(symmetric)))
+
+
+def cache_read_graph(base):
+    """loadCompressedGraphFromBinary (sph/utils/FileIO.cpp:895-937): (rowptr, ids, dist, symmetric)."""
+    n = np.zeros(1, np.int64)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_cache_read_graph(str(base).encode(), 0, 0, _p(n, i64p), _p(nnz, i64p), None, None, None, None))
+    nns = np.zeros(max(int(n[0]), 1), np.int64)
+    ids = np.zeros(max(int(nnz[0]), 1), np.int64)
+    dist = np.zeros(max(int(nnz[0]), 1), np.float32)
+    sym = C.c_int(0)
+    _check(load().sphb_cache_read_graph(str(base).encode(), len(nns), len(ids), _p(n, i64p), _p(nnz, i64p), _p(nns, i64p), _p(ids, i64p), _p(dist, f32p),
+                                        C.byref(sym)))
+    rowptr = np.concatenate([[0], np.cumsum(nns[: int(n[0])])]).astype(np.int64)
+    return rowptr, ids[: int(nnz[0])], dist[: int(nnz[0])], bool(sym.value)
+
+
+def cache_write_prob(path, rowptr, col, val):
+    """writeCompressedSparseMatHDIToBinary (sph/utils/FileIO.cpp:620-799)."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    _check(load().sphb_cache_write_prob(str(path).encode(), len(rowptr) - 1, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p)))
+
+
+def cache_read_prob(path):
+    """loadCompressedSparseMatHDIFromBinary (sph/utils/FileIO.cpp:1274-1460): (rowptr, col, val)."""
+    n = np.zeros(1, np.int64)
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_cache_read_prob(str(path).encode(), 0, 0, _p(n, i64p), _p(nnz, i64p), None, None, None))
+    rowptr = np.zeros(int(n[0]) + 1, np.int64)
+    col = np.zeros(max(int(nnz[0]), 1), np.uint32)
+    val = np.zeros(max(int(nnz[0]), 1), np.float32)
+    _check(load().sphb_cache_read_prob(str(path).encode(), int(n[0]), len(col), _p(n, i64p), _p(nnz, i64p), _p(rowptr, i64p), _p(col, u32p), _p(val, f32p)))
+    return rowptr, col[: int(nnz[0])], val[: int(nnz[0])]
 
 
 # ------------------------------------------------------------------ resident level pipeline

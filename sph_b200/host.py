@@ -751,6 +751,51 @@ def euclidDistance(data: np.ndarray, comp_ptr, comp_pix, pairs_a, pairs_b) -> np
     return capi.euclid_hausdorff(data, comp_ptr, comp_pix, pairs_a, pairs_b)
 
 
+# ---- the reference's stage-cache blobs (sph/utils/FileIO.{hpp,cpp}): LZ4 files this back-end writes and reads so
+# that its results can be dropped into the reference's cache directory (and the reference's loaded here)
+def writeCompressedGraphToBinary(file_name_base: str, graph) -> None:
+    """utils::writeCompressedGraphToBinary (sph/utils/FileIO.cpp:586-618)."""
+    from . import capi
+
+    capi.cache_write_graph(file_name_base, graph.knnIndices, graph.knnDistances, rowptr=getattr(graph, "rowptr", None), symmetric=bool(graph.symmetric))
+
+
+def loadCompressedGraphFromBinary(file_name_base: str) -> RaggedGraph:
+    """utils::loadCompressedGraphFromBinary (sph/utils/FileIO.cpp:895-937)."""
+    from . import capi
+
+    rp, ids, dist, sym = capi.cache_read_graph(file_name_base)
+    return RaggedGraph(rp, ids, dist, symmetric=sym)
+
+
+def writeCompressedSparseMatHDIToBinary(path: str, matrix: SparseRows) -> None:
+    """utils::writeCompressedSparseMatHDIToBinary (sph/utils/FileIO.cpp:620-799): a P matrix, e.g. `_lls_probDist<level>.cache`."""
+    from . import capi
+
+    capi.cache_write_prob(path, matrix.rowptr, matrix.col, matrix.val)
+
+
+def loadCompressedSparseMatHDIFromBinary(path: str) -> SparseRows:
+    """utils::loadCompressedSparseMatHDIFromBinary (sph/utils/FileIO.cpp:1274-1460)."""
+    from . import capi
+
+    return SparseRows(*capi.cache_read_prob(path))
+
+
+def writeCompressedVecToBinary(path: str, vec: np.ndarray) -> None:
+    """utils::writeCompressedVecToBinary<T> (sph/utils/FileIO.hpp:279-291), e.g. the connected-component labels."""
+    from . import capi
+
+    capi.cache_write_vec(path, vec)
+
+
+def loadCompressedVecFromBinary(path: str, dtype) -> np.ndarray:
+    """utils::loadCompressedVecFromBinary<T> (sph/utils/FileIO.hpp:523-640)."""
+    from . import capi
+
+    return capi.cache_read_vec(path, dtype)
+
+
 def geodesicDistance(graph, comp_ptr, comp_pix, pairs_a, pairs_b, labels=None) -> np.ndarray:
     """Batched utils::geodesicDistance (sph/utils/Similarities.cpp:234-309) over component pairs: one single-source search on the
     device per point of every first component (sphb_geodesic_hausdorff)."""
