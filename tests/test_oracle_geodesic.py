@@ -7,7 +7,10 @@ import pytest
 
 def knn_graph_l2(x, k):
     """Exact kNN graph with TRUE L2 distances (L2squared = false, the reference default), self first."""
-    d2 = ((x[:, None, :].astype(np.float64) - x[None, :, :].astype(np.float64)) ** 2).sum(-1)
+    x64 = x.astype(np.float64)
+    sq = (x64 * x64).sum(1)
+    d2 = np.maximum(sq[:, None] + sq[None, :] - 2.0 * (x64 @ x64.T), 0.0)
+    d2[np.arange(len(x)), np.arange(len(x))] = 0.0
     ids = np.argsort(d2, axis=1, kind="stable")[:, :k]
     for i in range(len(x)):  # ensureClosestPointIsSelf for duplicate points
         if ids[i, 0] != i:
