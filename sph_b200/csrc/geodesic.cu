@@ -422,7 +422,7 @@ static int geodesic_run(int64_t n, const int64_t* rowptr, int k, const int64_t* 
     SPHB_CUDA(d_dw.alloc(static_cast<size_t>(grid * n), s));
     SPHB_CUDA(d_bm.alloc(static_cast<size_t>(grid * nwords), s));
     const int sms = ctx().num_sms;
-    geo_fill_kernel<<<static_cast<unsigned>(std::min<int64_t>((cols + 255) / 256, static_cast<int64_t>(sms) * 8)), 256, 0, s>>>(d_colmin.p, cols, 0xffffffffu);
+    geo_fill_kernel<<<static_cast<unsigned>(std::max<int64_t>(1, std::min<int64_t>((cols + 255) / 256, static_cast<int64_t>(sms) * 8))), 256, 0, s>>>(d_colmin.p, cols, 0xffffffffu);
     count_launch();
     GeoGraph G{n, d_rowptr.p, d_ids.p, d_dist.p, labels ? d_labels.p : nullptr};
     GeoComps C{comp_ptr ? d_cptr.p : nullptr, comp_ptr ? d_cpix.p : nullptr};

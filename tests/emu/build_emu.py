@@ -15,7 +15,7 @@ ROOT = HERE.parent.parent
 CSRC = ROOT / "sph_b200" / "csrc"
 OUT = HERE / "_build"
 LIB = OUT / "libsphb200_emu.so"
-SOURCES = ["graph_merge.cu", "graph_ops.cu", "level_ops.cu", "sims.cu", "walks.cu", "prow.cu", "geodesic.cu", "level_api.cu"]
+SOURCES = ["graph_merge.cu", "graph_ops.cu", "level_ops.cu", "sims.cu", "walks.cu", "prow.cu", "geodesic.cu", "level_api.cu", "cache_io.cu"]
 
 
 def _split_top(s: str) -> list[str]:

@@ -156,3 +156,6 @@ def test_bad_arguments(capi):
     with pytest.raises(SphbError):
         capi.geodesic_distances(ids, np.array([[0, 1], [0, 1]], np.float32), [0], [2])
     assert len(capi.geodesic_distances(ids, np.array([[0, 1], [0, 1]], np.float32), [], [])) == 0
+    # nothing but empty components: no search, no column minima, distance 0 as utils::euclidDistance's batched form returns it
+    out = capi.geodesic_hausdorff(ids, np.array([[0, 1], [0, 1]], np.float32), [0, 0, 0], np.zeros(0, np.int64), [0, 1], [1, 1])
+    assert out.tolist() == [0, 0]
