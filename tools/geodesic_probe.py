@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--cpu-pairs", type=int, default=1500)
     ap.add_argument("--shape", default="512,217,204,16,1002")
     ap.add_argument("--k", type=int, default=91)
+    ap.add_argument("--level1", action="store_true")
     args = ap.parse_args()
     from sph_b200 import capi, synth
 
@@ -61,6 +62,31 @@ def main():
         st = capi.geodesic_last_stats()
         emit({"what": name, "pairs": len(pa), "sources": st["sources"], "searches": st["searches"], "expanded": st["expanded"], "passes": st["passes"],
               "seconds_host_buffers": sec, "pairs_per_s": len(pa) / sec, "no_path": int((out < 0).sum()), "checksum": float(out[out >= 0].astype(np.float64).sum())})
+    if args.level1:  # level 1 of a 2 x 2 block hierarchy: Hausdorff over the blocks' pixels, every block against its 4 block neighbours
+        hb, wb = h // 2, w // 2
+        blk = (np.arange(h)[:, None] // 2 * wb + np.arange(w)[None, :] // 2)[: hb * 2, : wb * 2].reshape(-1)
+        pix = (np.arange(hb * 2)[:, None] * w + np.arange(wb * 2)[None, :]).reshape(-1)
+        order = np.argsort(blk, kind="stable")
+        comp_pix = pix[order].astype(np.int64)
+        comp_ptr = np.arange(hb * wb + 1, dtype=np.int64) * 4
+        qa, qb = grid_pairs(hb, wb, 0, hb)
+        t = time.perf_counter()
+        o1 = capi.geodesic_hausdorff(ids, dist, comp_ptr, comp_pix, qa, qb)
+        sec = time.perf_counter() - t
+        st = capi.geodesic_last_stats()
+        emit({"what": "level1_2x2_blocks", "pairs": len(qa), "components": hb * wb, "sources": st["sources"], "searches": st["searches"],
+              "expanded": st["expanded"], "passes": st["passes"], "seconds_host_buffers": sec, "pairs_per_s": len(qa) / sec,
+              "checksum": float(o1.astype(np.float64).sum())})
+        if args.cpu_pairs > 0:
+            import oracle_lib
+
+            orc = oracle_lib.load()
+            sel = np.random.default_rng(1).choice(len(qa), min(args.cpu_pairs, len(qa)), replace=False)
+            t = time.perf_counter()
+            ref = orc.geodesic_hausdorff(None, ids, dist, comp_ptr, comp_pix, qa[sel], qb[sel])
+            csec = time.perf_counter() - t
+            emit({"what": "cpu_port_sample_level1", "pairs": len(sel), "seconds": csec, "pairs_per_s": len(sel) / csec, "cores": os.cpu_count(),
+                  "mismatches_vs_device": int((ref != o1[sel]).sum())})
     if args.cpu_pairs > 0:  # the oracle's restatement of computeShortestPath on a sample of the same pairs, all host cores
         import oracle_lib
 
