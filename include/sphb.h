@@ -436,6 +436,21 @@ SPHB_API int sphb_symmetrize_dev(int64_t n, const int64_t* d_rowptr, const uint3
 /* utils::findTopK / findBottomK batched (sph/utils/SparseMatrixAlgorithms.cpp:720-776); max_row_nnz <= 0: computed on the device. */
 SPHB_API int sphb_find_k_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int max_row_nnz, int64_t k, int top,
                              uint32_t* d_out_cols, float* d_out_vals, int32_t* d_row_nnz, void* stream);
+/* SURVEY 8(e), createSimilarities sharded by OUTPUT ROW: rows [r0, r1) of the result only (every output row needs the whole
+ * random-walk matrix and nothing of the other output rows, so slabs computed on different devices concatenate to exactly the
+ * one-call result).  Outputs hold r1 - r0 rows in the layout of sphb_create_similarities. */
+SPHB_API int sphb_create_similarities_slab(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int64_t k, float prune_val,
+                                           int variant, const int64_t* comp_sizes, int64_t r0, int64_t r1, uint32_t* out_cols, float* out_vals,
+                                           int32_t* row_nnz);
+SPHB_API int sphb_create_similarities_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k,
+                                               float prune_val, int variant, const int64_t* d_comp_sizes, int64_t r0, int64_t r1,
+                                               uint32_t* d_out_cols, float* d_out_vals, int32_t* d_row_nnz, void* stream);
+/* The part of sphb_level_prob_dist_dev behind createSimilarities / the top-k conversion: fixed-stride rows (n x k, cols padded
+ * 0xFFFFFFFF, row_nnz[n] — e.g. the gathered slabs of sphb_create_similarities_slab_dev) -> CSR -> Gaussian rows in place
+ * (scheme 1) -> zero removal -> symmetrizeTSNE (symmetrize != 0).  Output as sphb_level_prob_dist_dev. */
+SPHB_API int sphb_level_from_sims_dev(int64_t n, int64_t k, const uint32_t* d_cols, const float* d_vals, const int32_t* d_row_nnz, float perplexity,
+                                      int scheme, int symmetrize, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap,
+                                      int64_t* out_nnz, void* stream);
 /*
  * One level of LevelSimilarities::computeProbDistOnLevel's useRandomWalks branch + symmetrizeOutput in ONE call on the level's
  * random-walk matrix (sph/LevelSimilarities.cpp:460-508, 566-581, 589-623), every intermediate resident in HBM:

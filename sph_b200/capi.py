@@ -106,6 +106,11 @@ SIGNATURES = {
     "sphb_level_prob_dist": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, C.c_int, C.c_float, C.c_int, C.c_int, i64p,
                                        u32p, f32p, C.c_int64, i64p]),
     "sphb_level_last_timing": (C.c_int, [f32p]),
+    "sphb_create_similarities_slab": (C.c_int, [C.c_int64, i64p, u32p, f32p, C.c_int64, C.c_float, C.c_int, i64p, C.c_int64, C.c_int64, u32p, f32p, i32p]),
+    "sphb_create_similarities_slab_dev": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_float, C.c_int, C.c_void_p,
+                                                    C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sphb_level_from_sims_dev": (C.c_int, [C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_int64, i64p, C.c_void_p]),
     "sphb_geodesic_distances": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_geodesic_hausdorff": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_geodesic_last_stats": (C.c_int, [i64p]),
@@ -412,6 +417,22 @@ def create_similarities(rowptr, col, val, k: int, prune_val: float = 1e-4, varia
     _check(load().sphb_create_similarities(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), k, prune_val, variant,
                                            _p(cs, i64p) if cs is not None else None, _p(oc, u32p), _p(ov, f32p), _p(nnz, i32p)))
     return oc, ov, nnz
+
+
+def create_similarities_slab(rowptr, col, val, k: int, r0: int, r1: int, prune_val: float = 1e-4, variant: int = 0, comp_sizes=None):
+    """Rows [r0, r1) of createSimilarities (D1 sharded by output row); outputs hold r1 - r0 rows."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    col = np.ascontiguousarray(col, np.uint32)
+    val = np.ascontiguousarray(val, np.float32)
+    n = len(rowptr) - 1
+    nr = max(r1 - r0, 0)
+    oc = np.zeros((nr, k), np.uint32)
+    ov = np.zeros((nr, k), np.float32)
+    nnz = np.zeros(max(nr, 1), np.int32)
+    cs = None if comp_sizes is None else np.ascontiguousarray(comp_sizes, np.int64)
+    _check(load().sphb_create_similarities_slab(n, _p(rowptr, i64p), _p(col, u32p), _p(val, f32p), k, prune_val, variant,
+                                                _p(cs, i64p) if cs is not None else None, r0, r1, _p(oc, u32p), _p(ov, f32p), _p(nnz, i32p)))
+    return oc, ov, nnz[:nr]
 
 
 def pair_sims(rowptr, col, val, pa, pb, mode: int = 0) -> np.ndarray:
@@ -824,6 +845,19 @@ def rw_merge_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, parents_ptr, n_merged,
 def create_similarities_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, out_cols_ptr, out_vals_ptr, row_nnz_ptr, stream):
     _check(load().sphb_create_similarities_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, out_cols_ptr, out_vals_ptr,
                                                row_nnz_ptr, stream))
+
+
+def create_similarities_slab_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, r0, r1, out_cols_ptr, out_vals_ptr,
+                                 row_nnz_ptr, stream):
+    _check(load().sphb_create_similarities_slab_dev(n, rowptr_ptr, col_ptr, val_ptr, nnz_in, k, prune_val, variant, comp_sizes_ptr, r0, r1, out_cols_ptr,
+                                                    out_vals_ptr, row_nnz_ptr, stream))
+
+
+def level_from_sims_dev(n, k, cols_ptr, vals_ptr, row_nnz_ptr, perplexity, scheme, symmetrize, out_rowptr_ptr, out_col_ptr, out_val_ptr, cap, stream) -> int:
+    nnz = np.zeros(1, np.int64)
+    _check(load().sphb_level_from_sims_dev(n, k, cols_ptr, vals_ptr, row_nnz_ptr, perplexity, scheme, int(symmetrize), out_rowptr_ptr, out_col_ptr,
+                                           out_val_ptr, cap, _p(nnz, i64p), stream))
+    return int(nnz[0])
 
 
 def prow_gaussian_inplace_dev(n, rowptr_ptr, val_ptr, max_row_nnz, perplexity, ignore, stream):

@@ -267,6 +267,9 @@ int random_walks_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, 
                      int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s);
 int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
                             int variant, const int64_t* d_comp_sizes, uint32_t* d_out_cols, float* d_out_vals, int32_t* d_row_nnz, cudaStream_t s);
+int create_similarities_rows_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
+                                 int variant, const int64_t* d_comp_sizes, int64_t r0, int64_t r1, uint32_t* d_out_cols, float* d_out_vals,
+                                 int32_t* d_row_nnz, cudaStream_t s);
 
 }  // namespace sphb
 
@@ -436,6 +439,40 @@ SPHB_API int sphb_create_similarities(int64_t n, const int64_t* rowptr, const ui
     SPHB_CUDA(cudaMemcpyAsync(out_cols, oc.p, nk * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaMemcpyAsync(out_vals, ov.p, nk * sizeof(float), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaMemcpyAsync(row_nnz, on.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaStreamSynchronize(s));
+    return SPHB_OK;
+}
+
+SPHB_API int sphb_create_similarities_slab(int64_t n, const int64_t* rowptr, const uint32_t* col, const float* val, int64_t k, float prune_val,
+                                           int variant, const int64_t* comp_sizes, int64_t r0, int64_t r1, uint32_t* out_cols, float* out_vals,
+                                           int32_t* row_nnz) {
+    if (int rc = ensure_init()) return rc;
+    if (bad_csr(n, rowptr, col, val) || k <= 0 || !out_cols || !out_vals || !row_nnz || variant < 0 || variant > 2)
+        return fail(SPHB_ERR_INVALID, "create_similarities: bad arguments");
+    if (r0 < 0 || r1 > n || r0 > r1) return fail(SPHB_ERR_INVALID, "create_similarities_slab: row range outside [0, n]");
+    if (r0 == r1) return SPHB_OK;
+    const int64_t nr = r1 - r0;
+    cudaStream_t s = ctx().stream;
+    DevCsr in;
+    if (int rc = upload_csr(n, rowptr, col, val, in, s)) return rc;
+    DevBuf<int64_t> dcs;
+    DevBuf<uint32_t> oc;
+    DevBuf<float> ov;
+    DevBuf<int32_t> on;
+    if (comp_sizes) {
+        SPHB_CUDA(dcs.alloc(n, s));
+        SPHB_CUDA(cudaMemcpyAsync(dcs.p, comp_sizes, n * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    }
+    const size_t nk = static_cast<size_t>(nr) * static_cast<size_t>(k);
+    SPHB_CUDA(oc.alloc(nk, s));
+    SPHB_CUDA(ov.alloc(nk, s));
+    SPHB_CUDA(on.alloc(nr, s));
+    if (int rc = create_similarities_rows_dev(n, in.rowptr.p, in.col.p, in.val.p, in.nnz, k, prune_val, variant, comp_sizes ? dcs.p : nullptr, r0, r1,
+                                              oc.p, ov.p, on.p, s))
+        return rc;
+    SPHB_CUDA(cudaMemcpyAsync(out_cols, oc.p, nk * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(out_vals, ov.p, nk * sizeof(float), cudaMemcpyDeviceToHost, s));
+    SPHB_CUDA(cudaMemcpyAsync(row_nnz, on.p, nr * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
     SPHB_CUDA(cudaStreamSynchronize(s));
     return SPHB_OK;
 }

@@ -22,6 +22,9 @@ int random_walks_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_
                           int64_t q1, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s);
 int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
                             int variant, const int64_t* d_comp_sizes, uint32_t* d_out_cols, float* d_out_vals, int32_t* d_row_nnz, cudaStream_t s);
+int create_similarities_rows_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
+                                 int variant, const int64_t* d_comp_sizes, int64_t r0, int64_t r1, uint32_t* d_out_cols, float* d_out_vals,
+                                 int32_t* d_row_nnz, cudaStream_t s);
 int find_k_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int max_nnz, int k, int top, uint32_t* d_out_cols,
                float* d_out_vals, int32_t* d_row_nnz, cudaStream_t s);
 int prow_inplace_launch(int64_t n, const int64_t* d_rowptr, float* d_val, int max_nnz, float perplexity, int ignore, cudaStream_t stream);
@@ -92,38 +95,18 @@ struct StageTimer {
 
 }  // namespace
 
-// The fused level pipeline on a resident random-walk matrix.  pair_sims = 1: createSimilarities(walks, k, prune_val)
-// (randomWalkPairSims, the default), 0: per-row top-k conversion (convertEigenSparseVecToHDILibSparseVec).
-// scheme: 1 t-SNE (in-place Gaussian rows with `perplexity`, ignore = -1; symmetrizeTSNE), 0 none.
-int level_prob_dist_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
-                        int variant, const int64_t* d_comp_sizes, int pair_sims, float perplexity, int scheme, int symmetrize,
-                        int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s) {
-    *out_nnz = 0;
-    if (n <= 0) return 0;
-    if (k <= 0) return fail(SPHB_ERR_INVALID, "level_prob_dist: k must be positive");
+// The pipeline behind D1 / D3: fixed-stride rows (cols padded, row_nnz) -> CSR -> B3 -> B7 -> B6.  Split off so that the rows can
+// come from anywhere — one call on this device, or slabs of output rows computed on several devices and gathered.
+static int level_from_rows(int64_t n, int64_t k, const uint32_t* d_fcols, const float* d_fvals, const int32_t* d_fnz, float perplexity, int scheme,
+                           int symmetrize, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz,
+                           StageTimer& tm, cudaStream_t s) {
     const int sms = ctx().num_sms;
-    StageTimer tm(s);
-    tm.mark(0);
-    // ---- D1 / D3: fixed-stride rows of at most k entries
-    DevBuf<uint32_t> fcols;
-    DevBuf<float> fvals;
-    DevBuf<int32_t> fnz;
-    SPHB_CUDA(fcols.alloc(static_cast<size_t>(n) * k, s));
-    SPHB_CUDA(fvals.alloc(static_cast<size_t>(n) * k, s));
-    SPHB_CUDA(fnz.alloc(n, s));
-    if (pair_sims) {
-        if (int rc = create_similarities_dev(n, d_rowptr, d_col, d_val, nnz, k, prune_val, variant, d_comp_sizes, fcols.p, fvals.p, fnz.p, s)) return rc;
-    } else {
-        int mx = 0;
-        if (int rc = max_row_len(n, d_rowptr, &mx, s)) return rc;
-        if (int rc = find_k_dev(n, d_rowptr, d_col, d_val, mx, static_cast<int>(k), 1, fcols.p, fvals.p, fnz.p, s)) return rc;
-    }
     tm.mark(1);
     // ---- to CSR
     DevBuf<int64_t> cnt64, rp;
     SPHB_CUDA(cnt64.alloc(n + 1, s));
     SPHB_CUDA(rp.alloc(n + 1, s));
-    la_widen<<<la_grid(n + 1, 256, sms), 256, 0, s>>>(fnz.p, n, cnt64.p);
+    la_widen<<<la_grid(n + 1, 256, sms), 256, 0, s>>>(d_fnz, n, cnt64.p);
     count_launch();
     if (int rc = exclusive_sum<int64_t>(cnt64.p, rp.p, n + 1, s)) return rc;
     int64_t m1 = 0;
@@ -133,7 +116,7 @@ int level_prob_dist_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_co
     DevBuf<float> v1;
     SPHB_CUDA(c1.alloc(std::max<int64_t>(m1, 1), s));
     SPHB_CUDA(v1.alloc(std::max<int64_t>(m1, 1), s));
-    la_fixed_to_csr<<<la_grid(n * 32, 256, sms), 256, 0, s>>>(n, static_cast<int>(k), fcols.p, fvals.p, rp.p, c1.p, v1.p);
+    la_fixed_to_csr<<<la_grid(n * 32, 256, sms), 256, 0, s>>>(n, static_cast<int>(k), d_fcols, d_fvals, rp.p, c1.p, v1.p);
     count_launch();
     tm.mark(2);
     // ---- B3: in-place Gaussian rows (rows hold at most k <= 1024 entries)
@@ -165,6 +148,44 @@ int level_prob_dist_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_co
     tm.collect(5);
     *out_nnz = m2;
     return 0;
+}
+
+// The fused level pipeline on a resident random-walk matrix.  pair_sims = 1: createSimilarities(walks, k, prune_val)
+// (randomWalkPairSims, the default), 0: per-row top-k conversion (convertEigenSparseVecToHDILibSparseVec).
+// scheme: 1 t-SNE (in-place Gaussian rows with `perplexity`, ignore = -1; symmetrizeTSNE), 0 none.
+int level_prob_dist_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
+                        int variant, const int64_t* d_comp_sizes, int pair_sims, float perplexity, int scheme, int symmetrize,
+                        int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s) {
+    *out_nnz = 0;
+    if (n <= 0) return 0;
+    if (k <= 0) return fail(SPHB_ERR_INVALID, "level_prob_dist: k must be positive");
+    StageTimer tm(s);
+    tm.mark(0);
+    // ---- D1 / D3: fixed-stride rows of at most k entries
+    DevBuf<uint32_t> fcols;
+    DevBuf<float> fvals;
+    DevBuf<int32_t> fnz;
+    SPHB_CUDA(fcols.alloc(static_cast<size_t>(n) * k, s));
+    SPHB_CUDA(fvals.alloc(static_cast<size_t>(n) * k, s));
+    SPHB_CUDA(fnz.alloc(n, s));
+    if (pair_sims) {
+        if (int rc = create_similarities_dev(n, d_rowptr, d_col, d_val, nnz, k, prune_val, variant, d_comp_sizes, fcols.p, fvals.p, fnz.p, s)) return rc;
+    } else {
+        int mx = 0;
+        if (int rc = max_row_len(n, d_rowptr, &mx, s)) return rc;
+        if (int rc = find_k_dev(n, d_rowptr, d_col, d_val, mx, static_cast<int>(k), 1, fcols.p, fvals.p, fnz.p, s)) return rc;
+    }
+    return level_from_rows(n, k, fcols.p, fvals.p, fnz.p, perplexity, scheme, symmetrize, d_out_rowptr, d_out_col, d_out_val, cap, out_nnz, tm, s);
+}
+
+int level_from_sims_dev(int64_t n, int64_t k, const uint32_t* d_cols, const float* d_vals, const int32_t* d_row_nnz, float perplexity, int scheme,
+                        int symmetrize, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap, int64_t* out_nnz, cudaStream_t s) {
+    *out_nnz = 0;
+    if (n <= 0) return 0;
+    if (k <= 0) return fail(SPHB_ERR_INVALID, "level_from_sims: k must be positive");
+    StageTimer tm(s);
+    tm.mark(0);
+    return level_from_rows(n, k, d_cols, d_vals, d_row_nnz, perplexity, scheme, symmetrize, d_out_rowptr, d_out_col, d_out_val, cap, out_nnz, tm, s);
 }
 
 }  // namespace sphb
@@ -200,6 +221,25 @@ SPHB_API int sphb_create_similarities_dev(int64_t n, const int64_t* d_rowptr, co
     if (n == 0) return SPHB_OK;
     return create_similarities_dev(n, d_rowptr, d_col, d_val, nnz, k, prune_val, variant, d_comp_sizes, d_out_cols, d_out_vals, d_row_nnz,
                                    static_cast<cudaStream_t>(stream));
+}
+
+SPHB_API int sphb_create_similarities_slab_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k,
+                                               float prune_val, int variant, const int64_t* d_comp_sizes, int64_t r0, int64_t r1, uint32_t* d_out_cols,
+                                               float* d_out_vals, int32_t* d_row_nnz, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (!d_rowptr || !d_out_cols || !d_out_vals || !d_row_nnz || n < 0 || k <= 0) return fail(SPHB_ERR_INVALID, "create_similarities_slab_dev: bad arguments");
+    return create_similarities_rows_dev(n, d_rowptr, d_col, d_val, nnz, k, prune_val, variant, d_comp_sizes, r0, r1, d_out_cols, d_out_vals, d_row_nnz,
+                                        static_cast<cudaStream_t>(stream));
+}
+
+SPHB_API int sphb_level_from_sims_dev(int64_t n, int64_t k, const uint32_t* d_cols, const float* d_vals, const int32_t* d_row_nnz, float perplexity,
+                                      int scheme, int symmetrize, int64_t* d_out_rowptr, uint32_t* d_out_col, float* d_out_val, int64_t cap,
+                                      int64_t* out_nnz, void* stream) {
+    if (int rc = ensure_init()) return rc;
+    if (n < 0 || !d_cols || !d_vals || !d_row_nnz || !d_out_rowptr || !d_out_col || !d_out_val || !out_nnz)
+        return fail(SPHB_ERR_INVALID, "level_from_sims_dev: bad arguments");
+    return level_from_sims_dev(n, k, d_cols, d_vals, d_row_nnz, perplexity, scheme, symmetrize, d_out_rowptr, d_out_col, d_out_val, cap, out_nnz,
+                               static_cast<cudaStream_t>(stream));
 }
 
 SPHB_API int sphb_prow_gaussian_inplace_dev(int64_t n, const int64_t* d_rowptr, float* d_val, int max_row_nnz, float perplexity, int ignore,

@@ -91,6 +91,7 @@ __device__ __forceinline__ void block_bitonic_sort(uint64_t* sm, int cap) {
 
 struct SimsParams {
     int64_t n;
+    int64_t r0, r1;           // rows of the result this launch computes (a slab of output rows: SURVEY 8(e), D1 sharded by output row)
     const int64_t* srowptr;   // S rows
     const uint32_t* scol;
     const float* sval;
@@ -136,7 +137,7 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
     const int k = P.k, cap = P.cap;
     if constexpr (BITMAP)
         for (int t = threadIdx.x; t < nwords; t += blockDim.x) bm[t] = 0u;
-    for (int64_t i = blockIdx.x; i < P.n; i += gridDim.x) {
+    for (int64_t i = P.r0 + blockIdx.x; i < P.r1; i += gridDim.x) {
         if (threadIdx.x == 0) { s_touched = 0; s_valid = 0; s_nsel = 0; s_sum = 0.0; }
         __syncthreads();
         const int64_t rb = P.srowptr[i], re = P.srowptr[i + 1];
@@ -274,10 +275,10 @@ __global__ void __launch_bounds__(SIMS_WARPS * 32) sims_row_kernel(const SimsPar
                 ov = __uint_as_float(static_cast<uint32_t>(key));
                 if (divide) ov /= static_cast<float>(sum);
             }
-            P.out_cols[i * k + t] = oc;
-            P.out_vals[i * k + t] = ov;
+            P.out_cols[(i - P.r0) * k + t] = oc;
+            P.out_vals[(i - P.r0) * k + t] = ov;
         }
-        if (threadIdx.x == 0) P.row_nnz[i] = nsel;
+        if (threadIdx.x == 0) P.row_nnz[i - P.r0] = nsel;
         __syncthreads();
     }
 }
@@ -341,7 +342,7 @@ __global__ void __launch_bounds__(SC_WARPS * 32) sims_class_kernel(const SimsPar
     const int k = P.k, cap = P.cap;
     for (int t = threadIdx.x; t < SC_WARPS * CH; t += THREADS) sacc[t] = 0.f;
     if (threadIdx.x == 0) s_nreg = 0;
-    for (int64_t i = blockIdx.x; i < P.n; i += gridDim.x) {
+    for (int64_t i = P.r0 + blockIdx.x; i < P.r1; i += gridDim.x) {
         if (threadIdx.x == 0) { s_valid = 0; s_nsel = 0; s_sum = 0.0; }
         __syncthreads();
         const int64_t rb = P.srowptr[i], re = P.srowptr[i + 1];
@@ -616,16 +617,21 @@ __global__ void __launch_bounds__(SC_WARPS * 32) sims_class_kernel(const SimsPar
                 ov = __uint_as_float(static_cast<uint32_t>(key));
                 if (divide) ov /= static_cast<float>(sum);
             }
-            P.out_cols[i * k + t] = oc;
-            P.out_vals[i * k + t] = ov;
+            P.out_cols[(i - P.r0) * k + t] = oc;
+            P.out_vals[(i - P.r0) * k + t] = ov;
         }
-        if (threadIdx.x == 0) P.row_nnz[i] = nsel;
+        if (threadIdx.x == 0) P.row_nnz[i - P.r0] = nsel;
         __syncthreads();
     }
 }
 
-int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
-                            int variant, const int64_t* d_comp_sizes, uint32_t* d_out_cols, float* d_out_vals, int32_t* d_row_nnz, cudaStream_t s) {
+// Rows [r0, r1) of the result (every output row needs the whole matrix and nothing of the other output rows, so slabs of rows
+// computed anywhere concatenate to the one-call result: SURVEY 8(e), D1 sharded by output row); outputs hold (r1 - r0) rows.
+int create_similarities_rows_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
+                                 int variant, const int64_t* d_comp_sizes, int64_t r0, int64_t r1, uint32_t* d_out_cols, float* d_out_vals,
+                                 int32_t* d_row_nnz, cudaStream_t s) {
+    if (r0 < 0 || r1 > n || r0 > r1) return fail(SPHB_ERR_INVALID, "create_similarities: row range outside [0, n]");
+    if (r0 == r1) return 0;
     if (n >= (1ll << 32)) return fail(SPHB_ERR_UNSUPPORTED, "create_similarities: n must be < 2^32");
     if (k > 992) return fail(SPHB_ERR_UNSUPPORTED, "create_similarities: k > 992 unsupported");
     const int sms = ctx().num_sms;
@@ -661,7 +667,7 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
     int cap = 64;
     while (cap < k + 32) cap <<= 1;
     SimsParams P{};
-    P.n = n; P.srowptr = srowptr.p; P.scol = scol.p; P.sval = sval.p; P.colptr = colptr.p; P.tkeys = tk1.p; P.tval = tval.p;
+    P.n = n; P.r0 = r0; P.r1 = r1; P.srowptr = srowptr.p; P.scol = scol.p; P.sval = sval.p; P.colptr = colptr.p; P.tkeys = tk1.p; P.tval = tval.p;
     P.prune_val = prune_val; P.hdi = hdi ? 1 : 0; P.k = static_cast<int>(k); P.cap = cap;
     P.out_cols = d_out_cols; P.out_vals = d_out_vals; P.row_nnz = d_row_nnz;
     DevBuf<float> acc;
@@ -689,7 +695,7 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
         sims_zip_records<<<g, 256, 0, s>>>(ck1.p, cval.p, snnz, trec.p);
         count_launch(2);
         SPHB_CUDA(cudaFuncSetAttribute(sims_class_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(class_smem)));
-        const int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * (class_smem <= 100 * 1024 ? 2 : 1));
+        const int64_t grid = std::min<int64_t>(r1 - r0, static_cast<int64_t>(sms) * (class_smem <= 100 * 1024 ? 2 : 1));
         sims_class_kernel<<<static_cast<unsigned>(grid), SC_WARPS * 32, class_smem, s>>>(P, cptr.p, trec.p, CH);
         count_launch();
         SPHB_CUDA(cudaGetLastError());
@@ -706,12 +712,12 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
         const size_t slab_smem = list_bytes + (bitmap ? bitmap_bytes : 0);
         if (bitmap) SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(slab_smem)));
         else SPHB_CUDA(cudaFuncSetAttribute(sims_row_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(slab_smem)));
-        int64_t grid = std::min<int64_t>(n, static_cast<int64_t>(sms) * 2);
+        int64_t grid = std::min<int64_t>(r1 - r0, static_cast<int64_t>(sms) * 2);
         // bound the accumulator slabs to 8 GiB.  (Keeping the slabs L2-resident by running fewer CTAs does not help: 768 x 768 x 128
         // level 1, 296 / 136 / 68 CTAs: 9.2 / 10.4 / 11.6 s — the returning atomics, not L2 misses, were the bound.)
         while (grid > 1 && static_cast<double>(grid) * n * 8.0 > 8.0 * (1ull << 30)) grid /= 2;
 #ifdef SPHB_KNN_TUNING
-        if (const char* e = getenv("SPHB_SIMS_SLAB_CTAS")) grid = std::max<int64_t>(1, std::min<int64_t>(n, atoi(e)));
+        if (const char* e = getenv("SPHB_SIMS_SLAB_CTAS")) grid = std::max<int64_t>(1, std::min<int64_t>(r1 - r0, atoi(e)));
 #endif
         SPHB_CUDA(acc.alloc(static_cast<size_t>(grid) * n, s));
         SPHB_CUDA(touched.alloc(static_cast<size_t>(grid) * n, s));
@@ -723,6 +729,11 @@ int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* 
     count_launch();
     SPHB_CUDA(cudaGetLastError());
     return 0;
+}
+
+int create_similarities_dev(int64_t n, const int64_t* d_rowptr, const uint32_t* d_col, const float* d_val, int64_t nnz, int64_t k, float prune_val,
+                            int variant, const int64_t* d_comp_sizes, uint32_t* d_out_cols, float* d_out_vals, int32_t* d_row_nnz, cudaStream_t s) {
+    return create_similarities_rows_dev(n, d_rowptr, d_col, d_val, nnz, k, prune_val, variant, d_comp_sizes, 0, n, d_out_cols, d_out_vals, d_row_nnz, s);
 }
 
 }  // namespace sphb

@@ -576,7 +576,9 @@ class LevelSimilarities:
     def getSimilaritiesGraph(self, level: int):
         return self._distance_graphs.get(level)
 
-    def compute(self, lss: LevelSimilaritiesSettings | None = None) -> None:
+    def compute(self, lss: LevelSimilaritiesSettings | None = None, rank: int = 0, world: int = 1, group=None) -> None:
+        """LevelSimilarities::compute (sph/LevelSimilarities.cpp:118-182).  world > 1 (one process per GPU): createSimilarities is
+        sharded by output row over the ranks (createSimilarities above); every rank ends with the whole level."""
         from . import capi
 
         lss = lss or LevelSimilaritiesSettings()
@@ -619,7 +621,7 @@ class LevelSimilarities:
                 rowptr, c, v = scatter_flat_rows(g.knnIndices, temp)
             else:
                 if lss.randomWalkPairSims:
-                    cols, vals, nnz = capi.create_similarities(rw.rowptr, rw.col, rw.val, k_l, 1e-4)
+                    cols, vals, nnz = createSimilarities(rw, k_l, 1e-4, rank=rank, world=world, group=group)
                 else:  # convertEigenSparseVecToHDILibSparseVec: the k_l largest transition values per row (:481-486)
                     cols, vals, nnz = capi.find_k(rw.rowptr, rw.col, rw.val, k_l, top=True)
                 rowptr = np.concatenate([[0], np.cumsum(nnz, dtype=np.int64)])
@@ -710,6 +712,24 @@ def doRandomWalks(similarities: SparseRows, rws: RandomWalkSettings, rank: int =
     rp, c, v = capi.random_walks(similarities.rowptr, similarities.col, similarities.val, rws.numRandomWalks, rws.singleWalkLength,
                                  int(rws.importanceWeighting), rws.pruneValue, rws.pruneSteps, rws.randomSeed, rws.removeDiagonal, rws.normalize)
     return SparseRows(rp, c, v)
+
+
+def createSimilarities(matrix: SparseRows, k: int, prune_val: float = 1e-4, variant: int = 0, comp_sizes=None, rank: int = 0, world: int = 1, group=None,
+                       sims_fn=None):
+    """utils::createSimilarities (sph/utils/SparseMatrixAlgorithms.cpp:963-1378): (cols [n, k] padded 0xFFFFFFFF, vals [n, k], nnz [n]).
+    With world > 1 the OUTPUT ROWS are sharded over the ranks (the random-walk matrix is replicated, every rank computes
+    the rows of its slab against the whole matrix, one gather of the fixed-stride result)."""
+    from . import capi
+
+    if world > 1:
+        r0, r1 = shard_rows(matrix.n, world)[rank]
+        fn = sims_fn or (lambda m, r0, r1: capi.create_similarities_slab(m.rowptr, m.col, m.val, k, r0, r1, prune_val, variant, comp_sizes))
+        cols, vals, nnz = fn(matrix, r0, r1)
+        cols = gather_rows(np.ascontiguousarray(cols, np.uint32).view(np.int32), matrix.n, group).view(np.uint32)
+        vals = gather_rows(np.ascontiguousarray(vals, np.float32), matrix.n, group)
+        nnz = gather_rows(np.ascontiguousarray(nnz, np.int32), matrix.n, group)
+        return cols, vals, nnz
+    return capi.create_similarities(matrix.rowptr, matrix.col, matrix.val, k, prune_val, variant, comp_sizes)
 
 
 def mergeNodesRandomWalks(walks: SparseRows, num_merged: int, parents, norm: bool = True, weight_by_size: bool = True) -> SparseRows:

@@ -106,3 +106,67 @@ def knn_graph_prow_sharded(x: np.ndarray, k: int, rank: int, world: int, perplex
     job.compute(perplexity)
     torch.cuda.synchronize()
     return job.ids.cpu().numpy(), job.dist.cpu().numpy(), job.cols.cpu().numpy().view(np.uint32), job.vals.cpu().numpy()
+
+
+class ShardedLevel:
+    """One level of LevelSimilarities with createSimilarities sharded by OUTPUT ROW: the level's random-walk matrix
+    is present on every rank (replicate_csr broadcasts it over NCCL), rank r computes rows slab_bounds(n, r, world) of
+    -ln(sqrt(A) sqrt(A)^T) with their bottom-k (sphb_create_similarities_slab_dev — 99 % of a level's time), ONE all-gather of the
+    fixed-stride slabs (cols, vals, row_nnz: n * k * 8 bytes), then the cheap tail (CSR -> Gaussian rows -> zero removal ->
+    symmetrise, sphb_level_from_sims_dev) on every rank, so every rank ends with the level's whole P matrix in HBM.  An output row
+    needs the whole matrix and nothing of the other output rows: the gathered slabs are bit for bit the one-call result."""
+
+    def __init__(self, rank: int, world: int, group=None):
+        self.rank, self.world, self.group = rank, world, group
+
+    def replicate_csr(self, rowptr, col, val, src: int = 0):
+        """CUDA tensors on rank `src` (anything, e.g. None, elsewhere) -> the same CSR on every rank."""
+        import torch
+        import torch.distributed as dist
+
+        if self.world == 1:
+            return rowptr, col, val
+        dev = torch.device("cuda", torch.cuda.current_device())
+        meta = torch.zeros(2, dtype=torch.int64, device=dev)
+        if self.rank == src:
+            meta[0], meta[1] = rowptr.numel(), col.numel()
+        dist.broadcast(meta, src, group=self.group)
+        n1, nnz = int(meta[0]), int(meta[1])
+        if self.rank != src:
+            rowptr = torch.empty(n1, dtype=torch.int64, device=dev)
+            col = torch.empty(nnz, dtype=torch.int32, device=dev)
+            val = torch.empty(nnz, dtype=torch.float32, device=dev)
+        for t in (rowptr, col, val):
+            dist.broadcast(t, src, group=self.group)
+        return rowptr, col, val
+
+    def __call__(self, rowptr, col, val, k: int, perplexity: float, prune_val: float = 1e-4, variant: int = 0, comp_sizes=None, symmetrize: bool = True):
+        """rowptr int64 [n + 1], col int32 (uint32 bits) [nnz], val float32 [nnz]: CUDA tensors, the same on every rank.
+        Returns (out_rowptr, out_col, out_val) CUDA tensors of the level's P matrix."""
+        import torch
+        import torch.distributed as dist
+
+        n = rowptr.numel() - 1
+        nnz = col.numel()
+        dev = rowptr.device
+        s = torch.cuda.current_stream().cuda_stream
+        r0, r1, chunk = slab_bounds(n, self.rank, self.world)
+        rows = self.world * chunk
+        cols_all = torch.full((rows, k), -1, dtype=torch.int32, device=dev)  # 0xFFFFFFFF padding
+        vals_all = torch.zeros((rows, k), dtype=torch.float32, device=dev)
+        nnz_all = torch.zeros(rows, dtype=torch.int32, device=dev)
+        lo = self.rank * chunk
+        if r1 > r0:
+            capi.create_similarities_slab_dev(n, rowptr.data_ptr(), col.data_ptr(), val.data_ptr(), nnz, k, prune_val, variant,
+                                              comp_sizes.data_ptr() if comp_sizes is not None else None, r0, r1, cols_all[lo:].data_ptr(),
+                                              vals_all[lo:].data_ptr(), nnz_all[lo:].data_ptr(), s)
+        if self.world > 1:
+            for buf in (cols_all, vals_all, nnz_all):
+                dist.all_gather_into_tensor(buf, buf[lo:lo + chunk].clone(), group=self.group)  # clone: input must not alias the output
+        cap = max(2 * n * k, 1)
+        out_rowptr = torch.empty(n + 1, dtype=torch.int64, device=dev)
+        out_col = torch.empty(cap, dtype=torch.int32, device=dev)
+        out_val = torch.empty(cap, dtype=torch.float32, device=dev)
+        m = capi.level_from_sims_dev(n, k, cols_all.data_ptr(), vals_all.data_ptr(), nnz_all.data_ptr(), perplexity, 1, symmetrize, out_rowptr.data_ptr(),
+                                     out_col.data_ptr(), out_val.data_ptr(), cap, s)
+        return out_rowptr, out_col[:m], out_val[:m]

@@ -168,6 +168,37 @@ print("rank", rank, "ok")
 '''
 
 
+WORKER_SIMS = r'''
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+import torch.distributed as dist
+import oracle_lib
+from sph_b200 import host
+from test_gpu_level import walk_like_rows
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+orc = oracle_lib.load()
+rp, c, v = walk_like_rows(211, seed=4, lo=3, hi=30, window=40)
+m = host.SparseRows(rp, c, v)
+k = 9
+calls = []
+def sims(mat, r0, r1):                 # stand-in for the CUDA slab call: the checker on the same slab contract
+    calls.append((r0, r1))
+    return orc.create_similarities_rows(mat.rowptr, mat.col, mat.val, k, r0, r1, 1e-4, 1)
+cols, vals, nnz = host.createSimilarities(m, k, 1e-4, 1, rank=rank, world=world, sims_fn=sims)
+assert calls == [host.shard_rows(211, world)[rank]]
+fc, fv, fn = orc.create_similarities(rp, c, v, k, 1e-4, 1)
+np.testing.assert_array_equal(nnz, fn)
+np.testing.assert_array_equal(cols, fc)
+np.testing.assert_array_equal(vals, fv)
+assert cols.dtype == np.uint32 and cols.shape == (211, k)
+dist.barrier()
+dist.destroy_process_group()
+print("rank", rank, "ok")
+'''
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -194,6 +225,20 @@ def test_sharded_random_walks_world2_gloo(tmp_path):
 
     script = tmp_path / "worker_walks.py"
     script.write_text(WORKER_WALKS)
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1", "--master-port",
+           str(_free_port()), str(script), str(ROOT)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert r.stdout.count("ok") == 2
+
+
+def test_sharded_create_similarities_world2_gloo(tmp_path):
+    """SURVEY 8(e), D1 sharded by output row: every rank computes its slab of rows, one gather, every rank ends with the whole result."""
+    import subprocess
+
+    script = tmp_path / "worker_sims.py"
+    script.write_text(WORKER_SIMS)
     env = dict(os.environ, OMP_NUM_THREADS="2")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1", "--master-port",
            str(_free_port()), str(script), str(ROOT)]
