@@ -1,13 +1,14 @@
 """SURVEY 8(e), createSimilarities sharded by OUTPUT ROW: sphb_create_similarities_slab[_dev] (rows [r0, r1) of the result against
 the whole random-walk matrix) and sphb_level_from_sims_dev (the level pipeline behind the gathered slabs).  An output row needs
-the whole matrix and nothing of the other output rows, so the bar is: slabs concatenated == the one-call result, bit for bit,
-for both accumulator flavours of the kernel; and slabs -> level tail == sphb_level_prob_dist."""
+the whole matrix and nothing of the other output rows, so the bar is: slabs concatenated == the one-call result — bit for bit
+for the shared-memory class flavour of the kernel (deterministic sums), to float-atomic order for the L2-slab flavour — and
+slabs -> level tail == sphb_level_prob_dist."""
 import os
 
 import numpy as np
 import pytest
 
-from test_gpu_level import walk_like_rows
+from test_gpu_level import _sims_equal_up_to_ties, walk_like_rows
 
 pytestmark = pytest.mark.gpu
 EMU = os.environ.get("SPHB_EMULATE") == "1"
@@ -52,13 +53,14 @@ class Dev:
         return b.view(dtype) if dtype is not None else b
 
 
-SLABS = [(0, 0), (0, 1), (1, 137), (137, 138), (138, 700), (700, 700), (700, 1199), (1199, 1200)]
+N_ROWS = 240 if EMU else 1200  # the emulation switches fibers at every warp collective: keep its matrices small
+SLABS = [(0, 0), (0, 1), (1, 37), (37, 38), (38, 140), (140, 140), (140, N_ROWS - 1), (N_ROWS - 1, N_ROWS)]
 
 
 @pytest.mark.parametrize("variant,k,force_slab", [(1, 31, False), (2, 17, False), (1, 31, True), (0, 91, False)])
 def test_row_slabs_concatenate_to_the_one_call_result(capi, variant, k, force_slab):
-    rp, c, v = walk_like_rows(1200, seed=7 + k)
-    sizes = np.random.default_rng(k).integers(1, 40, 1200) if variant == 1 else None
+    rp, c, v = walk_like_rows(N_ROWS, seed=7 + k, hi=120 if not EMU else 40)
+    sizes = np.random.default_rng(k).integers(1, 40, N_ROWS) if variant == 1 else None
     capi.force_sims_slab(force_slab)
     try:
         full = capi.create_similarities(rp, c, v, k, 1e-4, variant, sizes)
@@ -67,9 +69,15 @@ def test_row_slabs_concatenate_to_the_one_call_result(capi, variant, k, force_sl
         capi.force_sims_slab(False)
     for (r0, r1), p in zip(SLABS, parts):
         assert p[0].shape == (r1 - r0, k) and len(p[2]) == r1 - r0
-    np.testing.assert_array_equal(np.concatenate([p[2] for p in parts]), full[2])
-    np.testing.assert_array_equal(np.concatenate([p[0] for p in parts]), full[0])
-    np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), full[1])
+    cat = [np.concatenate([p[j] for p in parts]) for j in range(3)]
+    if force_slab:
+        # the L2-slab flavour adds its products with float atomics, whose order is not fixed: two calls on the same rows agree to
+        # the last bits only, and a k-th-slot tie may swap (the comparison of test_similarities_slab_and_dense_agree)
+        _sims_equal_up_to_ties(cat[0], cat[1], cat[2], *full)
+        return
+    np.testing.assert_array_equal(cat[2], full[2])  # shared-memory class flavour: every sum in ascending column order, deterministic
+    np.testing.assert_array_equal(cat[0], full[0])
+    np.testing.assert_array_equal(cat[1], full[1])
 
 
 def test_slab_argument_checks(capi):
@@ -88,8 +96,8 @@ def test_gathered_slabs_through_the_level_tail_equal_the_fused_level(capi, world
     from sph_b200.multigpu import slab_bounds
 
     dev = Dev()
-    n, k, perplexity = 1000, 23, 7.0
-    rp, c, v = walk_like_rows(n, seed=77)
+    n, k, perplexity = (1000 if not EMU else 200), 23, 7.0
+    rp, c, v = walk_like_rows(n, seed=77, hi=120 if not EMU else 40)
     nnz = len(c)
     drp, dc, dv = dev.put(rp), dev.put(c), dev.put(v)
     chunk = slab_bounds(n, 0, world)[2]
