@@ -316,6 +316,17 @@ def level1_p_matrix(capi, synth, orc, peaks, workload="C2", cpu=True):
     hp = capi.level_prob_dist(h_mrp, h_mc, h_mv, k1, 1e-4, 0, None, True, 0.0, 1, True)
     out["wall_ms_host_buffers"] = 1e3 * (time.perf_counter() - t0)
     out["host_equals_resident"] = bool(np.array_equal(hp[0], g_prp) and np.array_equal(hp[1], g_pc) and np.array_equal(hp[2], g_pv))
+    # SURVEY 8(e), D1 sharded by output row: the one-rank replay of multigpu.ShardedLevel (slab call + level tail) against the fused call
+    try:
+        from sph_b200.multigpu import ShardedLevel
+
+        job = ShardedLevel(0, 1)
+        sh_ms, (srp, scol, sval) = timed(lambda: job(mrp, mc[:mnnz], mv[:mnnz], k1, 0.0))
+        out["sharded_level_one_rank"] = {"ms": sh_ms, "equals_fused_level": bool(torch.equal(srp, prp) and scol.numel() == pnnz and
+                                                                                   torch.equal(scol, pc[:pnnz]) and torch.equal(sval, pv[:pnnz]))}
+        del srp, scol, sval
+    except Exception as e:  # never let a side measurement take the bench line down
+        out["sharded_level_one_rank"] = {"error": repr(e)[:300]}
     if cpu and orc is not None:
         t0 = time.perf_counter()
         sc, sv, snz = orc.create_similarities(h_mrp, h_mc, h_mv, k1, 1e-4, 0)
@@ -343,6 +354,65 @@ def level1_p_matrix(capi, synth, orc, peaks, workload="C2", cpu=True):
         out["parity"] = {"rows": int(n1), "rows_identical_pattern": int(same), "max_rel_on_identical_rows": worst, "p_nnz_oracle": int(orp[-1]),
                          "note": "a 1-ulp tie at the k-th slot of createSimilarities changes that row's pattern (tolerated by the reference's own test, tests/UtilsTests.cpp:984-1027)"}
     return out, passes
+
+
+def geodesic_block(capi, synth, orc, workload="C2", cpu_pairs=20000):
+    """SURVEY 8(f)-4 on the configuration that uses it (C2, GEO_CENTROID): the geodesic component distances of level 0 (every pixel
+    against its 4 spatial neighbours, ImageHierarchy::computeDistances) and of level 1 of a 2 x 2 block hierarchy, through the
+    host-buffer C ABI (the graph upload is inside the wall time), with a sample of the pairs recomputed by the oracle."""
+    h, w, d, M, seed = SHAPES[workload]
+    k = K_NEIGHBOURS
+    x = make_stack(synth, workload)
+    ids, dist = capi.knn_exact(x, k)
+    del x
+    dist = np.sqrt(dist)  # L2squared = false: true L2 edge weights
+
+    def grid_pairs(hh, ww):
+        p = np.arange(hh * ww)
+        r, c = np.divmod(p, ww)
+        pa, pb = [], []
+        for dr, dc in ((-1, 0), (0, 1), (1, 0), (0, -1)):  # pixelNeighborIDs, FOUR
+            ok = (r + dr >= 0) & (r + dr < hh) & (c + dc >= 0) & (c + dc < ww)
+            pa.append(p[ok])
+            pb.append((r[ok] + dr) * ww + c[ok] + dc)
+        return np.concatenate(pa).astype(np.int64), np.concatenate(pb).astype(np.int64)
+
+    out = {"workload": f"{workload} {h}x{w}x{d}, k = {k}, true L2 edge weights; host buffers"}
+    pa, pb = grid_pairs(h, w)
+    capi.geodesic_distances(ids[:64], dist[:64], [0], [1])  # context / workspace warm-up on a tiny graph
+    t0 = time.perf_counter()
+    g0 = capi.geodesic_distances(ids, dist, pa, pb)
+    sec = time.perf_counter() - t0
+    st = capi.geodesic_last_stats()
+    out["level0"] = {"pairs": int(len(pa)), "seconds": sec, "pairs_per_s": len(pa) / sec, "searches": st["searches"], "sources": st["sources"],
+                     "vertices_expanded": st["expanded"], "passes": st["passes"], "no_path": int((g0 < 0).sum())}
+    hb, wb = h // 2, w // 2
+    blk = (np.arange(h)[:, None] // 2 * wb + np.arange(w)[None, :] // 2)[: hb * 2, : wb * 2].reshape(-1)
+    pix = (np.arange(hb * 2)[:, None] * w + np.arange(wb * 2)[None, :]).reshape(-1)
+    comp_pix = pix[np.argsort(blk, kind="stable")].astype(np.int64)
+    comp_ptr = np.arange(hb * wb + 1, dtype=np.int64) * 4
+    qa, qb = grid_pairs(hb, wb)
+    t0 = time.perf_counter()
+    g1 = capi.geodesic_hausdorff(ids, dist, comp_ptr, comp_pix, qa, qb)
+    sec = time.perf_counter() - t0
+    st = capi.geodesic_last_stats()
+    out["level1_2x2_blocks"] = {"pairs": int(len(qa)), "components": int(hb * wb), "seconds": sec, "pairs_per_s": len(qa) / sec, "searches": st["searches"],
+                                "vertices_expanded": st["expanded"], "passes": st["passes"]}
+    if orc is not None and cpu_pairs > 0:
+        rng = np.random.default_rng(0)
+        s0 = rng.choice(len(pa), min(cpu_pairs, len(pa)), replace=False)
+        t0 = time.perf_counter()
+        r0 = orc.shortest_paths(None, ids, dist, pa[s0], pb[s0])
+        c0 = time.perf_counter() - t0
+        s1 = rng.choice(len(qa), min(cpu_pairs, len(qa)), replace=False)
+        t0 = time.perf_counter()
+        r1 = orc.geodesic_hausdorff(None, ids, dist, comp_ptr, comp_pix, qa[s1], qb[s1])
+        c1 = time.perf_counter() - t0
+        out["cpu_baseline"] = {"kind": "port", "cores": os.cpu_count(), "level0_pairs_per_s": len(s0) / c0, "level1_pairs_per_s": len(s1) / c1,
+                               "sample": f"{len(s0)} level-0 pairs and {len(s1)} level-1 pairs of the same calls (oracle/oracle_geodesic.cpp: Dijkstra per source, OpenMP)"}
+        out["parity"] = {"level0_pairs_checked": int(len(s0)), "level0_mismatches": int((r0 != g0[s0]).sum()), "level1_pairs_checked": int(len(s1)),
+                         "level1_mismatches": int((r1 != g1[s1]).sum()), "bar": "bit-exact"}
+    return out
 
 
 def main():
@@ -589,6 +659,13 @@ def main():
                                          cpu=not args.no_cpu_baseline and orc is not None)
         graph_passes += passes
 
+    geodesic = None
+    if world == 1 and not args.no_level1:
+        try:
+            geodesic = geodesic_block(capi, synth, orc if not args.no_cpu_baseline else None, args.level1_workload)
+        except Exception as e:  # a side measurement must not take the bench line down
+            geodesic = {"error": repr(e)[:300]}
+
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         orc = orc or load_oracle()
@@ -605,7 +682,7 @@ def main():
                     "steps": e2e_steps, "api": e2e_api, "host_buffers": "pinned caller buffers (the reference's are pageable std::vectors)",
                     "result_checksum": checksum},
             "gpu_launches": launches, "roofline": roofline, "graph_pass_roofline": graph_passes, "parity": parity, "level1_p_matrix": level1,
-            "cpu_baseline": cpu_baseline, "knn_stats": stats}
+            "geodesic_distances": geodesic, "cpu_baseline": cpu_baseline, "knn_stats": stats}
     print(json.dumps(line))
 
 
