@@ -398,6 +398,18 @@ def geodesic_block(capi, synth, orc, workload="C2", cpu_pairs=20000):
     st = capi.geodesic_last_stats()
     out["level1_2x2_blocks"] = {"pairs": int(len(qa)), "components": int(hb * wb), "seconds": sec, "pairs_per_s": len(qa) / sec, "searches": st["searches"],
                                 "vertices_expanded": st["expanded"], "passes": st["passes"]}
+    # the same two calls on a graph kept on the device (sphb_geodesic_graph_create: one upload for all the levels of a hierarchy)
+    t0 = time.perf_counter()
+    with capi.GeodesicGraph(ids, dist) as gg:
+        up = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        h0 = gg.distances(pa, pb)
+        r0s = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        h1 = gg.hausdorff(comp_ptr, comp_pix, qa, qb)
+        r1s = time.perf_counter() - t0
+    out["resident_graph"] = {"upload_seconds": up, "level0_seconds": r0s, "level0_pairs_per_s": len(pa) / r0s, "level1_seconds": r1s,
+                             "level1_pairs_per_s": len(qa) / r1s, "equals_one_shot_calls": bool(np.array_equal(h0, g0) and np.array_equal(h1, g1))}
     if orc is not None and cpu_pairs > 0:
         rng = np.random.default_rng(0)
         s0 = rng.choice(len(pa), min(cpu_pairs, len(pa)), replace=False)

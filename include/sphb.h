@@ -373,6 +373,16 @@ SPHB_API int sphb_geodesic_hausdorff(int64_t n, const int64_t* rowptr, int k, co
                                      int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, const int64_t* pa, const int64_t* pb,
                                      int64_t npairs, float* out);
 SPHB_API int sphb_geodesic_last_stats(int64_t* out4);
+/* The same two calls on a graph that stays on the device between calls: ImageHierarchy::computeDistances asks for the distances of
+ * every level on the same data graph (sph/ImageHierarchy.cpp:192-249), and uploading it is about half of a level-0 call.  What
+ * _hierarchy.bgraph is to the reference (built once, sph/ImageHierarchy.cpp:427-431).  A handle belongs to the thread (device
+ * context) that created it; destroy it there. */
+SPHB_API int sphb_geodesic_graph_create(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const int64_t* labels,
+                                        void** handle);
+SPHB_API int sphb_geodesic_graph_destroy(void* handle);
+SPHB_API int sphb_geodesic_distances_g(void* handle, const int64_t* start, const int64_t* end, int64_t npairs, float* out);
+SPHB_API int sphb_geodesic_hausdorff_g(void* handle, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, const int64_t* pa,
+                                       const int64_t* pb, int64_t npairs, float* out);
 /* SURVEY 8(f)-4, cache blobs — the reference's stage-cache files (sph/utils/FileIO.hpp:165-291, 523-640; FileIO.cpp:586-618,
  * 620-799, 895-937, 1274-1460), written and read on the HOST so that results of this back-end can be dropped into the
  * reference's cache directory and loaded by it, and the reverse.  Blocks are LZ4 block format (LZ4_compress_default /

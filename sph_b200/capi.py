@@ -114,6 +114,10 @@ SIGNATURES = {
     "sphb_geodesic_distances": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_geodesic_hausdorff": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_geodesic_last_stats": (C.c_int, [i64p]),
+    "sphb_geodesic_graph_create": (C.c_int, [C.c_int64, i64p, C.c_int, i64p, f32p, i64p, C.POINTER(C.c_void_p)]),
+    "sphb_geodesic_graph_destroy": (C.c_int, [C.c_void_p]),
+    "sphb_geodesic_distances_g": (C.c_int, [C.c_void_p, i64p, i64p, C.c_int64, f32p]),
+    "sphb_geodesic_hausdorff_g": (C.c_int, [C.c_void_p, C.c_int64, i64p, i64p, i64p, i64p, C.c_int64, f32p]),
     "sphb_lz4_compress_bound": (C.c_int64, [C.c_int64]),
     "sphb_lz4_compress": (C.c_int64, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
     "sphb_lz4_decompress": (C.c_int64, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
@@ -709,6 +713,53 @@ def geodesic_hausdorff(ids, dist, comp_ptr, comp_pix, pa, pb, rowptr=None, label
     _check(load().sphb_geodesic_hausdorff(n, None if rp is None else _p(rp, i64p), k, _p(ids, i64p), _p(dist, f32p), None if lab is None else _p(lab, i64p),
                                           len(comp_ptr) - 1, _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa), _p(out, f32p)))
     return out
+
+
+class GeodesicGraph:
+    """The data-level kNN graph resident on the device (sphb_geodesic_graph_create): upload once, ask for the distances of every
+    level.  Use as a context manager or call close(); belongs to the thread that created it."""
+
+    def __init__(self, ids, dist, rowptr=None, labels=None):
+        n, rp, k, ids, dist = _geo_graph(ids, dist, rowptr)
+        lab = None if labels is None else np.ascontiguousarray(labels, np.int64)
+        self._h = C.c_void_p()
+        _check(load().sphb_geodesic_graph_create(n, None if rp is None else _p(rp, i64p), k, _p(ids, i64p), _p(dist, f32p),
+                                                 None if lab is None else _p(lab, i64p), C.byref(self._h)))
+        self.n = n
+
+    def distances(self, start, end) -> np.ndarray:
+        start = np.ascontiguousarray(start, np.int64)
+        end = np.ascontiguousarray(end, np.int64)
+        out = np.zeros(len(start), np.float32)
+        _check(load().sphb_geodesic_distances_g(self._h, _p(start, i64p), _p(end, i64p), len(start), _p(out, f32p)))
+        return out
+
+    def hausdorff(self, comp_ptr, comp_pix, pa, pb) -> np.ndarray:
+        comp_ptr = np.ascontiguousarray(comp_ptr, np.int64)
+        comp_pix = np.ascontiguousarray(comp_pix, np.int64)
+        pa = np.ascontiguousarray(pa, np.int64)
+        pb = np.ascontiguousarray(pb, np.int64)
+        out = np.zeros(len(pa), np.float32)
+        _check(load().sphb_geodesic_hausdorff_g(self._h, len(comp_ptr) - 1, _p(comp_ptr, i64p), _p(comp_pix, i64p), _p(pa, i64p), _p(pb, i64p), len(pa),
+                                                _p(out, f32p)))
+        return out
+
+    def close(self):
+        if self._h:
+            load().sphb_geodesic_graph_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def geodesic_last_stats() -> dict:

@@ -314,13 +314,19 @@ int geo_up(DevBuf<T>& b, const T* h, int64_t count, cudaStream_t s) {
 thread_local int64_t g_geo_stats[4] = {0, 0, 0, 0};  // vertices expanded, passes, searches, sources
 }  // namespace
 
-// Host driver.  comp_ptr == NULL: components are single points (pa / pb are point ids).
-static int geodesic_run(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const int64_t* labels, int64_t ncomp,
-                        const int64_t* comp_ptr, const int64_t* comp_pix, int64_t npairs, const int64_t* pa, const int64_t* pb, int raw, float* out) {
-    const char* who = raw ? "geodesic_distances" : "geodesic_hausdorff";
-    if (int rc = ensure_init()) return rc;
-    if (n <= 0 || n >= (int64_t(1) << 31) || !ids || !dist || (!rowptr && k <= 0) || npairs < 0 || (npairs > 0 && (!pa || !pb || !out)))
-        return fail(SPHB_ERR_INVALID, std::string(who) + ": bad arguments");
+// The kNN graph resident on the device: uploaded and validated once, used by any number of calls (a hierarchy asks for the
+// distances of every level on the same graph; the upload is 121 MB at C2 size, about half of a level-0 call).
+struct GeoGraphDev {
+    int64_t n = 0, nnz = 0;
+    float delta = 1.f;  // bucket width of the searches: the mean positive edge weight
+    bool has_labels = false;
+    DevBuf<int64_t> rowptr, ids, labels;
+    DevBuf<float> dist;
+};
+
+static int geo_graph_upload(GeoGraphDev& g, const char* who, int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist,
+                            const int64_t* labels) {
+    if (n <= 0 || n >= (int64_t(1) << 31) || !ids || !dist || (!rowptr && k <= 0)) return fail(SPHB_ERR_INVALID, std::string(who) + ": bad arguments");
     std::vector<int64_t> rp_own;
     if (!rowptr) {
         rp_own.resize(static_cast<size_t>(n) + 1);
@@ -341,6 +347,26 @@ static int geodesic_run(int64_t n, const int64_t* rowptr, int k, const int64_t* 
             ++wcount;
         }
     }
+    cudaStream_t s = ctx().stream;
+    g.n = n;
+    g.nnz = nnz;
+    g.delta = wcount ? SPHB_GEO_DELTA_MUL * static_cast<float>(wsum / static_cast<double>(wcount)) : 1.f;
+    g.has_labels = labels != nullptr;
+    if (int rc = geo_up(g.rowptr, rowptr, n + 1, s)) return rc;
+    if (int rc = geo_up(g.ids, ids, nnz, s)) return rc;
+    if (int rc = geo_up(g.dist, dist, nnz, s)) return rc;
+    if (labels)
+        if (int rc = geo_up(g.labels, labels, n, s)) return rc;
+    SPHB_CUDA(cudaStreamSynchronize(s));  // rp_own (and the caller's arrays) may go away after the return
+    return SPHB_OK;
+}
+
+// Host driver on a resident graph.  comp_ptr == NULL: components are single points (pa / pb are point ids).
+static int geodesic_pairs(const GeoGraphDev& gr, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, int64_t npairs, const int64_t* pa,
+                          const int64_t* pb, int raw, float* out) {
+    const char* who = raw ? "geodesic_distances" : "geodesic_hausdorff";
+    const int64_t n = gr.n;
+    if (npairs < 0 || (npairs > 0 && (!pa || !pb || !out))) return fail(SPHB_ERR_INVALID, std::string(who) + ": bad arguments");
     if (comp_ptr) {
         if (ncomp <= 0 || comp_ptr[0] != 0) return fail(SPHB_ERR_INVALID, std::string(who) + ": bad component lists");
         for (int64_t c = 0; c < ncomp; ++c)
@@ -383,19 +409,14 @@ static int geodesic_run(int64_t n, const int64_t* rowptr, int k, const int64_t* 
     }
     group_pairs.push_back(npairs);
     const int64_t T = static_cast<int64_t>(task_group.size());
-    const float delta = wcount ? SPHB_GEO_DELTA_MUL * static_cast<float>(wsum / static_cast<double>(wcount)) : 1.f;  // bucket width
+    const float delta = gr.delta;
 
     cudaStream_t s = ctx().stream;
-    DevBuf<int64_t> d_rowptr, d_ids, d_labels, d_cptr, d_cpix, d_pa, d_pb, d_gc, d_gp, d_order, d_roff, d_coff;
-    DevBuf<float> d_dist, d_out;
+    DevBuf<int64_t> d_cptr, d_cpix, d_pa, d_pb, d_gc, d_gp, d_order, d_roff, d_coff;
+    DevBuf<float> d_out;
     DevBuf<int> d_tg, d_tl;
     DevBuf<unsigned> d_rowmin, d_colmin, d_dw, d_bm;
     DevBuf<unsigned long long> d_stats;
-    if (int rc = geo_up(d_rowptr, rowptr, n + 1, s)) return rc;
-    if (int rc = geo_up(d_ids, ids, nnz, s)) return rc;
-    if (int rc = geo_up(d_dist, dist, nnz, s)) return rc;
-    if (labels)
-        if (int rc = geo_up(d_labels, labels, n, s)) return rc;
     if (comp_ptr) {
         if (int rc = geo_up(d_cptr, comp_ptr, ncomp + 1, s)) return rc;
         if (int rc = geo_up(d_cpix, comp_pix, comp_ptr[ncomp], s)) return rc;
@@ -424,7 +445,7 @@ static int geodesic_run(int64_t n, const int64_t* rowptr, int k, const int64_t* 
     const int sms = ctx().num_sms;
     geo_fill_kernel<<<static_cast<unsigned>(std::max<int64_t>(1, std::min<int64_t>((cols + 255) / 256, static_cast<int64_t>(sms) * 8))), 256, 0, s>>>(d_colmin.p, cols, 0xffffffffu);
     count_launch();
-    GeoGraph G{n, d_rowptr.p, d_ids.p, d_dist.p, labels ? d_labels.p : nullptr};
+    GeoGraph G{n, gr.rowptr.p, gr.ids.p, gr.dist.p, gr.has_labels ? gr.labels.p : nullptr};
     GeoComps C{comp_ptr ? d_cptr.p : nullptr, comp_ptr ? d_cpix.p : nullptr};
     GeoTasks K{d_gc.p, d_gp.p, d_order.p, d_pb.p, d_roff.p, d_coff.p, d_tg.p, d_tl.p, T};
     geo_search_kernel<<<static_cast<unsigned>(grid), GEO_THREADS, 0, s>>>(G, C, K, delta, d_dw.p, d_bm.p, d_rowmin.p, d_colmin.p, d_stats.p);
@@ -450,12 +471,49 @@ using namespace sphb;
 extern "C" {
 SPHB_API int sphb_geodesic_hausdorff(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const int64_t* labels, int64_t ncomp,
                                      const int64_t* comp_ptr, const int64_t* comp_pix, const int64_t* pa, const int64_t* pb, int64_t npairs, float* out) {
+    if (int rc = ensure_init()) return rc;
     if (!comp_ptr) return fail(SPHB_ERR_INVALID, "geodesic_hausdorff: bad component lists");
-    return geodesic_run(n, rowptr, k, ids, dist, labels, ncomp, comp_ptr, comp_pix, npairs, pa, pb, 0, out);
+    GeoGraphDev g;
+    if (int rc = geo_graph_upload(g, "geodesic_hausdorff", n, rowptr, k, ids, dist, labels)) return rc;
+    return geodesic_pairs(g, ncomp, comp_ptr, comp_pix, npairs, pa, pb, 0, out);
 }
 SPHB_API int sphb_geodesic_distances(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const int64_t* labels,
                                      const int64_t* start, const int64_t* end, int64_t npairs, float* out) {
-    return geodesic_run(n, rowptr, k, ids, dist, labels, n, nullptr, nullptr, npairs, start, end, 1, out);
+    if (int rc = ensure_init()) return rc;
+    GeoGraphDev g;
+    if (int rc = geo_graph_upload(g, "geodesic_distances", n, rowptr, k, ids, dist, labels)) return rc;
+    return geodesic_pairs(g, n, nullptr, nullptr, npairs, start, end, 1, out);
+}
+// The same two calls on a graph kept on the device between calls (ImageHierarchy asks for the distances of every level on the
+// same data graph).  A handle belongs to the thread (device context) that created it.
+SPHB_API int sphb_geodesic_graph_create(int64_t n, const int64_t* rowptr, int k, const int64_t* ids, const float* dist, const int64_t* labels,
+                                        void** handle) {
+    if (int rc = ensure_init()) return rc;
+    if (!handle) return fail(SPHB_ERR_INVALID, "geodesic_graph_create: null handle");
+    *handle = nullptr;
+    GeoGraphDev* g = new GeoGraphDev();
+    if (int rc = geo_graph_upload(*g, "geodesic_graph_create", n, rowptr, k, ids, dist, labels)) {
+        delete g;
+        return rc;
+    }
+    *handle = g;
+    return SPHB_OK;
+}
+SPHB_API int sphb_geodesic_graph_destroy(void* handle) {
+    delete static_cast<GeoGraphDev*>(handle);
+    return SPHB_OK;
+}
+SPHB_API int sphb_geodesic_hausdorff_g(void* handle, int64_t ncomp, const int64_t* comp_ptr, const int64_t* comp_pix, const int64_t* pa, const int64_t* pb,
+                                       int64_t npairs, float* out) {
+    if (int rc = ensure_init()) return rc;
+    if (!handle || !comp_ptr) return fail(SPHB_ERR_INVALID, "geodesic_hausdorff_g: bad arguments");
+    return geodesic_pairs(*static_cast<GeoGraphDev*>(handle), ncomp, comp_ptr, comp_pix, npairs, pa, pb, 0, out);
+}
+SPHB_API int sphb_geodesic_distances_g(void* handle, const int64_t* start, const int64_t* end, int64_t npairs, float* out) {
+    if (int rc = ensure_init()) return rc;
+    if (!handle) return fail(SPHB_ERR_INVALID, "geodesic_distances_g: bad arguments");
+    const GeoGraphDev& g = *static_cast<GeoGraphDev*>(handle);
+    return geodesic_pairs(g, g.n, nullptr, nullptr, npairs, start, end, 1, out);
 }
 SPHB_API int sphb_geodesic_last_stats(int64_t* out4) {
     if (!out4) return fail(SPHB_ERR_INVALID, "geodesic_last_stats: null output");

@@ -951,7 +951,16 @@ class DeviceOps:
         return capi.euclid_hausdorff(data, comp_ptr, comp_pix, pa, pb)
 
     def geodesic_hausdorff(self, graph, comp_ptr, comp_pix, pa, pb, labels=None) -> np.ndarray:
-        return geodesicDistance(graph, comp_ptr, comp_pix, pa, pb, labels)
+        # the data graph goes to the device once per hierarchy (what _hierarchy.bgraph is to the reference, ImageHierarchy.cpp:427-431)
+        from . import capi
+
+        key = (id(graph), id(labels))
+        if getattr(self, "_geo_key", None) != key:
+            if getattr(self, "_geo_graph", None) is not None:
+                self._geo_graph.close()
+            self._geo_graph = capi.GeodesicGraph(graph.knnIndices, graph.knnDistances, rowptr=getattr(graph, "rowptr", None), labels=labels)
+            self._geo_key = key
+        return self._geo_graph.hausdorff(comp_ptr, comp_pix, pa, pb)
 
 
 def pixelNeighborIDs(num_cols: int, num_rows: int, conn: NeighConnection, pid: int) -> list[int]:

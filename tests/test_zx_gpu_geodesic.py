@@ -147,6 +147,24 @@ def test_larger_graph(capi, oracle):
     assert ok.sum() > 200 and (out[ok] - l2[ok] >= -1e-4).all()  # tests/AStarTest.cpp:160
 
 
+def test_resident_graph_handle_equals_one_shot_calls(capi, oracle):
+    """sphb_geodesic_graph_create: the graph is uploaded once and serves several calls (every level of a hierarchy)."""
+    x = two_blobs(500, 6, 8)
+    ids, dist = knn_graph_l2(x, 9)
+    labels = (np.arange(500) % 7 != 0).astype(np.int64)
+    rng = np.random.default_rng(11)
+    comp_ptr, comp_pix = random_comps(rng, 500, [4, 9, 1, 16, 25])
+    pa = np.array([0, 1, 2, 3, 4, 4], np.int64)
+    pb = np.array([1, 3, 0, 4, 0, 4], np.int64)
+    start, end = rng.integers(0, 500, 100), rng.integers(0, 500, 100)
+    for lab in (None, labels):
+        with capi.GeodesicGraph(ids, dist, labels=lab) as g:
+            for _ in range(2):  # the handle survives a call
+                assert np.array_equal(g.distances(start, end), capi.geodesic_distances(ids, dist, start, end, labels=lab))
+                assert np.array_equal(g.hausdorff(comp_ptr, comp_pix, pa, pb), capi.geodesic_hausdorff(ids, dist, comp_ptr, comp_pix, pa, pb, labels=lab))
+        assert np.array_equal(capi.geodesic_distances(ids, dist, start, end, labels=lab), oracle.shortest_paths(None, ids, dist, start, end, labels=lab))
+
+
 def test_bad_arguments(capi):
     from sph_b200.capi import SphbError
 
