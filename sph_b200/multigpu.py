@@ -116,17 +116,33 @@ class ShardedLevel:
     symmetrise, sphb_level_from_sims_dev) on every rank, so every rank ends with the level's whole P matrix in HBM.  An output row
     needs the whole matrix and nothing of the other output rows: the gathered slabs are bit for bit the one-call result."""
 
-    def __init__(self, rank: int, world: int, group=None):
-        self.rank, self.world, self.group = rank, world, group
+    def __init__(self, rank: int, world: int, group=None, device=None):
+        """device: where the buffers live; default the current CUDA device.  A CPU device is accepted ONLY with the functional CPU
+        emulation build of the library (tests/emu, sphb_version() == -1, where "device" memory is host memory) — that is how the
+        world-size-2 flow of this class is exercised on gloo without GPUs (tests/test_emu_sharded_level.py)."""
+        self.rank, self.world, self.group, self.device = rank, world, group, device
+
+    def _dev(self):
+        import torch
+
+        dev = torch.device(self.device) if self.device is not None else torch.device("cuda", torch.cuda.current_device())
+        if dev.type != "cuda" and capi.load().sphb_version() != -1:
+            raise capi.SphbError("ShardedLevel: CPU tensors are only meaningful with the emulation build of the library")
+        return dev
+
+    def _stream(self, dev):
+        import torch
+
+        return torch.cuda.current_stream().cuda_stream if dev.type == "cuda" else 0
 
     def replicate_csr(self, rowptr, col, val, src: int = 0):
-        """CUDA tensors on rank `src` (anything, e.g. None, elsewhere) -> the same CSR on every rank."""
+        """Tensors on rank `src` (anything, e.g. None, elsewhere) -> the same CSR on every rank."""
         import torch
         import torch.distributed as dist
 
         if self.world == 1:
             return rowptr, col, val
-        dev = torch.device("cuda", torch.cuda.current_device())
+        dev = self._dev()
         meta = torch.zeros(2, dtype=torch.int64, device=dev)
         if self.rank == src:
             meta[0], meta[1] = rowptr.numel(), col.numel()
@@ -148,8 +164,8 @@ class ShardedLevel:
 
         n = rowptr.numel() - 1
         nnz = col.numel()
-        dev = rowptr.device
-        s = torch.cuda.current_stream().cuda_stream
+        dev = self._dev()
+        s = self._stream(dev)
         r0, r1, chunk = slab_bounds(n, self.rank, self.world)
         rows = self.world * chunk
         cols_all = torch.full((rows, k), -1, dtype=torch.int32, device=dev)  # 0xFFFFFFFF padding
