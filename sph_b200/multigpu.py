@@ -116,24 +116,20 @@ class ShardedLevel:
     symmetrise, sphb_level_from_sims_dev) on every rank, so every rank ends with the level's whole P matrix in HBM.  An output row
     needs the whole matrix and nothing of the other output rows: the gathered slabs are bit for bit the one-call result."""
 
-    def __init__(self, rank: int, world: int, group=None, device=None):
-        """device: where the buffers live; default the current CUDA device.  A CPU device is accepted ONLY with the functional CPU
-        emulation build of the library (tests/emu, sphb_version() == -1, where "device" memory is host memory) — that is how the
-        world-size-2 flow of this class is exercised on gloo without GPUs (tests/test_emu_sharded_level.py)."""
-        self.rank, self.world, self.group, self.device = rank, world, group, device
+    def __init__(self, rank: int, world: int, group=None):
+        self.rank, self.world, self.group = rank, world, group
 
     def _dev(self):
+        """Where the buffers live: the current CUDA device.  (tests/test_emu_sharded_level.py overrides _dev / _stream in a subclass
+        to drive the functional CPU emulation build of the library on gloo; the product has no CPU path.)"""
         import torch
 
-        dev = torch.device(self.device) if self.device is not None else torch.device("cuda", torch.cuda.current_device())
-        if dev.type != "cuda" and capi.load().sphb_version() != -1:
-            raise capi.SphbError("ShardedLevel: CPU tensors are only meaningful with the emulation build of the library")
-        return dev
+        return torch.device("cuda", torch.cuda.current_device())
 
     def _stream(self, dev):
         import torch
 
-        return torch.cuda.current_stream().cuda_stream if dev.type == "cuda" else 0
+        return torch.cuda.current_stream().cuda_stream
 
     def replicate_csr(self, rowptr, col, val, src: int = 0):
         """Tensors on rank `src` (anything, e.g. None, elsewhere) -> the same CSR on every rank."""

@@ -33,7 +33,12 @@ assert capi.load().sphb_version() == -1, "this test drives the emulation build o
 capi.init(0)
 n, k, perplexity = 150, 11, 5.0
 rp, c, v = walk_like_rows(n, seed=21, hi=30)
-job = ShardedLevel(rank, world, device="cpu")
+class EmuShardedLevel(ShardedLevel):   # test scaffolding: "device" memory of the emulation build is host memory
+    def _dev(self):
+        return torch.device("cpu")
+    def _stream(self, dev):
+        return 0
+job = EmuShardedLevel(rank, world)
 if rank == 0:
     t = (torch.from_numpy(rp), torch.from_numpy(c.view(np.int32)), torch.from_numpy(v))
 else:
