@@ -120,8 +120,8 @@ class ShardedLevel:
         self.rank, self.world, self.group = rank, world, group
 
     def _dev(self):
-        """Where the buffers live: the current CUDA device.  (tests/test_emu_sharded_level.py overrides _dev / _stream in a subclass
-        to drive the functional CPU emulation build of the library on gloo; the product has no CPU path.)"""
+        """Where the buffers live: the current CUDA device (there is no CPU path; _dev / _stream are separate methods so that a
+        subclass can place the buffers differently)."""
         import torch
 
         return torch.device("cuda", torch.cuda.current_device())
