@@ -15,6 +15,10 @@
 //                     symmetrizeTSNE pinned by tests/UtilsTests.cpp:1143-1221.
 //   Stage C / D:      pinned by the reference goldens listed in
 //                     tests/golden/README.md.
+//   Geodesic (8f-4):  parity UNPINNED against Boost.Graph (absent); pinned to the
+//                     reference's own A* test bar and to scipy's Dijkstra, see
+//                     oracle_geodesic.cpp.
+//   UMAP rows (8f-3): parity UNPINNED (umappp absent), see oracle_prow.cpp.
 #pragma once
 #include <cstdint>
 #include <cstddef>
