@@ -11,7 +11,7 @@
 //   bm[n/32]  one bit per vertex whose distance changed since it was last expanded
 //   loop      scan the bitmap; a flagged vertex u is   dropped   if dist[u] >= bound (the largest tentative distance of a
 //                                                                 target: nothing behind it can improve a target),
-//                                                      deferred  if dist[u] >= thr   (bucket limit, delta-stepping style),
+//                                                      deferred  if dist[u] >  thr   (bucket limit, delta-stepping style),
 //                                                      expanded  otherwise: a warp relaxes its out-edges, 32 per step;
 //             when a pass relaxes nothing up to thr, thr moves to (smallest deferred distance + delta), which always admits
 //             that vertex; the search ends when nothing is flagged any more.
