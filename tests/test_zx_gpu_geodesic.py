@@ -165,6 +165,30 @@ def test_resident_graph_handle_equals_one_shot_calls(capi, oracle):
         assert np.array_equal(capi.geodesic_distances(ids, dist, start, end, labels=lab), oracle.shortest_paths(None, ids, dist, start, end, labels=lab))
 
 
+@pytest.mark.parametrize("sim", ["GEO_CENTROID", "GEO_WALKS"])
+def test_image_hierarchy_geodesic_device_equals_oracle_ops(capi, oracle, sim):
+    """The host merge loop with the geodesic metric (ImageHierarchy::computeDistances -> geodesicDistance, sph/ImageHierarchy.cpp:192-249)
+    on the device ops (resident graph handle, one batched call per level) builds the hierarchy the oracle-backed ops build."""
+    import oracle_lib
+    from sph_b200 import host
+
+    rng = np.random.default_rng(31)
+    x = rng.normal(size=(8 * 6, 5)).astype(np.float32)
+    ids, dist = knn_graph_l2(x, 6)
+    graph = host.Graph(ids, dist)
+    settings = host.ImageHierarchySettings(componentSim=getattr(host.ComponentSim, sim), usePercentile=False)
+    rws = host.RandomWalkSettings(numRandomWalks=8, singleWalkLength=3)
+    a = host.ImageHierarchy(graph, x, 8, 6)
+    a.compute(settings, rws)
+    b = host.ImageHierarchy(graph, x, 8, 6, ops=oracle_lib.OracleOps(oracle))
+    b.compute(settings, rws)
+    assert a.getNumLevels() == b.getNumLevels() >= 3 and a.numComponents == b.numComponents
+    for la, lb in zip(a.parents, b.parents):
+        assert np.array_equal(la, lb)
+    d_a, d_b = a.computeDistances(1), b.computeDistances(1)
+    assert np.array_equal(d_a.knnIndices, d_b.knnIndices) and np.array_equal(d_a.knnDistances, d_b.knnDistances)
+
+
 def test_bad_arguments(capi):
     from sph_b200.capi import SphbError
 
