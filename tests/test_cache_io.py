@@ -220,3 +220,20 @@ def test_host_mirrors_round_trip(capi, tmp_path):
     labels = rng.integers(0, 3, 50).astype(np.int64)
     host.writeCompressedVecToBinary(str(tmp_path / "cc.cache"), labels)
     assert np.array_equal(host.loadCompressedVecFromBinary(str(tmp_path / "cc.cache"), np.int64), labels)
+
+
+def test_committed_liblz4_blocks_decode(capi, tmp_path):
+    """tests/golden/lz4_blocks_liblz4.json: blocks and one whole cache file written by the real liblz4 (make_external_goldens.py);
+    this pin does not need pyarrow at test time."""
+    import base64
+    import hashlib
+    import json
+    from pathlib import Path
+
+    g = json.loads((Path(__file__).parent / "golden" / "lz4_blocks_liblz4.json").read_text())
+    for name, b in g["blocks"].items():
+        data = capi.lz4_decompress(base64.b64decode(b["block_b64"]), b["size"])
+        assert len(data) == b["size"] and hashlib.sha256(data).hexdigest() == b["sha256"], name
+    p = tmp_path / "golden.cache"
+    p.write_bytes(base64.b64decode(g["vec_file"]["file_b64"]))
+    assert np.array_equal(capi.cache_read_vec(p, np.int64), (np.arange(2500, dtype=np.int64) * 7) % 1000)

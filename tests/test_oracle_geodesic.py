@@ -117,3 +117,20 @@ def test_geodesic_hausdorff_matches_definition(oracle, small):
         m = np.array([oracle.shortest_paths(None, ids, dist, np.full(len(b), s), b) for s in a])
         m[m < 0] = np.finfo(np.float32).max
         assert out[p] == max(m.min(1).max(), m.min(0).max())
+
+
+def test_sssp_matches_the_committed_scipy_distances(oracle):
+    """tests/golden/geodesic_scipy_60.json (make_external_goldens.py): an independent Dijkstra, pinned without scipy at test time."""
+    import json
+    from pathlib import Path
+
+    g = json.loads((Path(__file__).parent / "golden" / "geodesic_scipy_60.json").read_text())
+    ids = np.array(g["ids"], np.int64)
+    dist = np.array([[float.fromhex(v) for v in r] for r in g["dist_f32_hex"]], np.float32)
+    for s, row in zip(g["sources"], g["distances"]):
+        got = oracle.sssp(None, ids, dist, s).astype(np.float64)
+        for t, want in enumerate(row):
+            if want is None:
+                assert got[t] == np.finfo(np.float32).max
+            else:
+                assert abs(got[t] - want) <= 2e-6 * max(want, 1.0)
