@@ -225,8 +225,12 @@ __global__ void __launch_bounds__(GEO_THREADS) geo_search_kernel(GeoGraph G, Geo
                                 if (v == u || v < 0 || v >= n) continue;  // createBoostGraph: point != neighbour (AStarBoost.cpp:116)
                                 const float nd = __fadd_rn(du, G.dist[e]);
                                 const unsigned nd_bits = __float_as_uint(nd);
+                                // two filters in front of the L2 atomic (most relaxations fail): a distance at or above the bound can
+                                // improve no target, and a plain load that already shows a smaller or equal distance settles it —
+                                // distances only decrease, so a stale load errs towards doing the atomic
+                                if (nd_bits >= bound_bits || nd_bits >= __ldcg(dist + v)) continue;
                                 const unsigned old = atomicMin(dist + v, nd_bits);
-                                if (nd_bits < old && nd_bits < bound_bits) {
+                                if (nd_bits < old) {
                                     __threadfence();
                                     atomicOr(bm + (v >> 5), 1u << (v & 31));
                                     if (nd <= thr) s_changed = 1u;

@@ -139,9 +139,10 @@ struct Search {
                             if (v == u) continue;
                             const float nd = du + G.w[u * G.k + j];
                             const uint32_t nd_bits = f2u(nd);
+                            if (nd_bits >= bound_bits || nd_bits >= dist[v].load()) continue;  // the two filters in front of the atomic
                             uint32_t old;
                             atomic_min(dist[v], nd_bits, &old);
-                            if (nd_bits < old && nd_bits < bound_bits) {
+                            if (nd_bits < old) {
                                 bm[v >> 5].fetch_or(1u << (v & 31));
                                 if (nd <= thr) changed.store(1);
                                 else atomic_min(minpend, nd_bits);
