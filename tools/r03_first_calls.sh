@@ -19,7 +19,7 @@ two)
   timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29541 \
       tools/level1_sharded_probe.py --workload C2 --out gpurun_out/r03_level1_sharded_g2.json 2>&1 | tail -3
   timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29542 \
-      tools/level1_c4_sharded.py --workload C2 --band-rows 64 --out gpurun_out/r03_level1_c2_sharded_g2.json 2>&1 | tail -3
+      tools/level1_c4_sharded.py --shape 512,216,204,16,1002 --band-rows 64 --out gpurun_out/r03_level1_c2_sharded_g2.json 2>&1 | tail -3
   ;;
 eight)
   # the north_star target: C4 kNN + level-1 similarities + P matrix on 8 GPUs (one GPU: 117 s, tools/level1_c4.py)
